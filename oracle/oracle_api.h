@@ -1,0 +1,94 @@
+// TEST INFRASTRUCTURE ONLY.  Nothing under oracle/ is part of the product; only
+// tests/, __graft_entry__.smoke() and bench.py's CPU-baseline / --impl reference
+// legs may load these libraries.
+//
+// One C API, two implementations:
+//   oracle/_ref/libref_oracle.so   ref_harness.cpp  — the reference's OWN header-only
+//                                  DSP blocks, compiled in place from $REF_ROOT/core/src
+//                                  against oracle/shim (generic-C VOLK stand-in).
+//   oracle/libport_oracle.so       oracle_port.cpp — a self-contained restatement of the
+//                                  same algorithms (no reference includes) that travels
+//                                  to machines where /root/reference does not exist.
+// tests/test_oracle_*.py pin the port against _ref bit-for-bit and both against
+// tests/golden/*.npz.
+//
+// All complex buffers are interleaved float {re, im} (dsp::complex_t, dsp/types.h:93-94);
+// stereo buffers are interleaved {l, r}.  `count` is in samples, not floats.
+#pragma once
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* orc_kind(void); // "reference" or "port"
+
+// ---- dsp::channel::RxVFO (channel/rx_vfo.h:6-135)
+void* orc_vfo_create(double inSR, double outSR, double bandwidth, double offset);
+void orc_vfo_destroy(void* h);
+int orc_vfo_process(void* h, int count, const float* in, float* out); // returns out sample count
+void orc_vfo_set_offset(void* h, double offset);
+void orc_vfo_set_bandwidth(void* h, double bandwidth);
+void orc_vfo_set_in_samplerate(void* h, double inSR);
+void orc_vfo_set_out_samplerate(void* h, double outSR, double bandwidth);
+void orc_vfo_reset(void* h);
+void orc_vfo_get_phase(void* h, float* reim);               // FrequencyXlator::phase (frequency_xlator.h:70)
+void orc_vfo_set_phase(void* h, float re, float im);
+void orc_vfo_get_phase_delta(void* h, float* reim);         // FrequencyXlator::phaseDelta (:71)
+// info[0]=mode (0 BOTH,1 DECIM_ONLY,2 RESAMP_ONLY,3 NONE) [1]=pow2 ratio [2]=interp [3]=decim
+// [4]=resampler tap count [5]=tapsPerPhase [6]=channel-filter tap count (0 when bypassed)
+void orc_vfo_describe(void* h, int* info);
+int orc_vfo_get_resamp_taps(void* h, float* out, int cap);  // RationalResampler::rtaps after *interp
+int orc_vfo_get_chan_taps(void* h, float* out, int cap);    // RxVFO::ftaps
+
+// ---- dsp::multirate::PowerDecimator<complex_t> (multirate/power_decimator.h)
+void* orc_decim_create(int ratio);
+void orc_decim_destroy(void* h);
+int orc_decim_process(void* h, int count, const float* in, float* out);
+// plan introspection: returns stage count; stage s decimation / tap count / taps
+int orc_decim_plan(int ratio, int* decims, int* tapCounts, int cap);
+int orc_decim_stage_taps(int ratio, int stage, float* out, int cap);
+
+// ---- dsp::correction::DCBlocker<complex_t> (correction/dc_blocker.h:54-60), rate as double like IQFrontEnd::genDCBlockRate
+void* orc_dcblock_create(double rate);
+void orc_dcblock_destroy(void* h);
+int orc_dcblock_process(void* h, int count, const float* in, float* out);
+
+// ---- IQFrontEnd pre-processing chain order (signal_path/iq_frontend.cpp:40-44):
+// PowerDecimator -> DCBlocker -> Conjugate, each optional.
+void* orc_preproc_create(double sampleRate, int decimRatio, int dcBlocking, int invertIQ);
+void orc_preproc_destroy(void* h);
+int orc_preproc_process(void* h, int count, const float* in, float* out);
+
+// ---- taps & windows
+int orc_lowpass_taps(double cutoff, double transWidth, double sampleRate, float* out, int cap); // taps/low_pass.h:8-15
+// window type 0 RECT, 1 BLACKMAN, 2 NUTTALL; includes the (-1)^i alternation of updateFFTPath (iq_frontend.cpp:303-311)
+void orc_fft_window(int type, int nz, float* out);
+void orc_reshape_params(double sampleRate, int fftSize, double fftRate, int* skip, int* nz); // iq_frontend.h:88-92
+
+// ---- IQFrontEnd::handler (iq_frontend.cpp:267-287): window -> zero-pad -> forward FFT -> 10log10(|X|^2/N^2)
+// spectrum (optional, may be NULL) receives the N complex FFT outputs (before log).
+void orc_fft_frame(const float* iq, const float* window, int nz, int N, float* outDb, float* spectrum);
+
+// ---- waterfall math (gui/widgets/waterfall.cpp)
+void orc_do_zoom(int offset, int width, int inSize, int outSize, const float* in, float* out);   // :98-154
+void orc_zoom_indices(int offset, int width, int inSize, int outSize, int* sId, int* uFactor);   // the fp32 index walk of :108-152
+void orc_palette_indices(const float* row, int n, float wfMin, float wfMax, int* idx);          // :1229-1235 (index into the 1000-entry LUT)
+void orc_make_palette(const float* colors /*[n][3]*/, int colorCount, unsigned int* lut /*[1000]*/); // updatePallette :1282-1295
+
+// ---- demodulators (stereo_t output, as the radio module instantiates them)
+void* orc_fm_create(double samplerate, double bandwidth, int lowPass, int highPass); // demod/fm.h
+void orc_fm_destroy(void* h);
+int orc_fm_process(void* h, int count, const float* in, float* outStereo);
+void* orc_ssb_create(int mode /*0 USB 1 LSB 2 DSB*/, double bandwidth, double samplerate, double agcAttack, double agcDecay); // demod/ssb.h
+void orc_ssb_destroy(void* h);
+int orc_ssb_process(void* h, int count, const float* in, float* outStereo);
+void* orc_am_create(int agcMode /*0 CARRIER 1 AUDIO*/, double bandwidth, double agcAttack, double agcDecay, double dcBlockRate, double samplerate); // demod/am.h
+void orc_am_destroy(void* h);
+int orc_am_process(void* h, int count, const float* in, float* outStereo);
+// loop::AGC<float> stand-alone (loop/agc.h:85-139)
+void* orc_agc_create(double setPoint, double attack, double decay, double maxGain, double maxOutputAmp, double initGain);
+void orc_agc_destroy(void* h);
+int orc_agc_process(void* h, int count, const float* in, float* out);
+
+#ifdef __cplusplus
+}
+#endif

@@ -1,0 +1,170 @@
+// TEST INFRASTRUCTURE ONLY (oracle). Not linked into the product library.
+//
+// Stand-in for <volk/volk.h>.  VOLK is an un-vendored, un-pinned third-party
+// dependency of the reference (core/CMakeLists.txt:169, pkg_check_modules(VOLK
+// REQUIRED volk)); it is not installed in this image.  This header restates the
+// *generic* (non-SIMD) kernels of VOLK's public API for exactly the call sites
+// on the IQ-front-end path, so that the reference's own header-only DSP blocks
+// compile unchanged against it.  Every routine is plain sequential IEEE fp32
+// (compile with -ffp-contract=off so no FMA contraction sneaks in).
+//
+// Call sites served (reference file:line):
+//   dsp/buffer/buffer.h:20-34                  volk_malloc / volk_free / volk_get_alignment
+//   dsp/channel/frequency_xlator.h:47-51       rotator / rotator2
+//   dsp/filter/fir.h:71-78, decimating_fir.h:53-59, multirate/polyphase_resampler.h:78-81   dot products
+//   dsp/math/conjugate.h:13                    conjugate
+//   signal_path/iq_frontend.cpp:271,282        window multiply, power spectrum
+//   dsp/demod/am.h:109,120                     magnitude
+//   dsp/convert/complex_to_real.h:15, mono_to_stereo.h:13   deinterleave / interleave
+#pragma once
+#include <complex>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <cstdint>
+
+typedef std::complex<float> lv_32fc_t;
+#define lv_cmake(r, i) lv_32fc_t((r), (i))
+#define lv_creal(x) ((x).real())
+#define lv_cimag(x) ((x).imag())
+
+// Pretend to be an old VOLK so frequency_xlator.h picks the by-value rotator
+// (the by-pointer rotator2 of VOLK >= 3.1 has identical arithmetic).
+#ifndef VOLK_VERSION
+#define VOLK_VERSION 020500
+#endif
+
+static inline size_t volk_get_alignment(void) { return 64; }
+static inline void* volk_malloc(size_t size, size_t alignment) {
+    void* p = nullptr;
+    if (size == 0) size = alignment;
+    if (posix_memalign(&p, alignment, size) != 0) return nullptr;
+    return p;
+}
+static inline void volk_free(void* p) { free(p); }
+
+// ---- rotator: out = in * phase; phase *= inc; renormalise every 512 samples
+// and once more after a ragged tail (counters restart on every call).
+static inline void oracle_rotator_core(lv_32fc_t* out, const lv_32fc_t* in, lv_32fc_t inc, lv_32fc_t* phase, unsigned int n) {
+    float pr = phase->real(), pi = phase->imag();
+    const float dr = inc.real(), di = inc.imag();
+    unsigned int done = 0;
+    const unsigned int RELOAD = 512;
+    const unsigned int full = n / RELOAD;
+    for (unsigned int b = 0; b < full; b++) {
+        for (unsigned int j = 0; j < RELOAD; j++, done++) {
+            const float xr = in[done].real(), xi = in[done].imag();
+            out[done] = lv_32fc_t(xr * pr - xi * pi, xr * pi + xi * pr);
+            const float nr = pr * dr - pi * di;
+            const float ni = pr * di + pi * dr;
+            pr = nr; pi = ni;
+        }
+        const float h = hypotf(pr, pi);
+        pr /= h; pi /= h;
+    }
+    unsigned int tail = n % RELOAD;
+    for (unsigned int j = 0; j < tail; j++, done++) {
+        const float xr = in[done].real(), xi = in[done].imag();
+        out[done] = lv_32fc_t(xr * pr - xi * pi, xr * pi + xi * pr);
+        const float nr = pr * dr - pi * di;
+        const float ni = pr * di + pi * dr;
+        pr = nr; pi = ni;
+    }
+    if (tail) {
+        const float h = hypotf(pr, pi);
+        pr /= h; pi /= h;
+    }
+    *phase = lv_32fc_t(pr, pi);
+}
+static inline void volk_32fc_s32fc_x2_rotator_32fc(lv_32fc_t* out, const lv_32fc_t* in, lv_32fc_t inc, lv_32fc_t* phase, unsigned int n) {
+    oracle_rotator_core(out, in, inc, phase, n);
+}
+static inline void volk_32fc_s32fc_x2_rotator2_32fc(lv_32fc_t* out, const lv_32fc_t* in, const lv_32fc_t* inc, lv_32fc_t* phase, unsigned int n) {
+    oracle_rotator_core(out, in, *inc, phase, n);
+}
+
+// ---- dot products: one running fp32 sum per component, in index order
+static inline void volk_32fc_32f_dot_prod_32fc(lv_32fc_t* result, const lv_32fc_t* x, const float* taps, unsigned int n) {
+    float sr = 0.0f, si = 0.0f;
+    const float* p = reinterpret_cast<const float*>(x);
+    for (unsigned int i = 0; i < n; i++) {
+        sr += p[2 * i] * taps[i];
+        si += p[2 * i + 1] * taps[i];
+    }
+    *result = lv_32fc_t(sr, si);
+}
+static inline void volk_32f_x2_dot_prod_32f(float* result, const float* a, const float* b, unsigned int n) {
+    float s = 0.0f;
+    for (unsigned int i = 0; i < n; i++) { s += a[i] * b[i]; }
+    *result = s;
+}
+static inline void volk_32fc_x2_dot_prod_32fc(lv_32fc_t* result, const lv_32fc_t* a, const lv_32fc_t* b, unsigned int n) {
+    float sr = 0.0f, si = 0.0f;
+    for (unsigned int i = 0; i < n; i++) {
+        const float ar = a[i].real(), ai = a[i].imag(), br = b[i].real(), bi = b[i].imag();
+        sr += ar * br - ai * bi;
+        si += ar * bi + ai * br;
+    }
+    *result = lv_32fc_t(sr, si);
+}
+
+// ---- element-wise helpers
+static inline void volk_32fc_conjugate_32fc(lv_32fc_t* out, const lv_32fc_t* in, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = lv_32fc_t(in[i].real(), -in[i].imag()); }
+}
+static inline void volk_32fc_32f_multiply_32fc(lv_32fc_t* out, const lv_32fc_t* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = lv_32fc_t(a[i].real() * b[i], a[i].imag() * b[i]); }
+}
+static inline void volk_32fc_x2_multiply_32fc(lv_32fc_t* out, const lv_32fc_t* a, const lv_32fc_t* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) {
+        const float ar = a[i].real(), ai = a[i].imag(), br = b[i].real(), bi = b[i].imag();
+        out[i] = lv_32fc_t(ar * br - ai * bi, ar * bi + ai * br);
+    }
+}
+static inline void volk_32fc_magnitude_32f(float* out, const lv_32fc_t* in, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) {
+        const float r = in[i].real(), q = in[i].imag();
+        out[i] = sqrtf(r * r + q * q);
+    }
+}
+static inline void volk_32fc_deinterleave_real_32f(float* out, const lv_32fc_t* in, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = in[i].real(); }
+}
+static inline void volk_32f_x2_interleave_32fc(lv_32fc_t* out, const float* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = lv_32fc_t(a[i], b[i]); }
+}
+static inline void volk_32f_s32f_multiply_32f(float* out, const float* a, float s, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = a[i] * s; }
+}
+static inline void volk_32f_x2_add_32f(float* out, const float* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = a[i] + b[i]; }
+}
+static inline void volk_32f_x2_subtract_32f(float* out, const float* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = a[i] - b[i]; }
+}
+static inline void volk_32f_x2_multiply_32f(float* out, const float* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = a[i] * b[i]; }
+}
+static inline void volk_32f_accumulator_s32f(float* result, const float* in, unsigned int n) {
+    float s = 0.0f;
+    for (unsigned int i = 0; i < n; i++) { s += in[i]; }
+    *result = s;
+}
+static inline void volk_16i_s32f_convert_32f(float* out, const int16_t* in, float scalar, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = (float)in[i] / scalar; }
+}
+
+// ---- power spectrum: 10*log10(|x/norm|^2) done as (10/log2(10)) * log2f(.)
+// with log2 of zero/inf clamped to -/+127 (so an all-zero bin reads ~ -382.3 dB).
+static inline float oracle_log2f_clamped(float v) {
+    const float r = log2f(v);
+    return std::isinf(r) ? copysignf(127.0f, r) : r;
+}
+static inline void volk_32fc_s32f_power_spectrum_32f(float* out, const lv_32fc_t* in, float norm, unsigned int n) {
+    const float inv = 1.0f / norm;
+    for (unsigned int i = 0; i < n; i++) {
+        const float r = in[i].real() * inv;
+        const float q = in[i].imag() * inv;
+        out[i] = 3.01029995663981209120f * oracle_log2f_clamped(r * r + q * q);
+    }
+}

@@ -1,0 +1,280 @@
+"""ctypes binding of oracle/oracle_api.h (TEST INFRASTRUCTURE — checker only).
+
+Two builds export the same API:
+  * ``port``: oracle/libport_oracle.so — self-contained restatement, builds anywhere.
+  * ``ref`` : oracle/_ref/libref_oracle.so — the reference's own headers compiled in
+    place (needs /root/reference at build time; the built .so travels to the GPU box).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+PORT_SO = os.path.join(ORACLE_DIR, "libport_oracle.so")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libref_oracle.so")
+REF_ROOT = os.environ.get("REF_ROOT", "/root/reference")
+
+_vp, _i, _d, _f = C.c_void_p, C.c_int, C.c_double, C.c_float
+
+_SIGS = {
+    "orc_kind": (C.c_char_p, []),
+    "orc_vfo_create": (_vp, [_d, _d, _d, _d]),
+    "orc_vfo_destroy": (None, [_vp]),
+    "orc_vfo_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_vfo_set_offset": (None, [_vp, _d]),
+    "orc_vfo_set_bandwidth": (None, [_vp, _d]),
+    "orc_vfo_set_in_samplerate": (None, [_vp, _d]),
+    "orc_vfo_set_out_samplerate": (None, [_vp, _d, _d]),
+    "orc_vfo_reset": (None, [_vp]),
+    "orc_vfo_get_phase": (None, [_vp, _vp]),
+    "orc_vfo_set_phase": (None, [_vp, _f, _f]),
+    "orc_vfo_get_phase_delta": (None, [_vp, _vp]),
+    "orc_vfo_describe": (None, [_vp, _vp]),
+    "orc_vfo_get_resamp_taps": (_i, [_vp, _vp, _i]),
+    "orc_vfo_get_chan_taps": (_i, [_vp, _vp, _i]),
+    "orc_decim_create": (_vp, [_i]),
+    "orc_decim_destroy": (None, [_vp]),
+    "orc_decim_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_decim_plan": (_i, [_i, _vp, _vp, _i]),
+    "orc_decim_stage_taps": (_i, [_i, _i, _vp, _i]),
+    "orc_dcblock_create": (_vp, [_d]),
+    "orc_dcblock_destroy": (None, [_vp]),
+    "orc_dcblock_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_preproc_create": (_vp, [_d, _i, _i, _i]),
+    "orc_preproc_destroy": (None, [_vp]),
+    "orc_preproc_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_lowpass_taps": (_i, [_d, _d, _d, _vp, _i]),
+    "orc_fft_window": (None, [_i, _i, _vp]),
+    "orc_reshape_params": (None, [_d, _i, _d, _vp, _vp]),
+    "orc_fft_frame": (None, [_vp, _vp, _i, _i, _vp, _vp]),
+    "orc_do_zoom": (None, [_i, _i, _i, _i, _vp, _vp]),
+    "orc_zoom_indices": (None, [_i, _i, _i, _i, _vp, _vp]),
+    "orc_palette_indices": (None, [_vp, _i, _f, _f, _vp]),
+    "orc_make_palette": (None, [_vp, _i, _vp]),
+    "orc_fm_create": (_vp, [_d, _d, _i, _i]),
+    "orc_fm_destroy": (None, [_vp]),
+    "orc_fm_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_ssb_create": (_vp, [_i, _d, _d, _d, _d]),
+    "orc_ssb_destroy": (None, [_vp]),
+    "orc_ssb_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_am_create": (_vp, [_i, _d, _d, _d, _d, _d]),
+    "orc_am_destroy": (None, [_vp]),
+    "orc_am_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_agc_create": (_vp, [_d, _d, _d, _d, _d, _d]),
+    "orc_agc_destroy": (None, [_vp]),
+    "orc_agc_process": (_i, [_vp, _i, _vp, _vp]),
+}
+
+
+def build(which="port"):
+    """Compile the oracle library if its .so is missing (or stale for the port)."""
+    if which == "port":
+        subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "port"])
+        return PORT_SO
+    if os.path.isdir(os.path.join(REF_ROOT, "core", "src", "dsp")):
+        subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "ref", "REF_ROOT=" + REF_ROOT])
+    return REF_SO if os.path.exists(REF_SO) else None
+
+
+class Oracle:
+    def __init__(self, which="port"):
+        path = build(which)
+        if path is None or not os.path.exists(path):
+            raise FileNotFoundError("oracle library '%s' is not built and cannot be built here" % which)
+        self.lib = C.CDLL(path)
+        for name, (res, args) in _SIGS.items():
+            fn = getattr(self.lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        self.kind = self.lib.orc_kind().decode()
+
+    # ------------------------------------------------------------ helpers
+    @staticmethod
+    def _c(a):
+        a = np.ascontiguousarray(a)
+        return a, a.ctypes.data
+
+    def lowpass(self, cutoff, trans, sr):
+        n = self.lib.orc_lowpass_taps(cutoff, trans, sr, None, 0)
+        out = np.zeros(n, np.float32)
+        self.lib.orc_lowpass_taps(cutoff, trans, sr, out.ctypes.data, n)
+        return out
+
+    def fft_window(self, wtype, nz):
+        out = np.zeros(nz, np.float32)
+        self.lib.orc_fft_window(wtype, nz, out.ctypes.data)
+        return out
+
+    def reshape_params(self, sr, size, rate):
+        skip, nz = C.c_int(), C.c_int()
+        self.lib.orc_reshape_params(sr, size, rate, C.addressof(skip), C.addressof(nz))
+        return skip.value, nz.value
+
+    def fft_frame(self, iq, window, N, want_spectrum=False):
+        iq = np.ascontiguousarray(iq, np.complex64)
+        window = np.ascontiguousarray(window, np.float32)
+        nz = len(window)
+        db = np.zeros(N, np.float32)
+        spec = np.zeros(N, np.complex64) if want_spectrum else None
+        self.lib.orc_fft_frame(iq.ctypes.data, window.ctypes.data, nz, N, db.ctypes.data, spec.ctypes.data if want_spectrum else None)
+        return (db, spec) if want_spectrum else db
+
+    def do_zoom(self, offset, width, row, out_size):
+        row = np.ascontiguousarray(row, np.float32)
+        out = np.zeros(out_size, np.float32)
+        self.lib.orc_do_zoom(offset, width, len(row), out_size, row.ctypes.data, out.ctypes.data)
+        return out
+
+    def zoom_indices(self, offset, width, in_size, out_size):
+        s = np.zeros(out_size, np.int32)
+        u = np.zeros(out_size, np.int32)
+        self.lib.orc_zoom_indices(offset, width, in_size, out_size, s.ctypes.data, u.ctypes.data)
+        return s, u
+
+    def palette_indices(self, row, wf_min, wf_max):
+        row = np.ascontiguousarray(row, np.float32)
+        idx = np.zeros(len(row), np.int32)
+        self.lib.orc_palette_indices(row.ctypes.data, len(row), wf_min, wf_max, idx.ctypes.data)
+        return idx
+
+    def make_palette(self, colors):
+        colors = np.ascontiguousarray(colors, np.float32)
+        lut = np.zeros(1000, np.uint32)
+        self.lib.orc_make_palette(colors.ctypes.data, colors.shape[0], lut.ctypes.data)
+        return lut
+
+    def decim_plan(self, ratio):
+        d = np.zeros(8, np.int32)
+        t = np.zeros(8, np.int32)
+        n = self.lib.orc_decim_plan(ratio, d.ctypes.data, t.ctypes.data, 8)
+        taps = []
+        for s in range(n):
+            buf = np.zeros(t[s], np.float32)
+            self.lib.orc_decim_stage_taps(ratio, s, buf.ctypes.data, int(t[s]))
+            taps.append(buf)
+        return [(int(d[s]), taps[s]) for s in range(n)]
+
+
+class _Block:
+    """Streaming block wrapper: process(block) -> output array, state kept in the oracle."""
+    out_dtype = np.complex64
+    out_per_in = 1.0
+
+    def __init__(self, orc, handle, prefix):
+        self.orc, self.h, self.prefix = orc, handle, prefix
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(int(len(x) * self.out_per_in) + 1024, self.out_dtype)
+        n = getattr(self.orc.lib, self.prefix + "_process")(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:n].copy()
+
+    def close(self):
+        if self.h:
+            getattr(self.orc.lib, self.prefix + "_destroy")(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Vfo(_Block):
+    def __init__(self, orc, in_sr, out_sr, bw, offset):
+        self.out_per_in = max(1.0, 1.05 * out_sr / in_sr)
+        super().__init__(orc, orc.lib.orc_vfo_create(in_sr, out_sr, bw, offset), "orc_vfo")
+
+    def describe(self):
+        info = np.zeros(7, np.int32)
+        self.orc.lib.orc_vfo_describe(self.h, info.ctypes.data)
+        return dict(mode=int(info[0]), ratio=int(info[1]), interp=int(info[2]), decim=int(info[3]),
+                    resamp_taps=int(info[4]), taps_per_phase=int(info[5]), chan_taps=int(info[6]))
+
+    def phase(self):
+        p = np.zeros(2, np.float32)
+        self.orc.lib.orc_vfo_get_phase(self.h, p.ctypes.data)
+        return complex(p[0], p[1])
+
+    def set_phase(self, z):
+        self.orc.lib.orc_vfo_set_phase(self.h, float(np.float32(z.real)), float(np.float32(z.imag)))
+
+    def phase_delta(self):
+        p = np.zeros(2, np.float32)
+        self.orc.lib.orc_vfo_get_phase_delta(self.h, p.ctypes.data)
+        return complex(p[0], p[1])
+
+    def resamp_taps(self):
+        n = self.orc.lib.orc_vfo_get_resamp_taps(self.h, None, 0)
+        out = np.zeros(n, np.float32)
+        self.orc.lib.orc_vfo_get_resamp_taps(self.h, out.ctypes.data, n)
+        return out
+
+    def chan_taps(self):
+        n = self.orc.lib.orc_vfo_get_chan_taps(self.h, None, 0)
+        out = np.zeros(n, np.float32)
+        self.orc.lib.orc_vfo_get_chan_taps(self.h, out.ctypes.data, n)
+        return out
+
+    def set_offset(self, v): self.orc.lib.orc_vfo_set_offset(self.h, v)
+    def set_bandwidth(self, v): self.orc.lib.orc_vfo_set_bandwidth(self.h, v)
+    def set_in_samplerate(self, v): self.orc.lib.orc_vfo_set_in_samplerate(self.h, v)
+    def set_out_samplerate(self, sr, bw): self.orc.lib.orc_vfo_set_out_samplerate(self.h, sr, bw)
+    def reset(self): self.orc.lib.orc_vfo_reset(self.h)
+
+
+class Decim(_Block):
+    def __init__(self, orc, ratio):
+        super().__init__(orc, orc.lib.orc_decim_create(ratio), "orc_decim")
+
+
+class DcBlock(_Block):
+    def __init__(self, orc, rate):
+        super().__init__(orc, orc.lib.orc_dcblock_create(rate), "orc_dcblock")
+
+
+class Preproc(_Block):
+    def __init__(self, orc, sr, decim, dc, invert):
+        super().__init__(orc, orc.lib.orc_preproc_create(sr, decim, int(dc), int(invert)), "orc_preproc")
+
+
+class _Demod(_Block):
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros((len(x) + 16, 2), np.float32)
+        n = getattr(self.orc.lib, self.prefix + "_process")(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:n].copy()
+
+
+class Fm(_Demod):
+    def __init__(self, orc, sr, bw, low_pass=True, high_pass=False):
+        super().__init__(orc, orc.lib.orc_fm_create(sr, bw, int(low_pass), int(high_pass)), "orc_fm")
+
+
+class Ssb(_Demod):
+    def __init__(self, orc, mode, bw, sr, attack, decay):
+        super().__init__(orc, orc.lib.orc_ssb_create(mode, bw, sr, attack, decay), "orc_ssb")
+
+
+class Am(_Demod):
+    def __init__(self, orc, agc_mode, bw, attack, decay, dc_rate, sr):
+        super().__init__(orc, orc.lib.orc_am_create(agc_mode, bw, attack, decay, dc_rate, sr), "orc_am")
+
+
+class Agc(_Block):
+    def __init__(self, orc, set_point, attack, decay, max_gain, max_out, init_gain):
+        super().__init__(orc, orc.lib.orc_agc_create(set_point, attack, decay, max_gain, max_out, init_gain), "orc_agc")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.zeros(len(x), np.float32)
+        self.orc.lib.orc_agc_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out
+
+
+def have_ref():
+    return os.path.exists(REF_SO) or os.path.isdir(os.path.join(REF_ROOT, "core", "src", "dsp"))

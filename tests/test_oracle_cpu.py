@@ -1,0 +1,199 @@
+"""CPU tests of the oracle itself: the self-contained port (oracle/oracle_port.cpp) is pinned
+bit-for-bit against the reference's own headers compiled in place (oracle/_ref) whenever that
+library is available, and both are pinned against the committed vectors in tests/golden/."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from sdrplusplusbrown_b200 import synth
+
+PORT = ol.Oracle("port")
+REF = ol.Oracle("ref") if ol.have_ref() else None
+needs_ref = pytest.mark.skipif(REF is None, reason="oracle/_ref not built and /root/reference absent")
+
+VFO_CASES = [
+    # in_sr, out_sr, bw, offset, n
+    (2.4e6, 50e3, 12.5e3, 100e3, 60000),        # cfg1 NFM: /32 then 2/3, 304-tap FIR
+    (20e6, 24e3, 2.8e3, 1.25e6, 300000),        # cfg2 USB: /512 then 8000/13021
+    (61.44e6, 48e3, 12.5e3, -3.3e6, 300000),    # cfg3 NFM: /1024 then 4/5
+    (122.88e6, 15e3, 10e3, 7.7e6, 400000),      # cfg4 AM: /8192 DECIM_ONLY
+    (122.88e6, 500e3, 150e3, -20e6, 100000),    # cfg4 WFM: /128 then 25/48
+    (48e3, 48e3, 48e3, 1e3, 5000),              # NONE mode, filter bypassed (bw == outSR)
+    (24e3, 48e3, 12e3, 500.0, 5000),            # RESAMP_ONLY (interpolating)
+]
+
+
+def _split(x, sizes):
+    out, i, k = [], 0, 0
+    while i < len(x):
+        n = sizes[k % len(sizes)]
+        out.append(x[i:i + n])
+        i += n
+        k += 1
+    return out
+
+
+@needs_ref
+def test_decim_plans_port_equals_ref():
+    for k in range(1, 14):
+        p, r = PORT.decim_plan(1 << k), REF.decim_plan(1 << k)
+        assert len(p) == len(r) > 0
+        for (dp, tp), (dr, tr) in zip(p, r):
+            assert dp == dr
+            assert np.array_equal(tp.view(np.uint32), tr.view(np.uint32))
+
+
+@needs_ref
+def test_taps_and_windows_port_equals_ref():
+    for args in [(6250.0, 625.0, 50e3), (1400.0, 140.0, 24e3), (24000.0, 2400.0, 240000.0), (0.25, 0.1, 1.0)]:
+        a, b = PORT.lowpass(*args), REF.lowpass(*args)
+        assert len(a) == len(b) and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    for wt in (0, 1, 2):
+        for nz in (8192, 12000, 65536):
+            a, b = PORT.fft_window(wt, nz), REF.fft_window(wt, nz)
+            assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    for sr, size, rate in [(2.4e6, 8192, 20.0), (20e6, 65536, 60.0), (122.88e6, 1 << 20, 60.0), (48e3, 65536, 20.0)]:
+        assert PORT.reshape_params(sr, size, rate) == REF.reshape_params(sr, size, rate)
+
+
+@needs_ref
+@pytest.mark.parametrize("case", VFO_CASES)
+def test_vfo_port_equals_ref_bitwise(case):
+    in_sr, out_sr, bw, off, n = case
+    x = synth.make_iq(0, n, in_sr, tones=[(off + 300.0, 0.05)])
+    vp, vr = ol.Vfo(PORT, in_sr, out_sr, bw, off), ol.Vfo(REF, in_sr, out_sr, bw, off)
+    assert vp.describe() == vr.describe()
+    assert np.array_equal(vp.resamp_taps().view(np.uint32), vr.resamp_taps().view(np.uint32))
+    assert np.array_equal(vp.chan_taps().view(np.uint32), vr.chan_taps().view(np.uint32))
+    for blk in _split(x, [12000, 7777, 333, 65536]):
+        a, b = vp.process(blk), vr.process(blk)
+        assert len(a) == len(b)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        assert vp.phase() == vr.phase()
+
+
+def test_vfo_counts_are_chunk_invariant():
+    # 3 M samples 61.44M -> 48k give the same total count for any block partition
+    in_sr, out_sr, bw, off = 61.44e6, 48e3, 12.5e3, 2.0e6
+    n = 600000
+    x = synth.make_iq(0, n, in_sr)
+    totals = []
+    for sizes in ([n], [65536], [12000], [7777], [333, 100001]):
+        v = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+        totals.append(sum(len(v.process(b)) for b in _split(x, sizes)))
+    assert len(set(totals)) == 1
+
+
+@needs_ref
+def test_vfo_reconfigure_port_equals_ref():
+    in_sr = 2.4e6
+    x = synth.make_iq(0, 96000, in_sr, tones=[(100e3, 0.1)])
+    vp, vr = ol.Vfo(PORT, in_sr, 50e3, 12.5e3, 100e3), ol.Vfo(REF, in_sr, 50e3, 12.5e3, 100e3)
+    blocks = _split(x, [12000])
+    for i, blk in enumerate(blocks):
+        if i == 2:
+            vp.set_offset(-50e3); vr.set_offset(-50e3)
+        if i == 3:
+            vp.set_bandwidth(8000.0); vr.set_bandwidth(8000.0)
+        if i == 4:
+            vp.set_out_samplerate(24e3, 2.8e3); vr.set_out_samplerate(24e3, 2.8e3)
+        if i == 5:
+            vp.set_bandwidth(24e3); vr.set_bandwidth(24e3)   # filter bypass
+        if i == 6:
+            vp.reset(); vr.reset()
+        if i == 7:
+            vp.set_in_samplerate(1.2e6); vr.set_in_samplerate(1.2e6)
+        a, b = vp.process(blk), vr.process(blk)
+        assert len(a) == len(b), i
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), i
+
+
+@needs_ref
+def test_preproc_dcblock_decim_port_equals_ref():
+    x = synth.make_iq(0, 50000, 8e6)
+    for dec, dc, inv in [(1, 1, 0), (4, 1, 1), (16, 0, 0), (2, 1, 0), (1, 0, 1)]:
+        p, r = ol.Preproc(PORT, 8e6, dec, dc, inv), ol.Preproc(REF, 8e6, dec, dc, inv)
+        for blk in _split(x, [12000, 5001]):
+            a, b = p.process(blk), r.process(blk)
+            assert len(a) == len(b) and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    for ratio in (2, 8, 64, 2048):
+        p, r = ol.Decim(PORT, ratio), ol.Decim(REF, ratio)
+        for blk in _split(x, [20000, 4999]):
+            a, b = p.process(blk), r.process(blk)
+            assert len(a) == len(b) and np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+@needs_ref
+def test_demods_port_equals_ref():
+    x = synth.make_iq(0, 20000, 50e3, sigma=0.02, tones=[(1000.0, 0.3)])
+    x[5000:5010] = 0   # exercise the AGC's inAmp == 0 branch
+    pairs = [
+        (ol.Fm(PORT, 50e3, 12.5e3), ol.Fm(REF, 50e3, 12.5e3)),
+        (ol.Fm(PORT, 50e3, 12.5e3, False, False), ol.Fm(REF, 50e3, 12.5e3, False, False)),
+        (ol.Fm(PORT, 50e3, 12.5e3, True, True), ol.Fm(REF, 50e3, 12.5e3, True, True)),
+        (ol.Fm(PORT, 50e3, 12.5e3, False, True), ol.Fm(REF, 50e3, 12.5e3, False, True)),
+        (ol.Ssb(PORT, 0, 2800.0, 24e3, 50.0 / 24e3, 5.0 / 24e3), ol.Ssb(REF, 0, 2800.0, 24e3, 50.0 / 24e3, 5.0 / 24e3)),
+        (ol.Ssb(PORT, 1, 2800.0, 24e3, 50.0 / 24e3, 5.0 / 24e3), ol.Ssb(REF, 1, 2800.0, 24e3, 50.0 / 24e3, 5.0 / 24e3)),
+        (ol.Am(PORT, 1, 10e3, 50.0 / 15e3, 5.0 / 15e3, 100.0 / 15e3, 15e3), ol.Am(REF, 1, 10e3, 50.0 / 15e3, 5.0 / 15e3, 100.0 / 15e3, 15e3)),
+        (ol.Am(PORT, 0, 10e3, 50.0 / 15e3, 5.0 / 15e3, 100.0 / 15e3, 15e3), ol.Am(REF, 0, 10e3, 50.0 / 15e3, 5.0 / 15e3, 100.0 / 15e3, 15e3)),
+    ]
+    for p, r in pairs:
+        for blk in _split(x, [4800, 333, 7000]):
+            a, b = p.process(blk), r.process(blk)
+            assert a.shape == b.shape and np.array_equal(a.view(np.uint32), b.view(np.uint32)), type(p)
+
+
+def test_fft_frame_against_numpy_float64():
+    # second opinion: numpy float64 FFT of the fp32-windowed frame
+    for N, nz, wt in [(8192, 8192, 2), (65536, 65536, 1), (1024, 600, 0)]:
+        x = synth.make_iq(0, nz, 2.4e6, tones=[(300e3, 0.2)])
+        w = PORT.fft_window(wt, nz)
+        db, spec = PORT.fft_frame(x, w, N, want_spectrum=True)
+        xw = np.zeros(N, np.complex128)
+        xw[:nz] = (x.real * w).astype(np.float32) + 1j * (x.imag * w).astype(np.float32)
+        ref = np.fft.fft(xw)
+        err = np.sqrt(np.mean(np.abs(spec - ref) ** 2) / np.mean(np.abs(ref) ** 2))
+        assert err < 1e-6      # fp32 narrowing only
+        ref_db = 10 * np.log10(np.abs(ref / N) ** 2 + 1e-300)
+        assert np.max(np.abs(db - ref_db)) < 1e-3
+    # an exactly-zero bin reads the clamped floor, not -inf (VOLK generic log2 clamp)
+    db = PORT.fft_frame(np.zeros(64, np.complex64), np.ones(64, np.float32), 64)
+    assert np.all(np.isfinite(db)) and np.allclose(db, -382.3, atol=0.1)
+
+
+def test_zoom_and_palette_properties():
+    rng = np.random.default_rng(3)
+    row = rng.uniform(-120, -20, 65536).astype(np.float32)
+    out = PORT.do_zoom(1000, 40000, row, 1333)
+    s, u = PORT.zoom_indices(1000, 40000, 65536, 1333)
+    assert s[0] == 1000 and np.all(np.diff(s) >= 0) and np.all(u >= 1)
+    ref = np.array([row[a:a + b].max() for a, b in zip(s, u)], np.float32)
+    assert np.array_equal(out, ref)
+    idx = PORT.palette_indices(out, -100.0, -30.0)
+    assert idx.min() >= 0 and idx.max() <= 999
+    lut = PORT.make_palette(np.array([[0, 0, 32], [0, 0, 255], [255, 255, 0], [255, 0, 0]], np.float32))
+    assert lut.shape == (1000,) and np.all((lut >> 24) == 255)
+
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _golden_files():
+    if not os.path.isdir(GOLDEN_DIR):
+        return []
+    return sorted(f for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+
+
+@pytest.mark.parametrize("fname", _golden_files())
+def test_oracles_match_golden(fname):
+    import golden_cases
+    g = np.load(os.path.join(GOLDEN_DIR, fname))
+    for orc in [PORT] + ([REF] if REF is not None else []):
+        got = golden_cases.run_case(orc, fname[:-4])
+        assert set(got.keys()) == set(g.files)
+        for k in g.files:
+            a, b = np.asarray(got[k]), g[k]
+            assert a.shape == b.shape and a.dtype == b.dtype, (fname, k, orc.kind)
+            assert a.tobytes() == b.tobytes(), (fname, k, orc.kind)
