@@ -1,0 +1,190 @@
+/*
+ * b200dsp.h — C ABI of libb200dsp.so: SDR++Brown's IQ-front-end hot path on NVIDIA B200 (sm_100a).
+ *
+ * The reference has no C ABI for this path; its boundary is the C++ classes
+ * IQFrontEnd (core/src/signal_path/iq_frontend.h:18-135) and dsp::channel::RxVFO
+ * (core/src/dsp/channel/rx_vfo.h:6-135) plus the radio demodulators they feed.  Each entry
+ * point below names the reference member it replaces.  include/dsp/ holds header-compatible
+ * C++ classes (same names, same signatures) that sit on top of this ABI; INTEGRATION.md shows
+ * the binding a maintainer would add.
+ *
+ * Conventions
+ *   - Complex samples are interleaved float {re, im} (dsp::complex_t, dsp/types.h:93-94);
+ *     stereo samples are interleaved {l, r}.  Counts are in samples.
+ *   - Every function returns 0 (B200_OK) or a negative B200_E* code; no exception crosses the ABI.
+ *     b200_last_error() returns a thread-local message for the last failure.
+ *   - "device" pointers are CUDA device pointers on the handle's device.  `stream` is a
+ *     cudaStream_t passed as void* (NULL = the legacy default stream).  Work is stream-ordered;
+ *     one submitting thread per handle.  Setters may be called between process calls and take
+ *     effect at the next block boundary, in call order (the reference applies them under
+ *     ctrlMtx between blocks: rx_vfo.h:35-87).
+ *   - All DSP state (FIR histories, decimation offsets, resampler phase, rotator phase, framing
+ *     position, AGC state) lives in the handle, so any partition of a stream into blocks yields
+ *     identical sample counts and decimation phase as the reference, bit for bit.
+ *   - There is no CPU fallback: every process call runs CUDA kernels or fails.
+ */
+#ifndef B200DSP_H
+#define B200DSP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_OK 0
+#define B200_EINVAL (-1)   /* bad argument (NULL handle, bad index, unsupported size ...) */
+#define B200_ECUDA (-2)    /* a CUDA runtime call failed; see b200_last_error() */
+#define B200_ENOMEM (-3)   /* host or device allocation failed */
+#define B200_ESTATE (-4)   /* call not valid in the handle's current state */
+#define B200_ETOOBIG (-5)  /* block larger than the handle's max_block / a static limit */
+
+const char* b200_last_error(void);
+const char* b200_version(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+uint64_t b200_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------
+ * RxVFO bank — replaces N instances of dsp::channel::RxVFO (channel/rx_vfo.h) fed by the same
+ * Splitter output (routing/splitter.h:59-92).  One launch sequence serves every VFO of the bank.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_vfo_bank b200_vfo_bank;
+
+/* max_block: largest `count` a process call may carry (the reference's streams carry at most
+ * STREAM_BUFFER_SIZE = 1 000 000, dsp/stream.h:14; larger blocks are allowed here). */
+int b200_vfo_bank_create(b200_vfo_bank** out, double in_samplerate, int max_block, int device);
+int b200_vfo_bank_destroy(b200_vfo_bank* bank);
+
+/* RxVFO::RxVFO(in, inSamplerate, outSamplerate, bandwidth, offset) — rx_vfo.h:11,19-33.
+ * Returns the VFO's index (>= 0) or a negative error. */
+int b200_vfo_bank_add(b200_vfo_bank* bank, double out_samplerate, double bandwidth, double offset);
+/* IQFrontEnd::removeVFO — iq_frontend.cpp:181-202.  Indices of other VFOs do not change. */
+int b200_vfo_bank_remove(b200_vfo_bank* bank, int vfo);
+int b200_vfo_bank_count(b200_vfo_bank* bank);   /* number of live VFOs */
+
+int b200_vfo_set_offset(b200_vfo_bank* bank, int vfo, double offset);                          /* RxVFO::setOffset        rx_vfo.h:72-77 */
+int b200_vfo_set_bandwidth(b200_vfo_bank* bank, int vfo, double bandwidth);                    /* RxVFO::setBandwidth     rx_vfo.h:60-70 */
+int b200_vfo_set_out_samplerate(b200_vfo_bank* bank, int vfo, double out_sr, double bandwidth);/* RxVFO::setOutSamplerate rx_vfo.h:45-58 */
+int b200_vfo_bank_set_in_samplerate(b200_vfo_bank* bank, double in_samplerate);                /* RxVFO::setInSamplerate  rx_vfo.h:35-43, all VFOs */
+int b200_vfo_reset(b200_vfo_bank* bank, int vfo);                                              /* RxVFO::reset            rx_vfo.h:79-87 */
+
+/* Rotator phase (FrequencyXlator::phase, frequency_xlator.h:70).  The reference carries it as a
+ * recursive fp32 product; this library carries the angle in float64 and advances it by a step
+ * calibrated against that recursion (DESIGN.md "rotator").  get/set exist so tests can compare
+ * block by block from the same starting phase; set also serves checkpoint/restore. */
+int b200_vfo_get_phase(b200_vfo_bank* bank, int vfo, double* re, double* im);
+int b200_vfo_set_phase(b200_vfo_bank* bank, int vfo, double re, double im);
+
+/* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)
+ * [1]=power-of-two ratio [2]=interp [3]=decim [4]=resampler tap count [5]=taps per phase
+ * [6]=channel-filter tap count (0 when bypassed, rx_vfo.h:24,91-93) [7]=1 if stage 1 runs fused */
+int b200_vfo_describe(b200_vfo_bank* bank, int vfo, int* info8);
+/* Copies tap tables to host (which: 0 = resampler prototype after the *interp gain,
+ * 1 = channel filter, 10+s = decimator stage s).  Returns the tap count. */
+int b200_vfo_get_taps(b200_vfo_bank* bank, int vfo, int which, float* out, int cap);
+
+/* RxVFO::process(count, in, out) for every VFO — rx_vfo.h:89-100.  d_in: device cf32[count].
+ * Results stay on the device until fetched; out counts are exact and available on return
+ * (they depend only on counts and integer state, never on sample values). */
+int b200_vfo_bank_process(b200_vfo_bank* bank, const float* d_in, int count, void* stream);
+int b200_vfo_out_count(b200_vfo_bank* bank, int vfo);             /* outCount of the last process call */
+const float* b200_vfo_out_ptr(b200_vfo_bank* bank, int vfo);      /* device cf32[out_count] */
+/* Same, host buffers in and out (pinned staging + H2D/D2H inside; blocks until done).
+ * h_out[v] must hold b200_vfo_max_out(bank, v, count) samples; counts[v] receives outCount. */
+int b200_vfo_bank_process_host(b200_vfo_bank* bank, const float* h_in, int count, float* const* h_out, int* counts, void* stream);
+int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
+
+/* Demodulator attached to a VFO's output (decoder_modules/radio/src/radio_module.h:76-107):
+ *   B200_DEMOD_NFM  dsp::demod::FM<stereo_t>   (demod/fm.h:86-103, quadrature.h:39-46); p0=lowPass p1=highPass (flags)
+ *   B200_DEMOD_AM   dsp::demod::AM<stereo_t>   (demod/am.h:101-133); p0=agcMode (0 CARRIER,1 AUDIO) p1=attack p2=decay p3=dcBlockRate
+ *   B200_DEMOD_USB/LSB/DSB dsp::demod::SSB<stereo_t> (demod/ssb.h:82-97); p1=attack p2=decay
+ * attack/decay/dcBlockRate are per-sample coefficients as the radio module passes them
+ * (e.g. 50.0/IF rate, usb.h:34).  Demodulation runs at the VFO's out_samplerate with
+ * `bandwidth` = the VFO bandwidth.  Audio (stereo {l,r}, same count as the VFO output) is
+ * produced by b200_vfo_bank_process right after the channelizer. */
+#define B200_DEMOD_NONE 0
+#define B200_DEMOD_NFM 1
+#define B200_DEMOD_AM 2
+#define B200_DEMOD_USB 3
+#define B200_DEMOD_LSB 4
+#define B200_DEMOD_DSB 5
+int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double p1, double p2, double p3);
+const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo);    /* device stereo[out_count] or NULL */
+
+/* ------------------------------------------------------------------------------------------
+ * IQ front end — replaces IQFrontEnd (signal_path/iq_frontend.{h,cpp}): pre-processing chain
+ * (PowerDecimator -> DCBlocker -> Conjugate, iq_frontend.cpp:40-44), FFT branch (Reshaper framing
+ * iq_frontend.h:88-92 + handler iq_frontend.cpp:267-287) and the VFO bank it owns (addVFO :159-179).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_frontend b200_frontend;
+
+#define B200_WINDOW_RECTANGULAR 0
+#define B200_WINDOW_BLACKMAN 1
+#define B200_WINDOW_NUTTALL 2
+
+/* IQFrontEnd::init(in, sampleRate, buffering, decimRatio, dcBlocking, fftSize, fftRate, fftWindow, ...)
+ * — iq_frontend.cpp:19-83 followed by the updateFFTPath() every setter triggers (:289-325), i.e. the
+ * sign-alternating window is in force from the first frame.  fft_size must be a power of two
+ * in [32, 4194304]. */
+int b200_frontend_create(b200_frontend** out, double sample_rate, int decim_ratio, int dc_blocking, int invert_iq,
+                         int fft_size, double fft_rate, int fft_window, int max_block, int device);
+int b200_frontend_destroy(b200_frontend* fe);
+
+int b200_frontend_set_sample_rate(b200_frontend* fe, double sample_rate);   /* IQFrontEnd::setSampleRate  iq_frontend.cpp:90-118 */
+int b200_frontend_set_decimation(b200_frontend* fe, int ratio);             /* IQFrontEnd::setDecimation  :124-141 */
+int b200_frontend_set_dc_blocking(b200_frontend* fe, int enabled);          /* IQFrontEnd::setDCBlocking  :143-145 */
+int b200_frontend_set_invert_iq(b200_frontend* fe, int enabled);            /* IQFrontEnd::setInvertIQ    :147-149 */
+int b200_frontend_set_fft_size(b200_frontend* fe, int size);                /* IQFrontEnd::setFFTSize     :204-207 */
+int b200_frontend_set_fft_rate(b200_frontend* fe, double rate);             /* IQFrontEnd::setFFTRate     :209-212 */
+int b200_frontend_set_fft_window(b200_frontend* fe, int window);            /* IQFrontEnd::setFFTWindow   :214-217 */
+double b200_frontend_effective_samplerate(b200_frontend* fe);               /* IQFrontEnd::getEffectiveSamplerate :263-265 */
+/* Multi-GPU time sharding of FFT frames: this handle computes only frames with
+ * (frame_index % world) == rank; every rank still tracks the framing position. Default 0 of 1. */
+int b200_frontend_set_frame_shard(b200_frontend* fe, int rank, int world);
+
+/* The bank fed by this front end's pre-processed stream (IQFrontEnd::addVFO/removeVFO go
+ * through b200_vfo_bank_add/remove on it).  Owned by the front end. */
+b200_vfo_bank* b200_frontend_vfo_bank(b200_frontend* fe);
+
+/* One block through the whole front end: pre-processing -> {FFT frames, every VFO (+demod)}.
+ * d_in: device cf32[count].  After return:
+ *   b200_frontend_preproc_out  -> the stream the Splitter would fan out (device cf32[n])
+ *   b200_frontend_frame_count  -> FFT frames completed by this block (on this rank's shard)
+ *   b200_frontend_frame_ptr(i) -> device float[fft_size], 10*log10(|X|^2/N^2), DC at N/2 */
+int b200_frontend_process(b200_frontend* fe, const float* d_in, int count, void* stream);
+int b200_frontend_preproc_out(b200_frontend* fe, const float** d_out, int* count);
+int b200_frontend_frame_count(b200_frontend* fe);
+const float* b200_frontend_frame_ptr(b200_frontend* fe, int i);
+int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index of frame i (for sharded reassembly) */
+/* Host-buffer variant (the drop-in path of include/dsp/iq_frontend.h): H2D of the block, then D2H
+ * of `h_frames` (frame_count x fft_size floats, may be NULL) and each VFO's output (h_vfo_out[v],
+ * may be NULL) / audio (h_audio[v], may be NULL).  Blocks until done. */
+int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
+                               float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
+
+/* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
+int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Waterfall math — WaterFall::pushFFT (gui/widgets/waterfall.cpp:1204-1276): doZoom (:98-154) and the
+ * dB -> palette mapping (:1229-1235).  Headless: results go to device buffers, no GL.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_waterfall b200_waterfall;
+int b200_waterfall_create(b200_waterfall** out, int raw_fft_size, int data_width, int device);
+int b200_waterfall_destroy(b200_waterfall* wf);
+/* view: drawDataStart / drawDataSize of pushFFT (:1208-1210) */
+int b200_waterfall_set_view(b200_waterfall* wf, int offset, int width);
+int b200_waterfall_set_range(b200_waterfall* wf, float wf_min, float wf_max);
+/* 1000-entry RGBA LUT (WATERFALL_RESOLUTION); b200_waterfall_make_palette restates updatePallette (:1282-1295) */
+int b200_waterfall_set_palette(b200_waterfall* wf, const uint32_t* lut1000);
+int b200_waterfall_make_palette(const float* colors_rgb, int color_count, uint32_t* lut1000);
+/* nrows dB rows (device, row stride raw_fft_size) -> zoomed rows (device float[nrows][data_width], may be
+ * NULL) and RGBA rows (device uint32[nrows][data_width], may be NULL). */
+int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, float* d_zoom, uint32_t* d_rgba, void* stream);
+/* the start indices / spans the zoom uses (host copies, data_width each) */
+int b200_waterfall_zoom_table(b200_waterfall* wf, int* sid, int* ufactor);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DSP_H */

@@ -1,0 +1,331 @@
+"""ctypes binding of include/b200dsp.h (host side used by tests and bench.py).
+
+Importing this module loads ``libb200dsp.so``; if the library is missing it is built with nvcc,
+and if that fails the import fails — there is no CPU fallback for any process call.
+Device buffers are torch CUDA tensors (torch is the allocator / stream provider only).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200dsp.so")
+
+if not os.path.exists(LIB_PATH) or _build.stale():
+    _build.build()
+lib = C.CDLL(LIB_PATH)
+
+_vp, _i, _d, _f, _pp = C.c_void_p, C.c_int, C.c_double, C.c_float, C.POINTER(C.c_void_p)
+
+_SIGS = {
+    "b200_last_error": (C.c_char_p, []),
+    "b200_version": (C.c_char_p, []),
+    "b200_launch_count": (C.c_uint64, []),
+    "b200_vfo_bank_create": (_i, [_pp, _d, _i, _i]),
+    "b200_vfo_bank_destroy": (_i, [_vp]),
+    "b200_vfo_bank_add": (_i, [_vp, _d, _d, _d]),
+    "b200_vfo_bank_remove": (_i, [_vp, _i]),
+    "b200_vfo_bank_count": (_i, [_vp]),
+    "b200_vfo_set_offset": (_i, [_vp, _i, _d]),
+    "b200_vfo_set_bandwidth": (_i, [_vp, _i, _d]),
+    "b200_vfo_set_out_samplerate": (_i, [_vp, _i, _d, _d]),
+    "b200_vfo_bank_set_in_samplerate": (_i, [_vp, _d]),
+    "b200_vfo_reset": (_i, [_vp, _i]),
+    "b200_vfo_get_phase": (_i, [_vp, _i, C.POINTER(_d), C.POINTER(_d)]),
+    "b200_vfo_set_phase": (_i, [_vp, _i, _d, _d]),
+    "b200_vfo_describe": (_i, [_vp, _i, _vp]),
+    "b200_vfo_get_taps": (_i, [_vp, _i, _i, _vp, _i]),
+    "b200_vfo_bank_process": (_i, [_vp, _vp, _i, _vp]),
+    "b200_vfo_out_count": (_i, [_vp, _i]),
+    "b200_vfo_out_ptr": (_vp, [_vp, _i]),
+    "b200_vfo_bank_process_host": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
+    "b200_vfo_max_out": (_i, [_vp, _i, _i]),
+    "b200_vfo_set_demod": (_i, [_vp, _i, _i, _d, _d, _d, _d]),
+    "b200_vfo_audio_ptr": (_vp, [_vp, _i]),
+    "b200_frontend_create": (_i, [_pp, _d, _i, _i, _i, _i, _d, _i, _i, _i]),
+    "b200_frontend_destroy": (_i, [_vp]),
+    "b200_frontend_set_sample_rate": (_i, [_vp, _d]),
+    "b200_frontend_set_decimation": (_i, [_vp, _i]),
+    "b200_frontend_set_dc_blocking": (_i, [_vp, _i]),
+    "b200_frontend_set_invert_iq": (_i, [_vp, _i]),
+    "b200_frontend_set_fft_size": (_i, [_vp, _i]),
+    "b200_frontend_set_fft_rate": (_i, [_vp, _d]),
+    "b200_frontend_set_fft_window": (_i, [_vp, _i]),
+    "b200_frontend_effective_samplerate": (_d, [_vp]),
+    "b200_frontend_set_frame_shard": (_i, [_vp, _i, _i]),
+    "b200_frontend_vfo_bank": (_vp, [_vp]),
+    "b200_frontend_process": (_i, [_vp, _vp, _i, _vp]),
+    "b200_frontend_preproc_out": (_i, [_vp, _pp, C.POINTER(_i)]),
+    "b200_frontend_frame_count": (_i, [_vp]),
+    "b200_frontend_frame_ptr": (_vp, [_vp, _i]),
+    "b200_frontend_frame_index": (C.c_int64, [_vp, _i]),
+    "b200_frontend_process_host": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
+    "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
+    "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
+    "b200_waterfall_destroy": (_i, [_vp]),
+    "b200_waterfall_set_view": (_i, [_vp, _i, _i]),
+    "b200_waterfall_set_range": (_i, [_vp, _f, _f]),
+    "b200_waterfall_set_palette": (_i, [_vp, _vp]),
+    "b200_waterfall_make_palette": (_i, [_vp, _i, _vp]),
+    "b200_waterfall_push": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
+    "b200_waterfall_zoom_table": (_i, [_vp, _vp, _vp]),
+}
+
+EXPORTS = sorted(_SIGS.keys())
+for _name, (_res, _args) in _SIGS.items():
+    _fn = getattr(lib, _name)
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def _chk(rc):
+    if rc < 0:
+        raise B200Error("libb200dsp error %d: %s" % (rc, lib.b200_last_error().decode()))
+    return rc
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+        return torch.cuda.current_stream().cuda_stream
+    return getattr(stream, "cuda_stream", stream)
+
+
+def _dev_to_numpy(ptr, count, dtype, device):
+    """Copy `count` elements of `dtype` from a raw device pointer to a numpy array."""
+    import torch
+    out = np.empty(count, dtype)
+    if count == 0:
+        return out
+    torch.cuda.synchronize(device)
+    rt = C.CDLL("libcudart.so.12") if not hasattr(_dev_to_numpy, "_rt") else _dev_to_numpy._rt
+    _dev_to_numpy._rt = rt
+    rt.cudaMemcpy.argtypes = [_vp, _vp, C.c_size_t, _i]
+    rc = rt.cudaMemcpy(out.ctypes.data, ptr, out.nbytes, 2)
+    if rc != 0:
+        raise B200Error("cudaMemcpy D2H failed: %d" % rc)
+    return out
+
+
+class VfoBank:
+    """N RxVFOs fed by one input stream (dsp::channel::RxVFO, channel/rx_vfo.h)."""
+
+    def __init__(self, in_samplerate, max_block=1000000, device=0, _handle=None):
+        self.device = device
+        self.owned = _handle is None
+        if _handle is None:
+            h = _vp()
+            _chk(lib.b200_vfo_bank_create(C.byref(h), float(in_samplerate), int(max_block), int(device)))
+            self.h = h
+        else:
+            self.h = _vp(_handle)
+
+    def close(self):
+        if self.h and self.owned:
+            lib.b200_vfo_bank_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def add(self, out_sr, bw, offset):
+        return _chk(lib.b200_vfo_bank_add(self.h, float(out_sr), float(bw), float(offset)))
+
+    def remove(self, v): _chk(lib.b200_vfo_bank_remove(self.h, v))
+    def count(self): return _chk(lib.b200_vfo_bank_count(self.h))
+    def set_offset(self, v, off): _chk(lib.b200_vfo_set_offset(self.h, v, float(off)))
+    def set_bandwidth(self, v, bw): _chk(lib.b200_vfo_set_bandwidth(self.h, v, float(bw)))
+    def set_out_samplerate(self, v, sr, bw): _chk(lib.b200_vfo_set_out_samplerate(self.h, v, float(sr), float(bw)))
+    def set_in_samplerate(self, sr): _chk(lib.b200_vfo_bank_set_in_samplerate(self.h, float(sr)))
+    def reset(self, v): _chk(lib.b200_vfo_reset(self.h, v))
+
+    def get_phase(self, v):
+        re, im = _d(), _d()
+        _chk(lib.b200_vfo_get_phase(self.h, v, C.byref(re), C.byref(im)))
+        return complex(re.value, im.value)
+
+    def set_phase(self, v, z): _chk(lib.b200_vfo_set_phase(self.h, v, float(z.real), float(z.imag)))
+
+    def describe(self, v):
+        info = np.zeros(8, np.int32)
+        _chk(lib.b200_vfo_describe(self.h, v, info.ctypes.data))
+        return dict(mode=int(info[0]), ratio=int(info[1]), interp=int(info[2]), decim=int(info[3]),
+                    resamp_taps=int(info[4]), taps_per_phase=int(info[5]), chan_taps=int(info[6]), fused=int(info[7]))
+
+    def taps(self, v, which):
+        n = _chk(lib.b200_vfo_get_taps(self.h, v, which, None, 0))
+        out = np.zeros(n, np.float32)
+        _chk(lib.b200_vfo_get_taps(self.h, v, which, out.ctypes.data, n))
+        return out
+
+    def set_demod(self, v, kind, p0=0.0, p1=0.0, p2=0.0, p3=0.0):
+        _chk(lib.b200_vfo_set_demod(self.h, v, int(kind), float(p0), float(p1), float(p2), float(p3)))
+
+    def process(self, d_in, count=None, stream=None):
+        """d_in: torch CUDA float32 tensor [count, 2] (or any tensor whose data_ptr holds cf32)."""
+        if count is None:
+            count = d_in.shape[0]
+        _chk(lib.b200_vfo_bank_process(self.h, d_in.data_ptr() if count else None, int(count), _stream_ptr(stream)))
+
+    def out_count(self, v): return _chk(lib.b200_vfo_out_count(self.h, v))
+    def out_ptr(self, v): return lib.b200_vfo_out_ptr(self.h, v)
+    def audio_ptr(self, v): return lib.b200_vfo_audio_ptr(self.h, v)
+
+    def output(self, v):
+        n = self.out_count(v)
+        return _dev_to_numpy(self.out_ptr(v), n, np.complex64, self.device)
+
+    def audio(self, v):
+        n = self.out_count(v)
+        p = self.audio_ptr(v)
+        if not p:
+            raise B200Error("VFO %d has no demodulator" % v)
+        return _dev_to_numpy(p, 2 * n, np.float32, self.device).reshape(n, 2)
+
+    def max_out(self, v, count): return _chk(lib.b200_vfo_max_out(self.h, v, int(count)))
+
+    def process_host(self, x, vfos, stream=None):
+        """Host-buffer variant: x complex64 numpy; returns {vfo: complex64 array}."""
+        x = np.ascontiguousarray(x, np.complex64)
+        nslots = max(vfos) + 1
+        bufs = {v: np.empty(self.max_out(v, len(x)), np.complex64) for v in vfos}
+        ptrs = (_vp * nslots)()
+        for v in vfos:
+            ptrs[v] = bufs[v].ctypes.data
+        counts = np.zeros(nslots, np.int32)
+        _chk(lib.b200_vfo_bank_process_host(self.h, x.ctypes.data, len(x), ptrs, counts.ctypes.data, _stream_ptr(stream)))
+        return {v: bufs[v][:counts[v]].copy() for v in vfos}
+
+
+class FrontEnd:
+    """IQFrontEnd (signal_path/iq_frontend.{h,cpp}) on one GPU."""
+
+    def __init__(self, sample_rate, decim_ratio=1, dc_blocking=False, invert_iq=False, fft_size=65536, fft_rate=20.0,
+                 fft_window=2, max_block=1000000, device=0):
+        h = _vp()
+        _chk(lib.b200_frontend_create(C.byref(h), float(sample_rate), int(decim_ratio), int(dc_blocking), int(invert_iq),
+                                      int(fft_size), float(fft_rate), int(fft_window), int(max_block), int(device)))
+        self.h = h
+        self.device = device
+        self.fft_size = fft_size
+        self.vfos = VfoBank(0, device=device, _handle=lib.b200_frontend_vfo_bank(self.h))
+
+    def close(self):
+        if self.h:
+            lib.b200_frontend_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_sample_rate(self, sr): _chk(lib.b200_frontend_set_sample_rate(self.h, float(sr)))
+    def set_decimation(self, r): _chk(lib.b200_frontend_set_decimation(self.h, int(r)))
+    def set_dc_blocking(self, e): _chk(lib.b200_frontend_set_dc_blocking(self.h, int(e)))
+    def set_invert_iq(self, e): _chk(lib.b200_frontend_set_invert_iq(self.h, int(e)))
+
+    def set_fft_size(self, n):
+        _chk(lib.b200_frontend_set_fft_size(self.h, int(n)))
+        self.fft_size = n
+
+    def set_fft_rate(self, r): _chk(lib.b200_frontend_set_fft_rate(self.h, float(r)))
+    def set_fft_window(self, w): _chk(lib.b200_frontend_set_fft_window(self.h, int(w)))
+    def set_frame_shard(self, rank, world): _chk(lib.b200_frontend_set_frame_shard(self.h, int(rank), int(world)))
+    def effective_samplerate(self): return lib.b200_frontend_effective_samplerate(self.h)
+
+    def process(self, d_in, count=None, stream=None):
+        if count is None:
+            count = d_in.shape[0]
+        _chk(lib.b200_frontend_process(self.h, d_in.data_ptr() if count else None, int(count), _stream_ptr(stream)))
+
+    def frame_count(self): return _chk(lib.b200_frontend_frame_count(self.h))
+    def frame_ptr(self, i): return lib.b200_frontend_frame_ptr(self.h, i)
+    def frame_index(self, i): return lib.b200_frontend_frame_index(self.h, i)
+
+    def frames(self):
+        n = self.frame_count()
+        return [_dev_to_numpy(self.frame_ptr(i), self.fft_size, np.float32, self.device) for i in range(n)]
+
+    def preproc_out(self):
+        p, n = _vp(), _i()
+        _chk(lib.b200_frontend_preproc_out(self.h, C.byref(p), C.byref(n)))
+        return _dev_to_numpy(p.value, n.value, np.complex64, self.device)
+
+    def process_host(self, x, max_frames=0, vfos=(), audio=(), stream=None):
+        x = np.ascontiguousarray(x, np.complex64)
+        frames = np.empty((max_frames, self.fft_size), np.float32) if max_frames else None
+        nslots = (max(list(vfos) + list(audio)) + 1) if (vfos or audio) else 0
+        obufs = {v: np.empty(self.vfos.max_out(v, len(x)), np.complex64) for v in vfos}
+        abufs = {v: np.empty((self.vfos.max_out(v, len(x)), 2), np.float32) for v in audio}
+        optrs = (_vp * max(nslots, 1))()
+        aptrs = (_vp * max(nslots, 1))()
+        for v in vfos:
+            optrs[v] = obufs[v].ctypes.data
+        for v in audio:
+            aptrs[v] = abufs[v].ctypes.data
+        counts = np.zeros(max(nslots, 1), np.int32)
+        _chk(lib.b200_frontend_process_host(self.h, x.ctypes.data, len(x), frames.ctypes.data if max_frames else None, max_frames,
+                                            optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
+        nf = self.frame_count()
+        return dict(frames=frames[:min(nf, max_frames)] if max_frames else None, n_frames=nf,
+                    vfo={v: obufs[v][:counts[v]] for v in vfos}, audio={v: abufs[v][:counts[v]] for v in audio})
+
+
+class Waterfall:
+    """doZoom + palette mapping of WaterFall::pushFFT (gui/widgets/waterfall.cpp:98-154,1229-1235), headless."""
+
+    def __init__(self, raw_fft_size, data_width, device=0):
+        h = _vp()
+        _chk(lib.b200_waterfall_create(C.byref(h), int(raw_fft_size), int(data_width), int(device)))
+        self.h, self.n, self.w, self.device = h, raw_fft_size, data_width, device
+
+    def close(self):
+        if self.h:
+            lib.b200_waterfall_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_view(self, offset, width): _chk(lib.b200_waterfall_set_view(self.h, int(offset), int(width)))
+    def set_range(self, lo, hi): _chk(lib.b200_waterfall_set_range(self.h, float(lo), float(hi)))
+
+    def set_palette(self, lut):
+        lut = np.ascontiguousarray(lut, np.uint32)
+        assert lut.shape == (1000,)
+        _chk(lib.b200_waterfall_set_palette(self.h, lut.ctypes.data))
+
+    @staticmethod
+    def make_palette(colors):
+        colors = np.ascontiguousarray(colors, np.float32)
+        lut = np.zeros(1000, np.uint32)
+        _chk(lib.b200_waterfall_make_palette(colors.ctypes.data, colors.shape[0], lut.ctypes.data))
+        return lut
+
+    def push(self, d_rows_ptr, nrows, d_zoom_ptr, d_rgba_ptr, stream=None):
+        _chk(lib.b200_waterfall_push(self.h, d_rows_ptr, int(nrows), d_zoom_ptr, d_rgba_ptr, _stream_ptr(stream)))
+
+    def zoom_table(self):
+        s = np.zeros(self.w, np.int32)
+        u = np.zeros(self.w, np.int32)
+        _chk(lib.b200_waterfall_zoom_table(self.h, s.ctypes.data, u.ctypes.data))
+        return s, u
+
+
+def fft_forward(d_in, nz, fft_size, d_out, stream=None):
+    _chk(lib.b200_fft_forward(d_in.data_ptr(), int(nz), int(fft_size), d_out.data_ptr(), _stream_ptr(stream)))

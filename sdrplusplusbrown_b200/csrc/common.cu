@@ -1,0 +1,65 @@
+#include "common.cuh"
+
+#include <cstring>
+
+namespace b200 {
+
+static thread_local char t_err[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+void setError(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(t_err, sizeof(t_err), fmt, ap);
+    va_end(ap);
+}
+
+int PinnedRing::init(size_t nbytes) {
+    bytes = nbytes;
+    for (int i = 0; i < kSlots; i++) {
+        B200_CUDA(cudaHostAlloc(&host[i], bytes, cudaHostAllocDefault));
+        B200_CUDA(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming));
+        used[i] = false;
+    }
+    return B200_OK;
+}
+
+void PinnedRing::destroy() {
+    for (int i = 0; i < kSlots; i++) {
+        if (host[i]) { cudaFreeHost(host[i]); host[i] = nullptr; }
+        if (done[i]) { cudaEventDestroy(done[i]); done[i] = nullptr; }
+    }
+}
+
+int PinnedRing::acquire(size_t nbytes, void** hostPtr, int* slot) {
+    if (nbytes > bytes) {
+        // grow every slot (rare: the VFO count grew); wait for in-flight copies first
+        for (int i = 0; i < kSlots; i++) {
+            if (used[i]) { B200_CUDA(cudaEventSynchronize(done[i])); used[i] = false; }
+            B200_CUDA(cudaFreeHost(host[i]));
+            host[i] = nullptr;
+        }
+        bytes = nbytes * 2;
+        for (int i = 0; i < kSlots; i++) { B200_CUDA(cudaHostAlloc(&host[i], bytes, cudaHostAllocDefault)); }
+    }
+    const int sidx = next;
+    next = (next + 1) % kSlots;
+    if (used[sidx]) { B200_CUDA(cudaEventSynchronize(done[sidx])); used[sidx] = false; }
+    *hostPtr = host[sidx];
+    *slot = sidx;
+    return B200_OK;
+}
+
+int PinnedRing::release(int slot, cudaStream_t s) {
+    B200_CUDA(cudaEventRecord(done[slot], s));
+    used[slot] = true;
+    return B200_OK;
+}
+
+} // namespace b200
+
+extern "C" {
+const char* b200_last_error(void) { return b200::t_err; }
+const char* b200_version(void) { return "b200dsp 0.1 (sm_100a)"; }
+uint64_t b200_launch_count(void) { return b200::g_launches.load(); }
+}

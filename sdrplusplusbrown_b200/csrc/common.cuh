@@ -1,0 +1,71 @@
+// Shared declarations for libb200dsp (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/b200dsp.h"
+
+namespace b200 {
+
+struct cf32 { float re, im; };
+
+void setError(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launches;
+inline void countLaunch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+#define B200_CUDA(call)                                                                         \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            ::b200::setError("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e__)); \
+            return B200_ECUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define B200_CHECK_LAUNCH()                                                                     \
+    do {                                                                                        \
+        cudaError_t e__ = cudaGetLastError();                                                   \
+        if (e__ != cudaSuccess) {                                                               \
+            ::b200::setError("kernel launch failed at %s:%d: %s", __FILE__, __LINE__, cudaGetErrorString(e__)); \
+            return B200_ECUDA;                                                                  \
+        }                                                                                       \
+    } while (0)
+
+#define B200_TRY(expr)                         \
+    do {                                       \
+        int rc__ = (expr);                     \
+        if (rc__ != B200_OK) { return rc__; }  \
+    } while (0)
+
+// RAII device selection
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) { ok = false; }
+    }
+    ~DeviceGuard() { if (prev >= 0) { cudaSetDevice(prev); } }
+};
+
+// Pinned host staging ring for per-call descriptor uploads (stream-ordered reuse).
+struct PinnedRing {
+    static constexpr int kSlots = 8;
+    void* host[kSlots] = {};
+    cudaEvent_t done[kSlots] = {};
+    bool used[kSlots] = {};
+    size_t bytes = 0;
+    int next = 0;
+    int init(size_t nbytes);
+    void destroy();
+    // returns a host slot that no in-flight copy still reads; *slot receives its index
+    int acquire(size_t nbytes, void** hostPtr, int* slot);
+    int release(int slot, cudaStream_t s);   // record the slot's event after the H2D copy was enqueued
+};
+
+} // namespace b200

@@ -1,0 +1,38 @@
+// Generic "FIR job" machinery shared by the VFO bank, the front-end decimator and the demodulators.
+//
+// A job is one streaming filter stage of the reference (DecimatingFIR, PolyphaseResampler or FIR)
+// with its carried history.  Its input is the concatenation [history (H = taps-1 samples) | data
+// (nIn samples)], exactly the reference's work buffer (filter/fir.h:25-27,66), but held as two
+// segments so no memcpy/memmove of the block is needed; the history is double-buffered and
+// refreshed by one kernel per process call.
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+enum JobKind : int { JOB_DECIM_FIR = 0, JOB_POLYPHASE = 1 };
+
+// Device-visible description of one job for one process call (uploaded per call).
+struct FirJob {
+    const void* hist;      // H samples carried from previous calls
+    const void* data;      // nIn new samples
+    void* out;             // nOut results
+    void* histNext;        // H samples to carry into the next call
+    const float* taps;     // DECIM_FIR: T taps; POLYPHASE: bank [L][rowStride]
+    int H;                 // history length = taps-1 (tapsPerPhase-1 for polyphase)
+    int T;                 // dot-product length (taps, or tapsPerPhase)
+    int D;                 // decimation (DECIM_FIR); 1 for a plain FIR
+    int offset;            // position of output 0 in [hist|data] coordinates (DecimatingFIR::offset / PolyphaseResampler::offset)
+    int nIn, nOut;
+    int kind;
+    int L, M, phase0, rowStride;   // POLYPHASE only
+    int elemFloats;        // 2 = complex samples, 1 = real samples
+    int pad;
+};
+
+// Launchers (all jobs of one "level" in a single launch; grid.y = job index)
+// every job of a launch must have the same elemFloats
+int launchFirJobs(const FirJob* d_jobs, int nJobs, int maxOut, int elemFloats, cudaStream_t s);
+int launchHistoryUpdate(const FirJob* d_jobs, int nJobs, int maxH, cudaStream_t s);
+
+} // namespace b200

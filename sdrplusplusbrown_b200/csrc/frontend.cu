@@ -1,0 +1,604 @@
+// IQ front end: pre-processing chain, FFT framing and the VFO bank it feeds.
+// Reference: IQFrontEnd (signal_path/iq_frontend.{h,cpp}); block order of iq_frontend.cpp:40-44 is
+// PowerDecimator -> DCBlocker -> Conjugate, then the Splitter (:46) fans the result out to the FFT
+// branch (Reshaper + handler, :50-52,267-287) and to every VFO (:159-179).  On the GPU the fan-out
+// costs nothing: every consumer reads the same device buffer.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "fft.cuh"
+#include "vfo_bank.cuh"
+
+namespace b200 {
+
+namespace {
+
+// ------------------------------------------------------------------ DC blocker (correction/dc_blocker.h:54-60)
+//   out[i] = in[i] - o;  o += out[i] * r      <=>      o' = (1-r) * o + r * in[i]
+// A first-order linear recurrence: each CTA folds its chunk into an affine map o -> A*o + B, a
+// single small CTA chains the chunk maps (float64), and the apply pass re-walks each chunk from
+// its exact starting offset.  The optional conjugate (math/conjugate.h:12-15) rides on the apply pass.
+constexpr int kDcThreads = 256;
+constexpr int kDcPerThread = 8;
+constexpr int kDcChunk = kDcThreads * kDcPerThread;
+
+struct DcParams {
+    float rate;        // (float)(50/sr), iq_frontend.h:84-86, DCBlocker::_rate is float
+    double a;          // 1 - rate
+    double aRun;       // a^kDcPerThread
+    double aChunk;     // a^kDcChunk
+};
+
+// B for a run of samples starting with offset 0: returns o after the run
+__device__ __forceinline__ float2 dcRunFold(const float2* x, int n, float r) {
+    float2 o = make_float2(0.f, 0.f);
+    for (int i = 0; i < n; i++) {
+        o.x += (x[i].x - o.x) * r;
+        o.y += (x[i].y - o.y) * r;
+    }
+    return o;
+}
+
+__global__ void __launch_bounds__(kDcThreads) dcReduceKernel(const cf32* __restrict__ in, int n, DcParams p, double2* __restrict__ chunkB) {
+    __shared__ double2 sB[kDcThreads];
+    const int base = blockIdx.x * kDcChunk + threadIdx.x * kDcPerThread;
+    float2 x[kDcPerThread];
+    int cnt = 0;
+#pragma unroll
+    for (int i = 0; i < kDcPerThread; i++) {
+        if (base + i < n) { x[i] = __ldg(reinterpret_cast<const float2*>(in) + base + i); cnt = i + 1; }
+        else { x[i] = make_float2(0.f, 0.f); }
+    }
+    // a zero sample leaves o' = a*o, so padding the tail with zeros keeps A = aRun for every thread;
+    // the true end-of-block state is recovered by the scan kernel from the exact tail length.
+    (void)cnt;
+    const float2 b = dcRunFold(x, kDcPerThread, p.rate);
+    sB[threadIdx.x] = make_double2((double)b.x, (double)b.y);
+    __syncthreads();
+    // inclusive scan of affine maps with equal slopes: S_t = aRun * S_{t-1} + B_t
+    double mul = p.aRun;
+    for (int d = 1; d < kDcThreads; d <<= 1) {
+        double2 add = make_double2(0.0, 0.0);
+        if ((int)threadIdx.x >= d) { add = sB[threadIdx.x - d]; }
+        __syncthreads();
+        if ((int)threadIdx.x >= d) { sB[threadIdx.x].x += mul * add.x; sB[threadIdx.x].y += mul * add.y; }
+        __syncthreads();
+        mul *= mul;
+    }
+    if (threadIdx.x == kDcThreads - 1) { chunkB[blockIdx.x] = sB[threadIdx.x]; }
+}
+
+// chunkStart[c] = offset entering chunk c; state[0] = offset after the whole block
+__global__ void __launch_bounds__(1024) dcScanKernel(const double2* __restrict__ chunkB, int nChunks, int n, DcParams p,
+                                                     double2* __restrict__ chunkStart, double2* __restrict__ state) {
+    __shared__ double2 sB[1024];
+    __shared__ double sA[1024];
+    const int per = (nChunks + 1023) / 1024;
+    const int c0 = threadIdx.x * per;
+    // fold this thread's run of chunks
+    double A = 1.0; double2 B = make_double2(0.0, 0.0);
+    for (int c = c0; c < min(c0 + per, nChunks); c++) {
+        const double2 b = chunkB[c];
+        B.x = p.aChunk * B.x + b.x; B.y = p.aChunk * B.y + b.y;
+        A *= p.aChunk;
+    }
+    sA[threadIdx.x] = A; sB[threadIdx.x] = B;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        double a2 = 1.0; double2 b2 = make_double2(0.0, 0.0);
+        const bool act = (int)threadIdx.x >= d;
+        if (act) { a2 = sA[threadIdx.x - d]; b2 = sB[threadIdx.x - d]; }
+        __syncthreads();
+        if (act) {
+            const double myA = sA[threadIdx.x];
+            sB[threadIdx.x].x += myA * b2.x; sB[threadIdx.x].y += myA * b2.y;
+            sA[threadIdx.x] = myA * a2;
+        }
+        __syncthreads();
+    }
+    // exclusive prefix for this thread = inclusive of thread-1, applied to the carried-in state
+    const double2 o0 = state[0];
+    double2 o;
+    if (threadIdx.x == 0) { o = o0; }
+    else {
+        const double Ap = sA[threadIdx.x - 1]; const double2 Bp = sB[threadIdx.x - 1];
+        o = make_double2(Ap * o0.x + Bp.x, Ap * o0.y + Bp.y);
+    }
+    for (int c = c0; c < min(c0 + per, nChunks); c++) {
+        chunkStart[c] = o;
+        const double2 b = chunkB[c];
+        o.x = p.aChunk * o.x + b.x; o.y = p.aChunk * o.y + b.y;
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) {
+        // the last chunk was zero padded to a full chunk: undo the surplus decay a^(pad)
+        const int pad = nChunks * kDcChunk - n;
+        const double Aall = sA[1023]; const double2 Ball = sB[1023];
+        double2 e = make_double2(Aall * o0.x + Ball.x, Aall * o0.y + Ball.y);
+        const double undo = pow(p.a, -(double)pad);
+        state[1] = make_double2(e.x * undo, e.y * undo);
+    }
+}
+
+__global__ void __launch_bounds__(kDcThreads) dcApplyKernel(const cf32* __restrict__ in, cf32* __restrict__ out, int n, DcParams p,
+                                                            const double2* __restrict__ chunkStart, int conj) {
+    __shared__ double2 sB[kDcThreads];
+    const int base = blockIdx.x * kDcChunk + threadIdx.x * kDcPerThread;
+    float2 x[kDcPerThread];
+#pragma unroll
+    for (int i = 0; i < kDcPerThread; i++) {
+        x[i] = (base + i < n) ? __ldg(reinterpret_cast<const float2*>(in) + base + i) : make_float2(0.f, 0.f);
+    }
+    const float2 b = dcRunFold(x, kDcPerThread, p.rate);
+    sB[threadIdx.x] = make_double2((double)b.x, (double)b.y);
+    __syncthreads();
+    double mul = p.aRun;
+    for (int d = 1; d < kDcThreads; d <<= 1) {
+        double2 add = make_double2(0.0, 0.0);
+        if ((int)threadIdx.x >= d) { add = sB[threadIdx.x - d]; }
+        __syncthreads();
+        if ((int)threadIdx.x >= d) { sB[threadIdx.x].x += mul * add.x; sB[threadIdx.x].y += mul * add.y; }
+        __syncthreads();
+        mul *= mul;
+    }
+    // offset entering this thread's run: a^(run*t) * chunkStart + S_{t-1}
+    const double2 cs = chunkStart[blockIdx.x];
+    const double at = pow(p.aRun, (double)threadIdx.x);
+    double2 o = make_double2(at * cs.x, at * cs.y);
+    if (threadIdx.x > 0) { o.x += sB[threadIdx.x - 1].x; o.y += sB[threadIdx.x - 1].y; }
+    float ox = (float)o.x, oy = (float)o.y;
+    const float sgn = conj ? -1.0f : 1.0f;
+#pragma unroll
+    for (int i = 0; i < kDcPerThread; i++) {
+        if (base + i < n) {
+            const float yx = x[i].x - ox, yy = x[i].y - oy;
+            ox += yx * p.rate; oy += yy * p.rate;
+            reinterpret_cast<float2*>(out)[base + i] = make_float2(yx, sgn * yy);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) conjKernel(const cf32* __restrict__ in, cf32* __restrict__ out, int n) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < n) {
+        const float2 x = __ldg(reinterpret_cast<const float2*>(in) + i);
+        reinterpret_cast<float2*>(out)[i] = make_float2(x.x, -x.y);
+    }
+}
+
+} // namespace
+
+// ------------------------------------------------------------------ front end object
+struct FrontEnd {
+    int device = 0;
+    double sampleRate = 0; int decimRatio = 1; bool dcBlocking = false, invertIQ = false;
+    int fftSize = 0; double fftRate = 0; int fftWindow = 0;
+    int maxBlock = 0;
+    double effectiveSr = 0;
+    b200_vfo_bank* bank = nullptr;
+    cudaStream_t lastStream = nullptr; bool everRan = false;
+
+    // pre-processing
+    std::vector<Stage> decimStages;
+    cf32* dDcOut = nullptr; size_t dcCap = 0;
+    double2* dChunkB = nullptr; double2* dChunkStart = nullptr; double2* dDcState = nullptr; int dcChunksCap = 0;
+    void* dJobDesc = nullptr; size_t jobDescBytes = 0;
+    PinnedRing ring;
+    const cf32* preOut = nullptr; int preCount = 0;
+
+    // FFT branch
+    FftPlan plan;
+    int nz = 0, skip = 0, interval = 0;
+    float* dWindow = nullptr;
+    int64_t streamPos = 0;       // samples of the pre-processed stream seen since the last FFT reconfiguration
+    int64_t nextFrame = 0;
+    cf32* dCarry = nullptr; int carryLen = 0;
+    float* dRows = nullptr; int rowsCap = 0;
+    FrameDesc* dFrameDesc = nullptr; int frameDescCap = 0;
+    std::vector<int64_t> frameIdx;   // frames produced by the last call
+    int shardRank = 0, shardWorld = 1;
+    // host staging
+    cf32* dStageIn = nullptr;
+
+    int init();
+    void destroy();
+    int syncLast() { if (everRan) { B200_CUDA(cudaStreamSynchronize(lastStream)); } return B200_OK; }
+    int rebuildDecim();
+    int updateFftPath();
+    int preprocess(const cf32* dIn, int count, cudaStream_t s);
+    int fftBranch(cudaStream_t s);
+    int process(const cf32* dIn, int count, cudaStream_t s);
+};
+
+int FrontEnd::rebuildDecim() {
+    for (auto& st : decimStages) { st.destroy(); }
+    decimStages.clear();
+    if (decimRatio > 1) {
+        const design::PlanDef* plan = design::findPlan(decimRatio);
+        if (!plan) { setError("decimation ratio %d is not a supported power of two", decimRatio); return B200_EINVAL; }
+        decimStages.resize(plan->nstages);
+        int cap = maxBlock;
+        for (int i = 0; i < plan->nstages; i++) {
+            std::vector<float> t(plan->stages[i].ntaps);
+            memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());
+            cap = cap / plan->stages[i].decim + 2;
+            B200_TRY(decimStages[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap));
+        }
+    }
+    return B200_OK;
+}
+
+// IQFrontEnd::updateFFTPath (iq_frontend.cpp:289-325)
+int FrontEnd::updateFftPath() {
+    design::reshapeParams(effectiveSr, fftSize, fftRate, skip, nz);
+    interval = nz + skip;
+    if (nz <= 0) { setError("fft rate %g too high for sample rate %g", fftRate, effectiveSr); return B200_EINVAL; }
+    if (plan.N != fftSize) { B200_TRY(plan.create(fftSize, device)); }
+    std::vector<float> w = design::fftWindow(fftWindow, nz);
+    if (dWindow) { cudaFree(dWindow); dWindow = nullptr; }
+    B200_CUDA(cudaMalloc((void**)&dWindow, (size_t)nz * sizeof(float)));
+    B200_CUDA(cudaMemcpy(dWindow, w.data(), (size_t)nz * sizeof(float), cudaMemcpyHostToDevice));
+    if (dCarry) { cudaFree(dCarry); dCarry = nullptr; }
+    B200_CUDA(cudaMalloc((void**)&dCarry, (size_t)nz * sizeof(cf32)));
+    carryLen = 0; streamPos = 0; nextFrame = 0;
+    const int maxFrames = maxBlock / std::max(interval, 1) + 2;
+    if (dRows) { cudaFree(dRows); dRows = nullptr; }
+    rowsCap = maxFrames;
+    B200_CUDA(cudaMalloc((void**)&dRows, (size_t)rowsCap * fftSize * sizeof(float)));
+    if (dFrameDesc) { cudaFree(dFrameDesc); dFrameDesc = nullptr; }
+    frameDescCap = maxFrames;
+    B200_CUDA(cudaMalloc((void**)&dFrameDesc, (size_t)frameDescCap * sizeof(FrameDesc)));
+    frameIdx.clear();
+    return B200_OK;
+}
+
+int FrontEnd::init() {
+    DeviceGuard g(device);
+    if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
+    effectiveSr = sampleRate / decimRatio;
+    B200_TRY(ring.init(64 * 1024));
+    B200_TRY(rebuildDecim());
+    B200_CUDA(cudaMalloc((void**)&dDcState, 2 * sizeof(double2)));
+    B200_CUDA(cudaMemset(dDcState, 0, 2 * sizeof(double2)));
+    B200_TRY(updateFftPath());
+    bank = new b200_vfo_bank;
+    bank->ownedByFrontend = true;
+    return bank->impl.init(effectiveSr, maxBlock, device);
+}
+
+void FrontEnd::destroy() {
+    DeviceGuard g(device);
+    if (everRan) { cudaStreamSynchronize(lastStream); }
+    if (bank) { bank->impl.destroy(); delete bank; bank = nullptr; }
+    for (auto& st : decimStages) { st.destroy(); }
+    decimStages.clear();
+    plan.destroy();
+    ring.destroy();
+    void* ptrs[] = { dDcOut, dChunkB, dChunkStart, dDcState, dJobDesc, dWindow, dCarry, dRows, dFrameDesc, dStageIn };
+    for (void* p : ptrs) { if (p) { cudaFree(p); } }
+}
+
+int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
+    const cf32* cur = dIn;
+    int n = count;
+    // ---- PowerDecimator (multirate/power_decimator.h:51-67)
+    if (decimRatio > 1 && !decimStages.empty()) {
+        std::vector<FirJob> jobs;
+        const void* data = cur;
+        for (auto& st : decimStages) {
+            FirJob j; st.fillJob(j, data, n);
+            jobs.push_back(j);
+            st.advance(n);
+            data = st.dOut; n = j.nOut;
+        }
+        const size_t bytes = jobs.size() * sizeof(FirJob);
+        if (!dJobDesc) { jobDescBytes = 16 * sizeof(FirJob); B200_CUDA(cudaMalloc(&dJobDesc, jobDescBytes)); }
+        void* hp = nullptr; int slot = 0;
+        B200_TRY(ring.acquire(bytes, &hp, &slot));
+        memcpy(hp, jobs.data(), bytes);
+        B200_CUDA(cudaMemcpyAsync(dJobDesc, hp, bytes, cudaMemcpyHostToDevice, s));
+        B200_TRY(ring.release(slot, s));
+        int maxH = 0;
+        for (size_t i = 0; i < jobs.size(); i++) {
+            B200_TRY(launchFirJobs((const FirJob*)dJobDesc + i, 1, jobs[i].nOut, 2, s));
+            maxH = std::max(maxH, jobs[i].H);
+        }
+        B200_TRY(launchHistoryUpdate((const FirJob*)dJobDesc, (int)jobs.size(), maxH, s));
+        cur = (const cf32*)data;
+    }
+    // ---- DCBlocker (+ Conjugate folded into the same pass)
+    bool conjDone = false;
+    if (dcBlocking && n > 0) {
+        if ((size_t)n > dcCap) {
+            if (dDcOut) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dDcOut); }
+            dcCap = (size_t)std::max(n, maxBlock / std::max(decimRatio, 1) + 2);
+            B200_CUDA(cudaMalloc((void**)&dDcOut, dcCap * sizeof(cf32)));
+        }
+        const int nChunks = (n + kDcChunk - 1) / kDcChunk;
+        if (nChunks > dcChunksCap) {
+            if (dChunkB) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dChunkB); cudaFree(dChunkStart); }
+            dcChunksCap = std::max(nChunks, (int)(dcCap / kDcChunk) + 2);
+            B200_CUDA(cudaMalloc((void**)&dChunkB, (size_t)dcChunksCap * sizeof(double2)));
+            B200_CUDA(cudaMalloc((void**)&dChunkStart, (size_t)dcChunksCap * sizeof(double2)));
+        }
+        DcParams p;
+        p.rate = (float)(50.0 / effectiveSr);
+        p.a = 1.0 - (double)p.rate;
+        p.aRun = pow(p.a, (double)kDcPerThread);
+        p.aChunk = pow(p.a, (double)kDcChunk);
+        dcReduceKernel<<<nChunks, kDcThreads, 0, s>>>(cur, n, p, dChunkB);
+        B200_CHECK_LAUNCH();
+        dcScanKernel<<<1, 1024, 0, s>>>(dChunkB, nChunks, n, p, dChunkStart, dDcState);
+        B200_CHECK_LAUNCH();
+        dcApplyKernel<<<nChunks, kDcThreads, 0, s>>>(cur, dDcOut, n, p, dChunkStart, invertIQ ? 1 : 0);
+        B200_CHECK_LAUNCH();
+        // state[1] -> state[0] for the next block
+        B200_CUDA(cudaMemcpyAsync(dDcState, dDcState + 1, sizeof(double2), cudaMemcpyDeviceToDevice, s));
+        countLaunch(3);
+        cur = dDcOut;
+        conjDone = invertIQ;
+    }
+    if (invertIQ && !conjDone && n > 0) {
+        if ((size_t)n > dcCap) {
+            if (dDcOut) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dDcOut); }
+            dcCap = (size_t)std::max(n, maxBlock / std::max(decimRatio, 1) + 2);
+            B200_CUDA(cudaMalloc((void**)&dDcOut, dcCap * sizeof(cf32)));
+        }
+        conjKernel<<<(n + 255) / 256, 256, 0, s>>>(cur, dDcOut, n);
+        B200_CHECK_LAUNCH();
+        countLaunch();
+        cur = dDcOut;
+    }
+    preOut = cur; preCount = n;
+    return B200_OK;
+}
+
+// Reshaper framing (buffer/reshaper.h:101-128 with skip >= 0): frame f = samples [f*I, f*I + nz)
+int FrontEnd::fftBranch(cudaStream_t s) {
+    frameIdx.clear();
+    const int64_t A = streamPos, E = streamPos + preCount;
+    std::vector<FrameDesc> descs;
+    // a frame that ends beyond this block is stashed in the carry buffer, but only after this call's FFT
+    // kernels (which may still read the carry) have been enqueued
+    const cf32* stashSrc = nullptr; int stashLen = 0, stashAt = 0;
+    while (true) {
+        const int64_t start = nextFrame * (int64_t)interval, end = start + nz;
+        const bool mine = (nextFrame % shardWorld) == shardRank;
+        if (end > E) {
+            if (start < E && mine) {
+                const int64_t from = std::max(start, A);
+                stashSrc = preOut + (from - A); stashLen = (int)(E - from); stashAt = carryLen;
+                carryLen += stashLen;
+            }
+            break;
+        }
+        if (mine) {
+            FrameDesc d;
+            const int64_t from = std::max(start, A);
+            d.src0 = dCarry; d.len0 = carryLen; d.src1 = preOut + (from - A); d.pad = 0;
+            if (carryLen == 0) { d.src0 = d.src1; }
+            descs.push_back(d);
+            frameIdx.push_back(nextFrame);
+            carryLen = 0;   // only the first frame of a call can start in the carry buffer
+        }
+        nextFrame++;
+    }
+    streamPos = E;
+    int rc = B200_OK;
+    if (!descs.empty()) {
+        if ((int)descs.size() > rowsCap) { setError("internal: %d frames exceed row capacity %d", (int)descs.size(), rowsCap); return B200_ESTATE; }
+        void* hp = nullptr; int slot = 0;
+        const size_t bytes = descs.size() * sizeof(FrameDesc);
+        B200_TRY(ring.acquire(bytes, &hp, &slot));
+        memcpy(hp, descs.data(), bytes);
+        B200_CUDA(cudaMemcpyAsync(dFrameDesc, hp, bytes, cudaMemcpyHostToDevice, s));
+        B200_TRY(ring.release(slot, s));
+        rc = plan.run(dFrameDesc, (int)descs.size(), dWindow, nz, dRows, nullptr, s);
+    }
+    if (rc == B200_OK && stashLen > 0) {
+        B200_CUDA(cudaMemcpyAsync(dCarry + stashAt, stashSrc, (size_t)stashLen * sizeof(cf32), cudaMemcpyDeviceToDevice, s));
+    }
+    return rc;
+}
+
+int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s) {
+    if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
+    DeviceGuard g(device);
+    if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
+    lastStream = s; everRan = true;
+    B200_TRY(preprocess(dIn, count, s));
+    B200_TRY(fftBranch(s));
+    if (bank->impl.liveCount() > 0) { B200_TRY(bank->impl.process(preOut, preCount, s)); }
+    return B200_OK;
+}
+
+} // namespace b200
+
+using namespace b200;
+
+struct b200_frontend { FrontEnd impl; };
+
+#define FE_OR_FAIL(f) \
+    if (!(f)) { setError("NULL front-end handle"); return B200_EINVAL; }
+
+extern "C" {
+
+int b200_frontend_create(b200_frontend** out, double sample_rate, int decim_ratio, int dc_blocking, int invert_iq,
+                         int fft_size, double fft_rate, int fft_window, int max_block, int device) {
+    if (!out || sample_rate <= 0 || max_block <= 0 || fft_rate <= 0 || fft_window < 0 || fft_window > 2) {
+        setError("bad arguments to b200_frontend_create"); return B200_EINVAL;
+    }
+    if (!design::validDecimRatio(decim_ratio)) { setError("decimation ratio %d is not a power of two <= %d", decim_ratio, design::maxDecimRatio()); return B200_EINVAL; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) { setError("no CUDA device available: libb200dsp has no CPU fallback"); return B200_ECUDA; }
+    if (device < 0 || device >= ndev) { setError("device %d out of range (%d devices)", device, ndev); return B200_EINVAL; }
+    auto* f = new (std::nothrow) b200_frontend;
+    if (!f) { return B200_ENOMEM; }
+    f->impl.device = device; f->impl.sampleRate = sample_rate; f->impl.decimRatio = decim_ratio;
+    f->impl.dcBlocking = dc_blocking != 0; f->impl.invertIQ = invert_iq != 0;
+    f->impl.fftSize = fft_size; f->impl.fftRate = fft_rate; f->impl.fftWindow = fft_window; f->impl.maxBlock = max_block;
+    int rc = f->impl.init();
+    if (rc != B200_OK) { f->impl.destroy(); delete f; return rc; }
+    *out = f;
+    return B200_OK;
+}
+
+int b200_frontend_destroy(b200_frontend* fe) {
+    FE_OR_FAIL(fe);
+    fe->impl.destroy();
+    delete fe;
+    return B200_OK;
+}
+
+// IQFrontEnd::setSampleRate (iq_frontend.cpp:90-118): new effective rate -> DC-block rate, every VFO's
+// input rate, FFT path.
+int b200_frontend_set_sample_rate(b200_frontend* fe, double sample_rate) {
+    FE_OR_FAIL(fe);
+    if (sample_rate <= 0) { setError("bad sample rate"); return B200_EINVAL; }
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    f.sampleRate = sample_rate;
+    f.effectiveSr = f.sampleRate / f.decimRatio;
+    B200_TRY(b200_vfo_bank_set_in_samplerate(f.bank, f.effectiveSr));
+    return f.updateFftPath();
+}
+
+// IQFrontEnd::setDecimation (iq_frontend.cpp:124-141)
+int b200_frontend_set_decimation(b200_frontend* fe, int ratio) {
+    FE_OR_FAIL(fe);
+    if (!design::validDecimRatio(ratio)) { setError("decimation ratio %d is not a power of two <= %d", ratio, design::maxDecimRatio()); return B200_EINVAL; }
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    f.decimRatio = ratio;
+    if (ratio > 1) { B200_TRY(f.rebuildDecim()); }   // decim.setRatio() only when > 1 (:130)
+    return b200_frontend_set_sample_rate(fe, f.sampleRate);
+}
+
+int b200_frontend_set_dc_blocking(b200_frontend* fe, int enabled) { FE_OR_FAIL(fe); fe->impl.dcBlocking = enabled != 0; return B200_OK; }
+int b200_frontend_set_invert_iq(b200_frontend* fe, int enabled) { FE_OR_FAIL(fe); fe->impl.invertIQ = enabled != 0; return B200_OK; }
+
+int b200_frontend_set_fft_size(b200_frontend* fe, int size) {
+    FE_OR_FAIL(fe);
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    const int old = f.fftSize;
+    f.fftSize = size;
+    int rc = f.updateFftPath();
+    if (rc != B200_OK) { f.fftSize = old; f.updateFftPath(); }
+    return rc;
+}
+
+int b200_frontend_set_fft_rate(b200_frontend* fe, double rate) {
+    FE_OR_FAIL(fe);
+    if (rate <= 0) { setError("bad fft rate"); return B200_EINVAL; }
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    f.fftRate = rate;
+    return f.updateFftPath();
+}
+
+int b200_frontend_set_fft_window(b200_frontend* fe, int window) {
+    FE_OR_FAIL(fe);
+    if (window < 0 || window > 2) { setError("bad window type"); return B200_EINVAL; }
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    f.fftWindow = window;
+    return f.updateFftPath();
+}
+
+double b200_frontend_effective_samplerate(b200_frontend* fe) { return fe ? fe->impl.effectiveSr : 0.0; }
+
+int b200_frontend_set_frame_shard(b200_frontend* fe, int rank, int world) {
+    FE_OR_FAIL(fe);
+    if (world < 1 || rank < 0 || rank >= world) { setError("bad shard %d of %d", rank, world); return B200_EINVAL; }
+    fe->impl.shardRank = rank; fe->impl.shardWorld = world;
+    return B200_OK;
+}
+
+b200_vfo_bank* b200_frontend_vfo_bank(b200_frontend* fe) { return fe ? fe->impl.bank : nullptr; }
+
+int b200_frontend_process(b200_frontend* fe, const float* d_in, int count, void* stream) {
+    FE_OR_FAIL(fe);
+    if (!d_in && count > 0) { setError("NULL input"); return B200_EINVAL; }
+    return fe->impl.process((const cf32*)d_in, count, (cudaStream_t)stream);
+}
+
+int b200_frontend_preproc_out(b200_frontend* fe, const float** d_out, int* count) {
+    FE_OR_FAIL(fe);
+    if (d_out) { *d_out = (const float*)fe->impl.preOut; }
+    if (count) { *count = fe->impl.preCount; }
+    return B200_OK;
+}
+
+int b200_frontend_frame_count(b200_frontend* fe) { FE_OR_FAIL(fe); return (int)fe->impl.frameIdx.size(); }
+
+const float* b200_frontend_frame_ptr(b200_frontend* fe, int i) {
+    if (!fe || i < 0 || i >= (int)fe->impl.frameIdx.size()) { return nullptr; }
+    return fe->impl.dRows + (size_t)i * fe->impl.fftSize;
+}
+
+int64_t b200_frontend_frame_index(b200_frontend* fe, int i) {
+    if (!fe || i < 0 || i >= (int)fe->impl.frameIdx.size()) { return -1; }
+    return fe->impl.frameIdx[i];
+}
+
+int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
+                               float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
+    FE_OR_FAIL(fe);
+    FrontEnd& f = fe->impl;
+    if (count < 0 || count > f.maxBlock) { setError("block of %d samples exceeds max_block %d", count, f.maxBlock); return B200_ETOOBIG; }
+    if (!h_in && count > 0) { setError("NULL input"); return B200_EINVAL; }
+    DeviceGuard g(f.device);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!f.dStageIn) { B200_CUDA(cudaMalloc((void**)&f.dStageIn, (size_t)f.maxBlock * sizeof(cf32))); }
+    B200_CUDA(cudaMemcpyAsync(f.dStageIn, h_in, (size_t)count * sizeof(cf32), cudaMemcpyHostToDevice, s));
+    B200_TRY(f.process(f.dStageIn, count, s));
+    const int nf = std::min((int)f.frameIdx.size(), max_frames);
+    if (h_frames && nf > 0) {
+        B200_CUDA(cudaMemcpyAsync(h_frames, f.dRows, (size_t)nf * f.fftSize * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    VfoBank& b = f.bank->impl;
+    for (size_t i = 0; i < b.vfos.size(); i++) {
+        const Vfo& v = b.vfos[i];
+        if (!v.live) { continue; }
+        if (vfo_counts) { vfo_counts[i] = v.lastOut; }
+        if (v.lastOut <= 0) { continue; }
+        if (h_vfo_out && h_vfo_out[i]) {
+            B200_CUDA(cudaMemcpyAsync(h_vfo_out[i], v.lastOutPtr, (size_t)v.lastOut * sizeof(cf32), cudaMemcpyDeviceToHost, s));
+        }
+        if (h_audio && h_audio[i]) {
+            const float* ap = b200_vfo_audio_ptr(f.bank, (int)i);
+            if (ap) { B200_CUDA(cudaMemcpyAsync(h_audio[i], ap, (size_t)v.lastOut * 2 * sizeof(float), cudaMemcpyDeviceToHost, s)); }
+        }
+    }
+    B200_CUDA(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+// complex spectrum of one already-windowed frame (tests of the FFT alone)
+int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream) {
+    if (!d_in || !d_out || nz <= 0 || nz > fft_size) { setError("bad arguments to b200_fft_forward"); return B200_EINVAL; }
+    int dev = 0;
+    B200_CUDA(cudaGetDevice(&dev));
+    FftPlan plan;
+    int rc = plan.create(fft_size, dev);
+    if (rc != B200_OK) { return rc; }
+    FrameDesc d; d.src0 = (const cf32*)d_in; d.src1 = (const cf32*)d_in; d.len0 = nz; d.pad = 0;
+    FrameDesc* dd = nullptr;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaMalloc((void**)&dd, sizeof(FrameDesc)) != cudaSuccess) { plan.destroy(); setError("cudaMalloc failed"); return B200_ENOMEM; }
+    cudaMemcpyAsync(dd, &d, sizeof(FrameDesc), cudaMemcpyHostToDevice, s);
+    rc = plan.run(dd, 1, nullptr, nz, nullptr, (cf32*)d_out, s);
+    cudaStreamSynchronize(s);
+    cudaFree(dd);
+    plan.destroy();
+    return rc;
+}
+
+} // extern "C"

@@ -1,0 +1,201 @@
+"""GPU parity: IQ front end (pre-processing, FFT frames, waterfall zoom/palette) against the oracle.
+
+Tolerances (SURVEY §8c / BASELINE.md §4): pre-processed stream -80 dB per block, counts exact;
+complex spectrum -80 dB vs the float64 oracle FFT; dB rows within 0.01 dB for bins within 80 dB of the
+frame peak; zoomed rows select identical bins; palette index +-1."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases
+import oracle_lib as ol
+from gpu_util import err_db, split, to_dev
+from sdrplusplusbrown_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+PORT = ol.Oracle("port")
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _fe(*a, **k):
+    from sdrplusplusbrown_b200 import binding
+    return binding.FrontEnd(*a, **k)
+
+
+@pytest.mark.parametrize("cfg", [(1, 1, 0), (4, 1, 1), (16, 0, 0), (2, 1, 0), (1, 0, 1), (1, 0, 0), (64, 1, 0)])
+def test_preproc_chain_matches_oracle(cfg):
+    dec, dc, inv = cfg
+    sr = 8e6
+    x = synth.make_iq(0, 200000, sr, tones=[(1e6, 0.1)], dc=(0.05, -0.08))
+    o = ol.Preproc(PORT, sr, dec, dc, inv)
+    fe = _fe(sr, decim_ratio=dec, dc_blocking=bool(dc), invert_iq=bool(inv), fft_size=1024, fft_rate=20.0, max_block=70000)
+    for blk in split(x, [65536, 7001, 33]):
+        ref = o.process(blk)
+        fe.process(to_dev(blk))
+        got = fe.preproc_out()
+        assert len(got) == len(ref)
+        if len(ref):
+            assert err_db(got, ref) <= -80.0, cfg
+
+
+def test_dc_blocker_long_stream_state_carry():
+    sr = 20e6
+    o = ol.Preproc(PORT, sr, 1, 1, 0)
+    fe = _fe(sr, dc_blocking=True, fft_size=1024, fft_rate=60.0)
+    for i in range(3):
+        blk = synth.make_iq(i * 1000000, 1000000, sr, dc=(0.2, -0.1))
+        ref = o.process(blk)
+        fe.process(to_dev(blk))
+        assert err_db(fe.preproc_out(), ref) <= -80.0
+
+
+@pytest.mark.parametrize("N", [32, 256, 1024, 8192, 16384, 65536, 1 << 18, 1 << 20])
+def test_fft_complex_spectrum(N):
+    from sdrplusplusbrown_b200 import binding
+    import torch
+    nz = N if N < 4096 else N - 37
+    x = synth.make_iq(0, nz, 2.4e6, tones=[(300e3, 0.2), (-777e3, 0.05)])
+    d_out = torch.empty((N, 2), dtype=torch.float32, device="cuda")
+    binding.fft_forward(to_dev(x), nz, N, d_out)
+    got = d_out.cpu().numpy().view(np.complex64).reshape(-1)
+    xw = np.zeros(N, np.complex128)
+    xw[:nz] = x
+    ref = np.fft.fft(xw)
+    assert err_db(got, ref) <= -80.0
+
+
+FFT_CASES = [
+    (2.4e6, 8192, 20.0, 2, [12000]),            # cfg1: nz = N, 20 fps
+    (20e6, 65536, 60.0, 1, [1000000]),          # cfg2: two-pass, I = 333333
+    (48e3, 4096, 20.0, 0, [1000, 777]),         # nz (2400) < N, frames straddle blocks
+    (2.4e6, 1024, 2000.0, 1, [5000]),           # nz == I (no skip): back-to-back frames
+]
+
+
+@pytest.mark.parametrize("case", FFT_CASES)
+def test_fft_frames_match_oracle(case):
+    sr, N, rate, wt, sizes = case
+    skip, nz = PORT.reshape_params(sr, N, rate)
+    interval = nz + skip
+    n = interval * 3 + nz + 17
+    x = synth.make_iq(0, n, sr, tones=[(0.11 * sr, 0.2), (-0.31 * sr, 0.01)])
+    w = PORT.fft_window(wt, nz)
+    fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=wt, max_block=max(sizes))
+    rows, idx = [], []
+    for blk in split(x, sizes):
+        fe.process(to_dev(blk))
+        for i, r in enumerate(fe.frames()):
+            rows.append(r)
+            idx.append(fe.frame_index(i))
+    assert idx == list(range(4))
+    for f, row in zip(idx, rows):
+        ref = PORT.fft_frame(x[f * interval:f * interval + nz], w, N)
+        strong = ref > ref.max() - 80.0
+        assert np.max(np.abs(row[strong] - ref[strong])) <= 0.01
+        assert np.all(np.isfinite(row))
+
+
+def test_fft_zero_input_reads_clamped_floor():
+    fe = _fe(48e3, fft_size=1024, fft_rate=40.0, fft_window=0, max_block=4096)
+    fe.process(to_dev(np.zeros(2400, np.complex64)))
+    rows = fe.frames()
+    assert len(rows) == 2
+    assert np.allclose(rows[0], -382.3, atol=0.1)   # VOLK generic: log2(0) clamped to -127
+
+
+def test_fft_frame_sharding_partitions_frames():
+    sr, N, rate = 2.4e6, 1024, 2000.0
+    x = synth.make_iq(0, 1200 * 9, sr, tones=[(1e5, 0.1)])
+    full = _fe(sr, fft_size=N, fft_rate=rate, max_block=20000)
+    full.process(to_dev(x))
+    all_rows = full.frames()
+    assert len(all_rows) == 9
+    seen = {}
+    for r in range(2):
+        fe = _fe(sr, fft_size=N, fft_rate=rate, max_block=20000)
+        fe.set_frame_shard(r, 2)
+        for blk in split(x, [5000, 3333]):
+            fe.process(to_dev(blk))
+            for i, row in enumerate(fe.frames()):
+                seen[fe.frame_index(i)] = row
+    assert sorted(seen) == list(range(9))
+    for f in range(9):
+        assert np.max(np.abs(seen[f] - all_rows[f])) <= 1e-4
+
+
+@pytest.mark.parametrize("name", sorted(golden_cases.FFT_GOLDEN))
+def test_fft_zoom_palette_against_golden(name):
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    sr, N, rate, wt, zoom, lo, hi = golden_cases.FFT_GOLDEN[name]
+    x, nz = golden_cases.fft_input(name)
+    fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=wt, max_block=max(nz, 1024))
+    fe.process(to_dev(x))
+    assert fe.frame_count() == 1
+    row = fe.frames()[0]
+    stride = max(1, N // 4096)
+    ref_sub = g["db_sub"]
+    strong = ref_sub > g["db_peak"][0] - 80.0
+    assert np.max(np.abs(row[::stride][strong] - ref_sub[strong])) <= 0.01
+    assert int(np.argmax(row)) == int(g["db_peak"][1])
+    wf = binding.Waterfall(N, zoom[2])
+    wf.set_view(zoom[0], zoom[1])
+    wf.set_range(lo, hi)
+    sid, uf = wf.zoom_table()
+    assert np.array_equal(sid, g["zoom_sid"]) and np.array_equal(uf, g["zoom_uf"])   # identical bin selection
+    d_zoom = torch.empty(zoom[2], dtype=torch.float32, device="cuda")
+    d_rgba = torch.empty(zoom[2], dtype=torch.int32, device="cuda")
+    colors = np.array([[0, 0, 0], [255, 255, 255]], np.float32)
+    lut = binding.Waterfall.make_palette(colors)
+    assert np.array_equal(lut, PORT.make_palette(colors))
+    wf.set_palette(np.arange(1000, dtype=np.uint32))    # identity LUT: rgba output = palette index
+    wf.push(fe.frame_ptr(0), 1, d_zoom.data_ptr(), d_rgba.data_ptr())
+    z = d_zoom.cpu().numpy()
+    zs = g["zoom"] > g["db_peak"][0] - 80.0
+    assert np.max(np.abs(z[zs] - g["zoom"][zs])) <= 0.01
+    pal = d_rgba.cpu().numpy()
+    assert np.max(np.abs(pal[zs] - g["palette"][zs])) <= 1
+    # and the device zoom is exactly the max over the reference's bins of the device row
+    ref_z = np.array([row[a:a + b].max() for a, b in zip(sid, uf)], np.float32)
+    assert np.array_equal(z, ref_z)
+
+
+def test_preproc_against_golden():
+    g = np.load(os.path.join(GOLDEN, "preproc.npz"))
+    x = golden_cases.preproc_input()
+    for tag, (dec, dc, inv) in dict(dc=(1, 1, 0), d4_dc_inv=(4, 1, 1), d16=(16, 0, 0)).items():
+        fe = _fe(8e6, decim_ratio=dec, dc_blocking=bool(dc), invert_iq=bool(inv), fft_size=1024, fft_rate=20.0, max_block=8192)
+        outs = []
+        for blk in split(x, [7000]):
+            fe.process(to_dev(blk))
+            outs.append(fe.preproc_out())
+        got = np.concatenate(outs)
+        assert len(got) == len(g["out_" + tag])
+        assert err_db(got, g["out_" + tag]) <= -80.0
+
+
+def test_frontend_feeds_vfos_and_fft_together():
+    """cfg1 end to end: 2.4 MS/s, 8192-pt Nuttall FFT at 20 fps + one NFM VFO, file-source block size 12000."""
+    sr = 2.4e6
+    x = synth.make_iq(0, 240000, sr, tones=[(100e3 + 1e3, 0.05)])
+    fe = _fe(sr, fft_size=8192, fft_rate=20.0, fft_window=2, max_block=12000)
+    v = fe.vfos.add(50e3, 12.5e3, 100e3)
+    o = ol.Vfo(PORT, sr, 50e3, 12.5e3, 100e3)
+    w = PORT.fft_window(2, 8192)
+    nframes = 0
+    for i, blk in enumerate(split(x, [12000])):
+        fe.vfos.set_phase(v, o.phase())
+        ref = o.process(blk)
+        fe.process(to_dev(blk))
+        assert fe.vfos.out_count(v) == len(ref) == 250
+        assert err_db(fe.vfos.output(v), ref) <= -80.0
+        for j, row in enumerate(fe.frames()):
+            f = fe.frame_index(j)
+            refrow = PORT.fft_frame(x[f * 120000:f * 120000 + 8192], w, 8192)
+            strong = refrow > refrow.max() - 80.0
+            assert np.max(np.abs(row[strong] - refrow[strong])) <= 0.01
+            nframes += 1
+    assert nframes == 2

@@ -1,0 +1,225 @@
+"""GPU parity: RxVFO bank (CUDA, through the C ABI) against the oracle.
+
+Tolerance (BASELINE.json north_star): per-block output error at least 80 dB below the block's
+signal RMS; sample counts and decimation phase bit-exact.  The rotator phase is taken from the oracle
+at each block start (SURVEY §7 recipe: the reference's phase is a chaotic fp32 recursion; the
+free-running drift is checked separately with a looser, reported bound)."""
+import os
+
+import numpy as np
+import pytest
+
+import golden_cases
+import oracle_lib as ol
+from gpu_util import err_db, split, to_dev
+from sdrplusplusbrown_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+TOL_DB = -80.0
+PORT = ol.Oracle("port")
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _bank(in_sr, max_block=1000000):
+    from sdrplusplusbrown_b200 import binding
+    return binding.VfoBank(in_sr, max_block=max_block)
+
+
+CASES = [
+    # in_sr, out_sr, bw, offset, n, block sizes
+    (2.4e6, 50e3, 12.5e3, 100e3, 120000, [12000]),
+    (2.4e6, 50e3, 12.5e3, -431e3, 100000, [7777, 333, 20000]),
+    (20e6, 24e3, 2.8e3, 1.25e6, 1000000, [500000]),
+    (61.44e6, 48e3, 12.5e3, -3.3e6, 1000000, [1000000]),
+    (61.44e6, 50e3, 12.5e3, 27.1e6, 600000, [65536]),
+    (122.88e6, 15e3, 10e3, 7.7e6, 1000000, [250000]),
+    (122.88e6, 24e3, 2.8e3, -31.0e6, 1000000, [333333]),
+    (122.88e6, 500e3, 150e3, -20e6, 300000, [100000]),
+    (48e3, 48e3, 48e3, 1e3, 20000, [5000]),          # NONE, filter bypassed: pure rotation
+    (24e3, 48e3, 12e3, 500.0, 20000, [4096]),        # RESAMP_ONLY, interpolating
+    (1e6, 250e3, 200e3, 10e3, 50000, [9999]),        # /4 plan (unfused small-D first stage), no resampler
+    (8e6, 2e6, 2e6, -1e6, 50000, [8192]),            # DECIM_ONLY, filter bypassed
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_vfo_matches_oracle_per_block(case):
+    in_sr, out_sr, bw, off, n, sizes = case
+    x = synth.make_iq(0, n, in_sr, tones=[(off + 0.1 * bw, 0.05), (off + 40 * bw, 0.3)])
+    o = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    b = _bank(in_sr, max_block=max(sizes))
+    v = b.add(out_sr, bw, off)
+    d_o, d_g = o.describe(), b.describe(v)
+    for k in ("mode", "ratio", "interp", "decim", "resamp_taps", "taps_per_phase", "chan_taps"):
+        assert d_o[k] == d_g[k], (k, d_o, d_g)
+    # tap tables bit-identical to the reference designers
+    if d_o["resamp_taps"]:
+        assert np.array_equal(b.taps(v, 0).view(np.uint32), o.resamp_taps().view(np.uint32))
+    if d_o["chan_taps"]:
+        assert np.array_equal(b.taps(v, 1).view(np.uint32), o.chan_taps().view(np.uint32))
+    worst = -np.inf
+    for blk in split(x, sizes):
+        b.set_phase(v, o.phase())
+        ref = o.process(blk)
+        b.process(to_dev(blk))
+        assert b.out_count(v) == len(ref)            # bit-exact count / decimation phase
+        got = b.output(v)
+        if len(ref):
+            e = err_db(got, ref)
+            worst = max(worst, e)
+            assert e <= TOL_DB, (e, len(ref))
+    print("worst block error %.1f dB" % worst)
+
+
+def test_vfo_free_running_phase_drift_is_bounded():
+    """No re-sync: the calibrated float64 phase accumulator must track the reference's fp32 recursion.
+    Reported (looser) bound: -60 dB after 4 M samples at 61.44 MS/s."""
+    in_sr, out_sr, bw, off = 61.44e6, 48e3, 12.5e3, 5e6
+    o = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    b = _bank(in_sr)
+    v = b.add(out_sr, bw, off)
+    errs = []
+    for i in range(4):
+        blk = synth.make_iq(i * 1000000, 1000000, in_sr, tones=[(off + 1000.0, 0.1)])
+        ref = o.process(blk)
+        b.process(to_dev(blk))
+        assert b.out_count(v) == len(ref)
+        errs.append(err_db(b.output(v), ref))
+    print("free-running block errors (dB):", ["%.1f" % e for e in errs])
+    assert max(errs) <= -60.0
+
+
+def test_bank_of_many_vfos_one_launch_sequence():
+    """32 NFM VFOs + mixed modes on the same input: every VFO equals its own single-VFO oracle."""
+    in_sr, n = 61.44e6, 400000
+    rng = np.random.default_rng(7)
+    specs = [(48e3, 12.5e3, float(f)) for f in rng.uniform(-28e6, 28e6, 12)] + \
+            [(15e3, 10e3, 3.1e6), (24e3, 2.8e3, -9.9e6), (500e3, 150e3, 12e6), (50e3, 12.5e3, -1e6)]
+    x = synth.make_iq(0, n, in_sr, tones=[(s[2] + 500.0, 0.02) for s in specs])
+    b = _bank(in_sr)
+    ids = [b.add(*s) for s in specs]
+    oracles = [ol.Vfo(PORT, in_sr, *s) for s in specs]
+    for blk in split(x, [150000, 250000]):
+        for i, o in zip(ids, oracles):
+            b.set_phase(i, o.phase())
+        d = to_dev(blk)
+        b.process(d)
+        for i, o in zip(ids, oracles):
+            ref = o.process(blk)
+            assert b.out_count(i) == len(ref)
+            assert err_db(b.output(i), ref) <= TOL_DB
+
+
+def test_vfo_reconfiguration_matches_oracle():
+    """setOffset / setBandwidth / setOutSamplerate / reset / setInSamplerate between blocks."""
+    in_sr = 2.4e6
+    x = synth.make_iq(0, 108000, in_sr, tones=[(100e3, 0.1), (-50e3, 0.1)])
+    o = ol.Vfo(PORT, in_sr, 50e3, 12.5e3, 100e3)
+    b = _bank(in_sr)
+    v = b.add(50e3, 12.5e3, 100e3)
+    for i, blk in enumerate(split(x, [12000])):
+        if i == 2:
+            o.set_offset(-50e3); b.set_offset(v, -50e3)
+        if i == 3:
+            o.set_bandwidth(8000.0); b.set_bandwidth(v, 8000.0)
+        if i == 4:
+            o.set_out_samplerate(24e3, 2.8e3); b.set_out_samplerate(v, 24e3, 2.8e3)
+        if i == 5:
+            o.set_bandwidth(24e3); b.set_bandwidth(v, 24e3)     # filter bypass
+        if i == 6:
+            o.reset(); b.reset(v)
+        if i == 7:
+            o.set_in_samplerate(1.2e6); b.set_in_samplerate(1.2e6)
+        b.set_phase(v, o.phase())
+        ref = o.process(blk)
+        b.process(to_dev(blk))
+        assert b.out_count(v) == len(ref), i
+        if len(ref):
+            assert err_db(b.output(v), ref) <= TOL_DB, i
+
+
+def test_ragged_and_empty_blocks():
+    in_sr, out_sr, bw, off = 2.4e6, 50e3, 12.5e3, 100e3
+    x = synth.make_iq(0, 30000, in_sr, tones=[(off, 0.1)])
+    o = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    b = _bank(in_sr)
+    v = b.add(out_sr, bw, off)
+    total = 0
+    for blk in split(x, [1, 0, 7, 31, 0, 4096, 1, 12000]):
+        b.set_phase(v, o.phase())
+        ref = o.process(blk) if len(blk) else np.zeros(0, np.complex64)
+        if len(blk):
+            b.process(to_dev(blk))
+        else:
+            b.process(to_dev(np.zeros(1, np.complex64)), count=0)
+        assert b.out_count(v) == len(ref)
+        total += len(ref)
+        if len(ref):
+            assert err_db(b.output(v), ref) <= TOL_DB
+    assert total == 625
+
+
+def test_max_block_is_enforced():
+    from sdrplusplusbrown_b200 import binding
+    b = _bank(2.4e6, max_block=1000)
+    b.add(50e3, 12.5e3, 0.0)
+    with pytest.raises(binding.B200Error):
+        b.process(to_dev(np.zeros(1001, np.complex64)))
+
+
+def test_host_buffer_entry_point():
+    in_sr, out_sr, bw, off = 2.4e6, 50e3, 12.5e3, 100e3
+    x = synth.make_iq(0, 48000, in_sr, tones=[(off + 700.0, 0.1)])
+    o = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    b = _bank(in_sr)
+    v = b.add(out_sr, bw, off)
+    for blk in split(x, [12000]):
+        b.set_phase(v, o.phase())
+        ref = o.process(blk)
+        got = b.process_host(blk, [v])[v]
+        assert len(got) == len(ref) and err_db(got, ref) <= TOL_DB
+
+
+@pytest.mark.parametrize("name", sorted(golden_cases.VFO_GOLDEN))
+def test_vfo_against_golden_vectors(name):
+    """Committed fixtures generated from the reference's own headers (tests/golden/make_golden.py)."""
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    in_sr, out_sr, bw, off, n, blk, tone = golden_cases.VFO_GOLDEN[name]
+    x = golden_cases.vfo_input(name)
+    b = _bank(in_sr)
+    v = b.add(out_sr, bw, off)
+    pos = 0
+    for i, blkx in enumerate(split(x, [blk])):
+        b.set_phase(v, complex(g["phases"][i]))
+        b.process(to_dev(blkx))
+        c = int(g["counts"][i])
+        assert b.out_count(v) == c
+        if c:
+            assert err_db(b.output(v), g["out"][pos:pos + c]) <= TOL_DB
+        pos += c
+    assert pos == len(g["out"])
+
+
+def test_chunk_invariance_at_full_size():
+    """Size-independent property at BASELINE sizes: 8 M samples at 61.44 MS/s cut three ways give identical
+    counts and the same output within tolerance (the reference's chunking invariance)."""
+    in_sr, out_sr, bw, off = 61.44e6, 48e3, 12.5e3, 4.2e6
+    n = 8000000
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    d = synth.make_iq_torch(n, in_sr, "cuda", tones=[(off + 1500.0, 0.05)])
+    outs = []
+    for sizes in ([1000000], [777777, 65536], [4000000]):
+        b = binding.VfoBank(in_sr, max_block=max(sizes))
+        v = b.add(out_sr, bw, off)
+        parts, i, k = [], 0, 0
+        while i < n:
+            m = min(sizes[k % len(sizes)], n - i)
+            b.process(d[i:i + m])
+            parts.append(b.output(v))
+            i += m
+            k += 1
+        outs.append(np.concatenate(parts))
+    assert len(outs[0]) == len(outs[1]) == len(outs[2]) == 6250
+    assert err_db(outs[1], outs[0]) <= TOL_DB and err_db(outs[2], outs[0]) <= TOL_DB
