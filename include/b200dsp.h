@@ -75,6 +75,24 @@ int b200_vfo_reset(b200_vfo_bank* bank, int vfo);                               
 int b200_vfo_get_phase(b200_vfo_bank* bank, int vfo, double* re, double* im);
 int b200_vfo_set_phase(b200_vfo_bank* bank, int vfo, double re, double im);
 
+/* How the per-sample rotator phase is produced (DESIGN.md "rotator"):
+ *   B200_ROTATOR_FAST  (default) closed form in float64 from a step calibrated against the reference's
+ *       fp32 recursion at every retune.  Fully parallel; matches the reference to better than -80 dB per
+ *       block of <= 1 M samples when the block starts from the reference's phase.
+ *   B200_ROTATOR_EXACT one GPU thread per VFO replays VOLK's generic recursion bit for bit (phase *= delta,
+ *       renormalise every 512 samples of a call) and the kernels interpolate between its checkpoints.
+ *       Tracks the reference free-running for any offset and any stream length; sequential, so a stream
+ *       advances at most ~230 MS/s (still above every configuration's real-time rate). */
+#define B200_ROTATOR_FAST 0
+#define B200_ROTATOR_EXACT 1
+int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
+/* Tuning/test switches: B200_OPT_FUSED_STAGE1 (1 = fused xlate+decimate kernel where available, default;
+ * 0 = separate rotation and generic FIR kernels, process-wide), B200_OPT_CALIBRATION_STEPS (length of the
+ * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step). */
+#define B200_OPT_FUSED_STAGE1 1
+#define B200_OPT_CALIBRATION_STEPS 2
+int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
+
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)
  * [1]=power-of-two ratio [2]=interp [3]=decim [4]=resampler tap count [5]=taps per phase
  * [6]=channel-filter tap count (0 when bypassed, rx_vfo.h:24,91-93) [7]=1 if stage 1 runs fused */

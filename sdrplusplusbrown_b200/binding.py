@@ -37,6 +37,8 @@ _SIGS = {
     "b200_vfo_get_phase": (_i, [_vp, _i, C.POINTER(_d), C.POINTER(_d)]),
     "b200_vfo_set_phase": (_i, [_vp, _i, _d, _d]),
     "b200_vfo_describe": (_i, [_vp, _i, _vp]),
+    "b200_vfo_bank_set_rotator_mode": (_i, [_vp, _i]),
+    "b200_vfo_bank_set_option": (_i, [_vp, _i, _i]),
     "b200_vfo_get_taps": (_i, [_vp, _i, _i, _vp, _i]),
     "b200_vfo_bank_process": (_i, [_vp, _vp, _i, _vp]),
     "b200_vfo_out_count": (_i, [_vp, _i]),
@@ -79,6 +81,11 @@ for _name, (_res, _args) in _SIGS.items():
     _fn = getattr(lib, _name)
     _fn.restype = _res
     _fn.argtypes = _args
+
+
+ROTATOR_FAST, ROTATOR_EXACT = 0, 1
+OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS = 1, 2
+DEMOD_NONE, DEMOD_NFM, DEMOD_AM, DEMOD_USB, DEMOD_LSB, DEMOD_DSB = 0, 1, 2, 3, 4, 5
 
 
 class B200Error(RuntimeError):
@@ -155,6 +162,8 @@ class VfoBank:
         return complex(re.value, im.value)
 
     def set_phase(self, v, z): _chk(lib.b200_vfo_set_phase(self.h, v, float(z.real), float(z.imag)))
+    def set_rotator_mode(self, mode): _chk(lib.b200_vfo_bank_set_rotator_mode(self.h, int(mode)))
+    def set_option(self, opt, value): _chk(lib.b200_vfo_bank_set_option(self.h, int(opt), int(value)))
 
     def describe(self, v):
         info = np.zeros(8, np.int32)

@@ -106,16 +106,32 @@ int b200_vfo_get_phase(b200_vfo_bank* bank, int vfo, double* re, double* im) {
     BANK_OR_FAIL(bank);
     B200_TRY(bank->impl.check(vfo));
     if (!re || !im) { return B200_EINVAL; }
-    *re = cos(bank->impl.vfos[vfo].angle); *im = sin(bank->impl.vfos[vfo].angle);
-    return B200_OK;
+    return bank->impl.getPhase(bank->impl.vfos[vfo], re, im);
 }
 
 int b200_vfo_set_phase(b200_vfo_bank* bank, int vfo, double re, double im) {
     BANK_OR_FAIL(bank);
     B200_TRY(bank->impl.check(vfo));
     if (re == 0.0 && im == 0.0) { setError("zero phasor"); return B200_EINVAL; }
-    bank->impl.vfos[vfo].angle = atan2(im, re);
-    return B200_OK;
+    return bank->impl.setPhase(bank->impl.vfos[vfo], re, im);
+}
+
+int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode) {
+    BANK_OR_FAIL(bank);
+    return bank->impl.setRotatorMode(mode);
+}
+
+int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
+    BANK_OR_FAIL(bank);
+    if (option == B200_OPT_FUSED_STAGE1) { fusedEnabled = value != 0; return B200_OK; }
+    if (option == B200_OPT_CALIBRATION_STEPS) {
+        if (value < 0) { setError("bad calibration length"); return B200_EINVAL; }
+        bank->impl.calSteps = value;
+        for (auto& v : bank->impl.vfos) { v.calDirty = true; }
+        return B200_OK;
+    }
+    setError("unknown option %d", option);
+    return B200_EINVAL;
 }
 
 int b200_vfo_describe(b200_vfo_bank* bank, int vfo, int* info) {
@@ -131,7 +147,7 @@ int b200_vfo_describe(b200_vfo_bank* bank, int vfo, int* info) {
     info[4] = hasRes ? v.resampTapCount : 0;
     info[5] = hasRes ? v.poly.T : 0;
     info[6] = v.filterNeeded ? v.chan.T : 0;
-    info[7] = (hasDecim && !v.decimStages.empty() && fusedStageSupported(v.decimStages[0])) ? 1 : 0;
+    info[7] = (hasDecim && !v.decimStages.empty() && fusedStageSupported(v)) ? 1 : 0;
     return B200_OK;
 }
 

@@ -23,7 +23,7 @@ namespace tables {
 #define DECIM_ROW(...) __VA_ARGS__,
 #define DECIM_TABLE_END };
 #define DECIM_PLAN_BEGIN(ratio, nstages)
-#define DECIM_STAGE(decim, name, ntaps)
+#define DECIM_STAGE(index, decim, name, ntaps)
 #define DECIM_PLAN_END
 #include "decim_tables.inc"
 #undef DECIM_TABLE_U32
@@ -37,7 +37,7 @@ static const PlanDef kPlans[] = {
 #define DECIM_ROW(...)
 #define DECIM_TABLE_END
 #define DECIM_PLAN_BEGIN(ratio, nstages) { ratio, nstages, {
-#define DECIM_STAGE(decim, name, ntaps) { decim, name, ntaps },
+#define DECIM_STAGE(index, decim, name, ntaps) { decim, name, ntaps },
 #define DECIM_PLAN_END } },
 #include "decim_tables.inc"
 #undef DECIM_TABLE_U32

@@ -124,9 +124,11 @@ void VfoBank::destroy() {
         for (auto& st : v.decimStages) { st.destroy(); }
         v.poly.destroy(); v.chan.destroy();
         if (v.dZ) { cudaFree(v.dZ); }
+        freeRotator(v);
         demodDestroy(v.demod); v.demod = nullptr;
     }
     vfos.clear();
+    if (dDemodDesc) { cudaFree(dDemodDesc); dDemodDesc = nullptr; }
     ring.destroy();
     if (dDesc) { cudaFree(dDesc); dDesc = nullptr; }
     if (hPinnedIn) { cudaFreeHost(hPinnedIn); hPinnedIn = nullptr; }
@@ -155,6 +157,7 @@ int VfoBank::configureXlator(Vfo& v) {
     const double w = design::hzToRads(-v.offset, inSR);
     v.dRe = (float)cos(w); v.dIm = (float)sin(w);
     v.calDirty = true;
+    v.tableDirty = true;
     return B200_OK;
 }
 
@@ -192,11 +195,6 @@ int VfoBank::reconfigureResampler(Vfo& v) {
         v.hasPoly = false;
     }
     if (v.chanCreated) { B200_TRY(v.chan.ensureOutCap(cap)); }
-    // rotated-block buffer for the unfused path
-    if (!v.dZ) {
-        v.zCap = maxBlock;
-        B200_CUDA(cudaMalloc((void**)&v.dZ, (size_t)v.zCap * sizeof(cf32)));
-    }
     return B200_OK;
 }
 
@@ -241,7 +239,8 @@ int VfoBank::addVfo(double outSR, double bw, double offset) {
     v.filterNeeded = (bw != outSR);                 // rx_vfo.h:24
     v.angle = 0.0;                                  // phase = 1 + 0i
     configureXlator(v);
-    int rc = reconfigureResampler(v);
+    int rc = allocRotator(v);
+    if (rc == B200_OK) { rc = reconfigureResampler(v); }
     if (rc == B200_OK) { rc = regenChannelTaps(v, true); }
     if (rc != B200_OK) { removeVfo(idx); return rc; }
     return idx;
@@ -256,13 +255,14 @@ int VfoBank::removeVfo(int vi) {
     v.decimStages.clear();
     v.poly.destroy(); v.chan.destroy();
     if (v.dZ) { cudaFree(v.dZ); v.dZ = nullptr; }
+    freeRotator(v);
     demodDestroy(v.demod); v.demod = nullptr;
     v.live = false;
     return B200_OK;
 }
 
 int VfoBank::resetVfo(Vfo& v) {
-    v.angle = 0.0;                                  // FrequencyXlator::reset (frequency_xlator.h:35-41)
+    B200_TRY(setPhase(v, 1.0, 0.0));                // FrequencyXlator::reset (frequency_xlator.h:35-41)
     for (auto& st : v.decimStages) { B200_TRY(st.resetState()); }
     if (v.hasPoly) { B200_TRY(v.poly.resetState()); }
     B200_TRY(v.chan.resetState());                  // FIR::reset (fir.h:56-62)
@@ -293,23 +293,81 @@ int VfoBank::calibrateDirty() {
     return B200_OK;
 }
 
+int VfoBank::allocRotator(Vfo& v) {
+    v.chkCap = maxBlock / kRotChunk + 2;
+    B200_CUDA(cudaMalloc((void**)&v.dChk, (size_t)v.chkCap * sizeof(float2)));
+    B200_CUDA(cudaMalloc((void**)&v.dWtab, kRotChunk * sizeof(float2)));
+    B200_CUDA(cudaMalloc((void**)&v.dRotState, sizeof(float2)));
+    const float2 one = make_float2(1.0f, 0.0f);     // phase = 1 + 0i (frequency_xlator.h:16)
+    B200_CUDA(cudaMemcpy(v.dRotState, &one, sizeof(float2), cudaMemcpyHostToDevice));
+    v.tableDirty = true;
+    return B200_OK;
+}
+
+void VfoBank::freeRotator(Vfo& v) {
+    if (v.dChk) { cudaFree(v.dChk); v.dChk = nullptr; }
+    if (v.dWtab) { cudaFree(v.dWtab); v.dWtab = nullptr; }
+    if (v.dRotState) { cudaFree(v.dRotState); v.dRotState = nullptr; }
+}
+
+int VfoBank::getPhase(Vfo& v, double* re, double* im) {
+    if (rotatorMode == B200_ROTATOR_EXACT) {
+        DeviceGuard g(device);
+        B200_TRY(syncLast());
+        float2 p;
+        B200_CUDA(cudaMemcpy(&p, v.dRotState, sizeof(float2), cudaMemcpyDeviceToHost));
+        *re = p.x; *im = p.y;
+    }
+    else { *re = cos(v.angle); *im = sin(v.angle); }
+    return B200_OK;
+}
+
+int VfoBank::setPhase(Vfo& v, double re, double im) {
+    if (rotatorMode == B200_ROTATOR_EXACT) {
+        DeviceGuard g(device);
+        B200_TRY(syncLast());
+        const float2 p = make_float2((float)re, (float)im);
+        B200_CUDA(cudaMemcpy(v.dRotState, &p, sizeof(float2), cudaMemcpyHostToDevice));
+    }
+    v.angle = atan2(im, re);
+    return B200_OK;
+}
+
+int VfoBank::setRotatorMode(int mode) {
+    if (mode != B200_ROTATOR_FAST && mode != B200_ROTATOR_EXACT) { setError("bad rotator mode %d", mode); return B200_EINVAL; }
+    if (mode == rotatorMode) { return B200_OK; }
+    // carry every VFO's phase across the switch
+    std::vector<std::pair<double, double>> ph(vfos.size());
+    for (size_t i = 0; i < vfos.size(); i++) { if (vfos[i].live) { B200_TRY(getPhase(vfos[i], &ph[i].first, &ph[i].second)); } }
+    rotatorMode = mode;
+    for (size_t i = 0; i < vfos.size(); i++) { if (vfos[i].live) { B200_TRY(setPhase(vfos[i], ph[i].first, ph[i].second)); } }
+    return B200_OK;
+}
+
 // RxVFO::process for every live VFO (rx_vfo.h:89-100)
 int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
     if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
     DeviceGuard g(device);
     if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
     lastStream = s; everRan = true;
-    B200_TRY(calibrateDirty());
+    const bool exact = (rotatorMode == B200_ROTATOR_EXACT);
+    if (!exact) { B200_TRY(calibrateDirty()); }
 
-    // ---- build this call's descriptors: level -1 = rotation, levels 0.. = filter stages
-    const int nv = (int)vfos.size();
+    // ---- build this call's descriptors
+    std::vector<RotJob> rj;
     std::vector<XlateJob> xj;
     std::vector<FusedJob> fj;
     std::vector<std::vector<FirJob>> levels;
     std::vector<FirJob> histJobs;
-    xj.reserve(nv);
+    std::vector<Vfo*> dirtyTables;
     for (auto& v : vfos) {
         if (!v.live) { continue; }
+        if (v.tableDirty) { dirtyTables.push_back(&v); }
+        RotJob r;
+        r.chk = v.dChk; r.state = v.dRotState; r.angle0 = v.angle; r.theta = v.theta;
+        r.dRe = v.dRe; r.dIm = v.dIm; r.count = count; r.exact = exact ? 1 : 0;
+        rj.push_back(r);
+
         std::vector<Stage*> chain;
         if (v.mode == 0 || v.mode == 1) { for (auto& st : v.decimStages) { chain.push_back(&st); } }
         if (v.hasPoly && (v.mode == 0 || v.mode == 2)) { chain.push_back(&v.poly); }
@@ -318,22 +376,26 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         const void* data = v.dZ;
         int n = count;
         size_t first = 0;
-        const bool fused = !chain.empty() && fusedStageSupported(*chain[0]) && count > 0;
-        if (fused) {
-            // stage 1 consumes the shared input directly (rotation folded in)
+        if (!chain.empty() && fusedStageSupported(v)) {
+            // stage 1 consumes the shared input directly, rotation folded in; its history refresh is done
+            // by the fused edge kernel, so it is not added to histJobs
             FusedJob f;
             fillFusedJob(f, *chain[0], v, dIn, count);
             fj.push_back(f);
-            FirJob hj; chain[0]->fillJob(hj, nullptr, count);   // history refresh handled by the fused edge kernel
-            n = hj.nOut;
+            n = f.nOut;
             data = chain[0]->dOut;
             chain[0]->advance(count);
             first = 1;
         }
         else {
+            if ((!v.dZ || v.zCap < count) && count > 0) {
+                if (v.dZ) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(v.dZ); v.dZ = nullptr; }
+                v.zCap = maxBlock;
+                B200_CUDA(cudaMalloc((void**)&v.dZ, (size_t)v.zCap * sizeof(cf32)));
+                data = v.dZ;
+            }
             XlateJob x;
-            x.in = dIn; x.out = chain.empty() ? v.dZ : v.dZ; x.angle0 = v.angle; x.theta = v.theta;
-            x.stepRe = (float)cos(v.theta); x.stepIm = (float)sin(v.theta); x.n = count; x.pad = 0;
+            x.in = dIn; x.out = v.dZ; x.chk = v.dChk; x.wtab = v.dWtab; x.n = count; x.pad = 0;
             xj.push_back(x);
         }
         for (size_t l = first; l < chain.size(); l++) {
@@ -346,34 +408,49 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         }
         v.lastOut = n;
         v.lastOutPtr = (const cf32*)data;
-        // advance the rotator angle (the reference's phase after `count` recursion steps)
-        v.angle = fmod(v.angle + v.theta * (double)count, 2.0 * design::kPi);
+        // FAST mode: the angle the reference's phase reaches after `count` recursion steps
+        if (!exact) { v.angle = fmod(v.angle + v.theta * (double)count, 2.0 * design::kPi); }
     }
+    std::stable_sort(fj.begin(), fj.end(), [](const FusedJob& a, const FusedJob& b) {
+        return a.ratio != b.ratio ? a.ratio < b.ratio : a.offset < b.offset;
+    });
 
-    // ---- one upload, then one launch per level
-    size_t bytes = xj.size() * sizeof(XlateJob) + fj.size() * sizeof(FusedJob) + histJobs.size() * sizeof(FirJob);
+    // ---- one upload (descriptors + any retuned rotator tables), then one launch per level
+    size_t bytes = rj.size() * sizeof(RotJob) + xj.size() * sizeof(XlateJob) + fj.size() * sizeof(FusedJob) + histJobs.size() * sizeof(FirJob);
     for (auto& l : levels) { bytes += l.size() * sizeof(FirJob); }
-    bytes += 64 * 16;
-    if (bytes > dDescBytes) {
-        B200_CUDA(cudaStreamSynchronize(s));
-        if (dDesc) { cudaFree(dDesc); }
-        dDescBytes = bytes * 2;
-        B200_CUDA(cudaMalloc(&dDesc, dDescBytes));
-    }
+    bytes += dirtyTables.size() * (kRotChunk * sizeof(float2)) + 64 * (16 + dirtyTables.size());
     void* hp = nullptr; int slot = 0;
     B200_TRY(ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
     auto put = [&](const void* src, size_t n) { size_t o = off; if (n) { memcpy(h + off, src, n); } off = (off + n + 63) & ~(size_t)63; return o; };
+    const size_t oR = put(rj.data(), rj.size() * sizeof(RotJob));
     const size_t oX = put(xj.data(), xj.size() * sizeof(XlateJob));
     const size_t oF = put(fj.data(), fj.size() * sizeof(FusedJob));
     std::vector<size_t> oL;
     for (auto& l : levels) { oL.push_back(put(l.data(), l.size() * sizeof(FirJob))); }
     const size_t oH = put(histJobs.data(), histJobs.size() * sizeof(FirJob));
-    B200_CUDA(cudaMemcpyAsync(dDesc, h, off, cudaMemcpyHostToDevice, s));
+    const size_t descBytes = off;
+    if (descBytes > dDescBytes) {
+        B200_CUDA(cudaStreamSynchronize(s));
+        if (dDesc) { cudaFree(dDesc); }
+        dDescBytes = descBytes * 2;
+        B200_CUDA(cudaMalloc(&dDesc, dDescBytes));
+    }
+    B200_CUDA(cudaMemcpyAsync(dDesc, h, descBytes, cudaMemcpyHostToDevice, s));
+    for (Vfo* v : dirtyTables) {
+        float2* tab = (float2*)(h + off);
+        makeRotatorTable(v->dRe, v->dIm, tab);
+        off += kRotChunk * sizeof(float2);
+        B200_CUDA(cudaMemcpyAsync(v->dWtab, tab, kRotChunk * sizeof(float2), cudaMemcpyHostToDevice, s));
+        v->tableDirty = false;
+    }
     B200_TRY(ring.release(slot, s));
     char* d = (char*)dDesc;
 
+    int maxH = 0;
+    for (auto& j : histJobs) { maxH = std::max(maxH, j.H); }
     if (count > 0) {
+        B200_TRY(launchCheckpoints((const RotJob*)(d + oR), (int)rj.size(), exact ? (int)rj.size() : 0, count, s));
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
         for (size_t l = 0; l < levels.size(); l++) {
@@ -381,16 +458,12 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
             for (auto& j : levels[l]) { maxOutL = std::max(maxOutL, j.nOut); }
             B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), (int)levels[l].size(), maxOutL, 2, s));
         }
-        int maxH = 0;
-        for (auto& j : histJobs) { maxH = std::max(maxH, j.H); }
-        B200_TRY(launchHistoryUpdate((const FirJob*)(d + oH), (int)histJobs.size(), maxH, s));
     }
-    else {
-        // an empty block still flips the ping-pong parity in advance(); copy histories across
-        int maxH = 0;
-        for (auto& j : histJobs) { maxH = std::max(maxH, j.H); }
-        B200_TRY(launchHistoryUpdate((const FirJob*)(d + oH), (int)histJobs.size(), maxH, s));
+    else if (!fj.empty()) {
+        // an empty block: the fused stages still flip their history ping-pong; copy the history across
+        B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
     }
+    B200_TRY(launchHistoryUpdate((const FirJob*)(d + oH), (int)histJobs.size(), maxH, s));
     B200_TRY(processDemods(*this, s));
     return B200_OK;
 }

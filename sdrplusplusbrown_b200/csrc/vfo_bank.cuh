@@ -5,6 +5,7 @@
 
 #include "common.cuh"
 #include "fir_jobs.cuh"
+#include "rotator.cuh"
 #include "host_design.h"
 
 namespace b200 {
@@ -34,13 +35,12 @@ struct Stage {
     void fillJob(FirJob& j, const void* data, int nIn) const;
 };
 
-// per-call rotation job (unfused path)
+// per-call rotation job (unfused path); phase = chk[m >> 9] * wtab[m & 511] (rotator.cuh)
 struct XlateJob {
     const cf32* in;
     cf32* out;
-    double angle0;    // rotator angle at sample 0 of this block
-    double theta;     // calibrated step per sample
-    float stepRe, stepIm;
+    const float2* chk;
+    const float2* wtab;
     int n;
     int pad;
 };
@@ -52,9 +52,13 @@ struct Vfo {
     double outSR = 0, bw = 0, offset = 0;
     // FrequencyXlator state (frequency_xlator.h:15-29,70-71)
     float dRe = 1.f, dIm = 0.f;      // phaseDelta as the reference stores it (fp32)
-    double theta = 0.0;              // calibrated effective step
-    double angle = 0.0;              // current phase angle (|phase| == 1)
+    double theta = 0.0;              // FAST mode: calibrated effective step
+    double angle = 0.0;              // FAST mode: current phase angle (|phase| == 1)
     bool calDirty = true;
+    bool tableDirty = true;          // wtab must be re-uploaded (phaseDelta changed)
+    float2* dChk = nullptr; int chkCap = 0;   // per-block phase checkpoints
+    float2* dWtab = nullptr;                  // phaseDelta^j, j < 512
+    float2* dRotState = nullptr;              // EXACT mode: the reference's fp32 phase
     // RationalResampler configuration
     int mode = 3, ratio = 1, interp = 1, decim = 1, resampTapCount = 0;
     std::vector<float> resampTaps;
@@ -74,6 +78,8 @@ struct VfoBank {
     int maxBlock = 0;
     std::vector<Vfo> vfos;
     int calSteps = 1 << 20;
+    int rotatorMode = 0;             // B200_ROTATOR_FAST / B200_ROTATOR_EXACT
+    void* dDemodDesc = nullptr; size_t dDemodDescBytes = 0;
     cudaStream_t lastStream = nullptr;
     bool everRan = false;
     // per-call descriptors
@@ -92,6 +98,11 @@ struct VfoBank {
     int check(int v) const;
     int syncLast();
     int configureXlator(Vfo& v);
+    int allocRotator(Vfo& v);
+    void freeRotator(Vfo& v);
+    int getPhase(Vfo& v, double* re, double* im);
+    int setPhase(Vfo& v, double re, double im);
+    int setRotatorMode(int mode);
     int reconfigureResampler(Vfo& v);            // RationalResampler::reconfigure
     int regenChannelTaps(Vfo& v, bool create);   // RxVFO::generateTaps + filter.setTaps
     int resetVfo(Vfo& v);

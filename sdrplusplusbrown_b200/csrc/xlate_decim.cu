@@ -1,13 +1,279 @@
+// Fused frequency translation + first decimating FIR stage, many VFOs per launch  (K1 + K2 of SURVEY §2.2).
+//
+// Reference work per VFO and input sample (rx_vfo.h:89-90 -> frequency_xlator.h:47-51 ->
+// power_decimator.h:58-65 -> decimating_fir.h:51-61): one complex multiply by the rotator phase, a copy
+// into the FIR work buffer, and T/D real-tap MACs; every VFO re-reads its own copy of the block that the
+// Splitter made for it (routing/splitter.h:74-83).  Here the block is read from HBM once per group of VFOs:
+//
+//   y[k] = sum_j h[j] * x[m0 + kD + j] * phase[m0 + kD + j]                      (m0 = offset - (T-1))
+//
+// is regrouped by input sub-block s of D samples.  With phase[m_s + r] = P_s * w[r], w[r] = phaseDelta^r:
+//
+//   c_q[s] = sum_r h[qD + r] * (x[m_s + r] * w[r])        q = 0..Q-1, Q = ceil(T/D)
+//   y[k]   = sum_q P_{k+q} * c_q[k+q]
+//
+// so each input sample is rotated once (4 flops-pairs) and feeds Q accumulators (2 FFMA each): ~12-16 FP32
+// instructions per sample per VFO, the minimum for this algorithm, instead of T/D rotations per sample.
+// One thread owns one sub-block: it walks D samples from shared memory (padded so a warp's lanes hit distinct
+// banks), taps come from the constant bank as FFMA immediates (the r loop is fully unrolled), w[r] is a
+// warp-uniform shared-memory broadcast.  Partial sums meet in shared memory.  The T-1 samples of rotated
+// history that the first outputs need, and the history refresh, are handled by a small edge kernel.
+//
+// CUDA FP32 pipes only: this is a bank of short real-tap FIRs on a shared stream, not a dense contraction.
 #include "xlate_decim.cuh"
 
+#include <algorithm>
+
+#include "host_design.h"
+#include "rotator.cuh"
 #include "vfo_bank.cuh"
 
 namespace b200 {
 
-bool fusedStageSupported(const Stage&) { return false; }
-void fillFusedJob(FusedJob&, const Stage&, const Vfo&, const cf32*, int) {}
-int launchFused(const FusedJob*, const std::vector<FusedJob>& hostJobs, cudaStream_t) {
-    return hostJobs.empty() ? B200_OK : B200_ESTATE;
+namespace {
+
+// ---- coefficient tables in the constant bank (all 13 stage filters, 9 KB)
+#define DECIM_TABLE_U32(name, count) __constant__ uint32_t c_##name[count] = {
+#define DECIM_ROW(...) __VA_ARGS__,
+#define DECIM_TABLE_END };
+#define DECIM_PLAN_BEGIN(ratio, nstages)
+#define DECIM_STAGE(index, decim, name, ntaps)
+#define DECIM_PLAN_END
+#include "decim_tables.inc"
+#undef DECIM_TABLE_U32
+#undef DECIM_ROW
+#undef DECIM_TABLE_END
+#undef DECIM_PLAN_BEGIN
+#undef DECIM_STAGE
+#undef DECIM_PLAN_END
+
+// ---- FirstStage<ratio>: decimation, tap count and tap accessor of each plan's first stage
+template <int RATIO> struct FirstStage;
+#define DECIM_TABLE_U32(name, count)
+#define DECIM_ROW(...)
+#define DECIM_TABLE_END
+#define DECIM_PLAN_BEGIN(ratio, nstages) template <> struct FirstStage<ratio> {
+#define DECIM_STAGE(index, decim, name, ntaps) DECIM_STAGE_##index(decim, name, ntaps)
+#define DECIM_STAGE_0(decim, name, ntaps)                                                      \
+    static constexpr int D = decim;                                                            \
+    static constexpr int T = ntaps;                                                            \
+    static __device__ __forceinline__ float tap(int i) { return __uint_as_float(c_##name[i]); }
+#define DECIM_STAGE_1(decim, name, ntaps)
+#define DECIM_STAGE_2(decim, name, ntaps)
+#define DECIM_STAGE_3(decim, name, ntaps)
+#define DECIM_PLAN_END };
+#include "decim_tables.inc"
+#undef DECIM_TABLE_U32
+#undef DECIM_ROW
+#undef DECIM_TABLE_END
+#undef DECIM_PLAN_BEGIN
+#undef DECIM_STAGE
+#undef DECIM_STAGE_0
+#undef DECIM_STAGE_1
+#undef DECIM_STAGE_2
+#undef DECIM_STAGE_3
+#undef DECIM_PLAN_END
+
+constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
+
+template <int D> struct TileCfg {
+    // sub-blocks (= threads) per CTA: ~8192 samples of input per tile
+    static constexpr int SB = (8192 / D) > 256 ? 256 : ((8192 / D) < 64 ? 64 : (8192 / D));
+};
+
+__device__ __forceinline__ float2 cmulf(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+
+// phase at sample m of the block, m may be negative (backward extension from chk[0]; only the m >= 0 part of
+// a sub-block that starts in the history region ever multiplies non-zero data)
+__device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
+    if (m >= 0) { return rotPhaseAt(j.chk, j.wtab, m); }
+    const float2 c0 = __ldg(j.chk);
+    double sd, cd;
+    sincos(j.thetaEff * (double)m, &sd, &cd);
+    const double r = exp(j.logMag * (double)m);
+    const float2 w = make_float2((float)(r * cd), (float)(r * sd));
+    return cmulf(c0, w);
+}
+
+// grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
+template <int RATIO>
+__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D>::SB)
+fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T, H = T - 1;
+    constexpr int Q = (T + D - 1) / D;
+    constexpr int SB = TileCfg<D>::SB;
+    constexpr int NB = SB - (Q - 1);        // outputs per tile
+    constexpr int LP = D + 1;               // padded sub-block pitch: lane stride 2(D+1) words -> distinct banks
+    extern __shared__ __align__(16) float2 sm[];
+    float2* xs = sm;                        // SB * LP
+    float2* ws = xs + SB * LP;              // D
+    float2* part = ws + D;                  // Q * SB
+
+    const int tid = threadIdx.x;
+    const int g0 = blockIdx.y * G;
+    const FusedJob j0 = jobs[g0];
+    const int k0 = blockIdx.x * NB;
+    if (k0 >= j0.nOut) { return; }
+    const int mStart = j0.offset - H + k0 * D;     // sample index of this tile's first sub-block
+    const float2* in = reinterpret_cast<const float2*>(j0.in);
+
+    // ---- stage the input tile once for the whole VFO group (zero outside [0, count))
+    for (int i = tid; i < SB * D; i += SB) {
+        const int m = mStart + i;
+        float2 v = make_float2(0.f, 0.f);
+        if (m >= 0 && m < j0.count) { v = __ldg(in + m); }
+        xs[i + i / D] = v;
+    }
+
+    const int ms = mStart + tid * D;
+    const int gEnd = min(g0 + G, nJobs);
+    for (int g = g0; g < gEnd; g++) {
+        const FusedJob j = jobs[g];
+        for (int r = tid; r < D; r += SB) { ws[r] = __ldg(j.wtab + r); }
+        float2 P = make_float2(0.f, 0.f);
+        if (ms < j.count && ms + D > 0) { P = phaseAtAny(j, ms); }
+        __syncthreads();                    // xs (first pass) and ws visible; previous pass's part[] consumed
+
+        float2 acc[Q];
+#pragma unroll
+        for (int q = 0; q < Q; q++) { acc[q] = make_float2(0.f, 0.f); }
+        const float2* xrow = xs + tid * LP;
+#pragma unroll
+        for (int r = 0; r < D; r++) {
+            const float2 z = cmulf(xrow[r], ws[r]);
+#pragma unroll
+            for (int q = 0; q < Q; q++) {
+                if (q * D + r < T) {
+                    const float h = FS::tap(q * D + r);
+                    acc[q].x = fmaf(h, z.x, acc[q].x);
+                    acc[q].y = fmaf(h, z.y, acc[q].y);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < Q; q++) { part[q * SB + tid] = cmulf(acc[q], P); }
+        __syncthreads();
+        if (tid < NB && k0 + tid < j.nOut) {
+            float2 y = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < Q; q++) {
+                const float2 c = part[q * SB + tid + q];
+                y.x += c.x; y.y += c.y;
+            }
+            reinterpret_cast<float2*>(j.out)[k0 + tid] = y;
+        }
+        __syncthreads();                    // part[] and ws free for the next VFO
+    }
+}
+
+// One CTA per VFO: (1) add the contribution of the carried, already-rotated history to the first outputs,
+// (2) write the rotated history for the next call: histNext[i] = workbuf[count + i] (decimating_fir.h:65).
+template <int RATIO>
+__global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restrict__ jobs) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T, H = T - 1;
+    const FusedJob j = jobs[blockIdx.x];
+    const float2* hist = reinterpret_cast<const float2*>(j.hist);
+    float2* out = reinterpret_cast<float2*>(j.out);
+    // outputs whose window starts inside the history: offset + k*D < H
+    const int nHead = (j.offset < H) ? min(j.nOut, (H - j.offset + D - 1) / D) : 0;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int k = warp; k < nHead; k += 8) {
+        const int p0 = j.offset + k * D;            // first work-buffer position of output k
+        float2 a = make_float2(0.f, 0.f);
+        for (int t = lane; p0 + t < H && t < T; t += 32) {
+            const float h = FS::tap(t);
+            const float2 z = __ldg(hist + p0 + t);
+            a.x = fmaf(h, z.x, a.x); a.y = fmaf(h, z.y, a.y);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a.x += __shfl_xor_sync(0xffffffffu, a.x, o);
+            a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        }
+        if (lane == 0) { float2 y = out[k]; y.x += a.x; y.y += a.y; out[k] = y; }
+    }
+    const float2* in = reinterpret_cast<const float2*>(j.in);
+    float2* hn = reinterpret_cast<float2*>(j.histNext);
+    for (int i = threadIdx.x; i < H; i += 256) {
+        const int p = j.count + i;                  // position in [hist | rotated block]
+        float2 v;
+        if (p < H) { v = __ldg(hist + p); }
+        else {
+            const int m = p - H;
+            v = cmulf(__ldg(in + m), rotPhaseAt(j.chk, j.wtab, m));
+        }
+        hn[i] = v;
+    }
+}
+
+template <int RATIO>
+int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, cudaStream_t s) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T;
+    constexpr int Q = (T + D - 1) / D;
+    constexpr int SB = TileCfg<D>::SB;
+    constexpr int NB = SB - (Q - 1);
+    constexpr size_t smem = ((size_t)SB * (D + 1) + D + (size_t)Q * SB) * sizeof(float2);
+    if (nOut > 0) {
+        B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
+        const int tiles = (nOut + NB - 1) / NB;
+        int G = 8;
+        while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
+        dim3 grid(tiles, (nJobs + G - 1) / G);
+        fusedXlateDecimKernel<RATIO><<<grid, SB, smem, s>>>(dJobs, nJobs, G);
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
+    fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
+    B200_CHECK_LAUNCH(); countLaunch();
+    return B200_OK;
+}
+
+int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, cudaStream_t s) {
+    switch (ratio) {
+    case 16: return launchPlan<16>(dJobs, nJobs, nOut, s);
+    case 32: return launchPlan<32>(dJobs, nJobs, nOut, s);
+    case 64: return launchPlan<64>(dJobs, nJobs, nOut, s);
+    case 128: return launchPlan<128>(dJobs, nJobs, nOut, s);
+    case 256: return launchPlan<256>(dJobs, nJobs, nOut, s);
+    case 512: return launchPlan<512>(dJobs, nJobs, nOut, s);
+    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, s);
+    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, s);
+    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, s);
+    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, s);
+    default: setError("no fused kernel for ratio %d", ratio); return B200_EINVAL;
+    }
+}
+
+} // namespace
+
+bool fusedEnabled = true;
+
+bool fusedStageSupported(const Vfo& v) {
+    return fusedEnabled && (v.mode == 0 || v.mode == 1) && v.ratio >= kMinFusedRatio && !v.decimStages.empty();
+}
+
+void fillFusedJob(FusedJob& f, const Stage& st, const Vfo& v, const cf32* dIn, int count) {
+    f.in = dIn; f.out = (cf32*)st.dOut;
+    f.hist = (const cf32*)st.dHist[st.cur]; f.histNext = (cf32*)st.dHist[st.cur ^ 1];
+    f.chk = v.dChk; f.wtab = v.dWtab;
+    f.thetaEff = atan2((double)v.dIm, (double)v.dRe);
+    f.logMag = log(hypot((double)v.dRe, (double)v.dIm));
+    f.ratio = v.ratio; f.offset = st.offset; f.count = count; f.nOut = st.outCountFor(count);
+}
+
+// hostJobs must already be sorted by (ratio, offset); dJobs is the device copy in the same order
+int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cudaStream_t s) {
+    size_t i = 0;
+    while (i < hostJobs.size()) {
+        size_t e = i + 1;
+        while (e < hostJobs.size() && hostJobs[e].ratio == hostJobs[i].ratio && hostJobs[e].offset == hostJobs[i].offset) { e++; }
+        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, s));
+        i = e;
+    }
+    return B200_OK;
 }
 
 } // namespace b200

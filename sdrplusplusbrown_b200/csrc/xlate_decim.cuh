@@ -13,15 +13,18 @@ struct Vfo;
 struct FusedJob {
     const cf32* in;        // shared input block (count samples)
     cf32* out;             // nOut results
-    const cf32* hist;      // H rotated samples carried from the previous call
-    cf32* histNext;        // H rotated samples to carry
-    double angle0, theta;  // rotator angle at sample 0, calibrated step
-    int planIndex;         // which pow-2 plan's first stage (selects taps/D/T at compile time)
+    const cf32* hist;      // T-1 rotated samples carried from the previous call
+    cf32* histNext;        // T-1 rotated samples to carry
+    const float2* chk;     // rotator checkpoints of this block (rotator.cuh)
+    const float2* wtab;    // phaseDelta^j, j < 512
+    double thetaEff, logMag;   // arg / log|.| of phaseDelta, for the backward extension into the history region
+    int ratio;             // pow-2 plan (selects D, T and the taps at compile time)
     int offset;            // DecimatingFIR::offset
     int count, nOut;
 };
 
-bool fusedStageSupported(const Stage& st);
+extern bool fusedEnabled;   // test hook: false forces the unfused xlate -> generic FIR path
+bool fusedStageSupported(const Vfo& v);
 void fillFusedJob(FusedJob& f, const Stage& st, const Vfo& v, const cf32* dIn, int count);
 int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cudaStream_t s);
 
