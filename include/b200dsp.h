@@ -44,6 +44,14 @@ const char* b200_version(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 uint64_t b200_launch_count(void);
 
+/* Measurement hooks (bench.py's roofline line): when enabled, every launch of the fused
+ * xlate+decimate kernel -- the kernel that streams the full-rate input -- is bracketed by CUDA events
+ * on its launch stream.  b200_profile_read synchronises those events and returns, since the last read,
+ * the summed kernel time (ms), the number of launches and the algorithmic bytes they moved
+ * (8 B per input sample read once per bank + 8 B per stage-1 output sample per VFO). */
+int b200_profile_enable(int enabled);
+int b200_profile_read(double* ms_total, long long* launches, double* algorithmic_bytes);
+
 /* ------------------------------------------------------------------------------------------
  * RxVFO bank — replaces N instances of dsp::channel::RxVFO (channel/rx_vfo.h) fed by the same
  * Splitter output (routing/splitter.h:59-92).  One launch sequence serves every VFO of the bank.

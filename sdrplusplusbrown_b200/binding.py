@@ -24,6 +24,8 @@ _SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (C.c_char_p, []),
     "b200_launch_count": (C.c_uint64, []),
+    "b200_profile_enable": (_i, [_i]),
+    "b200_profile_read": (_i, [C.POINTER(_d), C.POINTER(C.c_longlong), C.POINTER(_d)]),
     "b200_vfo_bank_create": (_i, [_pp, _d, _i, _i]),
     "b200_vfo_bank_destroy": (_i, [_vp]),
     "b200_vfo_bank_add": (_i, [_vp, _d, _d, _d]),
@@ -334,6 +336,17 @@ class Waterfall:
         u = np.zeros(self.w, np.int32)
         _chk(lib.b200_waterfall_zoom_table(self.h, s.ctypes.data, u.ctypes.data))
         return s, u
+
+
+def profile_enable(on):
+    _chk(lib.b200_profile_enable(int(on)))
+
+
+def profile_read():
+    """(kernel ms, launches, algorithmic bytes) of the fused xlate+decimate kernel since the last read."""
+    ms, n, by = _d(), C.c_longlong(), _d()
+    _chk(lib.b200_profile_read(C.byref(ms), C.byref(n), C.byref(by)))
+    return ms.value, n.value, by.value
 
 
 def fft_forward(d_in, nz, fft_size, d_out, stream=None):

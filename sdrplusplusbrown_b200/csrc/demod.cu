@@ -56,19 +56,49 @@ namespace {
 constexpr int kChunk = 1024;
 constexpr int kEnvLen = 4800;    // AGC::_totalEnvelopeLength (agc.h:162)
 
-// AGC recurrence over a staged chunk (lane 0 only).  sAmp[i] = |in[i]|; on return sAmp[i] holds the gain.
-// Follows agc.h:96-112: the average moves only for non-zero, non-NaN amplitudes; a skipped update means gain 1.
-__device__ void agcChain(float* sAmp, int n, float& amp, const AgcParams& p) {
-    for (int i = 0; i < n; i++) {
+// AGC recurrence over a staged chunk (agc.h:96-112).  The average moves only for non-zero, non-NaN amplitudes;
+// a skipped update means gain 1.  Because attack > decay, the reference's branch
+//     amp' = (a > amp) ? amp*(1-att) + a*att : amp*(1-dec) + a*dec
+// equals max(amp*(1-att) + a*att, amp*(1-dec) + a*dec): both candidates are evaluated as one FFMA each and
+// joined by FMNMX, so the loop-carried dependency is ~9 cycles per sample instead of a compare/select chain.
+// Products a*att / a*dec and the gains setPoint/amp do not depend on the running state and are computed by
+// the whole warp before / after the walk.  sAmp: |in| on entry; on exit the gain.  sPa/sPd: scratch.
+__device__ void agcChunk(float* sAmp, float* sPa, float* sPd, int n, float& amp, const AgcParams& p, int lane) {
+    const bool ordered = p.attack >= p.decay;   // the max form needs attack >= decay (always true for the radio's ranges)
+    for (int i = lane; i < n; i += 32) {
         const float a = sAmp[i];
-        float gain = 1.0f;
-        if (a != 0.0f) {
-            const float namp = (a > amp) ? __fadd_rn(__fmul_rn(amp, p.invAttack), __fmul_rn(a, p.attack))
-                                         : __fadd_rn(__fmul_rn(amp, p.invDecay), __fmul_rn(a, p.decay));
-            if (!isnan(namp)) { amp = namp; gain = fminf(__fdiv_rn(p.setPoint, amp), p.maxGain); }
-        }
-        sAmp[i] = gain;
+        sPa[i] = a * p.attack;
+        sPd[i] = a * p.decay;
     }
+    __syncwarp();
+    if (lane == 0) {
+        float am = amp;
+        if (ordered) {
+            for (int i = 0; i < n; i++) {
+                const float a = sAmp[i];
+                const float cand = fmaxf(fmaf(am, p.invAttack, sPa[i]), fmaf(am, p.invDecay, sPd[i]));
+                const bool upd = (a != 0.0f) && !isnan(cand);
+                am = upd ? cand : am;
+                sAmp[i] = upd ? am : -1.0f;          // -1 marks "no update": gain 1
+            }
+        }
+        else {
+            for (int i = 0; i < n; i++) {
+                const float a = sAmp[i];
+                const float cand = (a > am) ? fmaf(am, p.invAttack, sPa[i]) : fmaf(am, p.invDecay, sPd[i]);
+                const bool upd = (a != 0.0f) && !isnan(cand);
+                am = upd ? cand : am;
+                sAmp[i] = upd ? am : -1.0f;
+            }
+        }
+        amp = am;
+    }
+    __syncwarp();
+    for (int i = lane; i < n; i += 32) {
+        const float am = sAmp[i];
+        sAmp[i] = (am < 0.0f) ? 1.0f : fminf(__fdiv_rn(p.setPoint, am), p.maxGain);
+    }
+    __syncwarp();
 }
 
 // start ramp (agc.h:131-134): `envelope` is re-initialised to 1 on every process() call and keeps its last
@@ -82,6 +112,7 @@ __device__ __forceinline__ float envelopeAt(int startEnvAtCall, int i) {
 // one warp per demodulator with a sequential part (SSB, AM)
 __global__ void __launch_bounds__(32) seqDemodKernel(const DemodJob* __restrict__ jobs) {
     __shared__ float sA[kChunk];     // amplitudes -> gains
+    __shared__ float sPa[kChunk], sPd[kChunk];
     __shared__ float sV[kChunk];     // real working values
     __shared__ float2 sC[kChunk];    // complex working values (AM carrier AGC)
     const DemodJob j = jobs[blockIdx.x];
@@ -101,8 +132,7 @@ __global__ void __launch_bounds__(32) seqDemodKernel(const DemodJob* __restrict_
             }
             __syncwarp();
             if (j.agcMode == 0 && agcOn) {
-                if (lane == 0) { agcChain(sA, m, st.carrier.amp, j.agc); }
-                __syncwarp();
+                agcChunk(sA, sPa, sPd, m, st.carrier.amp, j.agc, lane);
                 for (int i = lane; i < m; i += 32) {
                     const float g = sA[i], e = envelopeAt(envCarrier0, base + i);
                     float2 x = sC[i];
@@ -131,8 +161,7 @@ __global__ void __launch_bounds__(32) seqDemodKernel(const DemodJob* __restrict_
             if (j.agcMode == 1 && agcOn) {
                 for (int i = lane; i < m; i += 32) { sA[i] = fabsf(sV[i]); }
                 __syncwarp();
-                if (lane == 0) { agcChain(sA, m, st.audio.amp, j.agc); }
-                __syncwarp();
+                agcChunk(sA, sPa, sPd, m, st.audio.amp, j.agc, lane);
                 for (int i = lane; i < m; i += 32) {
                     sV[i] = __fmul_rn(__fmul_rn(sV[i], sA[i]), envelopeAt(envAudio0, base + i));
                 }
@@ -155,8 +184,7 @@ __global__ void __launch_bounds__(32) seqDemodKernel(const DemodJob* __restrict_
             }
             __syncwarp();
             if (agcOn) {
-                if (lane == 0) { agcChain(sA, m, st.audio.amp, j.agc); }
-                __syncwarp();
+                agcChunk(sA, sPa, sPd, m, st.audio.amp, j.agc, lane);
                 for (int i = lane; i < m; i += 32) {
                     sV[i] = __fmul_rn(__fmul_rn(sV[i], sA[i]), envelopeAt(envAudio0, base + i));
                 }

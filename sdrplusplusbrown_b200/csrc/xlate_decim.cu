@@ -208,8 +208,29 @@ __global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restric
     }
 }
 
+// ---- optional per-launch timing of the fused kernel (bench.py's roofline line): CUDA events on the launch stream
+struct FusedProfile {
+    bool enabled = false;
+    std::vector<cudaEvent_t> start, stop;
+    std::vector<double> bytes;
+    size_t used = 0;
+    double msTotal = 0.0, bytesTotal = 0.0;
+    long long launches = 0;
+} g_prof;
+
+int profDrain() {
+    for (size_t i = 0; i < g_prof.used; i++) {
+        float ms = 0.f;
+        B200_CUDA(cudaEventSynchronize(g_prof.stop[i]));
+        B200_CUDA(cudaEventElapsedTime(&ms, g_prof.start[i], g_prof.stop[i]));
+        g_prof.msTotal += ms; g_prof.bytesTotal += g_prof.bytes[i]; g_prof.launches++;
+    }
+    g_prof.used = 0;
+    return B200_OK;
+}
+
 template <int RATIO>
-int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, cudaStream_t s) {
+int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
@@ -223,26 +244,42 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, cudaStream_t s) {
         int G = 8;
         while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
         dim3 grid(tiles, (nJobs + G - 1) / G);
+        size_t slot = 0;
+        if (g_prof.enabled) {
+            if (g_prof.used == g_prof.start.size()) {
+                if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
+                else {
+                    cudaEvent_t a, b;
+                    B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
+                    g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
+                }
+            }
+            slot = g_prof.used++;
+            // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples
+            g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
+            B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
+        }
         fusedXlateDecimKernel<RATIO><<<grid, SB, smem, s>>>(dJobs, nJobs, G);
         B200_CHECK_LAUNCH(); countLaunch();
+        if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }
 
-int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, cudaStream_t s) {
+int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
     switch (ratio) {
-    case 16: return launchPlan<16>(dJobs, nJobs, nOut, s);
-    case 32: return launchPlan<32>(dJobs, nJobs, nOut, s);
-    case 64: return launchPlan<64>(dJobs, nJobs, nOut, s);
-    case 128: return launchPlan<128>(dJobs, nJobs, nOut, s);
-    case 256: return launchPlan<256>(dJobs, nJobs, nOut, s);
-    case 512: return launchPlan<512>(dJobs, nJobs, nOut, s);
-    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, s);
-    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, s);
-    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, s);
-    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, s);
+    case 16: return launchPlan<16>(dJobs, nJobs, nOut, count, s);
+    case 32: return launchPlan<32>(dJobs, nJobs, nOut, count, s);
+    case 64: return launchPlan<64>(dJobs, nJobs, nOut, count, s);
+    case 128: return launchPlan<128>(dJobs, nJobs, nOut, count, s);
+    case 256: return launchPlan<256>(dJobs, nJobs, nOut, count, s);
+    case 512: return launchPlan<512>(dJobs, nJobs, nOut, count, s);
+    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, count, s);
+    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, count, s);
+    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, count, s);
+    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, count, s);
     default: setError("no fused kernel for ratio %d", ratio); return B200_EINVAL;
     }
 }
@@ -270,10 +307,31 @@ int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cu
     while (i < hostJobs.size()) {
         size_t e = i + 1;
         while (e < hostJobs.size() && hostJobs[e].ratio == hostJobs[i].ratio && hostJobs[e].offset == hostJobs[i].offset) { e++; }
-        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, s));
+        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, hostJobs[i].count, s));
         i = e;
     }
     return B200_OK;
 }
 
 } // namespace b200
+
+extern "C" {
+
+int b200_profile_enable(int enabled) {
+    using namespace b200;
+    if (!enabled && g_prof.enabled) { B200_TRY(profDrain()); }
+    g_prof.enabled = enabled != 0;
+    return B200_OK;
+}
+
+int b200_profile_read(double* ms_total, long long* launches, double* algorithmic_bytes) {
+    using namespace b200;
+    B200_TRY(profDrain());
+    if (ms_total) { *ms_total = g_prof.msTotal; }
+    if (launches) { *launches = g_prof.launches; }
+    if (algorithmic_bytes) { *algorithmic_bytes = g_prof.bytesTotal; }
+    g_prof.msTotal = 0.0; g_prof.bytesTotal = 0.0; g_prof.launches = 0;
+    return B200_OK;
+}
+
+} // extern "C"

@@ -70,7 +70,16 @@ _SIGS = {
 
 
 def build(which="port"):
-    """Compile the oracle library if its .so is missing (or stale for the port)."""
+    """Compile the oracle library if its .so is missing (or stale for the port).
+    "port_fast" / "ref_fast" are the -O3 -march=native timing builds (bench.py only, never parity)."""
+    if which == "port_fast":
+        subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "fast"])
+        return os.path.join(ORACLE_DIR, "libport_oracle_fast.so")
+    if which == "ref_fast":
+        p = os.path.join(ORACLE_DIR, "_ref", "libref_oracle_fast.so")
+        if os.path.isdir(os.path.join(REF_ROOT, "core", "src", "dsp")):
+            subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "ref_fast", "REF_ROOT=" + REF_ROOT])
+        return p if os.path.exists(p) else None
     if which == "port":
         subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "port"])
         return PORT_SO

@@ -50,7 +50,7 @@ def test_vfo_plus_demod_chain_matches_oracle(name):
     x = synth.make_iq(0, n, in_sr, sigma=0.02, tones=[(off + 900.0, 0.3), (off - 1500.0, 0.05)])
     x[100000:100200] = 0
     o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
-    b = binding.VfoBank(in_sr, max_block=100000)
+    b = binding.VfoBank(in_sr, max_block=200000)
     b.set_rotator_mode(binding.ROTATOR_EXACT)
     v = b.add(out_sr, bw, off)
     b.set_demod(v, kind, p0, p1, p2, p3)
