@@ -9,6 +9,7 @@
 // whole warp), then all lanes apply gains and write out.  Many VFOs run side by side in one launch.
 #include "demod.cuh"
 
+#include <algorithm>
 #include <cmath>
 
 #include "vfo_bank.cuh"
@@ -23,6 +24,7 @@ struct SeqState {
     AgcDev carrier, audio;
     float dcOffset;
     float quadPhase[2];   // ping-pong: written by one call, read by the next
+    float2 rotPhase;      // SSB rotator, EXACT mode: the reference's fp32 phase
 };
 
 struct DemodState {
@@ -38,67 +40,81 @@ struct DemodState {
     float dcRate = 0.f;
     Stage fir; bool hasFir = false;          // real-valued FIR (FM audio filter / AM low-pass)
     SeqState* dState = nullptr;
+    float2* dWtab = nullptr;                 // SSB: phaseDelta^j, j < 512
     float* dMono = nullptr; float* dStereo = nullptr; int cap = 0;
+    float4* dMaps = nullptr; float* dAmps = nullptr;   // SSB fast path scratch
+    long long envCount = 0;                            // host mirror of AGC::_startEnvelope (SSB fast path)
     int lastCount = 0;
 };
 
 // per-call descriptor
 struct DemodJob {
-    const cf32* in; float* mono; float* stereo; const float* stereoSrc; SeqState* st;
+    const cf32* in; float* mono; float* stereo; const float* stereoSrc; SeqState* st; const float2* wtab;
+    float4* maps; float* amps;      // SSB fast path scratch: per-sample AGC maps, walked amplitudes
     AgcParams agc;
     double angle0, theta; float stepRe, stepIm;
     float invDeviation, dcRate;
-    int kind, agcMode, n, quadParity;
+    int kind, agcMode, n, quadParity, exact, env0;
 };
 
 namespace {
 
-constexpr int kChunk = 1024;
+constexpr int kSeqThreads = 128;
+constexpr int kChunk = 1024;     // multiple of 512 so rotator renormalisation points fall on chunk-relative multiples of 512
 constexpr int kEnvLen = 4800;    // AGC::_totalEnvelopeLength (agc.h:162)
 
 // AGC recurrence over a staged chunk (agc.h:96-112).  The average moves only for non-zero, non-NaN amplitudes;
-// a skipped update means gain 1.  Because attack > decay, the reference's branch
+// a skipped update means gain 1.  The reference's branch
 //     amp' = (a > amp) ? amp*(1-att) + a*att : amp*(1-dec) + a*dec
-// equals max(amp*(1-att) + a*att, amp*(1-dec) + a*dec): both candidates are evaluated as one FFMA each and
-// joined by FMNMX, so the loop-carried dependency is ~9 cycles per sample instead of a compare/select chain.
-// Products a*att / a*dec and the gains setPoint/amp do not depend on the running state and are computed by
-// the whole warp before / after the walk.  sAmp: |in| on entry; on exit the gain.  sPa/sPd: scratch.
-__device__ void agcChunk(float* sAmp, float* sPa, float* sPd, int n, float& amp, const AgcParams& p, int lane) {
-    const bool ordered = p.attack >= p.decay;   // the max form needs attack >= decay (always true for the radio's ranges)
-    for (int i = lane; i < n; i += 32) {
+// equals max(A, B) of the two candidates when att >= dec and min(A, B) when att < dec (A - B = (a-amp)(att-dec)),
+// and a skipped sample is the identity map (slope 1, intercept 0) in the same form.  The whole CTA precomputes
+// per-sample slopes and intercepts, so the single thread that walks the recurrence issues only
+// 2 FFMA + 1 FMNMX per sample (~9 cycles of loop-carried latency), and the CTA turns amplitudes into gains
+// afterwards.  sAmp: |in| on entry, the gain on exit.
+struct AgcScratch { float *sa, *ia, *sd, *id, *r; };
+
+__device__ void agcChunk(float* sAmp, const AgcScratch& w, int n, float* ampState, const AgcParams& p) {
+    const int tid = threadIdx.x;
+    const int n8 = (n + 7) & ~7;
+    for (int i = tid; i < n8; i += kSeqThreads) {
+        const float a = (i < n) ? sAmp[i] : 0.0f;
+        const bool ok = (a != 0.0f) && (a == a);
+        w.sa[i] = ok ? p.invAttack : 1.0f; w.ia[i] = ok ? a * p.attack : 0.0f;
+        w.sd[i] = ok ? p.invDecay : 1.0f;  w.id[i] = ok ? a * p.decay : 0.0f;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        float am = *ampState;
+        const bool useMax = p.attack >= p.decay;
+        for (int i = 0; i < n8; i += 8) {
+            float sa[8], ia[8], sd[8], id[8], r[8];
+#pragma unroll
+            for (int u = 0; u < 8; u += 4) {
+                *reinterpret_cast<float4*>(&sa[u]) = *reinterpret_cast<const float4*>(&w.sa[i + u]);
+                *reinterpret_cast<float4*>(&ia[u]) = *reinterpret_cast<const float4*>(&w.ia[i + u]);
+                *reinterpret_cast<float4*>(&sd[u]) = *reinterpret_cast<const float4*>(&w.sd[i + u]);
+                *reinterpret_cast<float4*>(&id[u]) = *reinterpret_cast<const float4*>(&w.id[i + u]);
+            }
+            if (useMax) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) { am = fmaxf(fmaf(am, sa[u], ia[u]), fmaf(am, sd[u], id[u])); r[u] = am; }
+            }
+            else {
+#pragma unroll
+                for (int u = 0; u < 8; u++) { am = fminf(fmaf(am, sa[u], ia[u]), fmaf(am, sd[u], id[u])); r[u] = am; }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u += 4) { *reinterpret_cast<float4*>(&w.r[i + u]) = *reinterpret_cast<const float4*>(&r[u]); }
+        }
+        *ampState = am;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += kSeqThreads) {
         const float a = sAmp[i];
-        sPa[i] = a * p.attack;
-        sPd[i] = a * p.decay;
+        const bool ok = (a != 0.0f) && (a == a);
+        sAmp[i] = ok ? fminf(__fdiv_rn(p.setPoint, w.r[i]), p.maxGain) : 1.0f;
     }
-    __syncwarp();
-    if (lane == 0) {
-        float am = amp;
-        if (ordered) {
-            for (int i = 0; i < n; i++) {
-                const float a = sAmp[i];
-                const float cand = fmaxf(fmaf(am, p.invAttack, sPa[i]), fmaf(am, p.invDecay, sPd[i]));
-                const bool upd = (a != 0.0f) && !isnan(cand);
-                am = upd ? cand : am;
-                sAmp[i] = upd ? am : -1.0f;          // -1 marks "no update": gain 1
-            }
-        }
-        else {
-            for (int i = 0; i < n; i++) {
-                const float a = sAmp[i];
-                const float cand = (a > am) ? fmaf(am, p.invAttack, sPa[i]) : fmaf(am, p.invDecay, sPd[i]);
-                const bool upd = (a != 0.0f) && !isnan(cand);
-                am = upd ? cand : am;
-                sAmp[i] = upd ? am : -1.0f;
-            }
-        }
-        amp = am;
-    }
-    __syncwarp();
-    for (int i = lane; i < n; i += 32) {
-        const float am = sAmp[i];
-        sAmp[i] = (am < 0.0f) ? 1.0f : fminf(__fdiv_rn(p.setPoint, am), p.maxGain);
-    }
-    __syncwarp();
+    __syncthreads();
 }
 
 // start ramp (agc.h:131-134): `envelope` is re-initialised to 1 on every process() call and keeps its last
@@ -109,99 +125,267 @@ __device__ __forceinline__ float envelopeAt(int startEnvAtCall, int i) {
     return (startEnvAtCall < kEnvLen) ? (float)(kEnvLen - 1) / (float)kEnvLen : 1.0f;
 }
 
-// one warp per demodulator with a sequential part (SSB, AM)
-__global__ void __launch_bounds__(32) seqDemodKernel(const DemodJob* __restrict__ jobs) {
-    __shared__ float sA[kChunk];     // amplitudes -> gains
-    __shared__ float sPa[kChunk], sPd[kChunk];
-    __shared__ float sV[kChunk];     // real working values
-    __shared__ float2 sC[kChunk];    // complex working values (AM carrier AGC)
+// one CTA per demodulator with a sequential part (SSB, AM)
+__global__ void __launch_bounds__(kSeqThreads) seqDemodKernel(const DemodJob* __restrict__ jobs) {
+    __shared__ __align__(16) float sA[kChunk + 8];     // amplitudes -> gains
+    __shared__ __align__(16) float sSa[kChunk + 8], sIa[kChunk + 8], sSd[kChunk + 8], sId[kChunk + 8], sR[kChunk + 8];
+    __shared__ __align__(16) float sV[kChunk];         // real working values
+    __shared__ float2 sC[kChunk];                      // complex working values (AM) / rotator phases (SSB)
+    __shared__ float2 sW[kRotChunk];                   // SSB: phaseDelta^j
+    __shared__ float2 sChk[kChunk / kRotChunk];
+    __shared__ SeqState sSt;
     const DemodJob j = jobs[blockIdx.x];
-    const int lane = threadIdx.x;
-    SeqState st = *j.st;
-    const int envCarrier0 = st.carrier.startEnvelope, envAudio0 = st.audio.startEnvelope;
+    const int tid = threadIdx.x;
+    const AgcScratch agcW{ sSa, sIa, sSd, sId, sR };
+    if (tid == 0) { sSt = *j.st; }
+    if (j.kind != B200_DEMOD_AM) { for (int i = tid; i < kRotChunk; i += kSeqThreads) { sW[i] = __ldg(j.wtab + i); } }
+    __syncthreads();
+    const int envCarrier0 = sSt.carrier.startEnvelope, envAudio0 = sSt.audio.startEnvelope;
     const bool agcOn = j.agc.attack > 0.0f;   // agc.h:87-90: attack <= 0 copies the input through
 
     for (int base = 0; base < j.n; base += kChunk) {
         const int m = min(kChunk, j.n - base);
         if (j.kind == B200_DEMOD_AM) {
             // ---- carrier AGC on the complex IF (am.h:103-106)
-            for (int i = lane; i < m; i += 32) {
+            for (int i = tid; i < m; i += kSeqThreads) {
                 const float2 x = __ldg(reinterpret_cast<const float2*>(j.in) + base + i);
                 sC[i] = x;
                 sA[i] = sqrtf(__fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y)));   // complex_t::amplitude (types.h:77-79)
             }
-            __syncwarp();
+            __syncthreads();
             if (j.agcMode == 0 && agcOn) {
-                agcChunk(sA, sPa, sPd, m, st.carrier.amp, j.agc, lane);
-                for (int i = lane; i < m; i += 32) {
+                agcChunk(sA, agcW, m, &sSt.carrier.amp, j.agc);
+                for (int i = tid; i < m; i += kSeqThreads) {
                     const float g = sA[i], e = envelopeAt(envCarrier0, base + i);
                     float2 x = sC[i];
                     x.x = __fmul_rn(__fmul_rn(x.x, g), e); x.y = __fmul_rn(__fmul_rn(x.y, g), e);
                     sC[i] = x;
                 }
-                __syncwarp();
+                __syncthreads();
             }
             // ---- magnitude (am.h:120) and 1-pole DC blocker (dc_blocker.h:54-60)
-            for (int i = lane; i < m; i += 32) {
+            for (int i = tid; i < m; i += kSeqThreads) {
                 const float2 x = sC[i];
                 sV[i] = sqrtf(__fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y)));
             }
-            __syncwarp();
-            if (lane == 0) {
-                float o = st.dcOffset;
+            __syncthreads();
+            if (tid == 0) {
+                float o = sSt.dcOffset;
                 for (int i = 0; i < m; i++) {
                     const float y = __fsub_rn(sV[i], o);
                     o = __fadd_rn(o, __fmul_rn(y, j.dcRate));
                     sV[i] = y;
                 }
-                st.dcOffset = o;
+                sSt.dcOffset = o;
             }
-            __syncwarp();
+            __syncthreads();
             // ---- audio AGC (am.h:122-124)
             if (j.agcMode == 1 && agcOn) {
-                for (int i = lane; i < m; i += 32) { sA[i] = fabsf(sV[i]); }
-                __syncwarp();
-                agcChunk(sA, sPa, sPd, m, st.audio.amp, j.agc, lane);
-                for (int i = lane; i < m; i += 32) {
+                for (int i = tid; i < m; i += kSeqThreads) { sA[i] = fabsf(sV[i]); }
+                __syncthreads();
+                agcChunk(sA, agcW, m, &sSt.audio.amp, j.agc);
+                for (int i = tid; i < m; i += kSeqThreads) {
                     sV[i] = __fmul_rn(__fmul_rn(sV[i], sA[i]), envelopeAt(envAudio0, base + i));
                 }
-                __syncwarp();
+                __syncthreads();
             }
-            for (int i = lane; i < m; i += 32) { j.mono[base + i] = sV[i]; }
-            __syncwarp();
+            for (int i = tid; i < m; i += kSeqThreads) { j.mono[base + i] = sV[i]; }
+            __syncthreads();
         }
         else {
-            // ---- SSB: rotate by +-bw/2, keep the real part (ssb.h:84-92)
-            for (int i = lane; i < m; i += 32) {
+            // ---- SSB: rotate by +-bw/2 (FrequencyXlator inside SSB, ssb.h:84), keep the real part (:86-92).
+            // Rotator phases come from per-512 checkpoints x the power table, like every other rotation here:
+            //   EXACT  thread 0 replays the reference recursion (renormalising every 512 samples of the call and
+            //          after the ragged tail) and records each sample's phase;
+            //   FAST   checkpoints in closed form from the calibrated step.
+            if (j.exact) {
+                if (tid == 0) {
+                    float pr = sSt.rotPhase.x, pi = sSt.rotPhase.y;
+                    const float dr = j.stepRe, di = j.stepIm;
+                    for (int c = 0; c < m; c += kRotChunk) {
+                        const int mm = min(kRotChunk, m - c);
+                        for (int i = 0; i < mm; i++) {
+                            sC[c + i] = make_float2(pr, pi);
+                            const float nr = __fsub_rn(__fmul_rn(pr, dr), __fmul_rn(pi, di));
+                            const float ni = __fadd_rn(__fmul_rn(pr, di), __fmul_rn(pi, dr));
+                            pr = nr; pi = ni;
+                        }
+                        const float h = __double2float_rn(__dsqrt_rn(__dadd_rn(__dmul_rn((double)pr, (double)pr), __dmul_rn((double)pi, (double)pi))));
+                        pr = __fdiv_rn(pr, h); pi = __fdiv_rn(pi, h);
+                    }
+                    sSt.rotPhase = make_float2(pr, pi);
+                }
+            }
+            else {
+                if (tid < kChunk / kRotChunk) {
+                    double a = fma(j.theta, (double)(base + tid * kRotChunk), j.angle0);
+                    a -= 6.283185307179586476925 * rint(a * 0.15915494309189533577);
+                    double sd, cd;
+                    sincos(a, &sd, &cd);
+                    sChk[tid] = make_float2((float)cd, (float)sd);
+                }
+                __syncthreads();
+                for (int i = tid; i < m; i += kSeqThreads) {
+                    const float2 c = sChk[i >> kRotChunkLog], w = sW[i & (kRotChunk - 1)];
+                    sC[i] = make_float2(c.x * w.x - c.y * w.y, c.x * w.y + c.y * w.x);
+                }
+            }
+            __syncthreads();
+            for (int i = tid; i < m; i += kSeqThreads) {
                 const float2 x = __ldg(reinterpret_cast<const float2*>(j.in) + base + i);
-                double a = fma(j.theta, (double)(base + i), j.angle0);
-                a -= 6.283185307179586476925 * rint(a * 0.15915494309189533577);
-                double sd, cd;
-                sincos(a, &sd, &cd);
-                const float re = __fsub_rn(__fmul_rn(x.x, (float)cd), __fmul_rn(x.y, (float)sd));
+                const float2 ph = sC[i];
+                const float re = __fsub_rn(__fmul_rn(x.x, ph.x), __fmul_rn(x.y, ph.y));
                 sV[i] = re;
                 sA[i] = fabsf(re);
             }
-            __syncwarp();
+            __syncthreads();
             if (agcOn) {
-                agcChunk(sA, sPa, sPd, m, st.audio.amp, j.agc, lane);
-                for (int i = lane; i < m; i += 32) {
+                agcChunk(sA, agcW, m, &sSt.audio.amp, j.agc);
+                for (int i = tid; i < m; i += kSeqThreads) {
                     sV[i] = __fmul_rn(__fmul_rn(sV[i], sA[i]), envelopeAt(envAudio0, base + i));
                 }
-                __syncwarp();
+                __syncthreads();
             }
-            for (int i = lane; i < m; i += 32) { j.mono[base + i] = sV[i]; }
-            __syncwarp();
+            for (int i = tid; i < m; i += kSeqThreads) { j.mono[base + i] = sV[i]; }
+            __syncthreads();
         }
     }
-    if (lane == 0) {
+    if (tid == 0) {
         if (j.kind == B200_DEMOD_AM) {
-            if (j.agcMode == 0 && agcOn) { st.carrier.startEnvelope = envCarrier0 + j.n; }
-            if (j.agcMode == 1 && agcOn) { st.audio.startEnvelope = envAudio0 + j.n; }
+            if (j.agcMode == 0 && agcOn) { sSt.carrier.startEnvelope = envCarrier0 + j.n; }
+            if (j.agcMode == 1 && agcOn) { sSt.audio.startEnvelope = envAudio0 + j.n; }
         }
-        else if (agcOn) { st.audio.startEnvelope = envAudio0 + j.n; }
-        j.st->carrier = st.carrier; j.st->audio = st.audio; j.st->dcOffset = st.dcOffset;
+        else if (agcOn) { sSt.audio.startEnvelope = envAudio0 + j.n; }
+        j.st->carrier = sSt.carrier; j.st->audio = sSt.audio; j.st->dcOffset = sSt.dcOffset; j.st->rotPhase = sSt.rotPhase;
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// SSB fast path: the same computation as the SSB branch of seqDemodKernel, split so that only the AGC
+// recurrence itself is sequential:
+//   ssbPrepKernel  (parallel)   rotate, take the real part, turn |re| into the AGC's per-sample slope/intercept pairs
+//   agcWalkKernel  (one warp per VFO)  lane 0 walks amp' = max/min(amp*sa+ia, amp*sd+id); the warp streams the
+//                                     operands through double-buffered shared memory with cp.async
+//   ssbFinishKernel (parallel)  gain = min(setPoint/amp, maxGain), start ramp, mono -> stereo
+// Used in FAST rotator mode; EXACT mode keeps seqDemodKernel, whose thread 0 also replays the rotator recursion.
+__global__ void __launch_bounds__(256) ssbPrepKernel(const DemodJob* __restrict__ jobs) {
+    const DemodJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= j.n) { return; }
+    const int c = i >> kRotChunkLog;
+    double a = fma(j.theta, (double)(c << kRotChunkLog), j.angle0);
+    a -= 6.283185307179586476925 * rint(a * 0.15915494309189533577);
+    // one checkpoint per 512 samples, evaluated by the first lane of each warp and broadcast
+    float2 chk;
+    {
+        double sd = 0.0, cd = 0.0;
+        if ((threadIdx.x & 31) == 0) { sincos(a, &sd, &cd); }
+        chk.x = __shfl_sync(0xffffffffu, (float)cd, 0);
+        chk.y = __shfl_sync(0xffffffffu, (float)sd, 0);
+    }
+    const float2 w = __ldg(j.wtab + (i & (kRotChunk - 1)));
+    const float2 ph = make_float2(chk.x * w.x - chk.y * w.y, chk.x * w.y + chk.y * w.x);
+    const float2 x = __ldg(reinterpret_cast<const float2*>(j.in) + i);
+    const float re = __fsub_rn(__fmul_rn(x.x, ph.x), __fmul_rn(x.y, ph.y));
+    j.mono[i] = re;
+    const float am = fabsf(re);
+    const bool ok = (am != 0.0f) && (am == am);
+    float4 m;
+    m.x = ok ? j.agc.invAttack : 1.0f; m.y = ok ? am * j.agc.attack : 0.0f;
+    m.z = ok ? j.agc.invDecay : 1.0f;  m.w = ok ? am * j.agc.decay : 0.0f;
+    j.maps[i] = m;
+}
+
+constexpr int kWalkChunk = 512;
+
+__device__ __forceinline__ void cpAsync16(void* smemDst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+__global__ void __launch_bounds__(32) agcWalkKernel(const DemodJob* __restrict__ jobs) {
+    __shared__ __align__(16) float4 sM[2][kWalkChunk];
+    __shared__ __align__(16) float sR[kWalkChunk];
+    const DemodJob j = jobs[blockIdx.x];
+    const int lane = threadIdx.x;
+    const int nChunks = (j.n + kWalkChunk - 1) / kWalkChunk;
+    float am = j.st->audio.amp;
+    const bool useMax = j.agc.attack >= j.agc.decay;
+    auto prefetch = [&](int c) {
+        const int base = c * kWalkChunk;
+        const int m = min(kWalkChunk, j.n - base);
+        for (int i = lane; i < m; i += 32) { cpAsync16(&sM[c & 1][i], j.maps + base + i); }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    if (nChunks > 0) { prefetch(0); }
+    for (int c = 0; c < nChunks; c++) {
+        if (c + 1 < nChunks) {
+            prefetch(c + 1);
+            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        }
+        else {
+            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        }
+        __syncwarp();
+        const int base = c * kWalkChunk;
+        const int m = min(kWalkChunk, j.n - base);
+        if (lane == 0) {
+            const float4* M = sM[c & 1];
+            // 16 samples per trip in two register sets: while one set's chain runs, the other set's operands are
+            // already in flight from shared memory, and no register copies are needed
+            auto walk8 = [&](const float4* q, int at) {
+                float r[8];
+                if (useMax) {
+#pragma unroll
+                    for (int u = 0; u < 8; u++) { am = fmaxf(fmaf(am, q[u].x, q[u].y), fmaf(am, q[u].z, q[u].w)); r[u] = am; }
+                }
+                else {
+#pragma unroll
+                    for (int u = 0; u < 8; u++) { am = fminf(fmaf(am, q[u].x, q[u].y), fmaf(am, q[u].z, q[u].w)); r[u] = am; }
+                }
+                *reinterpret_cast<float4*>(&sR[at]) = make_float4(r[0], r[1], r[2], r[3]);
+                *reinterpret_cast<float4*>(&sR[at + 4]) = make_float4(r[4], r[5], r[6], r[7]);
+            };
+            int i = 0;
+            float4 qa[8], qb[8];
+            if (m >= 16) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) { qa[u] = M[u]; }
+            }
+            for (; i + 16 <= m; i += 16) {
+#pragma unroll
+                for (int u = 0; u < 8; u++) { qb[u] = M[i + 8 + u]; }
+                walk8(qa, i);
+                if (i + 32 <= m) {
+#pragma unroll
+                    for (int u = 0; u < 8; u++) { qa[u] = M[i + 16 + u]; }
+                }
+                walk8(qb, i + 8);
+            }
+            for (; i < m; i++) {
+                const float4 q = M[i];
+                const float ca = fmaf(am, q.x, q.y), cd = fmaf(am, q.z, q.w);
+                am = useMax ? fmaxf(ca, cd) : fminf(ca, cd);
+                sR[i] = am;
+            }
+        }
+        __syncwarp();
+        for (int i = lane; i < m; i += 32) { j.amps[base + i] = sR[i]; }
+        __syncwarp();
+    }
+    if (lane == 0) { j.st->audio.amp = am; }
+}
+
+__global__ void __launch_bounds__(256) ssbFinishKernel(const DemodJob* __restrict__ jobs) {
+    const DemodJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= j.n) { return; }
+    const float re = j.mono[i];
+    const float a = fabsf(re);
+    const bool ok = (a != 0.0f) && (a == a);
+    const float gain = ok ? fminf(__fdiv_rn(j.agc.setPoint, __ldg(j.amps + i)), j.agc.maxGain) : 1.0f;
+    const float v = __fmul_rn(__fmul_rn(re, gain), envelopeAt(j.env0, i));
+    reinterpret_cast<float2*>(j.stereo)[i] = make_float2(v, v);
 }
 
 // Quadrature detector (quadrature.h:39-46): out[i] = normalizePhase(phase(x[i]) - phase(x[i-1])) / deviation
@@ -237,16 +421,45 @@ void demodDestroy(DemodState* d) {
     if (!d) { return; }
     d->fir.destroy();
     if (d->dState) { cudaFree(d->dState); }
+    if (d->dWtab) { cudaFree(d->dWtab); }
     if (d->dMono) { cudaFree(d->dMono); }
+    if (d->dMaps) { cudaFree(d->dMaps); }
+    if (d->dAmps) { cudaFree(d->dAmps); }
     if (d->dStereo) { cudaFree(d->dStereo); }
     delete d;
+}
+
+int demodSwitchRotatorMode(DemodState* d, int newMode) {
+    if (!d || !d->dWtab) { return B200_OK; }
+    float2* dPhase = &d->dState->rotPhase;
+    int* dEnv = &d->dState->audio.startEnvelope;
+    if (newMode == B200_ROTATOR_EXACT) {
+        const float2 p = make_float2((float)cos(d->angle), (float)sin(d->angle));
+        B200_CUDA(cudaMemcpy(dPhase, &p, sizeof(float2), cudaMemcpyHostToDevice));
+        const int env = (int)std::min<long long>(d->envCount, 1 << 30);
+        B200_CUDA(cudaMemcpy(dEnv, &env, sizeof(int), cudaMemcpyHostToDevice));
+    }
+    else {
+        float2 p; int env = 0;
+        B200_CUDA(cudaMemcpy(&p, dPhase, sizeof(float2), cudaMemcpyDeviceToHost));
+        B200_CUDA(cudaMemcpy(&env, dEnv, sizeof(int), cudaMemcpyDeviceToHost));
+        d->angle = atan2((double)p.y, (double)p.x);
+        d->envCount = env;
+    }
+    return B200_OK;
 }
 
 static int demodEnsureCap(DemodState& d, int n) {
     if (n <= d.cap) { return B200_OK; }
     if (d.dMono) { cudaFree(d.dMono); d.dMono = nullptr; }
     if (d.dStereo) { cudaFree(d.dStereo); d.dStereo = nullptr; }
+    if (d.dMaps) { cudaFree(d.dMaps); d.dMaps = nullptr; }
+    if (d.dAmps) { cudaFree(d.dAmps); d.dAmps = nullptr; }
     d.cap = n + 64;
+    if (d.dWtab) {
+        B200_CUDA(cudaMalloc((void**)&d.dMaps, (size_t)d.cap * sizeof(float4)));
+        B200_CUDA(cudaMalloc((void**)&d.dAmps, (size_t)d.cap * sizeof(float)));
+    }
     B200_CUDA(cudaMalloc((void**)&d.dMono, (size_t)d.cap * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&d.dStereo, (size_t)d.cap * 2 * sizeof(float)));
     if (d.hasFir) { B200_TRY(d.fir.ensureOutCap(d.cap)); }
@@ -264,6 +477,7 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
     d->kind = kind; d->p0 = p0; d->p1 = p1; d->p2 = p2; d->p3 = p3;
     d->sr = v.outSR; d->bw = v.bw;
     SeqState init{};
+    init.rotPhase = make_float2(1.0f, 0.0f);
     auto agcInit = [&](double attack, double decay) {
         // agc.init(NULL, 1.0, attack, decay, 10e6, 10.0, INFINITY) (ssb.h:29, am.h:34-35): amp = setPoint / initGain = 0
         d->agc.setPoint = 1.0f; d->agc.attack = (float)attack; d->agc.invAttack = 1.0f - d->agc.attack;
@@ -295,6 +509,10 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
         if (bank.calSteps <= 0) { d->theta = atan2((double)d->dIm, (double)d->dRe); }
         d->angle = 0.0;
         agcInit(p1, p2);
+        float2 tab[kRotChunk];
+        makeRotatorTable(d->dRe, d->dIm, tab);
+        B200_CUDA(cudaMalloc((void**)&d->dWtab, sizeof(tab)));
+        B200_CUDA(cudaMemcpy(d->dWtab, tab, sizeof(tab), cudaMemcpyHostToDevice));
     }
     else {
         setError("unknown demodulator kind %d", kind);
@@ -310,7 +528,7 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
 }
 
 int processDemods(VfoBank& bank, cudaStream_t s) {
-    std::vector<DemodJob> seq, quad, all;
+    std::vector<DemodJob> seq, quad, all, ssb;
     std::vector<FirJob> firs;
     int maxN = 0;
     for (size_t vi = 0; vi < bank.vfos.size(); vi++) {
@@ -321,7 +539,10 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         d.lastCount = n;
         if (n > d.cap) { B200_CUDA(cudaStreamSynchronize(s)); B200_TRY(demodEnsureCap(d, n)); }
         DemodJob j{};
-        j.in = v.lastOutPtr; j.mono = d.dMono; j.stereo = d.dStereo; j.st = d.dState;
+        j.in = v.lastOutPtr; j.mono = d.dMono; j.stereo = d.dStereo; j.st = d.dState; j.wtab = d.dWtab;
+        j.exact = (bank.rotatorMode == B200_ROTATOR_EXACT) ? 1 : 0;
+        j.maps = d.dMaps; j.amps = d.dAmps;
+        j.env0 = (int)std::min<long long>(d.envCount, 1 << 30);
         j.agc = d.agc; j.angle0 = d.angle; j.theta = d.theta; j.stepRe = d.dRe; j.stepIm = d.dIm;
         j.invDeviation = d.invDeviation; j.dcRate = d.dcRate; j.kind = d.kind; j.agcMode = d.agcMode; j.n = n; j.quadParity = d.quadParity;
         const float* src = d.dMono;
@@ -334,16 +555,23 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         j.stereoSrc = src;
         if (n > 0) {
             if (d.kind == B200_DEMOD_NFM) { quad.push_back(j); d.quadParity ^= 1; }
-            else { seq.push_back(j); d.angle = fmod(d.angle + d.theta * (double)n, 2.0 * design::kPi); }
+            else {
+                const bool isSsb = (d.kind != B200_DEMOD_AM);
+                const bool fastSsb = isSsb && !j.exact && d.agc.attack > 0.0f && d.dMaps;
+                if (fastSsb) { ssb.push_back(j); } else { seq.push_back(j); }
+                if (isSsb && !j.exact) { d.angle = fmod(d.angle + d.theta * (double)n, 2.0 * design::kPi); }
+                if (isSsb && d.agc.attack > 0.0f) { d.envCount += n; }
+                if (!fastSsb) { all.push_back(j); }
+                maxN = std::max(maxN, n);
+                continue;
+            }
             all.push_back(j);
             maxN = std::max(maxN, n);
         }
     }
-    if (all.empty() && firs.empty()) { return B200_OK; }
+    if (all.empty() && firs.empty() && ssb.empty()) { return B200_OK; }
     // one upload: [seq][quad][all][firs]
-    const size_t bytes = (seq.size() + quad.size() + all.size()) * sizeof(DemodJob) + firs.size() * sizeof(FirJob) + 256;
-    static thread_local std::vector<char> scratch;
-    (void)scratch;
+    const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + firs.size() * sizeof(FirJob) + 512;
     void* hp = nullptr; int slot = 0;
     B200_TRY(bank.ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -352,6 +580,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     const size_t oQ = put(quad.data(), quad.size() * sizeof(DemodJob));
     const size_t oA = put(all.data(), all.size() * sizeof(DemodJob));
     const size_t oF = put(firs.data(), firs.size() * sizeof(FirJob));
+    const size_t oB = put(ssb.data(), ssb.size() * sizeof(DemodJob));
     if (off > bank.dDemodDescBytes) {
         B200_CUDA(cudaStreamSynchronize(s));
         if (bank.dDemodDesc) { cudaFree(bank.dDemodDesc); }
@@ -365,14 +594,26 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         quadratureKernel<<<dim3((maxN + 255) / 256, (unsigned)quad.size()), 256, 0, s>>>((const DemodJob*)(dd + oQ));
         B200_CHECK_LAUNCH(); countLaunch();
     }
+    if (!ssb.empty()) {
+        int maxS = 0;
+        for (auto& j : ssb) { maxS = std::max(maxS, j.n); }
+        const dim3 grid((maxS + 255) / 256, (unsigned)ssb.size());
+        ssbPrepKernel<<<grid, 256, 0, s>>>((const DemodJob*)(dd + oB));
+        B200_CHECK_LAUNCH();
+        agcWalkKernel<<<(unsigned)ssb.size(), 32, 0, s>>>((const DemodJob*)(dd + oB));
+        B200_CHECK_LAUNCH();
+        ssbFinishKernel<<<grid, 256, 0, s>>>((const DemodJob*)(dd + oB));
+        B200_CHECK_LAUNCH();
+        countLaunch(3);
+    }
     if (!seq.empty()) {
-        seqDemodKernel<<<(unsigned)seq.size(), 32, 0, s>>>((const DemodJob*)(dd + oS));
+        seqDemodKernel<<<(unsigned)seq.size(), kSeqThreads, 0, s>>>((const DemodJob*)(dd + oS));
         B200_CHECK_LAUNCH(); countLaunch();
     }
     if (!firs.empty()) {
-        int maxOut = 0, maxH = 0;
-        for (auto& f : firs) { maxOut = std::max(maxOut, f.nOut); maxH = std::max(maxH, f.H); }
-        B200_TRY(launchFirJobs((const FirJob*)(dd + oF), (int)firs.size(), maxOut, 1, s));
+        int maxOut = 0, maxH = 0, maxSpan = 0;
+        for (auto& f : firs) { maxOut = std::max(maxOut, f.nOut); maxH = std::max(maxH, f.H); maxSpan = std::max(maxSpan, firJobSpan(f)); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oF), (int)firs.size(), maxOut, 1, maxSpan, s));
         B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oF), (int)firs.size(), maxH, s));
     }
     if (!all.empty()) {

@@ -7,4 +7,6 @@ struct VfoBank;
 struct DemodState;
 void demodDestroy(DemodState* d);
 int processDemods(VfoBank& bank, cudaStream_t s);
+// carries an SSB demodulator's internal rotator phase across a FAST <-> EXACT switch
+int demodSwitchRotatorMode(DemodState* d, int newMode);
 } // namespace b200

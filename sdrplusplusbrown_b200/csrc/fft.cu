@@ -2,10 +2,14 @@
 //   :271  fftIn[i] = data[i] * window[i]   (window carries the (-1)^i fft-shift, :303-311; tail zero, :317)
 //   :274  forward c2c FFT of size N (FFTW in the reference, utils/arrays.cpp:533-546)
 //   :282  out[k] = 10*log10((re^2+im^2)/N^2) (VOLK power spectrum, log2 clamped at +-127)
-// N <= 8192: one CTA per frame, whole transform in shared memory.
-// N >  8192: N = N1 x N2 in two kernels; the N1 x N2 intermediate lives in a small scratch ring that
-// stays resident in the 126 MB L2, so HBM sees the samples once and the dB row once.
-// Radix-2 DIT on bit-reversed shared-memory rows, twiddles from float64-designed tables.
+//
+// Stockham autosort FFT, radix 16/8/4/2 butterflies held in registers, stages exchanged through two
+// ping-pong shared-memory buffers (one barrier per stage, no bit reversal), twiddles from float64-designed
+// tables.  N <= 8192: one CTA per frame.  N > 8192: N = N1 x N2 in two kernels -- pass 1 transforms C adjacent
+// columns (stride N2, so global reads stay 64-128 B contiguous), applies the inter-pass twiddle and leaves the
+// N1 x N2 intermediate in a small scratch ring that stays resident in the 126 MB L2; pass 2 transforms R
+// adjacent rows and emits dB (or the complex spectrum) with R-wide contiguous stores.  HBM sees the windowed
+// samples once and the dB row once.
 #include "fft.cuh"
 
 #include <cmath>
@@ -16,8 +20,128 @@ namespace {
 
 constexpr int kThreads = 256;
 
-__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
-    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 mulNegI(float2 a) { return make_float2(a.y, -a.x); }   // a * (-i)
+
+// shared-memory slot of element i: one pad element per 16 so that the stride-R stores of the first Stockham
+// stage (and stride-2^k accesses in general) spread over the banks
+__device__ __host__ __forceinline__ int slot(int i) { return i + (i >> 4); }
+
+// exp(-2*pi*i*m/16), m = 0..15
+__device__ __forceinline__ float2 w16(int m) {
+    constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, C2 = 0.70710678118654752f;
+    switch (m & 15) {
+    case 0: return make_float2(1.f, 0.f);
+    case 1: return make_float2(C1, -S1);
+    case 2: return make_float2(C2, -C2);
+    case 3: return make_float2(S1, -C1);
+    case 4: return make_float2(0.f, -1.f);
+    case 5: return make_float2(-S1, -C1);
+    case 6: return make_float2(-C2, -C2);
+    case 7: return make_float2(-C1, -S1);
+    case 8: return make_float2(-1.f, 0.f);
+    case 9: return make_float2(-C1, S1);
+    case 10: return make_float2(-C2, C2);
+    case 11: return make_float2(-S1, C1);
+    case 12: return make_float2(0.f, 1.f);
+    case 13: return make_float2(S1, C1);
+    case 14: return make_float2(C2, C2);
+    default: return make_float2(C1, S1);
+    }
+}
+
+// ---- R-point forward DFTs in registers (natural order in, natural order out)
+template <int R> struct Dft;
+template <> struct Dft<2> {
+    static __device__ __forceinline__ void run(float2* v) {
+        const float2 a = v[0], b = v[1];
+        v[0] = cadd(a, b); v[1] = csub(a, b);
+    }
+};
+template <> struct Dft<4> {
+    static __device__ __forceinline__ void run(float2* v) {
+        const float2 a0 = cadd(v[0], v[2]), a1 = csub(v[0], v[2]), a2 = cadd(v[1], v[3]), a3 = mulNegI(csub(v[1], v[3]));
+        v[0] = cadd(a0, a2); v[2] = csub(a0, a2);
+        v[1] = cadd(a1, a3); v[3] = csub(a1, a3);
+    }
+};
+// R = R1 * R2 by Cooley-Tukey on registers: n = R2*n1 + n2, k = k1 + R1*k2
+template <int R1, int R2>
+__device__ __forceinline__ void dftComposite(float2* v) {
+    constexpr int R = R1 * R2;
+    float2 t[R];
+#pragma unroll
+    for (int n2 = 0; n2 < R2; n2++) {
+        float2 x[R1];
+#pragma unroll
+        for (int n1 = 0; n1 < R1; n1++) { x[n1] = v[R2 * n1 + n2]; }
+        Dft<R1>::run(x);
+#pragma unroll
+        for (int k1 = 0; k1 < R1; k1++) { t[k1 * R2 + n2] = (n2 * k1 == 0) ? x[k1] : cmul(x[k1], w16(n2 * k1 * (16 / R))); }
+    }
+#pragma unroll
+    for (int k1 = 0; k1 < R1; k1++) {
+        float2 y[R2];
+#pragma unroll
+        for (int n2 = 0; n2 < R2; n2++) { y[n2] = t[k1 * R2 + n2]; }
+        Dft<R2>::run(y);
+#pragma unroll
+        for (int k2 = 0; k2 < R2; k2++) { v[k1 + R1 * k2] = y[k2]; }
+    }
+}
+template <> struct Dft<8> { static __device__ __forceinline__ void run(float2* v) { dftComposite<4, 2>(v); } };
+template <> struct Dft<16> { static __device__ __forceinline__ void run(float2* v) { dftComposite<4, 4>(v); } };
+
+// One Stockham stage of radix R on nb rows of length L (row pitch LP slots) from src to dst.
+// Ns = product of the radices already applied.  tw[m] = exp(-2*pi*i*m/L), m < L.
+template <int R, int LOGR>
+__device__ __forceinline__ void stockhamStage(const float2* __restrict__ src, float2* __restrict__ dst, int logL, int logNs, int LP, int nb,
+                                              const float2* __restrict__ tw) {
+    const int logPer = logL - LOGR;
+    const int per = 1 << logPer;
+    const int total = nb << logPer;
+    const int Ns = 1 << logNs;
+    const int sh = logL - logNs - LOGR;              // twiddle index = (k*r) << sh
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const int b = idx >> logPer, j = idx & (per - 1);
+        const int k = j & (Ns - 1);
+        const float2* s = src + b * LP;
+        float2 v[R];
+#pragma unroll
+        for (int r = 0; r < R; r++) { v[r] = s[slot(j + r * per)]; }
+        if (logNs > 0) {
+#pragma unroll
+            for (int r = 1; r < R; r++) { v[r] = cmul(v[r], __ldg(tw + ((k * r) << sh))); }
+        }
+        Dft<R>::run(v);
+        const int j0 = ((j - k) << LOGR) + k;
+        float2* d = dst + b * LP;
+#pragma unroll
+        for (int r = 0; r < R; r++) { d[slot(j0 + r * Ns)] = v[r]; }
+    }
+}
+
+// all stages of a length-L transform; radix plan packed 4 bits per stage (log2 of the radix), first stage in the low nibble.
+// Returns the buffer holding the result.
+__device__ float2* fftRows(float2* a, float2* b, int logL, unsigned plan, int LP, int nb, const float2* __restrict__ tw) {
+    int logNs = 0;
+    float2 *src = a, *dst = b;
+    while (plan) {
+        const int lr = plan & 15;
+        plan >>= 4;
+        switch (lr) {
+        case 4: stockhamStage<16, 4>(src, dst, logL, logNs, LP, nb, tw); break;
+        case 3: stockhamStage<8, 3>(src, dst, logL, logNs, LP, nb, tw); break;
+        case 2: stockhamStage<4, 2>(src, dst, logL, logNs, LP, nb, tw); break;
+        default: stockhamStage<2, 1>(src, dst, logL, logNs, LP, nb, tw); break;
+        }
+        __syncthreads();
+        logNs += lr;
+        float2* t = src; src = dst; dst = t;
+    }
+    return src;
 }
 
 __device__ __forceinline__ float2 frameSample(const FrameDesc& f, const float* __restrict__ win, int i, int nz) {
@@ -26,30 +150,6 @@ __device__ __forceinline__ float2 frameSample(const FrameDesc& f, const float* _
                                   : __ldg(reinterpret_cast<const float2*>(f.src1) + (i - f.len0));
     const float w = win ? __ldg(win + i) : 1.0f;
     return make_float2(x.x * w, x.y * w);
-}
-
-// nb independent length-L transforms stored as rows of pitch LP in shared memory, inputs already in
-// bit-reversed order.  tw[j] = exp(-2*pi*i*j/L), j < L/2.
-__device__ void fftRows(float2* s, int L, int logL, int LP, int nb, const float2* __restrict__ tw) {
-    const int halfL = L >> 1;
-    const int total = nb * halfL;
-    for (int lg = 1; lg <= logL; lg++) {
-        const int half = 1 << (lg - 1);
-        const int twStride = L >> lg;
-        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-            const int b = idx / halfL;
-            const int r = idx - b * halfL;
-            const int k = r & (half - 1);
-            const int i0 = b * LP + ((r >> (lg - 1)) << lg) + k;
-            const int i1 = i0 + half;
-            const float2 w = __ldg(tw + k * twStride);
-            const float2 a = s[i0];
-            const float2 t = cmul(s[i1], w);
-            s[i0] = make_float2(a.x + t.x, a.y + t.y);
-            s[i1] = make_float2(a.x - t.x, a.y - t.y);
-        }
-        __syncthreads();
-    }
 }
 
 __device__ __forceinline__ float powerDb(float2 X, float invN) {
@@ -61,18 +161,20 @@ __device__ __forceinline__ float powerDb(float2 X, float invN) {
 
 // ---- N <= 8192: one CTA per frame
 __global__ void __launch_bounds__(kThreads) fftSingleKernel(const FrameDesc* __restrict__ frames, const float* __restrict__ win, int nz,
-                                                            int N, int logN, const float2* __restrict__ tw, float* __restrict__ outDb,
-                                                            cf32* __restrict__ outSpec) {
+                                                            int N, int logN, unsigned plan, const float2* __restrict__ tw,
+                                                            float* __restrict__ outDb, cf32* __restrict__ outSpec) {
     extern __shared__ __align__(16) float2 sm[];
+    const int LP = slot(N) + 1;
+    float2* bufA = sm;
+    float2* bufB = sm + LP;
     const FrameDesc f = frames[blockIdx.x];
-    for (int i = threadIdx.x; i < N; i += kThreads) {
-        sm[__brev((unsigned)i) >> (32 - logN)] = frameSample(f, win, i, nz);
-    }
+#pragma unroll 8
+    for (int i = threadIdx.x; i < N; i += kThreads) { bufA[slot(i)] = frameSample(f, win, i, nz); }
     __syncthreads();
-    fftRows(sm, N, logN, N, 1, tw);
+    const float2* res = fftRows(bufA, bufB, logN, plan, LP, 1, tw);
     const float invN = 1.0f / (float)N;
     for (int k = threadIdx.x; k < N; k += kThreads) {
-        const float2 X = sm[k];
+        const float2 X = res[slot(k)];
         if (outDb) { outDb[(size_t)blockIdx.x * N + k] = powerDb(X, invN); }
         if (outSpec) { reinterpret_cast<float2*>(outSpec)[(size_t)blockIdx.x * N + k] = X; }
     }
@@ -81,52 +183,62 @@ __global__ void __launch_bounds__(kThreads) fftSingleKernel(const FrameDesc* __r
 // ---- N = N1 * N2, pass 1: C adjacent columns n2 per CTA, length-N1 transforms over n1 (input stride N2),
 // then the inter-pass twiddle W_N^(n2*k1); result T[k1][n2].
 __global__ void __launch_bounds__(kThreads) fftPass1Kernel(const FrameDesc* __restrict__ frames, const float* __restrict__ win, int nz,
-                                                           int N1, int logN1, int N2, int C, const float2* __restrict__ twN1,
+                                                           int logN1, int logN2, int logC, unsigned plan, const float2* __restrict__ twN1,
                                                            const float2* __restrict__ twLo, const float2* __restrict__ twHi, int logS,
                                                            cf32* __restrict__ scratch, int scratchFrames) {
     extern __shared__ __align__(16) float2 sm[];
+    const int N1 = 1 << logN1, N2 = 1 << logN2, C = 1 << logC;
     const FrameDesc f = frames[blockIdx.y];
-    const int c0 = blockIdx.x * C;
-    const int LP = N1 + 1;
-    const int total = N1 * C;
+    const int c0 = blockIdx.x << logC;
+    const int LP = slot(N1) + 1;
+    float2* bufA = sm;
+    float2* bufB = sm + C * LP;
+    const int total = N1 << logC;
+#pragma unroll 8
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-        const int c = idx % C, n1 = idx / C;
-        sm[c * LP + (__brev((unsigned)n1) >> (32 - logN1))] = frameSample(f, win, n1 * N2 + c0 + c, nz);
+        const int c = idx & (C - 1), n1 = idx >> logC;
+        bufA[c * LP + slot(n1)] = frameSample(f, win, (n1 << logN2) + c0 + c, nz);
     }
     __syncthreads();
-    fftRows(sm, N1, logN1, LP, C, twN1);
-    float2* T = reinterpret_cast<float2*>(scratch) + (size_t)(blockIdx.y % scratchFrames) * ((size_t)N1 * N2);
+    const float2* res = fftRows(bufA, bufB, logN1, plan, LP, C, twN1);
+    float2* T = reinterpret_cast<float2*>(scratch) + ((size_t)(blockIdx.y % scratchFrames) << (logN1 + logN2));
     const int maskS = (1 << logS) - 1;
+#pragma unroll 4
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-        const int c = idx % C, k1 = idx / C;
+        const int c = idx & (C - 1), k1 = idx >> logC;
         const int m = (c0 + c) * k1;                     // < N
         const float2 w = cmul(__ldg(twLo + (m & maskS)), __ldg(twHi + (m >> logS)));
-        T[(size_t)k1 * N2 + c0 + c] = cmul(sm[c * LP + k1], w);
+        T[((size_t)k1 << logN2) + c0 + c] = cmul(res[c * LP + slot(k1)], w);
     }
 }
 
 // pass 2: R adjacent rows k1 per CTA, length-N2 transforms over n2; X[k1 + N1*k2].
-__global__ void __launch_bounds__(kThreads) fftPass2Kernel(int N1, int N2, int logN2, int R, const float2* __restrict__ twN2,
+__global__ void __launch_bounds__(kThreads) fftPass2Kernel(int logN1, int logN2, int logR, unsigned plan, const float2* __restrict__ twN2,
                                                            const cf32* __restrict__ scratch, int scratchFrames, int frameBase,
                                                            float* __restrict__ outDb, cf32* __restrict__ outSpec) {
     extern __shared__ __align__(16) float2 sm[];
+    const int N2 = 1 << logN2, R = 1 << logR;
     const int frame = frameBase + blockIdx.y;
-    const int r0 = blockIdx.x * R;
-    const int LP = N2 + 1;
-    const int total = N2 * R;
-    const float2* T = reinterpret_cast<const float2*>(scratch) + (size_t)(frame % scratchFrames) * ((size_t)N1 * N2);
+    const int r0 = blockIdx.x << logR;
+    const int LP = slot(N2) + 1;
+    float2* bufA = sm;
+    float2* bufB = sm + R * LP;
+    const int total = N2 << logR;
+    const float2* T = reinterpret_cast<const float2*>(scratch) + ((size_t)(frame % scratchFrames) << (logN1 + logN2));
+#pragma unroll 8
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-        const int n2 = idx % N2, r = idx / N2;
-        sm[r * LP + (__brev((unsigned)n2) >> (32 - logN2))] = T[(size_t)(r0 + r) * N2 + n2];
+        const int n2 = idx & (N2 - 1), r = idx >> logN2;
+        bufA[r * LP + slot(n2)] = T[((size_t)(r0 + r) << logN2) + n2];
     }
     __syncthreads();
-    fftRows(sm, N2, logN2, LP, R, twN2);
-    const size_t N = (size_t)N1 * N2;
+    const float2* res = fftRows(bufA, bufB, logN2, plan, LP, R, twN2);
+    const size_t N = (size_t)1 << (logN1 + logN2);
     const float invN = 1.0f / (float)N;
+#pragma unroll 4
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-        const int r = idx % R, k2 = idx / R;
-        const float2 X = sm[r * LP + k2];
-        const size_t k = (size_t)k2 * N1 + r0 + r;
+        const int r = idx & (R - 1), k2 = idx >> logR;
+        const float2 X = res[r * LP + slot(k2)];
+        const size_t k = ((size_t)k2 << logN1) + r0 + r;
         if (outDb) { outDb[(size_t)frame * N + k] = powerDb(X, invN); }
         if (outSpec) { reinterpret_cast<float2*>(outSpec)[(size_t)frame * N + k] = X; }
     }
@@ -143,13 +255,34 @@ int uploadTwiddles(float2** d, int count, int N, int stride) {
     return B200_OK;
 }
 
-int pickBatch(int L, int want, size_t smemCap) {
-    int b = want;
-    while (b > 1 && (size_t)b * (L + 1) * sizeof(float2) > smemCap) { b >>= 1; }
-    return b;
+// log2 radices, as even as possible, at most 4 bits (radix 16) per stage; first stage in the low nibble
+unsigned radixPlan(int logL) {
+    const int stages = (logL + 3) / 4;
+    unsigned plan = 0;
+    int left = logL;
+    for (int s = 0; s < stages; s++) {
+        const int lr = (left + (stages - s) - 1) / (stages - s);
+        plan |= (unsigned)lr << (4 * s);
+        left -= lr;
+    }
+    return plan;
 }
 
-constexpr size_t kSmemCap = 160 * 1024;
+int log2i(int v) { int l = 0; while ((1 << l) < v) { l++; } return l; }
+
+size_t rowsSmem(int L, int nb) { return (size_t)2 * nb * (slot(L) + 1) * sizeof(float2); }
+
+constexpr size_t kSmemSoft = 72 * 1024;    // 3 CTAs per SM
+constexpr size_t kSmemHard = 200 * 1024;
+
+// rows (or columns) per CTA: as many as wanted within the soft cap, but never fewer than 8 (32-byte segments)
+// unless even that exceeds the hard cap
+int pickBatchLog(int L, int wantLog) {
+    int lg = wantLog;
+    while (lg > 3 && rowsSmem(L, 1 << lg) > kSmemSoft) { lg--; }
+    while (lg > 0 && rowsSmem(L, 1 << lg) > kSmemHard) { lg--; }
+    return lg;
+}
 
 } // namespace
 
@@ -157,18 +290,17 @@ int FftPlan::create(int N_, int device_) {
     destroy();
     device = device_;
     N = N_;
-    logN = 0;
-    while ((1 << logN) < N) { logN++; }
+    logN = log2i(N);
     if ((1 << logN) != N || logN < 5 || logN > 22) { setError("fft size %d is not a power of two in [32, 4194304]", N); return B200_EINVAL; }
     if (logN <= 13) {
         N1 = 1; N2 = N;
-        B200_TRY(uploadTwiddles(&dTwN2, N / 2, N, 1));
+        B200_TRY(uploadTwiddles(&dTwN2, N, N, 1));
     }
     else {
         const int l2 = (logN + 1) / 2;
         N2 = 1 << l2; N1 = N >> l2;
-        B200_TRY(uploadTwiddles(&dTwN1, N1 / 2, N1, 1));
-        B200_TRY(uploadTwiddles(&dTwN2, N2 / 2, N2, 1));
+        B200_TRY(uploadTwiddles(&dTwN1, N1, N1, 1));
+        B200_TRY(uploadTwiddles(&dTwN2, N2, N2, 1));
         logS = l2; S = 1 << logS;
         B200_TRY(uploadTwiddles(&dTwLo, S, N, 1));
         B200_TRY(uploadTwiddles(&dTwHi, N >> logS, N, S));
@@ -197,30 +329,29 @@ int FftPlan::ensureScratch(int frames) {
 int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s) {
     if (nFrames <= 0) { return B200_OK; }
     if (N1 == 1) {
-        const size_t smem = (size_t)N * sizeof(float2);
+        const size_t smem = rowsSmem(N, 1);
         B200_CUDA(cudaFuncSetAttribute(fftSingleKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        fftSingleKernel<<<nFrames, kThreads, smem, s>>>(dFrames, dWindow, nz, N, logN, dTwN2, outDb, outSpec);
+        fftSingleKernel<<<nFrames, kThreads, smem, s>>>(dFrames, dWindow, nz, N, logN, radixPlan(logN), dTwN2, outDb, outSpec);
         B200_CHECK_LAUNCH();
         countLaunch();
         return B200_OK;
     }
     B200_TRY(ensureScratch(nFrames));
-    int logN1 = 0, logN2 = 0;
-    while ((1 << logN1) < N1) { logN1++; }
-    while ((1 << logN2) < N2) { logN2++; }
-    const int C = pickBatch(N1, 16, kSmemCap);
-    const int R = pickBatch(N2, 32, kSmemCap);
-    const size_t smem1 = (size_t)C * (N1 + 1) * sizeof(float2), smem2 = (size_t)R * (N2 + 1) * sizeof(float2);
+    const int logN1 = log2i(N1), logN2 = log2i(N2);
+    const int logC = pickBatchLog(N1, 4);      // up to 16 columns: 128-byte global segments
+    const int logR = pickBatchLog(N2, 5);      // up to 32 rows: 128-byte dB segments
+    const size_t smem1 = rowsSmem(N1, 1 << logC), smem2 = rowsSmem(N2, 1 << logR);
     B200_CUDA(cudaFuncSetAttribute(fftPass1Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     B200_CUDA(cudaFuncSetAttribute(fftPass2Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-    // frames are processed in groups that fit the scratch ring, pass 2 right behind pass 1 (L2 reuse)
+    const unsigned plan1 = radixPlan(logN1), plan2 = radixPlan(logN2);
+    // frames are processed in groups that fit the scratch ring, pass 2 right behind pass 1 (L2 reuse);
+    // the ring index is (frame % scratchFrames) and groups start at multiples of scratchFrames
     for (int f0 = 0; f0 < nFrames; f0 += scratchFrames) {
         const int nf = std::min(scratchFrames, nFrames - f0);
-        // the ring index is (frame % scratchFrames); groups start at multiples of scratchFrames
-        fftPass1Kernel<<<dim3(N2 / C, nf), kThreads, smem1, s>>>(dFrames + f0, dWindow, nz, N1, logN1, N2, C, dTwN1, dTwLo, dTwHi, logS,
-                                                                 dScratch, scratchFrames);
+        fftPass1Kernel<<<dim3(N2 >> logC, nf), kThreads, smem1, s>>>(dFrames + f0, dWindow, nz, logN1, logN2, logC, plan1, dTwN1, dTwLo, dTwHi,
+                                                                     logS, dScratch, scratchFrames);
         B200_CHECK_LAUNCH();
-        fftPass2Kernel<<<dim3(N1 / R, nf), kThreads, smem2, s>>>(N1, N2, logN2, R, dTwN2, dScratch, scratchFrames, f0, outDb, outSpec);
+        fftPass2Kernel<<<dim3(N1 >> logR, nf), kThreads, smem2, s>>>(logN1, logN2, logR, plan2, dTwN2, dScratch, scratchFrames, f0, outDb, outSpec);
         B200_CHECK_LAUNCH();
         countLaunch(2);
     }

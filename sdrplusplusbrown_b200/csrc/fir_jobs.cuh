@@ -32,7 +32,8 @@ struct FirJob {
 
 // Launchers (all jobs of one "level" in a single launch; grid.y = job index)
 // every job of a launch must have the same elemFloats
-int launchFirJobs(const FirJob* d_jobs, int nJobs, int maxOut, int elemFloats, cudaStream_t s);
+int firJobSpan(const FirJob& j);   // elements of input window one CTA stages for this job
+int launchFirJobs(const FirJob* d_jobs, int nJobs, int maxOut, int elemFloats, int maxSpanElems, cudaStream_t s);
 int launchHistoryUpdate(const FirJob* d_jobs, int nJobs, int maxH, cudaStream_t s);
 
 } // namespace b200

@@ -178,6 +178,10 @@ struct FrontEnd {
     double effectiveSr = 0;
     b200_vfo_bank* bank = nullptr;
     cudaStream_t lastStream = nullptr; bool everRan = false;
+    // the FFT branch and the VFO branch are independent consumers of the pre-processed block (the reference
+    // runs them on separate threads behind the Splitter): fork the FFT branch onto a side stream and join
+    cudaStream_t fftStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
 
     // pre-processing
     std::vector<Stage> decimStages;
@@ -258,6 +262,9 @@ int FrontEnd::init() {
     if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
     effectiveSr = sampleRate / decimRatio;
     B200_TRY(ring.init(64 * 1024));
+    B200_CUDA(cudaStreamCreateWithFlags(&fftStream, cudaStreamNonBlocking));
+    B200_CUDA(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
+    B200_CUDA(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
     B200_TRY(rebuildDecim());
     B200_CUDA(cudaMalloc((void**)&dDcState, 2 * sizeof(double2)));
     B200_CUDA(cudaMemset(dDcState, 0, 2 * sizeof(double2)));
@@ -270,6 +277,9 @@ int FrontEnd::init() {
 void FrontEnd::destroy() {
     DeviceGuard g(device);
     if (everRan) { cudaStreamSynchronize(lastStream); }
+    if (fftStream) { cudaStreamSynchronize(fftStream); cudaStreamDestroy(fftStream); fftStream = nullptr; }
+    if (evFork) { cudaEventDestroy(evFork); evFork = nullptr; }
+    if (evJoin) { cudaEventDestroy(evJoin); evJoin = nullptr; }
     if (bank) { bank->impl.destroy(); delete bank; bank = nullptr; }
     for (auto& st : decimStages) { st.destroy(); }
     decimStages.clear();
@@ -301,7 +311,7 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(ring.release(slot, s));
         int maxH = 0;
         for (size_t i = 0; i < jobs.size(); i++) {
-            B200_TRY(launchFirJobs((const FirJob*)dJobDesc + i, 1, jobs[i].nOut, 2, s));
+            B200_TRY(launchFirJobs((const FirJob*)dJobDesc + i, 1, jobs[i].nOut, 2, firJobSpan(jobs[i]), s));
             maxH = std::max(maxH, jobs[i].H);
         }
         B200_TRY(launchHistoryUpdate((const FirJob*)dJobDesc, (int)jobs.size(), maxH, s));
@@ -408,8 +418,18 @@ int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s) {
     if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
     lastStream = s; everRan = true;
     B200_TRY(preprocess(dIn, count, s));
-    B200_TRY(fftBranch(s));
-    if (bank->impl.liveCount() > 0) { B200_TRY(bank->impl.process(preOut, preCount, s)); }
+    const bool fork = bank->impl.liveCount() > 0;
+    if (fork) {
+        B200_CUDA(cudaEventRecord(evFork, s));
+        B200_CUDA(cudaStreamWaitEvent(fftStream, evFork, 0));
+        B200_TRY(fftBranch(fftStream));
+        B200_CUDA(cudaEventRecord(evJoin, fftStream));
+        B200_TRY(bank->impl.process(preOut, preCount, s));
+        B200_CUDA(cudaStreamWaitEvent(s, evJoin, 0));
+    }
+    else {
+        B200_TRY(fftBranch(s));
+    }
     return B200_OK;
 }
 

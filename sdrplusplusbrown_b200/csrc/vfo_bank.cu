@@ -340,7 +340,11 @@ int VfoBank::setRotatorMode(int mode) {
     std::vector<std::pair<double, double>> ph(vfos.size());
     for (size_t i = 0; i < vfos.size(); i++) { if (vfos[i].live) { B200_TRY(getPhase(vfos[i], &ph[i].first, &ph[i].second)); } }
     rotatorMode = mode;
-    for (size_t i = 0; i < vfos.size(); i++) { if (vfos[i].live) { B200_TRY(setPhase(vfos[i], ph[i].first, ph[i].second)); } }
+    for (size_t i = 0; i < vfos.size(); i++) {
+        if (!vfos[i].live) { continue; }
+        B200_TRY(setPhase(vfos[i], ph[i].first, ph[i].second));
+        B200_TRY(demodSwitchRotatorMode(vfos[i].demod, mode));
+    }
     return B200_OK;
 }
 
@@ -454,9 +458,9 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
         for (size_t l = 0; l < levels.size(); l++) {
-            int maxOutL = 0;
-            for (auto& j : levels[l]) { maxOutL = std::max(maxOutL, j.nOut); }
-            B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), (int)levels[l].size(), maxOutL, 2, s));
+            int maxOutL = 0, maxSpan = 0;
+            for (auto& j : levels[l]) { maxOutL = std::max(maxOutL, j.nOut); maxSpan = std::max(maxSpan, firJobSpan(j)); }
+            B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), (int)levels[l].size(), maxOutL, 2, maxSpan, s));
         }
     }
     else if (!fj.empty()) {

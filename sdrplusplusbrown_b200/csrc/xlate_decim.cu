@@ -77,9 +77,17 @@ template <int RATIO> struct FirstStage;
 constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
 
 template <int D> struct TileCfg {
-    // sub-blocks (= threads) per CTA: ~8192 samples of input per tile
-    static constexpr int SB = (8192 / D) > 256 ? 256 : ((8192 / D) < 64 ? 64 : (8192 / D));
+    // sub-blocks (= threads) per CTA: ~4096 samples (32 KB) of input per tile, so that 4-6 CTAs are resident per
+    // SM and one CTA's load phase overlaps its neighbours' arithmetic
+    static constexpr int SB = (4096 / D) > 256 ? 256 : ((4096 / D) < 64 ? 64 : (4096 / D));
 };
+
+// 8-byte asynchronous global->shared copy (LDGSTS); src_size 0 zero-fills without touching memory
+__device__ __forceinline__ void cpAsync8(float2* smemDst, const float2* gsrc, bool valid) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    const int sz = valid ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
 
 __device__ __forceinline__ float2 cmulf(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
@@ -119,12 +127,15 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     const float2* in = reinterpret_cast<const float2*>(j0.in);
 
     // ---- stage the input tile once for the whole VFO group (zero outside [0, count))
+    // (all D copies of a thread are in flight at once; no register staging)
+#pragma unroll 8
     for (int i = tid; i < SB * D; i += SB) {
         const int m = mStart + i;
-        float2 v = make_float2(0.f, 0.f);
-        if (m >= 0 && m < j0.count) { v = __ldg(in + m); }
-        xs[i + i / D] = v;
+        const bool ok = (m >= 0 && m < j0.count);
+        cpAsync8(xs + i + i / D, in + (ok ? m : 0), ok);
     }
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 
     const int ms = mStart + tid * D;
     const int gEnd = min(g0 + G, nJobs);

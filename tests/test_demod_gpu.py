@@ -39,9 +39,12 @@ def _demod_pair(name):
 DEMODS = ["demod_nfm", "demod_usb", "demod_lsb", "demod_am", "demod_am_carrier"]
 
 
+@pytest.mark.parametrize("mode", ["exact", "fast"])
 @pytest.mark.parametrize("name", DEMODS)
-def test_vfo_plus_demod_chain_matches_oracle(name):
-    """VFO (channel filter on) -> demodulator, both against the oracle chain, blocks of ragged size."""
+def test_vfo_plus_demod_chain_matches_oracle(name, mode):
+    """VFO (channel filter on) -> demodulator, both against the oracle chain, blocks of ragged size.
+    exact: free-running.  fast: the VFO's rotator phase is taken from the oracle per block; the SSB demodulator's
+    own rotator runs in closed form (parallel prep / AGC walk / finish kernels)."""
     from sdrplusplusbrown_b200 import binding
     out_sr, o_dem, (kind, p0, p1, p2, p3), bw = _demod_pair(name)
     in_sr = out_sr * 32
@@ -51,10 +54,13 @@ def test_vfo_plus_demod_chain_matches_oracle(name):
     x[100000:100200] = 0
     o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
     b = binding.VfoBank(in_sr, max_block=200000)
-    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    if mode == "exact":
+        b.set_rotator_mode(binding.ROTATOR_EXACT)
     v = b.add(out_sr, bw, off)
     b.set_demod(v, kind, p0, p1, p2, p3)
     for blk in split(x, [96000, 4800 * 32 + 17, 33]):
+        if mode == "fast":
+            b.set_phase(v, o_vfo.phase())
         iq = o_vfo.process(blk)
         ref = o_dem.process(iq) if len(iq) else np.zeros((0, 2), np.float32)
         b.process(to_dev(blk))
