@@ -188,6 +188,25 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index o
 int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
                                float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
 
+/* DC blocker (dsp::correction::DCBlocker<complex_t>::process, correction/dc_blocker.h:54-60) for callers that
+ * are not allowed to allocate.  This entry point has no counterpart in the reference; it exists for hosts that
+ * cannot call cudaMalloc while running -- a real-time DSP/audio callback thread (cudaMalloc can stall the whole
+ * device and has no latency bound), a plug-in sandbox with a memory budget fixed at load time, or a process whose
+ * device memory already belongs to another allocator's pool.  b200_frontend_process may cudaMalloc scan scratch
+ * when a larger block arrives; this call runs the same kernels with the scratch in a fixed ~256 KB array inside
+ * the library image (held by every GPU that loads the library until the process exits) and performs no
+ * allocation of any kind.
+ *   d_in, d_out   device cf32[count] on the current device (may alias)
+ *   count         at most B200_DC_NOALLOC_MAX_SAMPLES; larger blocks are refused with B200_ETOOBIG
+ *   rate          DCBlocker rate (IQFrontEnd uses 50 / sampleRate, iq_frontend.h:84-86)
+ *   d_offset      device double[2] {re, im}: the blocker's offset, read before and written after the block, so
+ *                 consecutive calls continue one stream; NULL = start from zero and discard the final offset
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call
+ * before any stream capture begins.  All calls on a device share the one array: calls whose GPU work can
+ * overlap (different streams without ordering, or several host threads) race on it -- serialise them. */
+#define B200_DC_NOALLOC_MAX_SAMPLES (1 << 24)
+int b200_dc_block_noalloc(const float* d_in, float* d_out, int count, double rate, double* d_offset, void* stream);
+
 /* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
 int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
 

@@ -68,6 +68,7 @@ _SIGS = {
     "b200_frontend_frame_index": (C.c_int64, [_vp, _i]),
     "b200_frontend_process_host": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
+    "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
     "b200_waterfall_destroy": (_i, [_vp]),
     "b200_waterfall_set_view": (_i, [_vp, _i, _i]),
@@ -347,6 +348,17 @@ def profile_read():
     ms, n, by = _d(), C.c_longlong(), _d()
     _chk(lib.b200_profile_read(C.byref(ms), C.byref(n), C.byref(by)))
     return ms.value, n.value, by.value
+
+
+DC_NOALLOC_MAX_SAMPLES = 1 << 24
+
+
+def dc_block_noalloc(d_in, d_out, count, rate, d_offset=None, stream=None):
+    """DC blocker through the allocation-free entry point (fixed scratch inside the library, <= 2**24 samples
+    per call).  d_in / d_out: CUDA float32 tensors [count, 2]; d_offset: CUDA float64 tensor [2] carried
+    between calls, or None to start from zero."""
+    _chk(lib.b200_dc_block_noalloc(d_in.data_ptr(), d_out.data_ptr(), int(count), float(rate),
+                                   d_offset.data_ptr() if d_offset is not None else None, _stream_ptr(stream)))
 
 
 def fft_forward(d_in, nz, fft_size, d_out, stream=None):

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 
 #include "fft.cuh"
 #include "vfo_bank.cuh"
@@ -622,3 +623,87 @@ int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------------
+// DC blocker for callers that must not allocate.
+//
+// Some hosts of this library are not allowed to call cudaMalloc once they are running: an audio / DSP
+// callback thread with a hard deadline (cudaMalloc may synchronise the whole device and has no latency
+// bound), a plug-in sandbox that hands each module a fixed memory budget at load time, or a process whose
+// device memory is already owned in full by another allocator's pool.  b200_frontend_process grows its
+// scan scratch with cudaMalloc when a larger block arrives; this entry point runs the same three kernels
+// (dcReduceKernel -> dcScanKernel -> dcApplyKernel) with the scratch in a fixed array that is part of the
+// library image, so it never allocates or frees anything, on the host or on the device.
+//
+// The array is per GPU: every device that loads the library carries its ~256 KB until the process exits.
+// Inside host code the array's name is only a host-side handle, not a device address, so its address is
+// fetched once per device with cudaGetSymbolAddress (return code checked) and cached; that happens on the
+// first call made while that device is current.  Make that first call before starting any stream capture.
+#define B200_DC_NOALLOC_MAX_CHUNKS (B200_DC_NOALLOC_MAX_SAMPLES / 2048)
+static_assert(B200_DC_NOALLOC_MAX_SAMPLES % 2048 == 0, "limit must be a whole number of scan chunks");
+
+namespace {
+struct DcNoAllocScratch {
+    double2 state[2];                                   // [0] offset entering the block, [1] offset leaving it
+    double2 pad[14];                                    // keep the arrays below 256-byte aligned
+    double2 chunkB[B200_DC_NOALLOC_MAX_CHUNKS];         // per-chunk fold, written by dcReduceKernel
+    double2 chunkStart[B200_DC_NOALLOC_MAX_CHUNKS];     // per-chunk entry offset, written by dcScanKernel
+};
+}
+static __device__ __align__(256) unsigned char g_dcNoAllocScratch[sizeof(DcNoAllocScratch)];
+
+static std::mutex g_dcNoAllocMtx;
+static DcNoAllocScratch* g_dcNoAllocPtr[64] = {};
+
+// device address of the scratch on the current device (looked up once per device)
+static int dcNoAllocScratch(DcNoAllocScratch** out) {
+    int dev = -1;
+    B200_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { setError("b200_dc_block_noalloc: unsupported device ordinal %d", dev); return B200_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_dcNoAllocMtx);
+    if (!g_dcNoAllocPtr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_dcNoAllocScratch);
+        if (e != cudaSuccess || !p) {
+            setError("b200_dc_block_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+            return B200_ECUDA;
+        }
+        g_dcNoAllocPtr[dev] = static_cast<DcNoAllocScratch*>(p);
+    }
+    *out = g_dcNoAllocPtr[dev];
+    return B200_OK;
+}
+
+extern "C" int b200_dc_block_noalloc(const float* d_in, float* d_out, int count, double rate, double* d_offset, void* stream) {
+    if (count < 0 || (!d_in && count > 0) || (!d_out && count > 0)) { setError("b200_dc_block_noalloc: bad arguments"); return B200_EINVAL; }
+    if (count > B200_DC_NOALLOC_MAX_SAMPLES) {
+        setError("b200_dc_block_noalloc: block of %d samples exceeds the fixed scratch limit of %d samples; split the block "
+                 "(pass d_offset to carry the state) or use b200_frontend_process", count, B200_DC_NOALLOC_MAX_SAMPLES);
+        return B200_ETOOBIG;
+    }
+    DcNoAllocScratch* sc = nullptr;
+    B200_TRY(dcNoAllocScratch(&sc));
+    if (count == 0) { return B200_OK; }
+    cudaStream_t s = (cudaStream_t)stream;
+    // The array keeps whatever the previous call left in it.  Only state[0] is read before it is written, so
+    // it is the one thing that has to be set: the caller's carried offset, or zero for a fresh blocker.
+    // chunkB / chunkStart entries are always written by this call's own kernels before they are read.
+    if (d_offset) { B200_CUDA(cudaMemcpyAsync(&sc->state[0], d_offset, sizeof(double2), cudaMemcpyDeviceToDevice, s)); }
+    else { B200_CUDA(cudaMemsetAsync(&sc->state[0], 0, sizeof(double2), s)); }
+    DcParams p;
+    p.rate = (float)rate;                                // DCBlocker::_rate is float (dc_blocker.h:74)
+    p.a = 1.0 - (double)p.rate;
+    p.aRun = pow(p.a, (double)kDcPerThread);
+    p.aChunk = pow(p.a, (double)kDcChunk);
+    const int nChunks = (count + kDcChunk - 1) / kDcChunk;
+    const cf32* in = (const cf32*)d_in;
+    dcReduceKernel<<<nChunks, kDcThreads, 0, s>>>(in, count, p, sc->chunkB);
+    B200_CHECK_LAUNCH();
+    dcScanKernel<<<1, 1024, 0, s>>>(sc->chunkB, nChunks, count, p, sc->chunkStart, sc->state);
+    B200_CHECK_LAUNCH();
+    dcApplyKernel<<<nChunks, kDcThreads, 0, s>>>(in, (cf32*)d_out, count, p, sc->chunkStart, 0);
+    B200_CHECK_LAUNCH();
+    countLaunch(3);
+    if (d_offset) { B200_CUDA(cudaMemcpyAsync(d_offset, &sc->state[1], sizeof(double2), cudaMemcpyDeviceToDevice, s)); }
+    return B200_OK;
+}
