@@ -26,6 +26,7 @@
 #ifndef B200DSP_H
 #define B200DSP_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -43,6 +44,14 @@ const char* b200_last_error(void);
 const char* b200_version(void);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 uint64_t b200_launch_count(void);
+
+/* Page-locked host memory for sample buffers (dsp::stream's buffers in include/dsp/stream.h; the reference uses
+ * volk_malloc, dsp/buffer/buffer.h:20-24) and a blocking device->host copy, so that the C++ drop-in headers need no
+ * CUDA headers.  b200_host_alloc falls back to ordinary aligned memory when no CUDA device is present (streams
+ * still work; every process call still fails without a GPU). */
+void* b200_host_alloc(size_t bytes);
+void b200_host_free(void* p);
+int b200_device_to_host(void* h_dst, const void* d_src, size_t bytes, void* stream);
 
 /* Measurement hooks (bench.py's roofline line): when enabled, every launch of the fused
  * xlate+decimate kernel -- the kernel that streams the full-rate input -- is bracketed by CUDA events

@@ -1,0 +1,180 @@
+// IQFrontEnd on the GPU (reference: core/src/signal_path/iq_frontend.{h,cpp}).
+// Same public surface: init(...) with the FFT acquire/release callbacks, the sample-rate / decimation /
+// DC-block / invert / FFT setters, addVFO/removeVFO returning dsp::channel::RxVFO*, bind/unbindIQStream,
+// start/stop.  One worker thread replaces the reference's SampleFrameBuffer + chain + Splitter + Reshaper +
+// Handler + per-VFO threads (iq_frontend.cpp:223-261): it takes a block from the input stream, runs
+// b200_frontend_process_host (pre-processing, every FFT frame of the block, every VFO), hands each dB row to
+// acquireFFTBuffer/releaseFFTBuffer and swaps each VFO's `out` stream.
+#pragma once
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "channel/rx_vfo.h"
+
+class IQFrontEnd {
+public:
+    ~IQFrontEnd() {
+        if (!_init) { return; }
+        stop();
+        for (auto& kv : vfos) { delete kv.second; }
+        b200_frontend_destroy(fe);
+    }
+
+    enum FFTWindow { RECTANGULAR, BLACKMAN, NUTTALL };
+
+    void init(dsp::stream<dsp::complex_t>* in, double sampleRate, bool buffering, int decimRatio, bool dcBlocking, int fftSize,
+              double fftRate, FFTWindow fftWindow, float* (*acquireFFTBuffer)(void* ctx), void (*releaseFFTBuffer)(void* ctx), void* fftCtx) {
+        _in = in; _sampleRate = sampleRate; _decimRatio = decimRatio; _fftSize = fftSize; _fftRate = fftRate; _fftWindow = fftWindow;
+        _acquire = acquireFFTBuffer; _release = releaseFFTBuffer; _ctx = fftCtx;
+        (void)buffering;   // the reference's 32-slot input FIFO only decouples the source thread; not needed here
+        if (b200_frontend_create(&fe, sampleRate, decimRatio, dcBlocking ? 1 : 0, 0, fftSize, fftRate, (int)fftWindow,
+                                 STREAM_BUFFER_SIZE, 0) != B200_OK) { fail("b200_frontend_create"); }
+        bank = b200_frontend_vfo_bank(fe);
+        b200_vfo_bank_set_rotator_mode(bank, B200_ROTATOR_EXACT);
+        resizeRows();
+        _init = true;
+    }
+
+    void setInput(dsp::stream<dsp::complex_t>* in) {
+        const bool was = running;
+        if (was) { stop(); }
+        _in = in;
+        if (was) { start(); }
+    }
+    void setSampleRate(double sampleRate) {
+        std::lock_guard<std::mutex> lk(mtx);
+        _sampleRate = sampleRate;
+        if (b200_frontend_set_sample_rate(fe, sampleRate) != B200_OK) { fail("setSampleRate"); }
+        resizeRows();
+    }
+    double getSampleRate() { return _sampleRate / _decimRatio; }
+    void setBuffering(bool) {}
+    void setDecimation(int ratio) {
+        std::lock_guard<std::mutex> lk(mtx);
+        _decimRatio = ratio;
+        if (b200_frontend_set_decimation(fe, ratio) != B200_OK) { fail("setDecimation"); }
+        resizeRows();
+    }
+    void setInvertIQ(bool enabled) { std::lock_guard<std::mutex> lk(mtx); b200_frontend_set_invert_iq(fe, enabled); }
+    void setDCBlocking(bool enabled) { std::lock_guard<std::mutex> lk(mtx); b200_frontend_set_dc_blocking(fe, enabled); }
+
+    // extra consumers of the pre-processed IQ (recorder, exporters): reference iq_frontend.cpp:151-157
+    void bindIQStream(dsp::stream<dsp::complex_t>* s) { std::lock_guard<std::mutex> lk(mtx); bound.push_back(s); }
+    void unbindIQStream(dsp::stream<dsp::complex_t>* s) {
+        std::lock_guard<std::mutex> lk(mtx);
+        bound.erase(std::remove(bound.begin(), bound.end(), s), bound.end());
+    }
+
+    dsp::channel::RxVFO* addVFO(std::string name, double sampleRate, double bandwidth, double offset) {
+        std::lock_guard<std::mutex> lk(mtx);
+        if (vfos.find(name) != vfos.end()) { fprintf(stderr, "[IQFrontEnd] Tried to add VFO with existing name.\n"); return nullptr; }
+        const int idx = b200_vfo_bank_add(bank, sampleRate, bandwidth, offset);
+        if (idx < 0) { fprintf(stderr, "[IQFrontEnd] addVFO failed: %s\n", b200_last_error()); return nullptr; }
+        auto* v = new dsp::channel::RxVFO();
+        v->attach(bank, idx, &mtx);
+        vfos[name] = v;
+        return v;
+    }
+    void removeVFO(std::string name) {
+        std::lock_guard<std::mutex> lk(mtx);
+        auto it = vfos.find(name);
+        if (it == vfos.end()) { fprintf(stderr, "[IQFrontEnd] Tried to remove a VFO that doesn't exist.\n"); return; }
+        it->second->out.stopWriter();
+        b200_vfo_bank_remove(bank, it->second->index());
+        delete it->second;
+        vfos.erase(it);
+    }
+
+    void setFFTSize(int size) { std::lock_guard<std::mutex> lk(mtx); _fftSize = size; if (b200_frontend_set_fft_size(fe, size) != B200_OK) { fail("setFFTSize"); } resizeRows(); }
+    void setFFTRate(double rate) { std::lock_guard<std::mutex> lk(mtx); _fftRate = rate; if (b200_frontend_set_fft_rate(fe, rate) != B200_OK) { fail("setFFTRate"); } resizeRows(); }
+    double getFFTRate() { return _fftRate; }
+    void setFFTWindow(FFTWindow w) { std::lock_guard<std::mutex> lk(mtx); _fftWindow = w; if (b200_frontend_set_fft_window(fe, (int)w) != B200_OK) { fail("setFFTWindow"); } }
+    void flushInputBuffer() {}
+
+    void start() {
+        if (running || !_in) { return; }
+        running = true;
+        _in->clearReadStop();
+        worker = std::thread([this] { while (step() >= 0) {} });
+    }
+    void stop() {
+        if (!running) { return; }
+        _in->stopReader();
+        for (auto& kv : vfos) { kv.second->out.stopWriter(); }
+        for (auto* s : bound) { s->stopWriter(); }
+        if (worker.joinable()) { worker.join(); }
+        _in->clearReadStop();
+        for (auto& kv : vfos) { kv.second->out.clearWriteStop(); }
+        for (auto* s : bound) { s->clearWriteStop(); }
+        running = false;
+    }
+
+    double getEffectiveSamplerate() { return b200_frontend_effective_samplerate(fe); }
+    b200_frontend* handle() { return fe; }
+
+protected:
+    // one block: the work of SampleFrameBuffer::run .. Splitter::run .. RxVFO::run / IQFrontEnd::handler
+    int step() {
+        const int count = _in->read();
+        if (count < 0) { return -1; }
+        std::vector<dsp::channel::RxVFO*> live;
+        int nFrames = 0, preCount = 0;
+        {
+            std::lock_guard<std::mutex> lk(mtx);
+            float* outs[kMaxVfos] = {};
+            int counts[kMaxVfos] = {};
+            for (auto& kv : vfos) { outs[kv.second->index()] = reinterpret_cast<float*>(kv.second->out.writeBuf); }
+            if (b200_frontend_process_host(fe, reinterpret_cast<const float*>(_in->readBuf), count, rows.data(), maxRows, outs, nullptr, counts,
+                                           nullptr) != B200_OK) { fail("process"); }
+            nFrames = std::min(b200_frontend_frame_count(fe), maxRows);
+            for (auto& kv : vfos) { kv.second->pending = counts[kv.second->index()]; live.push_back(kv.second); }
+            if (!bound.empty()) {
+                const float* dPre = nullptr;
+                b200_frontend_preproc_out(fe, &dPre, &preCount);
+                for (auto* s : bound) { b200_device_to_host(s->writeBuf, dPre, (size_t)preCount * sizeof(dsp::complex_t), nullptr); }
+            }
+        }
+        _in->flush();
+        for (int f = 0; f < nFrames; f++) {
+            float* dst = _acquire ? _acquire(_ctx) : nullptr;
+            if (dst) { memcpy(dst, rows.data() + (size_t)f * _fftSize, (size_t)_fftSize * sizeof(float)); }
+            if (_release) { _release(_ctx); }    // always called, even when acquire returned NULL (iq_frontend.cpp:281-286)
+        }
+        for (auto* v : live) { if (v->pending > 0 && !v->out.swap(v->pending)) { return -1; } }
+        for (auto* s : bound) { if (preCount > 0 && !s->swap(preCount)) { return -1; } }
+        return count;
+    }
+
+    void resizeRows() {
+        const double eff = _sampleRate / _decimRatio;
+        const int interval = std::max(1, (int)(eff / _fftRate + 0.5));
+        maxRows = STREAM_BUFFER_SIZE / interval + 2;
+        rows.assign((size_t)maxRows * _fftSize, 0.0f);
+    }
+
+    [[noreturn]] static void fail(const char* what) {
+        fprintf(stderr, "IQFrontEnd: %s failed: %s\n", what, b200_last_error());
+        abort();
+    }
+
+    static constexpr int kMaxVfos = 4096;
+    b200_frontend* fe = nullptr;
+    b200_vfo_bank* bank = nullptr;
+    dsp::stream<dsp::complex_t>* _in = nullptr;
+    std::map<std::string, dsp::channel::RxVFO*> vfos;
+    std::vector<dsp::stream<dsp::complex_t>*> bound;
+    std::vector<float> rows;
+    int maxRows = 0;
+    double _sampleRate = 0, _fftRate = 0;
+    int _decimRatio = 1, _fftSize = 0;
+    FFTWindow _fftWindow = NUTTALL;
+    float* (*_acquire)(void*) = nullptr;
+    void (*_release)(void*) = nullptr;
+    void* _ctx = nullptr;
+    std::mutex mtx;
+    std::thread worker;
+    bool running = false, _init = false;
+};

@@ -24,6 +24,9 @@ _SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (C.c_char_p, []),
     "b200_launch_count": (C.c_uint64, []),
+    "b200_host_alloc": (_vp, [C.c_size_t]),
+    "b200_host_free": (None, [_vp]),
+    "b200_device_to_host": (_i, [_vp, _vp, C.c_size_t, _vp]),
     "b200_profile_enable": (_i, [_i]),
     "b200_profile_read": (_i, [C.POINTER(_d), C.POINTER(C.c_longlong), C.POINTER(_d)]),
     "b200_vfo_bank_create": (_i, [_pp, _d, _i, _i]),

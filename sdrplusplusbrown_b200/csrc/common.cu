@@ -1,6 +1,9 @@
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <unordered_set>
 
 namespace b200 {
 
@@ -58,7 +61,45 @@ int PinnedRing::release(int slot, cudaStream_t s) {
 
 } // namespace b200
 
+// page-locked allocations are remembered so b200_host_free knows how to release them
+static std::mutex g_hostMtx;
+static std::unordered_set<void*> g_pinned;
+
 extern "C" {
+
+void* b200_host_alloc(size_t bytes) {
+    if (bytes == 0) { bytes = 64; }
+    void* p = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) == cudaSuccess && ndev > 0 && cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess && p) {
+        std::lock_guard<std::mutex> lk(g_hostMtx);
+        g_pinned.insert(p);
+        return p;
+    }
+    cudaGetLastError();   // clear the sticky "no device" error
+    if (posix_memalign(&p, 64, bytes) != 0) { return nullptr; }
+    return p;
+}
+
+void b200_host_free(void* p) {
+    if (!p) { return; }
+    bool pinned = false;
+    {
+        std::lock_guard<std::mutex> lk(g_hostMtx);
+        auto it = g_pinned.find(p);
+        if (it != g_pinned.end()) { g_pinned.erase(it); pinned = true; }
+    }
+    if (pinned) { cudaFreeHost(p); } else { free(p); }
+}
+
+int b200_device_to_host(void* h_dst, const void* d_src, size_t bytes, void* stream) {
+    if (bytes == 0) { return B200_OK; }
+    if (!h_dst || !d_src) { b200::setError("b200_device_to_host: NULL pointer"); return B200_EINVAL; }
+    B200_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    B200_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return B200_OK;
+}
+
 const char* b200_last_error(void) { return b200::t_err; }
 const char* b200_version(void) { return "b200dsp 0.1 (sm_100a)"; }
 uint64_t b200_launch_count(void) { return b200::g_launches.load(); }
