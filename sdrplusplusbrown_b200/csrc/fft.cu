@@ -95,7 +95,7 @@ template <> struct Dft<8> { static __device__ __forceinline__ void run(float2* v
 template <> struct Dft<16> { static __device__ __forceinline__ void run(float2* v) { dftComposite<4, 4>(v); } };
 
 // One Stockham stage of radix R on nb rows of length L (row pitch LP slots) from src to dst.
-// Ns = product of the radices already applied.  tw[m] = exp(-2*pi*i*m/L), m < L.
+// Ns = product of the radices already applied.  tw[m] = exp(-2*pi*i*m/L), m < L (staged in shared memory).
 template <int R, int LOGR>
 __device__ __forceinline__ void stockhamStage(const float2* __restrict__ src, float2* __restrict__ dst, int logL, int logNs, int LP, int nb,
                                               const float2* __restrict__ tw) {
@@ -113,7 +113,7 @@ __device__ __forceinline__ void stockhamStage(const float2* __restrict__ src, fl
         for (int r = 0; r < R; r++) { v[r] = s[slot(j + r * per)]; }
         if (logNs > 0) {
 #pragma unroll
-            for (int r = 1; r < R; r++) { v[r] = cmul(v[r], __ldg(tw + ((k * r) << sh))); }
+            for (int r = 1; r < R; r++) { v[r] = cmul(v[r], tw[(k * r) << sh]); }
         }
         Dft<R>::run(v);
         const int j0 = ((j - k) << LOGR) + k;
@@ -144,6 +144,21 @@ __device__ float2* fftRows(float2* a, float2* b, int logL, unsigned plan, int LP
     return src;
 }
 
+// 8-byte asynchronous global->shared copy; src_size 0 zero-fills without reading
+__device__ __forceinline__ void cpAsync8(float2* smemDst, const float2* gsrc, bool valid) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    const int sz = valid ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cpAsyncWaitAll() {
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+// address of frame sample i (the frame may straddle the carry buffer and the current block)
+__device__ __forceinline__ const float2* frameAddr(const FrameDesc& f, int i) {
+    return (i < f.len0) ? reinterpret_cast<const float2*>(f.src0) + i : reinterpret_cast<const float2*>(f.src1) + (i - f.len0);
+}
+
 __device__ __forceinline__ float2 frameSample(const FrameDesc& f, const float* __restrict__ win, int i, int nz) {
     if (i >= nz) { return make_float2(0.f, 0.f); }
     const float2 x = (i < f.len0) ? __ldg(reinterpret_cast<const float2*>(f.src0) + i)
@@ -168,10 +183,12 @@ __global__ void __launch_bounds__(kThreads) fftSingleKernel(const FrameDesc* __r
     float2* bufA = sm;
     float2* bufB = sm + LP;
     const FrameDesc f = frames[blockIdx.x];
+    float2* sTw = bufB + LP;                     // W_N^m, m < N
+    for (int m = threadIdx.x; m < N; m += kThreads) { sTw[m] = __ldg(tw + m); }
 #pragma unroll 8
     for (int i = threadIdx.x; i < N; i += kThreads) { bufA[slot(i)] = frameSample(f, win, i, nz); }
     __syncthreads();
-    const float2* res = fftRows(bufA, bufB, logN, plan, LP, 1, tw);
+    const float2* res = fftRows(bufA, bufB, logN, plan, LP, 1, sTw);
     const float invN = 1.0f / (float)N;
     for (int k = threadIdx.x; k < N; k += kThreads) {
         const float2 X = res[slot(k)];
@@ -182,7 +199,7 @@ __global__ void __launch_bounds__(kThreads) fftSingleKernel(const FrameDesc* __r
 
 // ---- N = N1 * N2, pass 1: C adjacent columns n2 per CTA, length-N1 transforms over n1 (input stride N2),
 // then the inter-pass twiddle W_N^(n2*k1); result T[k1][n2].
-__global__ void __launch_bounds__(kThreads) fftPass1Kernel(const FrameDesc* __restrict__ frames, const float* __restrict__ win, int nz,
+__global__ void __launch_bounds__(kThreads, 3) fftPass1Kernel(const FrameDesc* __restrict__ frames, const float* __restrict__ win, int nz,
                                                            int logN1, int logN2, int logC, unsigned plan, const float2* __restrict__ twN1,
                                                            const float2* __restrict__ twLo, const float2* __restrict__ twHi, int logS,
                                                            cf32* __restrict__ scratch, int scratchFrames) {
@@ -194,26 +211,60 @@ __global__ void __launch_bounds__(kThreads) fftPass1Kernel(const FrameDesc* __re
     float2* bufA = sm;
     float2* bufB = sm + C * LP;
     const int total = N1 << logC;
-#pragma unroll 8
-    for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-        const int c = idx & (C - 1), n1 = idx >> logC;
-        bufA[c * LP + slot(n1)] = frameSample(f, win, (n1 << logN2) + c0 + c, nz);
+    float2* sTw = bufB + C * LP;                 // W_N1^m, m < N1
+    float2* sLo = sTw + N1;                      // W_N^j, j < S
+    float2* sHi = sLo + (1 << logS);             // W_N^(j*S), j < N/S
+    // all of this thread's samples are put in flight at once (no register staging), then scaled by the window in place
+    constexpr int kBatch = 8;
+    for (int base = 0; base < total; base += kBatch * kThreads) {
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int idx = base + u * kThreads + threadIdx.x;
+            if (idx < total) {
+                const int c = idx & (C - 1), n1 = idx >> logC;
+                const int i = (n1 << logN2) + c0 + c;
+                const bool ok = i < nz;
+                cpAsync8(bufA + c * LP + slot(n1), frameAddr(f, ok ? i : 0), ok);
+            }
+        }
+        float wv[kBatch];
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int idx = base + u * kThreads + threadIdx.x;
+            const int i = ((idx >> logC) << logN2) + c0 + (idx & (C - 1));
+            wv[u] = (idx < total && i < nz && win) ? __ldg(win + i) : 1.0f;
+        }
+        if (base == 0) {
+            for (int m = threadIdx.x; m < N1; m += kThreads) { sTw[m] = __ldg(twN1 + m); }
+            for (int m = threadIdx.x; m < (1 << logS); m += kThreads) { sLo[m] = __ldg(twLo + m); }
+            for (int m = threadIdx.x; m < (1 << (logN1 + logN2 - logS)); m += kThreads) { sHi[m] = __ldg(twHi + m); }
+        }
+        cpAsyncWaitAll();
+#pragma unroll
+        for (int u = 0; u < kBatch; u++) {
+            const int idx = base + u * kThreads + threadIdx.x;
+            if (idx < total) {
+                float2* p = bufA + (idx & (C - 1)) * LP + slot(idx >> logC);
+                const float2 x = *p;
+                *p = make_float2(x.x * wv[u], x.y * wv[u]);
+            }
+        }
     }
     __syncthreads();
-    const float2* res = fftRows(bufA, bufB, logN1, plan, LP, C, twN1);
+    const float2* res = fftRows(bufA, bufB, logN1, plan, LP, C, sTw);
     float2* T = reinterpret_cast<float2*>(scratch) + ((size_t)(blockIdx.y % scratchFrames) << (logN1 + logN2));
     const int maskS = (1 << logS) - 1;
 #pragma unroll 4
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
         const int c = idx & (C - 1), k1 = idx >> logC;
         const int m = (c0 + c) * k1;                     // < N
-        const float2 w = cmul(__ldg(twLo + (m & maskS)), __ldg(twHi + (m >> logS)));
+        const float2 w = cmul(sLo[m & maskS], sHi[m >> logS]);
         T[((size_t)k1 << logN2) + c0 + c] = cmul(res[c * LP + slot(k1)], w);
     }
 }
 
 // pass 2: R adjacent rows k1 per CTA, length-N2 transforms over n2; X[k1 + N1*k2].
-__global__ void __launch_bounds__(kThreads) fftPass2Kernel(int logN1, int logN2, int logR, unsigned plan, const float2* __restrict__ twN2,
+__global__ void __launch_bounds__(kThreads, 3) fftPass2Kernel(int logN1, int logN2, int logR, unsigned plan, const float2* __restrict__ twN2,
                                                            const cf32* __restrict__ scratch, int scratchFrames, int frameBase,
                                                            float* __restrict__ outDb, cf32* __restrict__ outSpec) {
     extern __shared__ __align__(16) float2 sm[];
@@ -225,13 +276,16 @@ __global__ void __launch_bounds__(kThreads) fftPass2Kernel(int logN1, int logN2,
     float2* bufB = sm + R * LP;
     const int total = N2 << logR;
     const float2* T = reinterpret_cast<const float2*>(scratch) + ((size_t)(frame % scratchFrames) << (logN1 + logN2));
-#pragma unroll 8
+    float2* sTw = bufB + R * LP;                 // W_N2^m, m < N2
+    for (int m = threadIdx.x; m < N2; m += kThreads) { sTw[m] = __ldg(twN2 + m); }
+#pragma unroll 16
     for (int idx = threadIdx.x; idx < total; idx += kThreads) {
         const int n2 = idx & (N2 - 1), r = idx >> logN2;
-        bufA[r * LP + slot(n2)] = T[((size_t)(r0 + r) << logN2) + n2];
+        cpAsync8(bufA + r * LP + slot(n2), T + ((size_t)(r0 + r) << logN2) + n2, true);
     }
+    cpAsyncWaitAll();
     __syncthreads();
-    const float2* res = fftRows(bufA, bufB, logN2, plan, LP, R, twN2);
+    const float2* res = fftRows(bufA, bufB, logN2, plan, LP, R, sTw);
     const size_t N = (size_t)1 << (logN1 + logN2);
     const float invN = 1.0f / (float)N;
 #pragma unroll 4
@@ -270,17 +324,18 @@ unsigned radixPlan(int logL) {
 
 int log2i(int v) { int l = 0; while ((1 << l) < v) { l++; } return l; }
 
-size_t rowsSmem(int L, int nb) { return (size_t)2 * nb * (slot(L) + 1) * sizeof(float2); }
+// two ping-pong buffers of nb rows + `extra` twiddle entries
+size_t rowsSmem(int L, int nb, int extra = 0) { return ((size_t)2 * nb * (slot(L) + 1) + extra) * sizeof(float2); }
 
-constexpr size_t kSmemSoft = 72 * 1024;    // 3 CTAs per SM
+constexpr size_t kSmemSoft = 76 * 1024;    // 3 CTAs per SM
 constexpr size_t kSmemHard = 200 * 1024;
 
 // rows (or columns) per CTA: as many as wanted within the soft cap, but never fewer than 8 (32-byte segments)
 // unless even that exceeds the hard cap
-int pickBatchLog(int L, int wantLog) {
+int pickBatchLog(int L, int wantLog, int extra) {
     int lg = wantLog;
-    while (lg > 3 && rowsSmem(L, 1 << lg) > kSmemSoft) { lg--; }
-    while (lg > 0 && rowsSmem(L, 1 << lg) > kSmemHard) { lg--; }
+    while (lg > 3 && rowsSmem(L, 1 << lg, extra) > kSmemSoft) { lg--; }
+    while (lg > 0 && rowsSmem(L, 1 << lg, extra) > kSmemHard) { lg--; }
     return lg;
 }
 
@@ -329,7 +384,7 @@ int FftPlan::ensureScratch(int frames) {
 int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s) {
     if (nFrames <= 0) { return B200_OK; }
     if (N1 == 1) {
-        const size_t smem = rowsSmem(N, 1);
+        const size_t smem = rowsSmem(N, 1, N);
         B200_CUDA(cudaFuncSetAttribute(fftSingleKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         fftSingleKernel<<<nFrames, kThreads, smem, s>>>(dFrames, dWindow, nz, N, logN, radixPlan(logN), dTwN2, outDb, outSpec);
         B200_CHECK_LAUNCH();
@@ -338,9 +393,10 @@ int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, in
     }
     B200_TRY(ensureScratch(nFrames));
     const int logN1 = log2i(N1), logN2 = log2i(N2);
-    const int logC = pickBatchLog(N1, 4);      // up to 16 columns: 128-byte global segments
-    const int logR = pickBatchLog(N2, 5);      // up to 32 rows: 128-byte dB segments
-    const size_t smem1 = rowsSmem(N1, 1 << logC), smem2 = rowsSmem(N2, 1 << logR);
+    const int extra1 = N1 + S + (N >> logS), extra2 = N2;      // twiddle tables staged in shared memory
+    const int logC = pickBatchLog(N1, 4, extra1);      // up to 16 columns: 128-byte global segments
+    const int logR = pickBatchLog(N2, 5, extra2);      // up to 32 rows: 128-byte dB segments
+    const size_t smem1 = rowsSmem(N1, 1 << logC, extra1), smem2 = rowsSmem(N2, 1 << logR, extra2);
     B200_CUDA(cudaFuncSetAttribute(fftPass1Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
     B200_CUDA(cudaFuncSetAttribute(fftPass2Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     const unsigned plan1 = radixPlan(logN1), plan2 = radixPlan(logN2);

@@ -23,6 +23,7 @@
 #include "xlate_decim.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 #include "host_design.h"
 #include "rotator.cuh"
@@ -74,12 +75,18 @@ template <int RATIO> struct FirstStage;
 #undef DECIM_STAGE_3
 #undef DECIM_PLAN_END
 
+constexpr int kMaxGroup = 8;         // VFOs per CTA (the input tile is staged once per group)
 constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
 
 template <int D> struct TileCfg {
-    // sub-blocks (= threads) per CTA: ~4096 samples (32 KB) of input per tile, so that 4-6 CTAs are resident per
-    // SM and one CTA's load phase overlaps its neighbours' arithmetic
-    static constexpr int SB = (4096 / D) > 256 ? 256 : ((4096 / D) < 64 ? 64 : (4096 / D));
+    // sub-blocks per CTA: ~4096 samples (32 KB) of input per tile, so that several CTAs are resident per SM and one
+    // CTA's load phase overlaps its neighbours' arithmetic
+    static constexpr int SB = (4096 / D) > 256 ? 256 : ((4096 / D) < 32 ? 32 : (4096 / D));
+    // threads per sub-block: a sub-block of D samples is split into RS runs of DS = D/RS <= 32 samples, so that the
+    // shared-memory tile (8*D bytes per sub-block) does not cap the resident warps for the large-D plans
+    static constexpr int RS = D > 32 ? D / 32 : 1;
+    static constexpr int DS = D / RS;
+    static constexpr int THREADS = SB * RS;
 };
 
 // 8-byte asynchronous global->shared copy (LDGSTS); src_size 0 zero-fills without touching memory
@@ -103,22 +110,57 @@ __device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
     return cmulf(c0, w);
 }
 
+// One thread's run of DS samples of one sub-block for VB VFOs at once: each input sample is read from shared
+// memory once, rotated once per VFO, and feeds that VFO's Q accumulators.  RUN selects which DS-sample slice
+// of the D-sample sub-block this thread owns (compile time, so every tap is a constant-bank operand).
+template <int RATIO, int RUN, int VB>
+__device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, const float2* __restrict__ ws, float2 (*acc)[8]) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T;
+    constexpr int Q = (T + D - 1) / D;
+    constexpr int DS = TileCfg<D>::DS;
+#pragma unroll
+    for (int r = 0; r < DS; r++) {
+        const float2 x = xrow[r];
+#pragma unroll
+        for (int v = 0; v < VB; v++) {
+            const float2 z = cmulf(x, ws[v * D + r]);
+#pragma unroll
+            for (int q = 0; q < Q; q++) {
+                if (q * D + RUN * DS + r < T) {
+                    const float h = FS::tap(q * D + RUN * DS + r);
+                    acc[v][q].x = fmaf(h, z.x, acc[v][q].x);
+                    acc[v][q].y = fmaf(h, z.y, acc[v][q].y);
+                }
+            }
+        }
+    }
+}
+
 // grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
-template <int RATIO>
-__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D>::SB)
+// VB = VFOs per register pass (only VB = 1 is instantiated, see launchPlan).
+template <int RATIO, int VB>
+__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D>::THREADS)
 fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     using FS = FirstStage<RATIO>;
+    using TC = TileCfg<FS::D>;
     constexpr int D = FS::D, T = FS::T, H = T - 1;
     constexpr int Q = (T + D - 1) / D;
-    constexpr int SB = TileCfg<D>::SB;
+    static_assert(Q <= 8, "accumulator array is sized for Q <= 8");
+    constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
     constexpr int LP = D + 1;               // padded sub-block pitch: lane stride 2(D+1) words -> distinct banks
+    constexpr int PBUF = VB * Q * NT;       // partial sums of one pass
+    constexpr int NPB = (VB == 1) ? 2 : 1;  // VB == 1 double-buffers them (one barrier per VFO instead of two)
     extern __shared__ __align__(16) float2 sm[];
     float2* xs = sm;                        // SB * LP
-    float2* ws = xs + SB * LP;              // D
-    float2* part = ws + D;                  // Q * SB
+    float2* wsAll = xs + SB * LP;           // G * D      : phaseDelta^r of every VFO of the group
+    float2* part = wsAll + G * D;           // NPB * PBUF : partial sums [vfo][q][run][sub-block]
+    float2* pAll = part + NPB * PBUF;       // G * SB     : sub-block start phase of every (VFO, sub-block)
 
     const int tid = threadIdx.x;
+    const int sb = tid % SB;                // sub-block of this thread
+    const int run = tid / SB;               // which DS-sample slice of it (warp-uniform: SB % 32 == 0)
     const int g0 = blockIdx.y * G;
     const FusedJob j0 = jobs[g0];
     const int k0 = blockIdx.x * NB;
@@ -126,55 +168,79 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     const int mStart = j0.offset - H + k0 * D;     // sample index of this tile's first sub-block
     const float2* in = reinterpret_cast<const float2*>(j0.in);
 
-    // ---- stage the input tile once for the whole VFO group (zero outside [0, count))
-    // (all D copies of a thread are in flight at once; no register staging)
+    // ---- stage the input tile once for the whole VFO group (zero outside [0, count));
+    // all copies of a thread are in flight at once, no register staging
 #pragma unroll 8
-    for (int i = tid; i < SB * D; i += SB) {
+    for (int i = tid; i < SB * D; i += NT) {
         const int m = mStart + i;
         const bool ok = (m >= 0 && m < j0.count);
         cpAsync8(xs + i + i / D, in + (ok ? m : 0), ok);
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
+
+    // ---- while the tile is in flight: every VFO's w[r] table and every sub-block's start phase, so that the
+    // per-VFO loop below touches no global memory except its output
+    const int nG = min(G, nJobs - g0);
+    for (int g = 0; g < nG; g++) {
+        const FusedJob& j = jobs[g0 + g];
+        for (int r = tid; r < D; r += NT) { wsAll[g * D + r] = __ldg(j.wtab + r); }
+        if (tid < SB) {
+            const int ms = mStart + tid * D;
+            float2 p = make_float2(0.f, 0.f);
+            if (ms < j.count && ms + D > 0) { p = phaseAtAny(j, ms); }
+            pAll[g * SB + tid] = p;
+        }
+    }
+    // a ragged last pass re-reads the last VFO's table (its results are not stored)
+    for (int g = nG; g < ((nG + VB - 1) / VB) * VB; g++) {
+        for (int r = tid; r < D; r += NT) { wsAll[g * D + r] = make_float2(0.f, 0.f); }
+        if (tid < SB) { pAll[g * SB + tid] = make_float2(0.f, 0.f); }
+    }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    __syncthreads();
 
-    const int ms = mStart + tid * D;
-    const int gEnd = min(g0 + G, nJobs);
-    for (int g = g0; g < gEnd; g++) {
-        const FusedJob j = jobs[g];
-        for (int r = tid; r < D; r += SB) { ws[r] = __ldg(j.wtab + r); }
-        float2 P = make_float2(0.f, 0.f);
-        if (ms < j.count && ms + D > 0) { P = phaseAtAny(j, ms); }
-        __syncthreads();                    // xs (first pass) and ws visible; previous pass's part[] consumed
-
-        float2 acc[Q];
+    const float2* xrow = xs + sb * LP + run * DS;
+    for (int g = 0; g < nG; g += VB) {
+        const float2* ws = wsAll + g * D + run * DS;
+        float2* pbuf = part + ((NPB == 2) ? ((g & 1) * PBUF) : 0);
+        float2 acc[VB][8];
 #pragma unroll
-        for (int q = 0; q < Q; q++) { acc[q] = make_float2(0.f, 0.f); }
-        const float2* xrow = xs + tid * LP;
+        for (int v = 0; v < VB; v++) {
 #pragma unroll
-        for (int r = 0; r < D; r++) {
-            const float2 z = cmulf(xrow[r], ws[r]);
+            for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
+        }
+        switch (run) {
+        case 0: accumulateRun<RATIO, 0, VB>(xrow, ws, acc); break;
+        case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, VB>(xrow, ws, acc); } break;
+        case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, VB>(xrow, ws, acc); } break;
+        default: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB>(xrow, ws, acc); } break;
+        }
 #pragma unroll
-            for (int q = 0; q < Q; q++) {
-                if (q * D + r < T) {
-                    const float h = FS::tap(q * D + r);
-                    acc[q].x = fmaf(h, z.x, acc[q].x);
-                    acc[q].y = fmaf(h, z.y, acc[q].y);
+        for (int v = 0; v < VB; v++) {
+            const float2 P = pAll[(g + v) * SB + sb];
+#pragma unroll
+            for (int q = 0; q < Q; q++) { pbuf[(v * Q + q) * NT + tid] = cmulf(acc[v][q], P); }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int v = 0; v < VB; v++) {
+            if (g + v < nG) {
+                const FusedJob& j = jobs[g0 + g + v];
+                if (tid < NB && k0 + tid < j.nOut) {
+                    float2 y = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int q = 0; q < Q; q++) {
+#pragma unroll
+                        for (int h = 0; h < RS; h++) {
+                            const float2 c = pbuf[(v * Q + q) * NT + h * SB + tid + q];
+                            y.x += c.x; y.y += c.y;
+                        }
+                    }
+                    reinterpret_cast<float2*>(j.out)[k0 + tid] = y;
                 }
             }
         }
-#pragma unroll
-        for (int q = 0; q < Q; q++) { part[q * SB + tid] = cmulf(acc[q], P); }
-        __syncthreads();
-        if (tid < NB && k0 + tid < j.nOut) {
-            float2 y = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int q = 0; q < Q; q++) {
-                const float2 c = part[q * SB + tid + q];
-                y.x += c.x; y.y += c.y;
-            }
-            reinterpret_cast<float2*>(j.out)[k0 + tid] = y;
-        }
-        __syncthreads();                    // part[] and ws free for the next VFO
+        if (NPB == 1) { __syncthreads(); }   // single buffer: everyone must be done reading before the next pass writes
     }
 }
 
@@ -240,39 +306,56 @@ int profDrain() {
     return B200_OK;
 }
 
+template <int RATIO, int VB>
+int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T;
+    constexpr int Q = (T + D - 1) / D;
+    using TC = TileCfg<D>;
+    constexpr int SB = TC::SB;
+    constexpr int NB = SB - (Q - 1);
+    constexpr int NPB = (VB == 1) ? 2 : 1;
+    const int Gp = ((G + VB - 1) / VB) * VB;
+    const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gp * D + (size_t)NPB * VB * Q * TC::THREADS + (size_t)Gp * SB) * sizeof(float2);
+    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int tiles = (nOut + NB - 1) / NB;
+    dim3 grid(tiles, (nJobs + G - 1) / G);
+    size_t slot = 0;
+    if (g_prof.enabled) {
+        if (g_prof.used == g_prof.start.size()) {
+            if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
+            else {
+                cudaEvent_t a, b;
+                B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
+                g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
+            }
+        }
+        slot = g_prof.used++;
+        // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples
+        g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
+        B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
+    }
+    fusedXlateDecimKernel<RATIO, VB><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G);
+    B200_CHECK_LAUNCH(); countLaunch();
+    if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
+    return B200_OK;
+}
+
 template <int RATIO>
 int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
-    constexpr int SB = TileCfg<D>::SB;
-    constexpr int NB = SB - (Q - 1);
-    constexpr size_t smem = ((size_t)SB * (D + 1) + D + (size_t)Q * SB) * sizeof(float2);
+    constexpr int NB = TileCfg<D>::SB - (Q - 1);
     if (nOut > 0) {
-        B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
         const int tiles = (nOut + NB - 1) / NB;
-        int G = 8;
+        int G = std::min(kMaxGroup, nJobs);
         while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
-        dim3 grid(tiles, (nJobs + G - 1) / G);
-        size_t slot = 0;
-        if (g_prof.enabled) {
-            if (g_prof.used == g_prof.start.size()) {
-                if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
-                else {
-                    cudaEvent_t a, b;
-                    B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
-                    g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
-                }
-            }
-            slot = g_prof.used++;
-            // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples
-            g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
-            B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
-        }
-        fusedXlateDecimKernel<RATIO><<<grid, SB, smem, s>>>(dJobs, nJobs, G);
-        B200_CHECK_LAUNCH(); countLaunch();
-        if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
+        // One VFO per register pass.  Register-blocking 2 or 4 VFOs per pass (shared x reads, fewer barriers) was
+        // measured slower on B200: the 4-VFO unrolled body (57 KB at D=64) stalls on instruction fetch (39 % of
+        // stall samples), a rolled 4-VFO body with shared-memory taps reached 0.27 of the FP32 peak against 0.35 here.
+        B200_TRY((launchMain<RATIO, 1>(dJobs, nJobs, nOut, count, G, s)));
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
     B200_CHECK_LAUNCH(); countLaunch();
