@@ -235,6 +235,16 @@ int b200_waterfall_make_palette(const float* colors_rgb, int color_count, uint32
 /* nrows dB rows (device, row stride raw_fft_size) -> zoomed rows (device float[nrows][data_width], may be
  * NULL) and RGBA rows (device uint32[nrows][data_width], may be NULL). */
 int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, float* d_zoom, uint32_t* d_rgba, void* stream);
+/* WaterFall::calculateVFOSignalInfo (waterfall.cpp:688-759): strength and SNR of one VFO (centre offset and bandwidth
+ * in Hz, relative to a display `whole_bandwidth` wide) from each raw dB row: d_out[row] = {strength, snr}.
+ * Returns 1 (and launches nothing) where the reference returns false (empty side bands). */
+int b200_waterfall_vfo_signal(b200_waterfall* wf, const float* d_rows, int nrows, double whole_bandwidth, double center_offset,
+                              double bandwidth, float* d_out, void* stream);
+/* pushFFT's FFT smoothing (waterfall.cpp:1247-1252) and peak hold (:1269-1272) over nrows zoomed rows in frame order.
+ * d_zoom_rows is smoothed in place; d_hold_rows (may be NULL) receives the hold trace after each row.  The running
+ * buffers live in the handle and start at -1000 dB like the reference's. */
+int b200_waterfall_smooth_hold(b200_waterfall* wf, float* d_zoom_rows, int nrows, int smoothing, float alpha, int hold, float hold_speed,
+                               float* d_hold_rows, void* stream);
 /* the start indices / spans the zoom uses (host copies, data_width each) */
 int b200_waterfall_zoom_table(b200_waterfall* wf, int* sid, int* ufactor);
 

@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include "chain.h"
 #include "channel/rx_vfo.h"
 
 class IQFrontEnd {
@@ -27,7 +28,7 @@ public:
 
     void init(dsp::stream<dsp::complex_t>* in, double sampleRate, bool buffering, int decimRatio, bool dcBlocking, int fftSize,
               double fftRate, FFTWindow fftWindow, float* (*acquireFFTBuffer)(void* ctx), void (*releaseFFTBuffer)(void* ctx), void* fftCtx) {
-        _in = in; _sampleRate = sampleRate; _decimRatio = decimRatio; _fftSize = fftSize; _fftRate = fftRate; _fftWindow = fftWindow;
+        _in = in; preproc.init(in); workIn = in; _sampleRate = sampleRate; _decimRatio = decimRatio; _fftSize = fftSize; _fftRate = fftRate; _fftWindow = fftWindow;
         _acquire = acquireFFTBuffer; _release = releaseFFTBuffer; _ctx = fftCtx;
         (void)buffering;   // the reference's 32-slot input FIFO only decouples the source thread; not needed here
         if (b200_frontend_create(&fe, sampleRate, decimRatio, dcBlocking ? 1 : 0, 0, fftSize, fftRate, (int)fftWindow,
@@ -42,7 +43,23 @@ public:
         const bool was = running;
         if (was) { stop(); }
         _in = in;
+        preproc.setInput(in, [this](dsp::stream<dsp::complex_t>* out) { workIn = out; });
+        if (!userBlocks) { workIn = in; }
         if (was) { start(); }
+    }
+
+    // Plug-in pre-processors (reference: iq_frontend.cpp:327-342, e.g. the logmmse noise reduction module).  They are
+    // host blocks, so they run on their own threads in a dsp::chain in FRONT of the GPU stage; the built-in
+    // decimator / DC blocker / conjugate run on the GPU after them (the reference orders plug-ins after its
+    // built-in blocks -- the difference only matters for a plug-in that does not commute with those three).
+    void addPreprocessor(dsp::Processor<dsp::complex_t, dsp::complex_t>* processor, bool enabled) {
+        pauseFor([&] { preproc.addBlock(processor, false); userBlocks++; if (enabled) { preproc.enableBlock(processor, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); } });
+    }
+    void removePreprocessor(dsp::Processor<dsp::complex_t, dsp::complex_t>* processor) {
+        pauseFor([&] { preproc.removeBlock(processor, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); userBlocks--; });
+    }
+    void togglePreprocessor(dsp::Processor<dsp::complex_t, dsp::complex_t>* processor, bool enabled) {
+        pauseFor([&] { preproc.setBlockEnabled(processor, enabled, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); });
     }
     void setSampleRate(double sampleRate) {
         std::lock_guard<std::mutex> lk(mtx);
@@ -97,16 +114,18 @@ public:
     void start() {
         if (running || !_in) { return; }
         running = true;
-        _in->clearReadStop();
+        workIn->clearReadStop();
+        preproc.start();
         worker = std::thread([this] { while (step() >= 0) {} });
     }
     void stop() {
         if (!running) { return; }
-        _in->stopReader();
+        workIn->stopReader();
         for (auto& kv : vfos) { kv.second->out.stopWriter(); }
         for (auto* s : bound) { s->stopWriter(); }
         if (worker.joinable()) { worker.join(); }
-        _in->clearReadStop();
+        preproc.stop();
+        workIn->clearReadStop();
         for (auto& kv : vfos) { kv.second->out.clearWriteStop(); }
         for (auto* s : bound) { s->clearWriteStop(); }
         running = false;
@@ -118,7 +137,8 @@ public:
 protected:
     // one block: the work of SampleFrameBuffer::run .. Splitter::run .. RxVFO::run / IQFrontEnd::handler
     int step() {
-        const int count = _in->read();
+        dsp::stream<dsp::complex_t>* in = workIn;
+        const int count = in->read();
         if (count < 0) { return -1; }
         std::vector<dsp::channel::RxVFO*> live;
         int nFrames = 0, preCount = 0;
@@ -127,7 +147,7 @@ protected:
             float* outs[kMaxVfos] = {};
             int counts[kMaxVfos] = {};
             for (auto& kv : vfos) { outs[kv.second->index()] = reinterpret_cast<float*>(kv.second->out.writeBuf); }
-            if (b200_frontend_process_host(fe, reinterpret_cast<const float*>(_in->readBuf), count, rows.data(), maxRows, outs, nullptr, counts,
+            if (b200_frontend_process_host(fe, reinterpret_cast<const float*>(in->readBuf), count, rows.data(), maxRows, outs, nullptr, counts,
                                            nullptr) != B200_OK) { fail("process"); }
             nFrames = std::min(b200_frontend_frame_count(fe), maxRows);
             for (auto& kv : vfos) { kv.second->pending = counts[kv.second->index()]; live.push_back(kv.second); }
@@ -137,7 +157,7 @@ protected:
                 for (auto* s : bound) { b200_device_to_host(s->writeBuf, dPre, (size_t)preCount * sizeof(dsp::complex_t), nullptr); }
             }
         }
-        _in->flush();
+        in->flush();
         for (int f = 0; f < nFrames; f++) {
             float* dst = _acquire ? _acquire(_ctx) : nullptr;
             if (dst) { memcpy(dst, rows.data() + (size_t)f * _fftSize, (size_t)_fftSize * sizeof(float)); }
@@ -146,6 +166,14 @@ protected:
         for (auto* v : live) { if (v->pending > 0 && !v->out.swap(v->pending)) { return -1; } }
         for (auto* s : bound) { if (preCount > 0 && !s->swap(preCount)) { return -1; } }
         return count;
+    }
+
+    template <typename F>
+    void pauseFor(F change) {
+        const bool was = running;
+        if (was) { stop(); }
+        change();
+        if (was) { start(); }
     }
 
     void resizeRows() {
@@ -164,6 +192,9 @@ protected:
     b200_frontend* fe = nullptr;
     b200_vfo_bank* bank = nullptr;
     dsp::stream<dsp::complex_t>* _in = nullptr;
+    dsp::stream<dsp::complex_t>* workIn = nullptr;      // what the worker reads: _in, or the tail of the plug-in chain
+    dsp::chain<dsp::complex_t> preproc;
+    int userBlocks = 0;
     std::map<std::string, dsp::channel::RxVFO*> vfos;
     std::vector<dsp::stream<dsp::complex_t>*> bound;
     std::vector<float> rows;

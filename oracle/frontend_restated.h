@@ -133,4 +133,56 @@ inline void makePalette(const float* colors, int colorCount, uint32_t* lut) {
     }
 }
 
+// WaterFall::rawFFTIndex — gui/widgets/waterfall.cpp:761-763
+inline int rawFFTIndex(double frequency, double wholeBandwidth, int rawFFTSize) {
+    return std::clamp<int>((int)(((frequency / (wholeBandwidth / 2.0)) * (double)(rawFFTSize / 2)) + (rawFFTSize / 2)), 0, rawFFTSize);
+}
+
+// WaterFall::calculateVFOSignalInfo — gui/widgets/waterfall.cpp:688-759.  strength / snr of one VFO from one raw dB
+// row: the peak inside the VFO band against the mean of the two side bands (each one bandwidth wide), corrected by how
+// far that mean sits above the quietest quarter of the side-band bins.  Returns false where the reference does.
+inline bool vfoSignalInfo(const float* fftLine, int rawFFTSize, double wholeBandwidth, double centerOffset, double bandwidth,
+                          float* strength, float* snr) {
+    const int minSide = rawFFTIndex(centerOffset - bandwidth, wholeBandwidth, rawFFTSize);
+    const int minOff = rawFFTIndex(centerOffset - bandwidth / 2.0, wholeBandwidth, rawFFTSize);
+    const int maxOff = rawFFTIndex(centerOffset + bandwidth / 2.0, wholeBandwidth, rawFFTSize);
+    const int maxSide = rawFFTIndex(centerOffset + bandwidth, wholeBandwidth, rawFFTSize);
+    double avg = 0, qavg = 0;
+    std::vector<float> side;
+    for (int i = minSide; i < minOff; i++) { side.push_back(fftLine[i]); avg += fftLine[i]; }
+    for (int i = maxOff + 1; i < maxSide; i++) { side.push_back(fftLine[i]); avg += fftLine[i]; }
+    if (side.empty()) { return false; }
+    const size_t avgCount = side.size();
+    std::sort(side.begin(), side.end());
+    const size_t lower = side.size() / 4;
+    if (lower == 0) { return false; }
+    const float kth = side[lower];
+    for (size_t i = 0; i < side.size(); i++) { if (side[i] <= kth) { qavg += side[i]; } }   // ties above the quartile are included, as in the reference
+    qavg /= (double)lower;
+    avg /= (double)avgCount;
+    const double avgdiff = avg - qavg;
+    float mx = -INFINITY;
+    for (int i = minOff; i <= maxOff && i < rawFFTSize; i++) { if (fftLine[i] > mx) { mx = fftLine[i]; } }
+    *strength = (float)(mx - avgdiff);
+    *snr = (float)(mx - avg - avgdiff);
+    return true;
+}
+
+// pushFFT smoothing and peak hold — gui/widgets/waterfall.cpp:1247-1252,1269-1272 (buffers start at -1000, :1073,1090).
+// One zoomed row in, smoothed row out (in place), state carried in smoothingBuf / hold.
+inline void smoothAndHold(float* latest, float* smoothingBuf, float* hold, int width, bool smoothing, float alpha, bool doHold, float holdSpeed) {
+    if (smoothing) {
+        const float beta = 1.0f - alpha;
+        for (int i = 0; i < width; i++) {
+            const float a = latest[i] * alpha;
+            const float b = smoothingBuf[i] * beta;
+            smoothingBuf[i] = a + b;
+            latest[i] = smoothingBuf[i];
+        }
+    }
+    if (doHold) {
+        for (int i = 1; i < width; i++) { hold[i] = std::max<float>(latest[i], hold[i] - holdSpeed); }
+    }
+}
+
 } // namespace orc_restated

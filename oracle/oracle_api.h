@@ -74,6 +74,10 @@ void orc_zoom_indices(int offset, int width, int inSize, int outSize, int* sId, 
 void orc_palette_indices(const float* row, int n, float wfMin, float wfMax, int* idx);          // :1229-1235 (index into the 1000-entry LUT)
 void orc_make_palette(const float* colors /*[n][3]*/, int colorCount, unsigned int* lut /*[1000]*/); // updatePallette :1282-1295
 
+int orc_vfo_signal_info(const float* row, int rawFFTSize, double wholeBandwidth, double centerOffset, double bandwidth,
+                         float* strength, float* snr);                                                    // :688-759, returns 1 when computed
+void orc_smooth_hold(float* latest, float* smoothingBuf, float* hold, int width, int smoothing, float alpha, int doHold, float holdSpeed); // :1247-1272
+
 // ---- demodulators (stereo_t output, as the radio module instantiates them)
 void* orc_fm_create(double samplerate, double bandwidth, int lowPass, int highPass); // demod/fm.h
 void orc_fm_destroy(void* h);

@@ -615,6 +615,12 @@ void orc_fft_frame(const float* iq, const float* window, int nz, int N, float* o
 void orc_do_zoom(int offset, int width, int inSize, int outSize, const float* in, float* out) { orc_restated::doZoom(offset, width, inSize, outSize, in, out); }
 void orc_zoom_indices(int offset, int width, int inSize, int outSize, int* sId, int* uFactor) { orc_restated::zoomIndices(offset, width, inSize, outSize, sId, uFactor); }
 void orc_palette_indices(const float* row, int n, float wfMin, float wfMax, int* idx) { orc_restated::paletteIndices(row, n, wfMin, wfMax, idx); }
+int orc_vfo_signal_info(const float* row, int rawFFTSize, double wholeBandwidth, double centerOffset, double bandwidth, float* strength, float* snr) {
+    return orc_restated::vfoSignalInfo(row, rawFFTSize, wholeBandwidth, centerOffset, bandwidth, strength, snr) ? 1 : 0;
+}
+void orc_smooth_hold(float* latest, float* smoothingBuf, float* hold, int width, int smoothing, float alpha, int doHold, float holdSpeed) {
+    orc_restated::smoothAndHold(latest, smoothingBuf, hold, width, smoothing != 0, alpha, doHold != 0, holdSpeed);
+}
 void orc_make_palette(const float* colors, int colorCount, unsigned int* lut) { orc_restated::makePalette(colors, colorCount, lut); }
 
 void* orc_fm_create(double sr, double bw, int lp, int hp) { auto* d = new FmDemod; d->init(sr, bw, lp != 0, hp != 0); return d; }

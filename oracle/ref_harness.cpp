@@ -216,6 +216,12 @@ void orc_zoom_indices(int offset, int width, int inSize, int outSize, int* sId, 
 void orc_palette_indices(const float* row, int n, float wfMin, float wfMax, int* idx) {
     orc_restated::paletteIndices(row, n, wfMin, wfMax, idx);
 }
+int orc_vfo_signal_info(const float* row, int rawFFTSize, double wholeBandwidth, double centerOffset, double bandwidth, float* strength, float* snr) {
+    return orc_restated::vfoSignalInfo(row, rawFFTSize, wholeBandwidth, centerOffset, bandwidth, strength, snr) ? 1 : 0;
+}
+void orc_smooth_hold(float* latest, float* smoothingBuf, float* hold, int width, int smoothing, float alpha, int doHold, float holdSpeed) {
+    orc_restated::smoothAndHold(latest, smoothingBuf, hold, width, smoothing != 0, alpha, doHold != 0, holdSpeed);
+}
 void orc_make_palette(const float* colors, int colorCount, unsigned int* lut) {
     orc_restated::makePalette(colors, colorCount, lut);
 }

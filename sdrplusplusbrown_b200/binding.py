@@ -80,6 +80,8 @@ _SIGS = {
     "b200_waterfall_make_palette": (_i, [_vp, _i, _vp]),
     "b200_waterfall_push": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "b200_waterfall_zoom_table": (_i, [_vp, _vp, _vp]),
+    "b200_waterfall_vfo_signal": (_i, [_vp, _vp, _i, _d, _d, _d, _vp, _vp]),
+    "b200_waterfall_smooth_hold": (_i, [_vp, _vp, _i, _i, _f, _i, _f, _vp, _vp]),
 }
 
 EXPORTS = sorted(_SIGS.keys())
@@ -334,6 +336,13 @@ class Waterfall:
 
     def push(self, d_rows_ptr, nrows, d_zoom_ptr, d_rgba_ptr, stream=None):
         _chk(lib.b200_waterfall_push(self.h, d_rows_ptr, int(nrows), d_zoom_ptr, d_rgba_ptr, _stream_ptr(stream)))
+
+    def vfo_signal(self, d_rows_ptr, nrows, whole_bw, center, bw, d_out_ptr, stream=None):
+        """returns False where the reference's calculateVFOSignalInfo returns false"""
+        return _chk(lib.b200_waterfall_vfo_signal(self.h, d_rows_ptr, int(nrows), float(whole_bw), float(center), float(bw), d_out_ptr, _stream_ptr(stream))) == 0
+
+    def smooth_hold(self, d_zoom_ptr, nrows, smoothing, alpha, hold, hold_speed, d_hold_ptr=None, stream=None):
+        _chk(lib.b200_waterfall_smooth_hold(self.h, d_zoom_ptr, int(nrows), int(smoothing), float(alpha), int(hold), float(hold_speed), d_hold_ptr, _stream_ptr(stream)))
 
     def zoom_table(self):
         s = np.zeros(self.w, np.int32)

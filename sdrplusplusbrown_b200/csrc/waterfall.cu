@@ -26,6 +26,80 @@ __global__ void __launch_bounds__(256) zoomPaletteKernel(const float* __restrict
     }
 }
 
+// WaterFall::calculateVFOSignalInfo (waterfall.cpp:688-759), one CTA per dB row.  The side-band bins (one bandwidth on
+// each side of the VFO) are staged in shared memory; their mean, the mean of the bins at or below the lower-quartile
+// order statistic (found by rank counting, no sort needed) and the in-band peak give strength and SNR.
+__global__ void __launch_bounds__(256) vfoSignalKernel(const float* __restrict__ rows, int rawSize, int minSide, int minOff, int maxOff, int maxSide,
+                                                       float* __restrict__ out) {
+    extern __shared__ float side[];
+    __shared__ double red[256];
+    __shared__ float sKth;
+    const float* row = rows + (size_t)blockIdx.x * rawSize;
+    const int nL = minOff - minSide, nR = max(0, maxSide - (maxOff + 1));
+    const int n = nL + nR;
+    const int tid = threadIdx.x;
+    double acc = 0.0;
+    for (int i = tid; i < n; i += 256) {
+        const float v = (i < nL) ? __ldg(row + minSide + i) : __ldg(row + maxOff + 1 + (i - nL));
+        side[i] = v;
+        acc += v;
+    }
+    red[tid] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (tid < o) { red[tid] += red[tid + o]; } __syncthreads(); }
+    const double avg = red[0] / (double)n;
+    __syncthreads();
+    const int lower = n / 4;
+    for (int i = tid; i < n; i += 256) {
+        const float v = side[i];
+        int rank = 0;
+        for (int j = 0; j < n; j++) { const float u = side[j]; rank += (u < v || (u == v && j < i)) ? 1 : 0; }
+        if (rank == lower) { sKth = v; }
+    }
+    __syncthreads();
+    const float kth = sKth;
+    acc = 0.0;
+    for (int i = tid; i < n; i += 256) { if (side[i] <= kth) { acc += side[i]; } }
+    red[tid] = acc;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (tid < o) { red[tid] += red[tid + o]; } __syncthreads(); }
+    const double qavg = red[0] / (double)lower;
+    __syncthreads();
+    float mx = -INFINITY;
+    for (int i = minOff + tid; i <= maxOff && i < rawSize; i += 256) { mx = fmaxf(mx, __ldg(row + i)); }
+    red[tid] = mx;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (tid < o) { red[tid] = fmax(red[tid], red[tid + o]); } __syncthreads(); }
+    if (tid == 0) {
+        const double avgdiff = avg - qavg;
+        const float peak = (float)red[0];
+        out[2 * blockIdx.x] = (float)((double)peak - avgdiff);
+        out[2 * blockIdx.x + 1] = (float)((double)peak - avg - avgdiff);
+    }
+}
+
+// pushFFT smoothing (waterfall.cpp:1247-1252) and peak hold (:1269-1272): recurrences over successive rows, so one
+// thread owns one pixel column and walks the rows of the call in order; state persists in the handle.
+__global__ void __launch_bounds__(256) smoothHoldKernel(float* __restrict__ rows, int nrows, int width, float* __restrict__ smoothBuf,
+                                                        float* __restrict__ holdBuf, int smoothing, float alpha, int doHold, float holdSpeed,
+                                                        float* __restrict__ holdOut) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= width) { return; }
+    float s = smoothBuf[i], h = holdBuf[i];
+    const float beta = 1.0f - alpha;
+    for (int r = 0; r < nrows; r++) {
+        float v = rows[(size_t)r * width + i];
+        if (smoothing) {
+            s = __fadd_rn(__fmul_rn(v, alpha), __fmul_rn(s, beta));
+            v = s;
+            rows[(size_t)r * width + i] = v;
+        }
+        if (doHold && i >= 1) { h = fmaxf(v, __fsub_rn(h, holdSpeed)); }
+        if (holdOut) { holdOut[(size_t)r * width + i] = h; }
+    }
+    smoothBuf[i] = s; holdBuf[i] = h;
+}
+
 } // namespace
 } // namespace b200
 
@@ -37,6 +111,7 @@ struct b200_waterfall {
     float wfMin = -70.0f, wfMax = 0.0f;     // WaterFall::WaterFall defaults (waterfall.cpp:159-166)
     std::vector<int> sid, uf;
     int* dSid = nullptr; int* dUf = nullptr; uint32_t* dLut = nullptr;
+    float* dSmooth = nullptr; float* dHold = nullptr;     // smoothingBuf / latestFFTHold, both start at -1000 (waterfall.cpp:1073,1090)
     bool tableDirty = true;
 };
 
@@ -55,10 +130,16 @@ int b200_waterfall_create(b200_waterfall** out, int raw_fft_size, int data_width
     for (int i = 0; i < 1000; i++) { const uint32_t v = (uint32_t)(i * 255 / 999); grey[i] = 0xFF000000u | (v << 16) | (v << 8) | v; }
     if (cudaMalloc((void**)&w->dSid, data_width * sizeof(int)) != cudaSuccess || cudaMalloc((void**)&w->dUf, data_width * sizeof(int)) != cudaSuccess ||
         cudaMalloc((void**)&w->dLut, 1000 * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMalloc((void**)&w->dSmooth, data_width * sizeof(float)) != cudaSuccess || cudaMalloc((void**)&w->dHold, data_width * sizeof(float)) != cudaSuccess ||
         cudaMemcpy(w->dLut, grey.data(), 1000 * sizeof(uint32_t), cudaMemcpyHostToDevice) != cudaSuccess) {
         setError("device allocation failed in b200_waterfall_create");
         delete w;
         return B200_ENOMEM;
+    }
+    {
+        std::vector<float> init((size_t)data_width, -1000.0f);
+        cudaMemcpy(w->dSmooth, init.data(), init.size() * sizeof(float), cudaMemcpyHostToDevice);
+        cudaMemcpy(w->dHold, init.data(), init.size() * sizeof(float), cudaMemcpyHostToDevice);
     }
     *out = w;
     return B200_OK;
@@ -67,7 +148,7 @@ int b200_waterfall_create(b200_waterfall** out, int raw_fft_size, int data_width
 int b200_waterfall_destroy(b200_waterfall* wf) {
     if (!wf) { setError("NULL waterfall handle"); return B200_EINVAL; }
     DeviceGuard g(wf->device);
-    cudaFree(wf->dSid); cudaFree(wf->dUf); cudaFree(wf->dLut);
+    cudaFree(wf->dSid); cudaFree(wf->dUf); cudaFree(wf->dLut); cudaFree(wf->dSmooth); cudaFree(wf->dHold);
     delete wf;
     return B200_OK;
 }
@@ -143,6 +224,41 @@ int b200_waterfall_zoom_table(b200_waterfall* wf, int* sid, int* ufactor) {
     B200_TRY(refreshTable(wf));
     memcpy(sid, wf->sid.data(), wf->width * sizeof(int));
     memcpy(ufactor, wf->uf.data(), wf->width * sizeof(int));
+    return B200_OK;
+}
+
+// WaterFall::rawFFTIndex (waterfall.cpp:761-763)
+static int rawFftIndex(double f, double wholeBw, int n) {
+    const int v = (int)(((f / (wholeBw / 2.0)) * (double)(n / 2)) + (n / 2));
+    return std::min(std::max(v, 0), n);
+}
+
+int b200_waterfall_vfo_signal(b200_waterfall* wf, const float* d_rows, int nrows, double whole_bandwidth, double center_offset, double bandwidth,
+                              float* d_out, void* stream) {
+    if (!wf || !d_rows || !d_out || nrows < 0 || whole_bandwidth <= 0 || bandwidth <= 0) { setError("bad arguments to b200_waterfall_vfo_signal"); return B200_EINVAL; }
+    const int n = wf->rawSize;
+    const int minSide = rawFftIndex(center_offset - bandwidth, whole_bandwidth, n), minOff = rawFftIndex(center_offset - bandwidth / 2.0, whole_bandwidth, n);
+    const int maxOff = rawFftIndex(center_offset + bandwidth / 2.0, whole_bandwidth, n), maxSide = rawFftIndex(center_offset + bandwidth, whole_bandwidth, n);
+    const int side = std::max(0, minOff - minSide) + std::max(0, maxSide - (maxOff + 1));
+    if (side <= 0 || side / 4 <= 0) { return 1; }          // the reference returns false: nothing to measure against
+    if (side > 10000) { setError("VFO side bands span %d bins; at most 10000 are supported", side); return B200_ETOOBIG; }
+    if (nrows == 0) { return B200_OK; }
+    DeviceGuard g(wf->device);
+    vfoSignalKernel<<<nrows, 256, (size_t)side * sizeof(float), (cudaStream_t)stream>>>(d_rows, n, minSide, minOff, maxOff, maxSide, d_out);
+    B200_CHECK_LAUNCH();
+    countLaunch();
+    return B200_OK;
+}
+
+int b200_waterfall_smooth_hold(b200_waterfall* wf, float* d_zoom_rows, int nrows, int smoothing, float alpha, int hold, float hold_speed,
+                               float* d_hold_rows, void* stream) {
+    if (!wf || !d_zoom_rows || nrows < 0) { setError("bad arguments to b200_waterfall_smooth_hold"); return B200_EINVAL; }
+    if (nrows == 0 || (!smoothing && !hold)) { return B200_OK; }
+    DeviceGuard g(wf->device);
+    smoothHoldKernel<<<(wf->width + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_zoom_rows, nrows, wf->width, wf->dSmooth, wf->dHold, smoothing, alpha, hold,
+                                                                              hold_speed, d_hold_rows);
+    B200_CHECK_LAUNCH();
+    countLaunch();
     return B200_OK;
 }
 

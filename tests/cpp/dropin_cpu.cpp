@@ -4,7 +4,7 @@
 #include <cstdio>
 #include <numeric>
 
-#include <dsp/processor.h>
+#include <dsp/chain.h>
 
 #define CHECK(c) do { if (!(c)) { fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); return 1; } } while (0)
 
@@ -75,6 +75,36 @@ int main() {
         }
         d.stop();
         d.stop();
+    }
+    // 4. chain: blocks can be enabled / disabled while running; `out` always names the stream to read
+    {
+        dsp::stream<float> in;
+        Doubler a, b;
+        a.init(nullptr); b.init(nullptr);
+        dsp::chain<float> ch(&in);
+        dsp::stream<float>* tail = ch.out;
+        auto onOut = [&](dsp::stream<float>* o) { tail = o; };
+        CHECK(ch.out == &in);
+        ch.addBlock(&a, false);
+        ch.addBlock(&b, false);
+        ch.start();
+        auto pump = [&](float expectGain) {
+            in.writeBuf[0] = 3.0f;
+            if (!in.swap(1)) { return false; }
+            if (tail->read() != 1) { return false; }
+            const bool ok = tail->readBuf[0] == 3.0f * expectGain;
+            tail->flush();
+            return ok;
+        };
+        CHECK(pump(1.0f));                                  // nothing enabled: output is the input stream itself
+        ch.enableBlock(&b, onOut);   CHECK(tail == &b.out); CHECK(pump(2.0f));
+        ch.enableBlock(&a, onOut);   CHECK(tail == &b.out); CHECK(pump(4.0f));   // a is linked in front of b
+        ch.disableBlock(&b, onOut);  CHECK(tail == &a.out); CHECK(pump(2.0f));
+        ch.setBlockEnabled(&a, false, onOut); CHECK(tail == &in); CHECK(pump(1.0f));
+        bool threw = false;
+        try { ch.addBlock(&a, false); } catch (const std::runtime_error&) { threw = true; }
+        CHECK(threw);                                       // misuse raises std::runtime_error like the reference (chain.h:35)
+        ch.stop();
     }
     printf("dropin_cpu ok\n");
     return 0;

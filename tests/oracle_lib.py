@@ -54,6 +54,8 @@ _SIGS = {
     "orc_zoom_indices": (None, [_i, _i, _i, _i, _vp, _vp]),
     "orc_palette_indices": (None, [_vp, _i, _f, _f, _vp]),
     "orc_make_palette": (None, [_vp, _i, _vp]),
+    "orc_vfo_signal_info": (_i, [_vp, _i, _d, _d, _d, _vp, _vp]),
+    "orc_smooth_hold": (None, [_vp, _vp, _vp, _i, _i, _f, _i, _f]),
     "orc_fm_create": (_vp, [_d, _d, _i, _i]),
     "orc_fm_destroy": (None, [_vp]),
     "orc_fm_process": (_i, [_vp, _i, _vp, _vp]),
@@ -154,6 +156,16 @@ class Oracle:
         lut = np.zeros(1000, np.uint32)
         self.lib.orc_make_palette(colors.ctypes.data, colors.shape[0], lut.ctypes.data)
         return lut
+
+    def vfo_signal_info(self, row, whole_bw, center, bw):
+        row = np.ascontiguousarray(row, np.float32)
+        st, sn = C.c_float(), C.c_float()
+        ok = self.lib.orc_vfo_signal_info(row.ctypes.data, len(row), whole_bw, center, bw, C.addressof(st), C.addressof(sn))
+        return (st.value, sn.value) if ok else None
+
+    def smooth_hold(self, latest, smoothing_buf, hold, smoothing, alpha, do_hold, hold_speed):
+        """in place on the three float32 arrays"""
+        self.lib.orc_smooth_hold(latest.ctypes.data, smoothing_buf.ctypes.data, hold.ctypes.data, len(latest), int(smoothing), alpha, int(do_hold), hold_speed)
 
     def decim_plan(self, ratio):
         d = np.zeros(8, np.int32)

@@ -199,3 +199,43 @@ def test_frontend_feeds_vfos_and_fft_together():
             assert np.max(np.abs(row[strong] - refrow[strong])) <= 0.01
             nframes += 1
     assert nframes == 2
+
+
+def test_vfo_signal_info_smoothing_and_hold_match_oracle():
+    """calculateVFOSignalInfo (strength / SNR), FFT smoothing and peak hold of WaterFall::pushFFT."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    sr, N, W = 2.4e6, 8192, 1000
+    x = synth.make_iq(0, 8192 * 6, sr, tones=[(100e3 + 1e3, 0.05), (-400e3, 0.2)])
+    fe = _fe(sr, fft_size=N, fft_rate=sr / 8192.0, fft_window=2, max_block=len(x))
+    fe.process(to_dev(x))
+    rows = fe.frames()
+    assert len(rows) == 6
+    wf = binding.Waterfall(N, W)
+    wf.set_view(0, N)
+    d_sig = torch.empty((6, 2), dtype=torch.float32, device="cuda")
+    for center, bw in [(100e3, 12.5e3), (-400e3, 50e3), (900e3, 200e3)]:
+        assert wf.vfo_signal(fe.frame_ptr(0), 6, sr, center, bw, d_sig.data_ptr())
+        got = d_sig.cpu().numpy()
+        for f in range(6):
+            ref = PORT.vfo_signal_info(rows[f], sr, center, bw)
+            assert ref is not None
+            assert abs(got[f, 0] - ref[0]) <= 1e-3 and abs(got[f, 1] - ref[1]) <= 1e-3
+    assert not wf.vfo_signal(fe.frame_ptr(0), 6, sr, 100e3, 100.0, d_sig.data_ptr())     # band narrower than a bin: the reference returns false
+    assert PORT.vfo_signal_info(rows[0], sr, 100e3, 100.0) is None
+    # zoom -> smoothing + hold across the six rows, state carried inside the handle across two calls
+    d_zoom = torch.empty((6, W), dtype=torch.float32, device="cuda")
+    d_hold = torch.empty((6, W), dtype=torch.float32, device="cuda")
+    wf.push(fe.frame_ptr(0), 6, d_zoom.data_ptr(), None)
+    zoomed = d_zoom.cpu().numpy().copy()
+    wf.smooth_hold(d_zoom.data_ptr(), 4, True, 0.3, True, 0.5, d_hold.data_ptr())
+    wf.smooth_hold(d_zoom[4:].data_ptr(), 2, True, 0.3, True, 0.5, d_hold[4:].data_ptr())
+    sm, hd = d_zoom.cpu().numpy(), d_hold.cpu().numpy()
+    sbuf = np.full(W, -1000.0, np.float32)
+    hbuf = np.full(W, -1000.0, np.float32)
+    for f in range(6):
+        latest = zoomed[f].copy()
+        PORT.smooth_hold(latest, sbuf, hbuf, True, 0.3, True, 0.5)
+        assert np.max(np.abs(sm[f] - latest)) <= 1e-3
+        assert np.max(np.abs(hd[f][1:] - hbuf[1:])) <= 1e-3
+        assert hd[f][0] == -1000.0        # pixel 0 is never updated by the reference's hold loop

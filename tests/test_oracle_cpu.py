@@ -197,3 +197,22 @@ def test_oracles_match_golden(fname):
             a, b = np.asarray(got[k]), g[k]
             assert a.shape == b.shape and a.dtype == b.dtype, (fname, k, orc.kind)
             assert a.tobytes() == b.tobytes(), (fname, k, orc.kind)
+
+
+def test_vfo_signal_info_against_numpy():
+    rng = np.random.default_rng(5)
+    row = rng.uniform(-110, -70, 65536).astype(np.float32)
+    row[40000:40050] += 50
+    wb, center, bw = 20e6, 2.2e6, 30e3
+    st, snr = PORT.vfo_signal_info(row, wb, center, bw)
+    idx = lambda f: int(np.clip(int(f / (wb / 2) * 32768 + 32768), 0, 65536))
+    a, b, c, d = idx(center - bw), idx(center - bw / 2), idx(center + bw / 2), idx(center + bw)
+    side = np.concatenate([row[a:b], row[c + 1:d]]).astype(np.float64)
+    avg = side.mean()
+    srt = np.sort(side.astype(np.float32))
+    lower = len(srt) // 4
+    qavg = srt[srt <= srt[lower]].astype(np.float64).sum() / lower
+    mx = row[b:c + 1].max()
+    assert abs(st - (mx - (avg - qavg))) < 1e-3 and abs(snr - (mx - avg - (avg - qavg))) < 1e-3
+    if REF is not None:
+        assert REF.vfo_signal_info(row, wb, center, bw) == (st, snr)
