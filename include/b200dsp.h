@@ -105,9 +105,12 @@ int b200_vfo_set_phase(b200_vfo_bank* bank, int vfo, double re, double im);
 int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
 /* Tuning/test switches: B200_OPT_FUSED_STAGE1 (1 = fused xlate+decimate kernel where available, default;
  * 0 = separate rotation and generic FIR kernels, process-wide), B200_OPT_CALIBRATION_STEPS (length of the
- * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step). */
+ * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step), B200_OPT_TILE_SAMPLES (input
+ * samples per CTA tile of the fused kernel, process-wide: 0 = chosen by VFO count (default), 2048 or 4096;
+ * results do not depend on it). */
 #define B200_OPT_FUSED_STAGE1 1
 #define B200_OPT_CALIBRATION_STEPS 2
+#define B200_OPT_TILE_SAMPLES 3
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)
@@ -144,7 +147,15 @@ int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
 #define B200_DEMOD_LSB 4
 #define B200_DEMOD_DSB 5
 int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double p1, double p2, double p3);
-const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo);    /* device stereo[out_count] or NULL */
+/* The radio module's AF chain behind the demodulator (decoder_modules/radio/src/radio_module.h:101-107,756-765):
+ * dsp::multirate::RationalResampler<stereo_t> from the demodulator's rate to the audio device rate, then
+ * dsp::filter::Deemphasis<stereo_t> (core/src/dsp/filter/deephasis.h:58-92).  audio_samplerate <= 0 keeps the audio at
+ * the demodulator's rate; deemph_tau <= 0 leaves the de-emphasis out (the reference's default).  Needs a demodulator
+ * on the VFO; b200_vfo_set_demod() drops the setting again (call this after it). */
+int b200_vfo_set_audio_post(b200_vfo_bank* bank, int vfo, double audio_samplerate, double deemph_tau);
+const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo);    /* device stereo[audio_count] or NULL */
+int b200_vfo_audio_count(b200_vfo_bank* bank, int vfo);           /* stereo samples of the last call (== out_count without a resampler) */
+int b200_vfo_audio_max_out(b200_vfo_bank* bank, int vfo, int count);   /* upper bound of audio_count for `count` input samples */
 
 /* ------------------------------------------------------------------------------------------
  * IQ front end — replaces IQFrontEnd (signal_path/iq_frontend.{h,cpp}): pre-processing chain
@@ -193,7 +204,8 @@ const float* b200_frontend_frame_ptr(b200_frontend* fe, int i);
 int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index of frame i (for sharded reassembly) */
 /* Host-buffer variant (the drop-in path of include/dsp/iq_frontend.h): H2D of the block, then D2H
  * of `h_frames` (frame_count x fft_size floats, may be NULL) and each VFO's output (h_vfo_out[v],
- * may be NULL) / audio (h_audio[v], may be NULL).  Blocks until done. */
+ * may be NULL) / audio (h_audio[v], may be NULL; b200_vfo_audio_count(v) stereo samples, size it with
+ * b200_vfo_audio_max_out).  Blocks until done. */
 int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
                                float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
 

@@ -88,6 +88,11 @@ int orc_ssb_process(void* h, int count, const float* in, float* outStereo);
 void* orc_am_create(int agcMode /*0 CARRIER 1 AUDIO*/, double bandwidth, double agcAttack, double agcDecay, double dcBlockRate, double samplerate); // demod/am.h
 void orc_am_destroy(void* h);
 int orc_am_process(void* h, int count, const float* in, float* outStereo);
+// radio AF chain (decoder_modules/radio/src/radio_module.h:101-107,756-765): RationalResampler<stereo_t> to the audio
+// device rate, then optional Deemphasis<stereo_t> (filter/deephasis.h:58-76).  tau <= 0 disables the de-emphasis.
+void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau);
+void orc_afpost_destroy(void* h);
+int orc_afpost_process(void* h, int count, const float* inStereo, float* outStereo);   // returns out sample count
 // loop::AGC<float> stand-alone (loop/agc.h:85-139)
 void* orc_agc_create(double setPoint, double attack, double decay, double maxGain, double maxOutputAmp, double initGain);
 void orc_agc_destroy(void* h);

@@ -498,6 +498,31 @@ struct AmDemod {
     }
 };
 
+// ------------------------------------------------------------------ radio AF chain: RationalResampler<stereo_t> + Deemphasis<stereo_t>
+// (radio_module.h:101-107; filter/deephasis.h:58-76,89-92).  stereo_t goes through the same complex-by-real dot product.
+struct AfPost {
+    Rational resamp; bool deOn = false; float alpha = 0.f; cf last{ 0.f, 0.f };
+    void init(double inSR, double outSR, double tau) {
+        resamp.init(inSR, outSR);
+        deOn = tau > 0;
+        float dt = 1.0f / outSR;                 // updateAlpha: float dt, then float alpha = dt / (tau + dt) evaluated in double
+        alpha = dt / ((tau > 0 ? tau : 50e-6) + dt);
+    }
+    int process(int count, const cf* in, cf* out) {
+        int n = resamp.process(count, in, out);
+        if (deOn && n > 0) {
+            out[0].re = (alpha * out[0].re) + ((1 - alpha) * last.re);
+            out[0].im = (alpha * out[0].im) + ((1 - alpha) * last.im);
+            for (int i = 1; i < n; i++) {
+                out[i].re = (alpha * out[i].re) + ((1 - alpha) * out[i - 1].re);
+                out[i].im = (alpha * out[i].im) + ((1 - alpha) * out[i - 1].im);
+            }
+            last = out[n - 1];
+        }
+        return n;
+    }
+};
+
 // ------------------------------------------------------------------ IQFrontEnd pre-processing chain — iq_frontend.cpp:29-44
 struct Preproc {
     PowerDecim decim; DcBlockC dc; bool useDecim, useDc, useConj;
@@ -632,6 +657,9 @@ int orc_ssb_process(void* h, int count, const float* in, float* out) { return ((
 void* orc_am_create(int agcMode, double bw, double att, double dec, double dcRate, double sr) { auto* d = new AmDemod; d->init(agcMode, bw, att, dec, dcRate, sr); return d; }
 void orc_am_destroy(void* h) { delete (AmDemod*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) { return ((AmDemod*)h)->process(count, (const cf*)in, out); }
+void* orc_afpost_create(double inSR, double outSR, double tau) { auto* a = new AfPost; a->init(inSR, outSR, tau); return a; }
+void orc_afpost_destroy(void* h) { delete (AfPost*)h; }
+int orc_afpost_process(void* h, int count, const float* in, float* out) { return ((AfPost*)h)->process(count, (const cf*)in, (cf*)out); }
 void* orc_agc_create(double sp, double att, double dec, double mg, double moa, double ig) { auto* a = new Agc<float>; a->init(sp, att, dec, mg, moa, ig); return a; }
 void orc_agc_destroy(void* h) { delete (Agc<float>*)h; }
 int orc_agc_process(void* h, int count, const float* in, float* out) { return ((Agc<float>*)h)->process(count, in, out); }

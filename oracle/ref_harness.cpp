@@ -43,6 +43,7 @@
 #include <dsp/demod/ssb.h>
 #include <dsp/demod/am.h>
 #include <dsp/loop/agc.h>
+#include <dsp/filter/deephasis.h>
 #undef protected
 #undef private
 
@@ -253,6 +254,21 @@ void* orc_am_create(int agcMode, double bandwidth, double agcAttack, double agcD
 void orc_am_destroy(void* h) { delete (dsp::demod::AM<stereo_t>*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) {
     return ((dsp::demod::AM<stereo_t>*)h)->process(count, (complex_t*)in, (stereo_t*)out);
+}
+namespace { struct AfPost { dsp::multirate::RationalResampler<stereo_t> resamp; dsp::filter::Deemphasis<stereo_t> deemp; bool deOn; }; }
+void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau) {
+    auto* a = new AfPost;
+    a->resamp.init(NULL, inSamplerate, audioSamplerate);
+    a->deOn = tau > 0;
+    a->deemp.init(NULL, tau > 0 ? tau : 50e-6, audioSamplerate);
+    return a;
+}
+void orc_afpost_destroy(void* h) { delete (AfPost*)h; }
+int orc_afpost_process(void* h, int count, const float* in, float* out) {
+    auto* a = (AfPost*)h;
+    int n = a->resamp.process(count, (const stereo_t*)in, (stereo_t*)out);
+    if (a->deOn && n > 0) { a->deemp.process(n, (stereo_t*)out, (stereo_t*)out); }
+    return n;
 }
 void* orc_agc_create(double setPoint, double attack, double decay, double maxGain, double maxOutputAmp, double initGain) {
     auto* a = new dsp::loop::AGC<float>();

@@ -51,7 +51,10 @@ _SIGS = {
     "b200_vfo_bank_process_host": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
     "b200_vfo_max_out": (_i, [_vp, _i, _i]),
     "b200_vfo_set_demod": (_i, [_vp, _i, _i, _d, _d, _d, _d]),
+    "b200_vfo_set_audio_post": (_i, [_vp, _i, _d, _d]),
     "b200_vfo_audio_ptr": (_vp, [_vp, _i]),
+    "b200_vfo_audio_count": (_i, [_vp, _i]),
+    "b200_vfo_audio_max_out": (_i, [_vp, _i, _i]),
     "b200_frontend_create": (_i, [_pp, _d, _i, _i, _i, _i, _d, _i, _i, _i]),
     "b200_frontend_destroy": (_i, [_vp]),
     "b200_frontend_set_sample_rate": (_i, [_vp, _d]),
@@ -92,7 +95,7 @@ for _name, (_res, _args) in _SIGS.items():
 
 
 ROTATOR_FAST, ROTATOR_EXACT = 0, 1
-OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS = 1, 2
+OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS, OPT_TILE_SAMPLES = 1, 2, 3
 DEMOD_NONE, DEMOD_NFM, DEMOD_AM, DEMOD_USB, DEMOD_LSB, DEMOD_DSB = 0, 1, 2, 3, 4, 5
 
 
@@ -188,6 +191,10 @@ class VfoBank:
     def set_demod(self, v, kind, p0=0.0, p1=0.0, p2=0.0, p3=0.0):
         _chk(lib.b200_vfo_set_demod(self.h, v, int(kind), float(p0), float(p1), float(p2), float(p3)))
 
+    def set_audio_post(self, v, audio_samplerate=0.0, deemph_tau=0.0):
+        """radio AF chain behind the demodulator: resampler to the audio rate + de-emphasis (0 = leave out)"""
+        _chk(lib.b200_vfo_set_audio_post(self.h, v, float(audio_samplerate), float(deemph_tau)))
+
     def process(self, d_in, count=None, stream=None):
         """d_in: torch CUDA float32 tensor [count, 2] (or any tensor whose data_ptr holds cf32)."""
         if count is None:
@@ -202,8 +209,11 @@ class VfoBank:
         n = self.out_count(v)
         return _dev_to_numpy(self.out_ptr(v), n, np.complex64, self.device)
 
+    def audio_count(self, v): return _chk(lib.b200_vfo_audio_count(self.h, v))
+    def audio_max_out(self, v, count): return _chk(lib.b200_vfo_audio_max_out(self.h, v, int(count)))
+
     def audio(self, v):
-        n = self.out_count(v)
+        n = self.audio_count(v)
         p = self.audio_ptr(v)
         if not p:
             raise B200Error("VFO %d has no demodulator" % v)

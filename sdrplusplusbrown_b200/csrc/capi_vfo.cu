@@ -130,6 +130,11 @@ int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
         for (auto& v : bank->impl.vfos) { v.calDirty = true; }
         return B200_OK;
     }
+    if (option == B200_OPT_TILE_SAMPLES) {
+        if (value != 0 && value != 2048 && value != 4096) { setError("tile must be 0 (automatic), 2048 or 4096"); return B200_EINVAL; }
+        fusedTileSamples = value;
+        return B200_OK;
+    }
     setError("unknown option %d", option);
     return B200_EINVAL;
 }

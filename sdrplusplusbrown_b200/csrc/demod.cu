@@ -25,6 +25,7 @@ struct SeqState {
     float dcOffset;
     float quadPhase[2];   // ping-pong: written by one call, read by the next
     float2 rotPhase;      // SSB rotator, EXACT mode: the reference's fp32 phase
+    float2 deLast;        // Deemphasis<stereo_t>::lastOut (deephasis.h:92)
 };
 
 struct DemodState {
@@ -45,7 +46,15 @@ struct DemodState {
     float4* dMaps = nullptr; float* dAmps = nullptr;   // SSB fast path scratch
     long long envCount = 0;                            // host mirror of AGC::_startEnvelope (SSB fast path)
     int lastCount = 0;
+    // radio AF chain (radio_module.h:101-107): RationalResampler<stereo_t> to the audio rate, then Deemphasis<stereo_t>
+    bool afResamp = false; double afOutSR = 0.0;
+    std::vector<Stage> afDecim; Stage afPoly; bool afHasPoly = false; int afMode = 3;
+    bool deOn = false; float deAlpha = 0.f;
+    const float* lastAudio = nullptr; int lastAudioCount = 0;
 };
+
+// per-call descriptor of the de-emphasis walk
+struct DeemphJob { float2* data; SeqState* st; float alpha; int n; };
 
 // per-call descriptor
 struct DemodJob {
@@ -415,11 +424,47 @@ __global__ void __launch_bounds__(256) stereoKernel(const DemodJob* __restrict__
     reinterpret_cast<float2*>(j.stereo)[i] = make_float2(v, v);
 }
 
+// Deemphasis<stereo_t> (filter/deephasis.h:58-76): out[i] = alpha*in[i] + (1-alpha)*out[i-1], in place, state carried
+// between calls.  A first-order recurrence whose fp32 rounding depends on the order, so it is walked in order: the CTA
+// stages a chunk and forms alpha*in[i] for every sample, two threads (left, right) walk FMUL -> FADD, the CTA stores.
+constexpr int kDeChunk = 1024;
+__global__ void __launch_bounds__(64) deemphKernel(const DeemphJob* __restrict__ jobs) {
+    const DeemphJob j = jobs[blockIdx.x];
+    __shared__ float sv[2][kDeChunk + 1];
+    const float beta = __fsub_rn(1.0f, j.alpha);
+    float prev = 0.f;
+    if (threadIdx.x < 2) { prev = threadIdx.x == 0 ? j.st->deLast.x : j.st->deLast.y; }
+    for (int base = 0; base < j.n; base += kDeChunk) {
+        const int m = min(kDeChunk, j.n - base);
+        for (int i = threadIdx.x; i < m; i += 64) {
+            const float2 v = j.data[base + i];
+            sv[0][i] = __fmul_rn(j.alpha, v.x);
+            sv[1][i] = __fmul_rn(j.alpha, v.y);
+        }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            float* row = sv[threadIdx.x];
+#pragma unroll 8
+            for (int i = 0; i < m; i++) {
+                prev = __fadd_rn(row[i], __fmul_rn(beta, prev));
+                row[i] = prev;
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < m; i += 64) { j.data[base + i] = make_float2(sv[0][i], sv[1][i]); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && j.n > 0) { j.st->deLast.x = prev; }
+    if (threadIdx.x == 1 && j.n > 0) { j.st->deLast.y = prev; }
+}
+
 } // namespace
 
 void demodDestroy(DemodState* d) {
     if (!d) { return; }
     d->fir.destroy();
+    for (auto& st : d->afDecim) { st.destroy(); }
+    d->afPoly.destroy();
     if (d->dState) { cudaFree(d->dState); }
     if (d->dWtab) { cudaFree(d->dWtab); }
     if (d->dMono) { cudaFree(d->dMono); }
@@ -527,9 +572,63 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
     return demodEnsureCap(*d, bank.maxOut((int)(&v - bank.vfos.data()), bank.maxBlock) + 8);
 }
 
+static int afMaxOut(const DemodState& d, int count) {
+    int64_t n = count;
+    if (!d.afResamp) { return (int)n; }
+    if (d.afMode == 0 || d.afMode == 1) { for (auto& st : d.afDecim) { n = n / st.D + 2; } }
+    if (d.afMode == 0 || d.afMode == 2) { n = (n * d.afPoly.L) / d.afPoly.M + 4; }
+    return (int)n;
+}
+
+// afChain of the radio module: resamp.init(NULL, afRate, audioRate) (radio_module.h:101,757-758) and
+// deemp.init(NULL, tau, audioRate) (:102).  audioSR <= 0 leaves the audio at the demodulator's rate, tau <= 0
+// leaves the de-emphasis out (its default state in the reference).
+static int afConfigure(VfoBank& bank, Vfo& v, double audioSR, double tau) {
+    if (!v.demod) { setError("audio post-processing needs a demodulator on the VFO first"); return B200_EINVAL; }
+    DemodState& d = *v.demod;
+    for (auto& st : d.afDecim) { st.destroy(); }
+    d.afDecim.clear();
+    d.afPoly.destroy(); d.afHasPoly = false;
+    d.afResamp = audioSR > 0.0;
+    d.afOutSR = d.afResamp ? audioSR : d.sr;
+    d.afMode = 3;
+    int cap = std::max(d.cap, 64);
+    if (d.afResamp) {
+        design::ResampPlan p = design::planResampler(d.sr, audioSR);
+        d.afMode = p.mode;
+        if (p.mode == 0 || p.mode == 1) {
+            const design::PlanDef* plan = design::findPlan(p.ratio);
+            if (!plan) { setError("no decimation plan for ratio %d", p.ratio); return B200_EINVAL; }
+            d.afDecim.resize(plan->nstages);
+            for (int i = 0; i < plan->nstages; i++) {
+                std::vector<float> t(plan->stages[i].ntaps);
+                memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());   // the table holds IEEE bit patterns
+                cap = cap / plan->stages[i].decim + 2;
+                B200_TRY(d.afDecim[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap));
+            }
+        }
+        if (p.mode == 0 || p.mode == 2) {
+            const int pcap = (int)(((int64_t)cap * p.interp) / p.decim) + 4;
+            B200_TRY(d.afPoly.create(JOB_POLYPHASE, p.taps, 1, p.interp, p.decim, 2, pcap));
+            d.afHasPoly = true;
+        }
+    }
+    d.deOn = tau > 0.0;
+    if (d.deOn) {
+        const float dt = 1.0f / d.afOutSR;          // Deemphasis::updateAlpha (deephasis.h:82-85)
+        d.deAlpha = dt / (tau + dt);
+    }
+    const float2 zero = make_float2(0.f, 0.f);
+    B200_CUDA(cudaMemcpy(&d.dState->deLast, &zero, sizeof(zero), cudaMemcpyHostToDevice));
+    d.lastAudio = nullptr; d.lastAudioCount = 0;
+    return B200_OK;
+}
+
 int processDemods(VfoBank& bank, cudaStream_t s) {
     std::vector<DemodJob> seq, quad, all, ssb;
     std::vector<FirJob> firs;
+    std::vector<std::vector<FirJob>> afWaves;   // wave k = stage k of every VFO's audio resampler
+    std::vector<DeemphJob> deJobs;
     int maxN = 0;
     for (size_t vi = 0; vi < bank.vfos.size(); vi++) {
         Vfo& v = bank.vfos[vi];
@@ -553,6 +652,25 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             src = (const float*)d.fir.dOut;
         }
         j.stereoSrc = src;
+        {   // audio chain bookkeeping: what leaves the demodulator goes through resampler stages, then the de-emphasis
+            const void* data = d.dStereo; int m = n; size_t wave = 0;
+            if (d.afResamp) {
+                auto pushStage = [&](Stage& st) -> int {
+                    const int outN = st.outCountFor(m);
+                    if (outN > st.outCap) { B200_CUDA(cudaStreamSynchronize(s)); B200_TRY(st.ensureOutCap(outN + 64)); }
+                    FirJob f; st.fillJob(f, data, m);
+                    if (afWaves.size() <= wave) { afWaves.resize(wave + 1); }
+                    afWaves[wave++].push_back(f);
+                    st.advance(m);
+                    data = st.dOut; m = f.nOut;
+                    return B200_OK;
+                };
+                if (d.afMode == 0 || d.afMode == 1) { for (auto& st : d.afDecim) { B200_TRY(pushStage(st)); } }
+                if (d.afHasPoly) { B200_TRY(pushStage(d.afPoly)); }
+            }
+            if (d.deOn && m > 0) { deJobs.push_back(DeemphJob{ (float2*)data, d.dState, d.deAlpha, m }); }
+            d.lastAudio = (const float*)data; d.lastAudioCount = m;
+        }
         if (n > 0) {
             if (d.kind == B200_DEMOD_NFM) { quad.push_back(j); d.quadParity ^= 1; }
             else {
@@ -569,9 +687,12 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             maxN = std::max(maxN, n);
         }
     }
-    if (all.empty() && firs.empty() && ssb.empty()) { return B200_OK; }
-    // one upload: [seq][quad][all][firs]
-    const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + firs.size() * sizeof(FirJob) + 512;
+    if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty()) { return B200_OK; }
+    // one upload: [seq][quad][all][firs][ssb][af waves][deemph]
+    size_t afJobs = 0;
+    for (auto& w : afWaves) { afJobs += w.size(); }
+    const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + (firs.size() + afJobs) * sizeof(FirJob) +
+                         deJobs.size() * sizeof(DeemphJob) + 64 * (afWaves.size() + 8);
     void* hp = nullptr; int slot = 0;
     B200_TRY(bank.ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -581,6 +702,9 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     const size_t oA = put(all.data(), all.size() * sizeof(DemodJob));
     const size_t oF = put(firs.data(), firs.size() * sizeof(FirJob));
     const size_t oB = put(ssb.data(), ssb.size() * sizeof(DemodJob));
+    std::vector<size_t> oW(afWaves.size());
+    for (size_t w = 0; w < afWaves.size(); w++) { oW[w] = put(afWaves[w].data(), afWaves[w].size() * sizeof(FirJob)); }
+    const size_t oD = put(deJobs.data(), deJobs.size() * sizeof(DeemphJob));
     if (off > bank.dDemodDescBytes) {
         B200_CUDA(cudaStreamSynchronize(s));
         if (bank.dDemodDesc) { cudaFree(bank.dDemodDesc); }
@@ -620,6 +744,16 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         stereoKernel<<<dim3((maxN + 255) / 256, (unsigned)all.size()), 256, 0, s>>>((const DemodJob*)(dd + oA));
         B200_CHECK_LAUNCH(); countLaunch();
     }
+    for (size_t w = 0; w < afWaves.size(); w++) {
+        int maxOut = 0, maxH = 0, maxSpan = 0;
+        for (auto& f : afWaves[w]) { maxOut = std::max(maxOut, f.nOut); maxH = std::max(maxH, f.H); maxSpan = std::max(maxSpan, firJobSpan(f)); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oW[w]), (int)afWaves[w].size(), maxOut, 2, maxSpan, s));
+        B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oW[w]), (int)afWaves[w].size(), maxH, s));
+    }
+    if (!deJobs.empty()) {
+        deemphKernel<<<(unsigned)deJobs.size(), 64, 0, s>>>((const DeemphJob*)(dd + oD));
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
     return B200_OK;
 }
 
@@ -637,10 +771,35 @@ int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double
     return demodConfigure(bank->impl, bank->impl.vfos[vfo], kind, p0, p1, p2, p3);
 }
 
+int b200_vfo_set_audio_post(b200_vfo_bank* bank, int vfo, double audio_samplerate, double deemph_tau) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    DeviceGuard g(bank->impl.device);
+    B200_TRY(bank->impl.syncLast());
+    return afConfigure(bank->impl, bank->impl.vfos[vfo], audio_samplerate, deemph_tau);
+}
+
 const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo) {
     if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
     const Vfo& v = bank->impl.vfos[vfo];
-    return v.demod ? v.demod->dStereo : nullptr;
+    if (!v.demod) { return nullptr; }
+    return v.demod->lastAudio ? v.demod->lastAudio : v.demod->dStereo;
+}
+
+int b200_vfo_audio_count(b200_vfo_bank* bank, int vfo) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    const Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { setError("VFO %d has no demodulator", vfo); return B200_EINVAL; }
+    return v.demod->lastAudioCount;
+}
+
+int b200_vfo_audio_max_out(b200_vfo_bank* bank, int vfo, int count) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    const Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { setError("VFO %d has no demodulator", vfo); return B200_EINVAL; }
+    return afMaxOut(*v.demod, bank->impl.maxOut(vfo, count));
 }
 
 } // extern "C"

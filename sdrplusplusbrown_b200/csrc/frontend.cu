@@ -595,7 +595,8 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
         }
         if (h_audio && h_audio[i]) {
             const float* ap = b200_vfo_audio_ptr(f.bank, (int)i);
-            if (ap) { B200_CUDA(cudaMemcpyAsync(h_audio[i], ap, (size_t)v.lastOut * 2 * sizeof(float), cudaMemcpyDeviceToHost, s)); }
+            const int an = ap ? b200_vfo_audio_count(f.bank, (int)i) : 0;   // differs from lastOut behind an audio resampler
+            if (an > 0) { B200_CUDA(cudaMemcpyAsync(h_audio[i], ap, (size_t)an * 2 * sizeof(float), cudaMemcpyDeviceToHost, s)); }
         }
     }
     B200_CUDA(cudaStreamSynchronize(s));

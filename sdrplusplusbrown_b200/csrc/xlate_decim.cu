@@ -31,6 +31,9 @@
 
 namespace b200 {
 
+int fusedTileSamples = 0;   // 0 = choose by VFO count (B200_OPT_TILE_SAMPLES)
+
+
 namespace {
 
 // ---- coefficient tables in the constant bank (all 13 stage filters, 9 KB)
@@ -78,10 +81,15 @@ template <int RATIO> struct FirstStage;
 constexpr int kMaxGroup = 8;         // VFOs per CTA (the input tile is staged once per group)
 constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
 
-template <int D> struct TileCfg {
-    // sub-blocks per CTA: ~4096 samples (32 KB) of input per tile, so that several CTAs are resident per SM and one
-    // CTA's load phase overlaps its neighbours' arithmetic
-    static constexpr int SB = (4096 / D) > 256 ? 256 : ((4096 / D) < 32 ? 32 : (4096 / D));
+// Input samples per CTA tile.  Measured on B200 (tools/bench_bank.py): with a single VFO the kernel is HBM-bound and
+// the smaller tile wins (more resident CTAs, the load phase of one overlaps the arithmetic of its neighbours: 0.65 of
+// the copy bandwidth against 0.58); from two VFOs on the larger tile wins (fewer
+// overlap sub-blocks recomputed per output: 0.35 of the FFMA peak against 0.32).
+constexpr int kTileSmall = 2048, kTileLarge = 4096;
+
+template <int D, int TILE> struct TileCfg {
+    // sub-blocks per CTA
+    static constexpr int SB = (TILE / D) > 256 ? 256 : ((TILE / D) < 32 ? 32 : (TILE / D));
     // threads per sub-block: a sub-block of D samples is split into RS runs of DS = D/RS <= 32 samples, so that the
     // shared-memory tile (8*D bytes per sub-block) does not cap the resident warps for the large-D plans
     static constexpr int RS = D > 32 ? D / 32 : 1;
@@ -113,12 +121,11 @@ __device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
 // One thread's run of DS samples of one sub-block for VB VFOs at once: each input sample is read from shared
 // memory once, rotated once per VFO, and feeds that VFO's Q accumulators.  RUN selects which DS-sample slice
 // of the D-sample sub-block this thread owns (compile time, so every tap is a constant-bank operand).
-template <int RATIO, int RUN, int VB>
+template <int RATIO, int RUN, int VB, int DS>
 __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, const float2* __restrict__ ws, float2 (*acc)[8]) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
-    constexpr int DS = TileCfg<D>::DS;
 #pragma unroll
     for (int r = 0; r < DS; r++) {
         const float2 x = xrow[r];
@@ -139,11 +146,11 @@ __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, c
 
 // grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
 // VB = VFOs per register pass (only VB = 1 is instantiated, see launchPlan).
-template <int RATIO, int VB>
-__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D>::THREADS)
+template <int RATIO, int VB, int TILE>
+__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
 fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     using FS = FirstStage<RATIO>;
-    using TC = TileCfg<FS::D>;
+    using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T, H = T - 1;
     constexpr int Q = (T + D - 1) / D;
     static_assert(Q <= 8, "accumulator array is sized for Q <= 8");
@@ -210,10 +217,10 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
             for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
         }
         switch (run) {
-        case 0: accumulateRun<RATIO, 0, VB>(xrow, ws, acc); break;
-        case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, VB>(xrow, ws, acc); } break;
-        case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, VB>(xrow, ws, acc); } break;
-        default: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB>(xrow, ws, acc); } break;
+        case 0: accumulateRun<RATIO, 0, VB, DS>(xrow, ws, acc); break;
+        case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, VB, DS>(xrow, ws, acc); } break;
+        case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, VB, DS>(xrow, ws, acc); } break;
+        default: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB, DS>(xrow, ws, acc); } break;
         }
 #pragma unroll
         for (int v = 0; v < VB; v++) {
@@ -306,18 +313,18 @@ int profDrain() {
     return B200_OK;
 }
 
-template <int RATIO, int VB>
+template <int RATIO, int VB, int TILE>
 int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
-    using TC = TileCfg<D>;
+    using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB;
     constexpr int NB = SB - (Q - 1);
     constexpr int NPB = (VB == 1) ? 2 : 1;
     const int Gp = ((G + VB - 1) / VB) * VB;
     const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gp * D + (size_t)NPB * VB * Q * TC::THREADS + (size_t)Gp * SB) * sizeof(float2);
-    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + G - 1) / G);
     size_t slot = 0;
@@ -335,7 +342,7 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
         g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
         B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
     }
-    fusedXlateDecimKernel<RATIO, VB><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G);
+    fusedXlateDecimKernel<RATIO, VB, TILE><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G);
     B200_CHECK_LAUNCH(); countLaunch();
     if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
     return B200_OK;
@@ -346,8 +353,10 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
-    constexpr int NB = TileCfg<D>::SB - (Q - 1);
     if (nOut > 0) {
+        const int tile = fusedTileSamples > 0 ? fusedTileSamples : (nJobs == 1 ? kTileSmall : kTileLarge);
+        const bool small = tile <= kTileSmall;
+        const int NB = (small ? TileCfg<D, kTileSmall>::SB : TileCfg<D, kTileLarge>::SB) - (Q - 1);
         // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
         const int tiles = (nOut + NB - 1) / NB;
         int G = std::min(kMaxGroup, nJobs);
@@ -355,7 +364,8 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream
         // One VFO per register pass.  Register-blocking 2 or 4 VFOs per pass (shared x reads, fewer barriers) was
         // measured slower on B200: the 4-VFO unrolled body (57 KB at D=64) stalls on instruction fetch (39 % of
         // stall samples), a rolled 4-VFO body with shared-memory taps reached 0.27 of the FP32 peak against 0.35 here.
-        B200_TRY((launchMain<RATIO, 1>(dJobs, nJobs, nOut, count, G, s)));
+        if (small) { B200_TRY((launchMain<RATIO, 1, kTileSmall>(dJobs, nJobs, nOut, count, G, s))); }
+        else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
     B200_CHECK_LAUNCH(); countLaunch();

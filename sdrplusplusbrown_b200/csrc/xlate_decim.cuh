@@ -24,6 +24,7 @@ struct FusedJob {
 };
 
 extern bool fusedEnabled;   // test hook: false forces the unfused xlate -> generic FIR path
+extern int fusedTileSamples; // tuning hook: 0 = by VFO count, else input samples per CTA tile
 bool fusedStageSupported(const Vfo& v);
 void fillFusedJob(FusedJob& f, const Stage& st, const Vfo& v, const cf32* dIn, int count);
 int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cudaStream_t s);

@@ -65,6 +65,9 @@ _SIGS = {
     "orc_am_create": (_vp, [_i, _d, _d, _d, _d, _d]),
     "orc_am_destroy": (None, [_vp]),
     "orc_am_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_afpost_create": (_vp, [_d, _d, _d]),
+    "orc_afpost_destroy": (None, [_vp]),
+    "orc_afpost_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_agc_create": (_vp, [_d, _d, _d, _d, _d, _d]),
     "orc_agc_destroy": (None, [_vp]),
     "orc_agc_process": (_i, [_vp, _i, _vp, _vp]),
@@ -284,6 +287,19 @@ class Ssb(_Demod):
 class Am(_Demod):
     def __init__(self, orc, agc_mode, bw, attack, decay, dc_rate, sr):
         super().__init__(orc, orc.lib.orc_am_create(agc_mode, bw, attack, decay, dc_rate, sr), "orc_am")
+
+
+class AfPost(_Block):
+    """radio AF chain: stereo in at the demodulator's rate -> stereo out at the audio rate (+ de-emphasis)"""
+    def __init__(self, orc, in_sr, audio_sr, tau=0.0):
+        self.ratio = audio_sr / in_sr
+        super().__init__(orc, orc.lib.orc_afpost_create(in_sr, audio_sr, tau), "orc_afpost")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.float32).reshape(-1, 2)
+        out = np.zeros((int(len(x) * max(self.ratio, 1.0) * 1.05) + 1024, 2), np.float32)   # stages also use `out` as scratch
+        n = self.orc.lib.orc_afpost_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:n].copy()
 
 
 class Agc(_Block):

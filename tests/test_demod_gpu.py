@@ -136,3 +136,65 @@ def test_many_demods_in_one_bank():
             got = b.audio(v)
             assert len(got) == len(ref)
             assert err_db(got[:, 0], ref[:, 0]) <= -80.0, name
+
+
+# radio AF chain behind the demodulator: (demod rate, audio rate, de-emphasis tau) -> resampler mode it exercises
+AF_CASES = [
+    ("demod_nfm", 48e3, 0.0),        # 50k -> 48k   24/25 polyphase only
+    ("demod_nfm", 48e3, 50e-6),      # the same with the 50 us de-emphasis
+    ("demod_usb", 48e3, 75e-6),      # 24k -> 48k   interpolate by 2
+    ("demod_am", 48e3, 50e-6),       # 15k -> 48k   16/5
+    ("demod_nfm", 11025.0, 50e-6),   # 50k -> 11.025k  power-of-two decimator + polyphase
+    ("demod_nfm", 12500.0, 0.0),     # 50k -> 12.5k    decimator only
+    ("demod_usb", 24e3, 50e-6),      # equal rates: resampler is a copy, de-emphasis runs
+    ("demod_usb", 0.0, 22e-6),       # no resampler block at all
+]
+
+
+@pytest.mark.parametrize("name,audio_sr,tau", AF_CASES)
+def test_audio_post_chain_matches_oracle(name, audio_sr, tau):
+    """VFO -> demodulator -> RationalResampler<stereo_t> -> Deemphasis<stereo_t>, ragged blocks, exact rotators.
+    Audio sample counts must agree exactly; audio error <= -80 dB of the block's RMS."""
+    from sdrplusplusbrown_b200 import binding
+    out_sr, o_dem, (kind, p0, p1, p2, p3), bw = _demod_pair(name)
+    in_sr = out_sr * 32
+    off = -21e3 + 3.0
+    n = 32 * 12000
+    x = synth.make_iq(3, n, in_sr, sigma=0.02, tones=[(off + 700.0, 0.3), (off - 1200.0, 0.07)])
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_af = ol.AfPost(PORT, out_sr, audio_sr if audio_sr > 0 else out_sr, tau)
+    b = binding.VfoBank(in_sr, max_block=200000)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, kind, p0, p1, p2, p3)
+    b.set_audio_post(v, audio_sr, tau)
+    total = 0
+    for blk in split(x, [64000, 4800 * 32 + 17, 33, 5]):
+        iq = o_vfo.process(blk)
+        au = o_dem.process(iq) if len(iq) else np.zeros((0, 2), np.float32)
+        ref = o_af.process(au) if len(au) else np.zeros((0, 2), np.float32)
+        b.process(to_dev(blk))
+        assert b.audio_count(v) == len(ref), (name, audio_sr)
+        assert b.audio_count(v) <= b.audio_max_out(v, len(blk))
+        total += len(ref)
+        if len(ref) > 8:
+            got = b.audio(v)
+            e = max(err_db(got[:, 0], ref[:, 0]), err_db(got[:, 1], ref[:, 1]))
+            assert e <= -80.0, (name, audio_sr, tau, e)
+    assert total > 0
+
+
+def test_audio_post_needs_a_demodulator_and_is_dropped_by_set_demod():
+    from sdrplusplusbrown_b200 import binding
+    b = binding.VfoBank(1.6e6, max_block=65536)
+    v = b.add(50e3, 12.5e3, 0.0)
+    with pytest.raises(binding.B200Error):
+        b.set_audio_post(v, 48e3, 0.0)
+    b.set_demod(v, binding.DEMOD_NFM, 1, 0, 0, 0)
+    b.set_audio_post(v, 48e3, 50e-6)
+    x = synth.make_iq(1, 64000, 1.6e6, sigma=0.1)
+    b.process(to_dev(x))
+    assert b.audio_count(v) == 1920                 # 2000 IF samples * 24/25
+    b.set_demod(v, binding.DEMOD_NFM, 1, 0, 0, 0)   # rebuilding the demodulator rebuilds a plain AF path
+    b.process(to_dev(x))
+    assert b.audio_count(v) == b.out_count(v) == 2000

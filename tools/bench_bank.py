@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1 << 24)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--demod", action="store_true")
+    ap.add_argument("--tile", type=int, default=0, help="fused-kernel tile samples (0 = library default)")
     args = ap.parse_args()
     cfg = configs.CONFIGS[args.cfg]
     sr = cfg["sample_rate"]
@@ -43,6 +44,7 @@ def main():
     for n in [int(c) for c in args.counts.split(",")]:
         vfos = configs.vfo_list(args.cfg, n)
         bank = binding.VfoBank(sr, max_block=args.batch)
+        bank.set_option(binding.OPT_TILE_SAMPLES, args.tile)
         instr = 0.0
         for mode, out_sr, bw, off in vfos:
             v = bank.add(out_sr, bw, off)
