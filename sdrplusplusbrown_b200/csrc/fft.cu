@@ -169,8 +169,10 @@ __device__ __forceinline__ float2 frameSample(const FrameDesc& f, const float* _
 
 __device__ __forceinline__ float powerDb(float2 X, float invN) {
     const float r = X.x * invN, q = X.y * invN;
-    float l = log2f(r * r + q * q);
-    if (isinf(l)) { l = copysignf(127.0f, l); }
+    // MUFU.LG2: absolute error < 1e-6 in log2, i.e. < 4e-6 dB; an exact zero gives -inf and is clamped like the
+    // reference's generic power-spectrum kernel does (log2 limited to +-127)
+    float l = __log2f(r * r + q * q);
+    l = fminf(fmaxf(l, -127.0f), 127.0f);
     return 3.01029995663981209120f * l;
 }
 
@@ -204,7 +206,7 @@ __global__ void __launch_bounds__(kThreads, 3) fftPass1Kernel(const FrameDesc* _
                                                            const float2* __restrict__ twLo, const float2* __restrict__ twHi, int logS,
                                                            cf32* __restrict__ scratch, int scratchFrames) {
     extern __shared__ __align__(16) float2 sm[];
-    const int N1 = 1 << logN1, N2 = 1 << logN2, C = 1 << logC;
+    const int N1 = 1 << logN1, C = 1 << logC;
     const FrameDesc f = frames[blockIdx.y];
     const int c0 = blockIdx.x << logC;
     const int LP = slot(N1) + 1;
@@ -298,6 +300,222 @@ __global__ void __launch_bounds__(kThreads, 3) fftPass2Kernel(int logN1, int log
     }
 }
 
+// ---- register-resident passes for N1, N2 in {64, 128, 256} (N = 2^14 .. 2^16, the waterfall sizes of cfg2)
+// A length-L transform with L = RA * RB is two Stockham stages.  Each thread loads the RA points of its first
+// butterfly straight from global memory into registers (window applied on the way), the single exchange between
+// the stages goes through shared memory once, and the RB results of the second butterfly leave from registers
+// (inter-pass twiddle or |X|^2 -> dB applied on the way).  Shared memory is touched twice per point instead of
+// ten times, there is one barrier per CTA, and every global access is a 64-128 byte contiguous run per half-warp.
+template <int RA, int RB> struct TwoStage {
+    static constexpr int TPC = RA > RB ? RA : RB;     // threads per column (row): stage 1 uses RB of them, stage 2 RA
+};
+
+// pass 1: a tile = 16 adjacent columns n2 = c0 .. c0+15 of one frame, transforms over n1 (global stride N2).
+// Persistent CTAs: CTA b owns column block b % (N2/16) and walks the frames b / (N2/16), += gridDim.x / (N2/16), so
+// its window samples and inter-pass twiddles are loaded once; the next tile's samples are in flight (cp.async into the
+// other half of a double buffer) while the current tile is transformed.  The exchange between the two stages reuses
+// the tile's own buffer.
+template <int RA, int RB>
+__global__ void __launch_bounds__(16 * TwoStage<RA, RB>::TPC, 512 / (16 * TwoStage<RA, RB>::TPC))
+fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __restrict__ win, int nz, int logN2,
+              const float2* __restrict__ twN1, const float2* __restrict__ twLo, const float2* __restrict__ twHi, int logS,
+              cf32* __restrict__ scratch, int scratchFrames) {
+    constexpr int L = RA * RB, C = 16, NT = 16 * TwoStage<RA, RB>::TPC;
+    extern __shared__ __align__(16) float2 sm[];         // raw[2][L * C], [point][column]
+    const int blocksPerFrame = 1 << (logN2 - 4);
+    const int cb = blockIdx.x & (blocksPerFrame - 1);
+    const int fStep = gridDim.x >> (logN2 - 4);
+    const int c = threadIdx.x & (C - 1), j = threadIdx.x >> 4;
+    const int n2 = (cb << 4) + c;
+
+    // this thread's cp.async duties for a tile: elements e = threadIdx.x + u * NT of [n1][c]
+    auto issue = [&](int frame, float2* dst) {
+        const FrameDesc f = frames[frame];
+        // element e = threadIdx.x + u * NT of [n1][c] is frame sample i0 + u * iStep
+        const float2* p0 = reinterpret_cast<const float2*>(f.src0);
+        const float2* p1 = reinterpret_cast<const float2*>(f.src1) - f.len0;
+        int i = ((threadIdx.x >> 4) << logN2) + (cb << 4) + (threadIdx.x & 15);
+        const int iStep = (NT >> 4) << logN2;
+        float2* d = dst + threadIdx.x;
+#pragma unroll 4
+        for (int u = 0; u < (L * C) / NT; u++) {
+            const bool ok = i < nz;
+            const int ii = ok ? i : 0;
+            cpAsync8(d, (ii < f.len0 ? p0 : p1) + ii, ok);
+            i += iStep; d += NT;
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    // per-thread constants: window of the RA stage-1 inputs, inter-pass twiddle base and step
+    float wv[RA];
+    float2 g = make_float2(1.f, 0.f), g2 = g, wb = g;
+    if (j < RB) {
+#pragma unroll
+        for (int r = 0; r < RA; r++) {
+            const int i = ((j + r * RB) << logN2) + n2;
+            wv[r] = (win && i < nz) ? __ldg(win + i) : 1.0f;
+        }
+    }
+    if (j < RA) {
+        const int maskS = (1 << logS) - 1;
+        const int mb = n2 * j, mg = n2 * RA;             // both < N
+        g = cmul(__ldg(twLo + (mg & maskS)), __ldg(twHi + (mg >> logS)));
+        g2 = cmul(g, g);
+        wb = cmul(__ldg(twLo + (mb & maskS)), __ldg(twHi + (mb >> logS)));
+    }
+
+    int frame = blockIdx.x >> (logN2 - 4);
+    if (frame >= nFrames) { return; }
+    issue(frame, sm);
+    for (int it = 0; frame < nFrames; frame += fStep, it++) {
+        float2* raw = sm + (it & 1) * (L * C);
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();                                 // tile landed; everyone is done with the previous tile
+        if (frame + fStep < nFrames) { issue(frame + fStep, sm + ((it & 1) ^ 1) * (L * C)); }
+        float2 v[RA > RB ? RA : RB];
+        if (j < RB) {
+#pragma unroll
+            for (int r = 0; r < RA; r++) {
+                const float2 x = raw[(j + r * RB) * C + c];
+                v[r] = make_float2(x.x * wv[r], x.y * wv[r]);
+            }
+            Dft<RA>::run(v);
+        }
+        __syncthreads();                                 // all stage-1 reads done: the buffer becomes the exchange
+        if (j < RB) {
+#pragma unroll
+            for (int r = 0; r < RA; r++) { raw[(j * RA + r) * C + c] = v[r]; }
+        }
+        __syncthreads();
+        if (j < RA) {
+#pragma unroll
+            for (int r = 0; r < RB; r++) { v[r] = raw[(j + r * RA) * C + c]; }
+#pragma unroll
+            for (int r = 1; r < RB; r++) { v[r] = cmul(v[r], __ldg(twN1 + j * r)); }
+            Dft<RB>::run(v);
+            // inter-pass twiddle W_N^(n2*k1), k1 = j + r*RA: W^(n2*j) * (W^(n2*RA))^r by two interleaved recurrences
+            // (even / odd r), at most RB/2 roundings deep
+            float2* T = reinterpret_cast<float2*>(scratch) + (size_t)(frame % scratchFrames) * ((size_t)L << logN2) + ((size_t)j << logN2) + n2;
+            const size_t tStep = (size_t)RA << logN2;
+            float2 we = wb, wo = cmul(wb, g);
+#pragma unroll
+            for (int r = 0; r < RB; r += 2) {
+                T[0] = cmul(v[r], we);
+                T[tStep] = cmul(v[r + 1], wo);
+                T += 2 * tStep;
+                we = cmul(we, g2); wo = cmul(wo, g2);
+            }
+        }
+    }
+}
+
+// pass 2: a tile = 16 adjacent rows k1 = r0 .. r0+15 of one frame's intermediate (32 KB contiguous in the scratch
+// ring), transforms over n2; X[k1 + N1*k2].  Persistent CTAs walk the tiles in order with the next tile's copy
+// (16-byte cp.async) in flight behind the current transform; the stage-2 twiddles stay in registers for the CTA's
+// lifetime.
+template <int RA, int RB>
+__global__ void __launch_bounds__(16 * TwoStage<RA, RB>::TPC, 512 / (16 * TwoStage<RA, RB>::TPC))
+fftRowsKernel(int logN1, int nTiles, const float2* __restrict__ twN2, const cf32* __restrict__ scratch, int frameBase,
+              float* __restrict__ outDb, cf32* __restrict__ outSpec) {
+    constexpr int L = RA * RB, R = 16, NT = 16 * TwoStage<RA, RB>::TPC;
+    // exchange layout [point p][row] with one pad element per RA points: the stage-1 stores (lanes step p by RA) and the
+    // stage-2 loads (lanes step the row) are both conflict-free.  Each buffer first receives the raw tile [row][n2].
+    constexpr int BUF = (L * R + RB + 2) & ~1;
+    extern __shared__ __align__(16) float2 sm[];
+    const size_t N = (size_t)L << logN1;
+    const float invN = 1.0f / (float)N;
+    const int tilesPerFrame = 1 << (logN1 - 4);
+
+    auto issue = [&](int tile, float2* dst) {
+        const float4* src = reinterpret_cast<const float4*>(scratch) + (size_t)tile * (L * R / 2);
+        const unsigned d0 = (unsigned)__cvta_generic_to_shared(dst);
+#pragma unroll 4
+        for (int u = 0; u < (L * R / 2) / NT; u++) {
+            const int e = threadIdx.x + u * NT;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d0 + e * 16), "l"(src + e) : "memory");
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    const int j1 = threadIdx.x % RB, row1 = threadIdx.x / RB;      // stage 1: lanes walk n2
+    const int row2 = threadIdx.x & (R - 1), j2 = threadIdx.x >> 4;  // stage 2: lanes walk the row (contiguous stores)
+    float2 tw[RB];
+#pragma unroll
+    for (int r = 1; r < RB; r++) { tw[r] = (j2 < RA) ? __ldg(twN2 + j2 * r) : make_float2(1.f, 0.f); }
+
+    int tile = blockIdx.x;
+    if (tile >= nTiles) { return; }
+    issue(tile, sm);
+    for (int it = 0; tile < nTiles; tile += gridDim.x, it++) {
+        float2* buf = sm + (it & 1) * BUF;
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();
+        if (tile + (int)gridDim.x < nTiles) { issue(tile + gridDim.x, sm + ((it & 1) ^ 1) * BUF); }
+        float2 v[RA > RB ? RA : RB];
+        if (row1 < R) {
+#pragma unroll
+            for (int r = 0; r < RA; r++) { v[r] = buf[row1 * L + j1 + r * RB]; }
+            Dft<RA>::run(v);
+        }
+        __syncthreads();
+        if (row1 < R) {
+#pragma unroll
+            for (int r = 0; r < RA; r++) { buf[(j1 * RA + r) * R + j1 + row1] = v[r]; }
+        }
+        __syncthreads();
+        if (j2 < RA) {
+#pragma unroll
+            for (int r = 0; r < RB; r++) { v[r] = buf[(j2 + r * RA) * R + r + row2]; }
+#pragma unroll
+            for (int r = 1; r < RB; r++) { v[r] = cmul(v[r], tw[r]); }
+            Dft<RB>::run(v);
+            const int frame = frameBase + (tile >> (logN1 - 4));
+            const int r0 = (tile & (tilesPerFrame - 1)) << 4;
+            const size_t k0 = (size_t)frame * N + ((size_t)j2 << logN1) + r0 + row2;
+            const size_t kStep = (size_t)RA << logN1;
+            if (outDb) {
+                float* o = outDb + k0;
+#pragma unroll
+                for (int r = 0; r < RB; r++) { *o = powerDb(v[r], invN); o += kStep; }
+            }
+            if (outSpec) {
+                float2* o = reinterpret_cast<float2*>(outSpec) + k0;
+#pragma unroll
+                for (int r = 0; r < RB; r++) { *o = v[r]; o += kStep; }
+            }
+        }
+    }
+}
+
+template <int RA, int RB>
+int launchCols(int nf, int N2, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, int logN2, const float2* twN1,
+               const float2* twLo, const float2* twHi, int logS, cf32* scratch, int scratchFrames) {
+    constexpr int L = RA * RB;
+    const size_t smem = (size_t)2 * L * 16 * sizeof(float2);
+    B200_CUDA(cudaFuncSetAttribute(fftColsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // persistent grid: a whole number of column-block sets, about three CTAs per SM
+    const int blocksPerFrame = N2 >> 4;
+    const int ctasPerSm = 512 / (16 * TwoStage<RA, RB>::TPC);
+    int sets = std::max(1, (148 * ctasPerSm) / blocksPerFrame);
+    sets = std::min(sets, nf);
+    fftColsKernel<RA, RB><<<sets * blocksPerFrame, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(frames, nf, win, nz, logN2, twN1, twLo, twHi, logS,
+                                                                                     scratch, scratchFrames);
+    return B200_OK;
+}
+template <int RA, int RB>
+int launchRows(int nf, int N1, cudaStream_t s, int logN1, const float2* twN2, const cf32* scratch, int frameBase, float* outDb, cf32* outSpec) {
+    constexpr int L = RA * RB;
+    constexpr int BUF = (L * 16 + RB + 2) & ~1;
+    const size_t smem = (size_t)2 * BUF * sizeof(float2);
+    B200_CUDA(cudaFuncSetAttribute(fftRowsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int nTiles = nf * (N1 >> 4);
+    const int ctasPerSm = 512 / (16 * TwoStage<RA, RB>::TPC);
+    const int grid = std::min(nTiles, 148 * ctasPerSm);
+    fftRowsKernel<RA, RB><<<grid, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(logN1, nTiles, twN2, scratch, frameBase, outDb, outSpec);
+    return B200_OK;
+}
+
 int uploadTwiddles(float2** d, int count, int N, int stride) {
     std::vector<float2> h((size_t)std::max(count, 1));
     for (int j = 0; j < count; j++) {
@@ -372,8 +590,8 @@ void FftPlan::destroy() {
 
 int FftPlan::ensureScratch(int frames) {
     if (N1 == 1) { return B200_OK; }
-    // keep the ring small enough to stay in L2 (~126 MB): at most 32 MB of intermediates
-    int want = (int)std::max<size_t>(1, std::min<size_t>((size_t)frames, (32u << 20) / ((size_t)N * sizeof(cf32))));
+    // at most 256 MB of intermediates per launch pair (measured: one long persistent launch beats several L2-sized ones)
+    int want = (int)std::max<size_t>(1, std::min<size_t>((size_t)frames, ((size_t)256 << 20) / ((size_t)N * sizeof(cf32))));
     if (want <= scratchFrames) { return B200_OK; }
     if (dScratch) { cudaFree(dScratch); dScratch = nullptr; }
     B200_CUDA(cudaMalloc((void**)&dScratch, (size_t)want * N * sizeof(cf32)));
@@ -393,6 +611,26 @@ int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, in
     }
     B200_TRY(ensureScratch(nFrames));
     const int logN1 = log2i(N1), logN2 = log2i(N2);
+    if (logN1 >= 6 && logN1 <= 8 && logN2 >= 6 && logN2 <= 8) {
+        // register-resident passes (64 = 8x8, 128 = 16x8, 256 = 16x16)
+        for (int f0 = 0; f0 < nFrames; f0 += scratchFrames) {
+            const int nf = std::min(scratchFrames, nFrames - f0);
+            switch (logN1) {
+            case 6: B200_TRY((launchCols<8, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            case 7: B200_TRY((launchCols<16, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            default: B200_TRY((launchCols<16, 16>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            }
+            B200_CHECK_LAUNCH();
+            switch (logN2) {
+            case 6: B200_TRY((launchRows<8, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            case 7: B200_TRY((launchRows<16, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            default: B200_TRY((launchRows<16, 16>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            }
+            B200_CHECK_LAUNCH();
+            countLaunch(2);
+        }
+        return B200_OK;
+    }
     const int extra1 = N1 + S + (N >> logS), extra2 = N2;      // twiddle tables staged in shared memory
     const int logC = pickBatchLog(N1, 4, extra1);      // up to 16 columns: 128-byte global segments
     const int logR = pickBatchLog(N2, 5, extra2);      // up to 32 rows: 128-byte dB segments

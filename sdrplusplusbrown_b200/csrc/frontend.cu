@@ -263,7 +263,13 @@ int FrontEnd::init() {
     if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
     effectiveSr = sampleRate / decimRatio;
     B200_TRY(ring.init(64 * 1024));
-    B200_CUDA(cudaStreamCreateWithFlags(&fftStream, cudaStreamNonBlocking));
+    {
+        int lo = 0, hi = 0;
+        B200_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        const char* e = getenv("B200_FFT_PRIORITY");     // EXPERIMENT
+        const int prio = (e && atoi(e)) ? hi : lo;
+        B200_CUDA(cudaStreamCreateWithPriority(&fftStream, cudaStreamNonBlocking, prio));
+    }
     B200_CUDA(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
     B200_CUDA(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
     B200_TRY(rebuildDecim());
