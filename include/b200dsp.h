@@ -205,7 +205,13 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index o
 /* Host-buffer variant (the drop-in path of include/dsp/iq_frontend.h): H2D of the block, then D2H
  * of `h_frames` (frame_count x fft_size floats, may be NULL) and each VFO's output (h_vfo_out[v],
  * may be NULL) / audio (h_audio[v], may be NULL; b200_vfo_audio_count(v) stereo samples, size it with
- * b200_vfo_audio_max_out).  Blocks until done. */
+ * b200_vfo_audio_max_out).  Blocks until done.
+ * Blocks of 2^22 samples or more (without decimation / DC blocking / IQ inversion) are cut into 2^21-sample chunks:
+ * the copy of the following chunks runs behind the kernels of the current one and the results travel back over the
+ * other PCIe direction meanwhile (give pinned host buffers, b200_host_alloc, for that to overlap).  All dB rows of
+ * the block stay resident (frame_count / frame_ptr / frame_index cover the whole block); the per-VFO device
+ * accessors (b200_vfo_out_ptr / out_count / audio_ptr) then describe the last chunk only -- use the host buffers and
+ * vfo_counts, which always cover the whole block. */
 int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
                                float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
 

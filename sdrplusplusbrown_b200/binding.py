@@ -295,7 +295,7 @@ class FrontEnd:
         frames = np.empty((max_frames, self.fft_size), np.float32) if max_frames else None
         nslots = (max(list(vfos) + list(audio)) + 1) if (vfos or audio) else 0
         obufs = {v: np.empty(self.vfos.max_out(v, len(x)), np.complex64) for v in vfos}
-        abufs = {v: np.empty((self.vfos.max_out(v, len(x)), 2), np.float32) for v in audio}
+        abufs = {v: np.empty((self.vfos.audio_max_out(v, len(x)), 2), np.float32) for v in audio}
         optrs = (_vp * max(nslots, 1))()
         aptrs = (_vp * max(nslots, 1))()
         for v in vfos:
@@ -307,7 +307,7 @@ class FrontEnd:
                                             optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
         nf = self.frame_count()
         return dict(frames=frames[:min(nf, max_frames)] if max_frames else None, n_frames=nf,
-                    vfo={v: obufs[v][:counts[v]] for v in vfos}, audio={v: abufs[v][:counts[v]] for v in audio})
+                    vfo={v: obufs[v][:counts[v]] for v in vfos}, audio={v: abufs[v] for v in audio})
 
 
 class Waterfall:

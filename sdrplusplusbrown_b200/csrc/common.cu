@@ -53,6 +53,33 @@ int PinnedRing::acquire(size_t nbytes, void** hostPtr, int* slot) {
     return B200_OK;
 }
 
+namespace {
+struct DescBlob { uint4 q[248]; };     // 3968 bytes: with the two scalars the launch stays under the 4 KB parameter limit
+__global__ void __launch_bounds__(256) putDescKernel(const __grid_constant__ DescBlob blob, uint4* __restrict__ dst, int n16) {
+    if ((int)threadIdx.x < n16) { dst[threadIdx.x] = blob.q[threadIdx.x]; }
+}
+} // namespace
+
+int uploadDesc(void* dDst, const void* hSrc, size_t bytes, cudaStream_t s, bool viaParams) {
+    if (bytes == 0) { return B200_OK; }
+    if (!viaParams || bytes > 16 * sizeof(DescBlob)) {
+        B200_CUDA(cudaMemcpyAsync(dDst, hSrc, bytes, cudaMemcpyHostToDevice, s));
+        return B200_OK;
+    }
+    // descriptor buffers are allocated with slack and the ring slots are larger than any upload, so rounding the
+    // length up to 16 bytes stays inside both
+    const unsigned char* src = (const unsigned char*)hSrc;
+    unsigned char* dst = (unsigned char*)dDst;
+    for (size_t off = 0; off < bytes; off += sizeof(DescBlob)) {
+        const size_t n = std::min(sizeof(DescBlob), bytes - off);
+        DescBlob blob;
+        memcpy(&blob, src + off, n);
+        putDescKernel<<<1, 256, 0, s>>>(blob, (uint4*)(dst + off), (int)((n + 15) / 16));
+        B200_CHECK_LAUNCH();
+    }
+    return B200_OK;
+}
+
 int PinnedRing::release(int slot, cudaStream_t s) {
     B200_CUDA(cudaEventRecord(done[slot], s));
     used[slot] = true;

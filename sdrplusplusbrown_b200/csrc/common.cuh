@@ -68,4 +68,10 @@ struct PinnedRing {
     int release(int slot, cudaStream_t s);   // record the slot's event after the H2D copy was enqueued
 };
 
+// Small host -> device transfer of per-call descriptors.  viaParams = false: cudaMemcpyAsync from the pinned slot.
+// viaParams = true: the bytes ride in the parameter block of a tiny kernel that stores them (several launches for
+// more than 3.9 KB), so the transfer goes through the stream's command buffer instead of the copy engine -- the
+// pipelined host path uses this while the copy engine is busy with the block copies queued ahead.
+int uploadDesc(void* dDst, const void* hSrc, size_t bytes, cudaStream_t s, bool viaParams);
+
 } // namespace b200

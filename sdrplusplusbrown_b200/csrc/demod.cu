@@ -711,8 +711,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         bank.dDemodDescBytes = off * 2;
         B200_CUDA(cudaMalloc(&bank.dDemodDesc, bank.dDemodDescBytes));
     }
-    B200_CUDA(cudaMemcpyAsync(bank.dDemodDesc, h, off, cudaMemcpyHostToDevice, s));
-    B200_TRY(bank.ring.release(slot, s));
+    B200_TRY(uploadDesc(bank.dDemodDesc, h, off, s, bank.descViaParams));
     char* dd = (char*)bank.dDemodDesc;
     if (!quad.empty()) {
         quadratureKernel<<<dim3((maxN + 255) / 256, (unsigned)quad.size()), 256, 0, s>>>((const DemodJob*)(dd + oQ));
@@ -735,9 +734,9 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         B200_CHECK_LAUNCH(); countLaunch();
     }
     if (!firs.empty()) {
-        int maxOut = 0, maxH = 0, maxSpan = 0;
-        for (auto& f : firs) { maxOut = std::max(maxOut, f.nOut); maxH = std::max(maxH, f.H); maxSpan = std::max(maxSpan, firJobSpan(f)); }
-        B200_TRY(launchFirJobs((const FirJob*)(dd + oF), (int)firs.size(), maxOut, 1, maxSpan, s));
+        int maxH = 0;
+        for (auto& f : firs) { maxH = std::max(maxH, f.H); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oF), firs.data(), (int)firs.size(), 1, s));
         B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oF), (int)firs.size(), maxH, s));
     }
     if (!all.empty()) {
@@ -745,15 +744,16 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         B200_CHECK_LAUNCH(); countLaunch();
     }
     for (size_t w = 0; w < afWaves.size(); w++) {
-        int maxOut = 0, maxH = 0, maxSpan = 0;
-        for (auto& f : afWaves[w]) { maxOut = std::max(maxOut, f.nOut); maxH = std::max(maxH, f.H); maxSpan = std::max(maxSpan, firJobSpan(f)); }
-        B200_TRY(launchFirJobs((const FirJob*)(dd + oW[w]), (int)afWaves[w].size(), maxOut, 2, maxSpan, s));
+        int maxH = 0;
+        for (auto& f : afWaves[w]) { maxH = std::max(maxH, f.H); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oW[w]), afWaves[w].data(), (int)afWaves[w].size(), 2, s));
         B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oW[w]), (int)afWaves[w].size(), maxH, s));
     }
     if (!deJobs.empty()) {
         deemphKernel<<<(unsigned)deJobs.size(), 64, 0, s>>>((const DeemphJob*)(dd + oD));
         B200_CHECK_LAUNCH(); countLaunch();
     }
+    B200_TRY(bank.ring.release(slot, s));   // after the last reader of the slot was enqueued
     return B200_OK;
 }
 

@@ -3,6 +3,16 @@
 // many independent jobs per launch (grid.y = job).  These serve the low-rate tail of every VFO
 // (stages 2.., resampler, channel filter), the front-end decimator and the demodulator filters;
 // the full-rate first stage has its own fused kernel (xlate_decim.cu).
+//
+// Three ways a CTA can work on a job (FirJob::plan, chosen on the host by firJobPlan):
+//   blocked   (DECIM_FIR, power-of-two decimation D <= 8): each thread owns 8 consecutive outputs.  A decimating FIR is
+//             the sum of D ordinary FIRs over the polyphase components x[D*m + v]; per component the thread slides an
+//             8-sample register window along the staged input, so one shared-memory load and one tap feed 16 FFMAs.
+//             Long filters are split over `plan` adjacent lanes (partial sums folded with shuffles) so that short
+//             blocks still fill the GPU.
+//   lanes     (POLYPHASE): 8 lanes per output; a bank row is read as 128-byte runs (one float4 per lane) instead of
+//             one row per thread, partial sums folded with three shuffles.
+//   simple    one output per thread; kept for shapes the other two do not cover.
 #include "fir_jobs.cuh"
 
 #include <algorithm>
@@ -11,48 +21,169 @@ namespace b200 {
 
 namespace {
 
-constexpr int kThreads = 128;               // one output per thread: even a 20 k-sample tail stage fills the 148 SMs
-constexpr int kOutPerCta = kThreads;
+constexpr int kThreads = 128;
+constexpr int kR = 8;                       // outputs per thread, blocked path
+constexpr int kPolyLanes = 8;               // lanes per output, polyphase path
+constexpr int kPolyOutPerCta = 128;         // outputs per CTA, polyphase path (8 rounds of 16)
+constexpr int kSimpleOutPerCta = kThreads;
+constexpr size_t kSmemCap = 160 * 1024;
 
 template <int EF> struct Elem;
 template <> struct Elem<2> {
     using T = float2;
     static __device__ __forceinline__ T zero() { return make_float2(0.f, 0.f); }
     static __device__ __forceinline__ void fma(T& a, float t, T x) { a.x = fmaf(t, x.x, a.x); a.y = fmaf(t, x.y, a.y); }
-    // shared-memory slot of window position p: one pad element per 16 keeps lanes that step by 1, 2, 4 or 8
-    // samples (the decimations of every non-fused stage) on distinct banks
+    static __device__ __forceinline__ void add(T& a, T b) { a.x += b.x; a.y += b.y; }
+    static __device__ __forceinline__ T shflXor(T a, int m) { return make_float2(__shfl_xor_sync(0xffffffffu, a.x, m), __shfl_xor_sync(0xffffffffu, a.y, m)); }
+    // shared-memory slot of window position p (simple path): one pad element per 16 keeps lanes that step by 1, 2, 4
+    // or 8 samples on distinct banks
     static __device__ __forceinline__ int slot(int p) { return p + (p >> 4); }
 };
 template <> struct Elem<1> {
     using T = float;
     static __device__ __forceinline__ T zero() { return 0.f; }
     static __device__ __forceinline__ void fma(T& a, float t, T x) { a = fmaf(t, x, a); }
+    static __device__ __forceinline__ void add(T& a, T b) { a += b; }
+    static __device__ __forceinline__ T shflXor(T a, int m) { return __shfl_xor_sync(0xffffffffu, a, m); }
     static __device__ __forceinline__ int slot(int p) { return p + (p >> 5); }
 };
 
-// sample at position p of the job's [hist | data] work buffer
+// sample at position p of the job's [hist | data] work buffer; zero beyond the end of the block (only ever multiplied
+// by padding taps or belonging to outputs that are not stored)
 template <int EF>
 __device__ __forceinline__ typename Elem<EF>::T loadPos(const FirJob& j, int p) {
     using T = typename Elem<EF>::T;
-    return (p < j.H) ? __ldg(reinterpret_cast<const T*>(j.hist) + p) : __ldg(reinterpret_cast<const T*>(j.data) + (p - j.H));
+    if (p < j.H) { return __ldg(reinterpret_cast<const T*>(j.hist) + p); }
+    if (p - j.H < j.nIn) { return __ldg(reinterpret_cast<const T*>(j.data) + (p - j.H)); }
+    return Elem<EF>::zero();
 }
 
-// One CTA = up to kOutPerCta consecutive outputs of one job.  The CTA's input window is staged in shared
-// memory (coalesced global reads, each sample reused T/D times); taps are read through the read-only path
-// (warp-uniform address -> broadcast) for FIR jobs and per-thread bank rows for the polyphase resampler.
+__device__ __forceinline__ int ilog2(int v) { return 31 - __clz(v); }
+
+// ---- blocked decimating FIR --------------------------------------------------------------------------------------
+// CTA tile: (kThreads / S) threads-groups x 8 outputs.  Window position p (relative to the tile's first sample) lives
+// in slot p + p / (8*D): one pad element per thread-group stride, so the lanes of a warp (8*D samples apart) hit
+// distinct banks.
 template <int EF>
-__global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restrict__ jobs, int smemElems) {
+__device__ __forceinline__ void blockedFir(const FirJob& j, typename Elem<EF>::T* win, int smemElems) {
     using E = Elem<EF>;
     using T = typename E::T;
-    extern __shared__ __align__(16) unsigned char smemRaw[];
-    T* win = reinterpret_cast<T*>(smemRaw);
-
-    const FirJob j = jobs[blockIdx.y];
-    const int k0 = blockIdx.x * kOutPerCta;
+    const int S = j.plan;
+    const int logS = ilog2(S), logD = ilog2(j.D);
+    const int opc = (kThreads >> logS) * kR;
+    const int k0 = blockIdx.x * opc;
     if (k0 >= j.nOut) { return; }
-    const int nk = min(kOutPerCta, j.nOut - k0);
-    const int k = threadIdx.x;
+    const int nk = min(opc, j.nOut - k0);
+    const int base = j.offset + k0 * j.D;
+    const int span = (nk - 1) * j.D + j.T + (kR - 1) * j.D;       // the last thread's window may run past its last output
+    const int sh = 3 + logD;
+    for (int i = threadIdx.x; i < span; i += kThreads) { win[i + (i >> sh)] = loadPos<EF>(j, base + i); }
+    __syncthreads();
+    const int grp = threadIdx.x >> logS, seg = threadIdx.x & (S - 1);
+    const int kt = grp * kR;                                       // first output of this thread within the tile
+    T acc[kR];
+#pragma unroll
+    for (int r = 0; r < kR; r++) { acc[r] = E::zero(); }
+    if (kt < nk) {
+        // sample (r + u) of polyphase component v sits at window position (kt + r + u) * D + v, i.e. slot
+        // grp * (8*D + 1) + v + i * D + (i >> 3) with i = r + u
+        const T* wbase = win + grp * ((kR << logD) + 1);
+        for (int v = 0; v < j.D; v++) {
+            const int nU = (j.T - v + j.D - 1) >> logD;            // taps v, v + D, v + 2D, ... < T
+            const int u0 = (seg * nU) >> logS, u1 = ((seg + 1) * nU) >> logS;
+            if (u1 <= u0) { continue; }
+            const T* wv = wbase + v;
+            const float* tp = j.taps + v + ((size_t)u0 << logD);
+            T xw[kR];
+#pragma unroll
+            for (int r = 0; r < kR - 1; r++) { const int i = u0 + r; xw[r] = wv[(i << logD) + (i >> 3)]; }
+            int u = u0;
+            for (; u + kR <= u1; u += kR) {
+#pragma unroll
+                for (int q = 0; q < kR; q++) {
+                    const int i = u + q + kR - 1;
+                    xw[(q + kR - 1) & (kR - 1)] = wv[(i << logD) + (i >> 3)];
+                    const float h = __ldg(tp + ((size_t)q << logD));
+#pragma unroll
+                    for (int r = 0; r < kR; r++) { E::fma(acc[r], h, xw[(q + r) & (kR - 1)]); }
+                }
+                tp += (size_t)kR << logD;
+            }
+            // remainder: rotate the window by hand so that xw[r] is again the sample of output r
+            for (; u < u1; u++) {
+                const int i = u + kR - 1;
+                xw[kR - 1] = wv[(i << logD) + (i >> 3)];
+                const float h = __ldg(tp);
+                tp += j.D;
+#pragma unroll
+                for (int r = 0; r < kR; r++) { E::fma(acc[r], h, xw[r]); }
+#pragma unroll
+                for (int r = 0; r < kR - 1; r++) { xw[r] = xw[r + 1]; }
+            }
+        }
+    }
+    // fold the tap segments (adjacent lanes)
+    for (int m = 1; m < S; m <<= 1) {
+#pragma unroll
+        for (int r = 0; r < kR; r++) { E::add(acc[r], E::shflXor(acc[r], m)); }
+    }
+    if (seg == 0 && kt < nk) {
+        T* out = reinterpret_cast<T*>(j.out) + k0 + kt;
+#pragma unroll
+        for (int r = 0; r < kR; r++) { if (kt + r < nk) { out[r] = acc[r]; } }
+    }
+}
 
+// ---- polyphase resampler, 8 lanes per output ----------------------------------------------------------------------
+// output k sits at offset + (phase0 + k*M)/L and uses bank row (phase0 + k*M) % L; rows are padded with zeros to a
+// multiple of 4 floats (rowStride) and 16-byte aligned.
+template <int EF>
+__device__ __forceinline__ void lanesPoly(const FirJob& j, typename Elem<EF>::T* win, int smemElems) {
+    using E = Elem<EF>;
+    using T = typename E::T;
+    const int k0 = blockIdx.x * kPolyOutPerCta;
+    if (k0 >= j.nOut) { return; }
+    const int nk = min(kPolyOutPerCta, j.nOut - k0);
+    const long long tot0 = (long long)j.phase0 + (long long)k0 * j.M;
+    const long long totL = (long long)j.phase0 + (long long)(k0 + nk - 1) * j.M;
+    const int base = j.offset + (int)(tot0 / j.L);
+    const unsigned rem0 = (unsigned)(tot0 % j.L);                 // per output: 32-bit arithmetic from here (128 * M < 2^31)
+    const int span = (int)(totL / j.L) - (int)(tot0 / j.L) + j.rowStride;
+    for (int i = threadIdx.x; i < span; i += kThreads) { win[E::slot(i)] = loadPos<EF>(j, base + i); }
+    __syncthreads();
+    const int q = threadIdx.x & (kPolyLanes - 1), g = threadIdx.x >> 3;
+    constexpr int kGroups = kThreads / kPolyLanes;
+    for (int kk = g; kk < kPolyOutPerCta; kk += kGroups) {          // same trip count for every lane of a warp
+        T acc = E::zero();
+        if (kk < nk) {
+            const unsigned total = rem0 + (unsigned)kk * (unsigned)j.M;
+            const unsigned adv = total / (unsigned)j.L;
+            const int p0 = (int)adv;
+            const float* row = j.taps + (size_t)(total - adv * (unsigned)j.L) * j.rowStride;
+            for (int t = 4 * q; t < j.rowStride; t += 4 * kPolyLanes) {
+                const float4 h = __ldg(reinterpret_cast<const float4*>(row + t));
+                E::fma(acc, h.x, win[E::slot(p0 + t)]);
+                E::fma(acc, h.y, win[E::slot(p0 + t + 1)]);
+                E::fma(acc, h.z, win[E::slot(p0 + t + 2)]);
+                E::fma(acc, h.w, win[E::slot(p0 + t + 3)]);
+            }
+        }
+        E::add(acc, E::shflXor(acc, 1));
+        E::add(acc, E::shflXor(acc, 2));
+        E::add(acc, E::shflXor(acc, 4));
+        if (q == 0 && kk < nk) { reinterpret_cast<T*>(j.out)[k0 + kk] = acc; }
+    }
+}
+
+// ---- one output per thread ----------------------------------------------------------------------------------------
+template <int EF>
+__device__ __forceinline__ void simpleJob(const FirJob& j, typename Elem<EF>::T* win, int smemElems) {
+    using E = Elem<EF>;
+    using T = typename E::T;
+    const int k0 = blockIdx.x * kSimpleOutPerCta;
+    if (k0 >= j.nOut) { return; }
+    const int nk = min(kSimpleOutPerCta, j.nOut - k0);
+    const int k = threadIdx.x;
     if (j.kind == JOB_DECIM_FIR) {
         const int base = j.offset + k0 * j.D;                 // first work-buffer position this CTA touches
         const int span = (nk - 1) * j.D + j.T;                // positions [base, base+span)
@@ -79,40 +210,26 @@ __global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restri
         }
         if (k < nk) { reinterpret_cast<T*>(j.out)[k0 + k] = acc; }
     }
-    else {
-        // polyphase: output k sits at offset + (phase0 + k*M)/L and uses bank row (phase0 + k*M) % L
-        const long long tot0 = (long long)j.phase0 + (long long)k0 * j.M;
-        const long long totL = (long long)j.phase0 + (long long)(k0 + nk - 1) * j.M;
-        const int base = j.offset + (int)(tot0 / j.L);
-        const int span = (int)(totL / j.L) - (int)(tot0 / j.L) + j.T;
-        const bool staged = E::slot(span) + 1 <= smemElems;
-        if (staged) {
-            for (int i = threadIdx.x; i < span; i += kThreads) { win[E::slot(i)] = loadPos<EF>(j, base + i); }
-            __syncthreads();
-        }
-        if (k < nk) {
-            const long long total = (long long)j.phase0 + (long long)(k0 + k) * j.M;
-            const int pos = j.offset + (int)(total / j.L);
-            const float* row = j.taps + (size_t)(total % j.L) * j.rowStride;
-            T acc = E::zero();
-            if (staged) {
-                const int p0 = pos - base;
-                int t = 0;
-                for (; t + 4 <= j.T; t += 4) {          // rows are padded to a multiple of 4 floats and 16-byte aligned
-                    const float4 h = __ldg(reinterpret_cast<const float4*>(row) + (t >> 2));
-                    E::fma(acc, h.x, win[E::slot(p0 + t)]);
-                    E::fma(acc, h.y, win[E::slot(p0 + t + 1)]);
-                    E::fma(acc, h.z, win[E::slot(p0 + t + 2)]);
-                    E::fma(acc, h.w, win[E::slot(p0 + t + 3)]);
-                }
-                for (; t < j.T; t++) { E::fma(acc, __ldg(row + t), win[E::slot(p0 + t)]); }
-            }
-            else {
-                for (int t = 0; t < j.T; t++) { E::fma(acc, __ldg(row + t), loadPos<EF>(j, pos + t)); }
-            }
-            reinterpret_cast<T*>(j.out)[k0 + k] = acc;
-        }
+    else if (k < nk) {
+        // polyphase without staging (a span that does not fit in shared memory)
+        const long long total = (long long)j.phase0 + (long long)(k0 + k) * j.M;
+        const int pos = j.offset + (int)(total / j.L);
+        const float* row = j.taps + (size_t)(total % j.L) * j.rowStride;
+        T acc = E::zero();
+        for (int t = 0; t < j.T; t++) { E::fma(acc, __ldg(row + t), loadPos<EF>(j, pos + t)); }
+        reinterpret_cast<T*>(j.out)[k0 + k] = acc;
     }
+}
+
+template <int EF>
+__global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restrict__ jobs, int smemElems) {
+    using T = typename Elem<EF>::T;
+    extern __shared__ __align__(16) unsigned char smemRaw[];
+    T* win = reinterpret_cast<T*>(smemRaw);
+    const FirJob j = jobs[blockIdx.y];
+    if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { blockedFir<EF>(j, win, smemElems); }
+    else if (j.plan > 0) { lanesPoly<EF>(j, win, smemElems); }
+    else { simpleJob<EF>(j, win, smemElems); }
 }
 
 // histNext[i] = workbuf[nIn + i], i < H  (the reference's memmove of the last taps-1 samples, fir.h:86-87)
@@ -129,28 +246,73 @@ __global__ void __launch_bounds__(256) historyUpdateKernel(const FirJob* __restr
     }
 }
 
-} // namespace
-
-// input window (in elements) a CTA of this job needs to stage
-int firJobSpan(const FirJob& j) {
-    if (j.kind == JOB_DECIM_FIR) { return (kOutPerCta - 1) * j.D + j.T; }
-    return (int)(((long long)kOutPerCta * j.M) / j.L) + j.T + 2;
+// ---- host-side geometry (must mirror the device code above)
+int outPerCta(const FirJob& j) {
+    if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { return (kThreads / j.plan) * kR; }
+    if (j.plan > 0) { return kPolyOutPerCta; }
+    return kSimpleOutPerCta;
 }
 
-int launchFirJobs(const FirJob* d_jobs, int nJobs, int maxOut, int elemFloats, int maxSpanElems, cudaStream_t s) {
-    if (nJobs <= 0 || maxOut <= 0) { return B200_OK; }
-    dim3 grid((maxOut + kOutPerCta - 1) / kOutPerCta, nJobs);
-    // request only what the widest job of this launch needs (more resident CTAs per SM); jobs whose window
-    // would not fit in 160 KB read through L1 instead
+// shared-memory elements one CTA of this job wants (0 = reads through L1)
+size_t smemElemsFor(const FirJob& j) {
+    if (j.plan > 0 && j.kind == JOB_DECIM_FIR) {
+        const size_t span = (size_t)outPerCta(j) * j.D + j.T + (size_t)kR * j.D;
+        return span + span / ((size_t)kR * j.D) + 2;
+    }
+    if (j.plan > 0) {
+        const size_t span = (size_t)(((long long)kPolyOutPerCta * j.M) / j.L) + j.rowStride + 2;
+        return span + (span >> 4) + 2;
+    }
+    const size_t span = (j.kind == JOB_DECIM_FIR) ? (size_t)(kSimpleOutPerCta - 1) * j.D + j.T : 0;
+    return span + (span >> 4) + 8;
+}
+
+} // namespace
+
+void firJobPlan(FirJob& j) {
+    j.plan = 0;
+    const size_t elemBytes = (size_t)j.elemFloats * sizeof(float);
+    if (j.kind == JOB_DECIM_FIR) {
+        if (j.D < 1 || j.D > 8 || (j.D & (j.D - 1)) != 0) { return; }
+        // split the taps of each polyphase component over S lanes while that leaves at least 8 taps per lane and the
+        // launch has fewer than ~4 warps per scheduler
+        const int nU = j.T / j.D;
+        if (nU < kR) { return; }        // fewer taps per component than the register window: no reuse to gain
+        int S = 1;
+        while (S < 16 && (long long)(j.nOut / kR + 1) * S < 148LL * 512 && nU / (2 * S) >= 8) { S *= 2; }
+        j.plan = S;
+        if (smemElemsFor(j) * elemBytes > kSmemCap) { j.plan = 0; }
+    }
+    else {
+        if (j.rowStride % 4 != 0 || (long long)j.L + (long long)kPolyOutPerCta * j.M >= (1LL << 31)) { return; }
+        j.plan = kPolyLanes;
+        if (smemElemsFor(j) * elemBytes > kSmemCap) { j.plan = 0; }
+    }
+}
+
+int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s) {
+    if (nJobs <= 0) { return B200_OK; }
+    int tiles = 0;
+    size_t elems = 0;
+    for (int i = 0; i < nJobs; i++) {
+        const FirJob& j = h_jobs[i];
+        if (j.nOut <= 0) { continue; }
+        const int opc = outPerCta(j);
+        tiles = std::max(tiles, (j.nOut + opc - 1) / opc);
+        elems = std::max(elems, smemElemsFor(j));
+    }
+    if (tiles == 0) { return B200_OK; }
+    // request only what the widest job of this launch needs (more resident CTAs per SM); simple-path jobs whose window
+    // would not fit read through L1 instead
     const size_t elemBytes = (size_t)elemFloats * sizeof(float);
-    size_t want = ((size_t)maxSpanElems + (maxSpanElems >> 4) + 8) * elemBytes;
-    const size_t smemBytes = std::min<size_t>(std::max<size_t>(want, 1024), 160 * 1024);
+    const size_t smemBytes = std::min<size_t>(std::max<size_t>(elems * elemBytes, 1024), kSmemCap);
+    dim3 grid(tiles, nJobs);
     if (elemFloats == 2) {
-        B200_CUDA(cudaFuncSetAttribute(firJobsKernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(160 * 1024)));
+        B200_CUDA(cudaFuncSetAttribute(firJobsKernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap));
         firJobsKernel<2><<<grid, kThreads, smemBytes, s>>>(d_jobs, (int)(smemBytes / elemBytes));
     }
     else {
-        B200_CUDA(cudaFuncSetAttribute(firJobsKernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(160 * 1024)));
+        B200_CUDA(cudaFuncSetAttribute(firJobsKernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemCap));
         firJobsKernel<1><<<grid, kThreads, smemBytes, s>>>(d_jobs, (int)(smemBytes / elemBytes));
     }
     B200_CHECK_LAUNCH();

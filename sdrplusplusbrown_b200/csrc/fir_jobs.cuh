@@ -27,13 +27,17 @@ struct FirJob {
     int kind;
     int L, M, phase0, rowStride;   // POLYPHASE only
     int elemFloats;        // 2 = complex samples, 1 = real samples
-    int pad;
+    int plan;              // how a CTA works on this job (firJobPlan): 0 = one output per thread;
+                           // DECIM_FIR > 0: 8 outputs per thread, taps split over `plan` adjacent lanes;
+                           // POLYPHASE > 0: `plan` (= 8) lanes per output
 };
 
+// chooses FirJob::plan from the job's shape (host side, called by Stage::fillJob)
+void firJobPlan(FirJob& j);
+
 // Launchers (all jobs of one "level" in a single launch; grid.y = job index)
-// every job of a launch must have the same elemFloats
-int firJobSpan(const FirJob& j);   // elements of input window one CTA stages for this job
-int launchFirJobs(const FirJob* d_jobs, int nJobs, int maxOut, int elemFloats, int maxSpanElems, cudaStream_t s);
+// every job of a launch must have the same elemFloats; h_jobs is the host copy of d_jobs (grid and shared-memory sizing)
+int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s);
 int launchHistoryUpdate(const FirJob* d_jobs, int nJobs, int maxH, cudaStream_t s);
 
 } // namespace b200

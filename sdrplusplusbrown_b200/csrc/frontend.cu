@@ -205,6 +205,9 @@ struct FrontEnd {
     int shardRank = 0, shardWorld = 1;
     // host staging
     cf32* dStageIn = nullptr;
+    cudaStream_t hostCopyStream = nullptr;      // H2D of the next chunks while the current one is processed
+    std::vector<cudaEvent_t> hostCopyDone;
+    cudaEvent_t evHostStart = nullptr;
 
     int init();
     void destroy();
@@ -212,8 +215,8 @@ struct FrontEnd {
     int rebuildDecim();
     int updateFftPath();
     int preprocess(const cf32* dIn, int count, cudaStream_t s);
-    int fftBranch(cudaStream_t s);
-    int process(const cf32* dIn, int count, cudaStream_t s);
+    int fftBranch(cudaStream_t s, bool append);
+    int process(const cf32* dIn, int count, cudaStream_t s, bool append = false);   // append: keep the rows of the previous call(s)
 };
 
 int FrontEnd::rebuildDecim() {
@@ -253,7 +256,7 @@ int FrontEnd::updateFftPath() {
     B200_CUDA(cudaMalloc((void**)&dRows, (size_t)rowsCap * fftSize * sizeof(float)));
     if (dFrameDesc) { cudaFree(dFrameDesc); dFrameDesc = nullptr; }
     frameDescCap = maxFrames;
-    B200_CUDA(cudaMalloc((void**)&dFrameDesc, (size_t)frameDescCap * sizeof(FrameDesc)));
+    B200_CUDA(cudaMalloc((void**)&dFrameDesc, (size_t)frameDescCap * sizeof(FrameDesc) + 16));
     frameIdx.clear();
     return B200_OK;
 }
@@ -263,13 +266,7 @@ int FrontEnd::init() {
     if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
     effectiveSr = sampleRate / decimRatio;
     B200_TRY(ring.init(64 * 1024));
-    {
-        int lo = 0, hi = 0;
-        B200_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-        const char* e = getenv("B200_FFT_PRIORITY");     // EXPERIMENT
-        const int prio = (e && atoi(e)) ? hi : lo;
-        B200_CUDA(cudaStreamCreateWithPriority(&fftStream, cudaStreamNonBlocking, prio));
-    }
+    B200_CUDA(cudaStreamCreateWithFlags(&fftStream, cudaStreamNonBlocking));
     B200_CUDA(cudaEventCreateWithFlags(&evFork, cudaEventDisableTiming));
     B200_CUDA(cudaEventCreateWithFlags(&evJoin, cudaEventDisableTiming));
     B200_TRY(rebuildDecim());
@@ -287,6 +284,10 @@ void FrontEnd::destroy() {
     if (fftStream) { cudaStreamSynchronize(fftStream); cudaStreamDestroy(fftStream); fftStream = nullptr; }
     if (evFork) { cudaEventDestroy(evFork); evFork = nullptr; }
     if (evJoin) { cudaEventDestroy(evJoin); evJoin = nullptr; }
+    if (hostCopyStream) { cudaStreamSynchronize(hostCopyStream); cudaStreamDestroy(hostCopyStream); hostCopyStream = nullptr; }
+    for (auto e : hostCopyDone) { cudaEventDestroy(e); }
+    hostCopyDone.clear();
+    if (evHostStart) { cudaEventDestroy(evHostStart); evHostStart = nullptr; }
     if (bank) { bank->impl.destroy(); delete bank; bank = nullptr; }
     for (auto& st : decimStages) { st.destroy(); }
     decimStages.clear();
@@ -318,7 +319,7 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(ring.release(slot, s));
         int maxH = 0;
         for (size_t i = 0; i < jobs.size(); i++) {
-            B200_TRY(launchFirJobs((const FirJob*)dJobDesc + i, 1, jobs[i].nOut, 2, firJobSpan(jobs[i]), s));
+            B200_TRY(launchFirJobs((const FirJob*)dJobDesc + i, &jobs[i], 1, 2, s));
             maxH = std::max(maxH, jobs[i].H);
         }
         B200_TRY(launchHistoryUpdate((const FirJob*)dJobDesc, (int)jobs.size(), maxH, s));
@@ -372,8 +373,9 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
 }
 
 // Reshaper framing (buffer/reshaper.h:101-128 with skip >= 0): frame f = samples [f*I, f*I + nz)
-int FrontEnd::fftBranch(cudaStream_t s) {
-    frameIdx.clear();
+int FrontEnd::fftBranch(cudaStream_t s, bool append) {
+    if (!append) { frameIdx.clear(); }
+    const size_t rowBase = frameIdx.size();
     const int64_t A = streamPos, E = streamPos + preCount;
     std::vector<FrameDesc> descs;
     // a frame that ends beyond this block is stashed in the carry buffer, but only after this call's FFT
@@ -404,14 +406,14 @@ int FrontEnd::fftBranch(cudaStream_t s) {
     streamPos = E;
     int rc = B200_OK;
     if (!descs.empty()) {
-        if ((int)descs.size() > rowsCap) { setError("internal: %d frames exceed row capacity %d", (int)descs.size(), rowsCap); return B200_ESTATE; }
+        if ((int)(rowBase + descs.size()) > rowsCap) { setError("internal: %d frames exceed row capacity %d", (int)(rowBase + descs.size()), rowsCap); return B200_ESTATE; }
         void* hp = nullptr; int slot = 0;
         const size_t bytes = descs.size() * sizeof(FrameDesc);
         B200_TRY(ring.acquire(bytes, &hp, &slot));
         memcpy(hp, descs.data(), bytes);
-        B200_CUDA(cudaMemcpyAsync(dFrameDesc, hp, bytes, cudaMemcpyHostToDevice, s));
+        B200_TRY(uploadDesc(dFrameDesc, hp, bytes, s, bank->impl.descViaParams));
+        rc = plan.run(dFrameDesc, (int)descs.size(), dWindow, nz, dRows + rowBase * (size_t)fftSize, nullptr, s);
         B200_TRY(ring.release(slot, s));
-        rc = plan.run(dFrameDesc, (int)descs.size(), dWindow, nz, dRows, nullptr, s);
     }
     if (rc == B200_OK && stashLen > 0) {
         B200_CUDA(cudaMemcpyAsync(dCarry + stashAt, stashSrc, (size_t)stashLen * sizeof(cf32), cudaMemcpyDeviceToDevice, s));
@@ -419,7 +421,7 @@ int FrontEnd::fftBranch(cudaStream_t s) {
     return rc;
 }
 
-int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s) {
+int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s, bool append) {
     if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
     DeviceGuard g(device);
     if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
@@ -429,13 +431,13 @@ int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s) {
     if (fork) {
         B200_CUDA(cudaEventRecord(evFork, s));
         B200_CUDA(cudaStreamWaitEvent(fftStream, evFork, 0));
-        B200_TRY(fftBranch(fftStream));
+        B200_TRY(fftBranch(fftStream, append));
         B200_CUDA(cudaEventRecord(evJoin, fftStream));
         B200_TRY(bank->impl.process(preOut, preCount, s));
         B200_CUDA(cudaStreamWaitEvent(s, evJoin, 0));
     }
     else {
-        B200_TRY(fftBranch(s));
+        B200_TRY(fftBranch(s, append));
     }
     return B200_OK;
 }
@@ -575,6 +577,33 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i) {
     return fe->impl.frameIdx[i];
 }
 
+// D2H of what the last f.process() call produced; host buffers are filled from `framesDone` / `done[v]` on
+static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& framesDone, float* const* h_vfo_out, float* const* h_audio,
+                       std::vector<int>& done, std::vector<int>& audioDone, cudaStream_t s) {
+    const int total = std::min((int)f.frameIdx.size(), max_frames);
+    if (h_frames && total > framesDone) {
+        B200_CUDA(cudaMemcpyAsync(h_frames + (size_t)framesDone * f.fftSize, f.dRows + (size_t)framesDone * f.fftSize,
+                                  (size_t)(total - framesDone) * f.fftSize * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    framesDone = std::max(framesDone, total);
+    VfoBank& b = f.bank->impl;
+    for (size_t i = 0; i < b.vfos.size(); i++) {
+        const Vfo& v = b.vfos[i];
+        if (!v.live) { continue; }
+        if (v.lastOut > 0 && h_vfo_out && h_vfo_out[i]) {
+            B200_CUDA(cudaMemcpyAsync(h_vfo_out[i] + 2 * (size_t)done[i], v.lastOutPtr, (size_t)v.lastOut * sizeof(cf32), cudaMemcpyDeviceToHost, s));
+        }
+        done[i] += v.lastOut;
+        if (h_audio && h_audio[i]) {
+            const float* ap = b200_vfo_audio_ptr(f.bank, (int)i);
+            const int an = ap ? b200_vfo_audio_count(f.bank, (int)i) : 0;   // differs from lastOut behind an audio resampler
+            if (an > 0) { B200_CUDA(cudaMemcpyAsync(h_audio[i] + 2 * (size_t)audioDone[i], ap, (size_t)an * 2 * sizeof(float), cudaMemcpyDeviceToHost, s)); }
+            audioDone[i] += an;
+        }
+    }
+    return B200_OK;
+}
+
 int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
                                float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
     FE_OR_FAIL(fe);
@@ -584,27 +613,54 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
     DeviceGuard g(f.device);
     cudaStream_t s = (cudaStream_t)stream;
     if (!f.dStageIn) { B200_CUDA(cudaMalloc((void**)&f.dStageIn, (size_t)f.maxBlock * sizeof(cf32))); }
-    B200_CUDA(cudaMemcpyAsync(f.dStageIn, h_in, (size_t)count * sizeof(cf32), cudaMemcpyHostToDevice, s));
-    B200_TRY(f.process(f.dStageIn, count, s));
-    const int nf = std::min((int)f.frameIdx.size(), max_frames);
-    if (h_frames && nf > 0) {
-        B200_CUDA(cudaMemcpyAsync(h_frames, f.dRows, (size_t)nf * f.fftSize * sizeof(float), cudaMemcpyDeviceToHost, s));
-    }
     VfoBank& b = f.bank->impl;
-    for (size_t i = 0; i < b.vfos.size(); i++) {
-        const Vfo& v = b.vfos[i];
-        if (!v.live) { continue; }
-        if (vfo_counts) { vfo_counts[i] = v.lastOut; }
-        if (v.lastOut <= 0) { continue; }
-        if (h_vfo_out && h_vfo_out[i]) {
-            B200_CUDA(cudaMemcpyAsync(h_vfo_out[i], v.lastOutPtr, (size_t)v.lastOut * sizeof(cf32), cudaMemcpyDeviceToHost, s));
+    std::vector<int> done(b.vfos.size(), 0), audioDone(b.vfos.size(), 0);
+    int framesDone = 0;
+    // A long block is cut into chunks: the copy engine brings chunk k+1 (and the ones behind it) in while chunk k is
+    // processed and its results go back over the other PCIe direction.  The stages are streaming (results do not
+    // depend on how a block is cut), and the dB rows of all chunks stay in the row buffer.  Only without
+    // pre-processing, so that b200_frontend_preproc_out still names the whole block afterwards.
+    constexpr int kChunk = 1 << 21;
+    const bool plain = f.decimRatio == 1 && !f.dcBlocking && !f.invertIQ;
+    if (plain && count >= 2 * kChunk) {
+        const int nChunks = (count + kChunk - 1) / kChunk;
+        if (!f.hostCopyStream) {
+            B200_CUDA(cudaStreamCreateWithFlags(&f.hostCopyStream, cudaStreamNonBlocking));
+            B200_CUDA(cudaEventCreateWithFlags(&f.evHostStart, cudaEventDisableTiming));
         }
-        if (h_audio && h_audio[i]) {
-            const float* ap = b200_vfo_audio_ptr(f.bank, (int)i);
-            const int an = ap ? b200_vfo_audio_count(f.bank, (int)i) : 0;   // differs from lastOut behind an audio resampler
-            if (an > 0) { B200_CUDA(cudaMemcpyAsync(h_audio[i], ap, (size_t)an * 2 * sizeof(float), cudaMemcpyDeviceToHost, s)); }
+        while ((int)f.hostCopyDone.size() < nChunks) {
+            cudaEvent_t e;
+            B200_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            f.hostCopyDone.push_back(e);
         }
+        // the staging buffer may still be read by work already queued on s
+        B200_CUDA(cudaEventRecord(f.evHostStart, s));
+        B200_CUDA(cudaStreamWaitEvent(f.hostCopyStream, f.evHostStart, 0));
+        for (int c = 0; c < nChunks; c++) {
+            const size_t off = (size_t)c * kChunk;
+            const int n = (int)std::min<size_t>(kChunk, (size_t)count - off);
+            B200_CUDA(cudaMemcpyAsync(f.dStageIn + off, h_in + 2 * off, (size_t)n * sizeof(cf32), cudaMemcpyHostToDevice, f.hostCopyStream));
+            B200_CUDA(cudaEventRecord(f.hostCopyDone[c], f.hostCopyStream));
+        }
+        b.descViaParams = true;
+        int rc = B200_OK;
+        for (int c = 0; c < nChunks && rc == B200_OK; c++) {
+            const size_t off = (size_t)c * kChunk;
+            const int n = (int)std::min<size_t>(kChunk, (size_t)count - off);
+            if (cudaStreamWaitEvent(s, f.hostCopyDone[c], 0) != cudaSuccess) { setError("cudaStreamWaitEvent failed"); rc = B200_ECUDA; break; }
+            rc = f.process(f.dStageIn + off, n, s, c > 0);
+            if (rc == B200_OK) { rc = copyOutputs(f, h_frames, max_frames, framesDone, h_vfo_out, h_audio, done, audioDone, s); }
+        }
+        b.descViaParams = false;
+        if (rc != B200_OK) { cudaStreamSynchronize(f.hostCopyStream); return rc; }
+        f.preOut = f.dStageIn; f.preCount = count;
     }
+    else {
+        B200_CUDA(cudaMemcpyAsync(f.dStageIn, h_in, (size_t)count * sizeof(cf32), cudaMemcpyHostToDevice, s));
+        B200_TRY(f.process(f.dStageIn, count, s));
+        B200_TRY(copyOutputs(f, h_frames, max_frames, framesDone, h_vfo_out, h_audio, done, audioDone, s));
+    }
+    if (vfo_counts) { for (size_t i = 0; i < b.vfos.size(); i++) { if (b.vfos[i].live) { vfo_counts[i] = done[i]; } } }
     B200_CUDA(cudaStreamSynchronize(s));
     return B200_OK;
 }

@@ -104,7 +104,8 @@ void Stage::fillJob(FirJob& j, const void* data, int nIn) const {
     j.data = data; j.out = dOut; j.taps = dTaps;
     j.H = H; j.T = T; j.D = D; j.offset = offset; j.nIn = nIn; j.nOut = outCountFor(nIn);
     j.kind = kind; j.L = L; j.M = M; j.phase0 = phase; j.rowStride = rowStride;
-    j.elemFloats = elemFloats; j.pad = 0;
+    j.elemFloats = elemFloats; j.plan = 0;
+    firJobPlan(j);
 }
 
 // ------------------------------------------------------------------ bank
@@ -440,7 +441,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         dDescBytes = descBytes * 2;
         B200_CUDA(cudaMalloc(&dDesc, dDescBytes));
     }
-    B200_CUDA(cudaMemcpyAsync(dDesc, h, descBytes, cudaMemcpyHostToDevice, s));
+    B200_TRY(uploadDesc(dDesc, h, descBytes, s, descViaParams));
     for (Vfo* v : dirtyTables) {
         float2* tab = (float2*)(h + off);
         makeRotatorTable(v->dRe, v->dIm, tab);
@@ -448,7 +449,6 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_CUDA(cudaMemcpyAsync(v->dWtab, tab, kRotChunk * sizeof(float2), cudaMemcpyHostToDevice, s));
         v->tableDirty = false;
     }
-    B200_TRY(ring.release(slot, s));
     char* d = (char*)dDesc;
 
     int maxH = 0;
@@ -458,9 +458,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
         for (size_t l = 0; l < levels.size(); l++) {
-            int maxOutL = 0, maxSpan = 0;
-            for (auto& j : levels[l]) { maxOutL = std::max(maxOutL, j.nOut); maxSpan = std::max(maxSpan, firJobSpan(j)); }
-            B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), (int)levels[l].size(), maxOutL, 2, maxSpan, s));
+            B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), levels[l].data(), (int)levels[l].size(), 2, s));
         }
     }
     else if (!fj.empty()) {
@@ -468,6 +466,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
     }
     B200_TRY(launchHistoryUpdate((const FirJob*)(d + oH), (int)histJobs.size(), maxH, s));
+    B200_TRY(ring.release(slot, s));      // after the last reader of the slot was enqueued
     B200_TRY(processDemods(*this, s));
     return B200_OK;
 }

@@ -82,6 +82,7 @@ struct VfoBank {
     void* dDemodDesc = nullptr; size_t dDemodDescBytes = 0;
     cudaStream_t lastStream = nullptr;
     bool everRan = false;
+    bool descViaParams = false;      // descriptor uploads avoid the copy engine (uploadDesc); set by the pipelined host path
     // per-call descriptors
     PinnedRing ring;
     void* dDesc = nullptr; size_t dDescBytes = 0;

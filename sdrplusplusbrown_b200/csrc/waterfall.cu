@@ -8,21 +8,35 @@
 namespace b200 {
 namespace {
 
+// G = lanes per output pixel (power of two <= 32, chosen from the widest pixel): the lanes of a group walk the pixel's
+// bins side by side, so a warp reads contiguous runs of the dB row, and fold their maxima with shuffles.
 __global__ void __launch_bounds__(256) zoomPaletteKernel(const float* __restrict__ rows, int rawSize, int width, const int* __restrict__ sid,
                                                          const int* __restrict__ uf, float wfMin, float wfMax, const uint32_t* __restrict__ lut,
-                                                         float* __restrict__ zoom, uint32_t* __restrict__ rgba) {
-    const int i = blockIdx.x * 256 + threadIdx.x;
-    if (i >= width) { return; }
+                                                         float* __restrict__ zoom, uint32_t* __restrict__ rgba, int logG) {
+    const int G = 1 << logG;
+    const int t = blockIdx.x * 256 + threadIdx.x;
+    const int pix = t >> logG, sub = t & (G - 1);
+    const bool live = pix < width;
+    const int i = live ? pix : width - 1;
     const float* row = rows + (size_t)blockIdx.y * rawSize;
-    const int s = sid[i], n = uf[i];
+    const int s = __ldg(sid + i), n = __ldg(uf + i);
     float m = -INFINITY;
-    for (int j = 0; j < n; j++) { m = fmaxf(m, __ldg(row + s + j)); }
+    // eight loads in flight per lane: the kernel is bound by memory latency, not by the maxima
+    for (int j = sub; j < n; j += 8 * G) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { v[u] = (j + u * G < n) ? __ldg(row + s + j + u * G) : -INFINITY; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) { m = fmaxf(m, v[u]); }
+    }
+    for (int o = G >> 1; o > 0; o >>= 1) { m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o)); }
+    if (!live || sub != 0) { return; }
     if (zoom) { zoom[(size_t)blockIdx.y * width + i] = m; }
     if (rgba) {
         const float range = wfMax - wfMin;
         const float px = (fminf(fmaxf(m, wfMin), wfMax) - wfMin) / range;
         const int id = (int)(px * 999.0f);
-        rgba[(size_t)blockIdx.y * width + i] = lut[id];
+        rgba[(size_t)blockIdx.y * width + i] = __ldg(lut + id);
     }
 }
 
@@ -113,6 +127,7 @@ struct b200_waterfall {
     int* dSid = nullptr; int* dUf = nullptr; uint32_t* dLut = nullptr;
     float* dSmooth = nullptr; float* dHold = nullptr;     // smoothingBuf / latestFFTHold, both start at -1000 (waterfall.cpp:1073,1090)
     bool tableDirty = true;
+    int maxUf = 1;            // widest pixel (bins), picks the lanes-per-pixel of the zoom kernel
 };
 
 extern "C" {
@@ -200,6 +215,8 @@ static int refreshTable(b200_waterfall* wf) {
         if (wf->sid[i] >= wf->rawSize) { wf->sid[i] = wf->rawSize - 1; wf->uf[i] = 0; }
         if (wf->uf[i] < 0) { wf->uf[i] = 0; }
     }
+    wf->maxUf = 1;
+    for (int i = 0; i < wf->width; i++) { wf->maxUf = std::max(wf->maxUf, wf->uf[i]); }
     B200_CUDA(cudaMemcpy(wf->dSid, wf->sid.data(), wf->width * sizeof(int), cudaMemcpyHostToDevice));
     B200_CUDA(cudaMemcpy(wf->dUf, wf->uf.data(), wf->width * sizeof(int), cudaMemcpyHostToDevice));
     wf->tableDirty = false;
@@ -211,8 +228,10 @@ int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, floa
     if (nrows == 0) { return B200_OK; }
     DeviceGuard g(wf->device);
     B200_TRY(refreshTable(wf));
-    dim3 grid((wf->width + 255) / 256, nrows);
-    zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba);
+    int logG = 0;
+    while (logG < 5 && (8 << logG) < wf->maxUf) { logG++; }          // up to eight bins per lane before adding lanes
+    dim3 grid((unsigned)((((size_t)wf->width << logG) + 255) / 256), nrows);
+    zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba, logG);
     B200_CHECK_LAUNCH();
     countLaunch();
     return B200_OK;

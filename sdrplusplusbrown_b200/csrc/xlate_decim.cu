@@ -91,7 +91,9 @@ template <int D, int TILE> struct TileCfg {
     // sub-blocks per CTA
     static constexpr int SB = (TILE / D) > 256 ? 256 : ((TILE / D) < 32 ? 32 : (TILE / D));
     // threads per sub-block: a sub-block of D samples is split into RS runs of DS = D/RS <= 32 samples, so that the
-    // shared-memory tile (8*D bytes per sub-block) does not cap the resident warps for the large-D plans
+    // shared-memory tile (8*D bytes per sub-block) does not cap the resident warps for the large-D plans.  (Measured
+    // with one VFO: DS = 8, four times the warps on the same tile, gave the same 0.65 of the copy peak -- 100 M instead
+    // of 75 M instructions and the L1TEX data pipe at 76 % -- so the split stays as coarse as the tile allows.)
     static constexpr int RS = D > 32 ? D / 32 : 1;
     static constexpr int DS = D / RS;
     static constexpr int THREADS = SB * RS;
@@ -102,6 +104,11 @@ __device__ __forceinline__ void cpAsync8(float2* smemDst, const float2* gsrc, bo
     const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
     const int sz = valid ? 8 : 0;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz) : "memory");
+}
+
+__device__ __forceinline__ void cpAsync8Full(float2* smemDst, const float2* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc) : "memory");
 }
 
 __device__ __forceinline__ float2 cmulf(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
@@ -163,7 +170,7 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     float2* xs = sm;                        // SB * LP
     float2* wsAll = xs + SB * LP;           // G * D      : phaseDelta^r of every VFO of the group
     float2* part = wsAll + G * D;           // NPB * PBUF : partial sums [vfo][q][run][sub-block]
-    float2* pAll = part + NPB * PBUF;       // G * SB     : sub-block start phase of every (VFO, sub-block)
+    float2* pAll = part + ((NPB == 2 && G > 1) ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
 
     const int tid = threadIdx.x;
     const int sb = tid % SB;                // sub-block of this thread
@@ -177,11 +184,22 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
 
     // ---- stage the input tile once for the whole VFO group (zero outside [0, count));
     // all copies of a thread are in flight at once, no register staging
+    static_assert(NT % D == 0, "a thread's copies must land one constant smem stride apart");
+    if (mStart >= 0 && mStart + SB * D <= j0.count) {
+        // interior tile: no bounds to check, and copy u of a thread is a compile-time offset from copy 0 on both sides
+        // (sample tid + u*NT lands in slot tid + tid/D + u*(NT + NT/D)), so the loop is LDGSTS with immediates only
+        const float2* g = in + mStart + tid;
+        float2* d = xs + tid + tid / D;
+#pragma unroll
+        for (int u = 0; u < (SB * D) / NT; u++) { cpAsync8Full(d + u * (NT + NT / D), g + u * NT); }
+    }
+    else {
 #pragma unroll 8
-    for (int i = tid; i < SB * D; i += NT) {
-        const int m = mStart + i;
-        const bool ok = (m >= 0 && m < j0.count);
-        cpAsync8(xs + i + i / D, in + (ok ? m : 0), ok);
+        for (int i = tid; i < SB * D; i += NT) {
+            const int m = mStart + i;
+            const bool ok = (m >= 0 && m < j0.count);
+            cpAsync8(xs + i + i / D, in + (ok ? m : 0), ok);
+        }
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
 
@@ -220,7 +238,11 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
         case 0: accumulateRun<RATIO, 0, VB, DS>(xrow, ws, acc); break;
         case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, VB, DS>(xrow, ws, acc); } break;
         case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, VB, DS>(xrow, ws, acc); } break;
-        default: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB, DS>(xrow, ws, acc); } break;
+        case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB, DS>(xrow, ws, acc); } break;
+        case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, VB, DS>(xrow, ws, acc); } break;
+        case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, VB, DS>(xrow, ws, acc); } break;
+        case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, VB, DS>(xrow, ws, acc); } break;
+        default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, VB, DS>(xrow, ws, acc); } break;
         }
 #pragma unroll
         for (int v = 0; v < VB; v++) {
@@ -321,7 +343,7 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
     using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB;
     constexpr int NB = SB - (Q - 1);
-    constexpr int NPB = (VB == 1) ? 2 : 1;
+    const int NPB = (VB == 1 && G > 1) ? 2 : 1;        // one VFO per CTA never touches the second partial-sum buffer
     const int Gp = ((G + VB - 1) / VB) * VB;
     const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gp * D + (size_t)NPB * VB * Q * TC::THREADS + (size_t)Gp * SB) * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

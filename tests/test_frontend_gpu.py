@@ -239,3 +239,37 @@ def test_vfo_signal_info_smoothing_and_hold_match_oracle():
         assert np.max(np.abs(sm[f] - latest)) <= 1e-3
         assert np.max(np.abs(hd[f][1:] - hbuf[1:])) <= 1e-3
         assert hd[f][0] == -1000.0        # pixel 0 is never updated by the reference's hold loop
+
+
+def test_process_host_pipelined_long_block_matches_one_shot_device_path():
+    """b200_frontend_process_host cuts a long host block into chunks (copy of chunk k+1 behind the kernels of chunk k).
+    Frames, VFO output and counts must equal those of the same block processed in one device-resident call."""
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate = 20e6, 65536, 60.0
+    n = 5 * (1 << 21) + 12345                       # five and a bit chunks
+    x = synth.make_iq(7, n, sr, sigma=0.05, tones=[(2.5e6 + 900.0, 0.2), (-3.3e6, 0.1)])
+    a = _fe(sr, fft_size=N, fft_rate=rate, fft_window=1, max_block=n)
+    b = _fe(sr, fft_size=N, fft_rate=rate, fft_window=1, max_block=n)
+    va = a.vfos.add(24e3, 2.8e3, 2.5e6)
+    vb = b.vfos.add(24e3, 2.8e3, 2.5e6)
+    for fe, v in ((a, va), (b, vb)):
+        fe.vfos.set_rotator_mode(binding.ROTATOR_EXACT)
+    a.process(to_dev(x))
+    ref_frames = np.stack(a.frames())
+    ref_out = a.vfos.output(va)
+    got = b.process_host(x, max_frames=len(ref_frames) + 2, vfos=[vb])
+    assert got["n_frames"] == len(ref_frames) == b.frame_count()
+    assert len(got["vfo"][vb]) == len(ref_out)
+    assert err_db(got["vfo"][vb], ref_out) <= -80.0
+    peak = ref_frames.max(axis=1, keepdims=True)
+    m = ref_frames > peak - 80.0
+    assert np.max(np.abs(got["frames"][m] - ref_frames[m])) <= 0.01
+    # the rows of every chunk are still resident, and the pre-processed block is the whole staged block
+    assert np.array_equal(np.stack(b.frames()), got["frames"])
+    assert len(b.preproc_out()) == n
+    # a second long call continues the stream
+    y = synth.make_iq(8, 2 * (1 << 21) + 5, sr, sigma=0.05, tones=[(2.5e6 + 900.0, 0.2)])
+    a.process(to_dev(y))
+    got2 = b.process_host(y, max_frames=64, vfos=[vb])
+    assert got2["n_frames"] == a.frame_count()
+    assert err_db(got2["vfo"][vb], a.vfos.output(va)) <= -80.0

@@ -36,7 +36,7 @@ def main():
     sr = cfg["sample_rate"]
     B = args.batch
     dev = torch.device("cuda", 0)
-    fft_rate = 1e-3 if args.no_fft else cfg["fft_rate"]
+    fft_rate = 0.05 if args.no_fft else cfg["fft_rate"]
     fe = binding.FrontEnd(sr, fft_size=cfg["fft_size"], fft_rate=fft_rate, fft_window=cfg["window"], max_block=B, device=0)
     vl = configs.vfo_list(args.cfg)
     if not args.no_vfo:
