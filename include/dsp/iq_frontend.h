@@ -12,6 +12,8 @@
 #include <string>
 #include <vector>
 
+#include "../utils/event.h"
+#include "buffer/frame_buffer.h"
 #include "chain.h"
 #include "channel/rx_vfo.h"
 
@@ -28,9 +30,13 @@ public:
 
     void init(dsp::stream<dsp::complex_t>* in, double sampleRate, bool buffering, int decimRatio, bool dcBlocking, int fftSize,
               double fftRate, FFTWindow fftWindow, float* (*acquireFFTBuffer)(void* ctx), void (*releaseFFTBuffer)(void* ctx), void* fftCtx) {
-        _in = in; preproc.init(in); workIn = in; _sampleRate = sampleRate; _decimRatio = decimRatio; _fftSize = fftSize; _fftRate = fftRate; _fftWindow = fftWindow;
+        _in = in; _buffering = buffering;
+        // the reference always routes the source through its SampleFrameBuffer (a plain copy when buffering is off);
+        // here the FIFO is only in the path while buffering is on
+        inBuf.init(in);
+        inBuf.bypass = false;
+        preproc.init(head()); workIn = head(); _sampleRate = sampleRate; _decimRatio = decimRatio; _fftSize = fftSize; _fftRate = fftRate; _fftWindow = fftWindow;
         _acquire = acquireFFTBuffer; _release = releaseFFTBuffer; _ctx = fftCtx;
-        (void)buffering;   // the reference's 32-slot input FIFO only decouples the source thread; not needed here
         if (b200_frontend_create(&fe, sampleRate, decimRatio, dcBlocking ? 1 : 0, 0, fftSize, fftRate, (int)fftWindow,
                                  STREAM_BUFFER_SIZE, 0) != B200_OK) { fail("b200_frontend_create"); }
         bank = b200_frontend_vfo_bank(fe);
@@ -43,8 +49,9 @@ public:
         const bool was = running;
         if (was) { stop(); }
         _in = in;
-        preproc.setInput(in, [this](dsp::stream<dsp::complex_t>* out) { workIn = out; });
-        if (!userBlocks) { workIn = in; }
+        inBuf.setInput(in);
+        preproc.setInput(head(), [this](dsp::stream<dsp::complex_t>* out) { workIn = out; });
+        if (!userBlocks) { workIn = head(); }
         if (was) { start(); }
     }
 
@@ -62,18 +69,32 @@ public:
         pauseFor([&] { preproc.setBlockEnabled(processor, enabled, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); });
     }
     void setSampleRate(double sampleRate) {
-        std::lock_guard<std::mutex> lk(mtx);
-        _sampleRate = sampleRate;
-        if (b200_frontend_set_sample_rate(fe, sampleRate) != B200_OK) { fail("setSampleRate"); }
-        resizeRows();
+        {
+            std::lock_guard<std::mutex> lk(mtx);
+            _sampleRate = sampleRate;
+            if (b200_frontend_set_sample_rate(fe, sampleRate) != B200_OK) { fail("setSampleRate"); }
+            resizeRows();
+        }
+        onEffectiveSampleRateChange.emit(_sampleRate / _decimRatio);     // outside the lock: handlers may call back in
     }
     double getSampleRate() { return _sampleRate / _decimRatio; }
-    void setBuffering(bool) {}
+    // IQFrontEnd::setBuffering (iq_frontend.cpp:118-120): switch the input FIFO in or out
+    void setBuffering(bool enabled) {
+        if (enabled == _buffering) { return; }
+        pauseFor([&] {
+            _buffering = enabled;
+            preproc.setInput(head(), [this](dsp::stream<dsp::complex_t>* out) { workIn = out; });
+            if (!userBlocks) { workIn = head(); }
+        });
+    }
     void setDecimation(int ratio) {
-        std::lock_guard<std::mutex> lk(mtx);
-        _decimRatio = ratio;
-        if (b200_frontend_set_decimation(fe, ratio) != B200_OK) { fail("setDecimation"); }
-        resizeRows();
+        {
+            std::lock_guard<std::mutex> lk(mtx);
+            _decimRatio = ratio;
+            if (b200_frontend_set_decimation(fe, ratio) != B200_OK) { fail("setDecimation"); }
+            resizeRows();
+        }
+        onEffectiveSampleRateChange.emit(_sampleRate / _decimRatio);
     }
     void setInvertIQ(bool enabled) { std::lock_guard<std::mutex> lk(mtx); b200_frontend_set_invert_iq(fe, enabled); }
     void setDCBlocking(bool enabled) { std::lock_guard<std::mutex> lk(mtx); b200_frontend_set_dc_blocking(fe, enabled); }
@@ -109,12 +130,13 @@ public:
     void setFFTRate(double rate) { std::lock_guard<std::mutex> lk(mtx); _fftRate = rate; if (b200_frontend_set_fft_rate(fe, rate) != B200_OK) { fail("setFFTRate"); } resizeRows(); }
     double getFFTRate() { return _fftRate; }
     void setFFTWindow(FFTWindow w) { std::lock_guard<std::mutex> lk(mtx); _fftWindow = w; if (b200_frontend_set_fft_window(fe, (int)w) != B200_OK) { fail("setFFTWindow"); } }
-    void flushInputBuffer() {}
+    void flushInputBuffer() { inBuf.flush(); }
 
     void start() {
         if (running || !_in) { return; }
         running = true;
         workIn->clearReadStop();
+        if (_buffering) { inBuf.start(); }
         preproc.start();
         worker = std::thread([this] { while (step() >= 0) {} });
     }
@@ -125,6 +147,7 @@ public:
         for (auto* s : bound) { s->stopWriter(); }
         if (worker.joinable()) { worker.join(); }
         preproc.stop();
+        if (_buffering) { inBuf.stop(); }
         workIn->clearReadStop();
         for (auto& kv : vfos) { kv.second->out.clearWriteStop(); }
         for (auto* s : bound) { s->clearWriteStop(); }
@@ -132,6 +155,7 @@ public:
     }
 
     double getEffectiveSamplerate() { return b200_frontend_effective_samplerate(fe); }
+    Event<double> onEffectiveSampleRateChange;     // emitted by setSampleRate / setDecimation (iq_frontend.cpp:99,129)
     b200_frontend* handle() { return fe; }
 
 protected:
@@ -194,6 +218,9 @@ protected:
     dsp::stream<dsp::complex_t>* _in = nullptr;
     dsp::stream<dsp::complex_t>* workIn = nullptr;      // what the worker reads: _in, or the tail of the plug-in chain
     dsp::chain<dsp::complex_t> preproc;
+    dsp::buffer::SampleFrameBuffer<dsp::complex_t> inBuf;
+    bool _buffering = false;
+    dsp::stream<dsp::complex_t>* head() { return _buffering ? &inBuf.out : _in; }   // what the plug-in chain reads
     int userBlocks = 0;
     std::map<std::string, dsp::channel::RxVFO*> vfos;
     std::vector<dsp::stream<dsp::complex_t>*> bound;

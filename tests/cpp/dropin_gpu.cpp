@@ -27,7 +27,7 @@ int main(int argc, char** argv) {
 
     dsp::stream<dsp::complex_t> src;
     IQFrontEnd fe;
-    fe.init(&src, 2.4e6, true, 1, false, 8192, 20.0, IQFrontEnd::NUTTALL, acquire, release, nullptr);
+    fe.init(&src, 2.4e6, false, 1, false, 8192, 20.0, IQFrontEnd::NUTTALL, acquire, release, nullptr);
     dsp::channel::RxVFO* vfo = fe.addVFO("Radio", 50000.0, 12500.0, 100e3);
     if (!vfo) { return 3; }
     if (fe.addVFO("Radio", 50000.0, 12500.0, 0.0) != nullptr) { return 4; }   // duplicate name is refused
@@ -58,9 +58,31 @@ int main(int argc, char** argv) {
     }
     const int expectOut = (n / blk) * outPerBlock;
     for (int spin = 0; spin < 20000 && gotCount.load() < expectOut; spin++) { std::this_thread::sleep_for(std::chrono::milliseconds(1)); }
+    // the input FIFO (IQFrontEnd::setBuffering): the source may now run ahead of the worker; a short burst below the
+    // FIFO depth must still come out complete and in order
+    const int before = gotCount.load();
+    const size_t rowsBefore = g_rows.size();
+    const int acqBefore = g_acquires, relBefore = g_releases;
+    fe.setBuffering(true);
+    const int burst = 8;
+    for (int b = 0; b < burst; b++) {
+        memcpy(src.writeBuf, x.data() + (size_t)b * blk, blk * sizeof(dsp::complex_t));
+        if (!src.swap(blk)) { return 6; }
+    }
+    for (int spin = 0; spin < 20000 && gotCount.load() < before + burst * outPerBlock; spin++) { std::this_thread::sleep_for(std::chrono::milliseconds(1)); }
+    if (gotCount.load() != before + burst * outPerBlock) { fprintf(stderr, "buffered burst: %d of %d samples\n", gotCount.load() - before, burst * outPerBlock); return 7; }
+    // effective-sample-rate event
+    static double announced = 0.0;
+    EventHandler<double> onSr([](double v, void*) { announced = v; }, nullptr);
+    fe.onEffectiveSampleRateChange.bindHandler(&onSr);
     vfo->out.stopReader();
     sink.join();
     fe.stop();
+    fe.setSampleRate(2.4e6);
+    if (announced != 2.4e6) { return 8; }
+    fe.onEffectiveSampleRateChange.unbindHandler(&onSr);
+    got.resize((size_t)before);                           // the file compared by the Python test holds the first phase only
+    g_rows.resize(rowsBefore); g_acquires = acqBefore; g_releases = relBefore;
 
     FILE* o = fopen(argv[4], "wb");
     int hdr[4] = { (int)got.size(), (int)(g_rows.size() / 8192), g_acquires, g_releases };
