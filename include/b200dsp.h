@@ -253,6 +253,14 @@ int b200_waterfall_make_palette(const float* colors_rgb, int color_count, uint32
 /* nrows dB rows (device, row stride raw_fft_size) -> zoomed rows (device float[nrows][data_width], may be
  * NULL) and RGBA rows (device uint32[nrows][data_width], may be NULL). */
 int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, float* d_zoom, uint32_t* d_rgba, void* stream);
+/* WaterFall::rawFFTs / getFFTBuffer (waterfall.cpp:1188-1199): keep the newest `height` raw dB rows of every push on
+ * the device (0 = keep none, the default).  Rows handed to b200_waterfall_push must then be 16-byte aligned. */
+int b200_waterfall_set_history(b200_waterfall* wf, int height);
+/* WaterFall::updateWaterfallFb (waterfall.cpp:771-866): all stored rows through the current view / range / palette in
+ * one launch -- what the reference does on four CPU threads after a zoom, pan or palette change.  d_zoom
+ * (float[height][data_width]) and d_rgba (uint32[height][data_width]) may each be NULL; output row 0 is the newest
+ * stored row, rows past the number stored are opaque black (0xFF000000).  Returns the number of stored rows. */
+int b200_waterfall_regenerate(b200_waterfall* wf, float* d_zoom, uint32_t* d_rgba, void* stream);
 /* WaterFall::calculateVFOSignalInfo (waterfall.cpp:688-759): strength and SNR of one VFO (centre offset and bandwidth
  * in Hz, relative to a display `whole_bandwidth` wide) from each raw dB row: d_out[row] = {strength, snr}.
  * Returns 1 (and launches nothing) where the reference returns false (empty side bands). */

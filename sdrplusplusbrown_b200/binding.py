@@ -82,6 +82,8 @@ _SIGS = {
     "b200_waterfall_set_palette": (_i, [_vp, _vp]),
     "b200_waterfall_make_palette": (_i, [_vp, _i, _vp]),
     "b200_waterfall_push": (_i, [_vp, _vp, _i, _vp, _vp, _vp]),
+    "b200_waterfall_set_history": (_i, [_vp, _i]),
+    "b200_waterfall_regenerate": (_i, [_vp, _vp, _vp, _vp]),
     "b200_waterfall_zoom_table": (_i, [_vp, _vp, _vp]),
     "b200_waterfall_vfo_signal": (_i, [_vp, _vp, _i, _d, _d, _d, _vp, _vp]),
     "b200_waterfall_smooth_hold": (_i, [_vp, _vp, _i, _i, _f, _i, _f, _vp, _vp]),
@@ -346,6 +348,13 @@ class Waterfall:
 
     def push(self, d_rows_ptr, nrows, d_zoom_ptr, d_rgba_ptr, stream=None):
         _chk(lib.b200_waterfall_push(self.h, d_rows_ptr, int(nrows), d_zoom_ptr, d_rgba_ptr, _stream_ptr(stream)))
+
+    def set_history(self, height):
+        _chk(lib.b200_waterfall_set_history(self.h, int(height)))
+
+    def regenerate(self, d_zoom_ptr, d_rgba_ptr, stream=None):
+        """all stored raw rows through the current view/range/palette; returns the number of stored rows"""
+        return _chk(lib.b200_waterfall_regenerate(self.h, d_zoom_ptr, d_rgba_ptr, _stream_ptr(stream)))
 
     def vfo_signal(self, d_rows_ptr, nrows, whole_bw, center, bw, d_out_ptr, stream=None):
         """returns False where the reference's calculateVFOSignalInfo returns false"""

@@ -12,13 +12,21 @@ namespace {
 // bins side by side, so a warp reads contiguous runs of the dB row, and fold their maxima with shuffles.
 __global__ void __launch_bounds__(256) zoomPaletteKernel(const float* __restrict__ rows, int rawSize, int width, const int* __restrict__ sid,
                                                          const int* __restrict__ uf, float wfMin, float wfMax, const uint32_t* __restrict__ lut,
-                                                         float* __restrict__ zoom, uint32_t* __restrict__ rgba, int logG) {
+                                                         float* __restrict__ zoom, uint32_t* __restrict__ rgba, int logG,
+                                                         int ringHeight, int ringBase, int liveRows) {
     const int G = 1 << logG;
     const int t = blockIdx.x * 256 + threadIdx.x;
     const int pix = t >> logG, sub = t & (G - 1);
     const bool live = pix < width;
     const int i = live ? pix : width - 1;
-    const float* row = rows + (size_t)blockIdx.y * rawSize;
+    if ((int)blockIdx.y >= liveRows) {
+        // regeneration of a history that is not full yet: opaque black below the last stored line (waterfall.cpp:846-855)
+        if (live && sub == 0 && rgba) { rgba[(size_t)blockIdx.y * width + i] = 0xFF000000u; }
+        return;
+    }
+    // ringHeight > 0: output row y shows history line (ringBase + y) % ringHeight, newest first (waterfall.cpp:826)
+    const int srcRow = ringHeight > 0 ? (int)((ringBase + blockIdx.y) % ringHeight) : (int)blockIdx.y;
+    const float* row = rows + (size_t)srcRow * rawSize;
     const int s = __ldg(sid + i), n = __ldg(uf + i);
     float m = -INFINITY;
     // eight loads in flight per lane: the kernel is bound by memory latency, not by the maxima
@@ -38,6 +46,18 @@ __global__ void __launch_bounds__(256) zoomPaletteKernel(const float* __restrict
         const int id = (int)(px * 999.0f);
         rgba[(size_t)blockIdx.y * width + i] = __ldg(lut + id);
     }
+}
+
+// WaterFall::getFFTBuffer (waterfall.cpp:1188-1199) for a batch: pushed row r (oldest first) becomes history line
+// (cur0 - 1 - r) mod height -- the line index steps DOWN with every new row, so ascending lines run newest to oldest.
+__global__ void __launch_bounds__(256) storeRawKernel(const float* __restrict__ rows, int firstRow, int rawSize, float* __restrict__ ring, int height, int cur0) {
+    const int r = firstRow + blockIdx.y;
+    int line = (cur0 - 1 - r) % height;
+    if (line < 0) { line += height; }
+    const float4* src = reinterpret_cast<const float4*>(rows + (size_t)r * rawSize);
+    float4* dst = reinterpret_cast<float4*>(ring + (size_t)line * rawSize);
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < rawSize / 4; i += gridDim.x * 256) { dst[i] = __ldg(src + i); }
+    if (blockIdx.x == 0 && threadIdx.x < (rawSize & 3)) { ring[(size_t)line * rawSize + (rawSize & ~3) + threadIdx.x] = rows[(size_t)r * rawSize + (rawSize & ~3) + threadIdx.x]; }
 }
 
 // WaterFall::calculateVFOSignalInfo (waterfall.cpp:688-759), one CTA per dB row.  The side-band bins (one bandwidth on
@@ -128,6 +148,8 @@ struct b200_waterfall {
     float* dSmooth = nullptr; float* dHold = nullptr;     // smoothingBuf / latestFFTHold, both start at -1000 (waterfall.cpp:1073,1090)
     bool tableDirty = true;
     int maxUf = 1;            // widest pixel (bins), picks the lanes-per-pixel of the zoom kernel
+    // raw dB history (WaterFall::rawFFTs / currentFFTLine / fftLines, waterfall.cpp:1188-1199)
+    float* dRaw = nullptr; int height = 0, currentLine = 0, lines = 0;
 };
 
 extern "C" {
@@ -164,6 +186,7 @@ int b200_waterfall_destroy(b200_waterfall* wf) {
     if (!wf) { setError("NULL waterfall handle"); return B200_EINVAL; }
     DeviceGuard g(wf->device);
     cudaFree(wf->dSid); cudaFree(wf->dUf); cudaFree(wf->dLut); cudaFree(wf->dSmooth); cudaFree(wf->dHold);
+    if (wf->dRaw) { cudaFree(wf->dRaw); }
     delete wf;
     return B200_OK;
 }
@@ -231,10 +254,53 @@ int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, floa
     int logG = 0;
     while (logG < 5 && (8 << logG) < wf->maxUf) { logG++; }          // up to eight bins per lane before adding lanes
     dim3 grid((unsigned)((((size_t)wf->width << logG) + 255) / 256), nrows);
-    zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba, logG);
+    if (d_zoom || d_rgba) {
+        zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
+                                                                  logG, 0, 0, nrows);
+        B200_CHECK_LAUNCH();
+        countLaunch();
+    }
+    if (wf->dRaw) {
+        // keep the raw rows for a later full regeneration; of a batch longer than the history only the newest rows stay
+        const int first = std::max(0, nrows - wf->height);
+        if ((((uintptr_t)d_rows) & 15) != 0 || (wf->rawSize & 3) != 0) { setError("history rows must be 16-byte aligned with a multiple-of-4 size"); return B200_EINVAL; }
+        storeRawKernel<<<dim3(std::max(1, std::min(64, wf->rawSize / 1024)), nrows - first), 256, 0, (cudaStream_t)stream>>>(d_rows, first, wf->rawSize, wf->dRaw, wf->height,
+                                                                                                                  wf->currentLine);
+        B200_CHECK_LAUNCH();
+        countLaunch();
+        wf->currentLine = (int)((((long long)wf->currentLine - nrows) % wf->height + wf->height) % wf->height);
+        wf->lines = std::min(wf->height, wf->lines + nrows);
+    }
+    return B200_OK;
+}
+
+// WaterFall::rawFFTs: keep the last `height` raw dB rows on the device (0 = none)
+int b200_waterfall_set_history(b200_waterfall* wf, int height) {
+    if (!wf || height < 0) { setError("bad arguments to b200_waterfall_set_history"); return B200_EINVAL; }
+    DeviceGuard g(wf->device);
+    B200_CUDA(cudaDeviceSynchronize());
+    if (wf->dRaw) { cudaFree(wf->dRaw); wf->dRaw = nullptr; }
+    wf->height = height; wf->currentLine = 0; wf->lines = 0;
+    if (height > 0) { B200_CUDA(cudaMalloc((void**)&wf->dRaw, (size_t)height * wf->rawSize * sizeof(float))); }
+    return B200_OK;
+}
+
+// WaterFall::updateWaterfallFb (waterfall.cpp:771-866): every stored line through the CURRENT view, range and palette
+// in one launch (the reference splits the lines over four CPU threads).  Output row 0 is the newest line; rows past
+// the number of stored lines are opaque black.  Returns the number of stored lines.
+int b200_waterfall_regenerate(b200_waterfall* wf, float* d_zoom, uint32_t* d_rgba, void* stream) {
+    if (!wf || (!d_zoom && !d_rgba)) { setError("bad arguments to b200_waterfall_regenerate"); return B200_EINVAL; }
+    if (!wf->dRaw) { setError("b200_waterfall_regenerate needs b200_waterfall_set_history first"); return B200_ESTATE; }
+    DeviceGuard g(wf->device);
+    B200_TRY(refreshTable(wf));
+    int logG = 0;
+    while (logG < 5 && (8 << logG) < wf->maxUf) { logG++; }
+    dim3 grid((unsigned)((((size_t)wf->width << logG) + 255) / 256), wf->height);
+    zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(wf->dRaw, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
+                                                              logG, wf->height, wf->currentLine, wf->lines);
     B200_CHECK_LAUNCH();
     countLaunch();
-    return B200_OK;
+    return wf->lines;
 }
 
 int b200_waterfall_zoom_table(b200_waterfall* wf, int* sid, int* ufactor) {

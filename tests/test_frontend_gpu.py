@@ -273,3 +273,54 @@ def test_process_host_pipelined_long_block_matches_one_shot_device_path():
     got2 = b.process_host(y, max_frames=64, vfos=[vb])
     assert got2["n_frames"] == a.frame_count()
     assert err_db(got2["vfo"][vb], a.vfos.output(va)) <= -80.0
+
+
+def test_waterfall_history_and_full_regeneration_match_oracle():
+    """WaterFall::rawFFTs + updateWaterfallFb: rows pushed in ragged batches are kept (newest `height`), and a view /
+    range change regenerates every stored line -- newest first, opaque black past the stored lines -- with the oracle's
+    doZoom bins and palette indices."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    N, W, H = 4096, 333, 12
+    rng = np.random.default_rng(11)
+    rows = (rng.standard_normal((20, N)) * 12.0 - 60.0).astype(np.float32)
+    d_rows = torch.from_numpy(rows).cuda()
+    wf = binding.Waterfall(N, W)
+    wf.set_history(H)
+    wf.set_palette(np.arange(1000, dtype=np.uint32))          # identity LUT: rgba = palette index
+    wf.set_range(-100.0, -20.0)
+    d_zoom = torch.empty((H, W), dtype=torch.float32, device="cuda")
+    d_rgba = torch.empty((H, W), dtype=torch.int32, device="cuda")
+
+    def check(n_pushed, view, lo, hi):
+        wf.set_view(*view)
+        wf.set_range(lo, hi)
+        d_rgba.fill_(7)
+        stored = wf.regenerate(d_zoom.data_ptr(), d_rgba.data_ptr())
+        torch.cuda.synchronize()
+        assert stored == min(n_pushed, H)
+        z, p = d_zoom.cpu().numpy(), d_rgba.cpu().numpy()
+        for i in range(stored):
+            src = rows[n_pushed - 1 - i]                      # row 0 = newest
+            ref_z = PORT.do_zoom(view[0], view[1], src, W)
+            assert np.array_equal(z[i], ref_z), i
+            ref_p = PORT.palette_indices(ref_z, lo, hi)
+            assert np.max(np.abs(p[i] - ref_p)) <= 1
+        if stored < H:
+            assert np.all(p[stored:].view(np.uint32) == 0xFF000000)
+
+    wf.push(d_rows[0:5].data_ptr(), 5, None, None)            # history only, no per-row output
+    check(5, (0, N), -100.0, -20.0)
+    wf.push(d_rows[5:6].data_ptr(), 1, None, None)
+    wf.push(d_rows[6:17].data_ptr(), 11, None, None)          # wraps the ring
+    check(17, (1000, 1500), -90.0, -30.0)                     # zoomed-in view, new range
+    wf.push(d_rows[17:20].data_ptr(), 3, None, None)
+    check(20, (0, N), -100.0, -20.0)
+    wf.set_history(4)                                         # a batch longer than the history keeps its newest rows
+    d_zoom4 = torch.empty((4, W), dtype=torch.float32, device="cuda")
+    wf.push(d_rows[0:9].data_ptr(), 9, None, None)
+    wf.set_view(0, N)
+    assert wf.regenerate(d_zoom4.data_ptr(), None) == 4
+    z = d_zoom4.cpu().numpy()
+    for i in range(4):
+        assert np.array_equal(z[i], PORT.do_zoom(0, N, rows[8 - i], W))
