@@ -380,6 +380,29 @@ def run_gpu(args):
     nf2 = fe2.frame_count()
     d2h = nf2 * cfg["fft_size"] * 4 + int(counts[v2]) * 8 * 2
 
+    # ---- the same call fed with int16 I/Q (what the reference's file source and most SDR hardware deliver; converted on
+    # the device): reported beside e2e, not instead of it
+    h_i16 = (h_in * 32767.0).to(torch.int16).pin_memory()
+
+    def e2e_i16_step():
+        rc = binding.lib.b200_frontend_process_host_i16(fe2.h, h_i16.data_ptr(), Be, ctypes.c_float(32768.0), h_frames.data_ptr(), mf, optr, aptr,
+                                                        counts.ctypes.data, compute.cuda_stream)
+        if rc < 0:
+            raise RuntimeError(binding.lib.b200_last_error().decode())
+
+    for _ in range(2):
+        e2e_i16_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_i16_step()
+    torch.cuda.synchronize(dev)
+    ti = time.perf_counter() - t0
+    tti = torch.tensor([ti], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tti, op=dist.ReduceOp.MAX)
+    e2e_i16_value = world * Be * args.e2e_steps / float(tti.item()) / 1e6
+
     if rank == 0:
         peak, which = peaks()
         achieved = (kbytes / 1e9) / (kms * 1e-3) if kms > 0 else 0.0
@@ -389,7 +412,9 @@ def run_gpu(args):
             "config": _config(args, B, world),
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": Be * 8, "d2h_bytes_per_step": d2h,
-                    "batch_samples": Be, "path": "b200_frontend_process_host (pinned host buffers, H2D + kernels + D2H per call)"},
+                    "batch_samples": Be, "path": "b200_frontend_process_host (pinned host buffers, H2D + kernels + D2H per call)",
+                    "int16_input": {"value": e2e_i16_value, "unit": UNIT, "h2d_bytes_per_step": Be * 4,
+                                    "path": "b200_frontend_process_host_i16 (int16 I/Q over PCIe, converted on the device)"}},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "fusedXlateDecimKernel<512> (xlate + /32 decimating FIR, stage 1 of the VFO)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,

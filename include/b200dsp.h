@@ -206,7 +206,7 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index o
  * of `h_frames` (frame_count x fft_size floats, may be NULL) and each VFO's output (h_vfo_out[v],
  * may be NULL) / audio (h_audio[v], may be NULL; b200_vfo_audio_count(v) stereo samples, size it with
  * b200_vfo_audio_max_out).  Blocks until done.
- * Blocks of 2^22 samples or more (without decimation / DC blocking / IQ inversion) are cut into 2^21-sample chunks:
+ * Blocks of 32 MiB or more (without decimation / DC blocking / IQ inversion) are cut into 16 MiB chunks (2^21 cf32 samples):
  * the copy of the following chunks runs behind the kernels of the current one and the results travel back over the
  * other PCIe direction meanwhile (give pinned host buffers, b200_host_alloc, for that to overlap).  All dB rows of
  * the block stay resident (frame_count / frame_ptr / frame_index cover the whole block); the per-VFO device
@@ -214,6 +214,14 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index o
  * vfo_counts, which always cover the whole block. */
 int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
                                float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
+/* The same call for sources that deliver interleaved int16 I/Q (the file source's WAV path, most SDR hardware): the
+ * block crosses PCIe as 4 bytes per sample and becomes cf32 on the device, out = (float)in / scalar -- the arithmetic
+ * of volk_16i_s32f_convert_32f(stream.writeBuf, inBuf, 32768.0f, ...) at source_modules/file_source/src/main.cpp:409.
+ * Results are bit-identical to b200_frontend_process_host on the converted block. */
+int b200_frontend_process_host_i16(b200_frontend* fe, const int16_t* h_in, int count, float scalar, float* h_frames, int max_frames,
+                                   float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
+/* Device-resident form of that conversion: count complex samples, d_in int16[2*count] -> d_out float[2*count]. */
+int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out, void* stream);
 
 /* DC blocker (dsp::correction::DCBlocker<complex_t>::process, correction/dc_blocker.h:54-60) for callers that
  * are not allowed to allocate.  This entry point has no counterpart in the reference; it exists for hosts that

@@ -73,6 +73,8 @@ _SIGS = {
     "b200_frontend_frame_ptr": (_vp, [_vp, _i]),
     "b200_frontend_frame_index": (C.c_int64, [_vp, _i]),
     "b200_frontend_process_host": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
+    "b200_frontend_process_host_i16": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
+    "b200_convert_i16": (_i, [_vp, _i, _f, _vp, _vp]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
@@ -292,8 +294,12 @@ class FrontEnd:
         _chk(lib.b200_frontend_preproc_out(self.h, C.byref(p), C.byref(n)))
         return _dev_to_numpy(p.value, n.value, np.complex64, self.device)
 
-    def process_host(self, x, max_frames=0, vfos=(), audio=(), stream=None):
-        x = np.ascontiguousarray(x, np.complex64)
+    def process_host(self, x, max_frames=0, vfos=(), audio=(), stream=None, i16_scalar=None):
+        """x: complex64 block, or (with i16_scalar) an int16 array [n, 2] of I/Q converted on the device"""
+        if i16_scalar is not None:
+            x = np.ascontiguousarray(x, np.int16).reshape(-1, 2)
+        else:
+            x = np.ascontiguousarray(x, np.complex64)
         frames = np.empty((max_frames, self.fft_size), np.float32) if max_frames else None
         nslots = (max(list(vfos) + list(audio)) + 1) if (vfos or audio) else 0
         obufs = {v: np.empty(self.vfos.max_out(v, len(x)), np.complex64) for v in vfos}
@@ -305,8 +311,12 @@ class FrontEnd:
         for v in audio:
             aptrs[v] = abufs[v].ctypes.data
         counts = np.zeros(max(nslots, 1), np.int32)
-        _chk(lib.b200_frontend_process_host(self.h, x.ctypes.data, len(x), frames.ctypes.data if max_frames else None, max_frames,
-                                            optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
+        if i16_scalar is not None:
+            _chk(lib.b200_frontend_process_host_i16(self.h, x.ctypes.data, len(x), float(i16_scalar), frames.ctypes.data if max_frames else None, max_frames,
+                                                    optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
+        else:
+            _chk(lib.b200_frontend_process_host(self.h, x.ctypes.data, len(x), frames.ctypes.data if max_frames else None, max_frames,
+                                                optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
         nf = self.frame_count()
         return dict(frames=frames[:min(nf, max_frames)] if max_frames else None, n_frames=nf,
                     vfo={v: obufs[v][:counts[v]] for v in vfos}, audio={v: abufs[v] for v in audio})

@@ -171,6 +171,15 @@ __global__ void __launch_bounds__(256) conjKernel(const cf32* __restrict__ in, c
 } // namespace
 
 // ------------------------------------------------------------------ front end object
+// int16 I/Q -> cf32: out = (float)in / scalar, the arithmetic of VOLK's generic 16i_s32f_convert_32f
+// (reference call site: source_modules/file_source/src/main.cpp:409, scalar 32768)
+__global__ void __launch_bounds__(256) convertI16Kernel(const short2* __restrict__ in, float2* __restrict__ out, int n, float scalar) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const short2 v = __ldg(in + i);
+        out[i] = make_float2(__fdiv_rn((float)v.x, scalar), __fdiv_rn((float)v.y, scalar));
+    }
+}
+
 struct FrontEnd {
     int device = 0;
     double sampleRate = 0; int decimRatio = 1; bool dcBlocking = false, invertIQ = false;
@@ -205,6 +214,7 @@ struct FrontEnd {
     int shardRank = 0, shardWorld = 1;
     // host staging
     cf32* dStageIn = nullptr;
+    short2* dStageI16 = nullptr;                // int16 I/Q as it arrives from the host (process_host_i16)
     cudaStream_t hostCopyStream = nullptr;      // H2D of the next chunks while the current one is processed
     std::vector<cudaEvent_t> hostCopyDone;
     cudaEvent_t evHostStart = nullptr;
@@ -293,7 +303,7 @@ void FrontEnd::destroy() {
     decimStages.clear();
     plan.destroy();
     ring.destroy();
-    void* ptrs[] = { dDcOut, dChunkB, dChunkStart, dDcState, dJobDesc, dWindow, dCarry, dRows, dFrameDesc, dStageIn };
+    void* ptrs[] = { dDcOut, dChunkB, dChunkStart, dDcState, dJobDesc, dWindow, dCarry, dRows, dFrameDesc, dStageIn, dStageI16 };
     for (void* p : ptrs) { if (p) { cudaFree(p); } }
 }
 
@@ -604,8 +614,10 @@ static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& frames
     return B200_OK;
 }
 
-int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
-                               float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
+// sampleBytes = 8: h_in holds cf32; sampleBytes = 4: h_in holds interleaved int16 I/Q, converted on the device
+// (out = (float)in / scalar, the file source's volk_16i_s32f_convert_32f, file_source/src/main.cpp:409)
+static int processHostImpl(b200_frontend* fe, const void* h_in, int sampleBytes, float scalar, int count, float* h_frames, int max_frames,
+                           float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
     FE_OR_FAIL(fe);
     FrontEnd& f = fe->impl;
     if (count < 0 || count > f.maxBlock) { setError("block of %d samples exceeds max_block %d", count, f.maxBlock); return B200_ETOOBIG; }
@@ -613,6 +625,22 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
     DeviceGuard g(f.device);
     cudaStream_t s = (cudaStream_t)stream;
     if (!f.dStageIn) { B200_CUDA(cudaMalloc((void**)&f.dStageIn, (size_t)f.maxBlock * sizeof(cf32))); }
+    const bool i16 = sampleBytes == 4;
+    if (i16 && !f.dStageI16) { B200_CUDA(cudaMalloc((void**)&f.dStageI16, (size_t)f.maxBlock * sizeof(short2))); }
+    if (i16 && !(scalar != 0.0f)) { setError("int16 scale must not be zero"); return B200_EINVAL; }
+    const char* hIn = (const char*)h_in;
+    // brings chunk [off, off+n) to dStageIn: the copy goes on `cs`, the int16 -> float conversion (if any) on `ks`
+    auto stageCopy = [&](size_t off, int n, cudaStream_t cs) -> int {
+        void* dst = i16 ? (void*)(f.dStageI16 + off) : (void*)(f.dStageIn + off);
+        B200_CUDA(cudaMemcpyAsync(dst, hIn + off * sampleBytes, (size_t)n * sampleBytes, cudaMemcpyHostToDevice, cs));
+        return B200_OK;
+    };
+    auto stageConvert = [&](size_t off, int n, cudaStream_t ks) -> int {
+        if (!i16 || n <= 0) { return B200_OK; }
+        convertI16Kernel<<<std::min(148 * 8, (n + 255) / 256), 256, 0, ks>>>(f.dStageI16 + off, reinterpret_cast<float2*>(f.dStageIn + off), n, scalar);
+        B200_CHECK_LAUNCH(); countLaunch();
+        return B200_OK;
+    };
     VfoBank& b = f.bank->impl;
     std::vector<int> done(b.vfos.size(), 0), audioDone(b.vfos.size(), 0);
     int framesDone = 0;
@@ -620,7 +648,7 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
     // processed and its results go back over the other PCIe direction.  The stages are streaming (results do not
     // depend on how a block is cut), and the dB rows of all chunks stay in the row buffer.  Only without
     // pre-processing, so that b200_frontend_preproc_out still names the whole block afterwards.
-    constexpr int kChunk = 1 << 21;
+    const int kChunk = (16 << 20) / sampleBytes;          // 16 MiB of host data per chunk: 2^21 cf32 or 2^22 int16 samples
     const bool plain = f.decimRatio == 1 && !f.dcBlocking && !f.invertIQ;
     if (plain && count >= 2 * kChunk) {
         const int nChunks = (count + kChunk - 1) / kChunk;
@@ -639,7 +667,7 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
         for (int c = 0; c < nChunks; c++) {
             const size_t off = (size_t)c * kChunk;
             const int n = (int)std::min<size_t>(kChunk, (size_t)count - off);
-            B200_CUDA(cudaMemcpyAsync(f.dStageIn + off, h_in + 2 * off, (size_t)n * sizeof(cf32), cudaMemcpyHostToDevice, f.hostCopyStream));
+            B200_TRY(stageCopy(off, n, f.hostCopyStream));
             B200_CUDA(cudaEventRecord(f.hostCopyDone[c], f.hostCopyStream));
         }
         b.descViaParams = true;
@@ -648,7 +676,8 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
             const size_t off = (size_t)c * kChunk;
             const int n = (int)std::min<size_t>(kChunk, (size_t)count - off);
             if (cudaStreamWaitEvent(s, f.hostCopyDone[c], 0) != cudaSuccess) { setError("cudaStreamWaitEvent failed"); rc = B200_ECUDA; break; }
-            rc = f.process(f.dStageIn + off, n, s, c > 0);
+            rc = stageConvert(off, n, s);
+            if (rc == B200_OK) { rc = f.process(f.dStageIn + off, n, s, c > 0); }
             if (rc == B200_OK) { rc = copyOutputs(f, h_frames, max_frames, framesDone, h_vfo_out, h_audio, done, audioDone, s); }
         }
         b.descViaParams = false;
@@ -656,12 +685,31 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
         f.preOut = f.dStageIn; f.preCount = count;
     }
     else {
-        B200_CUDA(cudaMemcpyAsync(f.dStageIn, h_in, (size_t)count * sizeof(cf32), cudaMemcpyHostToDevice, s));
+        B200_TRY(stageCopy(0, count, s));
+        B200_TRY(stageConvert(0, count, s));
         B200_TRY(f.process(f.dStageIn, count, s));
         B200_TRY(copyOutputs(f, h_frames, max_frames, framesDone, h_vfo_out, h_audio, done, audioDone, s));
     }
     if (vfo_counts) { for (size_t i = 0; i < b.vfos.size(); i++) { if (b.vfos[i].live) { vfo_counts[i] = done[i]; } } }
     B200_CUDA(cudaStreamSynchronize(s));
+    return B200_OK;
+}
+
+int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, float* h_frames, int max_frames,
+                               float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
+    return processHostImpl(fe, h_in, 8, 1.0f, count, h_frames, max_frames, h_vfo_out, h_audio, vfo_counts, stream);
+}
+
+int b200_frontend_process_host_i16(b200_frontend* fe, const int16_t* h_in, int count, float scalar, float* h_frames, int max_frames,
+                                   float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
+    return processHostImpl(fe, h_in, 4, scalar, count, h_frames, max_frames, h_vfo_out, h_audio, vfo_counts, stream);
+}
+
+int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out, void* stream) {
+    if (count < 0 || (count > 0 && (!d_in || !d_out)) || !(scalar != 0.0f)) { setError("bad arguments to b200_convert_i16"); return B200_EINVAL; }
+    if (count == 0) { return B200_OK; }
+    convertI16Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const short2*>(d_in), reinterpret_cast<float2*>(d_out), count, scalar);
+    B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }
 

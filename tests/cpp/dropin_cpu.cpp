@@ -8,6 +8,7 @@
 #include <dsp/chain.h>
 #include <dsp/routing/splitter.h>
 #include <utils/event.h>
+#include <utils/wav.h>
 
 #define CHECK(c) do { if (!(c)) { fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); return 1; } } while (0)
 
@@ -170,6 +171,38 @@ int main() {
         ev.emit(1.0);
         CHECK(seen[0] == 2.5);
         CHECK(seen[1] == 3.5);
+    }
+    {   // wav::Reader: header fields, looping readSamples, plain readSamples2, rejection of a non-RIFF file
+        const char* path = "/tmp/b200_dropin_test.wav";
+        {
+            FILE* f = fopen(path, "wb");
+            CHECK(f != nullptr);
+            const uint32_t sr = 2400000, nbytes = 6 * 4;
+            const uint16_t pcm = 1, ch = 2, bps = 4, depth = 16;
+            const uint32_t fileSize = 36 + nbytes, fmtLen = 16, bytesPerSec = sr * 4;
+            fwrite("RIFF", 1, 4, f); fwrite(&fileSize, 4, 1, f); fwrite("WAVE", 1, 4, f); fwrite("fmt ", 1, 4, f); fwrite(&fmtLen, 4, 1, f);
+            fwrite(&pcm, 2, 1, f); fwrite(&ch, 2, 1, f); fwrite(&sr, 4, 1, f); fwrite(&bytesPerSec, 4, 1, f); fwrite(&bps, 2, 1, f); fwrite(&depth, 2, 1, f);
+            fwrite("data", 1, 4, f); fwrite(&nbytes, 4, 1, f);
+            const int16_t iq[12] = { 1, -1, 2, -2, 3, -3, 4, -4, 5, -5, 6, -6 };
+            fwrite(iq, 2, 12, f);
+            fclose(f);
+        }
+        wav::Reader r(path);
+        CHECK(r.isValid());
+        CHECK(r.getSampleRate() == 2400000 && r.getChannelCount() == 2 && r.getBitDepth() == 16);
+        CHECK(r.getSampleType() == wav::SAMP_TYPE_INT16);
+        int16_t buf[16];
+        r.readSamples(buf, 16 * sizeof(int16_t));             // 12 values in the file: wraps to the first sample
+        CHECK(buf[0] == 1 && buf[11] == -6 && buf[12] == 1 && buf[15] == -2);
+        r.rewind();
+        CHECK(r.readSamples2(buf, sizeof(buf)) == 12 * sizeof(int16_t));
+        r.close();
+        FILE* g = fopen(path, "wb"); fwrite("not a wav file, only some text that is long enough", 1, 50, g); fclose(g);
+        wav::Reader bad(path);
+        CHECK(!bad.isValid() && bad.error == "signature mismatch");
+        wav::Reader missing("/tmp/b200_no_such_file.wav");
+        CHECK(!missing.isValid() && missing.error == "cannot open file");
+        remove(path);
     }
     printf("dropin_cpu ok\n");
     return 0;

@@ -324,3 +324,48 @@ def test_waterfall_history_and_full_regeneration_match_oracle():
     z = d_zoom4.cpu().numpy()
     for i in range(4):
         assert np.array_equal(z[i], PORT.do_zoom(0, N, rows[8 - i], W))
+
+
+@pytest.mark.parametrize("n", [300000, 2 * (1 << 22) + 777])
+def test_process_host_int16_ingest_is_bit_identical_to_the_converted_block(n):
+    """int16 I/Q crosses PCIe as 4 bytes per sample and is converted on the device with the file source's arithmetic
+    (volk_16i_s32f_convert_32f, scalar 32768): outputs must equal the cf32 call on the host-converted block -- bit for
+    bit for a one-shot block, to rounding for one long enough to take the pipelined path."""
+    from sdrplusplusbrown_b200 import binding
+    import torch
+    sr, N, rate = 2.4e6, 8192, 20.0
+    rng = np.random.default_rng(5)
+    xi = rng.integers(-32768, 32767, size=(n, 2), dtype=np.int16)
+    t = np.arange(n)
+    xi[:, 0] = np.clip(xi[:, 0] // 16 + (9000 * np.cos(2 * np.pi * 100.7e3 / sr * t)).astype(np.int32), -32768, 32767).astype(np.int16)
+    xi[:, 1] = np.clip(xi[:, 1] // 16 + (9000 * np.sin(2 * np.pi * 100.7e3 / sr * t)).astype(np.int32), -32768, 32767).astype(np.int16)
+    xf = (xi.astype(np.float32) / np.float32(32768.0)).view(np.complex64).reshape(-1)
+    outs = []
+    for kind in ("f32", "i16"):
+        fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+        v = fe.vfos.add(50e3, 12.5e3, 100e3)
+        fe.vfos.set_demod(v, binding.DEMOD_NFM, 1, 0, 0, 0)
+        if kind == "f32":
+            outs.append(fe.process_host(xf, max_frames=64, vfos=[v], audio=[v]))
+        else:
+            outs.append(fe.process_host(xi, max_frames=64, vfos=[v], audio=[v], i16_scalar=32768.0))
+    a, b = outs
+    assert a["n_frames"] == b["n_frames"] > 0
+    assert len(a["vfo"][v]) == len(b["vfo"][v]) > 0
+    na = len(a["vfo"][v])
+    if n < (1 << 22):
+        # same cut of the block on both paths: the same kernels see the same numbers
+        assert np.array_equal(a["frames"], b["frames"])
+        assert np.array_equal(a["vfo"][v], b["vfo"][v])
+        assert np.array_equal(a["audio"][v][:na], b["audio"][v][:na])
+    else:
+        # the two paths chunk by bytes (16 MiB), i.e. at different sample counts: equal up to summation order at the cuts
+        assert np.max(np.abs(a["frames"] - b["frames"])) <= 1e-3
+        assert err_db(b["vfo"][v], a["vfo"][v]) <= -100.0
+        assert err_db(b["audio"][v][:na, 0], a["audio"][v][:na, 0]) <= -80.0
+    # the device-resident conversion entry point
+    d_in = torch.from_numpy(xi[:1000].copy()).cuda()
+    d_out = torch.empty((1000, 2), dtype=torch.float32, device="cuda")
+    assert binding.lib.b200_convert_i16(d_in.data_ptr(), 1000, 32768.0, d_out.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out.cpu().numpy(), xi[:1000].astype(np.float32) / np.float32(32768.0))
