@@ -147,6 +147,13 @@ int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
 #define B200_DEMOD_LSB 4
 #define B200_DEMOD_DSB 5
 int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double p1, double p2, double p3);
+/* The radio module's IF chain between the VFO and the demodulator (decoder_modules/radio/src/radio_module.h:92-98):
+ * dsp::noise_reduction::NoiseBlanker (core/src/dsp/noise_reduction/noise_blanker.h:38-56; rate and level as given to
+ * its setRate / setLevel, the radio uses rate = 500 / IF samplerate) followed by dsp::noise_reduction::Squelch
+ * (squelch.h:55-69; level in dB against 10*log10 of the block's mean magnitude -- per processed block, as in the
+ * reference).  Both are off by default, as in the reference.  b200_vfo_out_ptr keeps naming the VFO output in front
+ * of the chain.  Needs a demodulator on the VFO; b200_vfo_set_demod() drops the setting again. */
+int b200_vfo_set_if_chain(b200_vfo_bank* bank, int vfo, int nb_enabled, double nb_rate, double nb_level, int squelch_enabled, double squelch_level);
 /* The radio module's AF chain behind the demodulator (decoder_modules/radio/src/radio_module.h:101-107,756-765):
  * dsp::multirate::RationalResampler<stereo_t> from the demodulator's rate to the audio device rate, then
  * dsp::filter::Deemphasis<stereo_t> (core/src/dsp/filter/deephasis.h:58-92).  audio_samplerate <= 0 keeps the audio at

@@ -88,6 +88,11 @@ int orc_ssb_process(void* h, int count, const float* in, float* outStereo);
 void* orc_am_create(int agcMode /*0 CARRIER 1 AUDIO*/, double bandwidth, double agcAttack, double agcDecay, double dcBlockRate, double samplerate); // demod/am.h
 void orc_am_destroy(void* h);
 int orc_am_process(void* h, int count, const float* in, float* outStereo);
+// radio IF chain between the VFO and the demodulator (radio_module.h:92-98): NoiseBlanker (noise_reduction/noise_blanker.h:38-56)
+// then Squelch (noise_reduction/squelch.h:55-69, the complex_t overload); either may be off.
+void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel);
+void orc_ifchain_destroy(void* h);
+int orc_ifchain_process(void* h, int count, const float* in, float* out);
 // radio AF chain (decoder_modules/radio/src/radio_module.h:101-107,756-765): RationalResampler<stereo_t> to the audio
 // device rate, then optional Deemphasis<stereo_t> (filter/deephasis.h:58-76).  tau <= 0 disables the de-emphasis.
 void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau);

@@ -498,6 +498,40 @@ struct AmDemod {
     }
 };
 
+// ------------------------------------------------------------------ radio IF chain: NoiseBlanker then Squelch
+// (noise_reduction/noise_blanker.h:38-56: running mean amplitude, samples whose amplitude exceeds level x mean are
+// scaled down to the mean; noise_reduction/squelch.h:55-69: the block passes when 10*log10(mean |x|) >= level)
+struct IfChain {
+    bool nbOn = false, sqOn = false;
+    float rate = 0.f, invRate = 1.f, nbLevel = 0.f, amp = 1.0f, sqLevel = 0.f;
+    void init(int nb, double nbRate, double nbLvl, int sq, double sqLvl) {
+        nbOn = nb != 0; sqOn = sq != 0;
+        rate = nbRate; invRate = 1.0f - rate; nbLevel = nbLvl; sqLevel = sqLvl;
+    }
+    int process(int count, const cf* in, cf* out) {
+        for (int i = 0; i < count; i++) { out[i] = in[i]; }
+        if (nbOn) {
+            for (int i = 0; i < count; i++) {
+                const float inAmp = sqrt((out[i].re * out[i].re) + (out[i].im * out[i].im));
+                float gain = 1.0f;
+                if (inAmp != 0.0f) {
+                    amp = (amp * invRate) + (inAmp * rate);
+                    const float excess = inAmp / amp;
+                    if (excess > nbLevel) { gain = 1.0f / excess; }
+                }
+                out[i].re = out[i].re * gain; out[i].im = out[i].im * gain;
+            }
+        }
+        if (sqOn && count > 0) {
+            float sum = 0.0f;
+            for (int i = 0; i < count; i++) { sum += sqrtf(out[i].re * out[i].re + out[i].im * out[i].im); }   // generic VOLK magnitude + accumulator
+            sum /= (float)count;
+            if (!(10.0f * log10f(sum) >= sqLevel)) { for (int i = 0; i < count; i++) { out[i].re = 0.f; out[i].im = 0.f; } }
+        }
+        return count;
+    }
+};
+
 // ------------------------------------------------------------------ radio AF chain: RationalResampler<stereo_t> + Deemphasis<stereo_t>
 // (radio_module.h:101-107; filter/deephasis.h:58-76,89-92).  stereo_t goes through the same complex-by-real dot product.
 struct AfPost {
@@ -657,6 +691,9 @@ int orc_ssb_process(void* h, int count, const float* in, float* out) { return ((
 void* orc_am_create(int agcMode, double bw, double att, double dec, double dcRate, double sr) { auto* d = new AmDemod; d->init(agcMode, bw, att, dec, dcRate, sr); return d; }
 void orc_am_destroy(void* h) { delete (AmDemod*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) { return ((AmDemod*)h)->process(count, (const cf*)in, out); }
+void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int sqOn, double sqLevel) { auto* c = new IfChain; c->init(nbOn, nbRate, nbLevel, sqOn, sqLevel); return c; }
+void orc_ifchain_destroy(void* h) { delete (IfChain*)h; }
+int orc_ifchain_process(void* h, int count, const float* in, float* out) { return ((IfChain*)h)->process(count, (const cf*)in, (cf*)out); }
 void* orc_afpost_create(double inSR, double outSR, double tau) { auto* a = new AfPost; a->init(inSR, outSR, tau); return a; }
 void orc_afpost_destroy(void* h) { delete (AfPost*)h; }
 int orc_afpost_process(void* h, int count, const float* in, float* out) { return ((AfPost*)h)->process(count, (const cf*)in, (cf*)out); }

@@ -44,6 +44,8 @@
 #include <dsp/demod/am.h>
 #include <dsp/loop/agc.h>
 #include <dsp/filter/deephasis.h>
+#include <dsp/noise_reduction/noise_blanker.h>
+#include <dsp/noise_reduction/squelch.h>
 #undef protected
 #undef private
 
@@ -254,6 +256,22 @@ void* orc_am_create(int agcMode, double bandwidth, double agcAttack, double agcD
 void orc_am_destroy(void* h) { delete (dsp::demod::AM<stereo_t>*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) {
     return ((dsp::demod::AM<stereo_t>*)h)->process(count, (complex_t*)in, (stereo_t*)out);
+}
+namespace { struct IfChain { dsp::noise_reduction::NoiseBlanker nb; dsp::noise_reduction::Squelch sq; bool nbOn, sqOn; }; }
+void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel) {
+    auto* c = new IfChain;
+    c->nb.init(NULL, nbRate, nbLevel);
+    c->sq.init(NULL, squelchLevel);
+    c->nbOn = nbOn != 0; c->sqOn = squelchOn != 0;
+    return c;
+}
+void orc_ifchain_destroy(void* h) { delete (IfChain*)h; }
+int orc_ifchain_process(void* h, int count, const float* in, float* out) {
+    auto* c = (IfChain*)h;
+    memcpy(out, in, (size_t)count * sizeof(complex_t));
+    if (c->nbOn) { c->nb.process(count, (complex_t*)out, (complex_t*)out); }
+    if (c->sqOn && count > 0) { c->sq.process(count, (const complex_t*)out, (complex_t*)out); }
+    return count;
 }
 namespace { struct AfPost { dsp::multirate::RationalResampler<stereo_t> resamp; dsp::filter::Deemphasis<stereo_t> deemp; bool deOn; }; }
 void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau) {

@@ -52,6 +52,7 @@ _SIGS = {
     "b200_vfo_max_out": (_i, [_vp, _i, _i]),
     "b200_vfo_set_demod": (_i, [_vp, _i, _i, _d, _d, _d, _d]),
     "b200_vfo_set_audio_post": (_i, [_vp, _i, _d, _d]),
+    "b200_vfo_set_if_chain": (_i, [_vp, _i, _i, _d, _d, _i, _d]),
     "b200_vfo_audio_ptr": (_vp, [_vp, _i]),
     "b200_vfo_audio_count": (_i, [_vp, _i]),
     "b200_vfo_audio_max_out": (_i, [_vp, _i, _i]),
@@ -194,6 +195,10 @@ class VfoBank:
 
     def set_demod(self, v, kind, p0=0.0, p1=0.0, p2=0.0, p3=0.0):
         _chk(lib.b200_vfo_set_demod(self.h, v, int(kind), float(p0), float(p1), float(p2), float(p3)))
+
+    def set_if_chain(self, v, nb=False, nb_rate=0.0, nb_level=0.0, squelch=False, squelch_level=0.0):
+        """radio IF chain in front of the demodulator: noise blanker -> squelch"""
+        _chk(lib.b200_vfo_set_if_chain(self.h, v, int(nb), float(nb_rate), float(nb_level), int(squelch), float(squelch_level)))
 
     def set_audio_post(self, v, audio_samplerate=0.0, deemph_tau=0.0):
         """radio AF chain behind the demodulator: resampler to the audio rate + de-emphasis (0 = leave out)"""

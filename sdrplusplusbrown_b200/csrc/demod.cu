@@ -26,6 +26,7 @@ struct SeqState {
     float quadPhase[2];   // ping-pong: written by one call, read by the next
     float2 rotPhase;      // SSB rotator, EXACT mode: the reference's fp32 phase
     float2 deLast;        // Deemphasis<stereo_t>::lastOut (deephasis.h:92)
+    float nbAmp;          // NoiseBlanker::amp (noise_blanker.h:62)
 };
 
 struct DemodState {
@@ -51,7 +52,13 @@ struct DemodState {
     std::vector<Stage> afDecim; Stage afPoly; bool afHasPoly = false; int afMode = 3;
     bool deOn = false; float deAlpha = 0.f;
     const float* lastAudio = nullptr; int lastAudioCount = 0;
+    // radio IF chain in front of the demodulator (radio_module.h:92-98): NoiseBlanker -> Squelch
+    bool nbOn = false, sqOn = false; float nbRate = 0.f, nbLevel = 0.f, sqLevel = 0.f;
+    cf32* dIf = nullptr; int ifCap = 0;
 };
+
+// per-call descriptor of the IF chain
+struct IfJob { const cf32* in; cf32* out; SeqState* st; float rate, invRate, nbLevel, sqLevel; int n, nbOn, sqOn, pad; };
 
 // per-call descriptor of the de-emphasis walk
 struct DeemphJob { float2* data; SeqState* st; float alpha; int n; };
@@ -424,6 +431,74 @@ __global__ void __launch_bounds__(256) stereoKernel(const DemodJob* __restrict__
     reinterpret_cast<float2*>(j.stereo)[i] = make_float2(v, v);
 }
 
+// radio IF chain, one CTA per VFO.
+// NoiseBlanker (noise_blanker.h:38-56): amp follows the input amplitude as a first-order recurrence that only advances
+// on non-zero samples; a sample whose amplitude exceeds level x amp is scaled down to amp.  The recurrence is linear,
+// so every thread first composes the affine map of its own contiguous segment, the CTA scans the 256 maps to find
+// each segment's starting amp, and the segments are then walked in the reference's own arithmetic.
+// Squelch (squelch.h:55-69): the whole block passes when 10*log10(mean |x|) >= level, else it is zeroed.
+__global__ void __launch_bounds__(256) ifChainKernel(const IfJob* __restrict__ jobs) {
+    const IfJob j = jobs[blockIdx.x];
+    __shared__ float sA[256], sB[256];
+    __shared__ double sSum[256];
+    const int tid = threadIdx.x;
+    const int seg = (j.n + 255) / 256;
+    const int i0 = min(j.n, tid * seg), i1 = min(j.n, i0 + seg);
+    const float2* in = reinterpret_cast<const float2*>(j.in);
+    float2* out = reinterpret_cast<float2*>(j.out);
+    if (j.nbOn) {
+        float A = 1.0f, B = 0.0f;
+        for (int i = i0; i < i1; i++) {
+            const float2 x = __ldg(in + i);
+            const float a = sqrtf(__fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y)));
+            if (a != 0.0f) { A *= j.invRate; B = fmaf(B, j.invRate, a * j.rate); }
+        }
+        sA[tid] = A; sB[tid] = B;
+        __syncthreads();
+        // inclusive scan of the maps (apply the earlier map first): (A2,B2) o (A1,B1) = (A1*A2, B1*A2 + B2)
+        for (int o = 1; o < 256; o <<= 1) {
+            float pa = 1.0f, pb = 0.0f;
+            if (tid >= o) { pa = sA[tid - o]; pb = sB[tid - o]; }
+            __syncthreads();
+            if (tid >= o) { const float a2 = sA[tid], b2 = sB[tid]; sA[tid] = pa * a2; sB[tid] = fmaf(pb, a2, b2); }
+            __syncthreads();
+        }
+        const float amp0 = j.st->nbAmp;
+        float amp = tid == 0 ? amp0 : fmaf(amp0, sA[tid - 1], sB[tid - 1]);
+        for (int i = i0; i < i1; i++) {
+            const float2 x = __ldg(in + i);
+            const float a = sqrtf(__fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y)));
+            float gain = 1.0f;
+            if (a != 0.0f) {
+                amp = __fadd_rn(__fmul_rn(amp, j.invRate), __fmul_rn(a, j.rate));
+                const float excess = __fdiv_rn(a, amp);
+                if (excess > j.nbLevel) { gain = __fdiv_rn(1.0f, excess); }
+            }
+            out[i] = make_float2(__fmul_rn(x.x, gain), __fmul_rn(x.y, gain));
+        }
+        __syncthreads();
+        if (tid == 255 && j.n > 0) { j.st->nbAmp = fmaf(amp0, sA[255], sB[255]); }
+        in = out;                                    // the squelch looks at the blanked block
+        __syncthreads();
+    }
+    if (j.sqOn) {
+        double acc = 0.0;
+        for (int i = i0; i < i1; i++) {
+            const float2 x = in[i];
+            acc += (double)sqrtf(__fadd_rn(__fmul_rn(x.x, x.x), __fmul_rn(x.y, x.y)));
+        }
+        sSum[tid] = acc;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) { if (tid < o) { sSum[tid] += sSum[tid + o]; } __syncthreads(); }
+        const float mean = (float)(sSum[0] / (double)max(j.n, 1));
+        const bool open = (10.0f * log10f(mean)) >= j.sqLevel;
+        for (int i = i0; i < i1; i++) { out[i] = open ? in[i] : make_float2(0.f, 0.f); }
+    }
+    else if (!j.nbOn) {
+        for (int i = i0; i < i1; i++) { out[i] = in[i]; }
+    }
+}
+
 // Deemphasis<stereo_t> (filter/deephasis.h:58-76): out[i] = alpha*in[i] + (1-alpha)*out[i-1], in place, state carried
 // between calls.  A first-order recurrence whose fp32 rounding depends on the order, so it is walked in order: the CTA
 // stages a chunk and forms alpha*in[i] for every sample, two threads (left, right) walk FMUL -> FADD, the CTA stores.
@@ -471,6 +546,7 @@ void demodDestroy(DemodState* d) {
     if (d->dMaps) { cudaFree(d->dMaps); }
     if (d->dAmps) { cudaFree(d->dAmps); }
     if (d->dStereo) { cudaFree(d->dStereo); }
+    if (d->dIf) { cudaFree(d->dIf); }
     delete d;
 }
 
@@ -523,6 +599,7 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
     d->sr = v.outSR; d->bw = v.bw;
     SeqState init{};
     init.rotPhase = make_float2(1.0f, 0.0f);
+    init.nbAmp = 1.0f;
     auto agcInit = [&](double attack, double decay) {
         // agc.init(NULL, 1.0, attack, decay, 10e6, 10.0, INFINITY) (ssb.h:29, am.h:34-35): amp = setPoint / initGain = 0
         d->agc.setPoint = 1.0f; d->agc.attack = (float)attack; d->agc.invAttack = 1.0f - d->agc.attack;
@@ -629,6 +706,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     std::vector<FirJob> firs;
     std::vector<std::vector<FirJob>> afWaves;   // wave k = stage k of every VFO's audio resampler
     std::vector<DeemphJob> deJobs;
+    std::vector<IfJob> ifJobs;
     int maxN = 0;
     for (size_t vi = 0; vi < bank.vfos.size(); vi++) {
         Vfo& v = bank.vfos[vi];
@@ -638,7 +716,21 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         d.lastCount = n;
         if (n > d.cap) { B200_CUDA(cudaStreamSynchronize(s)); B200_TRY(demodEnsureCap(d, n)); }
         DemodJob j{};
-        j.in = v.lastOutPtr; j.mono = d.dMono; j.stereo = d.dStereo; j.st = d.dState; j.wtab = d.dWtab;
+        const cf32* demodIn = v.lastOutPtr;
+        if ((d.nbOn || d.sqOn) && n > 0) {
+            if (n > d.ifCap) {
+                B200_CUDA(cudaStreamSynchronize(s));
+                if (d.dIf) { cudaFree(d.dIf); d.dIf = nullptr; }
+                d.ifCap = std::max(n + 64, d.cap);
+                B200_CUDA(cudaMalloc((void**)&d.dIf, (size_t)d.ifCap * sizeof(cf32)));
+            }
+            IfJob f{};
+            f.in = v.lastOutPtr; f.out = d.dIf; f.st = d.dState; f.rate = d.nbRate; f.invRate = 1.0f - d.nbRate; f.nbLevel = d.nbLevel;
+            f.sqLevel = d.sqLevel; f.n = n; f.nbOn = d.nbOn ? 1 : 0; f.sqOn = d.sqOn ? 1 : 0;
+            ifJobs.push_back(f);
+            demodIn = d.dIf;
+        }
+        j.in = demodIn; j.mono = d.dMono; j.stereo = d.dStereo; j.st = d.dState; j.wtab = d.dWtab;
         j.exact = (bank.rotatorMode == B200_ROTATOR_EXACT) ? 1 : 0;
         j.maps = d.dMaps; j.amps = d.dAmps;
         j.env0 = (int)std::min<long long>(d.envCount, 1 << 30);
@@ -692,7 +784,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     size_t afJobs = 0;
     for (auto& w : afWaves) { afJobs += w.size(); }
     const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + (firs.size() + afJobs) * sizeof(FirJob) +
-                         deJobs.size() * sizeof(DeemphJob) + 64 * (afWaves.size() + 8);
+                         deJobs.size() * sizeof(DeemphJob) + ifJobs.size() * sizeof(IfJob) + 64 * (afWaves.size() + 10);
     void* hp = nullptr; int slot = 0;
     B200_TRY(bank.ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -705,6 +797,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     std::vector<size_t> oW(afWaves.size());
     for (size_t w = 0; w < afWaves.size(); w++) { oW[w] = put(afWaves[w].data(), afWaves[w].size() * sizeof(FirJob)); }
     const size_t oD = put(deJobs.data(), deJobs.size() * sizeof(DeemphJob));
+    const size_t oI = put(ifJobs.data(), ifJobs.size() * sizeof(IfJob));
     if (off > bank.dDemodDescBytes) {
         B200_CUDA(cudaStreamSynchronize(s));
         if (bank.dDemodDesc) { cudaFree(bank.dDemodDesc); }
@@ -713,6 +806,10 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     }
     B200_TRY(uploadDesc(bank.dDemodDesc, h, off, s, bank.descViaParams));
     char* dd = (char*)bank.dDemodDesc;
+    if (!ifJobs.empty()) {
+        ifChainKernel<<<(unsigned)ifJobs.size(), 256, 0, s>>>((const IfJob*)(dd + oI));
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
     if (!quad.empty()) {
         quadratureKernel<<<dim3((maxN + 255) / 256, (unsigned)quad.size()), 256, 0, s>>>((const DemodJob*)(dd + oQ));
         B200_CHECK_LAUNCH(); countLaunch();
@@ -777,6 +874,25 @@ int b200_vfo_set_audio_post(b200_vfo_bank* bank, int vfo, double audio_samplerat
     DeviceGuard g(bank->impl.device);
     B200_TRY(bank->impl.syncLast());
     return afConfigure(bank->impl, bank->impl.vfos[vfo], audio_samplerate, deemph_tau);
+}
+
+int b200_vfo_set_if_chain(b200_vfo_bank* bank, int vfo, int nb_enabled, double nb_rate, double nb_level, int squelch_enabled, double squelch_level) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { setError("the IF chain sits in front of a demodulator: attach one to the VFO first"); return B200_EINVAL; }
+    DeviceGuard g(bank->impl.device);
+    B200_TRY(bank->impl.syncLast());
+    DemodState& d = *v.demod;
+    const bool wasNb = d.nbOn;
+    d.nbOn = nb_enabled != 0; d.nbRate = (float)nb_rate; d.nbLevel = (float)nb_level;
+    d.sqOn = squelch_enabled != 0; d.sqLevel = (float)squelch_level;
+    if (d.nbOn && !wasNb) {
+        // a block that joins the chain starts from its initial state (NoiseBlanker::amp = 1)
+        const float one = 1.0f;
+        B200_CUDA(cudaMemcpy(&d.dState->nbAmp, &one, sizeof(float), cudaMemcpyHostToDevice));
+    }
+    return B200_OK;
 }
 
 const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo) {

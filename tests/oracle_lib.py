@@ -65,6 +65,9 @@ _SIGS = {
     "orc_am_create": (_vp, [_i, _d, _d, _d, _d, _d]),
     "orc_am_destroy": (None, [_vp]),
     "orc_am_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_ifchain_create": (_vp, [_i, _d, _d, _i, _d]),
+    "orc_ifchain_destroy": (None, [_vp]),
+    "orc_ifchain_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_afpost_create": (_vp, [_d, _d, _d]),
     "orc_afpost_destroy": (None, [_vp]),
     "orc_afpost_process": (_i, [_vp, _i, _vp, _vp]),
@@ -287,6 +290,18 @@ class Ssb(_Demod):
 class Am(_Demod):
     def __init__(self, orc, agc_mode, bw, attack, decay, dc_rate, sr):
         super().__init__(orc, orc.lib.orc_am_create(agc_mode, bw, attack, decay, dc_rate, sr), "orc_am")
+
+
+class IfChain(_Block):
+    """radio IF chain: NoiseBlanker -> Squelch on the VFO output (complex in, complex out, same count)"""
+    def __init__(self, orc, nb_on, nb_rate, nb_level, sq_on, sq_level):
+        super().__init__(orc, orc.lib.orc_ifchain_create(int(nb_on), nb_rate, nb_level, int(sq_on), sq_level), "orc_ifchain")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(len(x), np.complex64)
+        self.orc.lib.orc_ifchain_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out
 
 
 class AfPost(_Block):

@@ -198,3 +198,54 @@ def test_audio_post_needs_a_demodulator_and_is_dropped_by_set_demod():
     b.set_demod(v, binding.DEMOD_NFM, 1, 0, 0, 0)   # rebuilding the demodulator rebuilds a plain AF path
     b.process(to_dev(x))
     assert b.audio_count(v) == b.out_count(v) == 2000
+
+
+IF_CASES = [
+    # (noise blanker on, rate factor, level, squelch on, squelch level dB)
+    (True, 500.0, 3.0, False, 0.0),
+    (False, 0.0, 0.0, True, -10.0),       # opens on the strong blocks (-5 dB), closes on the weak one (-15 dB with the filter's tail)
+    (True, 500.0, 2.0, True, -10.0),
+    (True, 2000.0, 1.5, True, -60.0),     # always open
+]
+
+
+@pytest.mark.parametrize("nb,rate_hz,nb_level,sq,sq_level", IF_CASES)
+def test_if_chain_noise_blanker_and_squelch_match_oracle(nb, rate_hz, nb_level, sq, sq_level):
+    """VFO -> NoiseBlanker -> Squelch -> NFM demodulator against the oracle chain.  The input has impulses (the
+    blanker's business), a stretch of exact zeros (its skip branch) and one weak block (the squelch closes)."""
+    from sdrplusplusbrown_b200 import binding
+    out_sr, o_dem, (kind, p0, p1, p2, p3), bw = _demod_pair("demod_nfm")
+    in_sr = out_sr * 32
+    off = 21e3
+    n = 32 * 9000
+    x = synth.make_iq(4, n, in_sr, sigma=0.01, tones=[(off + 800.0, 0.3)])
+    x[40000:40016] += 8.0                 # impulses
+    x[90000:90400] = 0
+    x[32 * 6000:] *= 0.01                 # a weak tail: falls under the squelch level
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_if = ol.IfChain(PORT, nb, rate_hz / out_sr, nb_level, sq, sq_level)
+    b = binding.VfoBank(in_sr, max_block=200000)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, kind, p0, p1, p2, p3)
+    b.set_if_chain(v, nb, rate_hz / out_sr, nb_level, sq, sq_level)
+    states = []
+    for blk in split(x, [96000, 96000, 96000]):
+        iq = o_vfo.process(blk)
+        gated = o_if.process(iq)
+        ref = o_dem.process(gated)
+        b.process(to_dev(blk))
+        assert b.out_count(v) == len(ref)
+        assert err_db(b.output(v), iq) <= -80.0                   # the VFO output in front of the chain is untouched
+        got = b.audio(v)
+        closed = not np.any(gated)
+        states.append(closed)
+        if closed:
+            # NFM of an all-zero block: atan2(0, 0) = 0 through the audio filter's decaying history
+            assert np.max(np.abs(got[:, 0] - ref[:, 0])) <= 1e-4 * max(1.0, np.max(np.abs(ref[:, 0])))
+        else:
+            assert err_db(got[:, 0], ref[:, 0]) <= -80.0, (nb, sq, err_db(got[:, 0], ref[:, 0]))
+    if sq and sq_level > -40.0:
+        assert states == [False, False, True]
+    else:
+        assert states == [False, False, False]
