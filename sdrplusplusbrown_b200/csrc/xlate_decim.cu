@@ -32,6 +32,10 @@
 namespace b200 {
 
 int fusedTileSamples = 0;   // 0 = choose by VFO count (B200_OPT_TILE_SAMPLES)
+// VFOs accumulated between two barriers.  Measured on B200 (cfg3, 32 and 256 VFOs): 1 -> 0.33 of the FFMA peak, 2 -> 0.32,
+// 4 -> 0.25, 8 -> 0.15: every extra VFO per pass adds a partial-sum buffer, and the resident CTAs it costs outweigh the
+// barriers it saves.
+int fusedVfosPerBarrier = 1;
 
 
 namespace {
@@ -94,7 +98,9 @@ template <int D, int TILE> struct TileCfg {
     // shared-memory tile (8*D bytes per sub-block) does not cap the resident warps for the large-D plans.  (Measured
     // with one VFO: DS = 8, four times the warps on the same tile, gave the same 0.65 of the copy peak -- 100 M instead
     // of 75 M instructions and the L1TEX data pipe at 76 % -- so the split stays as coarse as the tile allows.)
-    static constexpr int RS = D > 32 ? D / 32 : 1;
+    // (measured for the many-VFO tile too: DS = 16 -> 0.30 of the FFMA peak, DS = 64 -> 0.31, DS = 32 -> 0.33)
+    static constexpr int DSMAX = 32;
+    static constexpr int RS = (D / DSMAX) > 8 ? 8 : ((D / DSMAX) < 1 ? 1 : (D / DSMAX));
     static constexpr int DS = D / RS;
     static constexpr int THREADS = SB * RS;
 };
@@ -155,7 +161,7 @@ __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, c
 // VB = VFOs per register pass (only VB = 1 is instantiated, see launchPlan).
 template <int RATIO, int VB, int TILE>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
-fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
+fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int pv) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T, H = T - 1;
@@ -164,13 +170,15 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
     constexpr int LP = D + 1;               // padded sub-block pitch: lane stride 2(D+1) words -> distinct banks
-    constexpr int PBUF = VB * Q * NT;       // partial sums of one pass
-    constexpr int NPB = (VB == 1) ? 2 : 1;  // VB == 1 double-buffers them (one barrier per VFO instead of two)
+    static_assert(VB == 1, "one VFO per register pass (see launchPlan)");
+    const int PBUF = pv * Q * NT;           // partial sums of one pass: pv VFOs between two barriers
     extern __shared__ __align__(16) float2 sm[];
     float2* xs = sm;                        // SB * LP
     float2* wsAll = xs + SB * LP;           // G * D      : phaseDelta^r of every VFO of the group
-    float2* part = wsAll + G * D;           // NPB * PBUF : partial sums [vfo][q][run][sub-block]
-    float2* pAll = part + ((NPB == 2 && G > 1) ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
+    float2* part = wsAll + G * D;           // 2 * PBUF   : partial sums [pass parity][vfo][q][run][sub-block] (one buffer when G == 1)
+    float2* pAll = part + (G > 1 ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
+    __shared__ float2* sOut[kMaxGroup];     // per-VFO output pointer and length: the per-VFO loop reads no global memory
+    __shared__ int sNOut[kMaxGroup];
 
     const int tid = threadIdx.x;
     const int sb = tid % SB;                // sub-block of this thread
@@ -184,8 +192,8 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
 
     // ---- stage the input tile once for the whole VFO group (zero outside [0, count));
     // all copies of a thread are in flight at once, no register staging
-    static_assert(NT % D == 0, "a thread's copies must land one constant smem stride apart");
-    if (mStart >= 0 && mStart + SB * D <= j0.count) {
+    constexpr bool kImmediateStaging = (NT % D == 0);   // a thread's copies land one constant smem stride apart
+    if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
         // interior tile: no bounds to check, and copy u of a thread is a compile-time offset from copy 0 on both sides
         // (sample tid + u*NT lands in slot tid + tid/D + u*(NT + NT/D)), so the loop is LDGSTS with immediates only
         const float2* g = in + mStart + tid;
@@ -206,70 +214,67 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G) {
     // ---- while the tile is in flight: every VFO's w[r] table and every sub-block's start phase, so that the
     // per-VFO loop below touches no global memory except its output
     const int nG = min(G, nJobs - g0);
-    for (int g = 0; g < nG; g++) {
+    // the (VFO, r) and (VFO, sub-block) pairs are spread over all threads, so the table and checkpoint loads of the
+    // whole group are in flight together instead of one VFO after the other
+    for (int p = tid; p < nG * D; p += NT) {
+        const int g = p / D, r = p - g * D;
+        wsAll[p] = __ldg(jobs[g0 + g].wtab + r);
+    }
+    for (int p = tid; p < nG * SB; p += NT) {
+        const int g = p / SB, b = p - g * SB;
         const FusedJob& j = jobs[g0 + g];
-        for (int r = tid; r < D; r += NT) { wsAll[g * D + r] = __ldg(j.wtab + r); }
-        if (tid < SB) {
-            const int ms = mStart + tid * D;
-            float2 p = make_float2(0.f, 0.f);
-            if (ms < j.count && ms + D > 0) { p = phaseAtAny(j, ms); }
-            pAll[g * SB + tid] = p;
-        }
+        const int ms = mStart + b * D;
+        float2 ph = make_float2(0.f, 0.f);
+        if (ms < j.count && ms + D > 0) { ph = phaseAtAny(j, ms); }
+        pAll[p] = ph;
     }
-    // a ragged last pass re-reads the last VFO's table (its results are not stored)
-    for (int g = nG; g < ((nG + VB - 1) / VB) * VB; g++) {
-        for (int r = tid; r < D; r += NT) { wsAll[g * D + r] = make_float2(0.f, 0.f); }
-        if (tid < SB) { pAll[g * SB + tid] = make_float2(0.f, 0.f); }
-    }
+    if (tid < nG) { sOut[tid] = reinterpret_cast<float2*>(jobs[g0 + tid].out); sNOut[tid] = jobs[g0 + tid].nOut; }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncthreads();
 
     const float2* xrow = xs + sb * LP + run * DS;
-    for (int g = 0; g < nG; g += VB) {
-        const float2* ws = wsAll + g * D + run * DS;
-        float2* pbuf = part + ((NPB == 2) ? ((g & 1) * PBUF) : 0);
-        float2 acc[VB][8];
+    for (int gp = 0, pass = 0; gp < nG; gp += pv, pass++) {
+        float2* pb = part + (pass & 1) * PBUF;
+        const int nv = min(pv, nG - gp);
+        // pv VFOs back to back between two barriers (a rolled loop: the unrolled tap code exists once)
+#pragma unroll 1
+        for (int v = 0; v < nv; v++) {
+            const float2* ws = wsAll + (gp + v) * D + run * DS;
+            float2 acc[1][8];
 #pragma unroll
-        for (int v = 0; v < VB; v++) {
+            for (int q = 0; q < Q; q++) { acc[0][q] = make_float2(0.f, 0.f); }
+            switch (run) {
+            case 0: accumulateRun<RATIO, 0, 1, DS>(xrow, ws, acc); break;
+            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 1, DS>(xrow, ws, acc); } break;
+            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 1, DS>(xrow, ws, acc); } break;
+            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 1, DS>(xrow, ws, acc); } break;
+            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 1, DS>(xrow, ws, acc); } break;
+            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 1, DS>(xrow, ws, acc); } break;
+            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 1, DS>(xrow, ws, acc); } break;
+            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 1, DS>(xrow, ws, acc); } break;
+            }
+            const float2 P = pAll[(gp + v) * SB + sb];
 #pragma unroll
-            for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
-        }
-        switch (run) {
-        case 0: accumulateRun<RATIO, 0, VB, DS>(xrow, ws, acc); break;
-        case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, VB, DS>(xrow, ws, acc); } break;
-        case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, VB, DS>(xrow, ws, acc); } break;
-        case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, VB, DS>(xrow, ws, acc); } break;
-        case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, VB, DS>(xrow, ws, acc); } break;
-        case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, VB, DS>(xrow, ws, acc); } break;
-        case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, VB, DS>(xrow, ws, acc); } break;
-        default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, VB, DS>(xrow, ws, acc); } break;
-        }
-#pragma unroll
-        for (int v = 0; v < VB; v++) {
-            const float2 P = pAll[(g + v) * SB + sb];
-#pragma unroll
-            for (int q = 0; q < Q; q++) { pbuf[(v * Q + q) * NT + tid] = cmulf(acc[v][q], P); }
+            for (int q = 0; q < Q; q++) { pb[(v * Q + q) * NT + tid] = cmulf(acc[0][q], P); }
         }
         __syncthreads();
+        // fold the partial sums: the (VFO, output) pairs of this pass are spread over all threads
+        for (int p = tid; p < nv * NB; p += NT) {
+            const int v = p / NB, k = p - v * NB;
+            if (k0 + k < sNOut[gp + v]) {
+                float2 y = make_float2(0.f, 0.f);
 #pragma unroll
-        for (int v = 0; v < VB; v++) {
-            if (g + v < nG) {
-                const FusedJob& j = jobs[g0 + g + v];
-                if (tid < NB && k0 + tid < j.nOut) {
-                    float2 y = make_float2(0.f, 0.f);
+                for (int q = 0; q < Q; q++) {
 #pragma unroll
-                    for (int q = 0; q < Q; q++) {
-#pragma unroll
-                        for (int h = 0; h < RS; h++) {
-                            const float2 c = pbuf[(v * Q + q) * NT + h * SB + tid + q];
-                            y.x += c.x; y.y += c.y;
-                        }
+                    for (int h = 0; h < RS; h++) {
+                        const float2 c = pb[(v * Q + q) * NT + h * SB + k + q];
+                        y.x += c.x; y.y += c.y;
                     }
-                    reinterpret_cast<float2*>(j.out)[k0 + tid] = y;
                 }
+                sOut[gp + v][k0 + k] = y;
             }
         }
-        if (NPB == 1) { __syncthreads(); }   // single buffer: everyone must be done reading before the next pass writes
+        if (G == 1) { __syncthreads(); }     // single buffer (never taken twice: one VFO, one pass)
     }
 }
 
@@ -343,9 +348,9 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
     using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB;
     constexpr int NB = SB - (Q - 1);
-    const int NPB = (VB == 1 && G > 1) ? 2 : 1;        // one VFO per CTA never touches the second partial-sum buffer
-    const int Gp = ((G + VB - 1) / VB) * VB;
-    const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gp * D + (size_t)NPB * VB * Q * TC::THREADS + (size_t)Gp * SB) * sizeof(float2);
+    const int NPB = G > 1 ? 2 : 1;                     // one VFO per CTA never touches the second partial-sum buffer
+    const int pv = std::min(G, fusedVfosPerBarrier);   // VFOs accumulated between two barriers
+    const size_t smem = ((size_t)SB * (D + 1) + (size_t)G * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + G - 1) / G);
@@ -364,7 +369,7 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
         g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
         B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
     }
-    fusedXlateDecimKernel<RATIO, VB, TILE><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G);
+    fusedXlateDecimKernel<RATIO, VB, TILE><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G, pv);
     B200_CHECK_LAUNCH(); countLaunch();
     if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
     return B200_OK;
