@@ -476,10 +476,18 @@ def main():
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
     ap.add_argument("--demod", action="store_true", help="include the SSB demodulator + AGC in the timed step")
     args = ap.parse_args()
+    # The contract is ONE JSON line on stdout.  Libraries below us write there too (NCCL prints its version banner on
+    # stdout when NCCL_DEBUG is set on the box): send file descriptor 1 to stderr for the duration of the run and give
+    # Python's print() the real stdout back.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
