@@ -5,7 +5,8 @@
 //
 // Stockham autosort FFT, radix 16/8/4/2 butterflies held in registers, stages exchanged through two
 // ping-pong shared-memory buffers (one barrier per stage, no bit reversal), twiddles from float64-designed
-// tables.  N <= 8192: one CTA per frame.  N > 8192: N = N1 x N2 in two kernels -- pass 1 transforms C adjacent
+// tables.  N <= 512: one CTA per frame.  Larger N: N = N1 x N2 in two kernels (register-resident passes for N1, N2 <= 256,
+// see fftColsKernel / fftRowsKernel; the generic shared-memory passes described here beyond that) -- pass 1 transforms C adjacent
 // columns (stride N2, so global reads stay 64-128 B contiguous), applies the inter-pass twiddle and leaves the
 // N1 x N2 intermediate in a small scratch ring that stays resident in the 126 MB L2; pass 2 transforms R
 // adjacent rows and emits dB (or the complex spectrum) with R-wide contiguous stores.  HBM sees the windowed
@@ -565,7 +566,7 @@ int FftPlan::create(int N_, int device_) {
     N = N_;
     logN = log2i(N);
     if ((1 << logN) != N || logN < 5 || logN > 22) { setError("fft size %d is not a power of two in [32, 4194304]", N); return B200_EINVAL; }
-    if (logN <= 13) {
+    if (logN <= 9) {           // up to 512 points: one CTA per frame (measured equal at 512, slower from 1024 up); above: two register-resident passes
         N1 = 1; N2 = N;
         B200_TRY(uploadTwiddles(&dTwN2, N, N, 1));
     }
@@ -611,17 +612,21 @@ int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, in
     }
     B200_TRY(ensureScratch(nFrames));
     const int logN1 = log2i(N1), logN2 = log2i(N2);
-    if (logN1 >= 6 && logN1 <= 8 && logN2 >= 6 && logN2 <= 8) {
-        // register-resident passes (64 = 8x8, 128 = 16x8, 256 = 16x16)
+    if (logN1 >= 4 && logN1 <= 8 && logN2 >= 4 && logN2 <= 8) {
+        // register-resident passes (16 = 4x4, 32 = 8x4, 64 = 8x8, 128 = 16x8, 256 = 16x16)
         for (int f0 = 0; f0 < nFrames; f0 += scratchFrames) {
             const int nf = std::min(scratchFrames, nFrames - f0);
             switch (logN1) {
+            case 4: B200_TRY((launchCols<4, 4>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            case 5: B200_TRY((launchCols<8, 4>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             case 6: B200_TRY((launchCols<8, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             case 7: B200_TRY((launchCols<16, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             default: B200_TRY((launchCols<16, 16>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             }
             B200_CHECK_LAUNCH();
             switch (logN2) {
+            case 4: B200_TRY((launchRows<4, 4>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            case 5: B200_TRY((launchRows<8, 4>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             case 6: B200_TRY((launchRows<8, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             case 7: B200_TRY((launchRows<16, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             default: B200_TRY((launchRows<16, 16>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;

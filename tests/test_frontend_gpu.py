@@ -51,7 +51,7 @@ def test_dc_blocker_long_stream_state_carry():
         assert err_db(fe.preproc_out(), ref) <= -80.0
 
 
-@pytest.mark.parametrize("N", [32, 256, 1024, 8192, 16384, 32768, 65536, 1 << 17, 1 << 18, 1 << 20])
+@pytest.mark.parametrize("N", [32, 256, 512, 1024, 2048, 4096, 8192, 16384, 32768, 65536, 1 << 17, 1 << 18, 1 << 20])
 def test_fft_complex_spectrum(N):
     from sdrplusplusbrown_b200 import binding
     import torch
