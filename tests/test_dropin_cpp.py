@@ -64,3 +64,34 @@ def test_iq_frontend_and_rxvfo_dropin_against_oracle(tmp_path):
         refrow = port.fft_frame(x[f * 120000:f * 120000 + 8192], w, 8192)
         strong = refrow > refrow.max() - 80.0
         assert np.max(np.abs(rows[f][strong] - refrow[strong])) <= 0.01
+
+
+def _build_module(tmp_path):
+    from sdrplusplusbrown_b200 import build
+    build.build()
+    mod = str(tmp_path / "b200_channel.so")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-shared", "-fPIC", "-pthread", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "examples", "b200_channel_module.cpp"), "-o", mod,
+                           "-L", PKG, "-lb200dsp", "-Wl,-rpath," + PKG, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"])
+    exe = str(tmp_path / "module_loader")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-pthread", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "cpp", "module_loader.cpp"), "-o", exe, "-ldl",
+                           "-L", PKG, "-lb200dsp", "-Wl,-rpath," + PKG, "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"])   # the host links the library too (dsp::stream buffers are pinned)
+    return mod, exe
+
+
+def test_module_abi_symbols_and_instance_lifecycle(tmp_path):
+    """a module built against include/module.h exports the reference's five symbols and its instances answer through
+    ModuleManager::Instance when loaded the way the reference's loader does (no device needed for this part)"""
+    mod, exe = _build_module(tmp_path)
+    out = subprocess.run([exe, mod], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "module_loader ok" in out.stdout
+
+
+@pytest.mark.gpu
+def test_module_instance_runs_a_gpu_channel(tmp_path):
+    mod, exe = _build_module(tmp_path)
+    out = subprocess.run([exe, mod, "gpu"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "module_loader ok (gpu)" in out.stdout
