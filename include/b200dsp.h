@@ -136,6 +136,8 @@ int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
  *   B200_DEMOD_NFM  dsp::demod::FM<stereo_t>   (demod/fm.h:86-103, quadrature.h:39-46); p0=lowPass p1=highPass (flags)
  *   B200_DEMOD_AM   dsp::demod::AM<stereo_t>   (demod/am.h:101-133); p0=agcMode (0 CARRIER,1 AUDIO) p1=attack p2=decay p3=dcBlockRate
  *   B200_DEMOD_USB/LSB/DSB dsp::demod::SSB<stereo_t> (demod/ssb.h:82-97); p1=attack p2=decay
+ *   B200_DEMOD_WFM  dsp::demod::BroadcastFM      (demod/broadcast_fm.h:144-190; deviation = bandwidth / 2 as in
+ *                   radio/src/demodulators/wfm.h:76); p0=stereo p1=lowPass (flags) p2=rds (must be 0: no RDS branch)
  * attack/decay/dcBlockRate are per-sample coefficients as the radio module passes them
  * (e.g. 50.0/IF rate, usb.h:34).  Demodulation runs at the VFO's out_samplerate with
  * `bandwidth` = the VFO bandwidth.  Audio (stereo {l,r}, same count as the VFO output) is
@@ -146,6 +148,7 @@ int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
 #define B200_DEMOD_USB 3
 #define B200_DEMOD_LSB 4
 #define B200_DEMOD_DSB 5
+#define B200_DEMOD_WFM 6
 int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double p1, double p2, double p3);
 /* The radio module's IF chain between the VFO and the demodulator (decoder_modules/radio/src/radio_module.h:92-98):
  * dsp::noise_reduction::NoiseBlanker (core/src/dsp/noise_reduction/noise_blanker.h:38-56; rate and level as given to

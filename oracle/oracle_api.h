@@ -88,6 +88,12 @@ int orc_ssb_process(void* h, int count, const float* in, float* outStereo);
 void* orc_am_create(int agcMode /*0 CARRIER 1 AUDIO*/, double bandwidth, double agcAttack, double agcDecay, double dcBlockRate, double samplerate); // demod/am.h
 void orc_am_destroy(void* h);
 int orc_am_process(void* h, int count, const float* in, float* outStereo);
+// demod::BroadcastFM (demod/broadcast_fm.h:34-215; radio wiring demodulators/wfm.h:76,261-263): quadrature detector, then mono
+// (MPX through the 15 kHz audio low-pass into both channels) or stereo (complex band-pass on the 19 kHz pilot, PLL,
+// delayed MPX mixed down by the squared conjugate VCO, L = (L+R)+(L-R), R = (L+R)-(L-R), audio low-pass on both).  No RDS branch.
+void* orc_wfm_create(double deviation, double samplerate, int stereo, int lowPass);
+void orc_wfm_destroy(void* h);
+int orc_wfm_process(void* h, int count, const float* in, float* outStereo);
 // radio IF chain between the VFO and the demodulator (radio_module.h:92-98): NoiseBlanker (noise_reduction/noise_blanker.h:38-56)
 // then Squelch (noise_reduction/squelch.h:55-69, the complex_t overload); either may be off.
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel);

@@ -453,6 +453,118 @@ struct FmDemod {
     }
 };
 
+// ------------------------------------------------------------------ demod::BroadcastFM — broadcast_fm.h:34-215
+// taps::bandPass<complex_t> (band_pass.h:10-24 over windowed_sinc.h:26-29): the sinc prototype is shifted to the band
+// centre by a complex exponential; every product is formed in float, in the order the complex_t operators give it
+std::vector<cf> bandPassComplex(double bandStart, double bandStop, double transWidth, double sr, bool oddTapCount) {
+    float offsetOmega = (float)hzToRads((bandStart + bandStop) / 2.0, sr);
+    int count = estimateTapCount(transWidth, sr);
+    if (oddTapCount && !(count % 2)) { count++; }
+    const double omega = hzToRads((bandStop - bandStart) / 2.0, sr);
+    std::vector<cf> taps(count);
+    const double half = (double)count / 2.0;
+    const double corr = 1.0 * omega / PI_D;
+    for (int i = 0; i < count; i++) {
+        const double t = (double)i - half + 0.5;
+        const double n = t - half;
+        const float x = -offsetOmega * (float)n;
+        const float wnd = (float)nuttall(n, (double)count);
+        const cf w{ cosf(x) * wnd, sinf(x) * wnd };                          // phasor * (double)nuttall
+        const cf c{ (float)sincD(t * omega), 0.0f };
+        const cf p{ (c.re * w.re) - (c.im * w.im), (c.im * w.re) + (c.re * w.im) };   // complex_t::operator*(complex_t)
+        taps[i] = cf{ p.re * (float)corr, p.im * (float)corr };
+    }
+    return taps;
+}
+struct WfmDemod {
+    float invDeviation = 0.f, qphase = 0.0f;
+    bool stereo = false, lowPassOn = true;
+    std::vector<cf> pilotTaps; std::vector<cf> pilotBuf;       // FIR<complex_t, complex_t>: [history | block]
+    float alpha = 0.f, beta = 0.f, pllPhase = 0.f, pllFreq = 0.f, minFreq = 0.f, maxFreq = 0.f;
+    int delay = 0; std::vector<float> lprBuf; std::vector<cf> lmrBuf;   // math::Delay buffers: [delay samples | block]
+    Fir<float> alFir, arFir;
+    std::vector<float> mpx, l, r, lmr; std::vector<cf> rtoc, pil, vco, lmrD;
+    void init(double deviation, double sr, bool st, bool lp) {
+        stereo = st; lowPassOn = lp;
+        invDeviation = (float)(1.0 / hzToRads(deviation, sr));
+        pilotTaps = bandPassComplex(18750.0, 19250.0, 3000.0, sr, true);
+        pilotBuf.assign(pilotTaps.size() + 4096, cf{ 0.f, 0.f });
+        // PLL::init -> PhaseControlLoop<float>::criticallyDamped (phase_control_loop.h:30-35), evaluated in float
+        {
+            const float bandwidth = (float)(25000.0 / sr);
+            const float damp = sqrt(2.0) / 2.0;
+            const float den = (1.0 + 2.0 * damp * bandwidth + bandwidth * bandwidth);
+            alpha = (4 * damp * bandwidth) / den;
+            beta = (4 * bandwidth * bandwidth) / den;
+        }
+        pllPhase = 0.0f; pllFreq = (float)hzToRads(19000.0, sr);
+        minFreq = (float)hzToRads(18750.0, sr); maxFreq = (float)hzToRads(19250.0, sr);
+        delay = (((int)pilotTaps.size() - 1) / 2) + 1;
+        lprBuf.assign(delay + 4096, 0.f); lmrBuf.assign(delay + 4096, cf{ 0.f, 0.f });
+        std::vector<float> at = lowPass(15000.0, 4000.0, sr);
+        alFir.init(at); arFir.init(at);
+    }
+    template <typename V> static void fit(V& v, size_t n) { if (v.size() < n) { v.resize(n); } }
+    int process(int count, const cf* in, float* outStereo) {
+        fit(mpx, count); fit(l, count); fit(r, count); fit(lmr, count); fit(rtoc, count); fit(pil, count); fit(vco, count); fit(lmrD, count);
+        for (int i = 0; i < count; i++) {
+            const float cphase = atan2f(in[i].im, in[i].re);
+            mpx[i] = normalizePhase(cphase - qphase) * invDeviation;
+            qphase = cphase;
+        }
+        if (!stereo) {
+            if (lowPassOn) { alFir.processFir(count, mpx.data(), mpx.data()); }
+            for (int i = 0; i < count; i++) { outStereo[2 * i] = mpx[i]; outStereo[2 * i + 1] = mpx[i]; }
+            return count;
+        }
+        for (int i = 0; i < count; i++) { rtoc[i] = cf{ mpx[i], 0.0f }; }
+        // pilot band-pass: complex taps x complex data (volk_32fc_x2_dot_prod_32fc, generic)
+        const int nt = (int)pilotTaps.size();
+        fit(pilotBuf, (size_t)nt + count);
+        memcpy(&pilotBuf[nt - 1], rtoc.data(), count * sizeof(cf));
+        for (int i = 0; i < count; i++) {
+            float sr = 0.0f, si = 0.0f;
+            for (int k = 0; k < nt; k++) {
+                const cf a = pilotBuf[i + k], b = pilotTaps[k];
+                sr += a.re * b.re - a.im * b.im;
+                si += a.re * b.im + a.im * b.re;
+            }
+            pil[i] = cf{ sr, si };
+        }
+        memmove(pilotBuf.data(), &pilotBuf[count], (nt - 1) * sizeof(cf));
+        // PLL::process (pll.h:64-70) over PhaseControlLoop::advance (phase_control_loop.h:58-66), phase kept in [-pi, pi]
+        for (int i = 0; i < count; i++) {
+            vco[i] = cf{ cosf(pllPhase), sinf(pllPhase) };
+            const float err = normalizePhase(atan2f(pil[i].im, pil[i].re) - pllPhase);
+            pllFreq += beta * err;
+            if (pllFreq > maxFreq) { pllFreq = maxFreq; } else if (pllFreq < minFreq) { pllFreq = minFreq; }
+            pllPhase += pllFreq + (alpha * err);
+            while (pllPhase > PI_F) { pllPhase -= (PI_F - (-PI_F)); }
+            while (pllPhase < -PI_F) { pllPhase += (PI_F - (-PI_F)); }
+        }
+        // Delay (math/delay.h:44-52) of the MPX and of its complex copy
+        fit(lprBuf, (size_t)delay + count); fit(lmrBuf, (size_t)delay + count);
+        memcpy(&lprBuf[delay], mpx.data(), count * sizeof(float));
+        memcpy(mpx.data(), lprBuf.data(), count * sizeof(float));
+        memmove(lprBuf.data(), &lprBuf[count], delay * sizeof(float));
+        memcpy(&lmrBuf[delay], rtoc.data(), count * sizeof(cf));
+        memcpy(lmrD.data(), lmrBuf.data(), count * sizeof(cf));
+        memmove(lmrBuf.data(), &lmrBuf[count], delay * sizeof(cf));
+        for (int i = 0; i < count; i++) {
+            const cf c{ vco[i].re, -vco[i].im };
+            cf a = lmrD[i];
+            a = cf{ a.re * c.re - a.im * c.im, a.re * c.im + a.im * c.re };
+            a = cf{ a.re * c.re - a.im * c.im, a.re * c.im + a.im * c.re };
+            lmr[i] = a.re * 2.0f;
+            l[i] = mpx[i] + lmr[i];
+            r[i] = mpx[i] - lmr[i];
+        }
+        if (lowPassOn) { alFir.processFir(count, l.data(), l.data()); arFir.processFir(count, r.data(), r.data()); }
+        for (int i = 0; i < count; i++) { outStereo[2 * i] = l[i]; outStereo[2 * i + 1] = r[i]; }
+        return count;
+    }
+};
+
 // ------------------------------------------------------------------ demod::SSB — ssb.h:23-36,82-123
 struct SsbDemod {
     Xlator xl; Agc<float> agc;
@@ -691,6 +803,9 @@ int orc_ssb_process(void* h, int count, const float* in, float* out) { return ((
 void* orc_am_create(int agcMode, double bw, double att, double dec, double dcRate, double sr) { auto* d = new AmDemod; d->init(agcMode, bw, att, dec, dcRate, sr); return d; }
 void orc_am_destroy(void* h) { delete (AmDemod*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) { return ((AmDemod*)h)->process(count, (const cf*)in, out); }
+void* orc_wfm_create(double deviation, double samplerate, int stereo, int lowPass) { auto* d = new WfmDemod; d->init(deviation, samplerate, stereo != 0, lowPass != 0); return d; }
+void orc_wfm_destroy(void* h) { delete (WfmDemod*)h; }
+int orc_wfm_process(void* h, int count, const float* in, float* out) { return ((WfmDemod*)h)->process(count, (const cf*)in, out); }
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int sqOn, double sqLevel) { auto* c = new IfChain; c->init(nbOn, nbRate, nbLevel, sqOn, sqLevel); return c; }
 void orc_ifchain_destroy(void* h) { delete (IfChain*)h; }
 int orc_ifchain_process(void* h, int count, const float* in, float* out) { return ((IfChain*)h)->process(count, (const cf*)in, (cf*)out); }

@@ -44,6 +44,7 @@
 #include <dsp/demod/am.h>
 #include <dsp/loop/agc.h>
 #include <dsp/filter/deephasis.h>
+#include <dsp/demod/broadcast_fm.h>
 #include <dsp/noise_reduction/noise_blanker.h>
 #include <dsp/noise_reduction/squelch.h>
 #undef protected
@@ -256,6 +257,16 @@ void* orc_am_create(int agcMode, double bandwidth, double agcAttack, double agcD
 void orc_am_destroy(void* h) { delete (dsp::demod::AM<stereo_t>*)h; }
 int orc_am_process(void* h, int count, const float* in, float* out) {
     return ((dsp::demod::AM<stereo_t>*)h)->process(count, (complex_t*)in, (stereo_t*)out);
+}
+void* orc_wfm_create(double deviation, double samplerate, int stereo, int lowPass) {
+    auto* d = new dsp::demod::BroadcastFM;
+    d->init(NULL, deviation, samplerate, stereo != 0, lowPass != 0, false);
+    return d;
+}
+void orc_wfm_destroy(void* h) { delete (dsp::demod::BroadcastFM*)h; }
+int orc_wfm_process(void* h, int count, const float* in, float* out) {
+    int rdsCount = 0;
+    return ((dsp::demod::BroadcastFM*)h)->process(count, (complex_t*)in, (stereo_t*)out, rdsCount, NULL);
 }
 namespace { struct IfChain { dsp::noise_reduction::NoiseBlanker nb; dsp::noise_reduction::Squelch sq; bool nbOn, sqOn; }; }
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel) {

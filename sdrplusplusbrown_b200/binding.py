@@ -101,7 +101,7 @@ for _name, (_res, _args) in _SIGS.items():
 
 ROTATOR_FAST, ROTATOR_EXACT = 0, 1
 OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS, OPT_TILE_SAMPLES = 1, 2, 3
-DEMOD_NONE, DEMOD_NFM, DEMOD_AM, DEMOD_USB, DEMOD_LSB, DEMOD_DSB = 0, 1, 2, 3, 4, 5
+DEMOD_NONE, DEMOD_NFM, DEMOD_AM, DEMOD_USB, DEMOD_LSB, DEMOD_DSB, DEMOD_WFM = 0, 1, 2, 3, 4, 5, 6
 
 
 class B200Error(RuntimeError):

@@ -27,6 +27,7 @@ struct SeqState {
     float2 rotPhase;      // SSB rotator, EXACT mode: the reference's fp32 phase
     float2 deLast;        // Deemphasis<stereo_t>::lastOut (deephasis.h:92)
     float nbAmp;          // NoiseBlanker::amp (noise_blanker.h:62)
+    float pllPhase, pllFreq;   // PhaseControlLoop::phase / freq of the WFM pilot PLL (phase_control_loop.h:69-70)
 };
 
 struct DemodState {
@@ -55,7 +56,19 @@ struct DemodState {
     // radio IF chain in front of the demodulator (radio_module.h:92-98): NoiseBlanker -> Squelch
     bool nbOn = false, sqOn = false; float nbRate = 0.f, nbLevel = 0.f, sqLevel = 0.f;
     cf32* dIf = nullptr; int ifCap = 0;
+    // broadcast FM stereo (demod/broadcast_fm.h:144-190)
+    bool wfmStereo = false;
+    Stage pilotRe, pilotIm;                  // the complex pilot band-pass on the real MPX = two real FIRs (real / imaginary taps)
+    Stage firR;                              // right-channel audio low-pass (`fir` serves the left channel / mono)
+    float pllAlpha = 0.f, pllBeta = 0.f, pllMinFreq = 0.f, pllMaxFreq = 0.f;
+    int wfmDelay = 0; float* dDelayHist[2] = { nullptr, nullptr }; int delayCur = 0;   // math::Delay of the MPX
+    float* dPllPhase = nullptr; float* dL = nullptr; float* dR = nullptr;
 };
+
+// per-call descriptors of the WFM stereo stages
+struct PllJob { const float* pr; const float* pi; float* phaseOut; SeqState* st; float alpha, beta, minFreq, maxFreq; int n, pad; };
+struct WfmMixJob { const float* mpx; const float* hist; float* histNext; const float* phase; float* l; float* r; int n, delay; };
+struct LrJob { const float* l; const float* r; float* stereo; int n, pad; };
 
 // per-call descriptor of the IF chain
 struct IfJob { const cf32* in; cf32* out; SeqState* st; float rate, invRate, nbLevel, sqLevel; int n, nbOn, sqOn, pad; };
@@ -431,6 +444,72 @@ __global__ void __launch_bounds__(256) stereoKernel(const DemodJob* __restrict__
     reinterpret_cast<float2*>(j.stereo)[i] = make_float2(v, v);
 }
 
+// ---- broadcast FM stereo ------------------------------------------------------------------------------------
+// Pilot PLL (loop/pll.h:64-70 over phase_control_loop.h:58-66), one warp per VFO.  The warp turns a chunk of pilot
+// samples into phases (atan2f) in shared memory, lane 0 walks the second-order loop -- frequency and phase both depend
+// on the previous sample's error, so the walk is sequential -- and the warp writes the VCO phase of every sample out.
+constexpr int kPllChunk = 512;
+__global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs) {
+    const PllJob j = jobs[blockIdx.x];
+    __shared__ float sIn[kPllChunk], sOut[kPllChunk];
+    const int lane = threadIdx.x;
+    const float PI = 3.1415926535f;      // FL_M_PI (math/constants.h:4); phase limits -PI..PI, phaseDelta = 2*PI
+    float phase = j.st->pllPhase, freq = j.st->pllFreq;
+    for (int base = 0; base < j.n; base += kPllChunk) {
+        const int m = min(kPllChunk, j.n - base);
+        for (int i = lane; i < m; i += 32) { sIn[i] = atan2f(__ldg(j.pi + base + i), __ldg(j.pr + base + i)); }
+        __syncwarp();
+        if (lane == 0) {
+            for (int i = 0; i < m; i++) {
+                sOut[i] = phase;
+                float err = __fsub_rn(sIn[i], phase);
+                if (err > PI) { err = __fsub_rn(err, 2.0f * PI); }
+                else if (err <= -PI) { err = __fadd_rn(err, 2.0f * PI); }
+                freq = __fadd_rn(freq, __fmul_rn(j.beta, err));
+                freq = fminf(fmaxf(freq, j.minFreq), j.maxFreq);
+                phase = __fadd_rn(phase, __fadd_rn(freq, __fmul_rn(j.alpha, err)));
+                while (phase > PI) { phase = __fsub_rn(phase, __fsub_rn(PI, -PI)); }
+                while (phase < -PI) { phase = __fadd_rn(phase, __fsub_rn(PI, -PI)); }
+            }
+        }
+        __syncwarp();
+        for (int i = lane; i < m; i += 32) { j.phaseOut[base + i] = sOut[i]; }
+        __syncwarp();
+    }
+    if (lane == 0) { j.st->pllPhase = phase; j.st->pllFreq = freq; }
+}
+
+// broadcast_fm.h:157-179: the MPX delayed by the pilot filter's group delay is mixed down by the squared conjugate VCO
+// (the 19 kHz pilot doubled to the 38 kHz subcarrier), L-R = 2 * Re(.), L = (L+R) + (L-R), R = (L+R) - (L-R).
+// Also refreshes the delay line: histNext[i] = [hist | mpx][n + i].
+__global__ void __launch_bounds__(256) wfmMixKernel(const WfmMixJob* __restrict__ jobs) {
+    const WfmMixJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < j.delay) {
+        const int p = j.n + i;                        // position in [hist (delay) | mpx (n)]
+        j.histNext[i] = (p < j.delay) ? j.hist[p] : j.mpx[p - j.delay];
+    }
+    if (i >= j.n) { return; }
+    const float x = (i < j.delay) ? j.hist[i] : j.mpx[i - j.delay];
+    float sn, cs;
+    sincosf(j.phase[i], &sn, &cs);
+    const float cr = cs, ci = -sn;                    // conjugate of the VCO phasor
+    // (x, 0) * c * c with the reference's complex product (re*re - im*im, re*im + im*re)
+    const float a1r = __fsub_rn(__fmul_rn(x, cr), __fmul_rn(0.0f, ci)), a1i = __fadd_rn(__fmul_rn(x, ci), __fmul_rn(0.0f, cr));
+    const float a2r = __fsub_rn(__fmul_rn(a1r, cr), __fmul_rn(a1i, ci));
+    const float lmr = __fmul_rn(a2r, 2.0f);
+    j.l[i] = __fadd_rn(x, lmr);
+    j.r[i] = __fsub_rn(x, lmr);
+}
+
+// LRToStereo (convert/l_r_to_stereo.h)
+__global__ void __launch_bounds__(256) lrKernel(const LrJob* __restrict__ jobs) {
+    const LrJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= j.n) { return; }
+    reinterpret_cast<float2*>(j.stereo)[i] = make_float2(__ldg(j.l + i), __ldg(j.r + i));
+}
+
 // radio IF chain, one CTA per VFO.
 // NoiseBlanker (noise_blanker.h:38-56): amp follows the input amplitude as a first-order recurrence that only advances
 // on non-zero samples; a sample whose amplitude exceeds level x amp is scaled down to amp.  The recurrence is linear,
@@ -547,6 +626,11 @@ void demodDestroy(DemodState* d) {
     if (d->dAmps) { cudaFree(d->dAmps); }
     if (d->dStereo) { cudaFree(d->dStereo); }
     if (d->dIf) { cudaFree(d->dIf); }
+    d->pilotRe.destroy(); d->pilotIm.destroy(); d->firR.destroy();
+    for (int i = 0; i < 2; i++) { if (d->dDelayHist[i]) { cudaFree(d->dDelayHist[i]); } }
+    if (d->dPllPhase) { cudaFree(d->dPllPhase); }
+    if (d->dL) { cudaFree(d->dL); }
+    if (d->dR) { cudaFree(d->dR); }
     delete d;
 }
 
@@ -584,6 +668,15 @@ static int demodEnsureCap(DemodState& d, int n) {
     B200_CUDA(cudaMalloc((void**)&d.dMono, (size_t)d.cap * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&d.dStereo, (size_t)d.cap * 2 * sizeof(float)));
     if (d.hasFir) { B200_TRY(d.fir.ensureOutCap(d.cap)); }
+    if (d.wfmStereo) {
+        for (float** p : { &d.dPllPhase, &d.dL, &d.dR }) {
+            if (*p) { cudaFree(*p); *p = nullptr; }
+            B200_CUDA(cudaMalloc((void**)p, (size_t)d.cap * sizeof(float)));
+        }
+        B200_TRY(d.pilotRe.ensureOutCap(d.cap));
+        B200_TRY(d.pilotIm.ensureOutCap(d.cap));
+        if (d.hasFir) { B200_TRY(d.firR.ensureOutCap(d.cap)); }
+    }
     return B200_OK;
 }
 
@@ -616,6 +709,37 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
         else if (hp) { firTaps = design::highPass(300.0, 100.0, d->sr); }                       // fm.h:130-132
         else if (lp) { firTaps = design::lowPass(d->bw / 2.0, (d->bw / 2.0) * 0.1, d->sr); }   // fm.h:133-135
     }
+    else if (kind == B200_DEMOD_WFM) {
+        // demod.init(input, bandwidth / 2, 500 kS/s, stereo, lowPass, rds) (radio/src/demodulators/wfm.h:76)
+        if (p2 != 0.0) { setError("the RDS branch of the broadcast FM demodulator is not provided"); v.demod = nullptr; delete d; return B200_EINVAL; }
+        d->invDeviation = (float)(1.0 / design::hzToRads(d->bw / 2.0, d->sr));
+        d->wfmStereo = p0 != 0.0;
+        d->filtering = p1 != 0.0;
+        if (d->filtering) { firTaps = design::lowPass(15000.0, 4000.0, d->sr); }              // broadcast_fm.h:49
+        if (d->wfmStereo) {
+            std::vector<float> tr, ti;
+            design::bandPassComplex(18750.0, 19250.0, 3000.0, d->sr, true, tr, ti);             // broadcast_fm.h:43
+            if (tr.empty()) { setError("pilot filter has no taps at %g S/s", d->sr); v.demod = nullptr; delete d; return B200_EINVAL; }
+            B200_TRY(d->pilotRe.create(JOB_DECIM_FIR, tr, 1, 1, 1, 1, 64));
+            B200_TRY(d->pilotIm.create(JOB_DECIM_FIR, ti, 1, 1, 1, 1, 64));
+            d->wfmDelay = (((int)tr.size() - 1) / 2) + 1;                                        // broadcast_fm.h:47-48
+            for (int i = 0; i < 2; i++) {
+                B200_CUDA(cudaMalloc((void**)&d->dDelayHist[i], (size_t)d->wfmDelay * sizeof(float)));
+                B200_CUDA(cudaMemset(d->dDelayHist[i], 0, (size_t)d->wfmDelay * sizeof(float)));
+            }
+            // PLL::init(bandwidth = 25000 / fs, phase 0, freq 19 kHz, limits 18.75 .. 19.25 kHz) (broadcast_fm.h:46),
+            // PhaseControlLoop<float>::criticallyDamped evaluated in float (phase_control_loop.h:30-35)
+            const float bandwidth = (float)(25000.0 / d->sr);
+            const float damp = sqrt(2.0) / 2.0;
+            const float den = (1.0 + 2.0 * damp * bandwidth + bandwidth * bandwidth);
+            d->pllAlpha = (4 * damp * bandwidth) / den;
+            d->pllBeta = (4 * bandwidth * bandwidth) / den;
+            d->pllMinFreq = (float)design::hzToRads(18750.0, d->sr);
+            d->pllMaxFreq = (float)design::hzToRads(19250.0, d->sr);
+            init.pllPhase = 0.0f;
+            init.pllFreq = (float)design::hzToRads(19000.0, d->sr);
+        }
+    }
     else if (kind == B200_DEMOD_AM) {
         d->agcMode = (int)p0;
         agcInit(p1, p2);
@@ -642,6 +766,7 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
     }
     if (!firTaps.empty()) {
         B200_TRY(d->fir.create(JOB_DECIM_FIR, firTaps, 1, 1, 1, 1, 64));
+        if (d->wfmStereo) { B200_TRY(d->firR.create(JOB_DECIM_FIR, firTaps, 1, 1, 1, 1, 64)); }
         d->hasFir = true;
     }
     B200_CUDA(cudaMalloc((void**)&d->dState, sizeof(SeqState)));
@@ -707,7 +832,11 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     std::vector<std::vector<FirJob>> afWaves;   // wave k = stage k of every VFO's audio resampler
     std::vector<DeemphJob> deJobs;
     std::vector<IfJob> ifJobs;
-    int maxN = 0;
+    std::vector<FirJob> wfmA, wfmB;             // WFM stereo: pilot band-pass (two real FIRs), then the two audio low-passes
+    std::vector<PllJob> pllJobs;
+    std::vector<WfmMixJob> mixJobs;
+    std::vector<LrJob> lrJobs;
+    int maxN = 0, maxMix = 0;
     for (size_t vi = 0; vi < bank.vfos.size(); vi++) {
         Vfo& v = bank.vfos[vi];
         if (!v.live || !v.demod) { continue; }
@@ -737,7 +866,30 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         j.agc = d.agc; j.angle0 = d.angle; j.theta = d.theta; j.stepRe = d.dRe; j.stepIm = d.dIm;
         j.invDeviation = d.invDeviation; j.dcRate = d.dcRate; j.kind = d.kind; j.agcMode = d.agcMode; j.n = n; j.quadParity = d.quadParity;
         const float* src = d.dMono;
-        if (d.hasFir && d.filtering) {
+        const bool wfmStereo = d.kind == B200_DEMOD_WFM && d.wfmStereo;
+        if (wfmStereo) {
+            FirJob f;
+            d.pilotRe.fillJob(f, d.dMono, n); wfmA.push_back(f); d.pilotRe.advance(n);
+            d.pilotIm.fillJob(f, d.dMono, n); wfmA.push_back(f); d.pilotIm.advance(n);
+            PllJob pj{};
+            pj.pr = (const float*)d.pilotRe.dOut; pj.pi = (const float*)d.pilotIm.dOut; pj.phaseOut = d.dPllPhase; pj.st = d.dState;
+            pj.alpha = d.pllAlpha; pj.beta = d.pllBeta; pj.minFreq = d.pllMinFreq; pj.maxFreq = d.pllMaxFreq; pj.n = n;
+            if (n > 0) { pllJobs.push_back(pj); }
+            WfmMixJob mj{};
+            mj.mpx = d.dMono; mj.hist = d.dDelayHist[d.delayCur]; mj.histNext = d.dDelayHist[d.delayCur ^ 1]; mj.phase = d.dPllPhase;
+            mj.l = d.dL; mj.r = d.dR; mj.n = n; mj.delay = d.wfmDelay;
+            mixJobs.push_back(mj);
+            d.delayCur ^= 1;
+            maxMix = std::max(maxMix, std::max(n, d.wfmDelay));
+            const float* lsrc = d.dL; const float* rsrc = d.dR;
+            if (d.hasFir && d.filtering) {
+                d.fir.fillJob(f, d.dL, n); wfmB.push_back(f); d.fir.advance(n);
+                d.firR.fillJob(f, d.dR, n); wfmB.push_back(f); d.firR.advance(n);
+                lsrc = (const float*)d.fir.dOut; rsrc = (const float*)d.firR.dOut;
+            }
+            if (n > 0) { lrJobs.push_back(LrJob{ lsrc, rsrc, d.dStereo, n, 0 }); }
+        }
+        else if (d.hasFir && d.filtering) {
             FirJob f; d.fir.fillJob(f, d.dMono, n);
             firs.push_back(f);
             d.fir.advance(n);
@@ -764,7 +916,10 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             d.lastAudio = (const float*)data; d.lastAudioCount = m;
         }
         if (n > 0) {
-            if (d.kind == B200_DEMOD_NFM) { quad.push_back(j); d.quadParity ^= 1; }
+            if (d.kind == B200_DEMOD_NFM || d.kind == B200_DEMOD_WFM) {
+                quad.push_back(j); d.quadParity ^= 1;
+                if (wfmStereo) { maxN = std::max(maxN, n); continue; }      // its stereo rows come from lrKernel, not stereoKernel
+            }
             else {
                 const bool isSsb = (d.kind != B200_DEMOD_AM);
                 const bool fastSsb = isSsb && !j.exact && d.agc.attack > 0.0f && d.dMaps;
@@ -779,12 +934,13 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             maxN = std::max(maxN, n);
         }
     }
-    if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty()) { return B200_OK; }
+    if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty() && wfmA.empty()) { return B200_OK; }
     // one upload: [seq][quad][all][firs][ssb][af waves][deemph]
     size_t afJobs = 0;
     for (auto& w : afWaves) { afJobs += w.size(); }
     const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + (firs.size() + afJobs) * sizeof(FirJob) +
-                         deJobs.size() * sizeof(DeemphJob) + ifJobs.size() * sizeof(IfJob) + 64 * (afWaves.size() + 10);
+                         deJobs.size() * sizeof(DeemphJob) + ifJobs.size() * sizeof(IfJob) + (wfmA.size() + wfmB.size()) * sizeof(FirJob) +
+                         pllJobs.size() * sizeof(PllJob) + mixJobs.size() * sizeof(WfmMixJob) + lrJobs.size() * sizeof(LrJob) + 64 * (afWaves.size() + 16);
     void* hp = nullptr; int slot = 0;
     B200_TRY(bank.ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -798,6 +954,11 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     for (size_t w = 0; w < afWaves.size(); w++) { oW[w] = put(afWaves[w].data(), afWaves[w].size() * sizeof(FirJob)); }
     const size_t oD = put(deJobs.data(), deJobs.size() * sizeof(DeemphJob));
     const size_t oI = put(ifJobs.data(), ifJobs.size() * sizeof(IfJob));
+    const size_t oWA = put(wfmA.data(), wfmA.size() * sizeof(FirJob));
+    const size_t oWB = put(wfmB.data(), wfmB.size() * sizeof(FirJob));
+    const size_t oP = put(pllJobs.data(), pllJobs.size() * sizeof(PllJob));
+    const size_t oM = put(mixJobs.data(), mixJobs.size() * sizeof(WfmMixJob));
+    const size_t oL = put(lrJobs.data(), lrJobs.size() * sizeof(LrJob));
     if (off > bank.dDemodDescBytes) {
         B200_CUDA(cudaStreamSynchronize(s));
         if (bank.dDemodDesc) { cudaFree(bank.dDemodDesc); }
@@ -813,6 +974,29 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     if (!quad.empty()) {
         quadratureKernel<<<dim3((maxN + 255) / 256, (unsigned)quad.size()), 256, 0, s>>>((const DemodJob*)(dd + oQ));
         B200_CHECK_LAUNCH(); countLaunch();
+    }
+    if (!wfmA.empty()) {
+        // broadcast FM stereo: pilot band-pass -> PLL -> mix-down + matrix -> audio low-passes -> interleave
+        int maxH = 0;
+        for (auto& f : wfmA) { maxH = std::max(maxH, f.H); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oWA), wfmA.data(), (int)wfmA.size(), 1, s));
+        B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oWA), (int)wfmA.size(), maxH, s));
+        if (!pllJobs.empty()) {
+            pllKernel<<<(unsigned)pllJobs.size(), 32, 0, s>>>((const PllJob*)(dd + oP));
+            B200_CHECK_LAUNCH(); countLaunch();
+        }
+        wfmMixKernel<<<dim3((maxMix + 255) / 256, (unsigned)mixJobs.size()), 256, 0, s>>>((const WfmMixJob*)(dd + oM));
+        B200_CHECK_LAUNCH(); countLaunch();
+        if (!wfmB.empty()) {
+            maxH = 0;
+            for (auto& f : wfmB) { maxH = std::max(maxH, f.H); }
+            B200_TRY(launchFirJobs((const FirJob*)(dd + oWB), wfmB.data(), (int)wfmB.size(), 1, s));
+            B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oWB), (int)wfmB.size(), maxH, s));
+        }
+        if (!lrJobs.empty()) {
+            lrKernel<<<dim3((maxN + 255) / 256, (unsigned)lrJobs.size()), 256, 0, s>>>((const LrJob*)(dd + oL));
+            B200_CHECK_LAUNCH(); countLaunch();
+        }
     }
     if (!ssb.empty()) {
         int maxS = 0;

@@ -95,6 +95,28 @@ inline std::vector<float> bandPass(double lo, double hi, double transWidth, doub
                         [=](double n, double N) { return (double)(2.0f * cosf(w0 * (float)n)) * nuttall(n, N); });
 }
 
+// taps::bandPass<complex_t> (taps/band_pass.h:10-24 over windowed_sinc.h:26-29): the low-pass prototype shifted to the
+// band centre by a complex exponential; the products are formed in float in the order the reference's complex_t
+// operators give them.  Real and imaginary parts are returned separately (the pilot filter runs as two real FIRs).
+inline void bandPassComplex(double lo, double hi, double transWidth, double sr, bool oddTapCount, std::vector<float>& re, std::vector<float>& im) {
+    const float w0 = (float)hzToRads((lo + hi) / 2.0, sr);
+    int count = estimateTapCount(transWidth, sr);
+    if (oddTapCount && !(count % 2)) { count++; }
+    re.assign((size_t)std::max(count, 0), 0.0f); im.assign((size_t)std::max(count, 0), 0.0f);
+    const double omega = hzToRads((hi - lo) / 2.0, sr);
+    const double half = (double)count / 2.0, corr = 1.0 * omega / kPi;
+    for (int i = 0; i < count; i++) {
+        const double t = (double)i - half + 0.5, n = t - half;
+        const float x = -w0 * (float)n;
+        const float wnd = (float)nuttall(n, (double)count);
+        const float wr = cosf(x) * wnd, wi = sinf(x) * wnd;
+        const double a = t * omega;
+        const float cr = (float)((a == 0.0) ? 1.0 : sin(a) / a), ci = 0.0f;          // math::sinc (math/sinc.h:5-7)
+        const float pr = (cr * wr) - (ci * wi), pi = (ci * wr) + (cr * wi);
+        re[i] = pr * (float)corr; im[i] = pi * (float)corr;
+    }
+}
+
 // ---- FFT window with the fft-shift alternation (iq_frontend.cpp:303-311)
 inline std::vector<float> fftWindow(int type, int nz) {
     std::vector<float> w((size_t)nz);

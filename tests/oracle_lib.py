@@ -65,6 +65,9 @@ _SIGS = {
     "orc_am_create": (_vp, [_i, _d, _d, _d, _d, _d]),
     "orc_am_destroy": (None, [_vp]),
     "orc_am_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_wfm_create": (_vp, [_d, _d, _i, _i]),
+    "orc_wfm_destroy": (None, [_vp]),
+    "orc_wfm_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_ifchain_create": (_vp, [_i, _d, _d, _i, _d]),
     "orc_ifchain_destroy": (None, [_vp]),
     "orc_ifchain_process": (_i, [_vp, _i, _vp, _vp]),
@@ -290,6 +293,18 @@ class Ssb(_Demod):
 class Am(_Demod):
     def __init__(self, orc, agc_mode, bw, attack, decay, dc_rate, sr):
         super().__init__(orc, orc.lib.orc_am_create(agc_mode, bw, attack, decay, dc_rate, sr), "orc_am")
+
+
+class Wfm(_Block):
+    """demod::BroadcastFM (mono or stereo, no RDS): complex IF in, stereo audio out at the same rate"""
+    def __init__(self, orc, deviation, samplerate, stereo, low_pass=True):
+        super().__init__(orc, orc.lib.orc_wfm_create(deviation, samplerate, int(stereo), int(low_pass)), "orc_wfm")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros((len(x), 2), np.float32)
+        n = self.orc.lib.orc_wfm_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:n]
 
 
 class IfChain(_Block):

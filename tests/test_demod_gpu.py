@@ -249,3 +249,62 @@ def test_if_chain_noise_blanker_and_squelch_match_oracle(nb, rate_hz, nb_level, 
         assert states == [False, False, True]
     else:
         assert states == [False, False, False]
+
+
+def _stereo_fm_iq(n, in_sr, off, seed=0):
+    """broadcast-FM test signal at `off` Hz: L = 1 kHz, R = 2.5 kHz, 19 kHz pilot, L-R on the 38 kHz subcarrier"""
+    t = np.arange(n) / in_sr
+    L = 0.5 * np.sin(2 * np.pi * 1000.0 * t)
+    R = 0.4 * np.sin(2 * np.pi * 2500.0 * t)
+    mpx = 0.45 * (L + R) + 0.1 * np.sin(2 * np.pi * 19000.0 * t) + 0.45 * (L - R) * np.sin(2 * np.pi * 38000.0 * t)
+    ph = 2 * np.pi * 75e3 * np.cumsum(mpx) / in_sr + 2 * np.pi * off * t
+    rng = np.random.default_rng(seed)
+    x = 0.5 * np.exp(1j * ph) + 0.002 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))
+    return x.astype(np.complex64)
+
+
+@pytest.mark.parametrize("stereo,low_pass", [(0, 1), (1, 1), (1, 0), (0, 0)])
+def test_wfm_broadcast_fm_matches_oracle(stereo, low_pass):
+    """VFO (4 MS/s -> 500 kS/s, the radio's WFM IF rate) -> BroadcastFM (mono, or stereo through the pilot PLL) against
+    the oracle chain, ragged blocks.  Stereo: the pilot PLL is a feedback loop, both sides start it from the same state
+    and see the same samples to -80 dB, so the decoded channels must agree to -80 dB too."""
+    from sdrplusplusbrown_b200 import binding
+    in_sr, out_sr, bw, off = 4e6, 500e3, 150e3, 600e3
+    n = 8 * 60000
+    x = _stereo_fm_iq(n, in_sr, off)
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_dem = ol.Wfm(PORT, bw / 2.0, out_sr, stereo, low_pass)
+    b = binding.VfoBank(in_sr, max_block=300000)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, binding.DEMOD_WFM, stereo, low_pass, 0, 0)
+    got_all, ref_all = [], []
+    for blk in split(x, [8 * 17000, 8 * 20000 + 3, 8 * 9000, 41]):
+        iq = o_vfo.process(blk)
+        ref = o_dem.process(iq) if len(iq) else np.zeros((0, 2), np.float32)
+        b.process(to_dev(blk))
+        assert b.out_count(v) == len(ref)
+        if len(ref):
+            got = b.audio(v)
+            got_all.append(got); ref_all.append(ref)
+            if not stereo:
+                assert np.array_equal(got[:, 0], got[:, 1])
+    got, ref = np.concatenate(got_all), np.concatenate(ref_all)
+    for ch in (0, 1):
+        e = err_db(got[:, ch], ref[:, ch])
+        assert e <= -80.0, (stereo, low_pass, ch, e)
+    if stereo and low_pass:
+        # and it is a stereo decoder: after the loop has locked, the 1 kHz tone sits in L and the 2.5 kHz tone in R
+        t = np.arange(len(got)) / out_sr
+        tail = slice(len(got) // 2, None)
+        amp = lambda ch, f: abs(np.vdot(np.exp(2j * np.pi * f * t[tail]), got[tail, ch])) / len(t[tail])
+        assert amp(0, 1000.0) > 4 * amp(0, 2500.0)
+        assert amp(1, 2500.0) > 4 * amp(1, 1000.0)
+
+
+def test_wfm_rds_branch_is_refused():
+    from sdrplusplusbrown_b200 import binding
+    b = binding.VfoBank(4e6, max_block=65536)
+    v = b.add(500e3, 150e3, 0.0)
+    with pytest.raises(binding.B200Error):
+        b.set_demod(v, binding.DEMOD_WFM, 1, 1, 1, 0)

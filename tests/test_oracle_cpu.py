@@ -216,3 +216,32 @@ def test_vfo_signal_info_against_numpy():
     assert abs(st - (mx - (avg - qavg))) < 1e-3 and abs(snr - (mx - avg - (avg - qavg))) < 1e-3
     if REF is not None:
         assert REF.vfo_signal_info(row, wb, center, bw) == (st, snr)
+
+
+@needs_ref
+def test_radio_chain_blocks_port_equals_ref_bitwise():
+    """IF chain (noise blanker, squelch), AF chain (stereo resampler, de-emphasis) and BroadcastFM (mono / stereo):
+    the self-contained restatement against the reference's own headers, bit for bit, over ragged blocks."""
+    rng = np.random.default_rng(21)
+    x = ((rng.standard_normal(9000) + 1j * rng.standard_normal(9000)) * 0.05).astype(np.complex64)
+    x[100:110] *= 40
+    x[3000:3005] = 0
+    for cfg in [(1, 500 / 50e3, 3.0, 0, 0.0), (0, 0.01, 1.0, 1, -30.0), (1, 0.02, 2.0, 1, -10.0), (1, 0.02, 2.0, 1, -40.0)]:
+        p, r = ol.IfChain(PORT, *cfg), ol.IfChain(REF, *cfg)
+        for i in range(0, len(x), 1700):
+            assert p.process(x[i:i + 1700]).tobytes() == r.process(x[i:i + 1700]).tobytes(), cfg
+    au = rng.standard_normal((9000, 2)).astype(np.float32)
+    for a, b, tau in [(50e3, 48e3, 0.0), (24e3, 48e3, 50e-6), (15e3, 48e3, 75e-6), (250e3, 48e3, 50e-6), (48e3, 48e3, 50e-6), (50e3, 11025.0, 50e-6), (50e3, 12500.0, 0.0)]:
+        p, r = ol.AfPost(PORT, a, b, tau), ol.AfPost(REF, a, b, tau)
+        for i in range(0, 9000, 2500):
+            yp, yr = p.process(au[i:i + 2500]), r.process(au[i:i + 2500])
+            assert yp.shape == yr.shape and yp.tobytes() == yr.tobytes(), (a, b, tau)
+    sr, n = 500e3, 40000
+    t = np.arange(n) / sr
+    L, R = 0.5 * np.sin(2 * np.pi * 1000 * t), 0.4 * np.sin(2 * np.pi * 2500 * t)
+    mpx = 0.45 * (L + R) + 0.1 * np.sin(2 * np.pi * 19000 * t) + 0.45 * (L - R) * np.sin(2 * np.pi * 38000 * t)
+    iq = np.exp(1j * 2 * np.pi * 75e3 * np.cumsum(mpx) / sr).astype(np.complex64)
+    for stereo, lp in [(0, 1), (1, 1), (1, 0)]:
+        p, r = ol.Wfm(PORT, 75e3, sr, stereo, lp), ol.Wfm(REF, 75e3, sr, stereo, lp)
+        for i in range(0, n, 17000):
+            assert p.process(iq[i:i + 17000]).tobytes() == r.process(iq[i:i + 17000]).tobytes(), (stereo, lp)
