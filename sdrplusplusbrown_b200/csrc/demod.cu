@@ -806,7 +806,7 @@ static int afConfigure(VfoBank& bank, Vfo& v, double audioSR, double tau) {
                 std::vector<float> t(plan->stages[i].ntaps);
                 memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());   // the table holds IEEE bit patterns
                 cap = cap / plan->stages[i].decim + 2;
-                B200_TRY(d.afDecim[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap));
+                B200_TRY(d.afDecim[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap, true));
             }
         }
         if (p.mode == 0 || p.mode == 2) {
@@ -935,6 +935,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         }
     }
     if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty() && wfmA.empty()) { return B200_OK; }
+    for (auto& w : afWaves) { firJobsBalance(w.data(), (int)w.size()); }
     // one upload: [seq][quad][all][firs][ssb][af waves][deemph]
     size_t afJobs = 0;
     for (auto& w : afWaves) { afJobs += w.size(); }

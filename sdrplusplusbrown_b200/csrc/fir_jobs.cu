@@ -12,7 +12,11 @@
 //             blocks still fill the GPU.
 //   lanes     (POLYPHASE): 8 lanes per output; a bank row is read as 128-byte runs (one float4 per lane) instead of
 //             one row per thread, partial sums folded with three shuffles.
-//   simple    one output per thread; kept for shapes the other two do not cover.
+//   plan      (DECIM_FIR whose taps are one of the later-stage tables of the pow-2 decimation plans: (D,T) = (2,69),
+//             (2,12), (4,27), (8,54), (8,44), (8,36)): 4 or 8 outputs per thread, the loop over the thread's input
+//             window fully unrolled with the taps as constant-bank operands -- each staged sample is loaded once and
+//             feeds every output it belongs to (T/D of them), against one load per tap in the simple path.
+//   simple    one output per thread; kept for shapes the others do not cover.
 #include "fir_jobs.cuh"
 
 #include <algorithm>
@@ -27,6 +31,36 @@ constexpr int kPolyLanes = 8;               // lanes per output, polyphase path
 constexpr int kPolyOutPerCta = 128;         // outputs per CTA, polyphase path (8 rounds of 16)
 constexpr int kSimpleOutPerCta = kThreads;
 constexpr size_t kSmemCap = 160 * 1024;
+
+// later-stage coefficient tables of the decimation plans in the constant bank (the same generated file the fused
+// first-stage kernel includes)
+#define DECIM_TABLE_U32(name, count) __constant__ uint32_t c_##name[count] = {
+#define DECIM_ROW(...) __VA_ARGS__,
+#define DECIM_TABLE_END };
+#define DECIM_PLAN_BEGIN(ratio, nstages)
+#define DECIM_STAGE(index, decim, name, ntaps)
+#define DECIM_PLAN_END
+#include "decim_tables.inc"
+#undef DECIM_TABLE_U32
+#undef DECIM_ROW
+#undef DECIM_TABLE_END
+#undef DECIM_PLAN_BEGIN
+#undef DECIM_STAGE
+#undef DECIM_PLAN_END
+
+template <int D, int T> struct PlanStage;
+#define B200_PLAN_STAGE(idx, D_, T_)                                                                         \
+    static_assert(sizeof(c_kDecimTaps_##idx) == (T_) * sizeof(uint32_t), "decim_tables.inc changed: stage table size"); \
+    template <> struct PlanStage<D_, T_> { static __device__ __forceinline__ float tap(int i) { return __uint_as_float(c_kDecimTaps_##idx[i]); } };
+B200_PLAN_STAGE(0, 2, 69)
+B200_PLAN_STAGE(1, 2, 12)
+B200_PLAN_STAGE(2, 4, 27)
+B200_PLAN_STAGE(3, 8, 54)
+B200_PLAN_STAGE(4, 8, 44)
+B200_PLAN_STAGE(5, 8, 36)
+#undef B200_PLAN_STAGE
+constexpr int kPlanBase = 1000;             // FirJob::plan = kPlanBase + D * 100 + T for the plan-table path
+__host__ __device__ constexpr int planOutPerThread(int D) { return D >= 8 ? 4 : 8; }
 
 template <int EF> struct Elem;
 template <> struct Elem<2> {
@@ -60,6 +94,29 @@ __device__ __forceinline__ typename Elem<EF>::T loadPos(const FirJob& j, int p) 
 
 __device__ __forceinline__ int ilog2(int v) { return 31 - __clz(v); }
 
+// stages work-buffer positions [base, base + span) into shared memory, position i in slot i + (i >> padShift).  A window
+// that lies wholly in the new block (every CTA but the first few of a job) is copied by a branch-free loop unrolled
+// eight deep, so that a thread has eight loads in flight instead of one.
+template <int EF>
+__device__ __forceinline__ void stageWindow(const FirJob& j, typename Elem<EF>::T* win, int base, int span, int padShift) {
+    using T = typename Elem<EF>::T;
+    if (base >= j.H && base - j.H + span <= j.nIn) {
+        const T* src = reinterpret_cast<const T*>(j.data) + (base - j.H);
+        int i = threadIdx.x;
+        for (; i + 7 * kThreads < span; i += 8 * kThreads) {
+            T v[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) { v[u] = __ldg(src + i + u * kThreads); }
+#pragma unroll
+            for (int u = 0; u < 8; u++) { const int p = i + u * kThreads; win[p + (p >> padShift)] = v[u]; }
+        }
+        for (; i < span; i += kThreads) { win[i + (i >> padShift)] = __ldg(src + i); }
+    }
+    else {
+        for (int i = threadIdx.x; i < span; i += kThreads) { win[i + (i >> padShift)] = loadPos<EF>(j, base + i); }
+    }
+}
+
 // ---- blocked decimating FIR --------------------------------------------------------------------------------------
 // CTA tile: (kThreads / S) threads-groups x 8 outputs.  Window position p (relative to the tile's first sample) lives
 // in slot p + p / (8*D): one pad element per thread-group stride, so the lanes of a warp (8*D samples apart) hit
@@ -77,7 +134,7 @@ __device__ __forceinline__ void blockedFir(const FirJob& j, typename Elem<EF>::T
     const int base = j.offset + k0 * j.D;
     const int span = (nk - 1) * j.D + j.T + (kR - 1) * j.D;       // the last thread's window may run past its last output
     const int sh = 3 + logD;
-    for (int i = threadIdx.x; i < span; i += kThreads) { win[i + (i >> sh)] = loadPos<EF>(j, base + i); }
+    stageWindow<EF>(j, win, base, span, sh);
     __syncthreads();
     const int grp = threadIdx.x >> logS, seg = threadIdx.x & (S - 1);
     const int kt = grp * kR;                                       // first output of this thread within the tile
@@ -134,6 +191,46 @@ __device__ __forceinline__ void blockedFir(const FirJob& j, typename Elem<EF>::T
     }
 }
 
+// ---- plan-table decimating FIR -------------------------------------------------------------------------------------
+// R consecutive outputs per thread; the thread's window of (R-1)*D + T samples is walked once, every sample feeding
+// the outputs r with 0 <= q - r*D < T (all decided at compile time).  Window position p sits in slot p + p/(R*D).
+template <int D, int T>
+__device__ __forceinline__ void planStage(const FirJob& j, float2* win) {
+    constexpr int R = planOutPerThread(D);
+    constexpr int RD = R * D;
+    constexpr int LOGRD = (RD == 16) ? 4 : 5;
+    static_assert(RD == 16 || RD == 32, "pad stride");
+    constexpr int OPC = kThreads * R;
+    const int k0 = blockIdx.x * OPC;
+    if (k0 >= j.nOut) { return; }
+    const int nk = min(OPC, j.nOut - k0);
+    const int base = j.offset + k0 * D;
+    const int span = (((nk + R - 1) / R) * R - 1) * D + T;
+    stageWindow<2>(j, win, base, span, LOGRD);
+    __syncthreads();
+    const int kt = threadIdx.x * R;
+    if (kt >= nk) { return; }
+    const float2* w = win + threadIdx.x * (RD + 1);
+    float2 acc[R];
+#pragma unroll
+    for (int r = 0; r < R; r++) { acc[r] = make_float2(0.f, 0.f); }
+#pragma unroll
+    for (int q = 0; q < (R - 1) * D + T; q++) {
+        const float2 x = w[q + (q >> LOGRD)];
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            if (q - r * D >= 0 && q - r * D < T) {
+                const float h = PlanStage<D, T>::tap(q - r * D);
+                acc[r].x = fmaf(h, x.x, acc[r].x);
+                acc[r].y = fmaf(h, x.y, acc[r].y);
+            }
+        }
+    }
+    float2* out = reinterpret_cast<float2*>(j.out) + k0 + kt;
+#pragma unroll
+    for (int r = 0; r < R; r++) { if (kt + r < nk) { out[r] = acc[r]; } }
+}
+
 // ---- polyphase resampler, 8 lanes per output ----------------------------------------------------------------------
 // output k sits at offset + (phase0 + k*M)/L and uses bank row (phase0 + k*M) % L; rows are padded with zeros to a
 // multiple of 4 floats (rowStride) and 16-byte aligned.
@@ -149,7 +246,7 @@ __device__ __forceinline__ void lanesPoly(const FirJob& j, typename Elem<EF>::T*
     const int base = j.offset + (int)(tot0 / j.L);
     const unsigned rem0 = (unsigned)(tot0 % j.L);                 // per output: 32-bit arithmetic from here (128 * M < 2^31)
     const int span = (int)(totL / j.L) - (int)(tot0 / j.L) + j.rowStride;
-    for (int i = threadIdx.x; i < span; i += kThreads) { win[E::slot(i)] = loadPos<EF>(j, base + i); }
+    stageWindow<EF>(j, win, base, span, EF == 2 ? 4 : 5);
     __syncthreads();
     const int q = threadIdx.x & (kPolyLanes - 1), g = threadIdx.x >> 3;
     constexpr int kGroups = kThreads / kPolyLanes;
@@ -190,7 +287,7 @@ __device__ __forceinline__ void simpleJob(const FirJob& j, typename Elem<EF>::T*
         const bool staged = E::slot(span) + 1 <= smemElems;
         T acc = E::zero();
         if (staged) {
-            for (int i = threadIdx.x; i < span; i += kThreads) { win[E::slot(i)] = loadPos<EF>(j, base + i); }
+            stageWindow<EF>(j, win, base, span, EF == 2 ? 4 : 5);
             __syncthreads();
             if (k < nk) {
                 const int p0 = k * j.D;
@@ -227,7 +324,19 @@ __global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restri
     extern __shared__ __align__(16) unsigned char smemRaw[];
     T* win = reinterpret_cast<T*>(smemRaw);
     const FirJob j = jobs[blockIdx.y];
-    if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { blockedFir<EF>(j, win, smemElems); }
+    if (j.plan >= kPlanBase) {
+        if constexpr (EF == 2) {
+            switch (j.plan - kPlanBase) {
+            case 2 * 100 + 69: planStage<2, 69>(j, win); break;
+            case 2 * 100 + 12: planStage<2, 12>(j, win); break;
+            case 4 * 100 + 27: planStage<4, 27>(j, win); break;
+            case 8 * 100 + 54: planStage<8, 54>(j, win); break;
+            case 8 * 100 + 44: planStage<8, 44>(j, win); break;
+            default: planStage<8, 36>(j, win); break;
+            }
+        }
+    }
+    else if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { blockedFir<EF>(j, win, smemElems); }
     else if (j.plan > 0) { lanesPoly<EF>(j, win, smemElems); }
     else { simpleJob<EF>(j, win, smemElems); }
 }
@@ -248,6 +357,7 @@ __global__ void __launch_bounds__(256) historyUpdateKernel(const FirJob* __restr
 
 // ---- host-side geometry (must mirror the device code above)
 int outPerCta(const FirJob& j) {
+    if (j.plan >= kPlanBase) { return kThreads * planOutPerThread(j.D); }
     if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { return (kThreads / j.plan) * kR; }
     if (j.plan > 0) { return kPolyOutPerCta; }
     return kSimpleOutPerCta;
@@ -255,6 +365,10 @@ int outPerCta(const FirJob& j) {
 
 // shared-memory elements one CTA of this job wants (0 = reads through L1)
 size_t smemElemsFor(const FirJob& j) {
+    if (j.plan >= kPlanBase) {
+        const size_t span = (size_t)outPerCta(j) * j.D + j.T;
+        return span + span / ((size_t)planOutPerThread(j.D) * j.D) + 2;
+    }
     if (j.plan > 0 && j.kind == JOB_DECIM_FIR) {
         const size_t span = (size_t)outPerCta(j) * j.D + j.T + (size_t)kR * j.D;
         return span + span / ((size_t)kR * j.D) + 2;
@@ -270,7 +384,14 @@ size_t smemElemsFor(const FirJob& j) {
 } // namespace
 
 void firJobPlan(FirJob& j) {
+    const bool fromPlanTable = j.plan == -1;
     j.plan = 0;
+    if (fromPlanTable && j.kind == JOB_DECIM_FIR && j.elemFloats == 2) {
+        const int shape = j.D * 100 + j.T;
+        for (int known : { 2 * 100 + 69, 2 * 100 + 12, 4 * 100 + 27, 8 * 100 + 54, 8 * 100 + 44, 8 * 100 + 36 }) {
+            if (shape == known) { j.plan = kPlanBase + shape; return; }
+        }
+    }
     const size_t elemBytes = (size_t)j.elemFloats * sizeof(float);
     if (j.kind == JOB_DECIM_FIR) {
         if (j.D < 1 || j.D > 8 || (j.D & (j.D - 1)) != 0) { return; }
@@ -288,6 +409,19 @@ void firJobPlan(FirJob& j) {
         j.plan = kPolyLanes;
         if (smemElemsFor(j) * elemBytes > kSmemCap) { j.plan = 0; }
     }
+}
+
+void firJobsBalance(FirJob* jobs, int nJobs) {
+    long long ctas = 0;
+    bool any = false;
+    for (int i = 0; i < nJobs; i++) {
+        if (jobs[i].nOut <= 0) { continue; }
+        const int opc = outPerCta(jobs[i]);
+        ctas += (jobs[i].nOut + opc - 1) / opc;
+        any = any || jobs[i].plan >= kPlanBase;
+    }
+    if (!any || ctas >= 148 * 8) { return; }
+    for (int i = 0; i < nJobs; i++) { if (jobs[i].plan >= kPlanBase) { jobs[i].plan = 0; firJobPlan(jobs[i]); } }   // the generic planner's choice
 }
 
 int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s) {

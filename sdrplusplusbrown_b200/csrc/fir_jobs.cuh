@@ -35,6 +35,10 @@ struct FirJob {
 // chooses FirJob::plan from the job's shape (host side, called by Stage::fillJob)
 void firJobPlan(FirJob& j);
 
+// Call on the jobs of one launch before they are uploaded: plan-table jobs fall back to one output per thread when the
+// whole launch would have too few CTAs to fill the GPU (a single VFO: 512 fat CTAs measured slower than 2048 thin ones).
+void firJobsBalance(FirJob* jobs, int nJobs);
+
 // Launchers (all jobs of one "level" in a single launch; grid.y = job index)
 // every job of a launch must have the same elemFloats; h_jobs is the host copy of d_jobs (grid and shared-memory sizing)
 int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s);

@@ -241,7 +241,7 @@ int FrontEnd::rebuildDecim() {
             std::vector<float> t(plan->stages[i].ntaps);
             memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());
             cap = cap / plan->stages[i].decim + 2;
-            B200_TRY(decimStages[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap));
+            B200_TRY(decimStages[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap, true));
         }
     }
     return B200_OK;
@@ -320,6 +320,7 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
             st.advance(n);
             data = st.dOut; n = j.nOut;
         }
+        for (auto& fjob : jobs) { firJobsBalance(&fjob, 1); }     // each stage is its own launch here
         const size_t bytes = jobs.size() * sizeof(FirJob);
         if (!dJobDesc) { jobDescBytes = 16 * sizeof(FirJob); B200_CUDA(cudaMalloc(&dJobDesc, jobDescBytes)); }
         void* hp = nullptr; int slot = 0;

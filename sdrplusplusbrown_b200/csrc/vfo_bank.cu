@@ -15,8 +15,9 @@
 namespace b200 {
 
 // ------------------------------------------------------------------ Stage
-int Stage::create(int kind_, const std::vector<float>& taps, int D_, int L_, int M_, int elemFloats_, int outCap_) {
+int Stage::create(int kind_, const std::vector<float>& taps, int D_, int L_, int M_, int elemFloats_, int outCap_, bool planTaps_) {
     destroy();
+    planTaps = planTaps_;
     kind = kind_; D = D_; L = L_; M = M_; elemFloats = elemFloats_;
     hostTaps = taps;
     offset = 0; phase = 0; cur = 0;
@@ -104,7 +105,7 @@ void Stage::fillJob(FirJob& j, const void* data, int nIn) const {
     j.data = data; j.out = dOut; j.taps = dTaps;
     j.H = H; j.T = T; j.D = D; j.offset = offset; j.nIn = nIn; j.nOut = outCountFor(nIn);
     j.kind = kind; j.L = L; j.M = M; j.phase0 = phase; j.rowStride = rowStride;
-    j.elemFloats = elemFloats; j.plan = 0;
+    j.elemFloats = elemFloats; j.plan = planTaps ? -1 : 0;     // -1: firJobPlan may pick the plan-table kernel
     firJobPlan(j);
 }
 
@@ -179,7 +180,7 @@ int VfoBank::reconfigureResampler(Vfo& v) {
             std::vector<float> t(plan->stages[i].ntaps);
             memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());
             cap = cap / plan->stages[i].decim + 2;
-            B200_TRY(v.decimStages[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap));
+            B200_TRY(v.decimStages[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap, true));
         }
     }
     const bool usesDecim = (p.mode == 0 || p.mode == 1);
@@ -421,6 +422,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
     });
 
     // ---- one upload (descriptors + any retuned rotator tables), then one launch per level
+    for (auto& l : levels) { firJobsBalance(l.data(), (int)l.size()); }
     size_t bytes = rj.size() * sizeof(RotJob) + xj.size() * sizeof(XlateJob) + fj.size() * sizeof(FusedJob) + histJobs.size() * sizeof(FirJob);
     for (auto& l : levels) { bytes += l.size() * sizeof(FirJob); }
     bytes += dirtyTables.size() * (kRotChunk * sizeof(float2)) + 64 * (16 + dirtyTables.size());

@@ -25,7 +25,8 @@ struct Stage {
     void* dOut = nullptr;
     int outCap = 0;
 
-    int create(int kind, const std::vector<float>& taps, int D, int L, int M, int elemFloats, int outCap);
+    bool planTaps = false;            // taps are one of the pow-2 plan tables (decim_tables.inc): the kernel may use its constant-bank copy
+    int create(int kind, const std::vector<float>& taps, int D, int L, int M, int elemFloats, int outCap, bool planTaps = false);
     void destroy();
     int resetState();                                   // zero history, offset = phase = 0
     int setTapsKeepHistory(const std::vector<float>& taps);   // FIR::setTaps (fir.h:33-54)

@@ -54,8 +54,10 @@ def main():
                 instr += 4.0 + 2.0 * T / D
             if args.demod:
                 kind = {"NFM48": binding.DEMOD_NFM, "NFM": binding.DEMOD_NFM, "AM": binding.DEMOD_AM, "USB": binding.DEMOD_USB, "LSB": binding.DEMOD_LSB,
-                        "WFM": binding.DEMOD_NFM}[mode]
-                if kind == binding.DEMOD_NFM:
+                        "WFM": binding.DEMOD_WFM}[mode]
+                if kind == binding.DEMOD_WFM:
+                    bank.set_demod(v, kind, 0, 1, 0, 0)          # the radio's defaults: mono, low-pass on, no RDS
+                elif kind == binding.DEMOD_NFM:
                     bank.set_demod(v, kind, 1, 0)
                 elif kind == binding.DEMOD_AM:
                     bank.set_demod(v, kind, 1, 50.0 / out_sr, 5.0 / out_sr, 100.0 / out_sr)
