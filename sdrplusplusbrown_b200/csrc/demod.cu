@@ -936,6 +936,9 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     }
     if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty() && wfmA.empty()) { return B200_OK; }
     for (auto& w : afWaves) { firJobsBalance(w.data(), (int)w.size()); }
+    firJobsBalance(firs.data(), (int)firs.size());
+    firJobsBalance(wfmA.data(), (int)wfmA.size());
+    firJobsBalance(wfmB.data(), (int)wfmB.size());
     // one upload: [seq][quad][all][firs][ssb][af waves][deemph]
     size_t afJobs = 0;
     for (auto& w : afWaves) { afJobs += w.size(); }

@@ -20,6 +20,7 @@
 #include "fir_jobs.cuh"
 
 #include <algorithm>
+#include <vector>
 
 namespace b200 {
 
@@ -248,8 +249,11 @@ __device__ __forceinline__ void lanesPoly(const FirJob& j, typename Elem<EF>::T*
     const int span = (int)(totL / j.L) - (int)(tot0 / j.L) + j.rowStride;
     stageWindow<EF>(j, win, base, span, EF == 2 ? 4 : 5);
     __syncthreads();
-    const int q = threadIdx.x & (kPolyLanes - 1), g = threadIdx.x >> 3;
-    constexpr int kGroups = kThreads / kPolyLanes;
+    // P lanes per output: 8 (a bank row is read as 128-byte runs) or 1 (plenty of outputs in the launch and a bank small
+    // enough to sit in L1: no shuffles, one thread walks the whole row)
+    const int P = j.plan, logP = ilog2(P);
+    const int q = threadIdx.x & (P - 1), g = threadIdx.x >> logP;
+    const int kGroups = kThreads >> logP;
     for (int kk = g; kk < kPolyOutPerCta; kk += kGroups) {          // same trip count for every lane of a warp
         T acc = E::zero();
         if (kk < nk) {
@@ -257,7 +261,7 @@ __device__ __forceinline__ void lanesPoly(const FirJob& j, typename Elem<EF>::T*
             const unsigned adv = total / (unsigned)j.L;
             const int p0 = (int)adv;
             const float* row = j.taps + (size_t)(total - adv * (unsigned)j.L) * j.rowStride;
-            for (int t = 4 * q; t < j.rowStride; t += 4 * kPolyLanes) {
+            for (int t = 4 * q; t < j.rowStride; t += 4 * P) {
                 const float4 h = __ldg(reinterpret_cast<const float4*>(row + t));
                 E::fma(acc, h.x, win[E::slot(p0 + t)]);
                 E::fma(acc, h.y, win[E::slot(p0 + t + 1)]);
@@ -265,10 +269,47 @@ __device__ __forceinline__ void lanesPoly(const FirJob& j, typename Elem<EF>::T*
                 E::fma(acc, h.w, win[E::slot(p0 + t + 3)]);
             }
         }
-        E::add(acc, E::shflXor(acc, 1));
-        E::add(acc, E::shflXor(acc, 2));
-        E::add(acc, E::shflXor(acc, 4));
+        for (int m = 1; m < P; m <<= 1) { E::add(acc, E::shflXor(acc, m)); }
         if (q == 0 && kk < nk) { reinterpret_cast<T*>(j.out)[k0 + kk] = acc; }
+    }
+}
+
+// ---- polyphase resampler with a short bank (L <= 16 rows), one output per thread -----------------------------------
+// Outputs k and k + L use the same bank row, and their windows start exactly M samples apart.  A CTA takes 128*L
+// consecutive outputs and walks the L residue classes one after the other: within a class every thread reads the
+// SAME row (uniform loads, one wavefront) and the threads' windows are M samples apart in shared memory.
+constexpr int kClassPlan = 2;
+template <int EF>
+__device__ __forceinline__ void classPoly(const FirJob& j, typename Elem<EF>::T* win) {
+    using E = Elem<EF>;
+    using T = typename E::T;
+    const int opc = kThreads * j.L;
+    const int k0 = blockIdx.x * opc;
+    if (k0 >= j.nOut) { return; }
+    const int nk = min(opc, j.nOut - k0);
+    const long long tot0 = (long long)j.phase0 + (long long)k0 * j.M;
+    const int base = j.offset + (int)(tot0 / j.L);
+    const unsigned rem0 = (unsigned)(tot0 % j.L);
+    const int span = (int)(((long long)rem0 + (long long)(nk - 1) * j.M) / j.L) + j.rowStride + 1;
+    stageWindow<EF>(j, win, base, span, 30);       // no padding: lanes M samples apart are conflict-free for odd M
+    __syncthreads();
+    const int t = threadIdx.x;
+    for (int c = 0; c < j.L; c++) {
+        const int kk = c + j.L * t;
+        if (kk >= nk) { continue; }
+        const unsigned total = rem0 + (unsigned)c * (unsigned)j.M;     // + L*t*M, which is a whole number of samples
+        const unsigned adv = total / (unsigned)j.L;
+        const float* row = j.taps + (size_t)(total - adv * (unsigned)j.L) * j.rowStride;
+        const int p0 = (int)adv + t * j.M;
+        T acc = E::zero();
+        for (int i = 0; i < j.rowStride; i += 4) {
+            const float4 h = __ldg(reinterpret_cast<const float4*>(row + i));
+            E::fma(acc, h.x, win[p0 + i]);
+            E::fma(acc, h.y, win[p0 + i + 1]);
+            E::fma(acc, h.z, win[p0 + i + 2]);
+            E::fma(acc, h.w, win[p0 + i + 3]);
+        }
+        reinterpret_cast<T*>(j.out)[k0 + kk] = acc;
     }
 }
 
@@ -337,6 +378,7 @@ __global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restri
         }
     }
     else if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { blockedFir<EF>(j, win, smemElems); }
+    else if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) { classPoly<EF>(j, win); }
     else if (j.plan > 0) { lanesPoly<EF>(j, win, smemElems); }
     else { simpleJob<EF>(j, win, smemElems); }
 }
@@ -359,6 +401,7 @@ __global__ void __launch_bounds__(256) historyUpdateKernel(const FirJob* __restr
 int outPerCta(const FirJob& j) {
     if (j.plan >= kPlanBase) { return kThreads * planOutPerThread(j.D); }
     if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { return (kThreads / j.plan) * kR; }
+    if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) { return kThreads * j.L; }
     if (j.plan > 0) { return kPolyOutPerCta; }
     return kSimpleOutPerCta;
 }
@@ -372,6 +415,10 @@ size_t smemElemsFor(const FirJob& j) {
     if (j.plan > 0 && j.kind == JOB_DECIM_FIR) {
         const size_t span = (size_t)outPerCta(j) * j.D + j.T + (size_t)kR * j.D;
         return span + span / ((size_t)kR * j.D) + 2;
+    }
+    if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) {
+        const size_t span = (size_t)kThreads * j.M + j.rowStride + 4;
+        return span + (span >> 4) + 2;
     }
     if (j.plan > 0) {
         const size_t span = (size_t)(((long long)kPolyOutPerCta * j.M) / j.L) + j.rowStride + 2;
@@ -406,6 +453,10 @@ void firJobPlan(FirJob& j) {
     }
     else {
         if (j.rowStride % 4 != 0 || (long long)j.L + (long long)kPolyOutPerCta * j.M >= (1LL << 31)) { return; }
+        if (j.L <= 16 && j.nOut >= 4 * kThreads * j.L) {
+            j.plan = kClassPlan;
+            if (smemElemsFor(j) * elemBytes <= kSmemCap / 2) { return; }
+        }
         j.plan = kPolyLanes;
         if (smemElemsFor(j) * elemBytes > kSmemCap) { j.plan = 0; }
     }
@@ -420,8 +471,28 @@ void firJobsBalance(FirJob* jobs, int nJobs) {
         ctas += (jobs[i].nOut + opc - 1) / opc;
         any = any || jobs[i].plan >= kPlanBase;
     }
-    if (!any || ctas >= 148 * 8) { return; }
-    for (int i = 0; i < nJobs; i++) { if (jobs[i].plan >= kPlanBase) { jobs[i].plan = 0; firJobPlan(jobs[i]); } }   // the generic planner's choice
+    if (any && ctas < 148 * 8) {
+        for (int i = 0; i < nJobs; i++) { if (jobs[i].plan >= kPlanBase) { jobs[i].plan = 0; firJobPlan(jobs[i]); } }   // the generic planner's choice
+    }
+    // The per-job planner splits long filters over lanes as if the job were alone in its launch.  With many jobs side
+    // by side the split only costs shuffles: halve it while the launch still has enough CTAs.
+    auto launchCtas = [&]() { long long c = 0; for (int i = 0; i < nJobs; i++) { if (jobs[i].nOut > 0) { const int o = outPerCta(jobs[i]); c += (jobs[i].nOut + o - 1) / o; } } return c; };
+    for (;;) {
+        std::vector<int> saved((size_t)nJobs);
+        bool changed = false;
+        for (int i = 0; i < nJobs; i++) {
+            FirJob& j = jobs[i];
+            saved[i] = j.plan;
+            if (j.kind == JOB_DECIM_FIR && j.plan > 1 && j.plan < kPlanBase) { j.plan >>= 1; changed = true; }
+        }
+        if (!changed) { break; }
+        if (launchCtas() < 148 * 8) {
+            for (int i = 0; i < nJobs; i++) { jobs[i].plan = saved[i]; }
+            break;
+        }
+    }
+    // (polyphase jobs keep their 8 lanes per output: one lane per output was measured slower even with 256 jobs in the
+    // launch and a four-row bank, 297 us against 229 us)
 }
 
 int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s) {
