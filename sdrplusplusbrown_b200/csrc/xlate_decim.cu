@@ -36,6 +36,9 @@ int fusedTileSamples = 0;   // 0 = choose by VFO count (B200_OPT_TILE_SAMPLES)
 // 4 -> 0.25, 8 -> 0.15: every extra VFO per pass adds a partial-sum buffer, and the resident CTAs it costs outweigh the
 // barriers it saves.
 int fusedVfosPerBarrier = 1;
+// Two VFOs per register pass (each staged sample loaded once for both, their w tables fetched by one 16-byte broadcast
+// load): 0.39 -> 0.43 of the FFMA peak at 32-256 NFM VFOs.  Only where the unrolled body fits the instruction cache.
+bool fusedPairVfos = true;
 
 
 namespace {
@@ -142,9 +145,16 @@ __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, c
 #pragma unroll
     for (int r = 0; r < DS; r++) {
         const float2 x = xrow[r];
+        float2 wv[VB];
+        if constexpr (VB == 2) {
+            // the pair's tables are interleaved [r][vfo]: one 16-byte broadcast load serves both VFOs
+            const float4 w2 = reinterpret_cast<const float4*>(ws)[r];
+            wv[0] = make_float2(w2.x, w2.y); wv[1] = make_float2(w2.z, w2.w);
+        }
+        else { wv[0] = ws[r]; }
 #pragma unroll
         for (int v = 0; v < VB; v++) {
-            const float2 z = cmulf(x, ws[v * D + r]);
+            const float2 z = cmulf(x, wv[v]);
 #pragma unroll
             for (int q = 0; q < Q; q++) {
                 if (q * D + RUN * DS + r < T) {
@@ -158,7 +168,7 @@ __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, c
 }
 
 // grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
-// VB = VFOs per register pass (only VB = 1 is instantiated, see launchPlan).
+// VB = VFOs per register pass (1 or 2, see launchPlan).
 template <int RATIO, int VB, int TILE>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
 fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int pv) {
@@ -170,13 +180,14 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
     constexpr int LP = D + 1;               // padded sub-block pitch: lane stride 2(D+1) words -> distinct banks
-    static_assert(VB == 1, "one VFO per register pass (see launchPlan)");
-    const int PBUF = pv * Q * NT;           // partial sums of one pass: pv VFOs between two barriers
+    static_assert(VB == 1 || VB == 2, "one or two VFOs per register pass");
+    const int PBUF = pv * Q * NT;           // partial sums of one pass: pv VFOs between two barriers (VB == 2: pv == 2)
+    const int Gw = (G + VB - 1) / VB * VB;  // table rows allocated (a ragged last pair gets a zero partner)
     extern __shared__ __align__(16) float2 sm[];
     float2* xs = sm;                        // SB * LP
     float2* wsAll = xs + SB * LP;           // G * D      : phaseDelta^r of every VFO of the group
-    float2* part = wsAll + G * D;           // 2 * PBUF   : partial sums [pass parity][vfo][q][run][sub-block] (one buffer when G == 1)
-    float2* pAll = part + (G > 1 ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
+    float2* part = wsAll + Gw * D;          // 2 * PBUF   : partial sums [pass parity][vfo][q][run][sub-block] (one buffer when G == 1 or VB == 2)
+    float2* pAll = part + ((G > 1 && VB == 1) ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
     __shared__ float2* sOut[kMaxGroup];     // per-VFO output pointer and length: the per-VFO loop reads no global memory
     __shared__ int sNOut[kMaxGroup];
 
@@ -216,9 +227,19 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     const int nG = min(G, nJobs - g0);
     // the (VFO, r) and (VFO, sub-block) pairs are spread over all threads, so the table and checkpoint loads of the
     // whole group are in flight together instead of one VFO after the other
-    for (int p = tid; p < nG * D; p += NT) {
-        const int g = p / D, r = p - g * D;
-        wsAll[p] = __ldg(jobs[g0 + g].wtab + r);
+    if constexpr (VB == 2) {
+        // pairs of VFOs interleaved: wsAll[((g >> 1) * D + r) * 2 + (g & 1)]
+        const int nGw = (nG + 1) & ~1;
+        for (int p = tid; p < nGw * D; p += NT) {
+            const int g = p / D, r = p - g * D;
+            wsAll[(((g >> 1) * D + r) << 1) + (g & 1)] = (g < nG) ? __ldg(jobs[g0 + g].wtab + r) : make_float2(0.f, 0.f);
+        }
+    }
+    else {
+        for (int p = tid; p < nG * D; p += NT) {
+            const int g = p / D, r = p - g * D;
+            wsAll[p] = __ldg(jobs[g0 + g].wtab + r);
+        }
     }
     for (int p = tid; p < nG * SB; p += NT) {
         const int g = p / SB, b = p - g * SB;
@@ -234,8 +255,37 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
 
     const float2* xrow = xs + sb * LP + run * DS;
     for (int gp = 0, pass = 0; gp < nG; gp += pv, pass++) {
-        float2* pb = part + (pass & 1) * PBUF;
+        float2* pb = part + ((VB == 1) ? (pass & 1) * PBUF : 0);
         const int nv = min(pv, nG - gp);
+        if constexpr (VB == 2) {
+            // two VFOs in one register pass: every staged sample is loaded once for both
+            const float2* ws = wsAll + ((((gp >> 1) * D) + run * DS) << 1);
+            float2 acc[2][8];
+#pragma unroll
+            for (int v = 0; v < 2; v++) {
+#pragma unroll
+                for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
+            }
+            switch (run) {
+            case 0: accumulateRun<RATIO, 0, 2, DS>(xrow, ws, acc); break;
+            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 2, DS>(xrow, ws, acc); } break;
+            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 2, DS>(xrow, ws, acc); } break;
+            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 2, DS>(xrow, ws, acc); } break;
+            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 2, DS>(xrow, ws, acc); } break;
+            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 2, DS>(xrow, ws, acc); } break;
+            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 2, DS>(xrow, ws, acc); } break;
+            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 2, DS>(xrow, ws, acc); } break;
+            }
+#pragma unroll
+            for (int v = 0; v < 2; v++) {
+                if (v < nv) {
+                    const float2 P = pAll[(gp + v) * SB + sb];
+#pragma unroll
+                    for (int q = 0; q < Q; q++) { pb[(v * Q + q) * NT + tid] = cmulf(acc[v][q], P); }
+                }
+            }
+        }
+        else {
         // pv VFOs back to back between two barriers (a rolled loop: the unrolled tap code exists once)
 #pragma unroll 1
         for (int v = 0; v < nv; v++) {
@@ -257,6 +307,7 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
 #pragma unroll
             for (int q = 0; q < Q; q++) { pb[(v * Q + q) * NT + tid] = cmulf(acc[0][q], P); }
         }
+        }
         __syncthreads();
         // fold the partial sums: the (VFO, output) pairs of this pass are spread over all threads
         for (int p = tid; p < nv * NB; p += NT) {
@@ -274,7 +325,7 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
                 sOut[gp + v][k0 + k] = y;
             }
         }
-        if (G == 1) { __syncthreads(); }     // single buffer (never taken twice: one VFO, one pass)
+        if (G == 1 || VB == 2) { __syncthreads(); }     // single partial-sum buffer: everyone must be done reading before the next pass writes
     }
 }
 
@@ -348,9 +399,10 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
     using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB;
     constexpr int NB = SB - (Q - 1);
-    const int NPB = G > 1 ? 2 : 1;                     // one VFO per CTA never touches the second partial-sum buffer
-    const int pv = std::min(G, fusedVfosPerBarrier);   // VFOs accumulated between two barriers
-    const size_t smem = ((size_t)SB * (D + 1) + (size_t)G * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
+    const int NPB = (G > 1 && VB == 1) ? 2 : 1;        // one VFO per CTA, or a two-VFO pass, use a single partial-sum buffer
+    const int pv = (VB == 2) ? 2 : std::min(G, fusedVfosPerBarrier);   // VFOs accumulated between two barriers
+    const int Gw = (G + VB - 1) / VB * VB;
+    const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gw * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + G - 1) / G);
@@ -388,10 +440,12 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream
         const int tiles = (nOut + NB - 1) / NB;
         int G = std::min(kMaxGroup, nJobs);
         while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
-        // One VFO per register pass.  Register-blocking 2 or 4 VFOs per pass (shared x reads, fewer barriers) was
-        // measured slower on B200: the 4-VFO unrolled body (57 KB at D=64) stalls on instruction fetch (39 % of
-        // stall samples), a rolled 4-VFO body with shared-memory taps reached 0.27 of the FP32 peak against 0.35 here.
+        // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
+        // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps reached
+        // 0.27 of the FP32 peak.  Two per pass is the sweet spot where the body fits.
         if (small) { B200_TRY((launchMain<RATIO, 1, kTileSmall>(dJobs, nJobs, nOut, count, G, s))); }
+        // two VFOs per register pass when the unrolled two-VFO body stays well inside the instruction cache
+        else if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
         else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
