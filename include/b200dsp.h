@@ -230,6 +230,10 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
  * Results are bit-identical to b200_frontend_process_host on the converted block. */
 int b200_frontend_process_host_i16(b200_frontend* fe, const int16_t* h_in, int count, float scalar, float* h_frames, int max_frames,
                                    float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
+/* And for interleaved int8 I/Q (the SDR++ server stream's PCM_TYPE_I8, converted by volk_8i_s32f_convert_32f with
+ * scalar 128 / scaler in core/src/dsp/compression/sample_stream_decompressor.h): 2 bytes per sample over PCIe. */
+int b200_frontend_process_host_i8(b200_frontend* fe, const int8_t* h_in, int count, float scalar, float* h_frames, int max_frames,
+                                  float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
 /* Device-resident form of that conversion: count complex samples, d_in int16[2*count] -> d_out float[2*count]. */
 int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out, void* stream);
 

@@ -75,6 +75,7 @@ _SIGS = {
     "b200_frontend_frame_index": (C.c_int64, [_vp, _i]),
     "b200_frontend_process_host": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_frontend_process_host_i16": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
+    "b200_frontend_process_host_i8": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_convert_i16": (_i, [_vp, _i, _f, _vp, _vp]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
@@ -299,9 +300,11 @@ class FrontEnd:
         _chk(lib.b200_frontend_preproc_out(self.h, C.byref(p), C.byref(n)))
         return _dev_to_numpy(p.value, n.value, np.complex64, self.device)
 
-    def process_host(self, x, max_frames=0, vfos=(), audio=(), stream=None, i16_scalar=None):
-        """x: complex64 block, or (with i16_scalar) an int16 array [n, 2] of I/Q converted on the device"""
-        if i16_scalar is not None:
+    def process_host(self, x, max_frames=0, vfos=(), audio=(), stream=None, i16_scalar=None, i8_scalar=None):
+        """x: complex64 block, or (with i16_scalar / i8_scalar) an int16 / int8 array [n, 2] of I/Q converted on the device"""
+        if i8_scalar is not None:
+            x = np.ascontiguousarray(x, np.int8).reshape(-1, 2)
+        elif i16_scalar is not None:
             x = np.ascontiguousarray(x, np.int16).reshape(-1, 2)
         else:
             x = np.ascontiguousarray(x, np.complex64)
@@ -316,7 +319,10 @@ class FrontEnd:
         for v in audio:
             aptrs[v] = abufs[v].ctypes.data
         counts = np.zeros(max(nslots, 1), np.int32)
-        if i16_scalar is not None:
+        if i8_scalar is not None:
+            _chk(lib.b200_frontend_process_host_i8(self.h, x.ctypes.data, len(x), float(i8_scalar), frames.ctypes.data if max_frames else None, max_frames,
+                                                   optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
+        elif i16_scalar is not None:
             _chk(lib.b200_frontend_process_host_i16(self.h, x.ctypes.data, len(x), float(i16_scalar), frames.ctypes.data if max_frames else None, max_frames,
                                                     optrs if vfos else None, aptrs if audio else None, counts.ctypes.data, _stream_ptr(stream)))
         else:

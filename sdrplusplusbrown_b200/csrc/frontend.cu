@@ -180,6 +180,15 @@ __global__ void __launch_bounds__(256) convertI16Kernel(const short2* __restrict
     }
 }
 
+// int8 I/Q -> cf32 (VOLK generic 8i_s32f_convert_32f; the server source's PCM_TYPE_I8 path,
+// core/src/dsp/compression/sample_stream_decompressor.h, scalar 128 / scaler)
+__global__ void __launch_bounds__(256) convertI8Kernel(const char2* __restrict__ in, float2* __restrict__ out, int n, float scalar) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const char2 v = in[i];
+        out[i] = make_float2(__fdiv_rn((float)v.x, scalar), __fdiv_rn((float)v.y, scalar));
+    }
+}
+
 struct FrontEnd {
     int device = 0;
     double sampleRate = 0; int decimRatio = 1; bool dcBlocking = false, invertIQ = false;
@@ -626,19 +635,24 @@ static int processHostImpl(b200_frontend* fe, const void* h_in, int sampleBytes,
     DeviceGuard g(f.device);
     cudaStream_t s = (cudaStream_t)stream;
     if (!f.dStageIn) { B200_CUDA(cudaMalloc((void**)&f.dStageIn, (size_t)f.maxBlock * sizeof(cf32))); }
-    const bool i16 = sampleBytes == 4;
+    const bool i16 = sampleBytes != 8;          // integer I/Q (int16: 4 bytes per sample, int8: 2), staged raw and converted on the device
     if (i16 && !f.dStageI16) { B200_CUDA(cudaMalloc((void**)&f.dStageI16, (size_t)f.maxBlock * sizeof(short2))); }
-    if (i16 && !(scalar != 0.0f)) { setError("int16 scale must not be zero"); return B200_EINVAL; }
+    if (i16 && !(scalar != 0.0f)) { setError("integer sample scale must not be zero"); return B200_EINVAL; }
     const char* hIn = (const char*)h_in;
     // brings chunk [off, off+n) to dStageIn: the copy goes on `cs`, the int16 -> float conversion (if any) on `ks`
     auto stageCopy = [&](size_t off, int n, cudaStream_t cs) -> int {
-        void* dst = i16 ? (void*)(f.dStageI16 + off) : (void*)(f.dStageIn + off);
+        void* dst = i16 ? (void*)((char*)f.dStageI16 + off * sampleBytes) : (void*)(f.dStageIn + off);
         B200_CUDA(cudaMemcpyAsync(dst, hIn + off * sampleBytes, (size_t)n * sampleBytes, cudaMemcpyHostToDevice, cs));
         return B200_OK;
     };
     auto stageConvert = [&](size_t off, int n, cudaStream_t ks) -> int {
         if (!i16 || n <= 0) { return B200_OK; }
-        convertI16Kernel<<<std::min(148 * 8, (n + 255) / 256), 256, 0, ks>>>(f.dStageI16 + off, reinterpret_cast<float2*>(f.dStageIn + off), n, scalar);
+        if (sampleBytes == 4) {
+            convertI16Kernel<<<std::min(148 * 8, (n + 255) / 256), 256, 0, ks>>>(f.dStageI16 + off, reinterpret_cast<float2*>(f.dStageIn + off), n, scalar);
+        }
+        else {
+            convertI8Kernel<<<std::min(148 * 8, (n + 255) / 256), 256, 0, ks>>>(reinterpret_cast<const char2*>(f.dStageI16) + off, reinterpret_cast<float2*>(f.dStageIn + off), n, scalar);
+        }
         B200_CHECK_LAUNCH(); countLaunch();
         return B200_OK;
     };
@@ -704,6 +718,11 @@ int b200_frontend_process_host(b200_frontend* fe, const float* h_in, int count, 
 int b200_frontend_process_host_i16(b200_frontend* fe, const int16_t* h_in, int count, float scalar, float* h_frames, int max_frames,
                                    float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
     return processHostImpl(fe, h_in, 4, scalar, count, h_frames, max_frames, h_vfo_out, h_audio, vfo_counts, stream);
+}
+
+int b200_frontend_process_host_i8(b200_frontend* fe, const int8_t* h_in, int count, float scalar, float* h_frames, int max_frames,
+                                  float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream) {
+    return processHostImpl(fe, h_in, 2, scalar, count, h_frames, max_frames, h_vfo_out, h_audio, vfo_counts, stream);
 }
 
 int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out, void* stream) {

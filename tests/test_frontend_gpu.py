@@ -369,3 +369,30 @@ def test_process_host_int16_ingest_is_bit_identical_to_the_converted_block(n):
     assert binding.lib.b200_convert_i16(d_in.data_ptr(), 1000, 32768.0, d_out.data_ptr(), None) == 0
     torch.cuda.synchronize()
     assert np.array_equal(d_out.cpu().numpy(), xi[:1000].astype(np.float32) / np.float32(32768.0))
+
+
+def test_process_host_int8_ingest_matches_the_converted_block():
+    """int8 I/Q (the server stream's PCM_TYPE_I8, scalar 128 / scaler): 2 bytes per sample over PCIe, converted on the
+    device; a one-shot block must equal the cf32 call on the host-converted block bit for bit."""
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate, n = 2.4e6, 8192, 20.0, 250000
+    rng = np.random.default_rng(9)
+    t = np.arange(n)
+    xi = np.empty((n, 2), np.int8)
+    xi[:, 0] = np.clip(rng.integers(-8, 8, n) + (90 * np.cos(2 * np.pi * 100.7e3 / sr * t)).astype(np.int32), -128, 127)
+    xi[:, 1] = np.clip(rng.integers(-8, 8, n) + (90 * np.sin(2 * np.pi * 100.7e3 / sr * t)).astype(np.int32), -128, 127)
+    scalar = np.float32(128.0 / 0.75)
+    xf = (xi.astype(np.float32) / scalar).view(np.complex64).reshape(-1)
+    outs = []
+    for kind in ("f32", "i8"):
+        fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+        v = fe.vfos.add(50e3, 12.5e3, 100e3)
+        if kind == "f32":
+            outs.append(fe.process_host(xf, max_frames=8, vfos=[v]))
+        else:
+            outs.append(fe.process_host(xi, max_frames=8, vfos=[v], i8_scalar=float(scalar)))
+    a, b = outs
+    assert a["n_frames"] == b["n_frames"] > 0
+    assert np.array_equal(a["frames"], b["frames"])
+    assert len(a["vfo"][v]) == len(b["vfo"][v]) > 0
+    assert np.array_equal(a["vfo"][v], b["vfo"][v])
