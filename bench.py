@@ -416,7 +416,7 @@ def run_gpu(args):
                     "int16_input": {"value": e2e_i16_value, "unit": UNIT, "h2d_bytes_per_step": Be * 4,
                                     "path": "b200_frontend_process_host_i16 (int16 I/Q over PCIe, converted on the device)"}},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "fusedXlateDecimKernel<512> (xlate + /32 decimating FIR, stage 1 of the VFO)",
+            "roofline": {"bound": "hbm", "kernel": "fusedStreamKernel<512> (xlate + /32 decimating FIR, stage 1 of the VFO; single-VFO variant of the fused kernel with 16-byte staging)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
                          "peak_source": which, "traffic": _traffic(), "launches": int(klaunches), "avg_launch_ms": kms / klaunches if klaunches else None,
                          "algorithmic_bytes_per_launch": kbytes / klaunches if klaunches else None,

@@ -39,6 +39,9 @@ int fusedVfosPerBarrier = 1;
 // Two VFOs per register pass (each staged sample loaded once for both, their w tables fetched by one 16-byte broadcast
 // load): 0.39 -> 0.43 of the FFMA peak at 32-256 NFM VFOs.  Only where the unrolled body fits the instruction cache.
 bool fusedPairVfos = true;
+// One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
+// the single-VFO kernel at 0.65 of the copy peak; with 16-byte cp.async.cg and LDS.128 it reaches 0.94.
+bool fusedStreamSingle = true;
 
 
 namespace {
@@ -329,6 +332,146 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     }
 }
 
+// ---- single-VFO variant with 16-byte staging --------------------------------------------------------------------
+// With one or two VFOs the kernel is bound by how fast an SM can take samples in, not by arithmetic.  This variant
+// moves the tile with 16-byte cp.async.cg (two samples per copy, no L1 allocation) and reads it back two samples per
+// LDS.128, on an even sub-block pitch (D + 2) where those accesses are aligned and conflict-free.  16-byte copies need
+// the tile to start on an even sample: when (offset - H) is odd the tile starts one sample early and the taps are
+// used shifted by one (h'[0] = 0, h'[t] = h[t-1]), which changes no result (ODD = 1).
+// PERSIST = 1: CTAs stride over the tiles with the next tile in flight (double buffer); 0: one tile per CTA.
+#ifndef B200_STREAM_DS
+#define B200_STREAM_DS 32
+#endif
+template <int D> struct StreamCfg {
+    static constexpr int SB = (2048 / D) > 256 ? 256 : ((2048 / D) < 32 ? 32 : (2048 / D));
+    static constexpr int RS = (D / B200_STREAM_DS) > 8 ? 8 : ((D / B200_STREAM_DS) < 1 ? 1 : (D / B200_STREAM_DS));
+    static constexpr int DS = D / RS;
+    static constexpr int THREADS = SB * RS;
+};
+
+// one thread's run of DS samples, two samples per shared-memory load; taps shifted by ODD
+template <int RATIO, int RUN, int DS, int ODD>
+__device__ __forceinline__ void accumulateRun2(const float4* __restrict__ x2, const float4* __restrict__ w2, float2* acc) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T + ODD;
+    constexpr int Q = (T + D - 1) / D;
+#pragma unroll
+    for (int r2 = 0; r2 < DS / 2; r2++) {
+        const float4 xx = x2[r2], ww = w2[r2];
+        const float2 z0 = cmulf(make_float2(xx.x, xx.y), make_float2(ww.x, ww.y));
+        const float2 z1 = cmulf(make_float2(xx.z, xx.w), make_float2(ww.z, ww.w));
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            constexpr int dummy = 0; (void)dummy;
+            const int t0 = q * D + RUN * DS + 2 * r2, t1 = t0 + 1;
+            if (t0 < T && t0 - ODD >= 0) { const float h = FS::tap(t0 - ODD); acc[q].x = fmaf(h, z0.x, acc[q].x); acc[q].y = fmaf(h, z0.y, acc[q].y); }
+            if (t1 < T && t1 - ODD >= 0) { const float h = FS::tap(t1 - ODD); acc[q].x = fmaf(h, z1.x, acc[q].x); acc[q].y = fmaf(h, z1.y, acc[q].y); }
+        }
+    }
+}
+
+__device__ __forceinline__ void cpAsync16(float2* smemDst, const float2* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+template <int RATIO, int ODD, int PERSIST>
+__global__ void __launch_bounds__(StreamCfg<FirstStage<RATIO>::D>::THREADS)
+fusedStreamKernel(const FusedJob* __restrict__ jobs, int tiles) {
+    using FS = FirstStage<RATIO>;
+    using SC = StreamCfg<FS::D>;
+    constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
+    constexpr int Q = (T + D - 1) / D;
+    static_assert(Q <= 8, "accumulator array is sized for Q <= 8");
+    constexpr int SB = SC::SB, RS = SC::RS, DS = SC::DS, NT = SC::THREADS;
+    constexpr int NB = SB - (Q - 1);
+    constexpr int LP = D + 2;                        // even pitch: 16-byte aligned rows
+    constexpr int NBUF = PERSIST ? 2 : 1;
+    constexpr bool kImmediateStaging = ((2 * NT) % D == 0);
+    extern __shared__ __align__(16) float2 sm[];
+    float2* xs = sm;                        // NBUF * SB * LP
+    float2* ws = xs + NBUF * SB * LP;       // D
+    float2* part = ws + D;                  // Q * NT
+    float2* pPh = part + Q * NT;            // NBUF * SB
+    const int tid = threadIdx.x;
+    const int sb = tid % SB, run = tid / SB;
+    const FusedJob j = jobs[blockIdx.y];
+    const float2* in = reinterpret_cast<const float2*>(j.in);
+    float2* out = reinterpret_cast<float2*>(j.out);
+
+    auto issue = [&](int tile, float2* dst) {
+        const int mStart = j.offset - H - ODD + tile * NB * D;
+        if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j.count) {
+            // pair e = tid + u*NT holds samples 2e, 2e+1 -> slot 2e + 2*(2e/D)
+            const int i0 = 2 * tid;
+            const float2* g = in + mStart + i0;
+            float2* d = dst + i0 + 2 * (i0 / D);
+#pragma unroll
+            for (int u = 0; u < (SB * D) / (2 * NT); u++) { cpAsync16(d + u * (2 * NT + 2 * (2 * NT / D)), g + u * 2 * NT); }
+        }
+        else {
+            for (int i = tid; i < SB * D; i += NT) {
+                const int m = mStart + i;
+                const bool ok = (m >= 0 && m < j.count);
+                cpAsync8(dst + i + 2 * (i / D), in + (ok ? m : 0), ok);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    int tile = blockIdx.x;
+    if (tile >= tiles) { return; }
+    issue(tile, xs);
+    for (int r = tid; r < D; r += NT) { ws[r] = __ldg(j.wtab + r); }
+    for (int it = 0; tile < tiles; tile += gridDim.x, it++) {
+        float2* xt = xs + (PERSIST ? (it & 1) : 0) * (SB * LP);
+        float2* ph = pPh + (PERSIST ? (it & 1) : 0) * SB;
+        const int k0 = tile * NB;
+        const int mStart = j.offset - H - ODD + k0 * D;
+        if (tid < SB) {                                  // sub-block start phases, while the tile is still in flight
+            const int ms = mStart + tid * D;
+            float2 p = make_float2(0.f, 0.f);
+            if (ms < j.count && ms + D > 0) { p = phaseAtAny(j, ms); }
+            ph[tid] = p;
+        }
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();                                 // tile and phases visible; everyone is done with the previous tile
+        if (PERSIST && tile + (int)gridDim.x < tiles) { issue(tile + gridDim.x, xs + ((it & 1) ^ 1) * (SB * LP)); }
+        const float4* x2 = reinterpret_cast<const float4*>(xt + sb * LP + run * DS);
+        const float4* w2 = reinterpret_cast<const float4*>(ws + run * DS);
+        float2 acc[8];
+#pragma unroll
+        for (int q = 0; q < Q; q++) { acc[q] = make_float2(0.f, 0.f); }
+        switch (run) {
+        case 0: accumulateRun2<RATIO, 0, DS, ODD>(x2, w2, acc); break;
+        case 1: if constexpr (RS > 1) { accumulateRun2<RATIO, 1, DS, ODD>(x2, w2, acc); } break;
+        case 2: if constexpr (RS > 2) { accumulateRun2<RATIO, 2, DS, ODD>(x2, w2, acc); } break;
+        case 3: if constexpr (RS > 3) { accumulateRun2<RATIO, 3, DS, ODD>(x2, w2, acc); } break;
+        case 4: if constexpr (RS > 4) { accumulateRun2<RATIO, 4, DS, ODD>(x2, w2, acc); } break;
+        case 5: if constexpr (RS > 5) { accumulateRun2<RATIO, 5, DS, ODD>(x2, w2, acc); } break;
+        case 6: if constexpr (RS > 6) { accumulateRun2<RATIO, 6, DS, ODD>(x2, w2, acc); } break;
+        default: if constexpr (RS > 7) { accumulateRun2<RATIO, 7, DS, ODD>(x2, w2, acc); } break;
+        }
+        const float2 P = ph[sb];
+#pragma unroll
+        for (int q = 0; q < Q; q++) { part[q * NT + tid] = cmulf(acc[q], P); }
+        __syncthreads();
+        if (tid < NB && k0 + tid < j.nOut) {
+            float2 y = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < Q; q++) {
+#pragma unroll
+                for (int h = 0; h < RS; h++) {
+                    const float2 c = part[q * NT + h * SB + tid + q];
+                    y.x += c.x; y.y += c.y;
+                }
+            }
+            out[k0 + tid] = y;
+        }
+        if (!PERSIST) { break; }
+    }
+}
+
 // One CTA per VFO: (1) add the contribution of the carried, already-rotated history to the first outputs,
 // (2) write the rotated history for the next call: histNext[i] = workbuf[count + i] (decimating_fir.h:65).
 template <int RATIO>
@@ -427,8 +570,61 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
     return B200_OK;
 }
 
+int profBegin(cudaStream_t s, double bytes, size_t* slotOut) {
+    if (!g_prof.enabled) { return B200_OK; }
+    if (g_prof.used == g_prof.start.size()) {
+        if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
+        else {
+            cudaEvent_t a, b;
+            B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
+            g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
+        }
+    }
+    *slotOut = g_prof.used++;
+    g_prof.bytes[*slotOut] = bytes;
+    B200_CUDA(cudaEventRecord(g_prof.start[*slotOut], s));
+    return B200_OK;
+}
+
+template <int RATIO, int ODD, int PERSIST>
+int launchStreamV(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
+    using FS = FirstStage<RATIO>;
+    using SC = StreamCfg<FS::D>;
+    constexpr int D = FS::D, T = FS::T + ODD;
+    constexpr int Q = (T + D - 1) / D;
+    constexpr int NB = SC::SB - (Q - 1);
+    constexpr int NBUF = PERSIST ? 2 : 1;
+    const size_t smem = ((size_t)NBUF * SC::SB * (D + 2) + D + (size_t)Q * SC::THREADS + NBUF * SC::SB) * sizeof(float2);
+    B200_CUDA(cudaFuncSetAttribute(fusedStreamKernel<RATIO, ODD, PERSIST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int tiles = (nOut + NB - 1) / NB;
+    int gx = tiles;
+    if (PERSIST) {
+        static int perSm = 0;           // resident CTAs per SM of this instantiation
+        if (perSm == 0) {
+            B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fusedStreamKernel<RATIO, ODD, PERSIST>, SC::THREADS, smem));
+            if (perSm < 1) { perSm = 1; }
+        }
+        const int maxX = std::max(1, (148 * perSm) / nJobs);
+        const int rounds = (tiles + maxX - 1) / maxX;          // equal numbers of tiles per CTA
+        gx = (tiles + rounds - 1) / rounds;
+    }
+    size_t slot = 0;
+    B200_TRY(profBegin(s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs, &slot));
+    fusedStreamKernel<RATIO, ODD, PERSIST><<<dim3(gx, nJobs), SC::THREADS, smem, s>>>(dJobs, tiles);
+    B200_CHECK_LAUNCH(); countLaunch();
+    if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
+    return B200_OK;
+}
+
+// odd: whether (input pointer / 8 + offset - H) is odd, i.e. whether the tile must start one sample early
 template <int RATIO>
-int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
+int launchStream(const FusedJob* dJobs, int nJobs, int nOut, int count, bool odd, cudaStream_t s) {
+    // (the persistent, double-buffered form -- PERSIST = 1 -- was measured slower: 0.85 against 0.94 of the copy peak)
+    return odd ? launchStreamV<RATIO, 1, 0>(dJobs, nJobs, nOut, count, s) : launchStreamV<RATIO, 0, 0>(dJobs, nJobs, nOut, count, s);
+}
+
+template <int RATIO>
+int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
@@ -443,7 +639,11 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream
         // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
         // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps reached
         // 0.27 of the FP32 peak.  Two per pass is the sweet spot where the body fits.
-        if (small) { B200_TRY((launchMain<RATIO, 1, kTileSmall>(dJobs, nJobs, nOut, count, G, s))); }
+        if (small && fusedStreamSingle && nJobs == 1) {
+            const bool odd = ((((uintptr_t)in >> 3) + (uintptr_t)(long long)(offset - (T - 1) + (1 << 20))) & 1) != 0;   // + 2^20 keeps the sum non-negative
+            B200_TRY((launchStream<RATIO>(dJobs, nJobs, nOut, count, odd, s)));
+        }
+        else if (small) { B200_TRY((launchMain<RATIO, 1, kTileSmall>(dJobs, nJobs, nOut, count, G, s))); }
         // two VFOs per register pass when the unrolled two-VFO body stays well inside the instruction cache
         else if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
         else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
@@ -453,18 +653,18 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream
     return B200_OK;
 }
 
-int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStream_t s) {
+int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
     switch (ratio) {
-    case 16: return launchPlan<16>(dJobs, nJobs, nOut, count, s);
-    case 32: return launchPlan<32>(dJobs, nJobs, nOut, count, s);
-    case 64: return launchPlan<64>(dJobs, nJobs, nOut, count, s);
-    case 128: return launchPlan<128>(dJobs, nJobs, nOut, count, s);
-    case 256: return launchPlan<256>(dJobs, nJobs, nOut, count, s);
-    case 512: return launchPlan<512>(dJobs, nJobs, nOut, count, s);
-    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, count, s);
-    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, count, s);
-    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, count, s);
-    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, count, s);
+    case 16: return launchPlan<16>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 32: return launchPlan<32>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 64: return launchPlan<64>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 128: return launchPlan<128>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 256: return launchPlan<256>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 512: return launchPlan<512>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, count, in, offset, s);
     default: setError("no fused kernel for ratio %d", ratio); return B200_EINVAL;
     }
 }
@@ -492,7 +692,7 @@ int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cu
     while (i < hostJobs.size()) {
         size_t e = i + 1;
         while (e < hostJobs.size() && hostJobs[e].ratio == hostJobs[i].ratio && hostJobs[e].offset == hostJobs[i].offset) { e++; }
-        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, hostJobs[i].count, s));
+        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, hostJobs[i].count, hostJobs[i].in, hostJobs[i].offset, s));
         i = e;
     }
     return B200_OK;
