@@ -296,3 +296,32 @@ def test_chunk_invariance_at_full_size():
         outs.append(np.concatenate(parts))
     assert len(outs[0]) == len(outs[1]) == len(outs[2]) == 6251
     assert err_db(outs[1], outs[0]) <= TOL_DB and err_db(outs[2], outs[0]) <= TOL_DB
+
+
+@pytest.mark.parametrize("lead", [0, 1])
+@pytest.mark.parametrize("sizes", [[40000], [40001, 39999], [12345, 3, 40002]])
+def test_single_vfo_kernel_every_start_parity(lead, sizes):
+    """The single-VFO fused kernel stages its tile with 16-byte copies and therefore starts tiles on an even sample of
+    a 16-byte aligned address, using its taps shifted by one when the block's own alignment is odd.  Both parities of
+    the input pointer (a view that starts one sample into an aligned buffer) and of the carried decimation offset
+    (odd block lengths) must give the oracle's output."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    in_sr, out_sr, bw, off = 2.4e6, 50e3, 12.5e3, 100e3
+    n = sum(sizes) * 3
+    x = synth.make_iq(5, n, in_sr, tones=[(off + 1e3, 0.1)])
+    o = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    b = binding.VfoBank(in_sr, max_block=max(sizes) + 8)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    assert b.describe(v)["fused"]
+    for blk in split(x, sizes):
+        ref = o.process(blk)
+        buf = torch.zeros((len(blk) + lead, 2), dtype=torch.float32, device="cuda")
+        buf[lead:] = to_dev(blk)
+        view = buf[lead:]
+        assert (view.data_ptr() % 16 == 0) == (lead == 0)
+        b.process(view, len(blk))
+        assert b.out_count(v) == len(ref)
+        if len(ref) > 8:
+            assert err_db(b.output(v), ref) <= -80.0
