@@ -123,6 +123,11 @@ __device__ __forceinline__ void cpAsync8Full(float2* smemDst, const float2* gsrc
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(gsrc) : "memory");
 }
 
+__device__ __forceinline__ void cpAsync16(float2* smemDst, const float2* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
+}
+
 __device__ __forceinline__ float2 cmulf(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
 // phase at sample m of the block, m may be negative (backward extension from chk[0]; only the m >= 0 part of
@@ -140,31 +145,36 @@ __device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
 // One thread's run of DS samples of one sub-block for VB VFOs at once: each input sample is read from shared
 // memory once, rotated once per VFO, and feeds that VFO's Q accumulators.  RUN selects which DS-sample slice
 // of the D-sample sub-block this thread owns (compile time, so every tap is a constant-bank operand).
-template <int RATIO, int RUN, int VB, int DS>
+template <int RATIO, int RUN, int VB, int DS, int ODD>
 __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, const float2* __restrict__ ws, float2 (*acc)[8]) {
     using FS = FirstStage<RATIO>;
-    constexpr int D = FS::D, T = FS::T;
+    constexpr int D = FS::D, T = FS::T + ODD;      // ODD: taps used shifted by one (h'[0] = 0, h'[t] = h[t-1])
     constexpr int Q = (T + D - 1) / D;
+    const float4* x2 = reinterpret_cast<const float4*>(xrow);     // even pitch, even run start: 16-byte aligned
+    const float4* w4 = reinterpret_cast<const float4*>(ws);
 #pragma unroll
-    for (int r = 0; r < DS; r++) {
-        const float2 x = xrow[r];
-        float2 wv[VB];
+    for (int r2 = 0; r2 < DS / 2; r2++) {
+        const float4 xx = x2[r2];
+        float2 w0[VB], w1[VB];
         if constexpr (VB == 2) {
-            // the pair's tables are interleaved [r][vfo]: one 16-byte broadcast load serves both VFOs
-            const float4 w2 = reinterpret_cast<const float4*>(ws)[r];
-            wv[0] = make_float2(w2.x, w2.y); wv[1] = make_float2(w2.z, w2.w);
+            // the pair's tables are interleaved [r][vfo]: one 16-byte broadcast load serves both VFOs of a sample
+            const float4 a = w4[2 * r2], b = w4[2 * r2 + 1];
+            w0[0] = make_float2(a.x, a.y); w0[1] = make_float2(a.z, a.w);
+            w1[0] = make_float2(b.x, b.y); w1[1] = make_float2(b.z, b.w);
         }
-        else { wv[0] = ws[r]; }
+        else {
+            const float4 a = w4[r2];
+            w0[0] = make_float2(a.x, a.y); w1[0] = make_float2(a.z, a.w);
+        }
 #pragma unroll
         for (int v = 0; v < VB; v++) {
-            const float2 z = cmulf(x, wv[v]);
+            const float2 z0 = cmulf(make_float2(xx.x, xx.y), w0[v]);
+            const float2 z1 = cmulf(make_float2(xx.z, xx.w), w1[v]);
 #pragma unroll
             for (int q = 0; q < Q; q++) {
-                if (q * D + RUN * DS + r < T) {
-                    const float h = FS::tap(q * D + RUN * DS + r);
-                    acc[v][q].x = fmaf(h, z.x, acc[v][q].x);
-                    acc[v][q].y = fmaf(h, z.y, acc[v][q].y);
-                }
+                const int t0 = q * D + RUN * DS + 2 * r2, t1 = t0 + 1;
+                if (t0 < T && t0 - ODD >= 0) { const float h = FS::tap(t0 - ODD); acc[v][q].x = fmaf(h, z0.x, acc[v][q].x); acc[v][q].y = fmaf(h, z0.y, acc[v][q].y); }
+                if (t1 < T && t1 - ODD >= 0) { const float h = FS::tap(t1 - ODD); acc[v][q].x = fmaf(h, z1.x, acc[v][q].x); acc[v][q].y = fmaf(h, z1.y, acc[v][q].y); }
             }
         }
     }
@@ -172,17 +182,17 @@ __device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, c
 
 // grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
 // VB = VFOs per register pass (1 or 2, see launchPlan).
-template <int RATIO, int VB, int TILE>
+template <int RATIO, int VB, int TILE, int ODD>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
 fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int pv) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
-    constexpr int D = FS::D, T = FS::T, H = T - 1;
+    constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
     constexpr int Q = (T + D - 1) / D;
     static_assert(Q <= 8, "accumulator array is sized for Q <= 8");
     constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
-    constexpr int LP = D + 1;               // padded sub-block pitch: lane stride 2(D+1) words -> distinct banks
+    constexpr int LP = D + 2;               // even sub-block pitch: rows 16-byte aligned, LDS.128 of a quarter-warp covers all banks
     static_assert(VB == 1 || VB == 2, "one or two VFOs per register pass");
     const int PBUF = pv * Q * NT;           // partial sums of one pass: pv VFOs between two barriers (VB == 2: pv == 2)
     const int Gw = (G + VB - 1) / VB * VB;  // table rows allocated (a ragged last pair gets a zero partner)
@@ -201,26 +211,28 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     const FusedJob j0 = jobs[g0];
     const int k0 = blockIdx.x * NB;
     if (k0 >= j0.nOut) { return; }
-    const int mStart = j0.offset - H + k0 * D;     // sample index of this tile's first sub-block
+    const int mStart = j0.offset - H - ODD + k0 * D;     // sample index of this tile's first sub-block (even, 16-byte aligned address)
     const float2* in = reinterpret_cast<const float2*>(j0.in);
 
     // ---- stage the input tile once for the whole VFO group (zero outside [0, count));
     // all copies of a thread are in flight at once, no register staging
-    constexpr bool kImmediateStaging = (NT % D == 0);   // a thread's copies land one constant smem stride apart
+    constexpr bool kImmediateStaging = ((2 * NT) % D == 0);   // a thread's copies land one constant smem stride apart
     if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
-        // interior tile: no bounds to check, and copy u of a thread is a compile-time offset from copy 0 on both sides
-        // (sample tid + u*NT lands in slot tid + tid/D + u*(NT + NT/D)), so the loop is LDGSTS with immediates only
-        const float2* g = in + mStart + tid;
-        float2* d = xs + tid + tid / D;
+        // interior tile: 16-byte copies (two samples, no L1 allocation), no bounds to check, and copy u of a thread is a
+        // compile-time offset from copy 0 on both sides (samples 2e, 2e+1 of pair e = tid + u*NT land in slot
+        // 2e + 2*(2e/D)), so the loop is LDGSTS with immediates only
+        const int i0 = 2 * tid;
+        const float2* g = in + mStart + i0;
+        float2* d = xs + i0 + 2 * (i0 / D);
 #pragma unroll
-        for (int u = 0; u < (SB * D) / NT; u++) { cpAsync8Full(d + u * (NT + NT / D), g + u * NT); }
+        for (int u = 0; u < (SB * D) / (2 * NT); u++) { cpAsync16(d + u * (2 * NT + 2 * (2 * NT / D)), g + u * 2 * NT); }
     }
     else {
 #pragma unroll 8
         for (int i = tid; i < SB * D; i += NT) {
             const int m = mStart + i;
             const bool ok = (m >= 0 && m < j0.count);
-            cpAsync8(xs + i + i / D, in + (ok ? m : 0), ok);
+            cpAsync8(xs + i + 2 * (i / D), in + (ok ? m : 0), ok);
         }
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
@@ -270,14 +282,14 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
                 for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
             }
             switch (run) {
-            case 0: accumulateRun<RATIO, 0, 2, DS>(xrow, ws, acc); break;
-            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 2, DS>(xrow, ws, acc); } break;
-            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 2, DS>(xrow, ws, acc); } break;
-            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 2, DS>(xrow, ws, acc); } break;
-            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 2, DS>(xrow, ws, acc); } break;
-            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 2, DS>(xrow, ws, acc); } break;
-            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 2, DS>(xrow, ws, acc); } break;
-            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 2, DS>(xrow, ws, acc); } break;
+            case 0: accumulateRun<RATIO, 0, 2, DS, ODD>(xrow, ws, acc); break;
+            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 2, DS, ODD>(xrow, ws, acc); } break;
+            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 2, DS, ODD>(xrow, ws, acc); } break;
+            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 2, DS, ODD>(xrow, ws, acc); } break;
+            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 2, DS, ODD>(xrow, ws, acc); } break;
+            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 2, DS, ODD>(xrow, ws, acc); } break;
+            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 2, DS, ODD>(xrow, ws, acc); } break;
+            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 2, DS, ODD>(xrow, ws, acc); } break;
             }
 #pragma unroll
             for (int v = 0; v < 2; v++) {
@@ -297,14 +309,14 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
 #pragma unroll
             for (int q = 0; q < Q; q++) { acc[0][q] = make_float2(0.f, 0.f); }
             switch (run) {
-            case 0: accumulateRun<RATIO, 0, 1, DS>(xrow, ws, acc); break;
-            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 1, DS>(xrow, ws, acc); } break;
-            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 1, DS>(xrow, ws, acc); } break;
-            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 1, DS>(xrow, ws, acc); } break;
-            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 1, DS>(xrow, ws, acc); } break;
-            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 1, DS>(xrow, ws, acc); } break;
-            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 1, DS>(xrow, ws, acc); } break;
-            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 1, DS>(xrow, ws, acc); } break;
+            case 0: accumulateRun<RATIO, 0, 1, DS, ODD>(xrow, ws, acc); break;
+            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 1, DS, ODD>(xrow, ws, acc); } break;
+            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 1, DS, ODD>(xrow, ws, acc); } break;
+            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 1, DS, ODD>(xrow, ws, acc); } break;
+            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 1, DS, ODD>(xrow, ws, acc); } break;
+            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 1, DS, ODD>(xrow, ws, acc); } break;
+            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 1, DS, ODD>(xrow, ws, acc); } break;
+            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 1, DS, ODD>(xrow, ws, acc); } break;
             }
             const float2 P = pAll[(gp + v) * SB + sb];
 #pragma unroll
@@ -368,11 +380,6 @@ __device__ __forceinline__ void accumulateRun2(const float4* __restrict__ x2, co
             if (t1 < T && t1 - ODD >= 0) { const float h = FS::tap(t1 - ODD); acc[q].x = fmaf(h, z1.x, acc[q].x); acc[q].y = fmaf(h, z1.y, acc[q].y); }
         }
     }
-}
-
-__device__ __forceinline__ void cpAsync16(float2* smemDst, const float2* gsrc) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(smemDst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
 }
 
 template <int RATIO, int ODD, int PERSIST>
@@ -534,10 +541,10 @@ int profDrain() {
     return B200_OK;
 }
 
-template <int RATIO, int VB, int TILE>
-int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
+template <int RATIO, int VB, int TILE, int ODD>
+int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
-    constexpr int D = FS::D, T = FS::T;
+    constexpr int D = FS::D, T = FS::T + ODD;
     constexpr int Q = (T + D - 1) / D;
     using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB;
@@ -545,8 +552,8 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
     const int NPB = (G > 1 && VB == 1) ? 2 : 1;        // one VFO per CTA, or a two-VFO pass, use a single partial-sum buffer
     const int pv = (VB == 2) ? 2 : std::min(G, fusedVfosPerBarrier);   // VFOs accumulated between two barriers
     const int Gw = (G + VB - 1) / VB * VB;
-    const size_t smem = ((size_t)SB * (D + 1) + (size_t)Gw * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
-    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = ((size_t)SB * (D + 2) + (size_t)Gw * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
+    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE, ODD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + G - 1) / G);
     size_t slot = 0;
@@ -564,10 +571,15 @@ int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cud
         g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
         B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
     }
-    fusedXlateDecimKernel<RATIO, VB, TILE><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G, pv);
+    fusedXlateDecimKernel<RATIO, VB, TILE, ODD><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G, pv);
     B200_CHECK_LAUNCH(); countLaunch();
     if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
     return B200_OK;
+}
+
+template <int RATIO, int VB, int TILE>
+int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, bool odd, cudaStream_t s) {
+    return odd ? launchMainV<RATIO, VB, TILE, 1>(dJobs, nJobs, nOut, count, G, s) : launchMainV<RATIO, VB, TILE, 0>(dJobs, nJobs, nOut, count, G, s);
 }
 
 int profBegin(cudaStream_t s, double bytes, size_t* slotOut) {
@@ -629,24 +641,25 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
     if (nOut > 0) {
-        const int tile = fusedTileSamples > 0 ? fusedTileSamples : (nJobs == 1 ? kTileSmall : kTileLarge);
-        const bool small = tile <= kTileSmall;
-        const int NB = (small ? TileCfg<D, kTileSmall>::SB : TileCfg<D, kTileLarge>::SB) - (Q - 1);
-        // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
-        const int tiles = (nOut + NB - 1) / NB;
-        int G = std::min(kMaxGroup, nJobs);
-        while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
-        // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
-        // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps reached
-        // 0.27 of the FP32 peak.  Two per pass is the sweet spot where the body fits.
-        if (small && fusedStreamSingle && nJobs == 1) {
-            const bool odd = ((((uintptr_t)in >> 3) + (uintptr_t)(long long)(offset - (T - 1) + (1 << 20))) & 1) != 0;   // + 2^20 keeps the sum non-negative
+        // tile start parity: 16-byte copies need an even sample index at a 16-byte aligned address (+ 2^20 keeps the sum non-negative)
+        const bool odd = ((((uintptr_t)in >> 3) + (uintptr_t)(long long)(offset - (T - 1) + (1 << 20))) & 1) != 0;
+        const bool single = nJobs == 1 && fusedStreamSingle && fusedTileSamples != kTileLarge;
+        if (single) {
+            // one VFO: HBM-bound, 2048-sample tiles, one tile per CTA
             B200_TRY((launchStream<RATIO>(dJobs, nJobs, nOut, count, odd, s)));
         }
-        else if (small) { B200_TRY((launchMain<RATIO, 1, kTileSmall>(dJobs, nJobs, nOut, count, G, s))); }
-        // two VFOs per register pass when the unrolled two-VFO body stays well inside the instruction cache
-        else if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
-        else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, s))); }
+        else {
+            const int NB = TileCfg<D, kTileLarge>::SB - (Q - 1);
+            // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
+            const int tiles = (nOut + NB - 1) / NB;
+            int G = std::min(kMaxGroup, nJobs);
+            while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
+            // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
+            // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps
+            // reached 0.27 of the FP32 peak.  Two per pass is the sweet spot, where the unrolled body fits the cache.
+            if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTileLarge>(dJobs, nJobs, nOut, count, G, odd, s))); }
+            else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, odd, s))); }
+        }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
     B200_CHECK_LAUNCH(); countLaunch();
