@@ -115,12 +115,14 @@ int VfoBank::init(double inSR_, int maxBlock_, int device_) {
     DeviceGuard g(device);
     if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
     B200_TRY(ring.init(64 * 1024));
+    B200_CUDA(cudaEventCreateWithFlags(&evStage1, cudaEventDisableTiming));
     return B200_OK;
 }
 
 void VfoBank::destroy() {
     DeviceGuard g(device);
     if (everRan) { cudaStreamSynchronize(lastStream); }
+    if (evStage1) { cudaEventDestroy(evStage1); evStage1 = nullptr; }
     for (auto& v : vfos) {
         if (!v.live) { continue; }
         for (auto& st : v.decimStages) { st.destroy(); }
@@ -459,6 +461,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(launchCheckpoints((const RotJob*)(d + oR), (int)rj.size(), exact ? (int)rj.size() : 0, count, s));
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
+        B200_CUDA(cudaEventRecord(evStage1, s));
         for (size_t l = 0; l < levels.size(); l++) {
             B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), levels[l].data(), (int)levels[l].size(), 2, s));
         }

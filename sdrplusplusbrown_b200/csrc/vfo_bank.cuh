@@ -83,6 +83,7 @@ struct VfoBank {
     void* dDemodDesc = nullptr; size_t dDemodDescBytes = 0;
     cudaStream_t lastStream = nullptr;
     bool everRan = false;
+    cudaEvent_t evStage1 = nullptr;  // recorded behind the full-rate stage of every process() call (the front end starts its FFT branch there)
     bool descViaParams = false;      // descriptor uploads avoid the copy engine (uploadDesc); set by the pipelined host path
     // per-call descriptors
     PinnedRing ring;
