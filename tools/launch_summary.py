@@ -34,7 +34,7 @@ def main():
     print("%-66s %5s %12s %10s %6s" % ("kernel", "n", "total us", "avg us", "share"))
     for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         print("%-66s %5d %12.1f %10.1f %5.1f%%" % (k, n, t, t / n, 100 * t / tot))
-    idx = [i for i, r in enumerate(rows) if "fusedXlateDecimKernel" in r[0]]
+    idx = [i for i, r in enumerate(rows) if "fusedXlateDecimKernel" in r[0] or "fusedStreamKernel" in r[0]]
     if len(idx) >= 3:
         s, e = idx[2], idx[3] if len(idx) > 3 else len(rows)
         print("\none step (launch order):")
