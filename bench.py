@@ -245,6 +245,7 @@ def run_gpu(args):
     max_frames = B // int(round(sr / cfg["fft_rate"])) + 2
     d_zoom = torch.empty((max_frames, DATA_WIDTH), dtype=torch.float32, device=dev)
     d_rgba = torch.empty((max_frames, DATA_WIDTH), dtype=torch.int32, device=dev)
+    fe.attach_waterfall(wf, d_zoom.data_ptr(), d_rgba.data_ptr(), max_frames)
 
     # ---- synthetic stream, resident in HBM (rank 0 is the ingest GPU)
     tones = [(off + 700.0 + 50e3 * r, 0.05) for r in range(world)] + [(3.3e6, 0.2)]
@@ -272,10 +273,7 @@ def run_gpu(args):
         if world > 1:
             compute.wait_event(ev_ready[i % 2])
         with torch.cuda.stream(compute):
-            fe.process(b, B, stream=compute)
-            nf = fe.frame_count()
-            if nf:
-                wf.push(fe.frame_ptr(0), nf, d_zoom.data_ptr(), d_rgba.data_ptr(), stream=compute)
+            fe.process(b, B, stream=compute)      # FFT rows -> zoom + palette rows inside the FFT branch (attached waterfall)
             if world > 1:
                 ev_free[i % 2].record(compute)
 

@@ -201,6 +201,13 @@ int b200_frontend_set_frame_shard(b200_frontend* fe, int rank, int world);
 /* The bank fed by this front end's pre-processed stream (IQFrontEnd::addVFO/removeVFO go
  * through b200_vfo_bank_add/remove on it).  Owned by the front end. */
 b200_vfo_bank* b200_frontend_vfo_bank(b200_frontend* fe);
+/* Runs a waterfall's row reduction (b200_waterfall_push) inside the front end's FFT branch, as the reference's FFT sink
+ * thread does when releaseFFTBuffer ends in WaterFall::pushFFT (gui/widgets/waterfall.cpp:1204-1276): frame i of a
+ * process call lands in row i of d_zoom (float[max_rows][data_width]) and d_rgba (uint32[max_rows][data_width]); either
+ * may be NULL.  data_width must be the waterfall's.  On the device the reduction then overlaps the channelizer's tail
+ * stages instead of following them.  wf = NULL detaches. */
+struct b200_waterfall;
+int b200_frontend_attach_waterfall(b200_frontend* fe, struct b200_waterfall* wf, int data_width, float* d_zoom, uint32_t* d_rgba, int max_rows);
 
 /* One block through the whole front end: pre-processing -> {FFT frames, every VFO (+demod)}.
  * d_in: device cf32[count].  After return:

@@ -73,6 +73,7 @@ _SIGS = {
     "b200_frontend_frame_count": (_i, [_vp]),
     "b200_frontend_frame_ptr": (_vp, [_vp, _i]),
     "b200_frontend_frame_index": (C.c_int64, [_vp, _i]),
+    "b200_frontend_attach_waterfall": (_i, [_vp, _vp, _i, _vp, _vp, _i]),
     "b200_frontend_process_host": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_frontend_process_host_i16": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_frontend_process_host_i8": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
@@ -294,6 +295,12 @@ class FrontEnd:
     def frames(self):
         n = self.frame_count()
         return [_dev_to_numpy(self.frame_ptr(i), self.fft_size, np.float32, self.device) for i in range(n)]
+
+    def attach_waterfall(self, wf, d_zoom_ptr, d_rgba_ptr, max_rows):
+        """run wf's row reduction inside the FFT branch: frame i of a call -> row i of the two device buffers"""
+        _chk(lib.b200_frontend_attach_waterfall(self.h, wf.h if wf is not None else None, int(wf.w) if wf is not None else 0,
+                                                d_zoom_ptr, d_rgba_ptr, int(max_rows)))
+        self._wf = wf      # keep it alive
 
     def preproc_out(self):
         p, n = _vp(), _i()

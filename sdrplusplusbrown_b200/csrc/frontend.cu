@@ -221,6 +221,8 @@ struct FrontEnd {
     FrameDesc* dFrameDesc = nullptr; int frameDescCap = 0;
     std::vector<int64_t> frameIdx;   // frames produced by the last call
     int shardRank = 0, shardWorld = 1;
+    // waterfall reduction attached to the FFT branch (the reference's FFT sink thread calls WaterFall::pushFFT itself)
+    b200_waterfall* wf = nullptr; float* wfZoom = nullptr; uint32_t* wfRgba = nullptr; int wfMaxRows = 0, wfWidth = 0;
     // host staging
     cf32* dStageIn = nullptr;
     short2* dStageI16 = nullptr;                // int16 I/Q as it arrives from the host (process_host_i16)
@@ -434,6 +436,14 @@ int FrontEnd::fftBranch(cudaStream_t s, bool append) {
         B200_TRY(uploadDesc(dFrameDesc, hp, bytes, s, bank->impl.descViaParams));
         rc = plan.run(dFrameDesc, (int)descs.size(), dWindow, nz, dRows + rowBase * (size_t)fftSize, nullptr, s);
         B200_TRY(ring.release(slot, s));
+        if (rc == B200_OK && wf) {
+            // rows of this call go to output rows rowBase.. of the attached buffers, on the FFT branch's own stream
+            const int n = std::min((int)descs.size(), wfMaxRows - (int)rowBase);
+            if (n > 0) {
+                rc = b200_waterfall_push(wf, dRows + rowBase * (size_t)fftSize, n, wfZoom ? wfZoom + rowBase * (size_t)wfWidth : nullptr,
+                                         wfRgba ? wfRgba + rowBase * (size_t)wfWidth : nullptr, s);
+            }
+        }
     }
     if (rc == B200_OK && stashLen > 0) {
         B200_CUDA(cudaMemcpyAsync(dCarry + stashAt, stashSrc, (size_t)stashLen * sizeof(cf32), cudaMemcpyDeviceToDevice, s));
@@ -575,6 +585,16 @@ int b200_frontend_set_frame_shard(b200_frontend* fe, int rank, int world) {
 }
 
 b200_vfo_bank* b200_frontend_vfo_bank(b200_frontend* fe) { return fe ? fe->impl.bank : nullptr; }
+
+int b200_frontend_attach_waterfall(b200_frontend* fe, b200_waterfall* wf, int data_width, float* d_zoom, uint32_t* d_rgba, int max_rows) {
+    FE_OR_FAIL(fe);
+    if (wf && (data_width <= 0 || max_rows <= 0 || (!d_zoom && !d_rgba))) { setError("bad arguments to b200_frontend_attach_waterfall"); return B200_EINVAL; }
+    FrontEnd& f = fe->impl;
+    DeviceGuard g(f.device);
+    B200_TRY(f.syncLast());
+    f.wf = wf; f.wfZoom = d_zoom; f.wfRgba = d_rgba; f.wfMaxRows = wf ? max_rows : 0; f.wfWidth = data_width;
+    return B200_OK;
+}
 
 int b200_frontend_process(b200_frontend* fe, const float* d_in, int count, void* stream) {
     FE_OR_FAIL(fe);

@@ -396,3 +396,41 @@ def test_process_host_int8_ingest_matches_the_converted_block():
     assert np.array_equal(a["frames"], b["frames"])
     assert len(a["vfo"][v]) == len(b["vfo"][v]) > 0
     assert np.array_equal(a["vfo"][v], b["vfo"][v])
+
+
+def test_attached_waterfall_rows_equal_a_separate_push():
+    """b200_frontend_attach_waterfall runs the zoom + palette reduction inside the FFT branch; its rows must be the
+    rows a separate b200_waterfall_push of the same frames gives, call after call (with a VFO present, so that the
+    branch really runs on its side stream)."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate, W = 20e6, 65536, 60.0, 1333
+    n = 1500000
+    x = synth.make_iq(2, 2 * n, sr, sigma=0.05, tones=[(2.5e6, 0.2), (-6.1e6, 0.02)])
+    fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=1, max_block=n)
+    fe.vfos.add(24e3, 2.8e3, 2.5e6)
+    wf = binding.Waterfall(N, W)
+    wf.set_view(8192, 40000)
+    wf.set_range(-110.0, -10.0)
+    wf.set_palette(np.arange(1000, dtype=np.uint32))
+    max_rows = n // int(round(sr / rate)) + 2
+    d_zoom = torch.full((max_rows, W), 123.0, dtype=torch.float32, device="cuda")
+    d_rgba = torch.zeros((max_rows, W), dtype=torch.int32, device="cuda")
+    fe.attach_waterfall(wf, d_zoom.data_ptr(), d_rgba.data_ptr(), max_rows)
+    ref_zoom = torch.empty((max_rows, W), dtype=torch.float32, device="cuda")
+    ref_rgba = torch.empty((max_rows, W), dtype=torch.int32, device="cuda")
+    for blk in (x[:n], x[n:]):
+        fe.process(to_dev(blk))
+        nf = fe.frame_count()
+        assert nf >= 4
+        torch.cuda.synchronize()
+        got_z, got_p = d_zoom[:nf].cpu().numpy(), d_rgba[:nf].cpu().numpy()
+        wf.push(fe.frame_ptr(0), nf, ref_zoom.data_ptr(), ref_rgba.data_ptr())
+        torch.cuda.synchronize()
+        assert np.array_equal(got_z, ref_zoom[:nf].cpu().numpy())
+        assert np.array_equal(got_p, ref_rgba[:nf].cpu().numpy())
+    fe.attach_waterfall(None, None, None, 0)
+    d_zoom.fill_(7.0)
+    fe.process(to_dev(x[:n]))
+    torch.cuda.synchronize()
+    assert float(d_zoom.min()) == 7.0          # detached: nothing written
