@@ -105,9 +105,10 @@ int b200_vfo_set_phase(b200_vfo_bank* bank, int vfo, double re, double im);
 int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
 /* Tuning/test switches: B200_OPT_FUSED_STAGE1 (1 = fused xlate+decimate kernel where available, default;
  * 0 = separate rotation and generic FIR kernels, process-wide), B200_OPT_CALIBRATION_STEPS (length of the
- * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step), B200_OPT_TILE_SAMPLES (input
- * samples per CTA tile of the fused kernel, process-wide: 0 = chosen by VFO count (default), 2048 or 4096;
- * results do not depend on it). */
+ * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step), B200_OPT_TILE_SAMPLES (process-wide
+ * choice of the first-stage kernel for a launch that holds ONE VFO: 0 or 2048 = the single-VFO kernel with
+ * 2048-sample tiles (default), 4096 = the grouped kernel with 4096-sample tiles, which launches of two or more
+ * VFOs always use; results do not depend on it). */
 #define B200_OPT_FUSED_STAGE1 1
 #define B200_OPT_CALIBRATION_STEPS 2
 #define B200_OPT_TILE_SAMPLES 3

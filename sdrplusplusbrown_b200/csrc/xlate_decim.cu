@@ -31,7 +31,7 @@
 
 namespace b200 {
 
-int fusedTileSamples = 0;   // 0 = choose by VFO count (B200_OPT_TILE_SAMPLES)
+int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grouped kernel for a one-VFO launch too; 0 / 2048 = default
 // VFOs accumulated between two barriers.  Measured on B200 (cfg3, 32 and 256 VFOs): 1 -> 0.33 of the FFMA peak, 2 -> 0.32,
 // 4 -> 0.25, 8 -> 0.15: every extra VFO per pass adds a partial-sum buffer, and the resident CTAs it costs outweigh the
 // barriers it saves.
@@ -91,10 +91,9 @@ template <int RATIO> struct FirstStage;
 constexpr int kMaxGroup = 8;         // VFOs per CTA (the input tile is staged once per group)
 constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
 
-// Input samples per CTA tile.  Measured on B200 (tools/bench_bank.py): with a single VFO the kernel is HBM-bound and
-// the smaller tile wins (more resident CTAs, the load phase of one overlaps the arithmetic of its neighbours: 0.65 of
-// the copy bandwidth against 0.58); from two VFOs on the larger tile wins (fewer
-// overlap sub-blocks recomputed per output: 0.35 of the FFMA peak against 0.32).
+// Input samples per CTA tile: 2048 for the single-VFO kernel (fusedStreamKernel, HBM-bound: more resident CTAs), 4096
+// for the grouped kernel (FP32-bound from a few VFOs on: fewer overlap sub-blocks recomputed per output; measured
+// 0.35 of the FFMA peak against 0.32 with 2048-sample tiles, before pairing and 16-byte staging).
 constexpr int kTileSmall = 2048, kTileLarge = 4096;
 
 template <int D, int TILE> struct TileCfg {
