@@ -94,11 +94,23 @@ int orc_am_process(void* h, int count, const float* in, float* outStereo);
 void* orc_wfm_create(double deviation, double samplerate, int stereo, int lowPass);
 void orc_wfm_destroy(void* h);
 int orc_wfm_process(void* h, int count, const float* in, float* outStereo);
+// The same demodulator with its RDS branch on (broadcast_fm.h:169-175,197-206): the real MPX as complex, FrequencyXlator by
+// -57 kHz, RationalResampler<complex_t> to 5 kS/s.  Writes the stereo audio (count samples) and returns the RDS sample count.
+void* orc_wfm_create_rds(double deviation, double samplerate, int stereo, int lowPass);
+int orc_wfm_process_rds(void* h, int count, const float* in, float* outStereo, float* rdsOut);
 // radio IF chain between the VFO and the demodulator (radio_module.h:92-98): NoiseBlanker (noise_reduction/noise_blanker.h:38-56)
 // then Squelch (noise_reduction/squelch.h:55-69, the complex_t overload); either may be off.
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel);
 void orc_ifchain_destroy(void* h);
 int orc_ifchain_process(void* h, int count, const float* in, float* out);
+// dsp::noise_reduction::FMIF (noise_reduction/fm_if.h:45-80), the last block of the IF chain (radio_module.h:93,98): per
+// sample, Nuttall-windowed `bins`-point forward DFT of the newest `bins` samples, all bins but the strongest zeroed,
+// backward DFT, element bins/2 of the result.  FFTW is served by oracle/shim/fftw3.h.
+void* orc_fmif_create(int bins);
+void orc_fmif_destroy(void* h);
+int orc_fmif_process(void* h, int count, const float* in, float* out);
+// dsp::audio::Volume (audio/volume.h:13-50), the sink stream's volume block (signal_path/sink.h:73): gain = volume^2 in float, 0 when muted
+int orc_volume_process(double volume, int muted, int count, const float* inStereo, float* outStereo);
 // radio AF chain (decoder_modules/radio/src/radio_module.h:101-107,756-765): RationalResampler<stereo_t> to the audio
 // device rate, then optional Deemphasis<stereo_t> (filter/deephasis.h:58-76).  tau <= 0 disables the de-emphasis.
 void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau);

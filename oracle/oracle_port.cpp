@@ -484,8 +484,16 @@ struct WfmDemod {
     int delay = 0; std::vector<float> lprBuf; std::vector<cf> lmrBuf;   // math::Delay buffers: [delay samples | block]
     Fir<float> alFir, arFir;
     std::vector<float> mpx, l, r, lmr; std::vector<cf> rtoc, pil, vco, lmrD;
-    void init(double deviation, double sr, bool st, bool lp) {
-        stereo = st; lowPassOn = lp;
+    bool rdsOn = false; Xlator rdsXlator; Rational rdsResamp; int rdsCount = 0;   // broadcast_fm.h:52-53
+    // RDS branch (broadcast_fm.h:169-175 stereo, :197-206 mono): the MPX as complex, down by 57 kHz, resampled to 5 kS/s
+    void rds(int count, cf* rdsOut) {
+        rdsXlator.process(count, rtoc.data(), rtoc.data());
+        rdsCount = rdsResamp.process(count, rtoc.data(), rdsOut);
+    }
+    void init(double deviation, double sr, bool st, bool lp, bool rdsOut = false) {
+        stereo = st; lowPassOn = lp; rdsOn = rdsOut;
+        rdsXlator.setOffset(-57000.0, sr);
+        rdsResamp.init(sr, 5000.0);
         invDeviation = (float)(1.0 / hzToRads(deviation, sr));
         pilotTaps = bandPassComplex(18750.0, 19250.0, 3000.0, sr, true);
         pilotBuf.assign(pilotTaps.size() + 4096, cf{ 0.f, 0.f });
@@ -505,7 +513,8 @@ struct WfmDemod {
         alFir.init(at); arFir.init(at);
     }
     template <typename V> static void fit(V& v, size_t n) { if (v.size() < n) { v.resize(n); } }
-    int process(int count, const cf* in, float* outStereo) {
+    int process(int count, const cf* in, float* outStereo, cf* rdsOut = nullptr) {
+        rdsCount = 0;
         fit(mpx, count); fit(l, count); fit(r, count); fit(lmr, count); fit(rtoc, count); fit(pil, count); fit(vco, count); fit(lmrD, count);
         for (int i = 0; i < count; i++) {
             const float cphase = atan2f(in[i].im, in[i].re);
@@ -513,6 +522,10 @@ struct WfmDemod {
             qphase = cphase;
         }
         if (!stereo) {
+            if (rdsOn) {
+                for (int i = 0; i < count; i++) { rtoc[i] = cf{ mpx[i], 0.0f }; }
+                rds(count, rdsOut);
+            }
             if (lowPassOn) { alFir.processFir(count, mpx.data(), mpx.data()); }
             for (int i = 0; i < count; i++) { outStereo[2 * i] = mpx[i]; outStereo[2 * i + 1] = mpx[i]; }
             return count;
@@ -559,6 +572,7 @@ struct WfmDemod {
             l[i] = mpx[i] + lmr[i];
             r[i] = mpx[i] - lmr[i];
         }
+        if (rdsOn) { rds(count, rdsOut); }   // rtoc still holds the undelayed MPX
         if (lowPassOn) { alFir.processFir(count, l.data(), l.data()); arFir.processFir(count, r.data(), r.data()); }
         for (int i = 0; i < count; i++) { outStereo[2 * i] = l[i]; outStereo[2 * i + 1] = r[i]; }
         return count;
@@ -640,6 +654,55 @@ struct IfChain {
             sum /= (float)count;
             if (!(10.0f * log10f(sum) >= sqLevel)) { for (int i = 0; i < count; i++) { out[i].re = 0.f; out[i].im = 0.f; } }
         }
+        return count;
+    }
+};
+
+// ------------------------------------------------------------------ noise_reduction::FMIF — fm_if.h:45-80,106-124
+// Per sample: window the newest `bins` samples (Nuttall over bins-1, volk_32fc_32f_multiply_32fc), forward DFT, keep the
+// strongest bin only (generic volk_32fc_magnitude_32f + volk_32f_index_max_32u: the first of equal maxima), backward DFT,
+// take element bins/2.  The DFTs follow oracle/shim/fftw3.h: float64 sums in index order, narrowed to fp32 once.
+struct FmIf {
+    int bins = 0;
+    std::vector<cf> buf; std::vector<float> win; std::vector<double> cs, sn;
+    void init(int b) {
+        bins = b;
+        buf.assign((size_t)bins - 1 + 4096, cf{ 0.f, 0.f });
+        win.resize(bins);
+        for (int i = 0; i < bins; i++) { win[i] = nuttall(i, bins - 1); }
+        cs.resize(bins); sn.resize(bins);
+        for (int m = 0; m < bins; m++) {
+            const double a = 2.0 * 3.14159265358979323846 * (double)m / (double)bins;
+            cs[m] = cos(a); sn[m] = sin(a);
+        }
+    }
+    int process(int count, const cf* in, cf* out) {
+        if (buf.size() < (size_t)bins - 1 + count) { buf.resize((size_t)bins - 1 + count); }
+        memcpy(&buf[bins - 1], in, (size_t)count * sizeof(cf));
+        std::vector<cf> w(bins), X(bins);
+        for (int i = 0; i < count; i++) {
+            for (int n = 0; n < bins; n++) { w[n] = cf{ buf[i + n].re * win[n], buf[i + n].im * win[n] }; }
+            for (int k = 0; k < bins; k++) {
+                double sr = 0.0, si = 0.0;
+                for (int n = 0; n < bins; n++) {
+                    const int m = (int)(((long long)k * n) % bins);
+                    const double c = cs[m], s = -sn[m];
+                    const double xr = w[n].re, xi = w[n].im;
+                    sr += xr * c - xi * s;
+                    si += xr * s + xi * c;
+                }
+                X[k] = cf{ (float)sr, (float)si };
+            }
+            int idx = 0; float best = sqrtf(X[0].re * X[0].re + X[0].im * X[0].im);
+            for (int k = 1; k < bins; k++) {
+                const float a = sqrtf(X[k].re * X[k].re + X[k].im * X[k].im);
+                if (a > best) { best = a; idx = k; }
+            }
+            const int m = (int)(((long long)(bins / 2) * idx) % bins);
+            const double xr = X[idx].re, xi = X[idx].im;
+            out[i] = cf{ (float)(xr * cs[m] - xi * sn[m]), (float)(xr * sn[m] + xi * cs[m]) };
+        }
+        memmove(buf.data(), &buf[count], (size_t)(bins - 1) * sizeof(cf));
         return count;
     }
 };
@@ -806,6 +869,17 @@ int orc_am_process(void* h, int count, const float* in, float* out) { return ((A
 void* orc_wfm_create(double deviation, double samplerate, int stereo, int lowPass) { auto* d = new WfmDemod; d->init(deviation, samplerate, stereo != 0, lowPass != 0); return d; }
 void orc_wfm_destroy(void* h) { delete (WfmDemod*)h; }
 int orc_wfm_process(void* h, int count, const float* in, float* out) { return ((WfmDemod*)h)->process(count, (const cf*)in, out); }
+void* orc_wfm_create_rds(double deviation, double samplerate, int stereo, int lowPass) { auto* d = new WfmDemod; d->init(deviation, samplerate, stereo != 0, lowPass != 0, true); return d; }
+int orc_wfm_process_rds(void* h, int count, const float* in, float* out, float* rdsOut) { auto* d = (WfmDemod*)h; d->process(count, (const cf*)in, out, (cf*)rdsOut); return d->rdsCount; }
+void* orc_fmif_create(int bins) { auto* f = new FmIf; f->init(bins); return f; }
+void orc_fmif_destroy(void* h) { delete (FmIf*)h; }
+int orc_fmif_process(void* h, int count, const float* in, float* out) { return ((FmIf*)h)->process(count, (const cf*)in, (cf*)out); }
+int orc_volume_process(double volume, int muted, int count, const float* in, float* out) {   // audio/volume.h:13-16,47-50
+    const float v = powf(volume, 2);
+    const float g = muted ? 0.0f : v;
+    for (int i = 0; i < 2 * count; i++) { out[i] = in[i] * g; }
+    return count;
+}
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int sqOn, double sqLevel) { auto* c = new IfChain; c->init(nbOn, nbRate, nbLevel, sqOn, sqLevel); return c; }
 void orc_ifchain_destroy(void* h) { delete (IfChain*)h; }
 int orc_ifchain_process(void* h, int count, const float* in, float* out) { return ((IfChain*)h)->process(count, (const cf*)in, (cf*)out); }

@@ -47,6 +47,8 @@
 #include <dsp/demod/broadcast_fm.h>
 #include <dsp/noise_reduction/noise_blanker.h>
 #include <dsp/noise_reduction/squelch.h>
+#include <dsp/noise_reduction/fm_if.h>
+#include <dsp/audio/volume.h>
 #undef protected
 #undef private
 
@@ -267,6 +269,30 @@ void orc_wfm_destroy(void* h) { delete (dsp::demod::BroadcastFM*)h; }
 int orc_wfm_process(void* h, int count, const float* in, float* out) {
     int rdsCount = 0;
     return ((dsp::demod::BroadcastFM*)h)->process(count, (complex_t*)in, (stereo_t*)out, rdsCount, NULL);
+}
+void* orc_wfm_create_rds(double deviation, double samplerate, int stereo, int lowPass) {
+    auto* d = new dsp::demod::BroadcastFM;
+    d->init(NULL, deviation, samplerate, stereo != 0, lowPass != 0, true);
+    return d;
+}
+int orc_wfm_process_rds(void* h, int count, const float* in, float* out, float* rdsOut) {
+    int rdsCount = 0;
+    ((dsp::demod::BroadcastFM*)h)->process(count, (complex_t*)in, (stereo_t*)out, rdsCount, (complex_t*)rdsOut);
+    return rdsCount;
+}
+void* orc_fmif_create(int bins) {
+    auto* f = new dsp::noise_reduction::FMIF;
+    f->init(NULL, bins);
+    return f;
+}
+void orc_fmif_destroy(void* h) { delete (dsp::noise_reduction::FMIF*)h; }
+int orc_fmif_process(void* h, int count, const float* in, float* out) {
+    return ((dsp::noise_reduction::FMIF*)h)->process(count, (const complex_t*)in, (complex_t*)out);
+}
+int orc_volume_process(double volume, int muted, int count, const float* in, float* out) {
+    dsp::audio::Volume v;
+    v.init(NULL, volume, muted != 0);
+    return v.process(count, (const stereo_t*)in, (stereo_t*)out);
 }
 namespace { struct IfChain { dsp::noise_reduction::NoiseBlanker nb; dsp::noise_reduction::Squelch sq; bool nbOn, sqOn; }; }
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel) {

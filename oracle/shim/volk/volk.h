@@ -16,6 +16,7 @@
 //   signal_path/iq_frontend.cpp:271,282        window multiply, power spectrum
 //   dsp/demod/am.h:109,120                     magnitude
 //   dsp/convert/complex_to_real.h:15, mono_to_stereo.h:13   deinterleave / interleave
+//   dsp/noise_reduction/fm_if.h:51,58-59       window multiply, magnitude, index of the maximum
 #pragma once
 #include <complex>
 #include <cstdlib>
@@ -126,6 +127,16 @@ static inline void volk_32fc_magnitude_32f(float* out, const lv_32fc_t* in, unsi
         const float r = in[i].real(), q = in[i].imag();
         out[i] = sqrtf(r * r + q * q);
     }
+}
+// index of the maximum: the first of equal maxima wins (strict >), as in VOLK's generic kernel
+static inline void volk_32f_index_max_32u(uint32_t* target, const float* src, uint32_t n) {
+    if (n == 0) { return; }
+    float best = src[0];
+    uint32_t idx = 0;
+    for (uint32_t i = 1; i < n; i++) {
+        if (src[i] > best) { best = src[i]; idx = i; }
+    }
+    *target = idx;
 }
 static inline void volk_32fc_deinterleave_real_32f(float* out, const lv_32fc_t* in, unsigned int n) {
     for (unsigned int i = 0; i < n; i++) { out[i] = in[i].real(); }

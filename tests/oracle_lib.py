@@ -68,6 +68,12 @@ _SIGS = {
     "orc_wfm_create": (_vp, [_d, _d, _i, _i]),
     "orc_wfm_destroy": (None, [_vp]),
     "orc_wfm_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_wfm_create_rds": (_vp, [_d, _d, _i, _i]),
+    "orc_wfm_process_rds": (_i, [_vp, _i, _vp, _vp, _vp]),
+    "orc_fmif_create": (_vp, [_i]),
+    "orc_fmif_destroy": (None, [_vp]),
+    "orc_fmif_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_volume_process": (_i, [_d, _i, _i, _vp, _vp]),
     "orc_ifchain_create": (_vp, [_i, _d, _d, _i, _d]),
     "orc_ifchain_destroy": (None, [_vp]),
     "orc_ifchain_process": (_i, [_vp, _i, _vp, _vp]),
@@ -305,6 +311,39 @@ class Wfm(_Block):
         out = np.zeros((len(x), 2), np.float32)
         n = self.orc.lib.orc_wfm_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
         return out[:n]
+
+
+class WfmRds(_Block):
+    """demod::BroadcastFM with the RDS branch on: process() returns (stereo audio, complex RDS baseband at 5 kS/s)"""
+    def __init__(self, orc, deviation, samplerate, stereo, low_pass=True):
+        super().__init__(orc, orc.lib.orc_wfm_create_rds(deviation, samplerate, int(stereo), int(low_pass)), "orc_wfm")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros((len(x), 2), np.float32)
+        rds = np.zeros(len(x) + 1024, np.complex64)       # the resampler's stages also use it as scratch
+        n = self.orc.lib.orc_wfm_process_rds(self.h, len(x), x.ctypes.data, out.ctypes.data, rds.ctypes.data)
+        return out, rds[:n].copy()
+
+
+class FmIf(_Block):
+    """noise_reduction::FMIF: complex in, complex out, same count"""
+    def __init__(self, orc, bins):
+        super().__init__(orc, orc.lib.orc_fmif_create(int(bins)), "orc_fmif")
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(len(x), np.complex64)
+        self.orc.lib.orc_fmif_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out
+
+
+def volume(orc, vol, muted, x):
+    """audio::Volume on a stereo block"""
+    x = np.ascontiguousarray(x, np.float32).reshape(-1, 2)
+    out = np.zeros_like(x)
+    orc.lib.orc_volume_process(float(vol), int(muted), len(x), x.ctypes.data, out.ctypes.data)
+    return out
 
 
 class IfChain(_Block):

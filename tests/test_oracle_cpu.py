@@ -245,3 +245,87 @@ def test_radio_chain_blocks_port_equals_ref_bitwise():
         p, r = ol.Wfm(PORT, 75e3, sr, stereo, lp), ol.Wfm(REF, 75e3, sr, stereo, lp)
         for i in range(0, n, 17000):
             assert p.process(iq[i:i + 17000]).tobytes() == r.process(iq[i:i + 17000]).tobytes(), (stereo, lp)
+
+
+def fmif_model(x, bins, hist=None):
+    """float64 numpy model of noise_reduction::FMIF (fm_if.h:45-80): returns (out, relative margin between the two
+    strongest bins of every window).  The window is Nuttall over bins-1 (fm_if.h:118); the backward DFT of a single
+    bin evaluated at element bins/2 is X[idx] * exp(+2 pi i idx (bins//2) / bins)."""
+    n = np.arange(bins)
+    c = [0.355768, 0.487396, 0.144232, 0.012604]
+    win = sum(((-1) ** k) * c[k] * np.cos(2 * np.pi * k * n / (bins - 1)) for k in range(4))
+    hist = np.zeros(bins - 1, np.complex128) if hist is None else hist
+    buf = np.concatenate([hist, x.astype(np.complex128)])
+    seg = np.lib.stride_tricks.sliding_window_view(buf, bins)[:len(x)]
+    # fp32 window product as the reference forms it, then the transform in float64
+    segw = (seg.real.astype(np.float32) * win.astype(np.float32)).astype(np.float64) + \
+        1j * (seg.imag.astype(np.float32) * win.astype(np.float32)).astype(np.float64)
+    F = np.exp(-2j * np.pi * np.outer(n, n) / bins)
+    X = segw @ F
+    mag = np.abs(X)
+    idx = np.argmax(mag, axis=1)
+    top2 = np.sort(mag, axis=1)[:, -2:]
+    margin = (top2[:, 1] - top2[:, 0]) / np.maximum(top2[:, 1], 1e-30)
+    out = X[np.arange(len(x)), idx] * np.exp(2j * np.pi * idx * (bins // 2) / bins)
+    return out, margin, buf[len(x):]
+
+
+@pytest.mark.parametrize("bins", [9, 15, 31, 32])
+def test_fmif_port_against_numpy_model_and_ref(bins):
+    """FM IF noise reduction at the radio module's four presets (radio/src/main.cpp:11-16): the restatement against a
+    float64 model (wherever the strongest bin is not a near-tie) and, bit for bit, against the reference's own header
+    compiled on oracle/shim/fftw3.h."""
+    rng = np.random.default_rng(100 + bins)
+    n = 6000
+    t = np.arange(n)
+    x = (0.4 * np.exp(2j * np.pi * (0.07 * t + 0.02 * np.sin(2 * np.pi * t / 700.0) * 50))
+         + 0.1 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    x[2000:2100] = 0                                     # all bins equal: index 0 wins, output 0
+    p = ol.FmIf(PORT, bins)
+    r = ol.FmIf(REF, bins) if REF is not None else None
+    hist = None
+    for i in range(0, n, 1700):
+        blk = x[i:i + 1700]
+        y = p.process(blk)
+        model, margin, hist = fmif_model(blk, bins, hist)
+        ok = margin > 1e-5
+        assert ok.sum() > 0.98 * len(blk) - 100
+        e = y[ok] - model[ok]
+        assert np.sqrt(np.mean(np.abs(e) ** 2)) <= 1e-6 * max(1e-9, np.sqrt(np.mean(np.abs(model[ok]) ** 2))) + 1e-12
+        if r is not None:
+            assert r.process(blk).tobytes() == y.tobytes()
+    assert not np.any(ol.FmIf(PORT, bins).process(np.zeros(10, np.complex64)))
+
+
+def test_wfm_rds_branch_and_volume_port_equals_ref():
+    """BroadcastFM with rdsOut (mono and stereo): audio and the 5 kS/s RDS baseband, port against the reference headers
+    bit for bit; a 57 kHz subcarrier in the MPX must come out of the branch at 0 Hz.  audio::Volume likewise."""
+    sr, n = 500e3, 60000
+    t = np.arange(n) / sr
+    mpx = 0.3 * np.sin(2 * np.pi * 1000 * t) + 0.1 * np.sin(2 * np.pi * 19000 * t) + 0.05 * np.cos(2 * np.pi * 57000 * t)
+    iq = np.exp(1j * 2 * np.pi * 75e3 * np.cumsum(mpx) / sr).astype(np.complex64)
+    for stereo, lp in [(0, 1), (1, 1)]:
+        p = ol.WfmRds(PORT, 75e3, sr, stereo, lp)
+        r = ol.WfmRds(REF, 75e3, sr, stereo, lp) if REF is not None else None
+        plain = ol.Wfm(PORT, 75e3, sr, stereo, lp)
+        rds_all = []
+        for i in range(0, n, 17001):
+            a, rds = p.process(iq[i:i + 17001])
+            assert a.tobytes() == plain.process(iq[i:i + 17001]).tobytes()      # the branch does not touch the audio
+            if r is not None:
+                a2, rds2 = r.process(iq[i:i + 17001])
+                assert a.tobytes() == a2.tobytes() and rds.tobytes() == rds2.tobytes(), (stereo, lp)
+            rds_all.append(rds)
+        rds = np.concatenate(rds_all)
+        assert abs(len(rds) - n * 5000 / sr) <= 2
+        tail = rds[len(rds) // 2:]
+        # 0.05 cos(57 kHz) -> 0.025 at DC after the -57 kHz shift (the other half lands at -114 kHz and is filtered out)
+        assert abs(abs(np.mean(tail)) - 0.025) < 0.004
+        assert np.std(tail - np.mean(tail)) < 0.01
+    au = np.random.default_rng(3).standard_normal((1000, 2)).astype(np.float32)
+    for vol, muted in [(0.5, 0), (1.0, 0), (0.37, 0), (0.8, 1)]:
+        y = ol.volume(PORT, vol, muted, au)
+        assert np.array_equal(y, au * (np.float32(0) if muted else np.float32(vol) ** 2)) or \
+            np.allclose(y, au * (0.0 if muted else vol ** 2), rtol=2e-7, atol=0)
+        if REF is not None:
+            assert ol.volume(REF, vol, muted, au).tobytes() == y.tobytes()
