@@ -138,7 +138,10 @@ int b200_vfo_max_out(b200_vfo_bank* bank, int vfo, int count);
  *   B200_DEMOD_AM   dsp::demod::AM<stereo_t>   (demod/am.h:101-133); p0=agcMode (0 CARRIER,1 AUDIO) p1=attack p2=decay p3=dcBlockRate
  *   B200_DEMOD_USB/LSB/DSB dsp::demod::SSB<stereo_t> (demod/ssb.h:82-97); p1=attack p2=decay
  *   B200_DEMOD_WFM  dsp::demod::BroadcastFM      (demod/broadcast_fm.h:144-190; deviation = bandwidth / 2 as in
- *                   radio/src/demodulators/wfm.h:76); p0=stereo p1=lowPass (flags) p2=rds (must be 0: no RDS branch)
+ *                   radio/src/demodulators/wfm.h:76); p0=stereo p1=lowPass p2=rdsOut (flags).  With rdsOut the RDS branch
+ *                   (broadcast_fm.h:169-175,197-206: MPX as complex, FrequencyXlator by -57 kHz, RationalResampler<complex_t>
+ *                   to 5 kS/s) runs too; its output is read with b200_vfo_rds_ptr / b200_vfo_rds_count and is what the
+ *                   reference hands to its host-side RDS bit decoder (radio/src/demodulators/wfm.h rdsHandler).
  * attack/decay/dcBlockRate are per-sample coefficients as the radio module passes them
  * (e.g. 50.0/IF rate, usb.h:34).  Demodulation runs at the VFO's out_samplerate with
  * `bandwidth` = the VFO bandwidth.  Audio (stereo {l,r}, same count as the VFO output) is
@@ -158,6 +161,16 @@ int b200_vfo_set_demod(b200_vfo_bank* bank, int vfo, int kind, double p0, double
  * reference).  Both are off by default, as in the reference.  b200_vfo_out_ptr keeps naming the VFO output in front
  * of the chain.  Needs a demodulator on the VFO; b200_vfo_set_demod() drops the setting again. */
 int b200_vfo_set_if_chain(b200_vfo_bank* bank, int vfo, int nb_enabled, double nb_rate, double nb_level, int squelch_enabled, double squelch_level);
+/* The last block of that chain: dsp::noise_reduction::FMIF (core/src/dsp/noise_reduction/fm_if.h:45-80; radio_module.h:93,98,
+ * setFMIFNREnabled :856-860, setIFNRPreset / FMIF::setBins :880-891).  Per sample: Nuttall-windowed `bins`-point DFT of the
+ * newest `bins` samples, strongest bin kept alone, backward DFT, element bins/2.  bins in 2..32 (the reference's
+ * presets: 9 NOAA APT, 15 voice, 31 narrow band, 32 broadcast; radio/src/main.cpp:11-16).  Enabling it, or changing bins,
+ * starts from a cleared delay line as FMIF::setBins does. */
+int b200_vfo_set_if_nr(b200_vfo_bank* bank, int vfo, int enabled, int bins);
+/* What the demodulator read in the last process call: the IF chain's output (ifChain.out, radio_module.h:92-98,
+ * selectedDemod->setInput at :859), device cf32[out_count]; the VFO output itself when no chain block is on.  NULL
+ * without a demodulator. */
+const float* b200_vfo_if_ptr(b200_vfo_bank* bank, int vfo);
 /* The radio module's AF chain behind the demodulator (decoder_modules/radio/src/radio_module.h:101-107,756-765):
  * dsp::multirate::RationalResampler<stereo_t> from the demodulator's rate to the audio device rate, then
  * dsp::filter::Deemphasis<stereo_t> (core/src/dsp/filter/deephasis.h:58-92).  audio_samplerate <= 0 keeps the audio at
@@ -167,6 +180,14 @@ int b200_vfo_set_audio_post(b200_vfo_bank* bank, int vfo, double audio_samplerat
 const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo);    /* device stereo[audio_count] or NULL */
 int b200_vfo_audio_count(b200_vfo_bank* bank, int vfo);           /* stereo samples of the last call (== out_count without a resampler) */
 int b200_vfo_audio_max_out(b200_vfo_bank* bank, int vfo, int count);   /* upper bound of audio_count for `count` input samples */
+/* The sink stream's volume block behind the AF chain: dsp::audio::Volume (core/src/dsp/audio/volume.h:13-50;
+ * SinkManager::Stream::volumeAjust, signal_path/sink.h:73, setVolume :44).  Audio is scaled by volume^2 (0 when muted),
+ * in place in the buffer b200_vfo_audio_ptr names.  Off until first called; b200_vfo_set_demod() drops it again. */
+int b200_vfo_set_volume(b200_vfo_bank* bank, int vfo, double volume, int muted);
+/* RDS baseband of a B200_DEMOD_WFM demodulator created with p2 != 0: device cf32[rds_count] at 5 kS/s
+ * (BroadcastFM::rdsOut, broadcast_fm.h:233). */
+const float* b200_vfo_rds_ptr(b200_vfo_bank* bank, int vfo);
+int b200_vfo_rds_count(b200_vfo_bank* bank, int vfo);
 
 /* ------------------------------------------------------------------------------------------
  * IQ front end — replaces IQFrontEnd (signal_path/iq_frontend.{h,cpp}): pre-processing chain

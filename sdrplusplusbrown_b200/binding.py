@@ -53,6 +53,11 @@ _SIGS = {
     "b200_vfo_set_demod": (_i, [_vp, _i, _i, _d, _d, _d, _d]),
     "b200_vfo_set_audio_post": (_i, [_vp, _i, _d, _d]),
     "b200_vfo_set_if_chain": (_i, [_vp, _i, _i, _d, _d, _i, _d]),
+    "b200_vfo_set_if_nr": (_i, [_vp, _i, _i, _i]),
+    "b200_vfo_set_volume": (_i, [_vp, _i, _d, _i]),
+    "b200_vfo_rds_ptr": (_vp, [_vp, _i]),
+    "b200_vfo_if_ptr": (_vp, [_vp, _i]),
+    "b200_vfo_rds_count": (_i, [_vp, _i]),
     "b200_vfo_audio_ptr": (_vp, [_vp, _i]),
     "b200_vfo_audio_count": (_i, [_vp, _i]),
     "b200_vfo_audio_max_out": (_i, [_vp, _i, _i]),
@@ -201,6 +206,32 @@ class VfoBank:
     def set_if_chain(self, v, nb=False, nb_rate=0.0, nb_level=0.0, squelch=False, squelch_level=0.0):
         """radio IF chain in front of the demodulator: noise blanker -> squelch"""
         _chk(lib.b200_vfo_set_if_chain(self.h, v, int(nb), float(nb_rate), float(nb_level), int(squelch), float(squelch_level)))
+
+    def set_if_nr(self, v, enabled=True, bins=32):
+        """FM IF noise reduction (noise_reduction::FMIF), the last block of the IF chain"""
+        _chk(lib.b200_vfo_set_if_nr(self.h, v, int(enabled), int(bins)))
+
+    def set_volume(self, v, volume=1.0, muted=False):
+        """sink-side audio::Volume behind the AF chain"""
+        _chk(lib.b200_vfo_set_volume(self.h, v, float(volume), int(muted)))
+
+    def if_output(self, v):
+        """the demodulator's input of the last call: the IF chain's output"""
+        n = self.out_count(v)
+        p = lib.b200_vfo_if_ptr(self.h, v)
+        if n == 0 or not p:
+            return np.zeros(0, np.complex64)
+        return _dev_to_numpy(p, n, np.complex64, self.device)
+
+    def rds_count(self, v): return _chk(lib.b200_vfo_rds_count(self.h, v))
+
+    def rds(self, v):
+        """5 kS/s complex RDS baseband of a WFM demodulator created with p2 != 0"""
+        n = self.rds_count(v)
+        p = lib.b200_vfo_rds_ptr(self.h, v)
+        if n == 0 or not p:
+            return np.zeros(0, np.complex64)
+        return _dev_to_numpy(p, n, np.complex64, self.device)
 
     def set_audio_post(self, v, audio_samplerate=0.0, deemph_tau=0.0):
         """radio AF chain behind the demodulator: resampler to the audio rate + de-emphasis (0 = leave out)"""

@@ -63,6 +63,20 @@ struct DemodState {
     float pllAlpha = 0.f, pllBeta = 0.f, pllMinFreq = 0.f, pllMaxFreq = 0.f;
     int wfmDelay = 0; float* dDelayHist[2] = { nullptr, nullptr }; int delayCur = 0;   // math::Delay of the MPX
     float* dPllPhase = nullptr; float* dL = nullptr; float* dR = nullptr;
+    // FM IF noise reduction, the last block of the IF chain (noise_reduction/fm_if.h; radio_module.h:93,98)
+    bool fmOn = false; int fmBins = 0;
+    float2* dFmTab = nullptr;                // [32][32] window x forward twiddle, then [32] backward twiddles of element bins/2
+    cf32* dFmHist[2] = { nullptr, nullptr }; int fmCur = 0;   // the bins-1 samples in front of the next block
+    cf32* dFm = nullptr; int fmCap = 0;
+    // sink-side volume (audio/volume.h; signal_path/sink.h:73)
+    bool volOn = false; float volGain = 1.0f;
+    // RDS branch of the broadcast FM demodulator (broadcast_fm.h:52-53,169-175,197-206)
+    bool rdsOn = false;
+    float rdsDRe = 1.f, rdsDIm = 0.f; double rdsTheta = 0.0, rdsAngle = 0.0;
+    float2* dRdsWtab = nullptr; float2* dRdsChk = nullptr; float2* dRdsPhase = nullptr; cf32* dRdsX = nullptr; int rdsCap = 0;
+    std::vector<Stage> rdsDecim; Stage rdsPoly; bool rdsHasPoly = false; int rdsMode = 3;
+    const float* lastRds = nullptr; int lastRdsCount = 0;
+    const cf32* lastIf = nullptr;            // what the demodulator read in the last call (the IF chain's output)
 };
 
 // per-call descriptors of the WFM stereo stages
@@ -72,6 +86,11 @@ struct LrJob { const float* l; const float* r; float* stereo; int n, pad; };
 
 // per-call descriptor of the IF chain
 struct IfJob { const cf32* in; cf32* out; SeqState* st; float rate, invRate, nbLevel, sqLevel; int n, nbOn, sqOn, pad; };
+
+// per-call descriptors of the FM IF noise reduction, the volume block and the RDS down-conversion
+struct FmifJob { const cf32* in; cf32* out; const cf32* hist; cf32* histNext; const float2* tab; int n, bins; };
+struct VolJob { float* data; float gain; int nFloats; };
+struct RdsXlateJob { const float* mpx; cf32* out; const float2* chk; const float2* wtab; int n, pad; };
 
 // per-call descriptor of the de-emphasis walk
 struct DeemphJob { float2* data; SeqState* st; float alpha; int n; };
@@ -612,6 +631,95 @@ __global__ void __launch_bounds__(64) deemphKernel(const DeemphJob* __restrict__
     if (threadIdx.x == 1 && j.n > 0) { j.st->deLast.y = prev; }
 }
 
+// FM IF noise reduction (noise_reduction/fm_if.h:45-80).  For every sample the reference windows the newest `bins`
+// samples, runs a forward FFT, keeps the strongest bin alone, runs the backward FFT and takes element bins/2: that is
+//     out[i] = X_i[k*] * exp(+2 pi i k* (bins/2) / bins),   X_i[k] = sum_n win[n] x[i+n] exp(-2 pi i k n / bins),
+// k* the first of the strongest bins.  Windows of neighbouring samples are independent, so one warp takes a sample at a
+// time with lane k holding bin k: the lane's column of the (window x twiddle) matrix stays in registers, the samples
+// come out of shared memory as broadcasts, the strongest bin is found with a warp reduction (ties to the lower index,
+// NaN handled like VOLK's generic index_max: only a NaN in bin 0 wins).  bins <= 32 (the reference's presets are 9,
+// 15, 31 and 32; radio/src/main.cpp:11-16).
+constexpr int kFmTile = 512, kFmThreads = 128, kFmMaxBins = 32;
+__global__ void __launch_bounds__(kFmThreads) fmifKernel(const FmifJob* __restrict__ jobs) {
+    const FmifJob j = jobs[blockIdx.y];
+    const int base = blockIdx.x * kFmTile;
+    if (base >= j.n) { return; }
+    __shared__ float2 sx[kFmTile + kFmMaxBins];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bins = j.bins, H = bins - 1;
+    const int m = min(kFmTile, j.n - base);
+    const float2* in = reinterpret_cast<const float2*>(j.in);
+    const float2* hist = reinterpret_cast<const float2*>(j.hist);
+    for (int i = tid; i < m + H; i += kFmThreads) {
+        const int g = base + i - H;                        // position in this block's input; negative = carried history
+        sx[i] = g >= 0 ? __ldg(in + g) : __ldg(hist + H + g);
+    }
+    if (blockIdx.x == 0) {
+        // the samples in front of the next block (fm_if.h:72): the last bins-1 of [history | block]
+        float2* next = reinterpret_cast<float2*>(j.histNext);
+        for (int t = tid; t < H; t += kFmThreads) {
+            const int g = j.n + t - H;
+            next[t] = g >= 0 ? __ldg(in + g) : __ldg(hist + H + g);
+        }
+    }
+    float2 t[kFmMaxBins];
+#pragma unroll
+    for (int n = 0; n < kFmMaxBins; n++) { t[n] = (n < bins && lane < bins) ? __ldg(j.tab + n * kFmMaxBins + lane) : make_float2(0.f, 0.f); }
+    const float2 back = lane < bins ? __ldg(j.tab + kFmMaxBins * kFmMaxBins + lane) : make_float2(0.f, 0.f);
+    __syncthreads();
+    float2* out = reinterpret_cast<float2*>(j.out);
+    for (int g0 = warp * 32; g0 < m; g0 += (kFmThreads / 32) * 32) {
+        const int cnt = min(32, m - g0);
+        float2 res = make_float2(0.f, 0.f);
+        for (int q = 0; q < cnt; q++) {
+            const float2* x = sx + g0 + q;
+            float re0 = 0.f, im0 = 0.f, re1 = 0.f, im1 = 0.f;
+#pragma unroll
+            for (int n = 0; n < kFmMaxBins; n++) {
+                if (n < bins) {
+                    const float2 v = x[n];
+                    re0 = fmaf(v.x, t[n].x, re0); re1 = fmaf(-v.y, t[n].y, re1);
+                    im0 = fmaf(v.x, t[n].y, im0); im1 = fmaf(v.y, t[n].x, im1);
+                }
+            }
+            const float re = re0 + re1, im = im0 + im1;
+            float mag = sqrtf(__fadd_rn(__fmul_rn(re, re), __fmul_rn(im, im)));
+            const bool nan0 = __shfl_sync(0xffffffffu, mag != mag ? 1 : 0, 0) != 0;
+            if (lane >= bins || mag != mag) { mag = -1.0f; }
+            int idx = lane;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float om = __shfl_xor_sync(0xffffffffu, mag, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+                if (om > mag || (om == mag && oi < idx)) { mag = om; idx = oi; }
+            }
+            if (nan0) { idx = 0; }
+            const float xr = __shfl_sync(0xffffffffu, re, idx), xi = __shfl_sync(0xffffffffu, im, idx);
+            const float br = __shfl_sync(0xffffffffu, back.x, idx), bi = __shfl_sync(0xffffffffu, back.y, idx);
+            if (lane == q) { res = make_float2(xr * br - xi * bi, xr * bi + xi * br); }
+        }
+        if (lane < cnt) { out[base + g0 + lane] = res; }
+    }
+}
+
+// audio::Volume (audio/volume.h:47-50): every float of the stereo block times volume^2 (0 when muted), in place
+__global__ void __launch_bounds__(256) volumeKernel(const VolJob* __restrict__ jobs) {
+    const VolJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < j.nFloats) { j.data[i] = __fmul_rn(j.data[i], j.gain); }
+}
+
+// RDS branch, first half (broadcast_fm.h:171,200-203): RealToComplex of the MPX, then FrequencyXlator by -57 kHz.  With a
+// zero imaginary part the rotator's complex product reduces to (x * phase.re, x * phase.im).
+__global__ void __launch_bounds__(256) rdsXlateKernel(const RdsXlateJob* __restrict__ jobs) {
+    const RdsXlateJob j = jobs[blockIdx.y];
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= j.n) { return; }
+    const float2 ph = rotPhaseAt(j.chk, j.wtab, i);
+    const float x = __ldg(j.mpx + i);
+    reinterpret_cast<float2*>(j.out)[i] = make_float2(__fmul_rn(x, ph.x), __fmul_rn(x, ph.y));
+}
+
 } // namespace
 
 void demodDestroy(DemodState* d) {
@@ -631,10 +739,28 @@ void demodDestroy(DemodState* d) {
     if (d->dPllPhase) { cudaFree(d->dPllPhase); }
     if (d->dL) { cudaFree(d->dL); }
     if (d->dR) { cudaFree(d->dR); }
+    if (d->dFmTab) { cudaFree(d->dFmTab); }
+    for (int i = 0; i < 2; i++) { if (d->dFmHist[i]) { cudaFree(d->dFmHist[i]); } }
+    if (d->dFm) { cudaFree(d->dFm); }
+    for (auto& st : d->rdsDecim) { st.destroy(); }
+    d->rdsPoly.destroy();
+    for (void* q : { (void*)d->dRdsWtab, (void*)d->dRdsChk, (void*)d->dRdsPhase, (void*)d->dRdsX }) { if (q) { cudaFree(q); } }
     delete d;
 }
 
 int demodSwitchRotatorMode(DemodState* d, int newMode) {
+    if (d && d->rdsOn && d->dRdsPhase) {
+        // the RDS branch's -57 kHz rotator: fp32 phase on the device in EXACT mode, a float64 angle on the host in FAST mode
+        if (newMode == B200_ROTATOR_EXACT) {
+            const float2 p = make_float2((float)cos(d->rdsAngle), (float)sin(d->rdsAngle));
+            B200_CUDA(cudaMemcpy(d->dRdsPhase, &p, sizeof(float2), cudaMemcpyHostToDevice));
+        }
+        else {
+            float2 p;
+            B200_CUDA(cudaMemcpy(&p, d->dRdsPhase, sizeof(float2), cudaMemcpyDeviceToHost));
+            d->rdsAngle = atan2((double)p.y, (double)p.x);
+        }
+    }
     if (!d || !d->dWtab) { return B200_OK; }
     float2* dPhase = &d->dState->rotPhase;
     int* dEnv = &d->dState->audio.startEnvelope;
@@ -677,6 +803,40 @@ static int demodEnsureCap(DemodState& d, int n) {
         B200_TRY(d.pilotIm.ensureOutCap(d.cap));
         if (d.hasFir) { B200_TRY(d.firR.ensureOutCap(d.cap)); }
     }
+    if (d.rdsOn && d.rdsCap < d.cap) {
+        if (d.dRdsX) { cudaFree(d.dRdsX); d.dRdsX = nullptr; }
+        if (d.dRdsChk) { cudaFree(d.dRdsChk); d.dRdsChk = nullptr; }
+        d.rdsCap = d.cap;
+        B200_CUDA(cudaMalloc((void**)&d.dRdsX, (size_t)d.rdsCap * sizeof(cf32)));
+        B200_CUDA(cudaMalloc((void**)&d.dRdsChk, (size_t)(d.rdsCap / kRotChunk + 2) * sizeof(float2)));
+    }
+    return B200_OK;
+}
+
+// dsp::multirate::RationalResampler<T> for a two-float element (complex_t or stereo_t; rational_resampler.h:128-173) as
+// a cascade of stages: the power-of-two decimator's plan, then the polyphase resampler
+static int buildResampler(double inSR, double outSR, int cap, std::vector<Stage>& decim, Stage& poly, bool& hasPoly, int& mode) {
+    for (auto& st : decim) { st.destroy(); }
+    decim.clear();
+    poly.destroy(); hasPoly = false;
+    design::ResampPlan p = design::planResampler(inSR, outSR);
+    mode = p.mode;
+    if (p.mode == 0 || p.mode == 1) {
+        const design::PlanDef* plan = design::findPlan(p.ratio);
+        if (!plan) { setError("no decimation plan for ratio %d", p.ratio); return B200_EINVAL; }
+        decim.resize(plan->nstages);
+        for (int i = 0; i < plan->nstages; i++) {
+            std::vector<float> t(plan->stages[i].ntaps);
+            memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());   // the table holds IEEE bit patterns
+            cap = cap / plan->stages[i].decim + 2;
+            B200_TRY(decim[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap, true));
+        }
+    }
+    if (p.mode == 0 || p.mode == 2) {
+        const int pcap = (int)(((int64_t)cap * p.interp) / p.decim) + 4;
+        B200_TRY(poly.create(JOB_POLYPHASE, p.taps, 1, p.interp, p.decim, 2, pcap));
+        hasPoly = true;
+    }
     return B200_OK;
 }
 
@@ -711,7 +871,7 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
     }
     else if (kind == B200_DEMOD_WFM) {
         // demod.init(input, bandwidth / 2, 500 kS/s, stereo, lowPass, rds) (radio/src/demodulators/wfm.h:76)
-        if (p2 != 0.0) { setError("the RDS branch of the broadcast FM demodulator is not provided"); v.demod = nullptr; delete d; return B200_EINVAL; }
+        d->rdsOn = p2 != 0.0;
         d->invDeviation = (float)(1.0 / design::hzToRads(d->bw / 2.0, d->sr));
         d->wfmStereo = p0 != 0.0;
         d->filtering = p1 != 0.0;
@@ -769,6 +929,23 @@ static int demodConfigure(VfoBank& bank, Vfo& v, int kind, double p0, double p1,
         if (d->wfmStereo) { B200_TRY(d->firR.create(JOB_DECIM_FIR, firTaps, 1, 1, 1, 1, 64)); }
         d->hasFir = true;
     }
+    if (d->rdsOn) {
+        // xlator.init(NULL, -57000.0, samplerate); rdsResamp.init(NULL, samplerate, 5000.0) (broadcast_fm.h:52-53)
+        const double w = design::hzToRads(-57000.0, d->sr);
+        d->rdsDRe = (float)cos(w); d->rdsDIm = (float)sin(w);
+        d->rdsTheta = (bank.calSteps > 0) ? design::calibrateRotatorStep(d->rdsDRe, d->rdsDIm, std::min(bank.calSteps, 1 << 18))
+                                          : atan2((double)d->rdsDIm, (double)d->rdsDRe);
+        d->rdsAngle = 0.0;
+        float2 tab[kRotChunk];
+        makeRotatorTable(d->rdsDRe, d->rdsDIm, tab);
+        B200_CUDA(cudaMalloc((void**)&d->dRdsWtab, sizeof(tab)));
+        B200_CUDA(cudaMemcpy(d->dRdsWtab, tab, sizeof(tab), cudaMemcpyHostToDevice));
+        const float2 one = make_float2(1.0f, 0.0f);
+        B200_CUDA(cudaMalloc((void**)&d->dRdsPhase, sizeof(float2)));
+        B200_CUDA(cudaMemcpy(d->dRdsPhase, &one, sizeof(float2), cudaMemcpyHostToDevice));
+        const int cap0 = bank.maxOut((int)(&v - bank.vfos.data()), bank.maxBlock) + 8 + 64;
+        B200_TRY(buildResampler(d->sr, 5000.0, cap0, d->rdsDecim, d->rdsPoly, d->rdsHasPoly, d->rdsMode));
+    }
     B200_CUDA(cudaMalloc((void**)&d->dState, sizeof(SeqState)));
     B200_CUDA(cudaMemcpy(d->dState, &init, sizeof(SeqState), cudaMemcpyHostToDevice));
     return demodEnsureCap(*d, bank.maxOut((int)(&v - bank.vfos.data()), bank.maxBlock) + 8);
@@ -794,27 +971,7 @@ static int afConfigure(VfoBank& bank, Vfo& v, double audioSR, double tau) {
     d.afResamp = audioSR > 0.0;
     d.afOutSR = d.afResamp ? audioSR : d.sr;
     d.afMode = 3;
-    int cap = std::max(d.cap, 64);
-    if (d.afResamp) {
-        design::ResampPlan p = design::planResampler(d.sr, audioSR);
-        d.afMode = p.mode;
-        if (p.mode == 0 || p.mode == 1) {
-            const design::PlanDef* plan = design::findPlan(p.ratio);
-            if (!plan) { setError("no decimation plan for ratio %d", p.ratio); return B200_EINVAL; }
-            d.afDecim.resize(plan->nstages);
-            for (int i = 0; i < plan->nstages; i++) {
-                std::vector<float> t(plan->stages[i].ntaps);
-                memcpy(t.data(), plan->stages[i].taps, sizeof(float) * t.size());   // the table holds IEEE bit patterns
-                cap = cap / plan->stages[i].decim + 2;
-                B200_TRY(d.afDecim[i].create(JOB_DECIM_FIR, t, plan->stages[i].decim, 1, 1, 2, cap, true));
-            }
-        }
-        if (p.mode == 0 || p.mode == 2) {
-            const int pcap = (int)(((int64_t)cap * p.interp) / p.decim) + 4;
-            B200_TRY(d.afPoly.create(JOB_POLYPHASE, p.taps, 1, p.interp, p.decim, 2, pcap));
-            d.afHasPoly = true;
-        }
-    }
+    if (d.afResamp) { B200_TRY(buildResampler(d.sr, audioSR, std::max(d.cap, 64), d.afDecim, d.afPoly, d.afHasPoly, d.afMode)); }
     d.deOn = tau > 0.0;
     if (d.deOn) {
         const float dt = 1.0f / d.afOutSR;          // Deemphasis::updateAlpha (deephasis.h:82-85)
@@ -836,7 +993,13 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     std::vector<PllJob> pllJobs;
     std::vector<WfmMixJob> mixJobs;
     std::vector<LrJob> lrJobs;
-    int maxN = 0, maxMix = 0;
+    std::vector<FmifJob> fmJobs;
+    std::vector<VolJob> volJobs;
+    std::vector<RotJob> rdsRot;
+    std::vector<RdsXlateJob> rdsX;
+    std::vector<std::vector<FirJob>> rdsWaves;  // wave k = stage k of every VFO's RDS resampler
+    const bool exactRot = bank.rotatorMode == B200_ROTATOR_EXACT;
+    int maxN = 0, maxMix = 0, maxFm = 0, maxVol = 0, maxRds = 0;
     for (size_t vi = 0; vi < bank.vfos.size(); vi++) {
         Vfo& v = bank.vfos[vi];
         if (!v.live || !v.demod) { continue; }
@@ -859,6 +1022,19 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             ifJobs.push_back(f);
             demodIn = d.dIf;
         }
+        if (d.fmOn && n > 0) {
+            if (n > d.fmCap) {
+                B200_CUDA(cudaStreamSynchronize(s));
+                if (d.dFm) { cudaFree(d.dFm); d.dFm = nullptr; }
+                d.fmCap = std::max(n + 64, d.cap);
+                B200_CUDA(cudaMalloc((void**)&d.dFm, (size_t)d.fmCap * sizeof(cf32)));
+            }
+            fmJobs.push_back(FmifJob{ demodIn, d.dFm, d.dFmHist[d.fmCur], d.dFmHist[d.fmCur ^ 1], d.dFmTab, n, d.fmBins });
+            d.fmCur ^= 1;
+            demodIn = d.dFm;
+            maxFm = std::max(maxFm, n);
+        }
+        d.lastIf = demodIn;
         j.in = demodIn; j.mono = d.dMono; j.stereo = d.dStereo; j.st = d.dState; j.wtab = d.dWtab;
         j.exact = (bank.rotatorMode == B200_ROTATOR_EXACT) ? 1 : 0;
         j.maps = d.dMaps; j.amps = d.dAmps;
@@ -913,7 +1089,34 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
                 if (d.afHasPoly) { B200_TRY(pushStage(d.afPoly)); }
             }
             if (d.deOn && m > 0) { deJobs.push_back(DeemphJob{ (float2*)data, d.dState, d.deAlpha, m }); }
+            if (d.volOn && m > 0) { volJobs.push_back(VolJob{ (float*)data, d.volGain, 2 * m }); maxVol = std::max(maxVol, 2 * m); }
             d.lastAudio = (const float*)data; d.lastAudioCount = m;
+        }
+        if (d.rdsOn) {
+            // RDS branch: MPX -> complex, down by 57 kHz, RationalResampler<complex_t> to 5 kS/s (broadcast_fm.h:169-175,197-206)
+            const void* data = d.dRdsX; int m = n; size_t wave = 0;
+            if (n > 0) {
+                RotJob r{};
+                r.chk = d.dRdsChk; r.state = d.dRdsPhase; r.angle0 = d.rdsAngle; r.theta = d.rdsTheta;
+                r.dRe = d.rdsDRe; r.dIm = d.rdsDIm; r.count = n; r.exact = exactRot ? 1 : 0;
+                rdsRot.push_back(r);
+                rdsX.push_back(RdsXlateJob{ d.dMono, d.dRdsX, d.dRdsChk, d.dRdsWtab, n, 0 });
+                if (!exactRot) { d.rdsAngle = fmod(d.rdsAngle + d.rdsTheta * (double)n, 2.0 * design::kPi); }
+                maxRds = std::max(maxRds, n);
+            }
+            auto pushStage = [&](Stage& st) -> int {
+                const int outN = st.outCountFor(m);
+                if (outN > st.outCap) { B200_CUDA(cudaStreamSynchronize(s)); B200_TRY(st.ensureOutCap(outN + 64)); }
+                FirJob f; st.fillJob(f, data, m);
+                if (rdsWaves.size() <= wave) { rdsWaves.resize(wave + 1); }
+                rdsWaves[wave++].push_back(f);
+                st.advance(m);
+                data = st.dOut; m = f.nOut;
+                return B200_OK;
+            };
+            if (d.rdsMode == 0 || d.rdsMode == 1) { for (auto& st : d.rdsDecim) { B200_TRY(pushStage(st)); } }
+            if (d.rdsHasPoly) { B200_TRY(pushStage(d.rdsPoly)); }
+            d.lastRds = (const float*)data; d.lastRdsCount = m;
         }
         if (n > 0) {
             if (d.kind == B200_DEMOD_NFM || d.kind == B200_DEMOD_WFM) {
@@ -934,17 +1137,21 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
             maxN = std::max(maxN, n);
         }
     }
-    if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty() && wfmA.empty()) { return B200_OK; }
+    if (all.empty() && firs.empty() && ssb.empty() && afWaves.empty() && wfmA.empty() && rdsWaves.empty()) { return B200_OK; }
     for (auto& w : afWaves) { firJobsBalance(w.data(), (int)w.size()); }
+    for (auto& w : rdsWaves) { firJobsBalance(w.data(), (int)w.size()); }
     firJobsBalance(firs.data(), (int)firs.size());
     firJobsBalance(wfmA.data(), (int)wfmA.size());
     firJobsBalance(wfmB.data(), (int)wfmB.size());
     // one upload: [seq][quad][all][firs][ssb][af waves][deemph]
     size_t afJobs = 0;
     for (auto& w : afWaves) { afJobs += w.size(); }
+    for (auto& w : rdsWaves) { afJobs += w.size(); }
     const size_t bytes = (seq.size() + quad.size() + all.size() + ssb.size()) * sizeof(DemodJob) + (firs.size() + afJobs) * sizeof(FirJob) +
                          deJobs.size() * sizeof(DeemphJob) + ifJobs.size() * sizeof(IfJob) + (wfmA.size() + wfmB.size()) * sizeof(FirJob) +
-                         pllJobs.size() * sizeof(PllJob) + mixJobs.size() * sizeof(WfmMixJob) + lrJobs.size() * sizeof(LrJob) + 64 * (afWaves.size() + 16);
+                         pllJobs.size() * sizeof(PllJob) + mixJobs.size() * sizeof(WfmMixJob) + lrJobs.size() * sizeof(LrJob) +
+                         fmJobs.size() * sizeof(FmifJob) + volJobs.size() * sizeof(VolJob) + rdsRot.size() * sizeof(RotJob) + rdsX.size() * sizeof(RdsXlateJob) +
+                         64 * (afWaves.size() + rdsWaves.size() + 24);
     void* hp = nullptr; int slot = 0;
     B200_TRY(bank.ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -963,6 +1170,12 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
     const size_t oP = put(pllJobs.data(), pllJobs.size() * sizeof(PllJob));
     const size_t oM = put(mixJobs.data(), mixJobs.size() * sizeof(WfmMixJob));
     const size_t oL = put(lrJobs.data(), lrJobs.size() * sizeof(LrJob));
+    const size_t oFm = put(fmJobs.data(), fmJobs.size() * sizeof(FmifJob));
+    const size_t oV = put(volJobs.data(), volJobs.size() * sizeof(VolJob));
+    const size_t oRr = put(rdsRot.data(), rdsRot.size() * sizeof(RotJob));
+    const size_t oRx = put(rdsX.data(), rdsX.size() * sizeof(RdsXlateJob));
+    std::vector<size_t> oRw(rdsWaves.size());
+    for (size_t w = 0; w < rdsWaves.size(); w++) { oRw[w] = put(rdsWaves[w].data(), rdsWaves[w].size() * sizeof(FirJob)); }
     if (off > bank.dDemodDescBytes) {
         B200_CUDA(cudaStreamSynchronize(s));
         if (bank.dDemodDesc) { cudaFree(bank.dDemodDesc); }
@@ -975,9 +1188,24 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         ifChainKernel<<<(unsigned)ifJobs.size(), 256, 0, s>>>((const IfJob*)(dd + oI));
         B200_CHECK_LAUNCH(); countLaunch();
     }
+    if (!fmJobs.empty()) {
+        fmifKernel<<<dim3((maxFm + kFmTile - 1) / kFmTile, (unsigned)fmJobs.size()), kFmThreads, 0, s>>>((const FmifJob*)(dd + oFm));
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
     if (!quad.empty()) {
         quadratureKernel<<<dim3((maxN + 255) / 256, (unsigned)quad.size()), 256, 0, s>>>((const DemodJob*)(dd + oQ));
         B200_CHECK_LAUNCH(); countLaunch();
+    }
+    if (!rdsX.empty()) {
+        B200_TRY(launchCheckpoints((const RotJob*)(dd + oRr), (int)rdsRot.size(), exactRot ? (int)rdsRot.size() : 0, maxRds, s));
+        rdsXlateKernel<<<dim3((maxRds + 255) / 256, (unsigned)rdsX.size()), 256, 0, s>>>((const RdsXlateJob*)(dd + oRx));
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
+    for (size_t w = 0; w < rdsWaves.size(); w++) {
+        int maxH = 0;
+        for (auto& f : rdsWaves[w]) { maxH = std::max(maxH, f.H); }
+        B200_TRY(launchFirJobs((const FirJob*)(dd + oRw[w]), rdsWaves[w].data(), (int)rdsWaves[w].size(), 2, s));
+        B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oRw[w]), (int)rdsWaves[w].size(), maxH, s));
     }
     if (!wfmA.empty()) {
         // broadcast FM stereo: pilot band-pass -> PLL -> mix-down + matrix -> audio low-passes -> interleave
@@ -1038,6 +1266,10 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         deemphKernel<<<(unsigned)deJobs.size(), 64, 0, s>>>((const DeemphJob*)(dd + oD));
         B200_CHECK_LAUNCH(); countLaunch();
     }
+    if (!volJobs.empty()) {
+        volumeKernel<<<dim3((maxVol + 255) / 256, (unsigned)volJobs.size()), 256, 0, s>>>((const VolJob*)(dd + oV));
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
     B200_TRY(bank.ring.release(slot, s));   // after the last reader of the slot was enqueued
     return B200_OK;
 }
@@ -1081,6 +1313,76 @@ int b200_vfo_set_if_chain(b200_vfo_bank* bank, int vfo, int nb_enabled, double n
         B200_CUDA(cudaMemcpy(&d.dState->nbAmp, &one, sizeof(float), cudaMemcpyHostToDevice));
     }
     return B200_OK;
+}
+
+int b200_vfo_set_if_nr(b200_vfo_bank* bank, int vfo, int enabled, int bins) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { setError("the IF chain sits in front of a demodulator: attach one to the VFO first"); return B200_EINVAL; }
+    if (enabled && (bins < 2 || bins > kFmMaxBins)) { setError("IF noise reduction takes 2..%d bins, got %d", kFmMaxBins, bins); return B200_EINVAL; }
+    DeviceGuard g(bank->impl.device);
+    B200_TRY(bank->impl.syncLast());
+    DemodState& d = *v.demod;
+    if (!enabled) { d.fmOn = false; return B200_OK; }
+    const bool fresh = !d.fmOn || d.fmBins != bins;
+    if (!d.dFmTab) {
+        B200_CUDA(cudaMalloc((void**)&d.dFmTab, (size_t)(kFmMaxBins * kFmMaxBins + kFmMaxBins) * sizeof(float2)));
+        for (int i = 0; i < 2; i++) { B200_CUDA(cudaMalloc((void**)&d.dFmHist[i], kFmMaxBins * sizeof(cf32))); }
+    }
+    if (fresh) {
+        // FMIF::initBuffers (fm_if.h:106-124): Nuttall window over bins-1, cleared delay line
+        std::vector<float2> tab((size_t)kFmMaxBins * kFmMaxBins + kFmMaxBins, make_float2(0.f, 0.f));
+        for (int n = 0; n < bins; n++) {
+            const float w = (float)design::nuttall(n, bins - 1);
+            for (int k = 0; k < bins; k++) {
+                const double a = -2.0 * design::kPi * (double)((k * n) % bins) / (double)bins;
+                tab[(size_t)n * kFmMaxBins + k] = make_float2((float)((double)w * cos(a)), (float)((double)w * sin(a)));
+            }
+        }
+        for (int k = 0; k < bins; k++) {
+            const double a = 2.0 * design::kPi * (double)((k * (bins / 2)) % bins) / (double)bins;
+            tab[(size_t)kFmMaxBins * kFmMaxBins + k] = make_float2((float)cos(a), (float)sin(a));
+        }
+        B200_CUDA(cudaMemcpy(d.dFmTab, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice));
+        for (int i = 0; i < 2; i++) { B200_CUDA(cudaMemset(d.dFmHist[i], 0, kFmMaxBins * sizeof(cf32))); }
+        d.fmCur = 0;
+    }
+    d.fmOn = true; d.fmBins = bins;
+    return B200_OK;
+}
+
+int b200_vfo_set_volume(b200_vfo_bank* bank, int vfo, double volume, int muted) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { setError("the volume block follows a demodulator: attach one to the VFO first"); return B200_EINVAL; }
+    B200_TRY(bank->impl.syncLast());
+    v.demod->volOn = true;
+    v.demod->volGain = muted ? 0.0f : powf((float)volume, 2.0f);   // Volume::init / setVolume (audio/volume.h:13-16,22-26)
+    return B200_OK;
+}
+
+const float* b200_vfo_if_ptr(b200_vfo_bank* bank, int vfo) {
+    if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    const Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod) { return nullptr; }
+    return (const float*)v.demod->lastIf;
+}
+
+const float* b200_vfo_rds_ptr(b200_vfo_bank* bank, int vfo) {
+    if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    const Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod || !v.demod->rdsOn) { return nullptr; }
+    return v.demod->lastRds;
+}
+
+int b200_vfo_rds_count(b200_vfo_bank* bank, int vfo) {
+    if (!bank) { setError("NULL bank handle"); return B200_EINVAL; }
+    B200_TRY(bank->impl.check(vfo));
+    const Vfo& v = bank->impl.vfos[vfo];
+    if (!v.demod || !v.demod->rdsOn) { setError("VFO %d has no RDS branch (broadcast FM demodulator with p2 != 0)", vfo); return B200_EINVAL; }
+    return v.demod->lastRdsCount;
 }
 
 const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo) {

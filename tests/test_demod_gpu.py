@@ -302,12 +302,130 @@ def test_wfm_broadcast_fm_matches_oracle(stereo, low_pass):
         assert amp(1, 2500.0) > 4 * amp(1, 1000.0)
 
 
-def test_wfm_rds_branch_is_refused():
+@pytest.mark.parametrize("stereo,mode", [(0, "exact"), (1, "exact"), (1, "fast")])
+def test_wfm_rds_branch_matches_oracle(stereo, mode):
+    """BroadcastFM with rdsOut: the 5 kS/s RDS baseband (MPX -> complex -> -57 kHz -> RationalResampler) next to the audio,
+    ragged and empty blocks, counts exact.  exact: the -57 kHz rotator replays the reference's fp32 recursion, -80 dB.
+    fast: closed-form rotator from the calibrated step; the reference's own phase is only defined up to its fp32 drift, so
+    each block is compared after removing one best-fit constant phase (which must stay a pure rotation)."""
     from sdrplusplusbrown_b200 import binding
-    b = binding.VfoBank(4e6, max_block=65536)
-    v = b.add(500e3, 150e3, 0.0)
+    in_sr, out_sr, bw, off = 4e6, 500e3, 150e3, 600e3
+    n = 8 * 70000
+    t = np.arange(n) / in_sr
+    rng = np.random.default_rng(5)
+    bits = rng.integers(0, 2, n // 3368 + 2) * 2.0 - 1.0                  # 1187.5 baud BPSK-ish subcarrier at 57 kHz
+    sym = bits[(np.arange(n) // 3368)]
+    mpx = 0.4 * np.sin(2 * np.pi * 1000.0 * t) + 0.1 * np.sin(2 * np.pi * 19000.0 * t) + 0.06 * sym * np.cos(2 * np.pi * 57000.0 * t)
+    ph = 2 * np.pi * 75e3 * np.cumsum(mpx) / in_sr + 2 * np.pi * off * t
+    x = (0.5 * np.exp(1j * ph) + 0.002 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_dem = ol.WfmRds(PORT, bw / 2.0, out_sr, stereo, 1)
+    b = binding.VfoBank(in_sr, max_block=300000)
+    if mode == "exact":
+        b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, binding.DEMOD_WFM, stereo, 1, 1, 0)
+    pos, got_all, ref_all = 0, [], []
+    for sz in [8 * 17000, 0, 8 * 20000 + 3, 5, 8 * 9000, 41, 8 * 23000]:
+        blk = x[pos:pos + sz]
+        pos += sz
+        if mode == "fast" and len(blk):
+            b.set_phase(v, o_vfo.phase())              # the VFO's own rotator follows the oracle's, as in the other fast-mode tests
+        iq = o_vfo.process(blk) if len(blk) else np.zeros(0, np.complex64)
+        ref_a, ref_r = o_dem.process(iq) if len(iq) else (np.zeros((0, 2), np.float32), np.zeros(0, np.complex64))
+        b.process(to_dev(blk) if len(blk) else to_dev(np.zeros(1, np.complex64)), count=len(blk))
+        assert b.out_count(v) == len(iq)
+        assert b.rds_count(v) == len(ref_r), (sz, b.rds_count(v), len(ref_r))
+        if len(ref_r) and mode == "exact":
+            got_all.append(b.rds(v)); ref_all.append(ref_r)
+            assert err_db(b.audio(v)[:, 0], ref_a[:, 0]) <= -80.0
+        elif len(ref_r) > 100:
+            got = b.rds(v)
+            c = np.vdot(ref_r, got) / np.vdot(ref_r, ref_r)
+            assert abs(abs(c) - 1.0) < 1e-3, c
+            assert err_db(got, c * ref_r) <= -60.0, err_db(got, c * ref_r)
+    if mode == "exact":
+        got, ref = np.concatenate(got_all), np.concatenate(ref_all)
+        assert err_db(got, ref) <= -80.0, err_db(got, ref)
+        # and it carries the 57 kHz subcarrier's data at baseband: its energy sits within +-2.4 kHz
+        spec = np.abs(np.fft.fft(got[len(got) // 2:])) ** 2
+        f = np.fft.fftfreq(len(spec), 1 / 5000.0)
+        assert spec[np.abs(f) < 2400].sum() > 0.95 * spec.sum()
+
+
+@pytest.mark.parametrize("bins", [9, 15, 31, 32])
+def test_if_noise_reduction_fmif_matches_oracle(bins):
+    """VFO -> [NoiseBlanker] -> FMIF -> NFM demodulator.  The block keeps one DFT bin per sample, the strongest: where
+    the two strongest bins of a window differ by less than 1e-5 relative the choice is decided by rounding (in the
+    reference by FFTW's own), so those samples are left out of the comparison; everywhere else -80 dB."""
+    from sdrplusplusbrown_b200 import binding
+    out_sr, o_dem, (kind, p0, p1, p2, p3), bw = _demod_pair("demod_nfm")
+    in_sr, off = out_sr * 32, 21e3
+    n = 32 * 9000
+    t = np.arange(n) / in_sr
+    fm = np.exp(2j * np.pi * (off * t + 3.0 * np.sin(2 * np.pi * 700.0 * t)))
+    rng = np.random.default_rng(bins)
+    x = (0.3 * fm + 0.02 * (rng.standard_normal(n) + 1j * rng.standard_normal(n))).astype(np.complex64)
+    x[100000:101000] = 0
+    nb = bins == 15
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_if = ol.IfChain(PORT, nb, 500.0 / out_sr, 3.0, False, 0.0)
+    o_nr = ol.FmIf(PORT, bins)
+    b = binding.VfoBank(in_sr, max_block=200000)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, kind, p0, p1, p2, p3)
+    b.set_if_chain(v, nb, 500.0 / out_sr, 3.0, False, 0.0)
+    b.set_if_nr(v, True, bins)
+    hist, seen = None, 0
+    for sz in [96000, 0, 7, 96000, 32 * 20 + 5, 90000]:
+        blk = x[seen:seen + sz]
+        seen += sz
+        iq = o_vfo.process(blk) if len(blk) else np.zeros(0, np.complex64)
+        pre = o_if.process(iq) if len(iq) else iq
+        ref_if = o_nr.process(pre) if len(pre) else pre
+        ref = o_dem.process(ref_if) if len(ref_if) else np.zeros((0, 2), np.float32)
+        b.process(to_dev(blk) if len(blk) else to_dev(np.zeros(1, np.complex64)), count=len(blk))
+        assert b.out_count(v) == len(iq)
+        if not len(iq):
+            continue
+        _, margin, hist = ol.fmif_model(pre, bins, hist)
+        ok = margin > 1e-5
+        assert ok.sum() >= 0.95 * len(ok) - 40
+        got_if = b.if_output(v)
+        assert err_db(got_if[ok], ref_if[ok]) <= -80.0, (bins, sz, err_db(got_if[ok], ref_if[ok]))
+        if ok.all() and len(iq) > 1000:
+            assert err_db(b.audio(v)[:, 0], ref[:, 0]) <= -80.0
     with pytest.raises(binding.B200Error):
-        b.set_demod(v, binding.DEMOD_WFM, 1, 1, 1, 0)
+        b.set_if_nr(v, True, 33)
+    b.set_if_nr(v, False, 0)
+    b.process(to_dev(x[:32000]))
+    assert np.array_equal(b.if_output(v), b.output(v))
+
+
+def test_volume_block_behind_the_af_chain():
+    """audio::Volume: volume^2 on the resampled audio, zero when muted, in the reference's arithmetic"""
+    from sdrplusplusbrown_b200 import binding
+    out_sr, o_dem, args, bw = _demod_pair("demod_nfm")
+    in_sr, off = out_sr * 32, 13e3
+    x = synth.make_iq(8, 32 * 6000, in_sr, sigma=0.02, tones=[(off + 600.0, 0.3)])
+    o_vfo = ol.Vfo(PORT, in_sr, out_sr, bw, off)
+    o_af = ol.AfPost(PORT, out_sr, 48e3, 50e-6)
+    b = binding.VfoBank(in_sr, max_block=200000)
+    b.set_rotator_mode(binding.ROTATOR_EXACT)
+    v = b.add(out_sr, bw, off)
+    b.set_demod(v, *args)
+    b.set_audio_post(v, 48e3, 50e-6)
+    for blk, (vol, muted) in zip(split(x, [64000, 64000, 64000]), [(0.5, False), (0.83, False), (0.7, True)]):
+        b.set_volume(v, vol, muted)
+        ref = ol.volume(PORT, vol, muted, o_af.process(o_dem.process(o_vfo.process(blk))))
+        b.process(to_dev(blk))
+        got = b.audio(v)
+        assert got.shape == ref.shape
+        if muted:
+            assert not np.any(got)
+        else:
+            assert err_db(got[:, 0], ref[:, 0]) <= -80.0
 
 
 @pytest.mark.parametrize("kind", ["nfm", "usb", "am", "wfm_stereo"])

@@ -247,29 +247,6 @@ def test_radio_chain_blocks_port_equals_ref_bitwise():
             assert p.process(iq[i:i + 17000]).tobytes() == r.process(iq[i:i + 17000]).tobytes(), (stereo, lp)
 
 
-def fmif_model(x, bins, hist=None):
-    """float64 numpy model of noise_reduction::FMIF (fm_if.h:45-80): returns (out, relative margin between the two
-    strongest bins of every window).  The window is Nuttall over bins-1 (fm_if.h:118); the backward DFT of a single
-    bin evaluated at element bins/2 is X[idx] * exp(+2 pi i idx (bins//2) / bins)."""
-    n = np.arange(bins)
-    c = [0.355768, 0.487396, 0.144232, 0.012604]
-    win = sum(((-1) ** k) * c[k] * np.cos(2 * np.pi * k * n / (bins - 1)) for k in range(4))
-    hist = np.zeros(bins - 1, np.complex128) if hist is None else hist
-    buf = np.concatenate([hist, x.astype(np.complex128)])
-    seg = np.lib.stride_tricks.sliding_window_view(buf, bins)[:len(x)]
-    # fp32 window product as the reference forms it, then the transform in float64
-    segw = (seg.real.astype(np.float32) * win.astype(np.float32)).astype(np.float64) + \
-        1j * (seg.imag.astype(np.float32) * win.astype(np.float32)).astype(np.float64)
-    F = np.exp(-2j * np.pi * np.outer(n, n) / bins)
-    X = segw @ F
-    mag = np.abs(X)
-    idx = np.argmax(mag, axis=1)
-    top2 = np.sort(mag, axis=1)[:, -2:]
-    margin = (top2[:, 1] - top2[:, 0]) / np.maximum(top2[:, 1], 1e-30)
-    out = X[np.arange(len(x)), idx] * np.exp(2j * np.pi * idx * (bins // 2) / bins)
-    return out, margin, buf[len(x):]
-
-
 @pytest.mark.parametrize("bins", [9, 15, 31, 32])
 def test_fmif_port_against_numpy_model_and_ref(bins):
     """FM IF noise reduction at the radio module's four presets (radio/src/main.cpp:11-16): the restatement against a
@@ -287,7 +264,7 @@ def test_fmif_port_against_numpy_model_and_ref(bins):
     for i in range(0, n, 1700):
         blk = x[i:i + 1700]
         y = p.process(blk)
-        model, margin, hist = fmif_model(blk, bins, hist)
+        model, margin, hist = ol.fmif_model(blk, bins, hist)
         ok = margin > 1e-5
         assert ok.sum() > 0.98 * len(blk) - 100
         e = y[ok] - model[ok]
