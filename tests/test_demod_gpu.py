@@ -399,6 +399,7 @@ def test_if_noise_reduction_fmif_matches_oracle(bins):
     with pytest.raises(binding.B200Error):
         b.set_if_nr(v, True, 33)
     b.set_if_nr(v, False, 0)
+    b.set_if_chain(v, False, 0.0, 0.0, False, 0.0)
     b.process(to_dev(x[:32000]))
     assert np.array_equal(b.if_output(v), b.output(v))
 
