@@ -208,7 +208,10 @@ def _config(args, batch, n_gpus):
         "sample_rate": cfg["sample_rate"], "fft_size": cfg["fft_size"], "fft_rate": cfg["fft_rate"], "window": "blackman",
         "vfos_per_gpu": 1, "vfo": "USB out 24 kS/s bw 2.8 kHz", "demod": bool(getattr(args, "demod", False)),
         "batch_samples_per_step": batch, "l2_policy": ("batch (%.0f MB) larger than L2 (126 MB)" % (batch * 8 / 1e6)) if args.impl == "b200" else "n/a (CPU arm)",
-        "rotator": "fast (closed form, calibrated step)", "parallelism": "vfo-shard x%d + stream broadcast, fft frames time-sharded" % n_gpus if n_gpus > 1 else "single GPU",
+        "rotator": "fast (closed form, calibrated step)",
+        "stage_overlap": ("B200_OPT_DEFER_TAIL: the VFO's later stages of step k run on their own stream beside the full-rate stage of step k+1; "
+                          "all K steps' outputs are complete when the timed region ends (device-wide synchronize)") if (args.impl == "b200" and args.defer_tail) else "none",
+        "parallelism": "vfo-shard x%d + stream broadcast, fft frames time-sharded" % n_gpus if n_gpus > 1 else "single GPU",
     }
 
 
@@ -239,6 +242,7 @@ def run_gpu(args):
     v = fe.vfos.add(out_sr, bw, off + 50e3 * rank)
     if args.demod:
         fe.vfos.set_demod(v, binding.DEMOD_USB, 0, 50.0 / out_sr, 5.0 / out_sr, 0)
+    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if args.defer_tail else 0)
     wf = binding.Waterfall(cfg["fft_size"], DATA_WIDTH, device=local)
     wf.set_view(0, cfg["fft_size"])
     wf.set_range(WF_MIN, WF_MAX)
@@ -303,6 +307,7 @@ def run_gpu(args):
     barrier()
     e0.record(compute)
     run(args.steps)
+    fe.vfos.out_ptr(v)            # orders the last steps' deferred stages into the compute stream: e1 fires behind ALL work of the K steps
     e1.record(compute)
     barrier()
     ms = e0.elapsed_time(e1)
@@ -329,6 +334,7 @@ def run_gpu(args):
         d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         d0.record(compute)
         run(max(3, args.steps // 2))
+        fe.vfos.out_ptr(v)
         d1.record(compute)
         barrier()
         td = torch.tensor([d0.elapsed_time(d1)], dtype=torch.float64, device=dev)
@@ -472,6 +478,8 @@ def main():
     ap.add_argument("--cpu-samples", type=int, default=1 << 24, help="samples per CPU-arm step (bounded sample of the workload)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--no-defer-tail", dest="defer_tail", action="store_false",
+                    help="run the VFO's later stages inline in the caller's stream (library default) instead of the streaming mode")
     ap.add_argument("--demod", action="store_true", help="include the SSB demodulator + AGC in the timed step")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries below us write there too (NCCL prints its version banner on

@@ -108,10 +108,25 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * FAST-mode calibration run, default 1048576; 0 = use atan2 of the fp32 step), B200_OPT_TILE_SAMPLES (process-wide
  * choice of the first-stage kernel for a launch that holds ONE VFO: 0 or 2048 = the single-VFO kernel with
  * 2048-sample tiles (default), 4096 = the grouped kernel with 4096-sample tiles, which launches of two or more
- * VFOs always use; results do not depend on it). */
+ * VFOs always use; results do not depend on it).
+ * Scheduling switches (process-wide; results do not depend on them, tools/order_sweep.py measures them):
+ * B200_OPT_DEFER_TAIL (default 0).  1 = streaming mode: the stages behind the full-rate first stage of every VFO, and the
+ *   demodulators, of block k run on an internal stream beside the full-rate stage of block k+1 (the first stage's output
+ *   is double-buffered; at most two blocks are in flight).  b200_vfo_bank_process / b200_frontend_process then return
+ *   with that work still running and NOT ordered into `stream`; it is ordered into `stream` by the next call of
+ *   b200_vfo_out_ptr / b200_vfo_audio_ptr / b200_vfo_if_ptr / b200_vfo_rds_ptr (call them after every process call whose
+ *   results are wanted -- the pointers may alternate between calls), by the *_process_host entry points, by any setter,
+ *   and by a device-wide synchronisation.  Used when every live VFO has a power-of-two decimator in front (the fused
+ *   first stage); otherwise the call runs inline as with 0.
+ * B200_OPT_BRANCH_ORDER (default 0): 0 = a front end enqueues its FFT branch before the channelizer, 1 = right behind
+ *   the channelizer's full-rate kernel.  B200_OPT_FFT_CTAS_PER_SM (default 0 = as many as fit): persistent CTAs per SM
+ *   of the two-pass FFT kernels. */
 #define B200_OPT_FUSED_STAGE1 1
 #define B200_OPT_CALIBRATION_STEPS 2
 #define B200_OPT_TILE_SAMPLES 3
+#define B200_OPT_FFT_CTAS_PER_SM 4
+#define B200_OPT_BRANCH_ORDER 5
+#define B200_OPT_DEFER_TAIL 6
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)

@@ -3,6 +3,7 @@
 #include <cstring>
 
 #include "vfo_bank.cuh"
+#include "fft.cuh"
 #include "xlate_decim.cuh"
 
 using namespace b200;
@@ -135,6 +136,21 @@ int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
         fusedTileSamples = value;
         return B200_OK;
     }
+    if (option == B200_OPT_FFT_CTAS_PER_SM) {
+        if (value < 0 || value > 4) { setError("FFT CTAs per SM must be 0 (automatic) .. 4"); return B200_EINVAL; }
+        fftCtasPerSm = value;
+        return B200_OK;
+    }
+    if (option == B200_OPT_DEFER_TAIL) {
+        B200_TRY(bank->impl.syncLast());
+        deferTail = value != 0;
+        return B200_OK;
+    }
+    if (option == B200_OPT_BRANCH_ORDER) {
+        if (value != 0 && value != 1) { setError("branch order must be 0 or 1"); return B200_EINVAL; }
+        branchOrder = value;
+        return B200_OK;
+    }
     setError("unknown option %d", option);
     return B200_EINVAL;
 }
@@ -183,6 +199,7 @@ int b200_vfo_out_count(b200_vfo_bank* bank, int vfo) {
 
 const float* b200_vfo_out_ptr(b200_vfo_bank* bank, int vfo) {
     if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    if (bank->impl.tailUnjoined) { DeviceGuard g(bank->impl.device); if (bank->impl.joinTail() != B200_OK) { return nullptr; } }
     return (const float*)bank->impl.vfos[vfo].lastOutPtr;
 }
 
@@ -207,6 +224,7 @@ int b200_vfo_bank_process_host(b200_vfo_bank* bank, const float* h_in, int count
     // include/dsp/stream.h are pinned, so the drop-in path copies at full PCIe rate)
     B200_CUDA(cudaMemcpyAsync(b.dStageIn, h_in, (size_t)count * sizeof(cf32), cudaMemcpyHostToDevice, s));
     B200_TRY(b.process(b.dStageIn, count, s));
+    B200_TRY(b.joinTail());
     for (size_t i = 0; i < b.vfos.size(); i++) {
         const Vfo& v = b.vfos[i];
         if (!v.live) { continue; }

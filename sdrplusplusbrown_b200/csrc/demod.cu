@@ -1365,6 +1365,7 @@ int b200_vfo_set_volume(b200_vfo_bank* bank, int vfo, double volume, int muted) 
 
 const float* b200_vfo_if_ptr(b200_vfo_bank* bank, int vfo) {
     if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    if (bank->impl.tailUnjoined) { DeviceGuard g(bank->impl.device); if (bank->impl.joinTail() != B200_OK) { return nullptr; } }
     const Vfo& v = bank->impl.vfos[vfo];
     if (!v.demod) { return nullptr; }
     return (const float*)v.demod->lastIf;
@@ -1372,6 +1373,7 @@ const float* b200_vfo_if_ptr(b200_vfo_bank* bank, int vfo) {
 
 const float* b200_vfo_rds_ptr(b200_vfo_bank* bank, int vfo) {
     if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    if (bank->impl.tailUnjoined) { DeviceGuard g(bank->impl.device); if (bank->impl.joinTail() != B200_OK) { return nullptr; } }
     const Vfo& v = bank->impl.vfos[vfo];
     if (!v.demod || !v.demod->rdsOn) { return nullptr; }
     return v.demod->lastRds;
@@ -1387,6 +1389,7 @@ int b200_vfo_rds_count(b200_vfo_bank* bank, int vfo) {
 
 const float* b200_vfo_audio_ptr(b200_vfo_bank* bank, int vfo) {
     if (!bank || bank->impl.check(vfo) != B200_OK) { return nullptr; }
+    if (bank->impl.tailUnjoined) { DeviceGuard g(bank->impl.device); if (bank->impl.joinTail() != B200_OK) { return nullptr; } }
     const Vfo& v = bank->impl.vfos[vfo];
     if (!v.demod) { return nullptr; }
     return v.demod->lastAudio ? v.demod->lastAudio : v.demod->dStereo;

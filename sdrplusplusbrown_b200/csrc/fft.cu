@@ -17,6 +17,8 @@
 
 namespace b200 {
 
+int fftCtasPerSm = 0;       // B200_OPT_FFT_CTAS_PER_SM: persistent CTAs per SM of the two register-resident passes; 0 = as many as fit
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -497,7 +499,7 @@ int launchCols(int nf, int N2, cudaStream_t s, const FrameDesc* frames, const fl
     B200_CUDA(cudaFuncSetAttribute(fftColsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // persistent grid: a whole number of column-block sets, about three CTAs per SM
     const int blocksPerFrame = N2 >> 4;
-    const int ctasPerSm = 512 / (16 * TwoStage<RA, RB>::TPC);
+    const int ctasPerSm = fftCtasPerSm > 0 ? fftCtasPerSm : 512 / (16 * TwoStage<RA, RB>::TPC);
     int sets = std::max(1, (148 * ctasPerSm) / blocksPerFrame);
     sets = std::min(sets, nf);
     fftColsKernel<RA, RB><<<sets * blocksPerFrame, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(frames, nf, win, nz, logN2, twN1, twLo, twHi, logS,
@@ -511,7 +513,7 @@ int launchRows(int nf, int N1, cudaStream_t s, int logN1, const float2* twN2, co
     const size_t smem = (size_t)2 * BUF * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fftRowsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int nTiles = nf * (N1 >> 4);
-    const int ctasPerSm = 512 / (16 * TwoStage<RA, RB>::TPC);
+    const int ctasPerSm = fftCtasPerSm > 0 ? fftCtasPerSm : 512 / (16 * TwoStage<RA, RB>::TPC);
     const int grid = std::min(nTiles, 148 * ctasPerSm);
     fftRowsKernel<RA, RB><<<grid, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(logN1, nTiles, twN2, scratch, frameBase, outDb, outSpec);
     return B200_OK;

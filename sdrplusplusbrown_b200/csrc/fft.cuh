@@ -6,6 +6,9 @@
 
 namespace b200 {
 
+extern int fftCtasPerSm;
+extern int branchOrder;    // frontend.cu
+
 // One frame of the Reshaper (keep nz samples every I): the samples may straddle the carry buffer
 // and the current block, so a frame is [src0[0..len0) | src1[0..nz-len0)].
 struct FrameDesc {

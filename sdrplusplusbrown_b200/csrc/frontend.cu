@@ -13,6 +13,8 @@
 
 namespace b200 {
 
+int branchOrder = 0;        // B200_OPT_BRANCH_ORDER
+
 namespace {
 
 // ------------------------------------------------------------------ DC blocker (correction/dc_blocker.h:54-60)
@@ -232,7 +234,7 @@ struct FrontEnd {
 
     int init();
     void destroy();
-    int syncLast() { if (everRan) { B200_CUDA(cudaStreamSynchronize(lastStream)); } return B200_OK; }
+    int syncLast() { if (everRan) { B200_CUDA(cudaStreamSynchronize(lastStream)); } if (bank) { B200_TRY(bank->impl.syncLast()); } return B200_OK; }
     int rebuildDecim();
     int updateFftPath();
     int preprocess(const cf32* dIn, int count, cudaStream_t s);
@@ -454,7 +456,7 @@ int FrontEnd::fftBranch(cudaStream_t s, bool append) {
 int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s, bool append) {
     if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
     DeviceGuard g(device);
-    if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
+    if (everRan && s != lastStream) { B200_TRY(syncLast()); }
     lastStream = s; everRan = true;
     B200_TRY(preprocess(dIn, count, s));
     const bool fork = bank->impl.liveCount() > 0;
@@ -464,10 +466,23 @@ int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s, bool append) {
         // channelizer's full-rate kernel (VfoBank::evStage1) lets that HBM-bound kernel run alone at 0.94 of the copy peak
         // instead of 0.78, but the step gets 4 % slower (0.266 against 0.256 ms): the FFT passes then collide with the
         // latency-bound tail stages instead.
-        B200_CUDA(cudaStreamWaitEvent(fftStream, evFork, 0));
-        B200_TRY(fftBranch(fftStream, append));
-        B200_CUDA(cudaEventRecord(evJoin, fftStream));
-        B200_TRY(bank->impl.process(preOut, preCount, s));
+        if (branchOrder == 0) {
+            B200_CUDA(cudaStreamWaitEvent(fftStream, evFork, 0));
+            B200_TRY(fftBranch(fftStream, append));
+            B200_CUDA(cudaEventRecord(evJoin, fftStream));
+            B200_TRY(bank->impl.process(preOut, preCount, s));
+        }
+        else {
+            // B200_OPT_BRANCH_ORDER 1: the FFT branch is enqueued right behind the channelizer's full-rate kernel, without
+            // waiting for it, so its CTAs take over the SMs as that kernel drains and run beside the latency-bound tail
+            const std::function<int()> hook = [&]() -> int {
+                B200_CUDA(cudaStreamWaitEvent(fftStream, evFork, 0));
+                B200_TRY(fftBranch(fftStream, append));
+                B200_CUDA(cudaEventRecord(evJoin, fftStream));
+                return B200_OK;
+            };
+            B200_TRY(bank->impl.process(preOut, preCount, s, &hook));
+        }
         B200_CUDA(cudaStreamWaitEvent(s, evJoin, 0));
     }
     else {
@@ -631,6 +646,7 @@ static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& frames
     }
     framesDone = std::max(framesDone, total);
     VfoBank& b = f.bank->impl;
+    B200_TRY(b.joinTail());
     for (size_t i = 0; i < b.vfos.size(); i++) {
         const Vfo& v = b.vfos[i];
         if (!v.live) { continue; }

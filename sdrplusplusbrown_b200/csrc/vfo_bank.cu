@@ -14,6 +14,8 @@
 
 namespace b200 {
 
+bool deferTail = false;     // B200_OPT_DEFER_TAIL
+
 // ------------------------------------------------------------------ Stage
 int Stage::create(int kind_, const std::vector<float>& taps, int D_, int L_, int M_, int elemFloats_, int outCap_, bool planTaps_) {
     destroy();
@@ -45,14 +47,22 @@ void Stage::destroy() {
     if (dTaps) { cudaFree(dTaps); dTaps = nullptr; }
     for (int i = 0; i < 2; i++) { if (dHist[i]) { cudaFree(dHist[i]); dHist[i] = nullptr; } }
     if (dOut) { cudaFree(dOut); dOut = nullptr; }
+    if (dOutAlt) { cudaFree(dOutAlt); dOutAlt = nullptr; }
     outCap = 0; T = 0; H = 0;
 }
 
 int Stage::ensureOutCap(int cap) {
     if (cap <= outCap && dOut) { return B200_OK; }
     if (dOut) { cudaFree(dOut); dOut = nullptr; }
+    if (dOutAlt) { cudaFree(dOutAlt); dOutAlt = nullptr; }
     outCap = std::max(cap, 16);
     B200_CUDA(cudaMalloc(&dOut, (size_t)outCap * elemFloats * sizeof(float)));
+    return B200_OK;
+}
+
+int Stage::flipOut() {
+    if (!dOutAlt) { B200_CUDA(cudaMalloc(&dOutAlt, (size_t)outCap * elemFloats * sizeof(float))); }
+    std::swap(dOut, dOutAlt);
     return B200_OK;
 }
 
@@ -122,6 +132,9 @@ int VfoBank::init(double inSR_, int maxBlock_, int device_) {
 void VfoBank::destroy() {
     DeviceGuard g(device);
     if (everRan) { cudaStreamSynchronize(lastStream); }
+    if (tailStream) { cudaStreamSynchronize(tailStream); cudaStreamDestroy(tailStream); tailStream = nullptr; }
+    for (int i = 0; i < 2; i++) { if (evTail[i]) { cudaEventDestroy(evTail[i]); evTail[i] = nullptr; } }
+    if (dTailDesc) { cudaFree(dTailDesc); dTailDesc = nullptr; }
     if (evStage1) { cudaEventDestroy(evStage1); evStage1 = nullptr; }
     for (auto& v : vfos) {
         if (!v.live) { continue; }
@@ -153,6 +166,16 @@ int VfoBank::liveCount() const {
 
 int VfoBank::syncLast() {
     if (everRan) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
+    if (tailStream) { B200_CUDA(cudaStreamSynchronize(tailStream)); }
+    tailUnjoined = false; tailPending[0] = tailPending[1] = false;
+    return B200_OK;
+}
+
+int VfoBank::joinTail() {
+    if (tailUnjoined) {
+        B200_CUDA(cudaStreamWaitEvent(lastStream, evTail[lastTailPar], 0));
+        tailUnjoined = false;
+    }
     return B200_OK;
 }
 
@@ -353,13 +376,42 @@ int VfoBank::setRotatorMode(int mode) {
 }
 
 // RxVFO::process for every live VFO (rx_vfo.h:89-100)
-int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
+int VfoBank::process(const cf32* dIn, int count, cudaStream_t s, const std::function<int()>* afterStage1) {
     if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
     DeviceGuard g(device);
-    if (everRan && s != lastStream) { B200_CUDA(cudaStreamSynchronize(lastStream)); }
+    if (everRan && s != lastStream) { B200_TRY(syncLast()); }
     lastStream = s; everRan = true;
     const bool exact = (rotatorMode == B200_ROTATOR_EXACT);
     if (!exact) { B200_TRY(calibrateDirty()); }
+
+    // Deferred tail (B200_OPT_DEFER_TAIL): possible when every VFO's first stage is the fused full-rate kernel, whose
+    // output buffer then alternates between two allocations so that block k's tail can still read one while block k+1's
+    // first stage fills the other.
+    bool defer = deferTail && count > 0;
+    if (defer) {
+        int live = 0;
+        for (auto& v : vfos) {
+            if (!v.live) { continue; }
+            live++;
+            const bool hasChain = ((v.mode == 0 || v.mode == 1) && !v.decimStages.empty());
+            if (!hasChain || !fusedStageSupported(v)) { defer = false; break; }
+        }
+        if (live == 0) { defer = false; }
+    }
+    const int par = tailPar;
+    if (defer) {
+        if (!tailStream) {
+            int lo = 0, hi = 0;
+            B200_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            B200_CUDA(cudaStreamCreateWithPriority(&tailStream, cudaStreamNonBlocking, hi));   // measured: the priority makes no difference (221-227 us/step either way)
+            for (int i = 0; i < 2; i++) { B200_CUDA(cudaEventCreateWithFlags(&evTail[i], cudaEventDisableTiming)); }
+        }
+        // at most two blocks in flight: this block reuses the first-stage output buffers of block k-2
+        if (tailPending[par]) { B200_CUDA(cudaStreamWaitEvent(s, evTail[par], 0)); tailPending[par] = false; }
+    }
+    else {
+        B200_TRY(joinTail());      // an inline tail follows every deferred one
+    }
 
     // ---- build this call's descriptors
     std::vector<RotJob> rj;
@@ -388,6 +440,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
             // stage 1 consumes the shared input directly, rotation folded in; its history refresh is done
             // by the fused edge kernel, so it is not added to histJobs
             FusedJob f;
+            if (defer) { B200_TRY(chain[0]->flipOut()); }
             fillFusedJob(f, *chain[0], v, dIn, count);
             fj.push_back(f);
             n = f.nOut;
@@ -423,11 +476,12 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         return a.ratio != b.ratio ? a.ratio < b.ratio : a.offset < b.offset;
     });
 
-    // ---- one upload (descriptors + any retuned rotator tables), then one launch per level
+    // ---- one upload (descriptors + any retuned rotator tables), then one launch per level.  With a deferred tail the
+    // descriptors of the later stages go to their own device buffer, uploaded on the tail's stream.
     for (auto& l : levels) { firJobsBalance(l.data(), (int)l.size()); }
     size_t bytes = rj.size() * sizeof(RotJob) + xj.size() * sizeof(XlateJob) + fj.size() * sizeof(FusedJob) + histJobs.size() * sizeof(FirJob);
     for (auto& l : levels) { bytes += l.size() * sizeof(FirJob); }
-    bytes += dirtyTables.size() * (kRotChunk * sizeof(float2)) + 64 * (16 + dirtyTables.size());
+    bytes += dirtyTables.size() * (kRotChunk * sizeof(float2)) + 64 * (16 + dirtyTables.size() + levels.size());
     void* hp = nullptr; int slot = 0;
     B200_TRY(ring.acquire(bytes, &hp, &slot));
     char* h = (char*)hp; size_t off = 0;
@@ -435,17 +489,25 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
     const size_t oR = put(rj.data(), rj.size() * sizeof(RotJob));
     const size_t oX = put(xj.data(), xj.size() * sizeof(XlateJob));
     const size_t oF = put(fj.data(), fj.size() * sizeof(FusedJob));
+    const size_t headBytes = off;
     std::vector<size_t> oL;
     for (auto& l : levels) { oL.push_back(put(l.data(), l.size() * sizeof(FirJob))); }
     const size_t oH = put(histJobs.data(), histJobs.size() * sizeof(FirJob));
     const size_t descBytes = off;
-    if (descBytes > dDescBytes) {
-        B200_CUDA(cudaStreamSynchronize(s));
+    const size_t firstBytes = defer ? headBytes : descBytes;
+    if (firstBytes > dDescBytes) {
+        B200_TRY(syncLast());
         if (dDesc) { cudaFree(dDesc); }
-        dDescBytes = descBytes * 2;
+        dDescBytes = firstBytes * 2;
         B200_CUDA(cudaMalloc(&dDesc, dDescBytes));
     }
-    B200_TRY(uploadDesc(dDesc, h, descBytes, s, descViaParams));
+    if (defer && descBytes - headBytes > dTailDescBytes) {
+        B200_TRY(syncLast());
+        if (dTailDesc) { cudaFree(dTailDesc); }
+        dTailDescBytes = (descBytes - headBytes) * 2;
+        B200_CUDA(cudaMalloc(&dTailDesc, dTailDescBytes));
+    }
+    B200_TRY(uploadDesc(dDesc, h, firstBytes, s, descViaParams));
     for (Vfo* v : dirtyTables) {
         float2* tab = (float2*)(h + off);
         makeRotatorTable(v->dRe, v->dIm, tab);
@@ -454,6 +516,10 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         v->tableDirty = false;
     }
     char* d = (char*)dDesc;
+    // where the later stages find their descriptors, and the stream they run on
+    char* dt = defer ? (char*)dTailDesc : d;
+    const size_t tailOff = defer ? headBytes : 0;
+    cudaStream_t ts = defer ? tailStream : s;
 
     int maxH = 0;
     for (auto& j : histJobs) { maxH = std::max(maxH, j.H); }
@@ -461,18 +527,28 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s) {
         B200_TRY(launchCheckpoints((const RotJob*)(d + oR), (int)rj.size(), exact ? (int)rj.size() : 0, count, s));
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
+        if (afterStage1) { B200_TRY((*afterStage1)()); afterStage1 = nullptr; }
         B200_CUDA(cudaEventRecord(evStage1, s));
+        if (defer) {
+            B200_CUDA(cudaStreamWaitEvent(ts, evStage1, 0));
+            B200_TRY(uploadDesc(dTailDesc, h + headBytes, descBytes - headBytes, ts, true));
+        }
         for (size_t l = 0; l < levels.size(); l++) {
-            B200_TRY(launchFirJobs((const FirJob*)(d + oL[l]), levels[l].data(), (int)levels[l].size(), 2, s));
+            B200_TRY(launchFirJobs((const FirJob*)(dt + oL[l] - tailOff), levels[l].data(), (int)levels[l].size(), 2, ts));
         }
     }
     else if (!fj.empty()) {
         // an empty block: the fused stages still flip their history ping-pong; copy the history across
         B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
     }
-    B200_TRY(launchHistoryUpdate((const FirJob*)(d + oH), (int)histJobs.size(), maxH, s));
-    B200_TRY(ring.release(slot, s));      // after the last reader of the slot was enqueued
-    B200_TRY(processDemods(*this, s));
+    if (afterStage1) { B200_TRY((*afterStage1)()); }
+    B200_TRY(launchHistoryUpdate((const FirJob*)(dt + oH - tailOff), (int)histJobs.size(), maxH, ts));
+    B200_TRY(ring.release(slot, ts));      // after the last reader of the slot was enqueued
+    B200_TRY(processDemods(*this, ts));
+    if (defer) {
+        B200_CUDA(cudaEventRecord(evTail[par], ts));
+        tailPending[par] = true; lastTailPar = par; tailPar = par ^ 1; tailUnjoined = true;
+    }
     return B200_OK;
 }
 

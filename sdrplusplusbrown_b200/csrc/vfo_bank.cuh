@@ -1,5 +1,6 @@
 // RxVFO bank: host-side state mirror + launch orchestration (device kernels in xlate.cu / fir_jobs.cu / demod.cu).
 #pragma once
+#include <functional>
 #include <memory>
 #include <vector>
 
@@ -23,6 +24,7 @@ struct Stage {
     int cur = 0;
     size_t histCapBytes = 0;
     void* dOut = nullptr;
+    void* dOutAlt = nullptr;          // second output buffer of a first stage whose consumers run one block behind (deferred tail)
     int outCap = 0;
 
     bool planTaps = false;            // taps are one of the pow-2 plan tables (decim_tables.inc): the kernel may use its constant-bank copy
@@ -31,6 +33,7 @@ struct Stage {
     int resetState();                                   // zero history, offset = phase = 0
     int setTapsKeepHistory(const std::vector<float>& taps);   // FIR::setTaps (fir.h:33-54)
     int ensureOutCap(int cap);
+    int flipOut();                                      // swap dOut and dOutAlt (allocated on first use)
     int outCountFor(int nIn) const;
     void advance(int nIn);                              // integer state after a block of nIn
     void fillJob(FirJob& j, const void* data, int nIn) const;
@@ -88,6 +91,15 @@ struct VfoBank {
     // per-call descriptors
     PinnedRing ring;
     void* dDesc = nullptr; size_t dDescBytes = 0;
+    // B200_OPT_DEFER_TAIL: the stages behind the full-rate one (and the demodulators) of block k run on tailStream beside
+    // the full-rate stage of block k+1; the caller's stream joins them when it asks for an output pointer.
+    cudaStream_t tailStream = nullptr;
+    cudaEvent_t evTail[2] = { nullptr, nullptr };
+    bool tailPending[2] = { false, false };
+    int tailPar = 0, lastTailPar = 0;
+    bool tailUnjoined = false;
+    void* dTailDesc = nullptr; size_t dTailDescBytes = 0;
+    int joinTail();                  // lastStream waits for the newest deferred tail
     // host staging for process_host
     cf32* hPinnedIn = nullptr; size_t hPinnedInCap = 0;
     cf32* dStageIn = nullptr; size_t dStageInCap = 0;
@@ -110,10 +122,13 @@ struct VfoBank {
     int regenChannelTaps(Vfo& v, bool create);   // RxVFO::generateTaps + filter.setTaps
     int resetVfo(Vfo& v);
     int calibrateDirty();
-    int process(const cf32* dIn, int count, cudaStream_t s);
+    // afterStage1: called once, right behind the launch of the full-rate first-stage kernels (the front end enqueues its
+    // FFT branch there when the branch order asks for it)
+    int process(const cf32* dIn, int count, cudaStream_t s, const std::function<int()>* afterStage1 = nullptr);
     int maxOut(int v, int count) const;
 };
 
+extern bool deferTail;
 int launchXlate(const XlateJob* dJobs, int nJobs, int maxN, cudaStream_t s);
 
 } // namespace b200

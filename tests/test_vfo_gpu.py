@@ -325,3 +325,71 @@ def test_single_vfo_kernel_every_start_parity(lead, sizes):
         assert b.out_count(v) == len(ref)
         if len(ref) > 8:
             assert err_db(b.output(v), ref) <= -80.0
+
+
+@pytest.mark.parametrize("with_fft", [False, True])
+def test_deferred_tail_gives_identical_results(with_fft):
+    """B200_OPT_DEFER_TAIL: the stages behind the full-rate one (and the demodulators) of block k run on their own stream
+    beside the full-rate stage of block k+1, and the caller's stream joins them when it asks for an output pointer.
+    Same blocks, same order => bit-identical outputs, whether the outputs are fetched after every block, after some, or
+    only at the end; a bank with a VFO the fused stage cannot serve falls back to the inline tail."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    in_sr = 2.4e6
+    n = 12000 * 40
+    x = synth.make_iq(11, n, in_sr, sigma=0.05, tones=[(100e3 + 700.0, 0.3), (-340e3 + 300.0, 0.2)])
+    blocks = split(x, [120000, 60000, 12000, 7, 150000, 0, 90000])
+    dev_blocks = [to_dev(b) if len(b) else to_dev(np.zeros(1, np.complex64)) for b in blocks]
+    stream = torch.cuda.Stream()
+
+    def run(defer, fetch_every):
+        if with_fft:
+            top = binding.FrontEnd(in_sr, fft_size=8192, fft_rate=20.0, fft_window=2, max_block=200000, device=0)
+            bank = top.vfos
+        else:
+            top = bank = binding.VfoBank(in_sr, max_block=200000)
+        bank.set_option(binding.OPT_DEFER_TAIL, int(defer))
+        try:
+            bank.set_rotator_mode(binding.ROTATOR_EXACT)
+            v0 = bank.add(50e3, 12.5e3, 100e3)
+            v1 = bank.add(24e3, 2.8e3, -340e3)
+            v2 = bank.add(15e3, 15e3, 5e3)          # bandwidth == rate: no channel filter, decimator only
+            bank.set_demod(v0, binding.DEMOD_NFM, 1, 0, 0, 0)
+            bank.set_demod(v1, binding.DEMOD_USB, 0, 50.0 / 24e3, 5.0 / 24e3, 0)
+            bank.set_audio_post(v0, 48e3, 50e-6)
+            outs = []
+            with torch.cuda.stream(stream):
+                for i, (blk, d) in enumerate(zip(blocks, dev_blocks)):
+                    top.process(d, len(blk), stream=stream)
+                    if fetch_every and (i % fetch_every) == fetch_every - 1:
+                        outs.append([bank.output(v).copy() for v in (v0, v1, v2)] + [bank.audio(v0).copy(), bank.audio(v1).copy()])
+                last = [bank.output(v).copy() for v in (v0, v1, v2)] + [bank.audio(v0).copy(), bank.audio(v1).copy()]
+            return outs, last
+        finally:
+            bank.set_option(binding.OPT_DEFER_TAIL, 0)
+
+    ref_outs, ref_last = run(False, 1)
+    for fetch_every in (1, 3, 0):
+        outs, last = run(True, fetch_every)
+        for a, b in zip(last, ref_last):
+            assert a.shape == b.shape and np.array_equal(a, b), fetch_every
+        if fetch_every:
+            picked = [ref_outs[i] for i in range(len(blocks)) if (i % fetch_every) == fetch_every - 1]
+            for got, want in zip(outs, picked):
+                for a, b in zip(got, want):
+                    assert a.shape == b.shape and np.array_equal(a, b), fetch_every
+    # a VFO with no decimation (rate == input rate) has no fused first stage: the bank runs its tail inline, same results
+    b = binding.VfoBank(in_sr, max_block=200000)
+    b.set_option(binding.OPT_DEFER_TAIL, 1)
+    try:
+        b.set_rotator_mode(binding.ROTATOR_EXACT)
+        va = b.add(50e3, 12.5e3, 100e3)
+        vb = b.add(in_sr, in_sr, 10e3)
+        o = ol.Vfo(PORT, in_sr, 50e3, 12.5e3, 100e3)
+        for blk, d in zip(blocks[:3], dev_blocks[:3]):
+            ref = o.process(blk)
+            b.process(d, len(blk))
+            assert err_db(b.output(va), ref) <= -80.0
+            assert b.out_count(vb) == len(blk)
+    finally:
+        b.set_option(binding.OPT_DEFER_TAIL, 0)

@@ -27,6 +27,10 @@ def main():
     ap.add_argument("--no-vfo", action="store_true")
     ap.add_argument("--demod", action="store_true")
     ap.add_argument("--cfg", default="cfg2")
+    ap.add_argument("--attach", action="store_true", help="waterfall attached to the FFT branch, as bench.py runs it")
+    ap.add_argument("--order", type=int, default=0, help="B200_OPT_BRANCH_ORDER")
+    ap.add_argument("--fft-ctas", type=int, default=0, help="B200_OPT_FFT_CTAS_PER_SM")
+    ap.add_argument("--defer", type=int, default=0, help="B200_OPT_DEFER_TAIL")
     args = ap.parse_args()
     import torch
     from torch.profiler import ProfilerActivity, profile
@@ -55,11 +59,17 @@ def main():
     x = synth.make_iq_torch(B, sr, dev, tones=[(3.3e6, 0.2)])
     s = torch.cuda.Stream(device=dev)
 
+    fe.vfos.set_option(binding.OPT_BRANCH_ORDER, args.order)
+    fe.vfos.set_option(binding.OPT_FFT_CTAS_PER_SM, args.fft_ctas)
+    fe.vfos.set_option(binding.OPT_DEFER_TAIL, args.defer)
+    if args.attach:
+        fe.attach_waterfall(wf, d_zoom.data_ptr(), d_rgba.data_ptr(), max_frames)
+
     def step():
         with torch.cuda.stream(s):
             fe.process(x, B, stream=s)
             nf = fe.frame_count()
-            if nf:
+            if nf and not args.attach:
                 wf.push(fe.frame_ptr(0), nf, d_zoom.data_ptr(), d_rgba.data_ptr(), stream=s)
 
     for _ in range(3):
@@ -80,7 +90,7 @@ def main():
         return
     # split into steps: a step begins at every rotator-checkpoint kernel (or FFT kernel when there is no VFO)
     per = len(ev) // args.steps
-    last = ev[-per:]
+    last = ev[-2 * per:] if args.defer else ev[-per:]      # deferred tail: two steps, to see what overlaps what
     t0 = last[0]["ts"]
     print("%-58s %7s %10s %9s" % ("kernel / copy", "stream", "start us", "dur us"))
     for e in last:
