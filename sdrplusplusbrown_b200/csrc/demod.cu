@@ -45,7 +45,7 @@ struct DemodState {
     SeqState* dState = nullptr;
     float2* dWtab = nullptr;                 // SSB: phaseDelta^j, j < 512
     float* dMono = nullptr; float* dStereo = nullptr; int cap = 0;
-    float4* dMaps = nullptr; float* dAmps = nullptr;   // SSB fast path scratch
+    float2* dMaps = nullptr; float* dAmps = nullptr;   // SSB fast path scratch
     long long envCount = 0;                            // host mirror of AGC::_startEnvelope (SSB fast path)
     int lastCount = 0;
     // radio AF chain (radio_module.h:101-107): RationalResampler<stereo_t> to the audio rate, then Deemphasis<stereo_t>
@@ -98,7 +98,7 @@ struct DeemphJob { float2* data; SeqState* st; float alpha; int n; };
 // per-call descriptor
 struct DemodJob {
     const cf32* in; float* mono; float* stereo; const float* stereoSrc; SeqState* st; const float2* wtab;
-    float4* maps; float* amps;      // SSB fast path scratch: per-sample AGC maps, walked amplitudes
+    float2* maps; float* amps;      // SSB fast path scratch: per-sample AGC intercepts (|x|*attack, |x|*decay; -1 marks a sample the AGC skips), walked amplitudes
     AgcParams agc;
     double angle0, theta; float stepRe, stepIm;
     float invDeviation, dcRate;
@@ -338,10 +338,9 @@ __global__ void __launch_bounds__(256) ssbPrepKernel(const DemodJob* __restrict_
     j.mono[i] = re;
     const float am = fabsf(re);
     const bool ok = (am != 0.0f) && (am == am);
-    float4 m;
-    m.x = ok ? j.agc.invAttack : 1.0f; m.y = ok ? am * j.agc.attack : 0.0f;
-    m.z = ok ? j.agc.invDecay : 1.0f;  m.w = ok ? am * j.agc.decay : 0.0f;
-    j.maps[i] = m;
+    // the two candidates of the next amplitude are amp*(1-attack) + |x|*attack and amp*(1-decay) + |x|*decay: only the
+    // intercepts depend on the sample.  A sample the AGC skips (zero or NaN amplitude, agc.h:99) is marked by -1.
+    j.maps[i] = ok ? make_float2(am * j.agc.attack, am * j.agc.decay) : make_float2(-1.0f, -1.0f);
 }
 
 constexpr int kWalkChunk = 512;
@@ -351,8 +350,49 @@ __device__ __forceinline__ void cpAsync16(void* smemDst, const void* gsrc) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");
 }
 
+// amp' = max/min(amp * (1-attack) + ia, amp * (1-decay) + id) over one staged chunk of intercept pairs, two samples per
+// 16-byte shared-memory read; 16 samples per trip in two register sets: while one set's chain runs, the other set's
+// operands are already in flight.  SKIPS: the chunk holds samples the AGC leaves the amplitude alone for (marked by a
+// negative intercept); the select then sits in the chain, which only matters for silence.
+template <bool MAX, bool SKIPS>
+__device__ __forceinline__ float walkChunk(const float2* __restrict__ M, float* __restrict__ R, int m, float am, float sa, float sd) {
+    auto one = [&](float ia, float id) {
+        const float a = fmaf(am, sa, ia), d = fmaf(am, sd, id);
+        const float nx = MAX ? fmaxf(a, d) : fminf(a, d);
+        am = (SKIPS && ia < 0.0f) ? am : nx;
+        return am;
+    };
+    auto walk8 = [&](const float4* q, int at) {
+        float r[8];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { r[2 * u] = one(q[u].x, q[u].y); r[2 * u + 1] = one(q[u].z, q[u].w); }
+        *reinterpret_cast<float4*>(&R[at]) = make_float4(r[0], r[1], r[2], r[3]);
+        *reinterpret_cast<float4*>(&R[at + 4]) = make_float4(r[4], r[5], r[6], r[7]);
+    };
+    const float4* M4 = reinterpret_cast<const float4*>(M);
+    int i = 0;
+    float4 qa[4], qb[4];
+    if (m >= 16) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) { qa[u] = M4[u]; }
+    }
+#pragma unroll 1
+    for (; i + 16 <= m; i += 16) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) { qb[u] = M4[(i >> 1) + 4 + u]; }
+        walk8(qa, i);
+        if (i + 32 <= m) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) { qa[u] = M4[(i >> 1) + 8 + u]; }
+        }
+        walk8(qb, i + 8);
+    }
+    for (; i < m; i++) { R[i] = one(M[i].x, M[i].y); }
+    return am;
+}
+
 __global__ void __launch_bounds__(32) agcWalkKernel(const DemodJob* __restrict__ jobs) {
-    __shared__ __align__(16) float4 sM[2][kWalkChunk];
+    __shared__ __align__(16) float2 sM[2][kWalkChunk];
     __shared__ __align__(16) float sR[kWalkChunk];
     const DemodJob j = jobs[blockIdx.x];
     const int lane = threadIdx.x;
@@ -362,7 +402,8 @@ __global__ void __launch_bounds__(32) agcWalkKernel(const DemodJob* __restrict__
     auto prefetch = [&](int c) {
         const int base = c * kWalkChunk;
         const int m = min(kWalkChunk, j.n - base);
-        for (int i = lane; i < m; i += 32) { cpAsync16(&sM[c & 1][i], j.maps + base + i); }
+        // 16 bytes = two samples per copy (the buffer is allocated with slack, an odd tail reads one sample past the block)
+        for (int i = lane; 2 * i < m; i += 32) { cpAsync16(&sM[c & 1][2 * i], j.maps + base + 2 * i); }
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
     if (nChunks > 0) { prefetch(0); }
@@ -377,46 +418,14 @@ __global__ void __launch_bounds__(32) agcWalkKernel(const DemodJob* __restrict__
         __syncwarp();
         const int base = c * kWalkChunk;
         const int m = min(kWalkChunk, j.n - base);
-        if (lane == 0) {
-            const float4* M = sM[c & 1];
-            // 16 samples per trip in two register sets: while one set's chain runs, the other set's operands are
-            // already in flight from shared memory, and no register copies are needed
-            auto walk8 = [&](const float4* q, int at) {
-                float r[8];
-                if (useMax) {
-#pragma unroll
-                    for (int u = 0; u < 8; u++) { am = fmaxf(fmaf(am, q[u].x, q[u].y), fmaf(am, q[u].z, q[u].w)); r[u] = am; }
-                }
-                else {
-#pragma unroll
-                    for (int u = 0; u < 8; u++) { am = fminf(fmaf(am, q[u].x, q[u].y), fmaf(am, q[u].z, q[u].w)); r[u] = am; }
-                }
-                *reinterpret_cast<float4*>(&sR[at]) = make_float4(r[0], r[1], r[2], r[3]);
-                *reinterpret_cast<float4*>(&sR[at + 4]) = make_float4(r[4], r[5], r[6], r[7]);
-            };
-            int i = 0;
-            float4 qa[8], qb[8];
-            if (m >= 16) {
-#pragma unroll
-                for (int u = 0; u < 8; u++) { qa[u] = M[u]; }
-            }
-            for (; i + 16 <= m; i += 16) {
-#pragma unroll
-                for (int u = 0; u < 8; u++) { qb[u] = M[i + 8 + u]; }
-                walk8(qa, i);
-                if (i + 32 <= m) {
-#pragma unroll
-                    for (int u = 0; u < 8; u++) { qa[u] = M[i + 16 + u]; }
-                }
-                walk8(qb, i + 8);
-            }
-            for (; i < m; i++) {
-                const float4 q = M[i];
-                const float ca = fmaf(am, q.x, q.y), cd = fmaf(am, q.z, q.w);
-                am = useMax ? fmaxf(ca, cd) : fminf(ca, cd);
-                sR[i] = am;
-            }
-        }
+        const float2* M = sM[c & 1];
+        bool skip = false;
+        for (int i = lane; i < m; i += 32) { skip = skip || (M[i].x < 0.0f); }
+        const bool skips = __any_sync(0xffffffffu, skip);
+        // Every lane walks the same chain: uniform control flow (no divergence bookkeeping around the walk), operands read
+        // as shared-memory broadcasts, identical stores.
+        if (useMax) { am = skips ? walkChunk<true, true>(M, sR, m, am, j.agc.invAttack, j.agc.invDecay) : walkChunk<true, false>(M, sR, m, am, j.agc.invAttack, j.agc.invDecay); }
+        else { am = skips ? walkChunk<false, true>(M, sR, m, am, j.agc.invAttack, j.agc.invDecay) : walkChunk<false, false>(M, sR, m, am, j.agc.invAttack, j.agc.invDecay); }
         __syncwarp();
         for (int i = lane; i < m; i += 32) { j.amps[base + i] = sR[i]; }
         __syncwarp();
@@ -788,7 +797,7 @@ static int demodEnsureCap(DemodState& d, int n) {
     if (d.dAmps) { cudaFree(d.dAmps); d.dAmps = nullptr; }
     d.cap = n + 64;
     if (d.dWtab) {
-        B200_CUDA(cudaMalloc((void**)&d.dMaps, (size_t)d.cap * sizeof(float4)));
+        B200_CUDA(cudaMalloc((void**)&d.dMaps, (size_t)d.cap * sizeof(float2)));
         B200_CUDA(cudaMalloc((void**)&d.dAmps, (size_t)d.cap * sizeof(float)));
     }
     B200_CUDA(cudaMalloc((void**)&d.dMono, (size_t)d.cap * sizeof(float)));
@@ -981,6 +990,23 @@ static int afConfigure(VfoBank& bank, Vfo& v, double audioSR, double tau) {
     B200_CUDA(cudaMemcpy(&d.dState->deLast, &zero, sizeof(zero), cudaMemcpyHostToDevice));
     d.lastAudio = nullptr; d.lastAudioCount = 0;
     return B200_OK;
+}
+
+// The sequential walks (AGC, pilot PLL) run one warp per VFO and are bound by the latency of a dependent chain; a warp
+// that shares its SM with the wide kernels of the next block waits for issue slots at every step of that chain (measured:
+// the AGC walk of the bench's one VFO takes 0.58 ms alone and 1.09 ms beside the next block's kernels).  While there are
+// few walks, each asks for so much dynamic shared memory that it gets an SM to itself; with many VFOs the walks fill the
+// machine themselves and take what fits.
+constexpr size_t kSoloSmemBytes = 180 * 1024;
+constexpr size_t kSoloMaxJobs = 24;
+static size_t soloSmem(size_t nJobs) {
+    static bool attr = false;
+    if (!attr) {
+        cudaFuncSetAttribute(agcWalkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
+        cudaFuncSetAttribute(pllKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
+        attr = true;
+    }
+    return nJobs <= kSoloMaxJobs ? kSoloSmemBytes : 0;
 }
 
 int processDemods(VfoBank& bank, cudaStream_t s) {
@@ -1214,7 +1240,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         B200_TRY(launchFirJobs((const FirJob*)(dd + oWA), wfmA.data(), (int)wfmA.size(), 1, s));
         B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oWA), (int)wfmA.size(), maxH, s));
         if (!pllJobs.empty()) {
-            pllKernel<<<(unsigned)pllJobs.size(), 32, 0, s>>>((const PllJob*)(dd + oP));
+            pllKernel<<<(unsigned)pllJobs.size(), 32, soloSmem(pllJobs.size()), s>>>((const PllJob*)(dd + oP));
             B200_CHECK_LAUNCH(); countLaunch();
         }
         wfmMixKernel<<<dim3((maxMix + 255) / 256, (unsigned)mixJobs.size()), 256, 0, s>>>((const WfmMixJob*)(dd + oM));
@@ -1236,7 +1262,7 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         const dim3 grid((maxS + 255) / 256, (unsigned)ssb.size());
         ssbPrepKernel<<<grid, 256, 0, s>>>((const DemodJob*)(dd + oB));
         B200_CHECK_LAUNCH();
-        agcWalkKernel<<<(unsigned)ssb.size(), 32, 0, s>>>((const DemodJob*)(dd + oB));
+        agcWalkKernel<<<(unsigned)ssb.size(), 32, soloSmem(ssb.size()), s>>>((const DemodJob*)(dd + oB));
         B200_CHECK_LAUNCH();
         ssbFinishKernel<<<grid, 256, 0, s>>>((const DemodJob*)(dd + oB));
         B200_CHECK_LAUNCH();
