@@ -474,12 +474,12 @@ __global__ void __launch_bounds__(256) stereoKernel(const DemodJob* __restrict__
 
 // ---- broadcast FM stereo ------------------------------------------------------------------------------------
 // Pilot PLL (loop/pll.h:64-70 over phase_control_loop.h:58-66), one warp per VFO.  The warp turns a chunk of pilot
-// samples into phases (atan2f) in shared memory, lane 0 walks the second-order loop -- frequency and phase both depend
-// on the previous sample's error, so the walk is sequential -- and the warp writes the VCO phase of every sample out.
+// samples into phases (atan2f) in shared memory, then walks the second-order loop -- frequency and phase both depend
+// on the previous sample's error, so the walk is sequential -- and writes the VCO phase of every sample out.
 constexpr int kPllChunk = 512;
 __global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs) {
     const PllJob j = jobs[blockIdx.x];
-    __shared__ float sIn[kPllChunk], sOut[kPllChunk];
+    __shared__ __align__(16) float sIn[kPllChunk], sOut[kPllChunk];
     const int lane = threadIdx.x;
     const float PI = 3.1415926535f;      // FL_M_PI (math/constants.h:4); phase limits -PI..PI, phaseDelta = 2*PI
     float phase = j.st->pllPhase, freq = j.st->pllFreq;
@@ -487,7 +487,45 @@ __global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs)
         const int m = min(kPllChunk, j.n - base);
         for (int i = lane; i < m; i += 32) { sIn[i] = atan2f(__ldg(j.pi + base + i), __ldg(j.pr + base + i)); }
         __syncwarp();
-        if (lane == 0) {
+        // every lane walks the same loop (uniform control flow, broadcast reads, identical writes): no divergence
+        // bookkeeping inside the dependent chain
+        // The wraps are written as selects so that the dependent chain holds no branches: the reference's while loops
+        // run at most once as long as a step stays under 2*pi.  Whether that held is collected in a flag; a chunk where
+        // it did not (never seen with the loop's gains) is walked again from its start with the loops as written.
+        const float TWO_PI = __fsub_rn(PI, -PI);
+        const float phase0 = phase, freq0 = freq;
+        bool bad = false;
+        auto step = [&](float in) {
+            const float out = phase;
+            float err = __fsub_rn(in, phase);
+            const float eHi = __fsub_rn(err, 2.0f * PI), eLo = __fadd_rn(err, 2.0f * PI);
+            err = (err > PI) ? eHi : ((err <= -PI) ? eLo : err);
+            freq = __fadd_rn(freq, __fmul_rn(j.beta, err));
+            freq = fminf(fmaxf(freq, j.minFreq), j.maxFreq);
+            const float p0 = __fadd_rn(phase, __fadd_rn(freq, __fmul_rn(j.alpha, err)));
+            float p1 = (p0 > PI) ? __fsub_rn(p0, TWO_PI) : p0;
+            p1 = (p1 < -PI) ? __fadd_rn(p1, TWO_PI) : p1;
+            bad = bad || (fabsf(p1) > PI);
+            phase = p1;
+            return out;
+        };
+        int i = 0;
+        // eight samples per trip: inputs read ahead of the chain (two 16-byte reads), phases written behind it
+        float4 xa, xb;
+        if (m >= 8) { xa = *reinterpret_cast<const float4*>(&sIn[0]); xb = *reinterpret_cast<const float4*>(&sIn[4]); }
+#pragma unroll 1
+        for (; i + 8 <= m; i += 8) {
+            const float4 ca = xa, cb = xb;
+            if (i + 16 <= m) { xa = *reinterpret_cast<const float4*>(&sIn[i + 8]); xb = *reinterpret_cast<const float4*>(&sIn[i + 12]); }
+            float4 oa, ob;
+            oa.x = step(ca.x); oa.y = step(ca.y); oa.z = step(ca.z); oa.w = step(ca.w);
+            ob.x = step(cb.x); ob.y = step(cb.y); ob.z = step(cb.z); ob.w = step(cb.w);
+            *reinterpret_cast<float4*>(&sOut[i]) = oa;
+            *reinterpret_cast<float4*>(&sOut[i + 4]) = ob;
+        }
+        for (; i < m; i++) { sOut[i] = step(sIn[i]); }
+        if (bad) {
+            phase = phase0; freq = freq0;
             for (int i = 0; i < m; i++) {
                 sOut[i] = phase;
                 float err = __fsub_rn(sIn[i], phase);
@@ -496,8 +534,8 @@ __global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs)
                 freq = __fadd_rn(freq, __fmul_rn(j.beta, err));
                 freq = fminf(fmaxf(freq, j.minFreq), j.maxFreq);
                 phase = __fadd_rn(phase, __fadd_rn(freq, __fmul_rn(j.alpha, err)));
-                while (phase > PI) { phase = __fsub_rn(phase, __fsub_rn(PI, -PI)); }
-                while (phase < -PI) { phase = __fadd_rn(phase, __fsub_rn(PI, -PI)); }
+                while (phase > PI) { phase = __fsub_rn(phase, TWO_PI); }
+                while (phase < -PI) { phase = __fadd_rn(phase, TWO_PI); }
             }
         }
         __syncwarp();
