@@ -280,6 +280,15 @@ int b200_frontend_process_host_i8(b200_frontend* fe, const int8_t* h_in, int cou
                                   float* const* h_vfo_out, float* const* h_audio, int* vfo_counts, void* stream);
 /* Device-resident form of that conversion: count complex samples, d_in int16[2*count] -> d_out float[2*count]. */
 int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out, void* stream);
+/* The other direction, for the recorder (misc_modules/recorder/src/main.cpp:528-558 -> wav::Writer::write,
+ * core/src/utils/wav.cpp:148-178): n_floats device floats (stereo audio or complex baseband, interleaved) -> PCM of the
+ * WAV file's sample type, bit for bit as the reference's writer converts them (uint8: (x*127)+128 truncated; int16 / int32:
+ * volk_32f_s32f_convert_16i / _32i with 32767 / 2147483647).  Recorded data then crosses PCIe at its file size; the RIFF
+ * container is host code (wav::Writer in include/utils/wav.h takes the converted bytes). */
+#define B200_PCM_UINT8 0
+#define B200_PCM_INT16 1
+#define B200_PCM_INT32 2
+int b200_convert_pcm(const float* d_in, void* d_out, int n_floats, int sample_type, void* stream);
 
 /* DC blocker (dsp::correction::DCBlocker<complex_t>::process, correction/dc_blocker.h:54-60) for callers that
  * are not allowed to allocate.  This entry point has no counterpart in the reference; it exists for hosts that

@@ -9,6 +9,8 @@
 #include <cstdint>
 #include <cstring>
 #include <fstream>
+#include <mutex>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -88,5 +90,94 @@ namespace wav {
         bool valid = false, looped = false;
         std::ifstream file;
         size_t bytesRead = 0;
+    };
+
+    // wav::Writer — the recorder's file writer (reference: core/src/utils/wav.h:41-76, wav.cpp:20-182 over riff::Writer,
+    // utils/riff.cpp; used by misc_modules/recorder/src/main.cpp:168-177,225,528-558).  Same members: open / isOpen / close /
+    // setChannels / setSamplerate / setFormat / setSampleType / getSamplesWritten / write; the setters throw
+    // std::runtime_error while a file is open, as the reference's do.  The container is host code.  The float -> PCM
+    // conversion of write() is not: for the uint8 / int16 / int32 sample types this writer takes samples that
+    // b200_convert_pcm already converted on the device (writePcm), so recorded data crosses PCIe at its file size;
+    // write(float*) serves SAMP_TYPE_FLOAT32, where the reference writes the floats as they are.
+    enum Format { FORMAT_WAV, FORMAT_RF64 };
+
+    class Writer {
+    public:
+        Writer(int channels = 2, uint64_t samplerate = 48000, Format format = FORMAT_WAV, SampleType type = SAMP_TYPE_INT16) {
+            if (channels < 1) { throw std::runtime_error("Channel count must be greater or equal to 1"); }
+            if (!samplerate) { throw std::runtime_error("Samplerate must be non-zero"); }
+            _channels = channels; _samplerate = samplerate; _format = format; _type = type;
+        }
+        ~Writer() { close(); }
+
+        bool open(std::string path) {
+            std::lock_guard<std::recursive_mutex> lck(mtx);
+            if (file.is_open()) { close(); }
+            samplesWritten = 0; dataBytes = 0;
+            const int bits = (_type == SAMP_TYPE_UINT8) ? 8 : (_type == SAMP_TYPE_INT16) ? 16 : 32;
+            bytesPerSamp = (size_t)(bits / 8) * (size_t)_channels;
+            file.open(path.c_str(), std::ios::out | std::ios::binary);
+            if (!file.is_open()) { return false; }
+            // "RIFF" <size> "WAVE" | "fmt " 16 <format header> | "data" <size>; the sizes are patched in by close()
+            put("RIFF", 4); put32(0); put("WAVE", 4);
+            put("fmt ", 4); put32(16);
+            put16((uint16_t)((_type == SAMP_TYPE_FLOAT32) ? CODEC_FLOAT : CODEC_PCM)); put16((uint16_t)_channels);
+            put32((uint32_t)_samplerate); put32((uint32_t)(bytesPerSamp * _samplerate));
+            put16((uint16_t)bytesPerSamp); put16((uint16_t)bits);
+            put("data", 4); put32(0);
+            return true;
+        }
+        bool isOpen() { std::lock_guard<std::recursive_mutex> lck(mtx); return file.is_open(); }
+        void close() {
+            std::lock_guard<std::recursive_mutex> lck(mtx);
+            if (!file.is_open()) { return; }
+            file.seekp(40); put32((uint32_t)dataBytes);
+            file.seekp(4); put32((uint32_t)(4 + (8 + 16) + (8 + dataBytes)));
+            file.close();
+        }
+
+        void setChannels(int channels) {
+            std::lock_guard<std::recursive_mutex> lck(mtx);
+            guard();
+            if (channels < 1) { throw std::runtime_error("Channel count must be greater or equal to 1"); }
+            _channels = channels;
+        }
+        void setSamplerate(uint64_t samplerate) {
+            std::lock_guard<std::recursive_mutex> lck(mtx);
+            guard();
+            if (!samplerate) { throw std::runtime_error("Samplerate must be non-zero"); }
+            _samplerate = samplerate;
+        }
+        void setFormat(Format format) { std::lock_guard<std::recursive_mutex> lck(mtx); guard(); _format = format; }
+        void setSampleType(SampleType type) { std::lock_guard<std::recursive_mutex> lck(mtx); guard(); _type = type; }
+        SampleType getSampleType() const { return _type; }
+        int getChannels() const { return _channels; }
+        size_t getSamplesWritten() { return samplesWritten; }
+
+        // `count` samples (frames of `channels` values) already in the file's sample type: the output of b200_convert_pcm
+        // copied to the host, or floats for SAMP_TYPE_FLOAT32
+        void writePcm(const void* data, int count) {
+            std::lock_guard<std::recursive_mutex> lck(mtx);
+            if (!file.is_open()) { return; }
+            const size_t bytes = (size_t)count * bytesPerSamp;
+            file.write(static_cast<const char*>(data), (std::streamsize)bytes);
+            dataBytes += bytes;
+            samplesWritten += (size_t)count;
+        }
+        // wav::Writer::write for float files (wav.cpp:168-170)
+        void write(float* samples, int count) {
+            if (_type != SAMP_TYPE_FLOAT32) { throw std::runtime_error("PCM sample types are converted on the device: b200_convert_pcm + writePcm"); }
+            writePcm(samples, count);
+        }
+
+    private:
+        void guard() { if (file.is_open()) { throw std::runtime_error("Cannot change parameters while file is open"); } }
+        void put(const char* p, size_t n) { file.write(p, (std::streamsize)n); }
+        void put32(uint32_t v) { file.write(reinterpret_cast<const char*>(&v), 4); }
+        void put16(uint16_t v) { file.write(reinterpret_cast<const char*>(&v), 2); }
+        std::recursive_mutex mtx;
+        std::ofstream file;
+        int _channels; uint64_t _samplerate; Format _format; SampleType _type;
+        size_t bytesPerSamp = 0, samplesWritten = 0, dataBytes = 0;
     };
 }

@@ -111,6 +111,9 @@ void orc_fmif_destroy(void* h);
 int orc_fmif_process(void* h, int count, const float* in, float* out);
 // dsp::audio::Volume (audio/volume.h:13-50), the sink stream's volume block (signal_path/sink.h:73): gain = volume^2 in float, 0 when muted
 int orc_volume_process(double volume, int muted, int count, const float* inStereo, float* outStereo);
+// wav::Writer (utils/wav.cpp:20-182 over riff::Writer, utils/riff.cpp): the recorder's file writer (misc_modules/recorder/src/main.cpp:168-177,528-558).
+// Writes `count` samples of `channels` floats each in blocks of blockLen samples; sampleType 0 UINT8, 1 INT16, 2 INT32, 3 FLOAT32.  Returns 0 when written.
+int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen);
 // radio AF chain (decoder_modules/radio/src/radio_module.h:101-107,756-765): RationalResampler<stereo_t> to the audio
 // device rate, then optional Deemphasis<stereo_t> (filter/deephasis.h:58-76).  tau <= 0 disables the de-emphasis.
 void* orc_afpost_create(double inSamplerate, double audioSamplerate, double tau);

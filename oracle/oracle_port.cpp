@@ -880,6 +880,58 @@ int orc_volume_process(double volume, int muted, int count, const float* in, flo
     for (int i = 0; i < 2 * count; i++) { out[i] = in[i] * g; }
     return count;
 }
+// wav::Writer over riff::Writer (utils/wav.cpp:36-98,148-182; utils/riff.cpp:17-141): "RIFF" <size> "WAVE", a 16-byte "fmt "
+// chunk (codec 1 PCM / 3 float, channels, rate, bytes per second, bytes per frame, bit depth), then one "data" chunk; chunk
+// sizes are patched in when the chunks end.  Conversions: uint8 (x*127)+128 truncated, int16 / int32 by VOLK's generic
+// convert (scale by 32767 / 2147483647, clamp, round to nearest even), float32 as is.
+int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen) {
+    FILE* f = fopen(path, "wb");
+    if (!f) { return -1; }
+    const int bits = (sampleType == 0) ? 8 : (sampleType == 1) ? 16 : 32;
+    const uint32_t bytesPerSamp = (uint32_t)(bits / 8) * (uint32_t)channels;
+    uint32_t dataBytes = 0;
+    auto u32 = [&](uint32_t v) { fwrite(&v, 4, 1, f); };
+    auto u16 = [&](uint16_t v) { fwrite(&v, 2, 1, f); };
+    fwrite("RIFF", 1, 4, f); u32(0); fwrite("WAVE", 1, 4, f);
+    fwrite("fmt ", 1, 4, f); u32(16);
+    u16(sampleType == 3 ? 3 : 1); u16((uint16_t)channels); u32((uint32_t)(uint64_t)samplerate);
+    u32((uint32_t)(bytesPerSamp * (uint64_t)samplerate)); u16((uint16_t)bytesPerSamp); u16((uint16_t)bits);
+    fwrite("data", 1, 4, f); u32(0);
+    std::vector<uint8_t> b8; std::vector<int16_t> b16; std::vector<int32_t> b32;
+    for (int i = 0; i < count; i += blockLen) {
+        const int n = std::min(blockLen, count - i), t = n * channels;
+        const float* x = samples + (size_t)i * channels;
+        if (sampleType == 0) {
+            b8.resize(t);
+            for (int k = 0; k < t; k++) { b8[k] = (x[k] * 127.0f) + 128.0f; }
+            fwrite(b8.data(), 1, t, f);
+        }
+        else if (sampleType == 1) {
+            b16.resize(t);
+            for (int k = 0; k < t; k++) {
+                float r = x[k] * 32767.0f;
+                if (r > 32767.0f) { r = 32767.0f; } else if (r < -32768.0f) { r = -32768.0f; }
+                b16[k] = (int16_t)rintf(r);
+            }
+            fwrite(b16.data(), 2, t, f);
+        }
+        else if (sampleType == 2) {
+            b32.resize(t);
+            for (int k = 0; k < t; k++) {
+                const float r = x[k] * 2147483647.0f;
+                b32[k] = (r >= 2147483648.0f) ? 2147483647 : (r < -2147483648.0f) ? (int32_t)(-2147483647 - 1) : (int32_t)rintf(r);
+            }
+            fwrite(b32.data(), 4, t, f);
+        }
+        else { fwrite(x, 4, t, f); }
+        dataBytes += (uint32_t)n * bytesPerSamp;
+    }
+    // endChunk(data), endRIFF: sizes patched; the RIFF size counts the form, the fmt chunk and the data chunk with their headers
+    fseek(f, 40, SEEK_SET); u32(dataBytes);
+    fseek(f, 4, SEEK_SET); u32(4 + (8 + 16) + (8 + dataBytes));
+    fclose(f);
+    return 0;
+}
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int sqOn, double sqLevel) { auto* c = new IfChain; c->init(nbOn, nbRate, nbLevel, sqOn, sqLevel); return c; }
 void orc_ifchain_destroy(void* h) { delete (IfChain*)h; }
 int orc_ifchain_process(void* h, int count, const float* in, float* out) { return ((IfChain*)h)->process(count, (const cf*)in, (cf*)out); }

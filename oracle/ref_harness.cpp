@@ -49,6 +49,7 @@
 #include <dsp/noise_reduction/squelch.h>
 #include <dsp/noise_reduction/fm_if.h>
 #include <dsp/audio/volume.h>
+#include <utils/wav.h>
 #undef protected
 #undef private
 
@@ -293,6 +294,15 @@ int orc_volume_process(double volume, int muted, int count, const float* in, flo
     dsp::audio::Volume v;
     v.init(NULL, volume, muted != 0);
     return v.process(count, (const stereo_t*)in, (stereo_t*)out);
+}
+int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen) {
+    wav::Writer w(channels, (uint64_t)samplerate, wav::FORMAT_WAV, (wav::SampleType)sampleType);
+    if (!w.open(path)) { return -1; }
+    for (int i = 0; i < count; i += blockLen) {
+        w.write((float*)samples + (size_t)i * channels, std::min(blockLen, count - i));
+    }
+    w.close();
+    return 0;
 }
 namespace { struct IfChain { dsp::noise_reduction::NoiseBlanker nb; dsp::noise_reduction::Squelch sq; bool nbOn, sqOn; }; }
 void* orc_ifchain_create(int nbOn, double nbRate, double nbLevel, int squelchOn, double squelchLevel) {

@@ -17,6 +17,7 @@
 //   dsp/demod/am.h:109,120                     magnitude
 //   dsp/convert/complex_to_real.h:15, mono_to_stereo.h:13   deinterleave / interleave
 //   dsp/noise_reduction/fm_if.h:51,58-59       window multiply, magnitude, index of the maximum
+//   utils/wav.cpp:161,165                      float -> int16 / int32 PCM
 #pragma once
 #include <complex>
 #include <cstdlib>
@@ -160,6 +161,23 @@ static inline void volk_32f_accumulator_s32f(float* result, const float* in, uns
     float s = 0.0f;
     for (unsigned int i = 0; i < n; i++) { s += in[i]; }
     *result = s;
+}
+// float -> integer PCM as VOLK's generic kernels do it: scale, clamp to the integer type's range, round to nearest even
+// (call site: utils/wav.cpp:161,165)
+static inline void volk_32f_s32f_convert_16i(int16_t* out, const float* in, float scalar, unsigned int n) {
+    const float lo = -32768.0f, hi = 32767.0f;
+    for (unsigned int i = 0; i < n; i++) {
+        float r = in[i] * scalar;
+        if (r > hi) { r = hi; } else if (r < lo) { r = lo; }
+        out[i] = (int16_t)rintf(r);
+    }
+}
+static inline void volk_32f_s32f_convert_32i(int32_t* out, const float* in, float scalar, unsigned int n) {
+    const float lo = -2147483648.0f, hi = 2147483647.0f;   // (float)INT_MAX is 2^31
+    for (unsigned int i = 0; i < n; i++) {
+        float r = in[i] * scalar;
+        if (r >= hi) { out[i] = 2147483647; } else if (r < lo) { out[i] = (int32_t)(-2147483647 - 1); } else { out[i] = (int32_t)rintf(r); }
+    }
 }
 static inline void volk_16i_s32f_convert_32f(float* out, const int16_t* in, float scalar, unsigned int n) {
     for (unsigned int i = 0; i < n; i++) { out[i] = (float)in[i] / scalar; }

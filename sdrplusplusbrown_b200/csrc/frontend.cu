@@ -175,6 +175,26 @@ __global__ void __launch_bounds__(256) conjKernel(const cf32* __restrict__ in, c
 // ------------------------------------------------------------------ front end object
 // int16 I/Q -> cf32: out = (float)in / scalar, the arithmetic of VOLK's generic 16i_s32f_convert_32f
 // (reference call site: source_modules/file_source/src/main.cpp:409, scalar 32768)
+template <int TYPE>
+__global__ void __launch_bounds__(256) toPcmKernel(const float* __restrict__ in, void* __restrict__ out, int n) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const float x = __ldg(in + i);
+        if (TYPE == 0) {
+            // the C conversion float -> uint8_t as x86 compilers emit it: truncate to int, keep the low byte
+            reinterpret_cast<unsigned char*>(out)[i] = (unsigned char)(__float2int_rz(__fadd_rn(__fmul_rn(x, 127.0f), 128.0f)) & 0xff);
+        }
+        else if (TYPE == 1) {
+            float r = __fmul_rn(x, 32767.0f);
+            r = (r > 32767.0f) ? 32767.0f : ((r < -32768.0f) ? -32768.0f : r);
+            reinterpret_cast<short*>(out)[i] = (short)__float2int_rn(r);
+        }
+        else {
+            const float r = __fmul_rn(x, 2147483647.0f);
+            reinterpret_cast<int*>(out)[i] = (r >= 2147483648.0f) ? 2147483647 : ((r < -2147483648.0f) ? (-2147483647 - 1) : __float2int_rn(r));
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) convertI16Kernel(const short2* __restrict__ in, float2* __restrict__ out, int n, float scalar) {
     for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
         const short2 v = __ldg(in + i);
@@ -769,6 +789,24 @@ int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out,
     if (count < 0 || (count > 0 && (!d_in || !d_out)) || !(scalar != 0.0f)) { setError("bad arguments to b200_convert_i16"); return B200_EINVAL; }
     if (count == 0) { return B200_OK; }
     convertI16Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const short2*>(d_in), reinterpret_cast<float2*>(d_out), count, scalar);
+    B200_CHECK_LAUNCH(); countLaunch();
+    return B200_OK;
+}
+
+// wav::Writer::write (utils/wav.cpp:148-178), the recorder's float -> PCM conversion, on the device so that recorded audio or
+// baseband crosses PCIe at its file size: uint8 (x*127)+128 truncated, int16 / int32 as VOLK's generic convert (scale by
+// 32767 / 2147483647, clamp, round to nearest even).
+int b200_convert_pcm(const float* d_in, void* d_out, int n_floats, int sample_type, void* stream) {
+    if (n_floats < 0 || (n_floats > 0 && (!d_in || !d_out))) { setError("bad arguments to b200_convert_pcm"); return B200_EINVAL; }
+    if (sample_type != B200_PCM_UINT8 && sample_type != B200_PCM_INT16 && sample_type != B200_PCM_INT32) {
+        setError("b200_convert_pcm converts to uint8, int16 or int32 (float32 files take the samples as they are)"); return B200_EINVAL;
+    }
+    if (n_floats == 0) { return B200_OK; }
+    const int grid = std::min(148 * 8, (n_floats + 255) / 256);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (sample_type == B200_PCM_UINT8) { toPcmKernel<0><<<grid, 256, 0, s>>>(d_in, d_out, n_floats); }
+    else if (sample_type == B200_PCM_INT16) { toPcmKernel<1><<<grid, 256, 0, s>>>(d_in, d_out, n_floats); }
+    else { toPcmKernel<2><<<grid, 256, 0, s>>>(d_in, d_out, n_floats); }
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }

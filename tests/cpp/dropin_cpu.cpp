@@ -9,6 +9,8 @@
 #include <dsp/routing/splitter.h>
 #include <utils/event.h>
 #include <utils/wav.h>
+#include <stdexcept>
+#include <vector>
 
 #define CHECK(c) do { if (!(c)) { fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); return 1; } } while (0)
 
@@ -203,6 +205,39 @@ int main() {
         wav::Reader missing("/tmp/b200_no_such_file.wav");
         CHECK(!missing.isValid() && missing.error == "cannot open file");
         remove(path);
+    }
+    {   // wav::Writer: container layout (checked byte for byte against the reference's writer by the Python side), the
+        // setters' refusal while a file is open, and a round trip through wav::Reader
+        const char* pf = "/tmp/b200_dropin_writer_f32.wav";
+        const char* pi = "/tmp/b200_dropin_writer_i16.wav";
+        std::vector<float> x(2 * 1000);
+        for (int i = 0; i < 2000; i++) { x[i] = (float)i / 2000.0f - 0.5f; }
+        wav::Writer w(2, 48000, wav::FORMAT_WAV, wav::SAMP_TYPE_FLOAT32);
+        CHECK(w.open(pf));
+        bool threw = false;
+        try { w.setChannels(1); } catch (const std::runtime_error&) { threw = true; }
+        CHECK(threw);
+        w.write(x.data(), 600);
+        w.write(x.data() + 1200, 400);
+        CHECK(w.getSamplesWritten() == 1000);
+        w.close();
+        CHECK(!w.isOpen());
+        w.setSampleType(wav::SAMP_TYPE_INT16);
+        w.setChannels(1);
+        w.setSamplerate(15000);
+        CHECK(w.open(pi));
+        threw = false;
+        try { w.write(x.data(), 10); } catch (const std::runtime_error&) { threw = true; }     // PCM types take device-converted bytes
+        CHECK(threw);
+        const int16_t pcm[5] = { 100, -200, 300, -400, 500 };
+        w.writePcm(pcm, 5);
+        w.close();
+        wav::Reader r(pi);
+        CHECK(r.isValid() && r.getSampleRate() == 15000 && r.getChannelCount() == 1 && r.getBitDepth() == 16 && r.getSampleType() == wav::SAMP_TYPE_INT16);
+        int16_t back[5];
+        CHECK(r.readSamples2(back, sizeof(back)) == sizeof(back) && back[0] == 100 && back[4] == 500);
+        r.close();
+        remove(pi);
     }
     printf("dropin_cpu ok\n");
     return 0;

@@ -74,6 +74,7 @@ _SIGS = {
     "orc_fmif_destroy": (None, [_vp]),
     "orc_fmif_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_volume_process": (_i, [_d, _i, _i, _vp, _vp]),
+    "orc_wav_write": (_i, [C.c_char_p, _i, _d, _i, _vp, _i, _i]),
     "orc_ifchain_create": (_vp, [_i, _d, _d, _i, _d]),
     "orc_ifchain_destroy": (None, [_vp]),
     "orc_ifchain_process": (_i, [_vp, _i, _vp, _vp]),
@@ -336,6 +337,14 @@ class FmIf(_Block):
         out = np.zeros(len(x), np.complex64)
         self.orc.lib.orc_fmif_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
         return out
+
+
+def wav_write(orc, path, channels, samplerate, sample_type, samples, block_len=4096):
+    """wav::Writer: `samples` float32 [count, channels] written as a WAV file of the given sample type (0 u8, 1 i16, 2 i32, 3 f32)"""
+    x = np.ascontiguousarray(samples, np.float32).reshape(-1, channels)
+    rc = orc.lib.orc_wav_write(str(path).encode(), int(channels), float(samplerate), int(sample_type), x.ctypes.data, len(x), int(block_len))
+    if rc != 0:
+        raise RuntimeError("orc_wav_write failed")
 
 
 def volume(orc, vol, muted, x):

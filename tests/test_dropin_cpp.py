@@ -23,6 +23,14 @@ def test_stream_and_block_semantics(tmp_path):
     out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert out.returncode == 0, out.stderr
     assert "dropin_cpu ok" in out.stdout
+    # the float32 file the C++ wav::Writer just wrote, against the oracle's writer on the same samples: same bytes
+    import oracle_lib as ol
+    x = (np.arange(2000, dtype=np.float32) / np.float32(2000.0) - np.float32(0.5)).reshape(1000, 2)
+    x = np.concatenate([x[:600], x[600:1000]])
+    ref = str(tmp_path / "ref_f32.wav")
+    ol.wav_write(ol.Oracle("port"), ref, 2, 48000, 3, x, 600)
+    assert open("/tmp/b200_dropin_writer_f32.wav", "rb").read() == open(ref, "rb").read()
+    os.remove("/tmp/b200_dropin_writer_f32.wav")
 
 
 def test_iq_frontend_header_compiles(tmp_path):

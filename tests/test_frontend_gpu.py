@@ -434,3 +434,29 @@ def test_attached_waterfall_rows_equal_a_separate_push():
     fe.process(to_dev(x[:n]))
     torch.cuda.synchronize()
     assert float(d_zoom.min()) == 7.0          # detached: nothing written
+
+
+@pytest.mark.parametrize("stype,np_type", [(0, np.uint8), (1, np.int16), (2, np.int32)])
+def test_recorder_pcm_conversion_matches_the_reference_writer(stype, np_type, tmp_path):
+    """b200_convert_pcm against wav::Writer::write (utils/wav.cpp:148-178): the converted samples are the bytes of the
+    data chunk the reference's writer produces, bit for bit, including rounding ties and values beyond full scale."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    rng = np.random.default_rng(70 + stype)
+    x = (rng.standard_normal(100003) * 0.4).astype(np.float32)
+    x[:8] = [1.0, -1.0, 0.999999, 0.5 / 32767.0, 1.5 / 32767.0, 2.5 / 32767.0, -0.5 / 32767.0, 0.0]
+    if stype:
+        x[8:12] = [1.7, -3.0, 1.00001, -1.00001]         # clamped; the uint8 path has no clamp and stays in range
+    else:
+        x = np.clip(x, -1.0, 0.99)
+    path = tmp_path / "ref.wav"
+    ol.wav_write(PORT, path, 1, 48000, stype, x, 8192)
+    want = np.frombuffer(open(path, "rb").read()[44:], np_type)
+    d_in = torch.from_numpy(x).cuda()
+    d_out = torch.zeros(len(x), dtype={0: torch.uint8, 1: torch.int16, 2: torch.int32}[stype], device="cuda")
+    assert binding.lib.b200_convert_pcm(d_in.data_ptr(), d_out.data_ptr(), len(x), stype, None) == 0
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy()
+    assert got.dtype == want.dtype and np.array_equal(got, want)
+    assert binding.lib.b200_convert_pcm(d_in.data_ptr(), d_out.data_ptr(), len(x), 3, None) != 0     # float files need no conversion
+    assert binding.lib.b200_convert_pcm(d_in.data_ptr(), d_out.data_ptr(), 0, stype, None) == 0

@@ -306,3 +306,22 @@ def test_wfm_rds_branch_and_volume_port_equals_ref():
             np.allclose(y, au * (0.0 if muted else vol ** 2), rtol=2e-7, atol=0)
         if REF is not None:
             assert ol.volume(REF, vol, muted, au).tobytes() == y.tobytes()
+
+
+@needs_ref
+@pytest.mark.parametrize("stype", [0, 1, 2, 3])
+def test_wav_writer_port_equals_ref_bytewise(stype, tmp_path):
+    """The recorder's file writer (wav::Writer over riff::Writer): the restatement writes the same bytes as the reference's
+    own wav.cpp / riff.cpp for every sample type, mono and stereo, including values that saturate."""
+    rng = np.random.default_rng(40 + stype)
+    for ch in (1, 2):
+        x = (rng.standard_normal((10001, ch)) * 0.4).astype(np.float32)
+        x[5] = 1.0; x[6] = -1.0; x[7] = 0.999999; x[9] = 0.5 / 32767.0; x[10] = 1.5 / 32767.0; x[11] = 2.5 / 32767.0
+        if stype in (1, 2):
+            x[8] = 1.7; x[12] = -3.0           # beyond full scale: clamped (the uint8 path has no clamp and is left in range)
+        a, b = tmp_path / ("p%d.wav" % ch), tmp_path / ("r%d.wav" % ch)
+        ol.wav_write(PORT, a, ch, 48000, stype, x, 4096)
+        ol.wav_write(REF, b, ch, 48000, stype, x, 4096)
+        pa, pb = open(a, "rb").read(), open(b, "rb").read()
+        assert len(pa) == 44 + len(x) * ch * (1 if stype == 0 else 2 if stype == 1 else 4)
+        assert pa == pb, (stype, ch)
