@@ -285,6 +285,17 @@ int b200_convert_i16(const int16_t* d_in, int count, float scalar, float* d_out,
  * WAV file's sample type, bit for bit as the reference's writer converts them (uint8: (x*127)+128 truncated; int16 / int32:
  * volk_32f_s32f_convert_16i / _32i with 32767 / 2147483647).  Recorded data then crosses PCIe at its file size; the RIFF
  * container is host code (wav::Writer in include/utils/wav.h takes the converted bytes). */
+/* The SDR++ server's sample packet, built on the device (dsp::compression::SampleStreamCompressor::process,
+ * core/src/dsp/compression/sample_stream_compressor.h:30-62; sent by core/src/server.cpp:444-459): d_out receives
+ * [u16 0][u16 pcm_type][f32 scaler][data], scaler = the largest float of the block (signed, as volk_32f_index_max_32u picks
+ * it; NaN samples are passed over), data = int8 (x * 128/scaler) or int16 (x * 32768/scaler) clamped and rounded to nearest
+ * even, or the floats themselves.  d_out must hold 8 + count * {2, 4, 8} bytes and be 8-byte aligned; the return value is
+ * the packet's byte count (negative = error).  The receiving side is b200_frontend_process_host_i8 / _i16 with
+ * scalar = 128 / scaler resp. 32768 / scaler (sample_stream_decompressor.h:24-32). */
+#define B200_STREAM_PCM_I8 0
+#define B200_STREAM_PCM_I16 1
+#define B200_STREAM_PCM_F32 2
+int b200_stream_compress(const float* d_in, int count, int pcm_type, void* d_out, void* stream);
 #define B200_PCM_UINT8 0
 #define B200_PCM_INT16 1
 #define B200_PCM_INT32 2

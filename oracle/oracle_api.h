@@ -111,6 +111,11 @@ void orc_fmif_destroy(void* h);
 int orc_fmif_process(void* h, int count, const float* in, float* out);
 // dsp::audio::Volume (audio/volume.h:13-50), the sink stream's volume block (signal_path/sink.h:73): gain = volume^2 in float, 0 when muted
 int orc_volume_process(double volume, int muted, int count, const float* inStereo, float* outStereo);
+// dsp::compression::SampleStreamCompressor::process (compression/sample_stream_compressor.h:30-62), the SDR++ server's
+// sample packet: [u16 0][u16 pcmType][f32 scaler][data]; pcmType 0 int8, 1 int16, 2 float32; scaler = the largest float of
+// the block (signed, first of equals).  Returns the byte count.  And SampleStreamDecompressor::process (:14-35).
+int orc_stream_compress(int count, int pcmType, const float* in, unsigned char* out);
+int orc_stream_decompress(int nbytes, const unsigned char* in, float* out);
 // wav::Writer (utils/wav.cpp:20-182 over riff::Writer, utils/riff.cpp): the recorder's file writer (misc_modules/recorder/src/main.cpp:168-177,528-558).
 // Writes `count` samples of `channels` floats each in blocks of blockLen samples; sampleType 0 UINT8, 1 INT16, 2 INT32, 3 FLOAT32.  Returns 0 when written.
 int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen);

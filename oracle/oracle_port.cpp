@@ -884,6 +884,57 @@ int orc_volume_process(double volume, int muted, int count, const float* in, flo
 // chunk (codec 1 PCM / 3 float, channels, rate, bytes per second, bytes per frame, bit depth), then one "data" chunk; chunk
 // sizes are patched in when the chunks end.  Conversions: uint8 (x*127)+128 truncated, int16 / int32 by VOLK's generic
 // convert (scale by 32767 / 2147483647, clamp, round to nearest even), float32 as is.
+// SampleStreamCompressor / SampleStreamDecompressor (compression/sample_stream_compressor.h:30-62, _decompressor.h:14-35)
+int orc_stream_compress(int count, int pcmType, const float* in, unsigned char* out) {
+    uint16_t z = 0, t = (uint16_t)pcmType;
+    memcpy(out, &z, 2); memcpy(out + 2, &t, 2);
+    if (pcmType == 2) {
+        const float zero = 0.0f;
+        memcpy(out + 4, &zero, 4);
+        memcpy(out + 8, in, (size_t)count * 8);
+        return 8 + count * 8;
+    }
+    float maxVal = 1.0f;
+    if (count > 0) {                                   // generic volk_32f_index_max_32u: strict >, first of equals
+        maxVal = in[0];
+        for (int i = 1; i < 2 * count; i++) { if (in[i] > maxVal) { maxVal = in[i]; } }
+    }
+    memcpy(out + 4, &maxVal, 4);
+    if (pcmType == 0) {
+        const float sc = 128.0f / maxVal;
+        int8_t* d = (int8_t*)(out + 8);
+        for (int i = 0; i < 2 * count; i++) {
+            float r = in[i] * sc;
+            if (r > 127.0f) { r = 127.0f; } else if (r < -128.0f) { r = -128.0f; }
+            d[i] = (int8_t)rintf(r);
+        }
+        return 8 + count * 2;
+    }
+    const float sc = 32768.0f / maxVal;
+    int16_t* d = (int16_t*)(out + 8);
+    for (int i = 0; i < 2 * count; i++) {
+        float r = in[i] * sc;
+        if (r > 32767.0f) { r = 32767.0f; } else if (r < -32768.0f) { r = -32768.0f; }
+        d[i] = (int16_t)rintf(r);
+    }
+    return 8 + count * 4;
+}
+int orc_stream_decompress(int nbytes, const unsigned char* in, float* out) {
+    uint16_t t; float scaler;
+    memcpy(&t, in + 2, 2); memcpy(&scaler, in + 4, 4);
+    if (t == 2) { memcpy(out, in + 8, (size_t)nbytes - 8); return (nbytes - 8) / 8; }
+    if (t == 1) {
+        const int n = (nbytes - 8) / 4; const float sc = 32768.0f / scaler; const int16_t* d = (const int16_t*)(in + 8);
+        for (int i = 0; i < 2 * n; i++) { out[i] = (float)d[i] / sc; }
+        return n;
+    }
+    if (t == 0) {
+        const int n = (nbytes - 8) / 2; const float sc = 128.0f / scaler; const int8_t* d = (const int8_t*)(in + 8);
+        for (int i = 0; i < 2 * n; i++) { out[i] = (float)d[i] / sc; }
+        return n;
+    }
+    return 0;
+}
 int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen) {
     FILE* f = fopen(path, "wb");
     if (!f) { return -1; }

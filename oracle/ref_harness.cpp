@@ -50,6 +50,8 @@
 #include <dsp/noise_reduction/fm_if.h>
 #include <dsp/audio/volume.h>
 #include <utils/wav.h>
+#include <dsp/compression/sample_stream_compressor.h>
+#include <dsp/compression/sample_stream_decompressor.h>
 #undef protected
 #undef private
 
@@ -294,6 +296,12 @@ int orc_volume_process(double volume, int muted, int count, const float* in, flo
     dsp::audio::Volume v;
     v.init(NULL, volume, muted != 0);
     return v.process(count, (const stereo_t*)in, (stereo_t*)out);
+}
+int orc_stream_compress(int count, int pcmType, const float* in, unsigned char* out) {
+    return dsp::compression::SampleStreamCompressor::process(count, (dsp::compression::PCMType)pcmType, (const complex_t*)in, out);
+}
+int orc_stream_decompress(int nbytes, const unsigned char* in, float* out) {
+    return dsp::compression::SampleStreamDecompressor::process(nbytes, in, (complex_t*)out);
 }
 int orc_wav_write(const char* path, int channels, double samplerate, int sampleType, const float* samples, int count, int blockLen) {
     wav::Writer w(channels, (uint64_t)samplerate, wav::FORMAT_WAV, (wav::SampleType)sampleType);

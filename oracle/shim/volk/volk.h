@@ -18,6 +18,7 @@
 //   dsp/convert/complex_to_real.h:15, mono_to_stereo.h:13   deinterleave / interleave
 //   dsp/noise_reduction/fm_if.h:51,58-59       window multiply, magnitude, index of the maximum
 //   utils/wav.cpp:161,165                      float -> int16 / int32 PCM
+//   dsp/compression/sample_stream_compressor.h:47-59, sample_stream_decompressor.h:24-32   server stream PCM
 #pragma once
 #include <complex>
 #include <cstdlib>
@@ -171,6 +172,17 @@ static inline void volk_32f_s32f_convert_16i(int16_t* out, const float* in, floa
         if (r > hi) { r = hi; } else if (r < lo) { r = lo; }
         out[i] = (int16_t)rintf(r);
     }
+}
+static inline void volk_32f_s32f_convert_8i(int8_t* out, const float* in, float scalar, unsigned int n) {
+    const float lo = -128.0f, hi = 127.0f;
+    for (unsigned int i = 0; i < n; i++) {
+        float r = in[i] * scalar;
+        if (r > hi) { r = hi; } else if (r < lo) { r = lo; }
+        out[i] = (int8_t)rintf(r);
+    }
+}
+static inline void volk_8i_s32f_convert_32f(float* out, const int8_t* in, float scalar, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = (float)in[i] / scalar; }
 }
 static inline void volk_32f_s32f_convert_32i(int32_t* out, const float* in, float scalar, unsigned int n) {
     const float lo = -2147483648.0f, hi = 2147483647.0f;   // (float)INT_MAX is 2^31

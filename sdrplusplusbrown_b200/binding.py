@@ -61,6 +61,7 @@ _SIGS = {
     "b200_vfo_audio_ptr": (_vp, [_vp, _i]),
     "b200_vfo_audio_count": (_i, [_vp, _i]),
     "b200_vfo_audio_max_out": (_i, [_vp, _i, _i]),
+    "b200_stream_compress": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_convert_pcm": (_i, [_vp, _vp, _i, _i, _vp]),
     "b200_frontend_create": (_i, [_pp, _d, _i, _i, _i, _i, _d, _i, _i, _i]),
     "b200_frontend_destroy": (_i, [_vp]),

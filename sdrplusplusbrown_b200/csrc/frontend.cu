@@ -175,6 +175,47 @@ __global__ void __launch_bounds__(256) conjKernel(const cf32* __restrict__ in, c
 // ------------------------------------------------------------------ front end object
 // int16 I/Q -> cf32: out = (float)in / scalar, the arithmetic of VOLK's generic 16i_s32f_convert_32f
 // (reference call site: source_modules/file_source/src/main.cpp:409, scalar 32768)
+// ---- the SDR++ server's sample packet (dsp/compression/sample_stream_compressor.h:30-62): [u16 0][u16 pcmType][f32 scaler][data]
+__global__ void streamHeaderKernel(unsigned char* out, int pcmType, float scaler) {
+    reinterpret_cast<unsigned short*>(out)[0] = 0;
+    reinterpret_cast<unsigned short*>(out)[1] = (unsigned short)pcmType;
+    reinterpret_cast<float*>(out)[1] = scaler;
+}
+// largest float of the block (signed), into the packet's scaler slot.  The slot starts at -inf; a non-negative candidate
+// goes in by a signed-integer max of its bit pattern, a negative one by an unsigned min (IEEE order within each sign).
+__global__ void __launch_bounds__(256) streamMaxKernel(const float2* __restrict__ in, int count, float* slot) {
+    float m = -INFINITY;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < count; i += gridDim.x * 256) {
+        const float2 v = __ldg(in + i);
+        m = fmaxf(m, fmaxf(v.x, v.y));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o)); }
+    __shared__ float sm[8];
+    if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5] = m; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int w = 1; w < 8; w++) { m = fmaxf(m, sm[w]); }
+        if (m >= 0.0f) { atomicMax(reinterpret_cast<int*>(slot), __float_as_int(m)); }
+        else { atomicMin(reinterpret_cast<unsigned int*>(slot), __float_as_uint(m)); }
+    }
+}
+// volk_32f_s32f_convert_8i / _16i (generic): scale, clamp, round to nearest even
+template <int TYPE>
+__global__ void __launch_bounds__(256) streamConvertKernel(const float2* __restrict__ in, int count, const float* __restrict__ slot, void* __restrict__ data) {
+    const float scale = __fdiv_rn(TYPE == 0 ? 128.0f : 32768.0f, *slot);
+    const float hi = TYPE == 0 ? 127.0f : 32767.0f, lo = TYPE == 0 ? -128.0f : -32768.0f;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < count; i += gridDim.x * 256) {
+        const float2 v = __ldg(in + i);
+        float a = __fmul_rn(v.x, scale), b = __fmul_rn(v.y, scale);
+        a = (a > hi) ? hi : ((a < lo) ? lo : a);
+        b = (b > hi) ? hi : ((b < lo) ? lo : b);
+        if (TYPE == 0) { reinterpret_cast<char2*>(data)[i] = make_char2((signed char)__float2int_rn(a), (signed char)__float2int_rn(b)); }
+        else { reinterpret_cast<short2*>(data)[i] = make_short2((short)__float2int_rn(a), (short)__float2int_rn(b)); }
+    }
+}
+
 template <int TYPE>
 __global__ void __launch_bounds__(256) toPcmKernel(const float* __restrict__ in, void* __restrict__ out, int n) {
     for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
@@ -809,6 +850,34 @@ int b200_convert_pcm(const float* d_in, void* d_out, int n_floats, int sample_ty
     else { toPcmKernel<2><<<grid, 256, 0, s>>>(d_in, d_out, n_floats); }
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
+}
+
+// SampleStreamCompressor::process (compression/sample_stream_compressor.h:30-62) on the device: the server's sample packet is
+// built in d_out (8 + count * {2, 4, 8} bytes for int8 / int16 / float32), ready for one D2H copy at its wire size.
+int b200_stream_compress(const float* d_in, int count, int pcm_type, void* d_out, void* stream) {
+    if (count < 0 || !d_out || (count > 0 && !d_in) || pcm_type < B200_STREAM_PCM_I8 || pcm_type > B200_STREAM_PCM_F32) {
+        setError("bad arguments to b200_stream_compress"); return B200_EINVAL;
+    }
+    if (count > (1 << 28) - 1) { setError("block of %d samples is too long for one packet", count); return B200_ETOOBIG; }
+    cudaStream_t s = (cudaStream_t)stream;
+    unsigned char* out = (unsigned char*)d_out;
+    if (pcm_type == B200_STREAM_PCM_F32) {
+        streamHeaderKernel<<<1, 1, 0, s>>>(out, pcm_type, 0.0f);
+        B200_CHECK_LAUNCH(); countLaunch();
+        if (count > 0) { B200_CUDA(cudaMemcpyAsync(out + 8, d_in, (size_t)count * 8, cudaMemcpyDeviceToDevice, s)); }
+        return 8 + count * 8;
+    }
+    // `maxVal = count == 0 ? 1.0 : in[maxIdx]` (:48-50)
+    streamHeaderKernel<<<1, 1, 0, s>>>(out, pcm_type, count == 0 ? 1.0f : -INFINITY);
+    B200_CHECK_LAUNCH(); countLaunch();
+    if (count == 0) { return 8; }
+    const int grid = std::min(148 * 8, (count + 255) / 256);
+    streamMaxKernel<<<grid, 256, 0, s>>>(reinterpret_cast<const float2*>(d_in), count, reinterpret_cast<float*>(out) + 1);
+    B200_CHECK_LAUNCH();
+    if (pcm_type == B200_STREAM_PCM_I8) { streamConvertKernel<0><<<grid, 256, 0, s>>>(reinterpret_cast<const float2*>(d_in), count, reinterpret_cast<const float*>(out) + 1, out + 8); }
+    else { streamConvertKernel<1><<<grid, 256, 0, s>>>(reinterpret_cast<const float2*>(d_in), count, reinterpret_cast<const float*>(out) + 1, out + 8); }
+    B200_CHECK_LAUNCH(); countLaunch(2);
+    return 8 + count * (pcm_type == B200_STREAM_PCM_I8 ? 2 : 4);
 }
 
 // complex spectrum of one already-windowed frame (tests of the FFT alone)

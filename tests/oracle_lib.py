@@ -74,6 +74,8 @@ _SIGS = {
     "orc_fmif_destroy": (None, [_vp]),
     "orc_fmif_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_volume_process": (_i, [_d, _i, _i, _vp, _vp]),
+    "orc_stream_compress": (_i, [_i, _i, _vp, _vp]),
+    "orc_stream_decompress": (_i, [_i, _vp, _vp]),
     "orc_wav_write": (_i, [C.c_char_p, _i, _d, _i, _vp, _i, _i]),
     "orc_ifchain_create": (_vp, [_i, _d, _d, _i, _d]),
     "orc_ifchain_destroy": (None, [_vp]),
@@ -337,6 +339,21 @@ class FmIf(_Block):
         out = np.zeros(len(x), np.complex64)
         self.orc.lib.orc_fmif_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
         return out
+
+
+def stream_compress(orc, x, pcm_type):
+    """SampleStreamCompressor::process: complex64 block -> the server's sample packet bytes"""
+    x = np.ascontiguousarray(x, np.complex64)
+    out = np.zeros(8 + 8 * len(x), np.uint8)
+    n = orc.lib.orc_stream_compress(len(x), int(pcm_type), x.ctypes.data, out.ctypes.data)
+    return out[:n].copy()
+
+
+def stream_decompress(orc, pkt):
+    pkt = np.ascontiguousarray(pkt, np.uint8)
+    out = np.zeros(len(pkt), np.complex64)
+    n = orc.lib.orc_stream_decompress(len(pkt), pkt.ctypes.data, out.ctypes.data)
+    return out[:n].copy()
 
 
 def wav_write(orc, path, channels, samplerate, sample_type, samples, block_len=4096):

@@ -460,3 +460,39 @@ def test_recorder_pcm_conversion_matches_the_reference_writer(stype, np_type, tm
     assert got.dtype == want.dtype and np.array_equal(got, want)
     assert binding.lib.b200_convert_pcm(d_in.data_ptr(), d_out.data_ptr(), len(x), 3, None) != 0     # float files need no conversion
     assert binding.lib.b200_convert_pcm(d_in.data_ptr(), d_out.data_ptr(), 0, stype, None) == 0
+
+
+@pytest.mark.parametrize("pcm", [0, 1, 2])
+def test_server_sample_packet_matches_the_reference_compressor(pcm):
+    """b200_stream_compress against SampleStreamCompressor::process: same packet bytes (header, scaler, payload) for a noisy
+    block, an all-negative block, a one-sample block and an empty one; and the packet fed back through the int16 / int8
+    ingest of the front end gives what SampleStreamDecompressor gives."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    rng = np.random.default_rng(90 + pcm)
+    blocks = [((rng.standard_normal(300001) + 1j * rng.standard_normal(300001)) * 0.3).astype(np.complex64),
+              (-(np.abs(rng.standard_normal(4097)) + 0.1) * (1 + 0.5j)).astype(np.complex64),
+              np.array([0.3 - 0.7j], np.complex64), np.zeros(0, np.complex64)]
+    for x in blocks:
+        want = ol.stream_compress(PORT, x, pcm)
+        d_in = torch.from_numpy(x.view(np.float32).copy()).cuda() if len(x) else torch.zeros(2, device="cuda")
+        d_out = torch.zeros(8 + 8 * max(len(x), 1), dtype=torch.uint8, device="cuda")
+        n = binding.lib.b200_stream_compress(d_in.data_ptr(), len(x), pcm, d_out.data_ptr(), None)
+        torch.cuda.synchronize()
+        assert n == len(want)
+        got = d_out.cpu().numpy()[:n]
+        assert np.array_equal(got, want), (pcm, len(x))
+    assert binding.lib.b200_stream_compress(0, 5, pcm, 0, None) < 0
+    if pcm < 2:
+        # receiving side: header read on the host, payload through the integer ingest
+        x = blocks[0][:65536]
+        pkt = ol.stream_compress(PORT, x, pcm)
+        scaler = pkt[4:8].view(np.float32)[0]
+        ref = ol.stream_decompress(PORT, pkt)
+        fe = binding.FrontEnd(2.4e6, fft_size=8192, fft_rate=20.0, fft_window=2, max_block=65536, device=0)
+        v = fe.vfos.add(2.4e6, 2.4e6, 0.0)             # no translation, no resampling: the VFO hands the ingested block through
+        payload = pkt[8:].view(np.int8 if pcm == 0 else np.int16).reshape(-1, 2)
+        kw = dict(i8_scalar=float(np.float32(128.0) / scaler)) if pcm == 0 else dict(i16_scalar=float(np.float32(32768.0) / scaler))
+        res = fe.process_host(payload, vfos=(v,), **kw)
+        got = res["vfo"][v] if isinstance(res, dict) and "vfo" in res else res[1][v]
+        assert err_db(got, ref) <= -120.0

@@ -325,3 +325,31 @@ def test_wav_writer_port_equals_ref_bytewise(stype, tmp_path):
         pa, pb = open(a, "rb").read(), open(b, "rb").read()
         assert len(pa) == 44 + len(x) * ch * (1 if stype == 0 else 2 if stype == 1 else 4)
         assert pa == pb, (stype, ch)
+
+
+@needs_ref
+def test_server_sample_packets_port_equals_ref():
+    """The SDR++ server's sample packets (SampleStreamCompressor / SampleStreamDecompressor): restatement against the
+    reference's headers byte for byte, for int8, int16 and float32 payloads, an empty block and a block of negatives."""
+    rng = np.random.default_rng(55)
+    blocks = [((rng.standard_normal(5000) + 1j * rng.standard_normal(5000)) * 0.3).astype(np.complex64),
+              np.zeros(0, np.complex64),
+              (-(np.abs(rng.standard_normal(300)) + 0.1) * (1 + 1j)).astype(np.complex64),
+              np.concatenate([np.full(64, 0.25 + 0.25j), np.full(8, 0.1 - 0.05j)]).astype(np.complex64)]
+    for x in blocks:
+        for t in (0, 1, 2):
+            p, r = ol.stream_compress(PORT, x, t), ol.stream_compress(REF, x, t)
+            assert p.tobytes() == r.tobytes(), (len(x), t)
+            assert len(p) == 8 + len(x) * (2, 4, 8)[t]
+            if len(x):
+                dp, dr = ol.stream_decompress(PORT, p), ol.stream_decompress(REF, p)
+                assert dp.tobytes() == dr.tobytes() and len(dp) == len(x)
+                if t == 2:
+                    assert np.array_equal(dp, x)
+                elif x.real.max() > 0:
+                    # the scaler is the largest SIGNED value: what lies within +-scaler comes back to one step, the rest clips
+                    xf, df = x.view(np.float32), dp.view(np.float32)
+                    mx = xf.max()
+                    step = mx / (128.0 if t == 0 else 32768.0)
+                    inside = np.abs(xf) <= mx * (1 - 2.0 / 128)
+                    assert inside.any() and np.max(np.abs(df[inside] - xf[inside])) <= 1.01 * step
