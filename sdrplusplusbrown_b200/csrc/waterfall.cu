@@ -48,6 +48,51 @@ __global__ void __launch_bounds__(256) zoomPaletteKernel(const float* __restrict
     }
 }
 
+// The same reduction for views whose pixels cover a few bins to a few hundred: a CTA takes kZoomPx adjacent pixels of one
+// row, brings the stretch of the dB row they cover into shared memory with coalesced 16-byte loads (a quarter of the load
+// instructions of the per-pixel walk above, every sector used once), and four lanes per pixel fold their bins from there.
+// tileLo / tileHi: first (rounded down to 4) and one-past-last bin of every pixel tile, from the host's zoom table.
+constexpr int kZoomPx = 64;
+constexpr int kZoomSpanCap = 12288;      // floats of shared memory per CTA (48 KB)
+__global__ void __launch_bounds__(256) zoomTileKernel(const float* __restrict__ rows, int rawSize, int width, const int* __restrict__ sid,
+                                                      const int* __restrict__ uf, const int* __restrict__ tileLo, const int* __restrict__ tileHi,
+                                                      float wfMin, float wfMax, const uint32_t* __restrict__ lut,
+                                                      float* __restrict__ zoom, uint32_t* __restrict__ rgba,
+                                                      int ringHeight, int ringBase, int liveRows) {
+    extern __shared__ __align__(16) float sRow[];
+    const int p0 = blockIdx.x * kZoomPx;
+    const int pix = p0 + (threadIdx.x >> 2), sub = threadIdx.x & 3;
+    const bool live = pix < width;
+    if ((int)blockIdx.y >= liveRows) {
+        if (live && sub == 0 && rgba) { rgba[(size_t)blockIdx.y * width + pix] = 0xFF000000u; }
+        return;
+    }
+    const int srcRow = ringHeight > 0 ? (int)((ringBase + blockIdx.y) % ringHeight) : (int)blockIdx.y;
+    const float* row = rows + (size_t)srcRow * rawSize;
+    const int lo = __ldg(tileLo + blockIdx.x), hi = __ldg(tileHi + blockIdx.x);
+    const int n4 = (hi - lo + 3) >> 2;
+    const float4* src = reinterpret_cast<const float4*>(row + lo);
+    for (int k = threadIdx.x; k < n4; k += 256) {
+        // rawSize is a multiple of 4 and lo is too: a float4 lies inside the row or wholly past its end
+        reinterpret_cast<float4*>(sRow)[k] = (lo + 4 * k < rawSize) ? __ldg(src + k) : make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    }
+    __syncthreads();
+    const int i = live ? pix : width - 1;
+    const int s = __ldg(sid + i) - lo, n = live ? __ldg(uf + i) : 0;
+    float m = -INFINITY;
+    for (int j = sub; j < n; j += 4) { m = fmaxf(m, sRow[s + j]); }
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+    if (!live || sub != 0) { return; }
+    if (zoom) { zoom[(size_t)blockIdx.y * width + i] = m; }
+    if (rgba) {
+        const float range = wfMax - wfMin;
+        const float px = (fminf(fmaxf(m, wfMin), wfMax) - wfMin) / range;
+        const int id = (int)(px * 999.0f);
+        rgba[(size_t)blockIdx.y * width + i] = __ldg(lut + id);
+    }
+}
+
 // WaterFall::getFFTBuffer (waterfall.cpp:1188-1199) for a batch: pushed row r (oldest first) becomes history line
 // (cur0 - 1 - r) mod height -- the line index steps DOWN with every new row, so ascending lines run newest to oldest.
 __global__ void __launch_bounds__(256) storeRawKernel(const float* __restrict__ rows, int firstRow, int rawSize, float* __restrict__ ring, int height, int cur0) {
@@ -148,6 +193,7 @@ struct b200_waterfall {
     float* dSmooth = nullptr; float* dHold = nullptr;     // smoothingBuf / latestFFTHold, both start at -1000 (waterfall.cpp:1073,1090)
     bool tableDirty = true;
     int maxUf = 1;            // widest pixel (bins), picks the lanes-per-pixel of the zoom kernel
+    std::vector<int> tileLo, tileHi; int* dTileLo = nullptr; int* dTileHi = nullptr; int tileSpan = 0;   // zoomTileKernel geometry (tileSpan 0 = not usable)
     // raw dB history (WaterFall::rawFFTs / currentFFTLine / fftLines, waterfall.cpp:1188-1199)
     float* dRaw = nullptr; int height = 0, currentLine = 0, lines = 0;
 };
@@ -185,7 +231,7 @@ int b200_waterfall_create(b200_waterfall** out, int raw_fft_size, int data_width
 int b200_waterfall_destroy(b200_waterfall* wf) {
     if (!wf) { setError("NULL waterfall handle"); return B200_EINVAL; }
     DeviceGuard g(wf->device);
-    cudaFree(wf->dSid); cudaFree(wf->dUf); cudaFree(wf->dLut); cudaFree(wf->dSmooth); cudaFree(wf->dHold);
+    cudaFree(wf->dSid); cudaFree(wf->dUf); cudaFree(wf->dTileLo); cudaFree(wf->dTileHi); cudaFree(wf->dLut); cudaFree(wf->dSmooth); cudaFree(wf->dHold);
     if (wf->dRaw) { cudaFree(wf->dRaw); }
     delete wf;
     return B200_OK;
@@ -229,6 +275,17 @@ int b200_waterfall_make_palette(const float* colors_rgb, int color_count, uint32
     return B200_OK;
 }
 
+static int launchZoomTiles(b200_waterfall* wf, const float* rows, float* d_zoom, uint32_t* d_rgba, int outRows, int ringHeight, int ringBase, int liveRows, cudaStream_t s) {
+    const size_t smem = (size_t)wf->tileSpan * sizeof(float);
+    static bool attr = false;
+    if (!attr) { B200_CUDA(cudaFuncSetAttribute(zoomTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kZoomSpanCap * sizeof(float) + 64))); attr = true; }
+    dim3 grid((unsigned)((wf->width + kZoomPx - 1) / kZoomPx), (unsigned)outRows);
+    zoomTileKernel<<<grid, 256, smem, s>>>(rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->dTileLo, wf->dTileHi, wf->wfMin, wf->wfMax, wf->dLut,
+                                            d_zoom, d_rgba, ringHeight, ringBase, liveRows);
+    B200_CHECK_LAUNCH();
+    return B200_OK;
+}
+
 static int refreshTable(b200_waterfall* wf) {
     if (!wf->tableDirty) { return B200_OK; }
     design::zoomTable(wf->viewOffset, wf->viewWidth, wf->rawSize, wf->width, wf->sid, wf->uf);
@@ -242,6 +299,31 @@ static int refreshTable(b200_waterfall* wf) {
     for (int i = 0; i < wf->width; i++) { wf->maxUf = std::max(wf->maxUf, wf->uf[i]); }
     B200_CUDA(cudaMemcpy(wf->dSid, wf->sid.data(), wf->width * sizeof(int), cudaMemcpyHostToDevice));
     B200_CUDA(cudaMemcpy(wf->dUf, wf->uf.data(), wf->width * sizeof(int), cudaMemcpyHostToDevice));
+    // pixel tiles of the shared-memory kernel: usable when every tile's stretch of the row fits its buffer
+    const int nTiles = (wf->width + kZoomPx - 1) / kZoomPx;
+    wf->tileLo.assign(nTiles, 0); wf->tileHi.assign(nTiles, 0);
+    wf->tileSpan = 0;
+    bool usable = (wf->rawSize & 3) == 0;
+    for (int t = 0; t < nTiles && usable; t++) {
+        int lo = wf->rawSize, hi = 0;
+        for (int i = t * kZoomPx; i < std::min(wf->width, (t + 1) * kZoomPx); i++) {
+            if (wf->uf[i] <= 0) { continue; }
+            lo = std::min(lo, wf->sid[i]); hi = std::max(hi, wf->sid[i] + wf->uf[i]);
+        }
+        if (hi <= lo) { lo = 0; hi = 0; }
+        lo &= ~3;
+        wf->tileLo[t] = lo; wf->tileHi[t] = hi;
+        wf->tileSpan = std::max(wf->tileSpan, ((hi - lo + 3) & ~3) + 4);
+        if (wf->tileSpan > kZoomSpanCap) { usable = false; }
+    }
+    if (!usable) { wf->tileSpan = 0; }
+    if (!wf->dTileLo) {
+        const int cap = (wf->width + kZoomPx - 1) / kZoomPx;
+        B200_CUDA(cudaMalloc((void**)&wf->dTileLo, cap * sizeof(int)));
+        B200_CUDA(cudaMalloc((void**)&wf->dTileHi, cap * sizeof(int)));
+    }
+    B200_CUDA(cudaMemcpy(wf->dTileLo, wf->tileLo.data(), nTiles * sizeof(int), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(wf->dTileHi, wf->tileHi.data(), nTiles * sizeof(int), cudaMemcpyHostToDevice));
     wf->tableDirty = false;
     return B200_OK;
 }
@@ -255,9 +337,14 @@ int b200_waterfall_push(b200_waterfall* wf, const float* d_rows, int nrows, floa
     while (logG < 5 && (8 << logG) < wf->maxUf) { logG++; }          // up to eight bins per lane before adding lanes
     dim3 grid((unsigned)((((size_t)wf->width << logG) + 255) / 256), nrows);
     if (d_zoom || d_rgba) {
-        zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
-                                                                  logG, 0, 0, nrows);
-        B200_CHECK_LAUNCH();
+        if (wf->tileSpan > 0 && (((uintptr_t)d_rows) & 15) == 0) {
+            B200_TRY(launchZoomTiles(wf, d_rows, d_zoom, d_rgba, nrows, 0, 0, nrows, (cudaStream_t)stream));
+        }
+        else {
+            zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
+                                                                      logG, 0, 0, nrows);
+            B200_CHECK_LAUNCH();
+        }
         countLaunch();
     }
     if (wf->dRaw) {
@@ -296,9 +383,14 @@ int b200_waterfall_regenerate(b200_waterfall* wf, float* d_zoom, uint32_t* d_rgb
     int logG = 0;
     while (logG < 5 && (8 << logG) < wf->maxUf) { logG++; }
     dim3 grid((unsigned)((((size_t)wf->width << logG) + 255) / 256), wf->height);
-    zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(wf->dRaw, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
-                                                              logG, wf->height, wf->currentLine, wf->lines);
-    B200_CHECK_LAUNCH();
+    if (wf->tileSpan > 0) {
+        B200_TRY(launchZoomTiles(wf, wf->dRaw, d_zoom, d_rgba, wf->height, wf->height, wf->currentLine, wf->lines, (cudaStream_t)stream));
+    }
+    else {
+        zoomPaletteKernel<<<grid, 256, 0, (cudaStream_t)stream>>>(wf->dRaw, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->wfMin, wf->wfMax, wf->dLut, d_zoom, d_rgba,
+                                                                  logG, wf->height, wf->currentLine, wf->lines);
+        B200_CHECK_LAUNCH();
+    }
     countLaunch();
     return wf->lines;
 }
