@@ -345,6 +345,25 @@ def run_gpu(args):
                       "note": "step + USB SSB demodulator (xlate, real part, AGC walk) on the VFO output"}
         fe.vfos.set_demod(v, binding.DEMOD_NONE)
 
+    # ---- the dominant kernel by itself: the same VFO bank on the same resident block, run without the FFT branch and with
+    # its later stages inline, so that nothing shares the SMs with the full-rate kernel (reported beside the in-step figure)
+    barrier()
+    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 0)
+    b0 = bufs[0]
+    with torch.cuda.stream(compute):
+        for _ in range(3):
+            fe.vfos.process(b0, B, stream=compute)
+    barrier()
+    binding.profile_enable(True)
+    binding.profile_read()
+    with torch.cuda.stream(compute):
+        for _ in range(20):
+            fe.vfos.process(b0, B, stream=compute)
+    barrier()
+    kms_alone, kl_alone, kb_alone = binding.profile_read()
+    binding.profile_enable(False)
+    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if args.defer_tail else 0)
+
     # ---- end to end through the host-buffer C-ABI call (H2D of the block + D2H of frames, VFO IQ and audio inside)
     Be = args.e2e_batch
     fe2 = binding.FrontEnd(sr, fft_size=cfg["fft_size"], fft_rate=cfg["fft_rate"], fft_window=cfg["window"], max_block=Be, device=local)
@@ -424,6 +443,10 @@ def run_gpu(args):
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
                          "peak_source": which, "traffic": _traffic(), "launches": int(klaunches), "avg_launch_ms": kms / klaunches if klaunches else None,
                          "algorithmic_bytes_per_launch": kbytes / klaunches if klaunches else None,
+                         "kernel_alone": {"achieved": (kb_alone / 1e9) / (kms_alone * 1e-3) if kms_alone > 0 else None,
+                                          "frac": ((kb_alone / 1e9) / (kms_alone * 1e-3)) / peak if (kms_alone > 0 and peak) else None,
+                                          "avg_launch_ms": kms_alone / kl_alone if kl_alone else None, "launches": int(kl_alone),
+                                          "note": "same kernel, same resident block, measured in this run with CUDA events: the VFO bank alone (no FFT branch, later stages inline), so nothing shares the SMs with it; `achieved` / `frac` above are its figures inside the timed step, where the FFT passes and the previous block's tail run beside it"},
                          "share_of_step": (kms / ms) if ms else None},
         }
         if with_demod is not None:
