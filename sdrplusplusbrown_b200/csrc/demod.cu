@@ -1038,13 +1038,11 @@ static int afConfigure(VfoBank& bank, Vfo& v, double audioSR, double tau) {
 constexpr size_t kSoloSmemBytes = 180 * 1024;
 constexpr size_t kSoloMaxJobs = 24;
 static size_t soloSmem(size_t nJobs) {
-    static bool attr = false;
-    if (!attr) {
-        cudaFuncSetAttribute(agcWalkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
-        cudaFuncSetAttribute(pllKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
-        attr = true;
-    }
-    return nJobs <= kSoloMaxJobs ? kSoloSmemBytes : 0;
+    if (nJobs > kSoloMaxJobs) { return 0; }
+    // (function attributes are per device: set on every use, as the FIR launches do)
+    cudaFuncSetAttribute(agcWalkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
+    cudaFuncSetAttribute(pllKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
+    return kSoloSmemBytes;
 }
 
 int processDemods(VfoBank& bank, cudaStream_t s) {

@@ -277,8 +277,7 @@ int b200_waterfall_make_palette(const float* colors_rgb, int color_count, uint32
 
 static int launchZoomTiles(b200_waterfall* wf, const float* rows, float* d_zoom, uint32_t* d_rgba, int outRows, int ringHeight, int ringBase, int liveRows, cudaStream_t s) {
     const size_t smem = (size_t)wf->tileSpan * sizeof(float);
-    static bool attr = false;
-    if (!attr) { B200_CUDA(cudaFuncSetAttribute(zoomTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kZoomSpanCap * sizeof(float) + 64))); attr = true; }
+    B200_CUDA(cudaFuncSetAttribute(zoomTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kZoomSpanCap * sizeof(float) + 64)));   // per device
     dim3 grid((unsigned)((wf->width + kZoomPx - 1) / kZoomPx), (unsigned)outRows);
     zoomTileKernel<<<grid, 256, smem, s>>>(rows, wf->rawSize, wf->width, wf->dSid, wf->dUf, wf->dTileLo, wf->dTileHi, wf->wfMin, wf->wfMax, wf->dLut,
                                             d_zoom, d_rgba, ringHeight, ringBase, liveRows);
