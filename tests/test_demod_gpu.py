@@ -471,3 +471,56 @@ def test_radio_chain_survives_empty_and_tiny_blocks(kind):
     got, ref = np.concatenate(got_all), np.concatenate(ref_all)
     for ch in (0, 1):
         assert err_db(got[:, ch], ref[:, ch]) <= -80.0, (kind, ch)
+
+
+def test_streaming_mode_radio_chains_are_bit_identical():
+    """B200_OPT_DEFER_TAIL with the whole radio chain behind the VFOs (IF noise blanker + FM IF noise reduction, NFM / USB /
+    AM / WFM stereo with RDS, audio resampler, de-emphasis, volume): everything behind the full-rate stage runs one block
+    late on the bank's own stream; outputs fetched only every third block, and at the end, equal the inline run's bit for bit."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    in_sr = 8e6
+    x = _stereo_fm_iq(8 * 50000, in_sr, 600e3, seed=3)
+    x = (x + synth.make_iq(9, len(x), in_sr, sigma=0.01, tones=[(-1.2e6 + 800.0, 0.2), (2.0e6 + 500.0, 0.1), (-2.5e6, 0.15)])).astype(np.complex64)
+    blocks = split(x, [100000, 64000, 8, 120000, 0, 70000])
+    devb = [to_dev(b) if len(b) else to_dev(np.zeros(1, np.complex64)) for b in blocks]
+    stream = torch.cuda.Stream()
+
+    def run(defer):
+        bank = binding.VfoBank(in_sr, max_block=150000)
+        bank.set_option(binding.OPT_DEFER_TAIL, int(defer))
+        try:
+            bank.set_rotator_mode(binding.ROTATOR_EXACT)
+            vw = bank.add(500e3, 150e3, 600e3)
+            vn = bank.add(50e3, 12.5e3, -1.2e6)
+            vu = bank.add(24e3, 2.8e3, 2.0e6)
+            va = bank.add(15e3, 10e3, -2.5e6)
+            bank.set_demod(vw, binding.DEMOD_WFM, 1, 1, 1, 0)
+            bank.set_demod(vn, binding.DEMOD_NFM, 1, 0, 0, 0)
+            bank.set_demod(vu, binding.DEMOD_USB, 0, 50.0 / 24e3, 5.0 / 24e3, 0)
+            bank.set_demod(va, binding.DEMOD_AM, 1, 50.0 / 15e3, 5.0 / 15e3, 100.0 / 15e3)
+            bank.set_if_chain(vn, True, 500.0 / 50e3, 3.0, False, 0.0)
+            bank.set_if_nr(vn, True, 15)
+            bank.set_if_nr(vw, True, 32)
+            for v in (vw, vn, vu, va):
+                bank.set_audio_post(v, 48e3, 50e-6 if v in (vw, vn) else 0.0)
+            bank.set_volume(vn, 0.6, False)
+            picks = []
+            with torch.cuda.stream(stream):
+                for i, (blk, d) in enumerate(zip(blocks, devb)):
+                    bank.process(d, len(blk), stream=stream)
+                    if i % 3 == 2:
+                        picks.append([bank.audio(v).copy() for v in (vw, vn, vu, va)] + [bank.rds(vw).copy(), bank.if_output(vn).copy()])
+                last = [bank.audio(v).copy() for v in (vw, vn, vu, va)] + [bank.rds(vw).copy(), bank.output(va).copy()]
+            return picks, last
+        finally:
+            bank.set_option(binding.OPT_DEFER_TAIL, 0)
+
+    p0, l0 = run(False)
+    p1, l1 = run(True)
+    for a, b in zip(l0, l1):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    for pa, pb in zip(p0, p1):
+        for a, b in zip(pa, pb):
+            assert a.shape == b.shape and np.array_equal(a, b)
+    assert len(l0[4]) > 0 and np.any(l0[0][:, 0] != l0[0][:, 1])       # RDS samples came out, and the WFM audio is stereo
