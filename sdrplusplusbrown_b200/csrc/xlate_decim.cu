@@ -648,7 +648,10 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
             B200_TRY((launchStream<RATIO>(dJobs, nJobs, nOut, count, odd, s)));
         }
         else {
-            const int NB = TileCfg<D, kTileLarge>::SB - (Q - 1);
+            // D = 128 (ratio 8192): 64 sub-blocks per tile instead of 32, so that the Q - 1 sub-blocks a tile recomputes for
+            // its neighbour are 8 % of it instead of 16 %
+            constexpr int kTile = (D >= 128) ? 2 * kTileLarge : kTileLarge;
+            const int NB = TileCfg<D, kTile>::SB - (Q - 1);
             // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
             const int tiles = (nOut + NB - 1) / NB;
             int G = std::min(kMaxGroup, nJobs);
@@ -656,8 +659,9 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
             // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
             // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps
             // reached 0.27 of the FP32 peak.  Two per pass is the sweet spot, where the unrolled body fits the cache.
-            if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTileLarge>(dJobs, nJobs, nOut, count, G, odd, s))); }
-            else { B200_TRY((launchMain<RATIO, 1, kTileLarge>(dJobs, nJobs, nOut, count, G, odd, s))); }
+            // (pairing beyond 32 KB of unrolled body was measured again on cfg4: 0.348 of the FFMA peak with a 40 KB limit, 0.342 with 80 KB, 0.356 as it is)
+            if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTile>(dJobs, nJobs, nOut, count, G, odd, s))); }
+            else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, G, odd, s))); }
         }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
