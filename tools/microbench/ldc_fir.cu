@@ -58,6 +58,48 @@ __device__ __forceinline__ void bodyC(const float2* x, const float2* w, float2* 
     }
 }
 
+// D  position-major: a thread owns 8 sample positions of the sub-block for good (their 8 x Q taps and 8 rotation factors
+//    live in registers, every FFMA is register-only) and walks over the sub-blocks; partial sums per (thread, sub-block)
+__global__ void __launch_bounds__(NT) firPos(const float2* in, float2* out, int iters) {
+    __shared__ __align__(16) float2 xs[SB * LP];
+    constexpr int PR = D / 8;                 // position runs per sub-block
+    constexpr int GR = NT / PR;               // sub-blocks worked on side by side
+    const int tid = threadIdx.x, pr = tid % PR, g = tid / PR;
+    for (int i = tid; i < SB * D; i += NT) { xs[i + 2 * (i / D)] = in[(size_t)blockIdx.x * SB * D + i]; }
+    float h[8][Q]; float2 w[8];
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        w[r] = make_float2(0.999f, 0.01f * (pr * 8 + r));
+#pragma unroll
+        for (int q = 0; q < Q; q++) { const int t = q * D + pr * 8 + r; h[r][q] = t < T ? c_taps[t] : 0.f; }
+    }
+    __syncthreads();
+    float2 tot = make_float2(0.f, 0.f);
+    for (int it = 0; it < iters; it++) {
+#pragma unroll 1
+        for (int sb = g; sb < SB; sb += GR) {
+            const float4* x4 = reinterpret_cast<const float4*>(xs + sb * LP + pr * 8);
+            float2 acc[Q];
+#pragma unroll
+            for (int q = 0; q < Q; q++) { acc[q] = make_float2(0.f, 0.f); }
+#pragma unroll
+            for (int r2 = 0; r2 < 4; r2++) {
+                const float4 xx = x4[r2];
+                const float2 z0 = cmulf(make_float2(xx.x, xx.y), w[2 * r2]), z1 = cmulf(make_float2(xx.z, xx.w), w[2 * r2 + 1]);
+#pragma unroll
+                for (int q = 0; q < Q; q++) {
+                    acc[q].x = fmaf(h[2 * r2][q], z0.x, acc[q].x); acc[q].y = fmaf(h[2 * r2][q], z0.y, acc[q].y);
+                    acc[q].x = fmaf(h[2 * r2 + 1][q], z1.x, acc[q].x); acc[q].y = fmaf(h[2 * r2 + 1][q], z1.y, acc[q].y);
+                }
+            }
+            // the real kernel stores the Q partial sums here; keep them alive at the same cost class (Q shared-memory stores)
+#pragma unroll
+            for (int q = 0; q < Q; q++) { tot.x += acc[q].x; tot.y += acc[q].y; }
+        }
+    }
+    out[(size_t)blockIdx.x * NT + tid] = tot;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(NT) fir(const float2* in, float2* out, int iters) {
     __shared__ __align__(16) float2 xs[SB * LP];
@@ -104,12 +146,12 @@ int main() {
     cudaMemset(in, 0, (size_t)ctas * SB * D * sizeof(float2));
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
     const double peak = (double)p.multiProcessorCount * 128.0 * (double)p.clockRate * 1e3;
-    const char* names[] = { "A unrolled, immediate constant taps", "B rolled, constant bank by register index", "C rolled, shared-memory taps" };
-    for (int m = 0; m < 3; m++) {
+    const char* names[] = { "A unrolled, immediate constant taps", "B rolled, constant bank by register index", "C rolled, shared-memory taps", "D position-major, taps in registers" };
+    for (int m = 0; m < 4; m++) {
         cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
         for (int rep = 0; rep < 2; rep++) {
             cudaEventRecord(a);
-            if (m == 0) { fir<0><<<ctas, NT>>>(in, out, iters); } else if (m == 1) { fir<1><<<ctas, NT>>>(in, out, iters); } else { fir<2><<<ctas, NT>>>(in, out, iters); }
+            if (m == 0) { fir<0><<<ctas, NT>>>(in, out, iters); } else if (m == 1) { fir<1><<<ctas, NT>>>(in, out, iters); } else if (m == 2) { fir<2><<<ctas, NT>>>(in, out, iters); } else { firPos<<<ctas, NT>>>(in, out, iters); }
             cudaEventRecord(b); cudaEventSynchronize(b);
         }
         float ms = 0; cudaEventElapsedTime(&ms, a, b);
