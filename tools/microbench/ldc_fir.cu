@@ -29,6 +29,21 @@ __device__ __forceinline__ void bodyA(const float2* x, const float2* w, float2* 
     }
 }
 
+// E  as A, but the taps are compile-time values: ptxas folds them into the FFMA as 32-bit immediates (no constant bank)
+__host__ __device__ constexpr float tapValue(int t) { return t < T ? 1e-3f * (float)((t * 37) % 101 - 50) : 0.f; }
+template <int RUN>
+__device__ __forceinline__ void bodyE(const float2* x, const float2* w, float2* acc) {
+#pragma unroll
+    for (int r = 0; r < DS; r++) {
+        const float2 z = cmulf(x[r], w[r]);
+#pragma unroll
+        for (int q = 0; q < Q; q++) {
+            const int t = q * D + RUN * DS + r;
+            if (t < T) { constexpr int dummy = 0; (void)dummy; const float h = tapValue(t); acc[q].x = fmaf(h, z.x, acc[q].x); acc[q].y = fmaf(h, z.y, acc[q].y); }
+        }
+    }
+}
+
 __device__ __forceinline__ void bodyB(const float2* x, const float2* w, float2* acc, int run) {
     const float4* tq = c_dq + run * DS * 2;
 #pragma unroll 4
@@ -123,6 +138,14 @@ __global__ void __launch_bounds__(NT) fir(const float2* in, float2* out, int ite
             default: bodyA<3>(x, w, acc); break;
             }
         }
+        else if (MODE == 3) {
+            switch (run) {
+            case 0: bodyE<0>(x, w, acc); break;
+            case 1: bodyE<1>(x, w, acc); break;
+            case 2: bodyE<2>(x, w, acc); break;
+            default: bodyE<3>(x, w, acc); break;
+            }
+        }
         else if (MODE == 1) { bodyB(x, w, acc, run); }
         else { bodyC(x, w, acc, ts + run * DS * 2); }
     }
@@ -146,12 +169,12 @@ int main() {
     cudaMemset(in, 0, (size_t)ctas * SB * D * sizeof(float2));
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
     const double peak = (double)p.multiProcessorCount * 128.0 * (double)p.clockRate * 1e3;
-    const char* names[] = { "A unrolled, immediate constant taps", "B rolled, constant bank by register index", "C rolled, shared-memory taps", "D position-major, taps in registers" };
-    for (int m = 0; m < 4; m++) {
+    const char* names[] = { "A unrolled, immediate constant taps", "B rolled, constant bank by register index", "C rolled, shared-memory taps", "D position-major, taps in registers", "E unrolled, taps as FFMA immediates" };
+    for (int m = 0; m < 5; m++) {
         cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
         for (int rep = 0; rep < 2; rep++) {
             cudaEventRecord(a);
-            if (m == 0) { fir<0><<<ctas, NT>>>(in, out, iters); } else if (m == 1) { fir<1><<<ctas, NT>>>(in, out, iters); } else if (m == 2) { fir<2><<<ctas, NT>>>(in, out, iters); } else { firPos<<<ctas, NT>>>(in, out, iters); }
+            if (m == 0) { fir<0><<<ctas, NT>>>(in, out, iters); } else if (m == 1) { fir<1><<<ctas, NT>>>(in, out, iters); } else if (m == 2) { fir<2><<<ctas, NT>>>(in, out, iters); } else if (m == 3) { firPos<<<ctas, NT>>>(in, out, iters); } else { fir<3><<<ctas, NT>>>(in, out, iters); }
             cudaEventRecord(b); cudaEventSynchronize(b);
         }
         float ms = 0; cudaEventElapsedTime(&ms, a, b);
