@@ -35,9 +35,11 @@ constexpr size_t kSmemCap = 160 * 1024;
 
 // later-stage coefficient tables of the decimation plans in the constant bank (the same generated file the fused
 // first-stage kernel includes)
-#define DECIM_TABLE_U32(name, count) __constant__ uint32_t c_##name[count] = {
+// (as function-local constant arrays: under the unrolled tap loops of planStage the loads fold and every tap is the
+// immediate of its FFMA; see xlate_decim.cu)
+#define DECIM_TABLE_U32(name, count) constexpr int n_##name = count; static __device__ __forceinline__ float imm_##name(int i) { const uint32_t t[count] = {
 #define DECIM_ROW(...) __VA_ARGS__,
-#define DECIM_TABLE_END };
+#define DECIM_TABLE_END }; return __uint_as_float(t[i]); }
 #define DECIM_PLAN_BEGIN(ratio, nstages)
 #define DECIM_STAGE(index, decim, name, ntaps)
 #define DECIM_PLAN_END
@@ -51,8 +53,8 @@ constexpr size_t kSmemCap = 160 * 1024;
 
 template <int D, int T> struct PlanStage;
 #define B200_PLAN_STAGE(idx, D_, T_)                                                                         \
-    static_assert(sizeof(c_kDecimTaps_##idx) == (T_) * sizeof(uint32_t), "decim_tables.inc changed: stage table size"); \
-    template <> struct PlanStage<D_, T_> { static __device__ __forceinline__ float tap(int i) { return __uint_as_float(c_kDecimTaps_##idx[i]); } };
+    static_assert(n_kDecimTaps_##idx == (T_), "decim_tables.inc changed: stage table size"); \
+    template <> struct PlanStage<D_, T_> { static __device__ __forceinline__ float tap(int i) { return imm_kDecimTaps_##idx(i); } };
 B200_PLAN_STAGE(0, 2, 69)
 B200_PLAN_STAGE(1, 2, 12)
 B200_PLAN_STAGE(2, 4, 27)
