@@ -53,7 +53,8 @@ def vfo_list(cfg_name, count=None, seed=1234):
         span = 0.9 * sr
         offs = (np.arange(n) - n / 2.0 + 0.5) * (span / n) + rng.uniform(-2e3, 2e3, n)
         for i in range(n):
-            # 512 AM + 384 SSB + 128 WFM per 1024, interleaved so any shard sees the same mix
+            # 512 AM + 384 SSB + 128 WFM per 1024, interleaved over the band.  (Sharding by i % 8 would put one mode on each
+            # rank -- all WFM channels on rank 7; tools/bench_bank_dist.py deals the bank out mode by mode instead.)
             k = i % 8
             mode = "WFM" if k == 7 else ("USB" if k in (1, 3, 5) else "AM")
             m = MODES[mode]
