@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Sharded VFO bank over N GPUs of one node: the whole bank of a configuration (cfg3: 256 NFM VFOs at
 61.44 MS/s; cfg4: 1024 mixed AM/SSB/WFM VFOs at 122.88 MS/s + 2^20-point FFT frames sharded by time) is dealt out
-mode by mode, the j-th VFO of a mode -> rank j % N (every shard the same mix); rank 0 holds the stream and broadcasts every block (NCCL over NVLink, double buffered
+by cost (sharding.shard_vfos: every shard the same mix of modes); rank 0 holds the stream and broadcasts every block (NCCL over NVLink, double buffered
 on a communication stream beside the kernels of the previous block); every rank runs its shard through the front end.
 STRONG scaling: the work per block is fixed, the time per block is the slowest rank's.
 
@@ -54,14 +54,11 @@ def main():
     if world > 1:
         fe.set_frame_shard(rank, world)
     vl = configs.vfo_list(args.cfg)
-    # deal the bank out mode by mode (balanced by cost, WFM > SSB > AM): the j-th VFO of a mode goes to rank
-    # j % N, so every shard holds the same mix whatever the order of the list
-    seen, mine = {}, []
-    for i, (mode, _, _, _) in enumerate(vl):
-        j = seen.get(mode, 0)
-        seen[mode] = j + 1
-        if j % world == rank:
-            mine.append(i)
+    # deal the bank out by cost (WFM > SSB > AM; sharding.shard_vfos, the same function the gloo tests cover).
+    # For cfg4 that is 64 AM + 48 SSB + 16 WFM on every one of 8 ranks -- the mix the recorded 46.4 x run had, dealt there
+    # mode by mode (the j-th VFO of a mode to rank j % N); plain i % N puts cfg4's 128 WFM channels on one rank.
+    from sdrplusplusbrown_b200 import sharding
+    mine = sorted(sharding.shard_vfos(vl, sr, world)[rank])
     demod_of = {"NFM48": (binding.DEMOD_NFM, 1, 0, 0, 0), "NFM": (binding.DEMOD_NFM, 1, 0, 0, 0),
                 "AM": (binding.DEMOD_AM, 1, None, None, None), "USB": (binding.DEMOD_USB, 0, None, None, 0),
                 "WFM": (binding.DEMOD_WFM, args.wfm_stereo, 1, 0, 0)}
