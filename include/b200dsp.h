@@ -309,9 +309,10 @@ int b200_convert_pcm(const float* d_in, void* d_out, int n_floats, int sample_ty
  * when a larger block arrives; this call runs the same kernels with the scratch in a fixed ~256 KB array inside
  * the library image (held by every GPU that loads the library until the process exits) and performs no
  * allocation of any kind.
- *   d_in, d_out   device cf32[count] on the current device (may alias)
+ *   d_in, d_out   device cf32[count] on the current device; d_out == d_in (in place) is allowed, partial overlap is not
  *   count         at most B200_DC_NOALLOC_MAX_SAMPLES; larger blocks are refused with B200_ETOOBIG
- *   rate          DCBlocker rate (IQFrontEnd uses 50 / sampleRate, iq_frontend.h:84-86)
+ *   rate          DCBlocker rate (IQFrontEnd uses 50 / sampleRate, iq_frontend.h:84-86); must lie in [0, 0.25],
+ *                 anything else is refused with B200_EINVAL
  *   d_offset      device double[2] {re, im}: the blocker's offset, read before and written after the block, so
  *                 consecutive calls continue one stream; NULL = start from zero and discard the final offset
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that call

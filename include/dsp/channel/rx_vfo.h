@@ -6,6 +6,7 @@
 // input block crosses PCIe once; a stand-alone RxVFO pays one H2D copy per VFO.)
 #pragma once
 #include <cstdio>
+#include <vector>
 
 #include "../processor.h"
 
@@ -73,12 +74,11 @@ namespace dsp::channel {
         // synchronous: count input samples -> returns the number of output samples written to `out`
         int process(int count, const complex_t* in, complex_t* out) {
             std::lock_guard<std::mutex> lk(lock());
-            float* outs[64] = {};
-            int counts[64] = {};
-            if (vfo >= 64) { fail("vfo index"); }
-            outs[vfo] = reinterpret_cast<float*>(out);
-            if (b200_vfo_bank_process_host(bank, reinterpret_cast<const float*>(in), count, outs, counts, nullptr) != B200_OK) { fail("process"); }
-            return counts[vfo];
+            hostOuts.assign((size_t)vfo + 1, nullptr);     // tables indexed by the VFO's slot in its bank, whatever that is
+            hostCounts.assign((size_t)vfo + 1, 0);
+            hostOuts[vfo] = reinterpret_cast<float*>(out);
+            if (b200_vfo_bank_process_host(bank, reinterpret_cast<const float*>(in), count, hostOuts.data(), hostCounts.data(), nullptr) != B200_OK) { fail("process"); }
+            return hostCounts[vfo];
         }
 
         int run() override {
@@ -105,6 +105,8 @@ namespace dsp::channel {
         int vfo = -1;
         bool ownsBank = false, attached = false;
         std::mutex procMtx;
+        std::vector<float*> hostOuts;
+        std::vector<int> hostCounts;
         std::mutex* sharedMtx = nullptr;
         std::mutex& lock() { return sharedMtx ? *sharedMtx : procMtx; }
     };

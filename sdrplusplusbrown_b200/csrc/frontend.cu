@@ -124,14 +124,16 @@ __global__ void __launch_bounds__(1024) dcScanKernel(const double2* __restrict__
     }
 }
 
-__global__ void __launch_bounds__(kDcThreads) dcApplyKernel(const cf32* __restrict__ in, cf32* __restrict__ out, int n, DcParams p,
+// `in` and `out` may be the same buffer (b200_dc_block_noalloc allows it): neither is __restrict__, the loads are
+// ordinary loads (not the read-only path), and a thread writes only the eight samples it has itself read before.
+__global__ void __launch_bounds__(kDcThreads) dcApplyKernel(const cf32* in, cf32* out, int n, DcParams p,
                                                             const double2* __restrict__ chunkStart, int conj) {
     __shared__ double2 sB[kDcThreads];
     const int base = blockIdx.x * kDcChunk + threadIdx.x * kDcPerThread;
     float2 x[kDcPerThread];
 #pragma unroll
     for (int i = 0; i < kDcPerThread; i++) {
-        x[i] = (base + i < n) ? __ldg(reinterpret_cast<const float2*>(in) + base + i) : make_float2(0.f, 0.f);
+        x[i] = (base + i < n) ? reinterpret_cast<const float2*>(in)[base + i] : make_float2(0.f, 0.f);
     }
     const float2 b = dcRunFold(x, kDcPerThread, p.rate);
     sB[threadIdx.x] = make_double2((double)b.x, (double)b.y);
@@ -958,6 +960,11 @@ extern "C" int b200_dc_block_noalloc(const float* d_in, float* d_out, int count,
         setError("b200_dc_block_noalloc: block of %d samples exceeds the fixed scratch limit of %d samples; split the block "
                  "(pass d_offset to carry the state) or use b200_frontend_process", count, B200_DC_NOALLOC_MAX_SAMPLES);
         return B200_ETOOBIG;
+    }
+    // the scan undoes the zero padding of the last chunk with a^-pad (pad < 2048): a must stay well away from 0
+    if (!(rate >= 0.0 && rate <= 0.25)) {
+        setError("b200_dc_block_noalloc: rate %g is outside [0, 0.25] (IQFrontEnd uses 50 / sampleRate)", rate);
+        return B200_EINVAL;
     }
     DcNoAllocScratch* sc = nullptr;
     B200_TRY(dcNoAllocScratch(&sc));

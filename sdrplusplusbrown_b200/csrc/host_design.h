@@ -1,6 +1,6 @@
 // Host-side filter/window design and integer state machines for the B200 IQ front end.
 // Double-precision math narrowed to fp32 exactly where the reference narrows, so tap tables
-// come out bit-identical to the reference's (checked in tests/test_parity_gpu.py against the oracle).
+// come out bit-identical to the reference's (checked against the oracle in tests/test_vfo_gpu.py: test_vfo_matches_oracle_per_block).
 #pragma once
 #include <algorithm>
 #include <cmath>

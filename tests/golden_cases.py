@@ -70,6 +70,7 @@ FFT_GOLDEN = {
     "fft_cfg1_8192_nuttall": (2.4e6, 8192, 20.0, 2, (1024, 6144, 1000), -110.0, -20.0),
     "fft_cfg2_65536_blackman": (20e6, 65536, 60.0, 1, (0, 65536, 1333), -120.0, -10.0),
     "fft_nz_lt_n_rect": (48e3, 4096, 20.0, 0, (100, 3000, 640), -100.0, 0.0),
+    "fft_cfg4_1048576_blackman": (122.88e6, 1 << 20, 60.0, 1, (0, 1 << 20, 1333), -120.0, -10.0),
 }
 
 

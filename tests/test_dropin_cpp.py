@@ -103,3 +103,24 @@ def test_module_instance_runs_a_gpu_channel(tmp_path):
     out = subprocess.run([exe, mod, "gpu"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "module_loader ok (gpu)" in out.stdout
+
+
+def test_iq_frontend_removal_program_compiles(tmp_path):
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_remove_gpu.cpp"), str(tmp_path / "dropin_remove_gpu"))
+
+
+@pytest.mark.gpu
+def test_iq_frontend_survives_vfo_removal_unbind_and_fft_resize_while_running(tmp_path):
+    """IQFrontEnd::removeVFO with the worker blocked on that VFO's stalled consumer and with a consumer that was
+    active until the removal, unbindIQStream of a stalled tap, setFFTSize under load, addVFO while running: the
+    remaining VFO and the FFT rows must keep flowing (reference: iq_frontend.cpp:181-202, routing/splitter.h:14-28)."""
+    from sdrplusplusbrown_b200 import synth
+    exe = str(tmp_path / "dropin_remove_gpu")
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_remove_gpu.cpp"), exe)
+    sr, n, blk = 2.4e6, 240000, 12000
+    x = synth.make_iq(0, n, sr, tones=[(100e3 + 1e3, 0.05), (300e3 + 700.0, 0.05)])
+    inp = str(tmp_path / "in.cf32")
+    x.tofile(inp)
+    r = subprocess.run([exe, inp, str(n), str(blk)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "dropin_remove_gpu ok" in r.stdout

@@ -71,6 +71,11 @@ FFT_CASES = [
     (20e6, 65536, 60.0, 1, [1000000]),          # cfg2: two-pass, I = 333333
     (48e3, 4096, 20.0, 0, [1000, 777]),         # nz (2400) < N, frames straddle blocks
     (2.4e6, 1024, 2000.0, 1, [5000]),           # nz == I (no skip): back-to-back frames
+    # the sizes above 2^16 (two passes of up to 1024 points each), window + dB epilogue and framing included:
+    (122.88e6, 1 << 20, 60.0, 1, [1000000]),    # cfg4: I = 2 048 000, nz = 2^20 -- every frame spans two or three blocks
+    (122.88e6, 1 << 17, 60.0, 1, [1 << 20]),
+    (61.44e6, 1 << 19, 60.0, 2, [777777]),      # the largest size the reference's display menu offers (display.cpp:54-66)
+    (30.72e6, 1 << 18, 60.0, 0, [1 << 19, 333]),
 ]
 
 

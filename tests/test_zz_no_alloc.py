@@ -65,3 +65,38 @@ def test_noalloc_dc_block_refuses_oversized_blocks():
         binding.dc_block_noalloc(d, d, binding.DC_NOALLOC_MAX_SAMPLES + 1, 1e-5, None)
     assert "exceeds the fixed scratch limit" in str(e.value)
     binding.dc_block_noalloc(d, d, 0, 1e-5, None)    # an empty block is fine
+
+
+def test_noalloc_dc_block_at_the_size_limit_in_place_against_the_oracle():
+    """The largest block the fixed array serves (its last chunk slot), run in place (d_out == d_in), and checked against
+    the CPU oracle's DCBlocker itself rather than against the front end; then a second, ragged block continues the
+    stream from the carried offset."""
+    import torch
+    import oracle_lib as ol
+    from sdrplusplusbrown_b200 import binding
+    sr = 20e6
+    rate = 50.0 / sr
+    n = binding.DC_NOALLOC_MAX_SAMPLES
+    port = ol.Oracle("port")
+    o = ol.DcBlock(port, rate)
+    d_off = torch.zeros(2, dtype=torch.float64, device="cuda")
+    for k, m in enumerate((n, 2049)):
+        x = synth.make_iq(k * n, m, sr, dc=(0.2, -0.1))
+        ref = o.process(x)
+        d = to_dev(x)
+        binding.dc_block_noalloc(d, d, m, rate, d_off)          # in place
+        torch.cuda.synchronize()
+        got = d.cpu().numpy().view(np.complex64).reshape(-1)
+        assert err_db(got, ref) <= TOL_DB
+        # the last samples of the block went through the array's last chunk
+        assert err_db(got[-2048:], ref[-2048:]) <= TOL_DB
+
+
+def test_noalloc_dc_block_refuses_rates_the_scan_cannot_represent():
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    d = torch.zeros((16, 2), dtype=torch.float32, device="cuda")
+    for bad in (-1e-3, 0.5, float("nan")):
+        with pytest.raises(binding.B200Error):
+            binding.dc_block_noalloc(d, d, 16, bad, None)
+    binding.dc_block_noalloc(d, d, 16, 0.0, None)            # rate 0: out = in - offset, offset never moves
