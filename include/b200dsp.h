@@ -60,6 +60,17 @@ int b200_device_to_host(void* h_dst, const void* d_src, size_t bytes, void* stre
  * (8 B per input sample read once per bank + 8 B per stage-1 output sample per VFO). */
 int b200_profile_enable(int enabled);
 int b200_profile_read(double* ms_total, long long* launches, double* algorithmic_bytes);
+/* The same per kernel family: B200_PROF_STAGE1 (what b200_profile_read reports), B200_PROF_FFT (all passes of one FFT-branch
+ * call -- window, FFT, log power -- between one pair of events; bytes = 8 per windowed sample + 4 per dB value written),
+ * B200_PROF_DC (the DC blocker of a block; 16 bytes per sample).  algorithmic_flops (may be NULL): SURVEY 8(d)'s count,
+ * 6 + 4 T/D per input sample and VFO for the fused stage, 5 N log2 N per FFT frame. */
+#define B200_PROF_STAGE1 0
+#define B200_PROF_FFT 1
+#define B200_PROF_DC 2
+int b200_profile_read_kind(int kind, double* ms_total, long long* launches, double* algorithmic_bytes, double* algorithmic_flops);
+/* The FP32 roof bench.py quotes the channelizer against, measured on `device` in the same run: independent FFMA chains
+ * with three register operands, every SM full of warps, best of three launches.  Result in FFMA per second (x2 = flop/s). */
+int b200_measure_fp32_peak(int device, double* ffma_per_second);
 
 /* ------------------------------------------------------------------------------------------
  * RxVFO bank — replaces N instances of dsp::channel::RxVFO (channel/rx_vfo.h) fed by the same

@@ -29,6 +29,8 @@ _SIGS = {
     "b200_device_to_host": (_i, [_vp, _vp, C.c_size_t, _vp]),
     "b200_profile_enable": (_i, [_i]),
     "b200_profile_read": (_i, [C.POINTER(_d), C.POINTER(C.c_longlong), C.POINTER(_d)]),
+    "b200_profile_read_kind": (_i, [_i, C.POINTER(_d), C.POINTER(C.c_longlong), C.POINTER(_d), C.POINTER(_d)]),
+    "b200_measure_fp32_peak": (_i, [_i, C.POINTER(_d)]),
     "b200_vfo_bank_create": (_i, [_pp, _d, _i, _i]),
     "b200_vfo_bank_destroy": (_i, [_vp]),
     "b200_vfo_bank_add": (_i, [_vp, _d, _d, _d]),
@@ -440,6 +442,23 @@ def profile_read():
     ms, n, by = _d(), C.c_longlong(), _d()
     _chk(lib.b200_profile_read(C.byref(ms), C.byref(n), C.byref(by)))
     return ms.value, n.value, by.value
+
+
+PROF_STAGE1, PROF_FFT, PROF_DC = 0, 1, 2
+
+
+def profile_read_kind(kind):
+    """(ms, launches, algorithmic bytes, algorithmic flops) of one kernel family since the last read."""
+    ms, n, by, fl = _d(), C.c_longlong(), _d(), _d()
+    _chk(lib.b200_profile_read_kind(int(kind), C.byref(ms), C.byref(n), C.byref(by), C.byref(fl)))
+    return ms.value, n.value, by.value, fl.value
+
+
+def measure_fp32_peak(device=0):
+    """FFMA per second of `device`, measured now (three-register FFMA chains on every SM)."""
+    r = _d()
+    _chk(lib.b200_measure_fp32_peak(int(device), C.byref(r)))
+    return r.value
 
 
 DC_NOALLOC_MAX_SAMPLES = 1 << 24

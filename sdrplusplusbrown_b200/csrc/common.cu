@@ -80,6 +80,76 @@ int uploadDesc(void* dDst, const void* hSrc, size_t bytes, cudaStream_t s, bool 
     return B200_OK;
 }
 
+// ---- optional per-launch timing (CUDA events on the launch stream), one accumulator per kernel family
+namespace {
+struct ProfFamily {
+    std::vector<cudaEvent_t> start, stop;
+    std::vector<double> bytes, flops;
+    size_t used = 0;
+    double msTotal = 0.0, bytesTotal = 0.0, flopsTotal = 0.0;
+    long long launches = 0;
+};
+struct Profiler {
+    bool enabled = false;
+    std::mutex mtx;
+    ProfFamily fam[PROF_KINDS];
+} g_prof;
+
+int profDrainLocked(ProfFamily& f) {
+    for (size_t i = 0; i < f.used; i++) {
+        float ms = 0.f;
+        B200_CUDA(cudaEventSynchronize(f.stop[i]));
+        B200_CUDA(cudaEventElapsedTime(&ms, f.start[i], f.stop[i]));
+        f.msTotal += ms; f.bytesTotal += f.bytes[i]; f.flopsTotal += f.flops[i]; f.launches++;
+    }
+    f.used = 0;
+    return B200_OK;
+}
+} // namespace
+
+bool profEnabled() { return g_prof.enabled; }
+
+int profBegin(int kind, cudaStream_t s, double bytes, double flops, size_t* slot) {
+    if (!g_prof.enabled) { return B200_OK; }
+    std::lock_guard<std::mutex> lk(g_prof.mtx);
+    ProfFamily& f = g_prof.fam[kind];
+    if (f.used == f.start.size()) {
+        if (f.used >= 4096) { B200_TRY(profDrainLocked(f)); }
+        else {
+            cudaEvent_t a, b;
+            B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
+            f.start.push_back(a); f.stop.push_back(b); f.bytes.push_back(0.0); f.flops.push_back(0.0);
+        }
+    }
+    *slot = f.used++;
+    f.bytes[*slot] = bytes; f.flops[*slot] = flops;
+    B200_CUDA(cudaEventRecord(f.start[*slot], s));
+    return B200_OK;
+}
+
+int profEnd(int kind, size_t slot, cudaStream_t s) {
+    if (!g_prof.enabled) { return B200_OK; }
+    std::lock_guard<std::mutex> lk(g_prof.mtx);
+    B200_CUDA(cudaEventRecord(g_prof.fam[kind].stop[slot], s));
+    return B200_OK;
+}
+
+// ---- FP32 roof, measured: independent FFMA chains with three register operands, every SM full of warps
+namespace {
+__global__ void __launch_bounds__(1024) ffmaPeakKernel(float* out, float s, int iters) {
+    float a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const float x0 = s, x1 = s + 1, x2 = s + 2, x3 = s + 3;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            a0 = fmaf(a0, x0, x1); a1 = fmaf(a1, x1, x2); a2 = fmaf(a2, x2, x3); a3 = fmaf(a3, x3, x0);
+            a4 = fmaf(a4, x0, x2); a5 = fmaf(a5, x1, x3); a6 = fmaf(a6, x2, x0); a7 = fmaf(a7, x3, x1);
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+} // namespace
+
 int PinnedRing::release(int slot, cudaStream_t s) {
     B200_CUDA(cudaEventRecord(done[slot], s));
     used[slot] = true;
@@ -124,6 +194,65 @@ int b200_device_to_host(void* h_dst, const void* d_src, size_t bytes, void* stre
     if (!h_dst || !d_src) { b200::setError("b200_device_to_host: NULL pointer"); return B200_EINVAL; }
     B200_CUDA(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     B200_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return B200_OK;
+}
+
+int b200_profile_enable(int enabled) {
+    using namespace b200;
+    if (!enabled && g_prof.enabled) {
+        std::lock_guard<std::mutex> lk(g_prof.mtx);
+        for (auto& f : g_prof.fam) { B200_TRY(profDrainLocked(f)); }
+    }
+    g_prof.enabled = enabled != 0;
+    return B200_OK;
+}
+
+int b200_profile_read_kind(int kind, double* ms_total, long long* launches, double* algorithmic_bytes, double* algorithmic_flops) {
+    using namespace b200;
+    if (kind < 0 || kind >= PROF_KINDS) { setError("b200_profile_read_kind: unknown kernel family %d", kind); return B200_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_prof.mtx);
+    ProfFamily& f = g_prof.fam[kind];
+    B200_TRY(profDrainLocked(f));
+    if (ms_total) { *ms_total = f.msTotal; }
+    if (launches) { *launches = f.launches; }
+    if (algorithmic_bytes) { *algorithmic_bytes = f.bytesTotal; }
+    if (algorithmic_flops) { *algorithmic_flops = f.flopsTotal; }
+    f.msTotal = 0.0; f.bytesTotal = 0.0; f.flopsTotal = 0.0; f.launches = 0;
+    return B200_OK;
+}
+
+int b200_profile_read(double* ms_total, long long* launches, double* algorithmic_bytes) {
+    return b200_profile_read_kind(b200::PROF_STAGE1, ms_total, launches, algorithmic_bytes, nullptr);
+}
+
+int b200_measure_fp32_peak(int device, double* ffma_per_second) {
+    using namespace b200;
+    if (!ffma_per_second) { setError("b200_measure_fp32_peak: NULL result pointer"); return B200_EINVAL; }
+    DeviceGuard g(device);
+    if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
+    int sms = 0;
+    B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    float* out = nullptr;
+    B200_CUDA(cudaMalloc((void**)&out, (size_t)sms * 2 * 1024 * sizeof(float)));
+    cudaEvent_t e0, e1;
+    B200_CUDA(cudaEventCreate(&e0)); B200_CUDA(cudaEventCreate(&e1));
+    const int iters = 8000;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; rep++) {
+        B200_CUDA(cudaEventRecord(e0, 0));
+        ffmaPeakKernel<<<sms * 2, 1024>>>(out, 0.5f, iters);
+        B200_CHECK_LAUNCH();
+        B200_CUDA(cudaEventRecord(e1, 0));
+        B200_CUDA(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        B200_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        const double rate = (double)sms * 2 * 1024 * iters * 64 / (ms * 1e-3);
+        if (rep > 0 && rate > best) { best = rate; }
+    }
+    countLaunch(4);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(out);
+    *ffma_per_second = best;
     return B200_OK;
 }
 

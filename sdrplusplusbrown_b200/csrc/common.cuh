@@ -68,6 +68,15 @@ struct PinnedRing {
     int release(int slot, cudaStream_t s);   // record the slot's event after the H2D copy was enqueued
 };
 
+// Measurement hooks (bench.py's roofline entries): when enabled, the launches of a kernel family are bracketed by CUDA
+// events on their launch stream.  Families: PROF_STAGE1 = the fused xlate + first-stage decimation kernel (the
+// full-rate kernel of the channelizer), PROF_FFT = the window + FFT + log-power passes of one FFT-branch call,
+// PROF_DC = the DC blocker pass.  `bytes` / `flops` are the ALGORITHMIC traffic and arithmetic of the launch.
+enum ProfKind { PROF_STAGE1 = 0, PROF_FFT = 1, PROF_DC = 2, PROF_KINDS = 3 };
+bool profEnabled();
+int profBegin(int kind, cudaStream_t s, double bytes, double flops, size_t* slot);
+int profEnd(int kind, size_t slot, cudaStream_t s);
+
 // Small host -> device transfer of per-call descriptors.  viaParams = false: cudaMemcpyAsync from the pinned slot.
 // viaParams = true: the bytes ride in the parameter block of a tiny kernel that stores them (several launches for
 // more than 3.9 KB), so the transfer goes through the stream's command buffer instead of the copy engine -- the

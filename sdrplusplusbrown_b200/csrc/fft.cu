@@ -604,6 +604,17 @@ int FftPlan::ensureScratch(int frames) {
 
 int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s) {
     if (nFrames <= 0) { return B200_OK; }
+    // measurement hook: all passes of this call between one pair of events.  Algorithmic traffic per frame: the nz
+    // samples in the window are read once (8 nz), the row is written once (4 N dB values, or 8 N for a complex spectrum)
+    size_t slot = 0;
+    B200_TRY(profBegin(PROF_FFT, s, (double)nFrames * (8.0 * nz + (outDb ? 4.0 : 0.0) * N + (outSpec ? 8.0 : 0.0) * N),
+                       (double)nFrames * 5.0 * (double)N * (double)logN, &slot));
+    const int rc = runPasses(dFrames, nFrames, dWindow, nz, outDb, outSpec, s);
+    B200_TRY(profEnd(PROF_FFT, slot, s));
+    return rc;
+}
+
+int FftPlan::runPasses(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s) {
     if (N1 == 1) {
         const size_t smem = rowsSmem(N, 1, N);
         B200_CUDA(cudaFuncSetAttribute(fftSingleKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

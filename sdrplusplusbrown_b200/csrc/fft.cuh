@@ -36,6 +36,7 @@ struct FftPlan {
     // frames: device array of FrameDesc; window: device float[nz] (may be NULL = no window);
     // outDb: device float[nFrames][N] (may be NULL), outSpec: device cf32[nFrames][N] (may be NULL)
     int run(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s);
+    int runPasses(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s);
 };
 
 } // namespace b200

@@ -432,12 +432,15 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
         p.a = 1.0 - (double)p.rate;
         p.aRun = pow(p.a, (double)kDcPerThread);
         p.aChunk = pow(p.a, (double)kDcChunk);
+        size_t slot = 0;
+        B200_TRY(profBegin(PROF_DC, s, 16.0 * n, 6.0 * n, &slot));      // algorithmic: every sample read once, written once
         dcReduceKernel<<<nChunks, kDcThreads, 0, s>>>(cur, n, p, dChunkB);
         B200_CHECK_LAUNCH();
         dcScanKernel<<<1, 1024, 0, s>>>(dChunkB, nChunks, n, p, dChunkStart, dDcState);
         B200_CHECK_LAUNCH();
         dcApplyKernel<<<nChunks, kDcThreads, 0, s>>>(cur, dDcOut, n, p, dChunkStart, invertIQ ? 1 : 0);
         B200_CHECK_LAUNCH();
+        B200_TRY(profEnd(PROF_DC, slot, s));
         // state[1] -> state[0] for the next block
         B200_CUDA(cudaMemcpyAsync(dDcState, dDcState + 1, sizeof(double2), cudaMemcpyDeviceToDevice, s));
         countLaunch(3);

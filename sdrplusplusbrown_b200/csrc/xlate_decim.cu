@@ -537,27 +537,6 @@ __global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restric
     }
 }
 
-// ---- optional per-launch timing of the fused kernel (bench.py's roofline line): CUDA events on the launch stream
-struct FusedProfile {
-    bool enabled = false;
-    std::vector<cudaEvent_t> start, stop;
-    std::vector<double> bytes;
-    size_t used = 0;
-    double msTotal = 0.0, bytesTotal = 0.0;
-    long long launches = 0;
-} g_prof;
-
-int profDrain() {
-    for (size_t i = 0; i < g_prof.used; i++) {
-        float ms = 0.f;
-        B200_CUDA(cudaEventSynchronize(g_prof.stop[i]));
-        B200_CUDA(cudaEventElapsedTime(&ms, g_prof.start[i], g_prof.stop[i]));
-        g_prof.msTotal += ms; g_prof.bytesTotal += g_prof.bytes[i]; g_prof.launches++;
-    }
-    g_prof.used = 0;
-    return B200_OK;
-}
-
 template <int RATIO, int VB, int TILE, int ODD>
 int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
@@ -574,45 +553,19 @@ int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cu
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + G - 1) / G);
     size_t slot = 0;
-    if (g_prof.enabled) {
-        if (g_prof.used == g_prof.start.size()) {
-            if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
-            else {
-                cudaEvent_t a, b;
-                B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
-                g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
-            }
-        }
-        slot = g_prof.used++;
-        // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples
-        g_prof.bytes[slot] = 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs;
-        B200_CUDA(cudaEventRecord(g_prof.start[slot], s));
-    }
+    // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples; algorithmic flops
+    // (SURVEY 8(d)): 6 for the rotation + 4 per tap and output, i.e. 6 + 4 T/D per input sample and VFO
+    B200_TRY(profBegin(PROF_STAGE1, s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs,
+                       (6.0 * (double)count + 4.0 * (double)FS::T * (double)nOut) * (double)nJobs, &slot));
     fusedXlateDecimKernel<RATIO, VB, TILE, ODD><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G, pv);
     B200_CHECK_LAUNCH(); countLaunch();
-    if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
+    B200_TRY(profEnd(PROF_STAGE1, slot, s));
     return B200_OK;
 }
 
 template <int RATIO, int VB, int TILE>
 int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, bool odd, cudaStream_t s) {
     return odd ? launchMainV<RATIO, VB, TILE, 1>(dJobs, nJobs, nOut, count, G, s) : launchMainV<RATIO, VB, TILE, 0>(dJobs, nJobs, nOut, count, G, s);
-}
-
-int profBegin(cudaStream_t s, double bytes, size_t* slotOut) {
-    if (!g_prof.enabled) { return B200_OK; }
-    if (g_prof.used == g_prof.start.size()) {
-        if (g_prof.used >= 4096) { B200_TRY(profDrain()); }
-        else {
-            cudaEvent_t a, b;
-            B200_CUDA(cudaEventCreate(&a)); B200_CUDA(cudaEventCreate(&b));
-            g_prof.start.push_back(a); g_prof.stop.push_back(b); g_prof.bytes.push_back(0.0);
-        }
-    }
-    *slotOut = g_prof.used++;
-    g_prof.bytes[*slotOut] = bytes;
-    B200_CUDA(cudaEventRecord(g_prof.start[*slotOut], s));
-    return B200_OK;
 }
 
 template <int RATIO, int ODD, int PERSIST>
@@ -638,10 +591,11 @@ int launchStreamV(const FusedJob* dJobs, int nJobs, int nOut, int count, cudaStr
         gx = (tiles + rounds - 1) / rounds;
     }
     size_t slot = 0;
-    B200_TRY(profBegin(s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs, &slot));
+    B200_TRY(profBegin(PROF_STAGE1, s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs,
+                       (6.0 * (double)count + 4.0 * (double)FS::T * (double)nOut) * (double)nJobs, &slot));
     fusedStreamKernel<RATIO, ODD, PERSIST><<<dim3(gx, nJobs), SC::THREADS, smem, s>>>(dJobs, tiles);
     B200_CHECK_LAUNCH(); countLaunch();
-    if (g_prof.enabled) { B200_CUDA(cudaEventRecord(g_prof.stop[slot], s)); }
+    B200_TRY(profEnd(PROF_STAGE1, slot, s));
     return B200_OK;
 }
 
@@ -733,24 +687,3 @@ int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cu
 }
 
 } // namespace b200
-
-extern "C" {
-
-int b200_profile_enable(int enabled) {
-    using namespace b200;
-    if (!enabled && g_prof.enabled) { B200_TRY(profDrain()); }
-    g_prof.enabled = enabled != 0;
-    return B200_OK;
-}
-
-int b200_profile_read(double* ms_total, long long* launches, double* algorithmic_bytes) {
-    using namespace b200;
-    B200_TRY(profDrain());
-    if (ms_total) { *ms_total = g_prof.msTotal; }
-    if (launches) { *launches = g_prof.launches; }
-    if (algorithmic_bytes) { *algorithmic_bytes = g_prof.bytesTotal; }
-    g_prof.msTotal = 0.0; g_prof.bytesTotal = 0.0; g_prof.launches = 0;
-    return B200_OK;
-}
-
-} // extern "C"
