@@ -138,6 +138,13 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
 #define B200_OPT_FFT_CTAS_PER_SM 4
 #define B200_OPT_BRANCH_ORDER 5
 #define B200_OPT_DEFER_TAIL 6
+/* B200_OPT_VFOS_PER_PASS (process-wide, default 0 = chosen by the size of the unrolled loop body): how many VFOs the
+ * grouped first-stage kernel accumulates in registers per pass over the staged input tile, 2 or 4.
+ * B200_OPT_VFOS_PER_CTA (process-wide, default 32): how many VFOs a CTA of that kernel serves from one staged tile
+ * (lowered automatically when the launch would not fill the GPU).  Results depend on neither; tools/bench_bank.py
+ * sweeps them. */
+#define B200_OPT_VFOS_PER_PASS 7
+#define B200_OPT_VFOS_PER_CTA 8
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)

@@ -136,6 +136,16 @@ int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
         fusedTileSamples = value;
         return B200_OK;
     }
+    if (option == B200_OPT_VFOS_PER_PASS) {
+        if (value != 0 && value != 2 && value != 4) { setError("VFOs per register pass must be 0 (automatic), 2 or 4"); return B200_EINVAL; }
+        fusedVfosPerPass = value;
+        return B200_OK;
+    }
+    if (option == B200_OPT_VFOS_PER_CTA) {
+        if (value < 2 || value > 4096) { setError("VFOs per CTA must be 2 .. 4096"); return B200_EINVAL; }
+        fusedVfosPerCta = value;
+        return B200_OK;
+    }
     if (option == B200_OPT_FFT_CTAS_PER_SM) {
         if (value < 0 || value > 4) { setError("FFT CTAs per SM must be 0 (automatic) .. 4"); return B200_EINVAL; }
         fftCtasPerSm = value;

@@ -32,13 +32,8 @@
 namespace b200 {
 
 int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grouped kernel for a one-VFO launch too; 0 / 2048 = default
-// VFOs accumulated between two barriers.  Measured on B200 (cfg3, 32 and 256 VFOs): 1 -> 0.33 of the FFMA peak, 2 -> 0.32,
-// 4 -> 0.25, 8 -> 0.15: every extra VFO per pass adds a partial-sum buffer, and the resident CTAs it costs outweigh the
-// barriers it saves.
-int fusedVfosPerBarrier = 1;
-// Two VFOs per register pass (each staged sample loaded once for both, their w tables fetched by one 16-byte broadcast
-// load): 0.39 -> 0.43 of the FFMA peak at 32-256 NFM VFOs.  Only where the unrolled body fits the instruction cache.
-bool fusedPairVfos = true;
+int fusedVfosPerPass = 0;   // B200_OPT_VFOS_PER_PASS: 0 = by code size (launchPlan), else 2 / 4
+int fusedVfosPerCta = 32;   // B200_OPT_VFOS_PER_CTA: VFOs a CTA of the grouped kernel serves from one staged tile
 // One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
 // the single-VFO kernel at 0.65 of the copy peak; with 16-byte cp.async.cg and LDS.128 it reaches 0.94.
 bool fusedStreamSingle = true;
@@ -106,7 +101,7 @@ template <int RATIO> struct FirstStage;
 #undef DECIM_STAGE_3
 #undef DECIM_PLAN_END
 
-constexpr int kMaxGroup = 8;         // VFOs per CTA (the input tile is staged once per group)
+constexpr int kMaxVfosPerCta = 64;     // VFOs a CTA of the grouped kernel serves from one staged tile (B200_OPT_VFOS_PER_CTA)
 constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4/8 start with /2 or /4: Q too large to pay off)
 
 // Input samples per CTA tile: 2048 for the single-VFO kernel (fusedStreamKernel, HBM-bound: more resident CTAs), 4096
@@ -147,6 +142,27 @@ __device__ __forceinline__ void cpAsync16(float2* smemDst, const float2* gsrc) {
 
 __device__ __forceinline__ float2 cmulf(float2 a, float2 b) { return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 
+// Blackwell's packed FP32 pair arithmetic (SASS FFMA2 / FMUL2): one issue slot for two FMAs, same FMA rate as the scalar
+// form (measured: 127 FMA/clk/SM at 2.0 warp-instructions/clk/SM, tools/microbench/ffma2_throughput.cu).  A scalar
+// multiplier is given as the pair (h, h): ptxas folds it into the instruction's broadcast operand form (a 32-bit
+// immediate for a constant tap, the .F32 register modifier for a loaded value), so no extra moves are issued.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra, rb, rc, rd;
+    ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b); rc = *reinterpret_cast<unsigned long long*>(&c);
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    return *reinterpret_cast<float2*>(&rd);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    unsigned long long ra, rb, rd;
+    ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b);
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    return *reinterpret_cast<float2*>(&rd);
+}
+// x * w with w given as the quad (w.re, w.im, -w.im, w.re):  x.re * (w.re, w.im) + x.im * (-w.im, w.re)
+__device__ __forceinline__ float2 rotate2(float xr, float xi, float4 wq) {
+    return ffma2(make_float2(xi, xi), make_float2(wq.z, wq.w), fmul2(make_float2(xr, xr), make_float2(wq.x, wq.y)));
+}
+
 // phase at sample m of the block, m may be negative (backward extension from chk[0]; only the m >= 0 part of
 // a sub-block that starts in the history region ever multiplies non-zero data)
 __device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
@@ -159,49 +175,57 @@ __device__ __forceinline__ float2 phaseAtAny(const FusedJob& j, int m) {
     return cmulf(c0, w);
 }
 
-// One thread's run of DS samples of one sub-block for VB VFOs at once: each input sample is read from shared
-// memory once, rotated once per VFO, and feeds that VFO's Q accumulators.  RUN selects which DS-sample slice
-// of the D-sample sub-block this thread owns (compile time, so every tap is a constant-bank operand).
-template <int RATIO, int RUN, int VB, int DS, int ODD>
-__device__ __forceinline__ void accumulateRun(const float2* __restrict__ xrow, const float2* __restrict__ ws, float2 (*acc)[8]) {
+// One thread's run of DS samples of one sub-block for NP pairs of VFOs at once.  The two VFOs of a pair ride in the
+// two lanes of the packed instructions ("structure of arrays" over the pair): zX = (zA.re, zB.re), zY = (zA.im, zB.im),
+// and the rotation table holds (wA.re, wB.re, wA.im, wB.im) per sample, so one 16-byte broadcast load serves both VFOs:
+//     zX = x.re * wX - x.im * wY          zY = x.re * wY + x.im * wX          (FMUL2 + FFMA2 each)
+//     accX[q] += h * zX                   accY[q] += h * zY                   (FFMA2 with the tap as immediate)
+// i.e. 2 + T/D packed instructions per sample and VFO.  Each input sample is read from shared memory once for all
+// 2 * NP VFOs of the pass.  RUN selects which DS-sample slice of the D-sample sub-block this thread owns (compile time).
+// wq: the pass's table, entry [r * NP + p].
+template <int RATIO, int RUN, int NP, int DS, int ODD>
+__device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xrow, const float4* __restrict__ wq, float2 (*accX)[8], float2 (*accY)[8]) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T + ODD;      // ODD: taps used shifted by one (h'[0] = 0, h'[t] = h[t-1])
     constexpr int Q = (T + D - 1) / D;
     const float4* x2 = reinterpret_cast<const float4*>(xrow);     // even pitch, even run start: 16-byte aligned
-    const float4* w4 = reinterpret_cast<const float4*>(ws);
 #pragma unroll
     for (int r2 = 0; r2 < DS / 2; r2++) {
         const float4 xx = x2[r2];
-        float2 w0[VB], w1[VB];
-        if constexpr (VB == 2) {
-            // the pair's tables are interleaved [r][vfo]: one 16-byte broadcast load serves both VFOs of a sample
-            const float4 a = w4[2 * r2], b = w4[2 * r2 + 1];
-            w0[0] = make_float2(a.x, a.y); w0[1] = make_float2(a.z, a.w);
-            w1[0] = make_float2(b.x, b.y); w1[1] = make_float2(b.z, b.w);
-        }
-        else {
-            const float4 a = w4[r2];
-            w0[0] = make_float2(a.x, a.y); w1[0] = make_float2(a.z, a.w);
-        }
 #pragma unroll
-        for (int v = 0; v < VB; v++) {
-            const float2 z0 = cmulf(make_float2(xx.x, xx.y), w0[v]);
-            const float2 z1 = cmulf(make_float2(xx.z, xx.w), w1[v]);
+        for (int half = 0; half < 2; half++) {
+            const float xr = half ? xx.z : xx.x, xi = half ? xx.w : xx.y;
+            const int r = 2 * r2 + half;
 #pragma unroll
-            for (int q = 0; q < Q; q++) {
-                const int t0 = q * D + RUN * DS + 2 * r2, t1 = t0 + 1;
-                if (t0 < T && t0 - ODD >= 0) { const float h = FS::tapImm(t0 - ODD); acc[v][q].x = fmaf(h, z0.x, acc[v][q].x); acc[v][q].y = fmaf(h, z0.y, acc[v][q].y); }
-                if (t1 < T && t1 - ODD >= 0) { const float h = FS::tapImm(t1 - ODD); acc[v][q].x = fmaf(h, z1.x, acc[v][q].x); acc[v][q].y = fmaf(h, z1.y, acc[v][q].y); }
+            for (int p = 0; p < NP; p++) {
+                const float4 w = wq[r * NP + p];
+                const float2 wX = make_float2(w.x, w.y), wY = make_float2(w.z, w.w);
+                const float2 zX = ffma2(make_float2(-xi, -xi), wY, fmul2(make_float2(xr, xr), wX));
+                const float2 zY = ffma2(make_float2(xi, xi), wX, fmul2(make_float2(xr, xr), wY));
+#pragma unroll
+                for (int q = 0; q < Q; q++) {
+                    const int t = q * D + RUN * DS + r;
+                    if (t < T && t - ODD >= 0) {
+                        const float h = FS::tapImm(t - ODD);
+                        accX[p][q] = ffma2(make_float2(h, h), zX, accX[p][q]);
+                        accY[p][q] = ffma2(make_float2(h, h), zY, accY[p][q]);
+                    }
+                }
             }
         }
     }
 }
 
-// grid.x = output tiles, grid.y = VFO groups of `G` jobs; all jobs of a launch share in/count/offset/nOut.
-// VB = VFOs per register pass (1 or 2, see launchPlan).
-template <int RATIO, int VB, int TILE, int ODD>
+// grid.x = output tiles, grid.y = ranges of GV VFOs; all jobs of a launch share in/count/offset/nOut.
+// A CTA stages its input tile once and walks its VFO range in passes of VB = 2 * NP VFOs.  Per pass: the threads
+// accumulate (above), multiply by their sub-block's start phase, fold the Q partial sums of neighbouring sub-blocks
+// with warp shuffles (output k = sum_q c_q[k + q]; what crosses a warp boundary or comes from another run goes
+// through a small shared-memory exchange), one barrier, and the outputs leave.  The next pass's rotation table is
+// fetched from global memory at the start of a pass and stored at its end (two table buffers), the start phases of a
+// pass are loaded at its start and used at its end, so no global load is waited for inside the pass loop.
+template <int RATIO, int NP, int TILE, int ODD>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
-fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int pv) {
+fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
@@ -210,28 +234,34 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
     constexpr int LP = D + 2;               // even sub-block pitch: rows 16-byte aligned, LDS.128 of a quarter-warp covers all banks
-    static_assert(VB == 1 || VB == 2, "one or two VFOs per register pass");
-    const int PBUF = pv * Q * NT;           // partial sums of one pass: pv VFOs between two barriers (VB == 2: pv == 2)
-    const int Gw = (G + VB - 1) / VB * VB;  // table rows allocated (a ragged last pair gets a zero partner)
+    constexpr int VB = 2 * NP;
+    constexpr int WS = SB / 32;             // warps per run
+    constexpr int HQ = Q * (Q - 1) / 2;     // halo entries per warp: (q, lane < q)
+    static_assert(SB % 32 == 0, "a warp holds 32 consecutive sub-blocks of one run");
+    static_assert(NP * D <= NT, "one table entry per thread");
     extern __shared__ __align__(16) float2 sm[];
-    float2* xs = sm;                        // SB * LP
-    float2* wsAll = xs + SB * LP;           // G * D      : phaseDelta^r of every VFO of the group
-    float2* part = wsAll + Gw * D;          // 2 * PBUF   : partial sums [pass parity][vfo][q][run][sub-block] (one buffer when G == 1 or VB == 2)
-    float2* pAll = part + ((G > 1 && VB == 1) ? 2 : 1) * PBUF;   // G * SB : sub-block start phase of every (VFO, sub-block)
-    __shared__ float2* sOut[kMaxGroup];     // per-VFO output pointer and length: the per-VFO loop reads no global memory
-    __shared__ int sNOut[kMaxGroup];
+    float2* xs = sm;                                               // SB * LP
+    float4* wqBuf = reinterpret_cast<float4*>(xs + SB * LP);       // 2 * NP * D      : rotation tables of two passes
+    float2* fbuf = reinterpret_cast<float2*>(wqBuf + 2 * NP * D);  // 2 * NP * 2 * RS * SB : in-warp folded sums [buf][p][X|Y][run][sub-block]
+    float2* halo = fbuf + 2 * NP * 2 * RS * SB;                    // 2 * NP * 2 * RS * WS * HQ : what the previous warp's last outputs need
+    // per-VFO pointers of the CTA's range, so that nothing inside the pass loop chases a pointer through global memory
+    __shared__ const float2* sChk[kMaxVfosPerCta];
+    __shared__ const float2* sWtab[kMaxVfosPerCta];
+    __shared__ float2* sOutPtr[kMaxVfosPerCta];
 
     const int tid = threadIdx.x;
     const int sb = tid % SB;                // sub-block of this thread
     const int run = tid / SB;               // which DS-sample slice of it (warp-uniform: SB % 32 == 0)
-    const int g0 = blockIdx.y * G;
+    const int lane = tid & 31;
+    const int ws = sb >> 5;
+    const int g0 = blockIdx.y * GV;
     const FusedJob j0 = jobs[g0];
     const int k0 = blockIdx.x * NB;
     if (k0 >= j0.nOut) { return; }
     const int mStart = j0.offset - H - ODD + k0 * D;     // sample index of this tile's first sub-block (even, 16-byte aligned address)
     const float2* in = reinterpret_cast<const float2*>(j0.in);
 
-    // ---- stage the input tile once for the whole VFO group (zero outside [0, count));
+    // ---- stage the input tile once for the whole VFO range (zero outside [0, count));
     // all copies of a thread are in flight at once, no register staging
     constexpr bool kImmediateStaging = ((2 * NT) % D == 0);   // a thread's copies land one constant smem stride apart
     if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
@@ -254,110 +284,131 @@ fusedXlateDecimKernel(const FusedJob* __restrict__ jobs, int nJobs, int G, int p
     }
     asm volatile("cp.async.commit_group;\n" ::: "memory");
 
-    // ---- while the tile is in flight: every VFO's w[r] table and every sub-block's start phase, so that the
-    // per-VFO loop below touches no global memory except its output
-    const int nG = min(G, nJobs - g0);
-    // the (VFO, r) and (VFO, sub-block) pairs are spread over all threads, so the table and checkpoint loads of the
-    // whole group are in flight together instead of one VFO after the other
-    if constexpr (VB == 2) {
-        // pairs of VFOs interleaved: wsAll[((g >> 1) * D + r) * 2 + (g & 1)]
-        const int nGw = (nG + 1) & ~1;
-        for (int p = tid; p < nGw * D; p += NT) {
-            const int g = p / D, r = p - g * D;
-            wsAll[(((g >> 1) * D + r) << 1) + (g & 1)] = (g < nG) ? __ldg(jobs[g0 + g].wtab + r) : make_float2(0.f, 0.f);
+    const int nG = min(GV, nJobs - g0);
+    const int nPass = (nG + VB - 1) / VB;
+    for (int g = tid; g < nG; g += NT) {
+        sChk[g] = jobs[g0 + g].chk; sWtab[g] = jobs[g0 + g].wtab; sOutPtr[g] = reinterpret_cast<float2*>(jobs[g0 + g].out);
+    }
+    __syncthreads();
+    // table entry e = r * NP + p of pass `pass`: (wA.re, wB.re, wA.im, wB.im), A = VFO gp + 2p, B = A + 1 (zero beyond the range)
+    const int eR = tid / NP, eP = tid % NP;
+    auto tableEntry = [&](int pass) -> float4 {
+        const int a = pass * VB + 2 * eP;
+        const float2 wA = (a < nG) ? __ldg(sWtab[a] + eR) : make_float2(0.f, 0.f);
+        const float2 wB = (a + 1 < nG) ? __ldg(sWtab[a + 1] + eR) : make_float2(0.f, 0.f);
+        return make_float4(wA.x, wB.x, wA.y, wB.y);
+    };
+    if (tid < NP * D) { wqBuf[tid] = tableEntry(0); }
+
+    const float2* xrow = xs + sb * LP + run * DS;
+    const int ms = mStart + sb * D;                      // first sample of this thread's sub-block
+    const bool msLive = ms < j0.count && ms + D > 0;     // the sub-block holds samples of the block
+    const bool msFwd = msLive && ms >= 0;                // ... and starts inside it: phase = chk[ms >> 9] * wtab[ms & 511]
+    // start phase of this thread's sub-block for the VFOs of a pass: the two factors are loaded one pass ahead
+    float2 pc[VB], pw[VB];
+    auto phaseLoads = [&](int pass) {
+#pragma unroll
+        for (int v = 0; v < VB; v++) {
+            const int a = pass * VB + v;
+            pc[v] = make_float2(0.f, 0.f); pw[v] = pc[v];
+            if (msFwd && a < nG) { pc[v] = __ldg(sChk[a] + (ms >> kRotChunkLog)); pw[v] = __ldg(sWtab[a] + (ms & (kRotChunk - 1))); }
         }
-    }
-    else {
-        for (int p = tid; p < nG * D; p += NT) {
-            const int g = p / D, r = p - g * D;
-            wsAll[p] = __ldg(jobs[g0 + g].wtab + r);
-        }
-    }
-    for (int p = tid; p < nG * SB; p += NT) {
-        const int g = p / SB, b = p - g * SB;
-        const FusedJob& j = jobs[g0 + g];
-        const int ms = mStart + b * D;
-        float2 ph = make_float2(0.f, 0.f);
-        if (ms < j.count && ms + D > 0) { ph = phaseAtAny(j, ms); }
-        pAll[p] = ph;
-    }
-    if (tid < nG) { sOut[tid] = reinterpret_cast<float2*>(jobs[g0 + tid].out); sNOut[tid] = jobs[g0 + tid].nOut; }
+    };
+    phaseLoads(0);
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     __syncthreads();
 
-    const float2* xrow = xs + sb * LP + run * DS;
-    for (int gp = 0, pass = 0; gp < nG; gp += pv, pass++) {
-        float2* pb = part + ((VB == 1) ? (pass & 1) * PBUF : 0);
-        const int nv = min(pv, nG - gp);
-        if constexpr (VB == 2) {
-            // two VFOs in one register pass: every staged sample is loaded once for both
-            const float2* ws = wsAll + ((((gp >> 1) * D) + run * DS) << 1);
-            float2 acc[2][8];
+    for (int pass = 0; pass < nPass; pass++) {
+        const int gp = pass * VB;
+        const int buf = pass & 1;
+        // ---- this pass's start phases from the factors loaded during the previous pass; then the loads for the next one
+        float2 PX[NP], PY[NP];                           // (PA.re, PB.re), (PA.im, PB.im)
 #pragma unroll
-            for (int v = 0; v < 2; v++) {
-#pragma unroll
-                for (int q = 0; q < Q; q++) { acc[v][q] = make_float2(0.f, 0.f); }
+        for (int p = 0; p < NP; p++) {
+            float2 pa = cmulf(pc[2 * p], pw[2 * p]), pb = cmulf(pc[2 * p + 1], pw[2 * p + 1]);
+            if (msLive && !msFwd) {                      // sub-block that starts in the history region (first tile only)
+                const int a = gp + 2 * p;
+                if (a < nG) { pa = phaseAtAny(jobs[g0 + a], ms); }
+                if (a + 1 < nG) { pb = phaseAtAny(jobs[g0 + a + 1], ms); }
             }
-            switch (run) {
-            case 0: accumulateRun<RATIO, 0, 2, DS, ODD>(xrow, ws, acc); break;
-            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 2, DS, ODD>(xrow, ws, acc); } break;
-            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 2, DS, ODD>(xrow, ws, acc); } break;
-            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 2, DS, ODD>(xrow, ws, acc); } break;
-            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 2, DS, ODD>(xrow, ws, acc); } break;
-            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 2, DS, ODD>(xrow, ws, acc); } break;
-            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 2, DS, ODD>(xrow, ws, acc); } break;
-            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 2, DS, ODD>(xrow, ws, acc); } break;
-            }
-#pragma unroll
-            for (int v = 0; v < 2; v++) {
-                if (v < nv) {
-                    const float2 P = pAll[(gp + v) * SB + sb];
-#pragma unroll
-                    for (int q = 0; q < Q; q++) { pb[(v * Q + q) * NT + tid] = cmulf(acc[v][q], P); }
-                }
-            }
+            PX[p] = make_float2(pa.x, pb.x); PY[p] = make_float2(pa.y, pb.y);
         }
-        else {
-        // pv VFOs back to back between two barriers (a rolled loop: the unrolled tap code exists once)
-#pragma unroll 1
-        for (int v = 0; v < nv; v++) {
-            const float2* ws = wsAll + (gp + v) * D + run * DS;
-            float2 acc[1][8];
+        float4 nextEntry = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bool haveNext = (pass + 1 < nPass) && (tid < NP * D);
+        if (haveNext) { nextEntry = tableEntry(pass + 1); }
+        if (pass + 1 < nPass) { phaseLoads(pass + 1); }
+        // ---- accumulate
+        const float4* wq = wqBuf + buf * (NP * D) + run * DS * NP;
+        float2 accX[NP][8], accY[NP][8];
 #pragma unroll
-            for (int q = 0; q < Q; q++) { acc[0][q] = make_float2(0.f, 0.f); }
-            switch (run) {
-            case 0: accumulateRun<RATIO, 0, 1, DS, ODD>(xrow, ws, acc); break;
-            case 1: if constexpr (RS > 1) { accumulateRun<RATIO, 1, 1, DS, ODD>(xrow, ws, acc); } break;
-            case 2: if constexpr (RS > 2) { accumulateRun<RATIO, 2, 1, DS, ODD>(xrow, ws, acc); } break;
-            case 3: if constexpr (RS > 3) { accumulateRun<RATIO, 3, 1, DS, ODD>(xrow, ws, acc); } break;
-            case 4: if constexpr (RS > 4) { accumulateRun<RATIO, 4, 1, DS, ODD>(xrow, ws, acc); } break;
-            case 5: if constexpr (RS > 5) { accumulateRun<RATIO, 5, 1, DS, ODD>(xrow, ws, acc); } break;
-            case 6: if constexpr (RS > 6) { accumulateRun<RATIO, 6, 1, DS, ODD>(xrow, ws, acc); } break;
-            default: if constexpr (RS > 7) { accumulateRun<RATIO, 7, 1, DS, ODD>(xrow, ws, acc); } break;
-            }
-            const float2 P = pAll[(gp + v) * SB + sb];
+        for (int p = 0; p < NP; p++) {
 #pragma unroll
-            for (int q = 0; q < Q; q++) { pb[(v * Q + q) * NT + tid] = cmulf(acc[0][q], P); }
+            for (int q = 0; q < Q; q++) { accX[p][q] = make_float2(0.f, 0.f); accY[p][q] = make_float2(0.f, 0.f); }
         }
+        switch (run) {
+        case 0: accumulateRunPairs<RATIO, 0, NP, DS, ODD>(xrow, wq, accX, accY); break;
+        case 1: if constexpr (RS > 1) { accumulateRunPairs<RATIO, 1, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 2: if constexpr (RS > 2) { accumulateRunPairs<RATIO, 2, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 3: if constexpr (RS > 3) { accumulateRunPairs<RATIO, 3, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 4: if constexpr (RS > 4) { accumulateRunPairs<RATIO, 4, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 5: if constexpr (RS > 5) { accumulateRunPairs<RATIO, 5, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 6: if constexpr (RS > 6) { accumulateRunPairs<RATIO, 6, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        default: if constexpr (RS > 7) { accumulateRunPairs<RATIO, 7, NP, DS, ODD>(xrow, wq, accX, accY); } break;
         }
-        __syncthreads();
-        // fold the partial sums: the (VFO, output) pairs of this pass are spread over all threads
-        for (int p = tid; p < nv * NB; p += NT) {
-            const int v = p / NB, k = p - v * NB;
-            if (k0 + k < sNOut[gp + v]) {
-                float2 y = make_float2(0.f, 0.f);
+        // ---- c_q = acc_q * P, then the in-warp part of y[k] = sum_q c_q[k + q]
 #pragma unroll
-                for (int q = 0; q < Q; q++) {
+        for (int p = 0; p < NP; p++) {
+            float2 fX = make_float2(0.f, 0.f), fY = fX;
+            float2* hl = halo + ((((buf * NP + p) * 2) * RS + run) * WS + ws) * HQ;      // X plane; the Y plane is RS * WS * HQ further
 #pragma unroll
-                    for (int h = 0; h < RS; h++) {
-                        const float2 c = pb[(v * Q + q) * NT + h * SB + k + q];
-                        y.x += c.x; y.y += c.y;
+            for (int q = 0; q < Q; q++) {
+                // (cX, cY) = (accX * PX - accY * PY, accX * PY + accY * PX), lane-wise over the pair
+                const float2 nY = make_float2(-accY[p][q].x, -accY[p][q].y);
+                const float2 cX = ffma2(nY, PY[p], fmul2(accX[p][q], PX[p]));
+                const float2 cY = ffma2(accY[p][q], PX[p], fmul2(accX[p][q], PY[p]));
+                if (q == 0) { fX = cX; fY = cY; }
+                else {
+                    const float tx0 = __shfl_down_sync(0xffffffffu, cX.x, q), tx1 = __shfl_down_sync(0xffffffffu, cX.y, q);
+                    const float ty0 = __shfl_down_sync(0xffffffffu, cY.x, q), ty1 = __shfl_down_sync(0xffffffffu, cY.y, q);
+                    if (lane + q < 32) { fX.x += tx0; fX.y += tx1; fY.x += ty0; fY.y += ty1; }
+                    if (lane < q) {                       // needed by output lane + 32 - q of the previous warp
+                        hl[q * (q - 1) / 2 + lane] = cX;
+                        hl[RS * WS * HQ + q * (q - 1) / 2 + lane] = cY;
                     }
                 }
-                sOut[gp + v][k0 + k] = y;
+            }
+            float2* fb = fbuf + (((buf * NP + p) * 2) * RS + run) * SB + sb;
+            fb[0] = fX;
+            fb[RS * SB] = fY;
+        }
+        if (haveNext) { wqBuf[(buf ^ 1) * (NP * D) + tid] = nextEntry; }
+        __syncthreads();
+        // ---- outputs: sum over the runs, add what came from the next warp, store (coalesced over k per VFO)
+        for (int idx = tid; idx < NP * SB; idx += NT) {
+            const int p = idx / SB, k = idx - p * SB;
+            const int a = gp + 2 * p;
+            if (k < NB && k0 + k < j0.nOut && a < nG) {
+                const float2* fb = fbuf + ((buf * NP + p) * 2) * RS * SB + k;
+                const float2* hl = halo + (((buf * NP + p) * 2) * RS * WS + ((k >> 5) + 1)) * HQ;
+                const int lk = k & 31;
+                float2 yX = make_float2(0.f, 0.f), yY = yX;
+#pragma unroll
+                for (int h = 0; h < RS; h++) {
+                    const float2 u = fb[h * SB], v = fb[(RS + h) * SB];
+                    yX.x += u.x; yX.y += u.y; yY.x += v.x; yY.y += v.y;
+#pragma unroll
+                    for (int q = 1; q < Q; q++) {
+                        if (lk + q >= 32) {
+                            const float2 cu = hl[h * WS * HQ + q * (q - 1) / 2 + (lk + q - 32)];
+                            const float2 cv = hl[(RS + h) * WS * HQ + q * (q - 1) / 2 + (lk + q - 32)];
+                            yX.x += cu.x; yX.y += cu.y; yY.x += cv.x; yY.y += cv.y;
+                        }
+                    }
+                }
+                sOutPtr[a][k0 + k] = make_float2(yX.x, yY.x);
+                if (a + 1 < nG) { sOutPtr[a + 1][k0 + k] = make_float2(yX.y, yY.y); }
             }
         }
-        if (G == 1 || VB == 2) { __syncthreads(); }     // single partial-sum buffer: everyone must be done reading before the next pass writes
     }
 }
 
@@ -537,35 +588,37 @@ __global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restric
     }
 }
 
-template <int RATIO, int VB, int TILE, int ODD>
-int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, cudaStream_t s) {
+template <int RATIO, int NP, int TILE, int ODD>
+int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T + ODD;
     constexpr int Q = (T + D - 1) / D;
     using TC = TileCfg<D, TILE>;
-    constexpr int SB = TC::SB;
+    constexpr int SB = TC::SB, RS = TC::RS;
     constexpr int NB = SB - (Q - 1);
-    const int NPB = (G > 1 && VB == 1) ? 2 : 1;        // one VFO per CTA, or a two-VFO pass, use a single partial-sum buffer
-    const int pv = (VB == 2) ? 2 : std::min(G, fusedVfosPerBarrier);   // VFOs accumulated between two barriers
-    const int Gw = (G + VB - 1) / VB * VB;
-    const size_t smem = ((size_t)SB * (D + 2) + (size_t)Gw * D + (size_t)NPB * pv * Q * TC::THREADS + (size_t)G * SB) * sizeof(float2);
-    B200_CUDA(cudaFuncSetAttribute(fusedXlateDecimKernel<RATIO, VB, TILE, ODD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    constexpr size_t smem = ((size_t)SB * (D + 2) + (size_t)2 * 2 * NP * D + (size_t)2 * NP * 2 * RS * SB
+                             + (size_t)2 * NP * 2 * RS * (SB / 32) * (Q * (Q - 1) / 2)) * sizeof(float2);
+    static bool attrSet = false;        // per instantiation
+    if (!attrSet) {
+        B200_CUDA(cudaFuncSetAttribute(fusedBankKernel<RATIO, NP, TILE, ODD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attrSet = true;
+    }
     const int tiles = (nOut + NB - 1) / NB;
-    dim3 grid(tiles, (nJobs + G - 1) / G);
+    dim3 grid(tiles, (nJobs + GV - 1) / GV);
     size_t slot = 0;
     // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples; algorithmic flops
     // (SURVEY 8(d)): 6 for the rotation + 4 per tap and output, i.e. 6 + 4 T/D per input sample and VFO
     B200_TRY(profBegin(PROF_STAGE1, s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs,
                        (6.0 * (double)count + 4.0 * (double)FS::T * (double)nOut) * (double)nJobs, &slot));
-    fusedXlateDecimKernel<RATIO, VB, TILE, ODD><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, G, pv);
+    fusedBankKernel<RATIO, NP, TILE, ODD><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, GV);
     B200_CHECK_LAUNCH(); countLaunch();
     B200_TRY(profEnd(PROF_STAGE1, slot, s));
     return B200_OK;
 }
 
-template <int RATIO, int VB, int TILE>
-int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int G, bool odd, cudaStream_t s) {
-    return odd ? launchMainV<RATIO, VB, TILE, 1>(dJobs, nJobs, nOut, count, G, s) : launchMainV<RATIO, VB, TILE, 0>(dJobs, nJobs, nOut, count, G, s);
+template <int RATIO, int NP, int TILE>
+int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, bool odd, cudaStream_t s) {
+    return odd ? launchMainV<RATIO, NP, TILE, 1>(dJobs, nJobs, nOut, count, GV, s) : launchMainV<RATIO, NP, TILE, 0>(dJobs, nJobs, nOut, count, GV, s);
 }
 
 template <int RATIO, int ODD, int PERSIST>
@@ -624,16 +677,25 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
             // its neighbour are 8 % of it instead of 16 %
             constexpr int kTile = (D >= 128) ? 2 * kTileLarge : kTileLarge;
             const int NB = TileCfg<D, kTile>::SB - (Q - 1);
-            // VFOs per CTA: amortise the tile load, but keep enough CTAs to fill 148 SMs
             const int tiles = (nOut + NB - 1) / NB;
-            int G = std::min(kMaxGroup, nJobs);
-            while (G > 1 && (long long)tiles * ((nJobs + G - 1) / G) < 148 * 4) { G >>= 1; }
-            // Register-blocking FOUR VFOs per pass was measured slower on B200: the 4-VFO unrolled body (57 KB at D=64)
-            // stalls on instruction fetch (39 % of stall samples), and a rolled 4-VFO body with shared-memory taps
-            // reached 0.27 of the FP32 peak.  Two per pass is the sweet spot, where the unrolled body fits the cache.
-            // (pairing beyond 32 KB of unrolled body was measured again on cfg4: 0.348 of the FFMA peak with a 40 KB limit, 0.342 with 80 KB, 0.356 as it is)
-            if (fusedPairVfos && G >= 2 && D * (2 + 2 * (4 + 2 * Q)) * 16 <= 32 * 1024) { B200_TRY((launchMain<RATIO, 2, kTile>(dJobs, nJobs, nOut, count, G, odd, s))); }
-            else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, G, odd, s))); }
+            // VFOs per register pass: the loop body is fully unrolled over the D samples of a sub-block (every tap is an
+            // immediate) and all RS run variants sit in the same code: about D * (5.5 + 2 T/D) instructions of 16 bytes per
+            // PAIR of VFOs.  Two pairs per pass halve the tile reads per VFO, but the body has to stay inside the 32 KB
+            // level of the instruction cache (round 1: a 57 KB body stalled on instruction fetch for 39 % of its samples).
+            // B200_OPT_VFOS_PER_PASS overrides the choice (2 or 4; results do not depend on it).
+            constexpr int kBodyPair = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0);
+            constexpr bool kTwoPairsFit = (2 * kBodyPair <= 34 * 1024) && (2 * D <= TileCfg<D, kTile>::THREADS);
+            int np = (kTwoPairsFit && nJobs >= 4) ? 2 : 1;
+            if (fusedVfosPerPass == 2) { np = 1; }
+            if (fusedVfosPerPass == 4 && kTwoPairsFit) { np = 2; }
+            // VFOs per CTA: the more, the better the tile load and the CTA prologue are amortised; but keep the SMs full
+            int GV = std::min(nJobs, std::min(kMaxVfosPerCta, std::max(2 * np, fusedVfosPerCta)));
+            while (GV > 2 * np && (long long)tiles * ((nJobs + GV - 1) / GV) < 148 * 8) { GV = std::max(2 * np, GV / 2); }
+            if constexpr (kTwoPairsFit) {
+                if (np == 2) { B200_TRY((launchMain<RATIO, 2, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
+                else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
+            }
+            else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
         }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);

@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--demod", action="store_true")
     ap.add_argument("--tile", type=int, default=0, help="fused-kernel tile samples (0 = library default)")
+    ap.add_argument("--vb", type=int, default=0, help="VFOs per register pass of the grouped first-stage kernel (0 = library default, 2, 4)")
+    ap.add_argument("--gv", type=int, default=32, help="VFOs per CTA of the grouped first-stage kernel")
     args = ap.parse_args()
     cfg = configs.CONFIGS[args.cfg]
     sr = cfg["sample_rate"]
@@ -45,6 +47,8 @@ def main():
         vfos = configs.vfo_list(args.cfg, n)
         bank = binding.VfoBank(sr, max_block=args.batch)
         bank.set_option(binding.OPT_TILE_SAMPLES, args.tile)
+        bank.set_option(binding.OPT_VFOS_PER_PASS, args.vb)
+        bank.set_option(binding.OPT_VFOS_PER_CTA, args.gv)
         instr = 0.0
         for mode, out_sr, bw, off in vfos:
             v = bank.add(out_sr, bw, off)
@@ -89,7 +93,7 @@ def main():
             "fused_hbm_frac": ((kb / args.steps) / 1e9 / (kms_per * 1e-3)) / hbm if kms_per > 0 else None,
             "fused_fp32_instr_per_s": instr * args.batch / (kms_per * 1e-3) if kms_per > 0 else None,
             "fused_fp32_frac": (instr * args.batch / (kms_per * 1e-3)) / peak_fp32 if kms_per > 0 else None,
-            "demod": args.demod,
+            "demod": args.demod, "vfos_per_pass": args.vb, "vfos_per_cta": args.gv,
         }
         print(json.dumps(line), flush=True)
         bank.close()
