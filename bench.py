@@ -4,17 +4,20 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (C ABI of libb200dsp.so)
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU blocks on the host cores
 
-Workload at every N (per GPU; weak scaling): BASELINE config[1] -- 20 MS/s IQ, 65536-point Blackman FFT
-waterfall at 60 fps (window + FFT + log power + max-bin zoom + palette) and one USB RxVFO channelizer (20 M -> 24 k:
-xlate, /512 decimator, 8000/13021 polyphase resampler, 651-tap channel filter).  The metric is "through FFT +
-N-VFO channelizer", so the timed step ends at the VFO's IF output; the radio module's SSB demodulator + AGC that
-the VFO feeds is timed in the same run as the extra key `with_demod` (its AGC is a strictly sequential
-recurrence per VFO, a latency chain that says nothing about the channelizer).
-A step is one pass of that path over one batch of synthetic cf32 IQ that is resident in HBM when the timed
-region starts (batch > L2).  With N > 1 ranks rank 0 owns the stream: every step's batch is NCCL-broadcast
-to the other ranks (double buffered, overlapped with the previous step's kernels), each rank channelizes it
-for its own VFO shard and computes the FFT frames f with f % N == rank.  `value` counts the samples every
-rank pushed through its channelizer shard.
+Workload: BASELINE config[3] (the largest configuration that fits one GPU) -- 122.88 MS/s IQ, 1024 mixed RxVFOs
+(512 AM 15 kS/s, 384 USB 24 kS/s, 128 WFM 500 kS/s: xlate, power-of-two decimator, polyphase resampler, channel filter)
+and a 2^20-point Blackman FFT waterfall at 60 fps (window + FFT + log power + max-bin zoom + palette).  The metric is
+"through FFT + N-VFO channelizer", so the timed step ends at every VFO's IF output and the waterfall rows.
+A step is one pass of that path over one 16 Mi-sample batch of synthetic cf32 IQ that is resident in HBM when the timed
+region starts.  STRONG scaling: with N > 1 ranks the same bank is dealt out over the ranks by cost
+(sharding.shard_vfos) and the FFT frames by time (f % N == rank); rank 0 owns the stream and every step's batch is
+NCCL-broadcast to the other ranks (double buffered, behind the previous step's kernels).  `value` is the stream rate
+the whole job sustains: batch samples x steps / time (max over ranks).
+
+Beside the headline: `roofline` holds the two dominant kernels (the fused first-stage bank kernel against the FP32
+roof measured in the same run, the FFT passes against the measured HBM copy peak); `extra.cfg2` / `extra.cfg3` are the
+same measurement on BASELINE config[1] (one USB VFO + 65536-pt FFT at 20 MS/s, HBM-bound) and config[2] (256 NFM VFOs at
+61.44 MS/s); `cpu_baseline` is the reference's blocks on ALL host cores (RxVFO::process over a thread pool).
 
 One JSON line on stdout (rank 0).  See the task contract for the keys.
 """
@@ -25,21 +28,25 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from sdrplusplusbrown_b200 import configs  # noqa: E402
+from sdrplusplusbrown_b200 import configs, sharding  # noqa: E402
 
 METRIC = "complex MS/s through FFT + N-VFO channelizer"
 UNIT = "MS/s"
-WORKLOAD = "cfg2"
+WORKLOAD = "cfg4"
 DATA_WIDTH = 1333                    # waterfall pixels per row (a typical dataWidth)
 WF_MIN, WF_MAX = -120.0, -10.0
+# first stage of each power-of-two plan: (decimation, taps) -- FMA lane operations per input sample and VFO in the
+# fused kernel = 4 (rotation) + 2 * taps / decimation
+STAGE1 = {16: (8, 54), 32: (8, 44), 64: (8, 36), 128: (16, 72), 256: (32, 143), 512: (32, 129), 1024: (64, 257),
+          2048: (64, 329), 4096: (64, 400), 8192: (128, 726)}
 
 
 def peaks():
@@ -48,6 +55,25 @@ def peaks():
         d = json.load(open(p))
         return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json copy bandwidth)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def workload_text(name):
+    cfg = configs.CONFIGS[name]
+    vl = configs.vfo_list(name)
+    modes = {}
+    for m, _, _, _ in vl:
+        modes[m] = modes.get(m, 0) + 1
+    return "BASELINE %s: %.2f MS/s synthetic IQ, %d RxVFOs (%s), %d-pt FFT waterfall at %g fps (+zoom to %d px, palette)" % (
+        name, cfg["sample_rate"] / 1e6, len(vl), ", ".join("%d %s" % (n, m) for m, n in sorted(modes.items())), cfg["fft_size"], cfg["fft_rate"], DATA_WIDTH)
+
+
+def make_config(name):
+    """The same dict in both arms (the driver compares them); run-specific sizes live in `run`."""
+    cfg = configs.CONFIGS[name]
+    return {"workload": workload_text(name), "sample_rate": cfg["sample_rate"], "fft_size": cfg["fft_size"], "fft_rate": cfg["fft_rate"],
+            "window": {0: "rectangular", 1: "blackman", 2: "nuttall"}[cfg["window"]], "vfos": len(configs.vfo_list(name)),
+            "demod": False, "rotator": "fast (closed form, calibrated step)",
+            "parallelism": "VFO bank dealt out over the GPUs by cost, every batch broadcast from rank 0, FFT frames time-sharded"}
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -122,12 +148,31 @@ def _oracle():
     raise RuntimeError("no oracle library could be loaded")
 
 
-class CpuPath:
-    """The reference's blocks for the workload, run the way the reference runs them: one thread per block
-    (dsp/block.h:82-84) -- the VFO(+demod) chain on one thread, the FFT branch (window, FFT, log power, zoom,
-    palette) on another; the Splitter's memcpy fan-out is replaced by sharing the block."""
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
 
-    def __init__(self, cfg_name=WORKLOAD, demod=False):
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+class CpuPath:
+    """The reference's blocks for the workload in the reference's best case (BASELINE.md 3 (i)): RxVFO::process
+    (channel/rx_vfo.h:89-100) called directly, no stream threads and no Splitter copies, the VFOs dealt round robin over a
+    pool of one thread per host core (the reference itself runs one thread per block, dsp/block.h:82-84), 1 M-sample
+    blocks (STREAM_BUFFER_SIZE, dsp/stream.h:14); the FFT branch (window, FFT, log power, zoom, palette: one thread in
+    the reference) is one more task of the same pool.  The oracle calls release the GIL (ctypes)."""
+
+    def __init__(self, cfg_name=WORKLOAD, threads=None):
         self.ol, self.orc = _oracle()
         cfg = configs.CONFIGS[cfg_name]
         self.sr = cfg["sample_rate"]
@@ -135,41 +180,47 @@ class CpuPath:
         self.skip, self.nz = self.orc.reshape_params(self.sr, self.N, cfg["fft_rate"])
         self.interval = self.nz + self.skip
         self.window = self.orc.fft_window(cfg["window"], self.nz)
-        self.vfos = []
-        for mode, out_sr, bw, off in configs.vfo_list(cfg_name):
-            v = self.ol.Vfo(self.orc, self.sr, out_sr, bw, off)
-            kind = {"USB": 0, "LSB": 1}.get(mode)
-            d = self.ol.Ssb(self.orc, kind, bw, out_sr, 50.0 / out_sr, 5.0 / out_sr) if (kind is not None and demod) else None
-            self.vfos.append((v, d))
+        self.vfos = [self.ol.Vfo(self.orc, self.sr, out_sr, bw, off) for _, out_sr, bw, off in configs.vfo_list(cfg_name)]
+        self.threads = threads or host_cores()
+        self.pool = ThreadPoolExecutor(max_workers=self.threads)
         self.pos = 0
+        self.buf = np.zeros(0, np.complex64)
+        self.buf_start = 0
+        self.next_frame = 0
         self.kind = "reference" if self.orc.kind == "reference" else "port"
 
+    def _vfo_task(self, k, x):
+        for v in self.vfos[k::self.threads]:
+            for i in range(0, len(x), 1000000):
+                v.process(x[i:i + 1000000])
+
+    def _fft_task(self, x):
+        # Reshaper framing: frame f = samples [f*I, f*I + nz) of the stream (iq_frontend.h:88-92); samples are kept until
+        # the frame they belong to is complete (the reference's ring buffer does the same)
+        self.buf = np.concatenate([self.buf, x]) if len(self.buf) else x
+        end = self.buf_start + len(self.buf)
+        while self.next_frame * self.interval + self.nz <= end:
+            s = self.next_frame * self.interval - self.buf_start
+            db = self.orc.fft_frame(self.buf[s:s + self.nz], self.window, self.N)
+            z = self.orc.do_zoom(0, self.N, db, DATA_WIDTH)
+            self.orc.palette_indices(z, WF_MIN, WF_MAX)
+            self.next_frame += 1
+        drop = min(len(self.buf), max(0, self.next_frame * self.interval - self.buf_start))
+        self.buf = self.buf[drop:].copy()
+        self.buf_start += drop
+
     def step(self, x):
-        """x: complex64 numpy block.  Returns after both branches finished (the slower thread bounds the rate)."""
-        def vfo_branch():
-            for v, d in self.vfos:
-                for i in range(0, len(x), 1000000):          # the reference's streams carry <= 1 M samples (dsp/stream.h:14)
-                    y = v.process(x[i:i + 1000000])
-                    if d is not None and len(y):
-                        d.process(y)
-
-        def fft_branch():
-            f = -(-self.pos // self.interval)
-            while f * self.interval + self.nz <= self.pos + len(x):
-                s = f * self.interval - self.pos
-                db = self.orc.fft_frame(x[s:s + self.nz], self.window, self.N)
-                z = self.orc.do_zoom(0, self.N, db, DATA_WIDTH)
-                self.orc.palette_indices(z, WF_MIN, WF_MAX)
-                f += 1
-
-        t1 = threading.Thread(target=vfo_branch)
-        t2 = threading.Thread(target=fft_branch)
-        t1.start(); t2.start(); t1.join(); t2.join()
+        """x: complex64 numpy block.  Returns when every task has finished (the slowest thread bounds the rate)."""
+        futs = [self.pool.submit(self._fft_task, x)] + [self.pool.submit(self._vfo_task, k, x) for k in range(self.threads)]
+        for fu in futs:
+            fu.result()
         self.pos += len(x)
 
-    @property
-    def threads(self):
-        return 2
+
+def cpu_sample_text(n, cfg_name, threads):
+    return ("%d-sample steps (%.1f ms of signal) of %s; reference blocks compiled from its own headers against generic-C VOLK and a float64 "
+            "radix-2 FFT stand-in (real VOLK SIMD / FFTW are not installable here, so this under-states the reference); RxVFO::process "
+            "over a pool of %d threads = all host cores (%s)" % (n, 1e3 * n / configs.CONFIGS[cfg_name]["sample_rate"], cfg_name, threads, cpu_model()))
 
 
 def run_reference(args):
@@ -180,7 +231,7 @@ def run_reference(args):
     cfg = configs.CONFIGS[WORKLOAD]
     sample = args.cpu_samples
     x = synth.make_iq(0, sample, cfg["sample_rate"], tones=[(1.25e6 + 700.0, 0.05), (3.3e6, 0.2)])
-    cpu = CpuPath(demod=args.demod)
+    cpu = CpuPath()
     for _ in range(args.warmup):
         cpu.step(x)
     t0 = time.perf_counter()
@@ -190,32 +241,107 @@ def run_reference(args):
     value = sample * args.steps / dt / 1e6
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": _config(args, sample, 1),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.threads, "kind": cpu.kind,
-                         "sample": "%d samples per step (%.2f s of signal), reference blocks on generic-C VOLK / float64 FFT stand-ins" % (sample, sample / cfg["sample_rate"])},
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": make_config(WORKLOAD),
+        "run": {"batch_samples_per_step": sample, "l2_policy": "n/a (CPU arm)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cpu.threads, "kind": cpu.kind, "sample": cpu_sample_text(sample, WORKLOAD, cpu.threads)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
 
 
-def _config(args, batch, n_gpus):
+def cpu_baseline(args):
+    from sdrplusplusbrown_b200 import synth
     cfg = configs.CONFIGS[WORKLOAD]
-    return {
-        "workload": "BASELINE config[1]: 20 MS/s synthetic IQ, 65536-pt Blackman FFT waterfall at 60 fps (+zoom to %d px, palette), "
-                    "1 USB SSB RxVFO channelizer (20M->24k), per GPU" % DATA_WIDTH,
-        "sample_rate": cfg["sample_rate"], "fft_size": cfg["fft_size"], "fft_rate": cfg["fft_rate"], "window": "blackman",
-        "vfos_per_gpu": 1, "vfo": "USB out 24 kS/s bw 2.8 kHz", "demod": bool(getattr(args, "demod", False)),
-        "batch_samples_per_step": batch, "l2_policy": ("batch (%.0f MB) larger than L2 (126 MB)" % (batch * 8 / 1e6)) if args.impl == "b200" else "n/a (CPU arm)",
-        "rotator": "fast (closed form, calibrated step)",
-        "stage_overlap": ("B200_OPT_DEFER_TAIL: the VFO's later stages of step k run on their own stream beside the full-rate stage of step k+1; "
-                          "all K steps' outputs are complete when the timed region ends (device-wide synchronize)") if (args.impl == "b200" and args.defer_tail) else "none",
-        "parallelism": "vfo-shard x%d + stream broadcast, fft frames time-sharded" % n_gpus if n_gpus > 1 else "single GPU",
-    }
+    n = args.cpu_samples
+    x = synth.make_iq(0, n, cfg["sample_rate"], tones=[(1.25e6 + 700.0, 0.05), (3.3e6, 0.2)])
+    cpu = CpuPath()
+    cpu.step(x[:200000])
+    t0 = time.perf_counter()
+    reps = 0
+    while True:
+        cpu.step(x)
+        reps += 1
+        if time.perf_counter() - t0 > args.cpu_seconds:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": n * reps / dt / 1e6, "unit": UNIT, "cores": cpu.threads, "kind": cpu.kind, "nproc": os.cpu_count(), "cpu_model": cpu_model(),
+            "sample": "%d x %s, %.1f s of wall time" % (reps, cpu_sample_text(n, WORKLOAD, cpu.threads), dt)}
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
+class Job:
+    """One front end with this rank's share of a configuration's VFO bank and its waterfall reduction attached."""
+
+    def __init__(self, binding, torch, cfg_name, B, local, rank, world, defer_tail=True, vfo_indices=None):
+        cfg = configs.CONFIGS[cfg_name]
+        self.cfg, self.name, self.B = cfg, cfg_name, B
+        self.sr = cfg["sample_rate"]
+        dev = torch.device("cuda", local)
+        self.fe = binding.FrontEnd(self.sr, fft_size=cfg["fft_size"], fft_rate=cfg["fft_rate"], fft_window=cfg["window"], max_block=B, device=local)
+        if world > 1:
+            self.fe.set_frame_shard(rank, world)
+        vl = configs.vfo_list(cfg_name)
+        self.mine = sorted(sharding.shard_vfos(vl, self.sr, world)[rank]) if vfo_indices is None else list(vfo_indices)
+        self.ids = []
+        self.lane_ops_per_sample = 0.0          # FMA lane operations per input sample of this rank's fused first stages
+        for i in self.mine:
+            _, out_sr, bw, off = vl[i]
+            v = self.fe.vfos.add(out_sr, bw, off)
+            self.ids.append(v)
+            d = self.fe.vfos.describe(v)
+            if d["fused"]:
+                D, T = STAGE1[d["ratio"]]
+                self.lane_ops_per_sample += 4.0 + 2.0 * T / D
+        self.fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if defer_tail else 0)
+        self.wf = binding.Waterfall(cfg["fft_size"], DATA_WIDTH, device=local)
+        self.wf.set_view(0, cfg["fft_size"])
+        self.wf.set_range(WF_MIN, WF_MAX)
+        self.max_frames = B // int(round(self.sr / cfg["fft_rate"])) + 2
+        self.d_zoom = torch.empty((self.max_frames, DATA_WIDTH), dtype=torch.float32, device=dev)
+        self.d_rgba = torch.empty((self.max_frames, DATA_WIDTH), dtype=torch.int32, device=dev)
+        self.fe.attach_waterfall(self.wf, self.d_zoom.data_ptr(), self.d_rgba.data_ptr(), self.max_frames)
+
+    def join(self):
+        """orders the last steps' deferred stages into the caller's stream"""
+        if self.ids:
+            self.fe.vfos.out_ptr(self.ids[0])
+
+
+def kernel_rooflines(binding, steps, ms_total, lane_ops, ffma_peak, hbm_peak, hbm_src, fused_name, fft_name):
+    """roofline entries of the two dominant kernel families from the library's CUDA-event hooks (timed on the launch stream)"""
+    kms, kl, kb, kf = binding.profile_read_kind(binding.PROF_STAGE1)
+    fms, fl, fb, ff = binding.profile_read_kind(binding.PROF_FFT)
+    out = {}
+    if kms > 0:
+        gbs = kb / 1e9 / (kms * 1e-3)
+        tfl = kf / 1e12 / (kms * 1e-3)
+        ops = lane_ops / (kms * 1e-3)
+        fp32_frac = tfl / (2.0 * ffma_peak / 1e12) if ffma_peak else None
+        hbm_frac = gbs / hbm_peak
+        fp32_bound = fp32_frac is not None and fp32_frac >= hbm_frac
+        out["fused"] = {
+            "kernel": fused_name, "bound": "fp32" if fp32_bound else "hbm",
+            "achieved": tfl if fp32_bound else gbs, "peak": (2.0 * ffma_peak / 1e12) if fp32_bound else hbm_peak, "unit": "TFLOP/s" if fp32_bound else "GB/s",
+            "frac": fp32_frac if fp32_bound else hbm_frac,
+            "fp32": {"achieved_tflops": tfl, "peak_tflops": 2.0 * ffma_peak / 1e12 if ffma_peak else None, "frac": fp32_frac,
+                     "flops": "SURVEY 8(d): 6 + 4 T/D per input sample and VFO", "fma_lane_ops_per_s": ops,
+                     "frac_by_instruction_count": ops / ffma_peak if ffma_peak else None,
+                     "peak_source": "FMA rate measured in this run (b200_measure_fp32_peak: packed FFMA2 chains on every SM, the form that reaches 128 FMA/clk/SM), x2 flop"},
+            "hbm": {"achieved_gbs": gbs, "peak_gbs": hbm_peak, "frac": hbm_frac, "peak_source": hbm_src},
+            "launches": int(kl), "avg_launch_ms": kms / kl if kl else None, "algorithmic_bytes_per_launch": kb / kl if kl else None,
+            "ms_per_step": kms / steps, "share_of_step": kms / ms_total if ms_total else None,
+        }
+    if fms > 0:
+        gbs = fb / 1e9 / (fms * 1e-3)
+        out["fft"] = {"kernel": fft_name, "bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": hbm_src,
+                      "bytes": "8 per windowed sample + 4 per dB value written, per frame", "calls": int(fl), "avg_call_ms": fms / fl if fl else None,
+                      "algorithmic_bytes_per_call": fb / fl if fl else None, "ms_per_step": fms / steps, "share_of_step": fms / ms_total if ms_total else None,
+                      "gflops": ff / 1e9 / (fms * 1e-3)}
+    return out
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -232,27 +358,14 @@ def run_gpu(args):
     cfg = configs.CONFIGS[WORKLOAD]
     sr = cfg["sample_rate"]
     B = args.batch
+    hbm_peak, hbm_src = peaks()
+    vl = configs.vfo_list(WORKLOAD)
 
-    # ---- handles: front end (FFT branch + VFO bank + demod) and waterfall reduction
-    fe = binding.FrontEnd(sr, fft_size=cfg["fft_size"], fft_rate=cfg["fft_rate"], fft_window=cfg["window"], max_block=B, device=local)
-    if world > 1:
-        fe.set_frame_shard(rank, world)
-    mode, out_sr, bw, off = configs.vfo_list(WORKLOAD)[0]
-    # every rank's shard holds one USB VFO; shards sit 50 kHz apart so no two ranks do identical work
-    v = fe.vfos.add(out_sr, bw, off + 50e3 * rank)
-    if args.demod:
-        fe.vfos.set_demod(v, binding.DEMOD_USB, 0, 50.0 / out_sr, 5.0 / out_sr, 0)
-    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if args.defer_tail else 0)
-    wf = binding.Waterfall(cfg["fft_size"], DATA_WIDTH, device=local)
-    wf.set_view(0, cfg["fft_size"])
-    wf.set_range(WF_MIN, WF_MAX)
-    max_frames = B // int(round(sr / cfg["fft_rate"])) + 2
-    d_zoom = torch.empty((max_frames, DATA_WIDTH), dtype=torch.float32, device=dev)
-    d_rgba = torch.empty((max_frames, DATA_WIDTH), dtype=torch.int32, device=dev)
-    fe.attach_waterfall(wf, d_zoom.data_ptr(), d_rgba.data_ptr(), max_frames)
+    job = Job(binding, torch, WORKLOAD, B, local, rank, world, defer_tail=args.defer_tail)
+    fe = job.fe
 
     # ---- synthetic stream, resident in HBM (rank 0 is the ingest GPU)
-    tones = [(off + 700.0 + 50e3 * r, 0.05) for r in range(world)] + [(3.3e6, 0.2)]
+    tones = [(vl[i][3] + 0.1 * vl[i][2], 0.02) for i in range(0, len(vl), 64)] + [(3.3e6, 0.2)]
     if rank == 0:
         src = synth.make_iq_torch(B, sr, dev, tones=tones)
         bufs = [src, src]          # the ingest GPU channelizes the stream in place and broadcasts from it
@@ -263,33 +376,36 @@ def run_gpu(args):
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     ev_ready = [torch.cuda.Event() for _ in bufs]
     ev_free = [torch.cuda.Event() for _ in bufs]
+    nb = 64
+    ev_b0 = [torch.cuda.Event(enable_timing=True) for _ in range(nb)]
+    ev_b1 = [torch.cuda.Event(enable_timing=True) for _ in range(nb)]
 
-    def bcast(i):
+    def bcast(i, timed=False):
         """rank 0 -> all: batch for step i into buffer i % 2 (NCCL over NVLink), on the comm stream."""
         b = bufs[i % 2]
         with torch.cuda.stream(comm):
             comm.wait_event(ev_free[i % 2])
+            if timed and i < nb:
+                ev_b0[i].record(comm)
             dist.broadcast(b, src=0)
+            if timed and i < nb:
+                ev_b1[i].record(comm)
             ev_ready[i % 2].record(comm)
 
-    def step(i):
-        b = bufs[i % len(bufs)]
-        if world > 1:
-            compute.wait_event(ev_ready[i % 2])
-        with torch.cuda.stream(compute):
-            fe.process(b, B, stream=compute)      # FFT rows -> zoom + palette rows inside the FFT branch (attached waterfall)
-            if world > 1:
-                ev_free[i % 2].record(compute)
-
-    def run(nsteps):
+    def run(j, nsteps, timed=False):
         if world > 1:
             for e in ev_free:
                 e.record(compute)
-            bcast(0)
+            bcast(0, timed)
         for i in range(nsteps):
             if world > 1 and i + 1 < nsteps:
-                bcast(i + 1)
-            step(i)
+                bcast(i + 1, timed)
+            if world > 1:
+                compute.wait_event(ev_ready[i % 2])
+            with torch.cuda.stream(compute):
+                j.fe.process(bufs[i % 2], j.B, stream=compute)      # FFT rows -> zoom + palette rows inside the FFT branch (attached waterfall)
+                if world > 1:
+                    ev_free[i % 2].record(compute)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -297,165 +413,235 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    def timed_run(j, nsteps, warm):
+        run(j, warm)
+        j.join()
+        barrier()
+        binding.profile_enable(True)
+        for k in (binding.PROF_STAGE1, binding.PROF_FFT, binding.PROF_DC):
+            binding.profile_read_kind(k)
+        l0 = binding.lib.b200_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(compute)
+        run(j, nsteps, timed=True)
+        j.join()            # e1 fires behind ALL work of the K steps, deferred stages included
+        e1.record(compute)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = binding.lib.b200_launch_count() - l0
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), ms, int(launches)
+
     clocks = ClockSampler(local) if rank == 0 else None      # spans warm-up, the timed region and a short tail of identical steps
-    run(max(args.warmup, 3))
-    barrier()
-    binding.profile_enable(True)
-    binding.profile_read()
-    launches0 = binding.lib.b200_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(compute)
-    run(args.steps)
-    fe.vfos.out_ptr(v)            # orders the last steps' deferred stages into the compute stream: e1 fires behind ALL work of the K steps
-    e1.record(compute)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = binding.lib.b200_launch_count() - launches0
-    kms, klaunches, kbytes = binding.profile_read()
+    warm = max(args.warmup, 3)
+    ms, ms_local, launches = timed_run(job, args.steps, warm)
+    value = B * args.steps / (ms * 1e-3) / 1e6
+    ffma_peak = binding.measure_fp32_peak(local)
+    roof = kernel_rooflines(binding, args.steps, ms_local, job.lane_ops_per_sample * B * args.steps, ffma_peak, hbm_peak, hbm_src,
+                            "fusedBankKernel<ratio> (xlate + first decimating FIR stage of every VFO of this GPU's shard: /8192 AM, /4096 USB, /128 WFM plans; "
+                            "packed FP32, pairs of VFOs per FFMA2)",
+                            "fftPass1Kernel + fftPass2Kernel (window, 2^20-pt FFT as 1024 x 1024, log power)")
     binding.profile_enable(False)
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    # the FFT branch by itself (a front end without VFOs on the same resident batch): inside the step its passes share the
+    # SMs with the bank kernel, so the events around them mostly measure waiting
+    if roof.get("fft") is not None:
+        jf = Job(binding, torch, WORKLOAD, B, local, rank, world, defer_tail=False, vfo_indices=[])
+        _, ms_f, _ = timed_run(jf, max(5, args.steps // 2), 3)
+        rf = kernel_rooflines(binding, max(5, args.steps // 2), ms_f, 0.0, ffma_peak, hbm_peak, hbm_src, "", roof["fft"]["kernel"])
+        binding.profile_enable(False)
+        if rf.get("fft"):
+            roof["fft"]["alone"] = {k: rf["fft"][k] for k in ("achieved", "frac", "avg_call_ms", "calls", "gflops")}
+            roof["fft"]["alone"]["note"] = "same frames, same resident batch, FFT branch without the VFO bank beside it (zoom + palette still attached)"
+        del jf
+    bc_ms = None
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    value = world * B * args.steps / (ms * 1e-3) / 1e6
+        n = min(args.steps, nb)
+        bc_ms = sum(ev_b0[i].elapsed_time(ev_b1[i]) for i in range(n)) / n
     # the timed region can be shorter than nvidia-smi's sampling period: keep the identical load running for ~0.6 s
     # (same step count on every rank) so the clock record holds samples taken under this workload
-    run(min(5000, int(600.0 / max(ms / args.steps, 1e-3)) + 1))
+    run(job, min(2000, int(600.0 / max(ms / args.steps, 1e-3)) + 1))
+    job.join()
     barrier()
     clk = clocks.stop() if clocks else None
 
-    # ---- same step with the VFO's SSB demodulator + AGC attached (reported beside the headline)
-    with_demod = None
-    if not args.demod:
-        fe.vfos.set_demod(v, binding.DEMOD_USB, 0, 50.0 / out_sr, 5.0 / out_sr, 0)
-        run(3)
-        barrier()
-        d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        d0.record(compute)
-        run(max(3, args.steps // 2))
-        fe.vfos.out_ptr(v)
-        d1.record(compute)
-        barrier()
-        td = torch.tensor([d0.elapsed_time(d1)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(td, op=dist.ReduceOp.MAX)
-        nd = max(3, args.steps // 2)
-        with_demod = {"value": world * B * nd / (float(td.item()) * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": float(td.item()) / nd,
-                      "note": "step + USB SSB demodulator (xlate, real part, AGC walk) on the VFO output"}
-        fe.vfos.set_demod(v, binding.DEMOD_NONE)
-
-    # ---- the dominant kernel by itself: the same VFO bank on the same resident block, run without the FFT branch and with
-    # its later stages inline, so that nothing shares the SMs with the full-rate kernel (reported beside the in-step figure)
-    barrier()
-    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 0)
-    b0 = bufs[0]
-    with torch.cuda.stream(compute):
-        for _ in range(3):
-            fe.vfos.process(b0, B, stream=compute)
-    barrier()
-    binding.profile_enable(True)
-    binding.profile_read()
-    with torch.cuda.stream(compute):
-        for _ in range(20):
-            fe.vfos.process(b0, B, stream=compute)
-    barrier()
-    kms_alone, kl_alone, kb_alone = binding.profile_read()
-    binding.profile_enable(False)
-    fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if args.defer_tail else 0)
-
-    # ---- end to end through the host-buffer C-ABI call (H2D of the block + D2H of frames, VFO IQ and audio inside)
-    Be = args.e2e_batch
-    fe2 = binding.FrontEnd(sr, fft_size=cfg["fft_size"], fft_rate=cfg["fft_rate"], fft_window=cfg["window"], max_block=Be, device=local)
+    # ---- N > 1: the sharded job's results against a single-GPU run of the same block, bit for bit
+    self_check = None
     if world > 1:
-        fe2.set_frame_shard(rank, world)
-    v2 = fe2.vfos.add(out_sr, bw, off + 50e3 * rank)
-    fe2.vfos.set_demod(v2, binding.DEMOD_USB, 0, 50.0 / out_sr, 5.0 / out_sr, 0)   # the drop-in path returns audio too
+        self_check = sharded_self_check(binding, torch, dist, bufs[0] if rank == 0 else bufs[(args.steps - 1) % 2], B, local, rank, world, compute)
+
+    # ---- end to end through the host-buffer C-ABI call (H2D of the block + D2H of frames and every VFO's IF output inside)
+    Be = args.e2e_batch
+    e2e = host_path(binding, torch, WORKLOAD, Be, local, rank, world, src if src is not None else bufs[0], compute, args.e2e_steps, dist, dev)
+
+    # ---- the lighter BASELINE configurations as extra keys (single GPU only: they are parity / regression lines)
+    extra = {}
+    if world == 1 and args.extras:
+        del job
+        torch.cuda.empty_cache()
+        for name, Bx, fused_name, fft_name in (("cfg2", 1 << 26, "fusedStreamKernel<512> (single-VFO variant, 16-byte staging)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)"),
+                                               ("cfg3", 1 << 24, "fusedBankKernel<1024> (256 NFM VFOs)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)")):
+            cx = configs.CONFIGS[name]
+            jx = Job(binding, torch, name, Bx, local, 0, 1, defer_tail=args.defer_tail)
+            sx = synth.make_iq_torch(Bx, cx["sample_rate"], dev, tones=[(configs.vfo_list(name)[0][3] + 700.0, 0.05), (3.3e6, 0.2)])
+            bufs[0] = bufs[1] = sx
+            kx = max(5, args.steps // 2)
+            msx, msx_local, lx = timed_run(jx, kx, 3)
+            rx = kernel_rooflines(binding, kx, msx_local, jx.lane_ops_per_sample * Bx * kx, ffma_peak, hbm_peak, hbm_src, fused_name, fft_name)
+            binding.profile_enable(False)
+            extra[name] = {"workload": workload_text(name), "value": Bx * kx / (msx * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": msx / kx, "steps": kx,
+                           "batch_samples_per_step": Bx, "x_real_time": Bx * kx / (msx * 1e-3) / cx["sample_rate"], "gpu_launches": lx, "roofline": rx}
+            del jx, sx
+            torch.cuda.empty_cache()
+
+    if rank == 0:
+        fused = roof.get("fused", {})
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": make_config(WORKLOAD),
+            "run": {"batch_samples_per_step": B, "l2_policy": "batch (%.0f MB) larger than L2 (126 MB); %d VFO output streams and the FFT intermediates on top" % (B * 8 / 1e6, len(job_mine_count(vl, sr, world, 0))),
+                    "vfos_on_rank0": len(job_mine_count(vl, sr, world, 0)), "x_real_time": value * 1e6 / sr,
+                    "stage_overlap": ("B200_OPT_DEFER_TAIL: the later stages of step k run on their own stream beside the full-rate stage of step k+1; "
+                                      "all K steps' outputs are complete when the timed region ends") if args.defer_tail else "none",
+                    "broadcast_ms_per_step_rank0": bc_ms},
+            "clocks": clk,
+            "e2e": e2e,
+            "gpu_launches": int(launches),
+            "roofline": dict(fused, **{"traffic": _traffic(), "fft": roof.get("fft"), "fp32_peak_ffma_per_s": ffma_peak}),
+        }
+        if self_check is not None:
+            line["self_check"] = self_check
+        if extra:
+            line["extra"] = extra
+        if args.cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(args)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def job_mine_count(vl, sr, world, rank):
+    return sharding.shard_vfos(vl, sr, world)[rank]
+
+
+def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, steps, dist, dev):
+    """b200_frontend_process_host on this rank's shard: pinned host input, H2D, kernels, D2H of the dB rows and of every
+    VFO's IF output.  With N ranks every rank feeds its own copy of the block over its own PCIe link (the host-fed path
+    has no broadcast; SURVEY 8(e): "replicas per source")."""
+    cfg = configs.CONFIGS[name]
+    sr = cfg["sample_rate"]
+    j = Job(binding, torch, name, Be, local, rank, world, defer_tail=False)
+    fe2 = j.fe
     h_in = torch.empty((Be, 2), dtype=torch.float32).pin_memory()
-    h_in.copy_((src if src is not None else bufs[0])[:Be].cpu())
+    h_in.copy_(d_src[:Be].cpu())
     mf = Be // int(round(sr / cfg["fft_rate"])) + 2
     h_frames = torch.empty((mf, cfg["fft_size"]), dtype=torch.float32).pin_memory()
-    mo = fe2.vfos.max_out(v2, Be)
-    h_iq = torch.empty((mo, 2), dtype=torch.float32).pin_memory()
-    h_au = torch.empty((mo, 2), dtype=torch.float32).pin_memory()
-    optr = (ctypes.c_void_p * (v2 + 1))(); optr[v2] = h_iq.data_ptr()
-    aptr = (ctypes.c_void_p * (v2 + 1))(); aptr[v2] = h_au.data_ptr()
-    counts = np.zeros(v2 + 1, np.int32)
+    nslots = max(j.ids) + 1 if j.ids else 1
+    sizes = [fe2.vfos.max_out(v, Be) for v in j.ids]
+    h_iq = torch.empty((max(1, sum(sizes)), 2), dtype=torch.float32).pin_memory()
+    optr = (ctypes.c_void_p * nslots)()
+    pos = 0
+    for v, n in zip(j.ids, sizes):
+        optr[v] = h_iq.data_ptr() + pos * 8
+        pos += n
+    counts = np.zeros(nslots, np.int32)
 
-    def e2e_step():
-        rc = binding.lib.b200_frontend_process_host(fe2.h, h_in.data_ptr(), Be, h_frames.data_ptr(), mf, optr, aptr, counts.ctypes.data, compute.cuda_stream)
+    def step():
+        rc = binding.lib.b200_frontend_process_host(fe2.h, h_in.data_ptr(), Be, h_frames.data_ptr(), mf, optr, None, counts.ctypes.data, compute.cuda_stream)
         if rc < 0:
             raise RuntimeError(binding.lib.b200_last_error().decode())
 
     for _ in range(2):
-        e2e_step()
-    barrier()
+        step()
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
     t0 = time.perf_counter()
-    for _ in range(args.e2e_steps):
-        e2e_step()
+    for _ in range(steps):
+        step()
     torch.cuda.synchronize(dev)
     te = time.perf_counter() - t0
     tt = torch.tensor([te], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     te = float(tt.item())
-    e2e_value = world * Be * args.e2e_steps / te / 1e6
-    nf2 = fe2.frame_count()
-    d2h = nf2 * cfg["fft_size"] * 4 + int(counts[v2]) * 8 * 2
+    d2h = fe2.frame_count() * cfg["fft_size"] * 4 + int(counts.sum()) * 8
+    return {"value": Be * steps / te / 1e6, "unit": UNIT, "h2d_bytes_per_step": Be * 8, "d2h_bytes_per_step": int(d2h), "batch_samples": Be,
+            "path": "b200_frontend_process_host (pinned host buffers; H2D of the block, kernels, D2H of the dB rows and of every VFO's IF output, per call)"}
 
-    # ---- the same call fed with int16 I/Q (what the reference's file source and most SDR hardware deliver; converted on
-    # the device): reported beside e2e, not instead of it
-    h_i16 = (h_in * 32767.0).to(torch.int16).pin_memory()
 
-    def e2e_i16_step():
-        rc = binding.lib.b200_frontend_process_host_i16(fe2.h, h_i16.data_ptr(), Be, ctypes.c_float(32768.0), h_frames.data_ptr(), mf, optr, aptr,
-                                                        counts.ctypes.data, compute.cuda_stream)
-        if rc < 0:
-            raise RuntimeError(binding.lib.b200_last_error().decode())
-
-    for _ in range(2):
-        e2e_i16_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.e2e_steps):
-        e2e_i16_step()
-    torch.cuda.synchronize(dev)
-    ti = time.perf_counter() - t0
-    tti = torch.tensor([ti], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tti, op=dist.ReduceOp.MAX)
-    e2e_i16_value = world * Be * args.e2e_steps / float(tti.item()) / 1e6
-
+def sharded_self_check(binding, torch, dist, d_block, B, local, rank, world, compute, per_rank=3):
+    """Every rank runs a fresh front end over its shard on the block it last received; rank 0 runs the same block through
+    ONE front end that holds the picked VFOs of every rank and all FFT frames.  The sharded outputs must equal the
+    single-GPU ones (bit for bit where the launch shape does not enter the order of summation, to -100 dB elsewhere); a
+    block that was broadcast into a buffer still being read, or a frame computed by the wrong rank, fails this at once."""
+    cfg = configs.CONFIGS[WORKLOAD]
+    sr = cfg["sample_rate"]
+    vl = configs.vfo_list(WORKLOAD)
+    shards = sharding.shard_vfos(vl, sr, world)
+    # the block of the last step is in different buffers on different ranks; make it the same bytes everywhere
+    blk = d_block if rank == 0 else torch.empty_like(d_block)
     if rank == 0:
-        peak, which = peaks()
-        achieved = (kbytes / 1e9) / (kms * 1e-3) if kms > 0 else 0.0
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": _config(args, B, world),
-            "clocks": clk,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": Be * 8, "d2h_bytes_per_step": d2h,
-                    "batch_samples": Be, "path": "b200_frontend_process_host (pinned host buffers, H2D + kernels + D2H per call)",
-                    "int16_input": {"value": e2e_i16_value, "unit": UNIT, "h2d_bytes_per_step": Be * 4,
-                                    "path": "b200_frontend_process_host_i16 (int16 I/Q over PCIe, converted on the device)"}},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "fusedStreamKernel<512> (xlate + /32 decimating FIR, stage 1 of the VFO; single-VFO variant of the fused kernel with 16-byte staging)",
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
-                         "peak_source": which, "traffic": _traffic(), "launches": int(klaunches), "avg_launch_ms": kms / klaunches if klaunches else None,
-                         "algorithmic_bytes_per_launch": kbytes / klaunches if klaunches else None,
-                         "kernel_alone": {"achieved": (kb_alone / 1e9) / (kms_alone * 1e-3) if kms_alone > 0 else None,
-                                          "frac": ((kb_alone / 1e9) / (kms_alone * 1e-3)) / peak if (kms_alone > 0 and peak) else None,
-                                          "avg_launch_ms": kms_alone / kl_alone if kl_alone else None, "launches": int(kl_alone),
-                                          "note": "same kernel, same resident block, measured in this run with CUDA events: the VFO bank alone (no FFT branch, later stages inline), so nothing shares the SMs with it; `achieved` / `frac` above are its figures inside the timed step, where the FFT passes and the previous block's tail run beside it"},
-                         "share_of_step": (kms / ms) if ms else None},
-        }
-        if with_demod is not None:
-            line["with_demod"] = with_demod
-        if args.cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_baseline(args)
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+        blk = d_block.clone()
+    dist.broadcast(blk, src=0)
+    picks = [sorted(s)[:: max(1, len(s) // per_rank)][:per_rank] for s in shards]
+    j = Job(binding, torch, WORKLOAD, B, local, rank, world, defer_tail=False)
+    with torch.cuda.stream(compute):
+        j.fe.process(blk, B, stream=compute)
+    torch.cuda.synchronize()
+    mine = {}
+    for i in picks[rank]:
+        v = j.ids[j.mine.index(i)]
+        mine[i] = j.fe.vfos.output(v)
+    rows = {int(j.fe.frame_index(k)): r for k, r in enumerate(j.fe.frames())}
+    gathered = [None] * world
+    dist.all_gather_object(gathered, {"vfo": mine, "rows": {f: r[:: max(1, len(r) // 4096)].copy() for f, r in rows.items()}})
+    res = None
+    if rank == 0:
+        allp = [i for p in picks for i in p]
+        ref = Job(binding, torch, WORKLOAD, B, local, 0, 1, defer_tail=False, vfo_indices=allp)
+        with torch.cuda.stream(compute):
+            ref.fe.process(blk, B, stream=compute)
+        torch.cuda.synchronize()
+        nv, nf, nv_exact, nf_exact = 0, 0, 0, 0
+        worst_db, worst_row = -400.0, 0.0
+        structure_ok = True
+        for g in gathered:
+            for i, y in g["vfo"].items():
+                want = ref.fe.vfos.output(ref.ids[allp.index(i)])
+                nv += 1
+                if want.shape != y.shape or len(want) == 0:
+                    structure_ok = False
+                    continue
+                nv_exact += int(np.array_equal(want.view(np.uint32), y.view(np.uint32)))
+                num = float(np.sqrt(np.mean(np.abs(want.astype(np.complex128) - y) ** 2)))
+                den = float(np.sqrt(np.mean(np.abs(want.astype(np.complex128)) ** 2)))
+                worst_db = max(worst_db, 20.0 * np.log10(max(num, 1e-30) / max(den, 1e-30)))
+        ref_rows = {int(ref.fe.frame_index(k)): r for k, r in enumerate(ref.fe.frames())}
+        seen = set()
+        for r, g in enumerate(gathered):
+            for f, sub in g["rows"].items():
+                nf += 1
+                if (f % world != r) or f not in ref_rows:
+                    structure_ok = False
+                    continue
+                want = ref_rows[f][:: max(1, len(ref_rows[f]) // 4096)]
+                nf_exact += int(np.array_equal(want.view(np.uint32), sub.view(np.uint32)))
+                worst_row = max(worst_row, float(np.max(np.abs(want - sub))))
+                seen.add(f)
+        structure_ok = structure_ok and seen == set(ref_rows)
+        # The first stage and the FFT give the same bits in any launch; the later stages split long filters over lanes by
+        # a balance taken over the whole launch, so a VFO's last bits can depend on how many VFOs share the launch.
+        ok = structure_ok and worst_db <= -100.0 and worst_row <= 1e-3
+        res = {"vfos_compared": nv, "vfos_bit_exact": nv_exact, "vfo_worst_error_db": worst_db, "frames_compared": nf, "frames_bit_exact": nf_exact,
+               "rows_worst_abs_diff_db": worst_row, "every_frame_on_its_rank_once": bool(structure_ok), "ok": bool(ok),
+               "tolerance": "VFO output error <= -100 dB of its RMS, dB rows within 0.001 dB, every frame f computed by rank f % N exactly once"}
+        if not ok:
+            raise RuntimeError("sharded run differs from the single-GPU run: %r" % res)
+    return res
 
 
 def _traffic():
@@ -469,41 +655,21 @@ def _traffic():
     return None
 
 
-def cpu_baseline(args):
-    from sdrplusplusbrown_b200 import synth
-    cfg = configs.CONFIGS[WORKLOAD]
-    n = args.cpu_samples
-    x = synth.make_iq(0, n, cfg["sample_rate"], tones=[(1.25e6 + 700.0, 0.05), (3.3e6, 0.2)])
-    cpu = CpuPath(demod=args.demod)
-    cpu.step(x[:1000000])
-    t0 = time.perf_counter()
-    reps = 0
-    while True:
-        cpu.step(x)
-        reps += 1
-        if time.perf_counter() - t0 > args.cpu_seconds:
-            break
-    dt = time.perf_counter() - t0
-    return {"value": n * reps / dt / 1e6, "unit": UNIT, "cores": cpu.threads, "kind": cpu.kind,
-            "sample": "%d x %d samples (%.1f s of CPU time) of the same workload; reference blocks compiled from its own headers against "
-                      "generic-C VOLK and a float64 radix-2 FFT stand-in (real VOLK SIMD / FFTW are not installable here, so this under-states the reference)" % (reps, n, dt)}
-
-
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=1 << 26, help="samples per step, device resident (default 64 Mi = 512 MiB > L2)")
-    ap.add_argument("--e2e-batch", type=int, default=1 << 24)
-    ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--cpu-samples", type=int, default=1 << 24, help="samples per CPU-arm step (bounded sample of the workload)")
+    ap.add_argument("--batch", type=int, default=1 << 24, help="samples per step, device resident (default 16 Mi = 134 MB > L2)")
+    ap.add_argument("--e2e-batch", type=int, default=1 << 23)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-samples", type=int, default=1000000, help="samples per CPU-arm step (bounded sample of the workload: one reference stream block)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    ap.add_argument("--no-extras", dest="extras", action="store_false", help="skip the cfg2 / cfg3 extra keys")
     ap.add_argument("--no-defer-tail", dest="defer_tail", action="store_false",
-                    help="run the VFO's later stages inline in the caller's stream (library default) instead of the streaming mode")
-    ap.add_argument("--demod", action="store_true", help="include the SSB demodulator + AGC in the timed step")
+                    help="run the VFOs' later stages inline in the caller's stream (library default) instead of the streaming mode")
     args = ap.parse_args()
     # The contract is ONE JSON line on stdout.  Libraries below us write there too (NCCL prints its version banner on
     # stdout when NCCL_DEBUG is set on the box): send file descriptor 1 to stderr for the duration of the run and give

@@ -68,8 +68,9 @@ int b200_profile_read(double* ms_total, long long* launches, double* algorithmic
 #define B200_PROF_FFT 1
 #define B200_PROF_DC 2
 int b200_profile_read_kind(int kind, double* ms_total, long long* launches, double* algorithmic_bytes, double* algorithmic_flops);
-/* The FP32 roof bench.py quotes the channelizer against, measured on `device` in the same run: independent FFMA chains
- * with three register operands, every SM full of warps, best of three launches.  Result in FFMA per second (x2 = flop/s). */
+/* The FP32 roof bench.py quotes the channelizer against, measured on `device` in the same run: independent chains of
+ * packed FMAs (FFMA2, the form that reaches the CUDA cores' 128 FMA per clock and SM), every SM full of warps, best of
+ * three launches.  Result in FMAs per second (x2 = flop/s). */
 int b200_measure_fp32_peak(int device, double* ffma_per_second);
 
 /* ------------------------------------------------------------------------------------------

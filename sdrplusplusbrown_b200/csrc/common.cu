@@ -134,19 +134,32 @@ int profEnd(int kind, size_t slot, cudaStream_t s) {
     return B200_OK;
 }
 
-// ---- FP32 roof, measured: independent FFMA chains with three register operands, every SM full of warps
+// ---- FP32 roof, measured: independent chains of packed FMAs (fma.rn.f32x2 -> FFMA2), every SM full of warps.  This is
+// the instruction form that reaches the CUDA cores' full rate of 128 FMA per clock and SM on B200 (measured 127.5;
+// three-register scalar FFMA chains stop at 77-85 because of operand bandwidth, tools/microbench/ffma2_throughput.cu).
 namespace {
-__global__ void __launch_bounds__(1024) ffmaPeakKernel(float* out, float s, int iters) {
-    float a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
-    const float x0 = s, x1 = s + 1, x2 = s + 2, x3 = s + 3;
-    for (int i = 0; i < iters; i++) {
+__device__ __forceinline__ float2 peakFma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra, rb, rc, rd;
+    ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b); rc = *reinterpret_cast<unsigned long long*>(&c);
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    return *reinterpret_cast<float2*>(&rd);
+}
+__global__ void __launch_bounds__(512) ffmaPeakKernel(float2* out, float s, int iters) {
+    float2 a[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = make_float2((float)threadIdx.x + i, (float)threadIdx.x - i); }
+    const float2 x0 = make_float2(s, s + 1.f), x1 = make_float2(s + 2.f, s + 3.f);
+    for (int it = 0; it < iters; it++) {
 #pragma unroll
         for (int u = 0; u < 8; u++) {
-            a0 = fmaf(a0, x0, x1); a1 = fmaf(a1, x1, x2); a2 = fmaf(a2, x2, x3); a3 = fmaf(a3, x3, x0);
-            a4 = fmaf(a4, x0, x2); a5 = fmaf(a5, x1, x3); a6 = fmaf(a6, x2, x0); a7 = fmaf(a7, x3, x1);
+#pragma unroll
+            for (int i = 0; i < 8; i++) { a[i] = peakFma2(a[i], x0, x1); }
         }
     }
-    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+    float2 r = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 8; i++) { r.x += a[i].x; r.y += a[i].y; }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 } // namespace
 
@@ -232,21 +245,21 @@ int b200_measure_fp32_peak(int device, double* ffma_per_second) {
     if (!g.ok) { setError("cannot select CUDA device %d", device); return B200_ECUDA; }
     int sms = 0;
     B200_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-    float* out = nullptr;
-    B200_CUDA(cudaMalloc((void**)&out, (size_t)sms * 2 * 1024 * sizeof(float)));
+    const int grid = sms * 4, threads = 512, iters = 8000;
+    float2* out = nullptr;
+    B200_CUDA(cudaMalloc((void**)&out, (size_t)grid * threads * sizeof(float2)));
     cudaEvent_t e0, e1;
     B200_CUDA(cudaEventCreate(&e0)); B200_CUDA(cudaEventCreate(&e1));
-    const int iters = 8000;
     double best = 0.0;
     for (int rep = 0; rep < 4; rep++) {
         B200_CUDA(cudaEventRecord(e0, 0));
-        ffmaPeakKernel<<<sms * 2, 1024>>>(out, 0.5f, iters);
+        ffmaPeakKernel<<<grid, threads>>>(out, 0.5f, iters);
         B200_CHECK_LAUNCH();
         B200_CUDA(cudaEventRecord(e1, 0));
         B200_CUDA(cudaEventSynchronize(e1));
         float ms = 0.f;
         B200_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-        const double rate = (double)sms * 2 * 1024 * iters * 64 / (ms * 1e-3);
+        const double rate = (double)grid * threads * iters * 128.0 / (ms * 1e-3);      // 64 FFMA2 = 128 FMAs per thread and iteration
         if (rep > 0 && rate > best) { best = rate; }
     }
     countLaunch(4);
