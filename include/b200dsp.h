@@ -340,6 +340,49 @@ int b200_convert_pcm(const float* d_in, void* d_out, int n_floats, int sample_ty
 #define B200_DC_NOALLOC_MAX_SAMPLES (1 << 24)
 int b200_dc_block_noalloc(const float* d_in, float* d_out, int count, double rate, double* d_offset, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Front-end group — one IQ front end over several GPUs of one node, in one process.  It replaces the
+ * same IQFrontEnd, with its Splitter fan-out (routing/splitter.h:74-83; bound in iq_frontend.cpp:46,79,159-179)
+ * carried over NVLink: member 0 (devices[0], the ingest GPU and display owner) runs the pre-processing chain, every
+ * block is broadcast to the other members (ncclBroadcast when libnccl.so.2 can be loaded -- the block leaves the
+ * ingest GPU once; cudaMemcpyPeerAsync to every member otherwise), each member channelizes the VFOs it was dealt
+ * (b200_frontend_group_add_vfo places a VFO on the member with the least work) and computes the FFT frames f with
+ * f % n == member, and the dB rows come back to the ingest GPU in frame order, so the waterfall reduction and the
+ * frame-order recurrences behind it (b200_waterfall_smooth_hold; waterfall.cpp:1247-1273) see every frame.
+ * Receive buffers are double buffered: the broadcast of block k + 1 overlaps the kernels of block k.
+ * One submitting thread per group.  `stream` belongs to devices[0]; the other members work on internal streams --
+ * b200_frontend_group_sync() (or a synchronisation of every device) before reading results from another member.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_frontend_group b200_frontend_group;
+int b200_frontend_group_create(b200_frontend_group** out, const int* devices, int n_devices, double sample_rate, int decim_ratio, int dc_blocking,
+                               int invert_iq, int fft_size, double fft_rate, int fft_window, int max_block);
+int b200_frontend_group_destroy(b200_frontend_group* g);
+int b200_frontend_group_size(b200_frontend_group* g);
+int b200_frontend_group_uses_nccl(b200_frontend_group* g);      /* 1: ncclBroadcast, 0: peer copies */
+/* Member m's own front end (on devices[m]): its setters, its VFO bank (b200_frontend_vfo_bank) and the per-VFO calls
+ * (b200_vfo_set_offset, b200_vfo_set_demod, b200_vfo_out_ptr ...) with the local index from
+ * b200_frontend_group_vfo_location.  FFT / sample-rate setters must be applied to every member alike. */
+b200_frontend* b200_frontend_group_member(b200_frontend_group* g, int member);
+/* IQFrontEnd::addVFO / removeVFO over the group; returns the VFO's group id (>= 0). */
+int b200_frontend_group_add_vfo(b200_frontend_group* g, double out_samplerate, double bandwidth, double offset);
+int b200_frontend_group_remove_vfo(b200_frontend_group* g, int vfo);
+int b200_frontend_group_vfo_location(b200_frontend_group* g, int vfo, int* member, int* local_index);
+/* zoom + palette rows of every frame, in frame order, on the ingest GPU (cf. b200_frontend_attach_waterfall) */
+int b200_frontend_group_attach_waterfall(b200_frontend_group* g, struct b200_waterfall* wf, int data_width, float* d_zoom, uint32_t* d_rgba, int max_rows);
+/* One block through the group.  d_in: cf32[count] on devices[0].  The host variants copy the block to the ingest GPU
+ * first; the int16 one broadcasts the integers (4 bytes per sample over NVLink instead of 8) and converts on every
+ * member when no pre-processing is configured (volk_16i_s32f_convert_32f's arithmetic, file_source/src/main.cpp:409). */
+int b200_frontend_group_process(b200_frontend_group* g, const float* d_in, int count, void* stream);
+int b200_frontend_group_process_host(b200_frontend_group* g, const float* h_in, int count, void* stream);
+int b200_frontend_group_process_host_i16(b200_frontend_group* g, const int16_t* h_in, int count, float scalar, void* stream);
+/* dB rows of the last call on the ingest GPU, ALL frames of the block in frame order (whichever member computed them) */
+int b200_frontend_group_frame_count(b200_frontend_group* g);
+const float* b200_frontend_group_frame_ptr(b200_frontend_group* g, int i);
+int64_t b200_frontend_group_frame_index(b200_frontend_group* g, int i);
+int b200_frontend_group_sync(b200_frontend_group* g);
+/* duration of the last block's broadcast on the ingest GPU's communication stream (waits for it to finish) */
+int b200_frontend_group_broadcast_ms(b200_frontend_group* g, double* ms);
+
 /* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
 int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
 

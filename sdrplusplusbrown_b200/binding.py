@@ -87,6 +87,23 @@ _SIGS = {
     "b200_frontend_process_host_i16": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_frontend_process_host_i8": (_i, [_vp, _vp, _i, _f, _vp, _i, _vp, _vp, _vp, _vp]),
     "b200_convert_i16": (_i, [_vp, _i, _f, _vp, _vp]),
+    "b200_frontend_group_create": (_i, [_pp, _vp, _i, _d, _i, _i, _i, _i, _d, _i, _i]),
+    "b200_frontend_group_destroy": (_i, [_vp]),
+    "b200_frontend_group_size": (_i, [_vp]),
+    "b200_frontend_group_uses_nccl": (_i, [_vp]),
+    "b200_frontend_group_member": (_vp, [_vp, _i]),
+    "b200_frontend_group_add_vfo": (_i, [_vp, _d, _d, _d]),
+    "b200_frontend_group_remove_vfo": (_i, [_vp, _i]),
+    "b200_frontend_group_vfo_location": (_i, [_vp, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "b200_frontend_group_attach_waterfall": (_i, [_vp, _vp, _i, _vp, _vp, _i]),
+    "b200_frontend_group_process": (_i, [_vp, _vp, _i, _vp]),
+    "b200_frontend_group_process_host": (_i, [_vp, _vp, _i, _vp]),
+    "b200_frontend_group_process_host_i16": (_i, [_vp, _vp, _i, _f, _vp]),
+    "b200_frontend_group_frame_count": (_i, [_vp]),
+    "b200_frontend_group_frame_ptr": (_vp, [_vp, _i]),
+    "b200_frontend_group_frame_index": (C.c_int64, [_vp, _i]),
+    "b200_frontend_group_sync": (_i, [_vp]),
+    "b200_frontend_group_broadcast_ms": (_i, [_vp, C.POINTER(_d)]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
@@ -373,6 +390,81 @@ class FrontEnd:
         nf = self.frame_count()
         return dict(frames=frames[:min(nf, max_frames)] if max_frames else None, n_frames=nf,
                     vfo={v: obufs[v][:counts[v]] for v in vfos}, audio={v: abufs[v] for v in audio})
+
+
+class FrontEndGroup:
+    """IQFrontEnd over several GPUs in one process (b200_frontend_group_*): member 0 ingests and owns the display."""
+
+    def __init__(self, devices, sample_rate, decim_ratio=1, dc_blocking=False, invert_iq=False, fft_size=65536, fft_rate=20.0,
+                 fft_window=2, max_block=1000000):
+        h = _vp()
+        devs = (C.c_int * len(devices))(*devices)
+        _chk(lib.b200_frontend_group_create(C.byref(h), devs, len(devices), float(sample_rate), int(decim_ratio), int(dc_blocking), int(invert_iq),
+                                            int(fft_size), float(fft_rate), int(fft_window), int(max_block)))
+        self.h, self.devices, self.fft_size = h, list(devices), fft_size
+        self.banks = [VfoBank(0, device=d, _handle=lib.b200_frontend_vfo_bank(lib.b200_frontend_group_member(h, m))) for m, d in enumerate(devices)]
+
+    def close(self):
+        if self.h:
+            lib.b200_frontend_group_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def uses_nccl(self): return bool(_chk(lib.b200_frontend_group_uses_nccl(self.h)))
+    def add_vfo(self, out_sr, bw, offset): return _chk(lib.b200_frontend_group_add_vfo(self.h, float(out_sr), float(bw), float(offset)))
+    def remove_vfo(self, v): _chk(lib.b200_frontend_group_remove_vfo(self.h, int(v)))
+
+    def location(self, v):
+        m, loc = _i(), _i()
+        _chk(lib.b200_frontend_group_vfo_location(self.h, int(v), C.byref(m), C.byref(loc)))
+        return m.value, loc.value
+
+    def attach_waterfall(self, wf, d_zoom_ptr, d_rgba_ptr, max_rows):
+        _chk(lib.b200_frontend_group_attach_waterfall(self.h, wf.h if wf is not None else None, int(wf.w) if wf is not None else 0, d_zoom_ptr, d_rgba_ptr, int(max_rows)))
+        self._wf = wf
+
+    def process(self, d_in, count=None, stream=None):
+        if count is None:
+            count = d_in.shape[0]
+        _chk(lib.b200_frontend_group_process(self.h, d_in.data_ptr() if count else None, int(count), _stream_ptr(stream)))
+
+    def process_host(self, x, stream=None, i16_scalar=None):
+        if i16_scalar is not None:
+            x = np.ascontiguousarray(x, np.int16).reshape(-1, 2)
+            _chk(lib.b200_frontend_group_process_host_i16(self.h, x.ctypes.data, len(x), float(i16_scalar), _stream_ptr(stream)))
+        else:
+            x = np.ascontiguousarray(x, np.complex64)
+            _chk(lib.b200_frontend_group_process_host(self.h, x.ctypes.data, len(x), _stream_ptr(stream)))
+        self.sync()           # the host block may be reused by the caller
+
+    def sync(self): _chk(lib.b200_frontend_group_sync(self.h))
+    def frame_count(self): return _chk(lib.b200_frontend_group_frame_count(self.h))
+    def frame_ptr(self, i): return lib.b200_frontend_group_frame_ptr(self.h, i)
+    def frame_index(self, i): return lib.b200_frontend_group_frame_index(self.h, i)
+
+    def frames(self):
+        self.sync()
+        return [_dev_to_numpy(self.frame_ptr(i), self.fft_size, np.float32, self.devices[0]) for i in range(self.frame_count())]
+
+    def output(self, v):
+        """IF output of group VFO v (fetched from the member that owns it)"""
+        self.sync()
+        m, loc = self.location(v)
+        return self.banks[m].output(loc)
+
+    def out_count(self, v):
+        m, loc = self.location(v)
+        return self.banks[m].out_count(loc)
+
+    def broadcast_ms(self):
+        r = _d()
+        _chk(lib.b200_frontend_group_broadcast_ms(self.h, C.byref(r)))
+        return r.value
 
 
 class Waterfall:

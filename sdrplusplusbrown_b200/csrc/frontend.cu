@@ -303,6 +303,7 @@ struct FrontEnd {
     int preprocess(const cf32* dIn, int count, cudaStream_t s);
     int fftBranch(cudaStream_t s, bool append);
     int process(const cf32* dIn, int count, cudaStream_t s, bool append = false);   // append: keep the rows of the previous call(s)
+    int branches(cudaStream_t s, bool append);   // FFT branch + VFO bank on the pre-processed block
 };
 
 int FrontEnd::rebuildDecim() {
@@ -525,6 +526,11 @@ int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s, bool append) {
     if (everRan && s != lastStream) { B200_TRY(syncLast()); }
     lastStream = s; everRan = true;
     B200_TRY(preprocess(dIn, count, s));
+    return branches(s, append);
+}
+
+// the two consumers of the pre-processed block (preOut / preCount): FFT branch and VFO bank
+int FrontEnd::branches(cudaStream_t s, bool append) {
     const bool fork = bank->impl.liveCount() > 0;
     if (fork) {
         B200_CUDA(cudaEventRecord(evFork, s));
@@ -995,3 +1001,515 @@ extern "C" int b200_dc_block_noalloc(const float* d_in, float* d_out, int count,
     if (d_offset) { B200_CUDA(cudaMemcpyAsync(d_offset, &sc->state[1], sizeof(double2), cudaMemcpyDeviceToDevice, s)); }
     return B200_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------
+// Front-end group: one IQ front end spread over several GPUs of one node, inside ONE process.
+//
+// The reference fans every pre-processed block out to its consumers with Splitter::run (routing/splitter.h:74-83,
+// bound in IQFrontEnd: iq_frontend.cpp:46,79,159-179).  Here member 0 (the ingest GPU) runs the pre-processing
+// chain, the block is broadcast to the other members over NVLink, every member channelizes its own share of the VFO
+// bank (VFOs are dealt out by cost when they are added) and computes the FFT frames f with f % N == member.  The dB rows
+// travel back to the ingest GPU, which is the display owner: there they sit in frame order, so the waterfall
+// reduction and the frame-order recurrences behind it (smoothing, peak hold: waterfall.cpp:1247-1273) see every frame.
+//
+// Transport: ncclBroadcast from libnccl (loaded with dlopen; one communicator per member, one call group per block --
+// NCCL sends every byte out of the ingest GPU once, through NVSwitch multicast where it is available); when libnccl
+// cannot be loaded, cudaMemcpyPeerAsync from the ingest GPU to every member.  Receive buffers are double buffered,
+// so the broadcast of block k + 1 runs beside the kernels of block k.  Integer sources are broadcast as they arrive
+// (4 or 2 bytes per sample) and converted on every member.
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace b200 {
+namespace {
+
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*commInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*commDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*groupStart)() = nullptr;
+    ncclResult_t (*groupEnd)() = nullptr;
+    ncclResult_t (*broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char* (*errorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+
+NcclApi& ncclApi() {
+    static NcclApi a;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        if (getenv("B200_GROUP_NO_NCCL")) { return; }
+        a.lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        if (!a.lib) { return; }
+        a.commInitAll = (decltype(a.commInitAll))dlsym(a.lib, "ncclCommInitAll");
+        a.commDestroy = (decltype(a.commDestroy))dlsym(a.lib, "ncclCommDestroy");
+        a.groupStart = (decltype(a.groupStart))dlsym(a.lib, "ncclGroupStart");
+        a.groupEnd = (decltype(a.groupEnd))dlsym(a.lib, "ncclGroupEnd");
+        a.broadcast = (decltype(a.broadcast))dlsym(a.lib, "ncclBroadcast");
+        a.errorString = (decltype(a.errorString))dlsym(a.lib, "ncclGetErrorString");
+        a.ok = a.commInitAll && a.commDestroy && a.groupStart && a.groupEnd && a.broadcast && a.errorString;
+    });
+    return a;
+}
+
+#define B200_NCCL(call)                                                                                          \
+    do {                                                                                                         \
+        ncclResult_t r__ = (call);                                                                               \
+        if (r__ != ncclSuccess) { setError("%s failed: %s", #call, ncclApi().errorString(r__)); return B200_ECUDA; } \
+    } while (0)
+
+// FP32 operations per input sample of one VFO (what the dealing-out balances; same model as sharding.vfo_cost)
+double vfoCost(double inSr, double outSr, double bw) {
+    const double ratio = std::max(1.0, inSr / outSr);
+    const double stage1 = (ratio >= 16.0) ? 12.0 : 4.0 + 2.0 * 35.0;
+    const double chanTaps = (bw != outSr) ? 3.8 * outSr / (bw / 20.0) : 0.0;
+    return stage1 + (2.0 * chanTaps + 2.0 * 130.0) * outSr / inSr;
+}
+
+} // namespace
+
+struct FrontEndGroup {
+    int n = 0;
+    std::vector<int> devices;
+    std::vector<b200_frontend*> fe;                 // fe[0] = ingest GPU / display owner
+    bool useNccl = false;
+    std::vector<ncclComm_t> comms;
+    std::vector<cudaStream_t> commStream, procStream;
+    std::vector<void*> rx[2];                       // receive buffers of the members (index 0 unused)
+    size_t rxBytes = 0;
+    std::vector<cudaEvent_t> evReady[2], evFree[2], evRows;
+    bool freeArmed[2] = { false, false };
+    cudaEvent_t evPre = nullptr, evB0 = nullptr, evB1 = nullptr, evOwner = nullptr;
+    bool bTimed = false;
+    int par = 0;
+    int maxBlock = 0, fftSize = 0;
+    double effectiveSr = 0;
+    // VFOs: group id -> (member, index in the member's bank)
+    struct Loc { int member = -1, local = -1; double cost = 0; };
+    std::vector<Loc> vfos;
+    std::vector<double> load;
+    // display owner: rows of the last call in frame order
+    float* dRowsAll = nullptr; int rowsCap = 0;
+    std::vector<int64_t> frameIdx;
+    b200_waterfall* wf = nullptr; float* wfZoom = nullptr; uint32_t* wfRgba = nullptr; int wfMaxRows = 0, wfWidth = 0;
+    // host staging on the ingest GPU
+    void* dStage = nullptr; size_t stageBytes = 0;
+    cf32* dConv = nullptr; size_t convSamples = 0;    // converted block of an integer source on the ingest GPU
+
+    FrontEnd& member(int m) { return fe[m]->impl; }
+    int create(const int* devs, int nDev, double sampleRate, int decimRatio, int dcBlocking, int invertIq, int fftSize, double fftRate,
+               int fftWindow, int maxBlock);
+    void destroy();
+    int ensureRx(size_t bytes);
+    int broadcast(const void* src, size_t bytes, cudaStream_t s);       // ingest GPU's `src` -> rx[par][m] of every member
+    int run(const cf32* rootBlock, int rawKind, float scalar, int count, cudaStream_t s);
+};
+
+int FrontEndGroup::create(const int* devs, int nDev, double sampleRate, int decimRatio, int dcBlocking, int invertIq, int fftSize_, double fftRate,
+                          int fftWindow, int maxBlock_) {
+    n = nDev; maxBlock = maxBlock_; fftSize = fftSize_;
+    devices.assign(devs, devs + nDev);
+    fe.assign(n, nullptr);
+    for (int m = 0; m < n; m++) {
+        // the ingest GPU owns the pre-processing chain; the others receive its output
+        if (m == 0) { B200_TRY(b200_frontend_create(&fe[m], sampleRate, decimRatio, dcBlocking, invertIq, fftSize, fftRate, fftWindow, maxBlock, devices[m])); }
+        else { B200_TRY(b200_frontend_create(&fe[m], sampleRate / decimRatio, 1, 0, 0, fftSize, fftRate, fftWindow, maxBlock / decimRatio + 2, devices[m])); }
+        B200_TRY(b200_frontend_set_frame_shard(fe[m], m, n));
+    }
+    effectiveSr = member(0).effectiveSr;
+    load.assign(n, 0.0);
+    commStream.assign(n, nullptr); procStream.assign(n, nullptr);
+    for (int k = 0; k < 2; k++) { rx[k].assign(n, nullptr); evReady[k].assign(n, nullptr); evFree[k].assign(n, nullptr); }
+    evRows.assign(n, nullptr);
+    for (int m = 0; m < n; m++) {
+        DeviceGuard g(devices[m]);
+        B200_CUDA(cudaStreamCreateWithFlags(&commStream[m], cudaStreamNonBlocking));
+        B200_CUDA(cudaStreamCreateWithFlags(&procStream[m], cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            B200_CUDA(cudaEventCreateWithFlags(&evReady[k][m], cudaEventDisableTiming));
+            B200_CUDA(cudaEventCreateWithFlags(&evFree[k][m], cudaEventDisableTiming));
+        }
+        B200_CUDA(cudaEventCreateWithFlags(&evRows[m], cudaEventDisableTiming));
+        if (m > 0) {
+            // peer access both ways: block copies out of the ingest GPU, dB rows back into it
+            int can = 0;
+            B200_CUDA(cudaDeviceCanAccessPeer(&can, devices[m], devices[0]));
+            if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(devices[0], 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { B200_CUDA(e); } cudaGetLastError(); }
+        }
+    }
+    {
+        DeviceGuard g(devices[0]);
+        for (int m = 1; m < n; m++) {
+            int can = 0;
+            B200_CUDA(cudaDeviceCanAccessPeer(&can, devices[0], devices[m]));
+            if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(devices[m], 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { B200_CUDA(e); } cudaGetLastError(); }
+        }
+        B200_CUDA(cudaEventCreateWithFlags(&evPre, cudaEventDisableTiming));
+        B200_CUDA(cudaEventCreateWithFlags(&evOwner, cudaEventDisableTiming));
+        B200_CUDA(cudaEventCreate(&evB0)); B200_CUDA(cudaEventCreate(&evB1));
+        rowsCap = member(0).rowsCap * n + 2;
+        B200_CUDA(cudaMalloc((void**)&dRowsAll, (size_t)rowsCap * fftSize * sizeof(float)));
+    }
+    useNccl = false;
+    if (n > 1 && ncclApi().ok) {
+        comms.assign(n, nullptr);
+        B200_NCCL(ncclApi().commInitAll(comms.data(), n, devices.data()));
+        useNccl = true;
+    }
+    return B200_OK;
+}
+
+void FrontEndGroup::destroy() {
+    for (int m = 0; m < n; m++) {
+        DeviceGuard g(devices[m]);
+        if (procStream[m]) { cudaStreamSynchronize(procStream[m]); }
+        if (commStream[m]) { cudaStreamSynchronize(commStream[m]); }
+    }
+    if (useNccl) { for (auto c : comms) { if (c) { ncclApi().commDestroy(c); } } }
+    for (int m = 0; m < n; m++) {
+        DeviceGuard g(devices[m]);
+        if (fe[m]) { b200_frontend_destroy(fe[m]); }
+        for (int k = 0; k < 2; k++) {
+            if (rx[k][m]) { cudaFree(rx[k][m]); }
+            if (evReady[k][m]) { cudaEventDestroy(evReady[k][m]); }
+            if (evFree[k][m]) { cudaEventDestroy(evFree[k][m]); }
+        }
+        if (evRows[m]) { cudaEventDestroy(evRows[m]); }
+        if (procStream[m]) { cudaStreamDestroy(procStream[m]); }
+        if (commStream[m]) { cudaStreamDestroy(commStream[m]); }
+    }
+    DeviceGuard g(devices.empty() ? 0 : devices[0]);
+    cudaEvent_t evs[] = { evPre, evOwner, evB0, evB1 };
+    for (auto e : evs) { if (e) { cudaEventDestroy(e); } }
+    if (dRowsAll) { cudaFree(dRowsAll); }
+    if (dStage) { cudaFree(dStage); }
+    if (dConv) { cudaFree(dConv); }
+}
+
+int FrontEndGroup::ensureRx(size_t bytes) {
+    if (bytes <= rxBytes) { return B200_OK; }
+    const size_t want = std::max(bytes, (size_t)maxBlock * sizeof(cf32));
+    for (int m = 1; m < n; m++) {
+        DeviceGuard g(devices[m]);
+        B200_CUDA(cudaStreamSynchronize(procStream[m]));
+        B200_CUDA(cudaStreamSynchronize(commStream[m]));
+        for (int k = 0; k < 2; k++) {
+            if (rx[k][m]) { cudaFree(rx[k][m]); rx[k][m] = nullptr; }
+            B200_CUDA(cudaMalloc(&rx[k][m], want));
+        }
+    }
+    rxBytes = want;
+    freeArmed[0] = freeArmed[1] = false;
+    return B200_OK;
+}
+
+// `src` lives on the ingest GPU and is complete once everything enqueued in `s` so far has run
+int FrontEndGroup::broadcast(const void* src, size_t bytes, cudaStream_t s) {
+    if (n == 1 || bytes == 0) { return B200_OK; }
+    B200_TRY(ensureRx(bytes));
+    {
+        DeviceGuard g(devices[0]);
+        B200_CUDA(cudaEventRecord(evPre, s));
+        B200_CUDA(cudaStreamWaitEvent(commStream[0], evPre, 0));
+        // the ingest GPU sends out of `src` on its communication stream; it must also wait until every member has let go
+        // of the receive buffer this block goes into (the block two calls ago)
+        if (freeArmed[par]) { for (int m = 1; m < n; m++) { B200_CUDA(cudaStreamWaitEvent(commStream[0], evFree[par][m], 0)); } }
+        B200_CUDA(cudaEventRecord(evB0, commStream[0]));
+    }
+    if (useNccl) {
+        for (int m = 1; m < n; m++) {
+            DeviceGuard g(devices[m]);
+            if (freeArmed[par]) { B200_CUDA(cudaStreamWaitEvent(commStream[m], evFree[par][m], 0)); }
+        }
+        B200_NCCL(ncclApi().groupStart());
+        for (int m = 0; m < n; m++) {
+            DeviceGuard g(devices[m]);
+            void* dst = (m == 0) ? const_cast<void*>(src) : rx[par][m];     // in place on the root: nothing is written there
+            ncclResult_t r = ncclApi().broadcast(m == 0 ? src : dst, dst, bytes, ncclChar, 0, comms[m], commStream[m]);
+            if (r != ncclSuccess) { ncclApi().groupEnd(); setError("ncclBroadcast failed: %s", ncclApi().errorString(r)); return B200_ECUDA; }
+        }
+        B200_NCCL(ncclApi().groupEnd());
+        for (int m = 1; m < n; m++) {
+            DeviceGuard g(devices[m]);
+            B200_CUDA(cudaEventRecord(evReady[par][m], commStream[m]));
+        }
+    }
+    else {
+        // peer copies, one per member, each on the member's own communication stream (the copies share the ingest GPU's
+        // NVLink egress: N - 1 times the block leaves it, where NCCL sends it once)
+        for (int m = 1; m < n; m++) {
+            DeviceGuard g(devices[m]);
+            B200_CUDA(cudaStreamWaitEvent(commStream[m], evPre, 0));
+            if (freeArmed[par]) { B200_CUDA(cudaStreamWaitEvent(commStream[m], evFree[par][m], 0)); }
+            B200_CUDA(cudaMemcpyPeerAsync(rx[par][m], devices[m], src, devices[0], bytes, commStream[m]));
+            B200_CUDA(cudaEventRecord(evReady[par][m], commStream[m]));
+        }
+        DeviceGuard g(devices[0]);
+        for (int m = 1; m < n; m++) { B200_CUDA(cudaStreamWaitEvent(commStream[0], evReady[par][m], 0)); }
+    }
+    {
+        DeviceGuard g(devices[0]);
+        B200_CUDA(cudaEventRecord(evB1, commStream[0]));
+        bTimed = true;
+        // the caller's stream may reuse `src` (its own input buffer) once the block has left the ingest GPU
+        B200_CUDA(cudaStreamWaitEvent(s, evB1, 0));
+    }
+    return B200_OK;
+}
+
+// rawKind 0: rootBlock is cf32 on the ingest GPU, goes through the pre-processing chain, the result is broadcast.
+// rawKind 2 / 1: dStage holds int16 / int8 I/Q (no pre-processing configured): the integers are broadcast and every
+// member converts its own copy with the file source's arithmetic (x / scalar).
+int FrontEndGroup::run(const cf32* rootBlock, int rawKind, float scalar, int count, cudaStream_t s) {
+    if (count < 0 || count > maxBlock) { setError("block of %d samples exceeds max_block %d", count, maxBlock); return B200_ETOOBIG; }
+    FrontEnd& root = member(0);
+    int nPre = count;
+    const int64_t frameBefore = root.nextFrame;
+    {
+        DeviceGuard g(devices[0]);
+        if (root.everRan && s != root.lastStream) { B200_TRY(root.syncLast()); }
+        root.lastStream = s; root.everRan = true;
+        if (rawKind == 0) {
+            B200_TRY(root.preprocess(rootBlock, count, s));
+            nPre = root.preCount;
+            B200_TRY(broadcast(root.preOut, (size_t)nPre * sizeof(cf32), s));
+        }
+        else {
+            const size_t bytes = (size_t)count * (rawKind == 2 ? sizeof(short2) : sizeof(char2));
+            B200_TRY(broadcast(dStage, bytes, s));
+            if ((size_t)count > convSamples) {
+                if (dConv) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dConv); dConv = nullptr; }
+                convSamples = (size_t)std::max(count, maxBlock);
+                B200_CUDA(cudaMalloc((void**)&dConv, convSamples * sizeof(cf32)));
+            }
+            if (count > 0) {
+                if (rawKind == 2) { convertI16Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, s>>>((const short2*)dStage, (float2*)dConv, count, scalar); }
+                else { convertI8Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, s>>>((const char2*)dStage, (float2*)dConv, count, scalar); }
+                B200_CHECK_LAUNCH(); countLaunch();
+            }
+            root.preOut = dConv; root.preCount = count;
+        }
+        B200_TRY(root.branches(s, false));
+    }
+    // ---- the other members: their share of the bank and of the frames, on their own streams
+    for (int m = 1; m < n; m++) {
+        FrontEnd& f = member(m);
+        DeviceGuard g(devices[m]);
+        cudaStream_t ps = procStream[m];
+        B200_CUDA(cudaStreamWaitEvent(ps, evReady[par][m], 0));
+        const cf32* blk = (const cf32*)rx[par][m];
+        if (rawKind != 0) {
+            // converted in place is not possible (the integers are narrower): the member's staging buffer takes the floats
+            if (!f.dStageIn) { B200_CUDA(cudaMalloc((void**)&f.dStageIn, (size_t)f.maxBlock * sizeof(cf32))); }
+            if (count > 0) {
+                if (rawKind == 2) { convertI16Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, ps>>>((const short2*)rx[par][m], (float2*)f.dStageIn, count, scalar); }
+                else { convertI8Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, ps>>>((const char2*)rx[par][m], (float2*)f.dStageIn, count, scalar); }
+                B200_CHECK_LAUNCH(); countLaunch();
+            }
+            blk = f.dStageIn;
+        }
+        B200_TRY(f.process(blk, nPre, ps));
+        B200_CUDA(cudaEventRecord(evFree[par][m], ps));
+    }
+    if (n > 1) { freeArmed[par] = true; }
+    // ---- dB rows to the display owner, in frame order
+    const int64_t frameAfter = root.nextFrame;
+    const int nFrames = (int)(frameAfter - frameBefore);
+    if (nFrames > rowsCap) { setError("internal: %d frames exceed the owner's row capacity %d", nFrames, rowsCap); return B200_ESTATE; }
+    frameIdx.resize(nFrames);
+    for (int i = 0; i < nFrames; i++) { frameIdx[i] = frameBefore + i; }
+    const size_t rowBytes = (size_t)fftSize * sizeof(float);
+    for (int m = 0; m < n; m++) {
+        FrontEnd& f = member(m);
+        DeviceGuard g(devices[m]);
+        cudaStream_t ps = (m == 0) ? s : procStream[m];
+        for (size_t i = 0; i < f.frameIdx.size(); i++) {
+            const int64_t slot = f.frameIdx[i] - frameBefore;
+            if (slot < 0 || slot >= nFrames) { setError("internal: member %d produced frame %lld outside the block", m, (long long)f.frameIdx[i]); return B200_ESTATE; }
+            float* dst = dRowsAll + (size_t)slot * fftSize;
+            const float* src = f.dRows + i * (size_t)fftSize;
+            if (m == 0) { B200_CUDA(cudaMemcpyAsync(dst, src, rowBytes, cudaMemcpyDeviceToDevice, ps)); }
+            else { B200_CUDA(cudaMemcpyPeerAsync(dst, devices[0], src, devices[m], rowBytes, ps)); }
+        }
+        if (m > 0) { B200_CUDA(cudaEventRecord(evRows[m], ps)); }
+    }
+    {
+        DeviceGuard g(devices[0]);
+        for (int m = 1; m < n; m++) { B200_CUDA(cudaStreamWaitEvent(s, evRows[m], 0)); }
+        if (wf && nFrames > 0) {
+            const int k = std::min(nFrames, wfMaxRows);
+            B200_TRY(b200_waterfall_push(wf, dRowsAll, k, wfZoom, wfRgba, s));
+        }
+    }
+    par ^= 1;
+    return B200_OK;
+}
+
+} // namespace b200
+
+struct b200_frontend_group { b200::FrontEndGroup impl; };
+
+#define GROUP_OR_FAIL(g) \
+    if (!(g)) { setError("NULL front-end group handle"); return B200_EINVAL; }
+
+extern "C" {
+
+int b200_frontend_group_create(b200_frontend_group** out, const int* devices, int n_devices, double sample_rate, int decim_ratio, int dc_blocking,
+                               int invert_iq, int fft_size, double fft_rate, int fft_window, int max_block) {
+    if (!out || !devices || n_devices < 1 || n_devices > 64) { setError("bad arguments to b200_frontend_group_create"); return B200_EINVAL; }
+    for (int i = 0; i < n_devices; i++) {
+        for (int j = 0; j < i; j++) { if (devices[i] == devices[j]) { setError("device %d is listed twice", devices[i]); return B200_EINVAL; } }
+    }
+    auto* g = new (std::nothrow) b200_frontend_group;
+    if (!g) { return B200_ENOMEM; }
+    const int rc = g->impl.create(devices, n_devices, sample_rate, decim_ratio < 1 ? 1 : decim_ratio, dc_blocking, invert_iq, fft_size, fft_rate, fft_window, max_block);
+    if (rc != B200_OK) { g->impl.destroy(); delete g; return rc; }
+    *out = g;
+    return B200_OK;
+}
+
+int b200_frontend_group_destroy(b200_frontend_group* g) {
+    GROUP_OR_FAIL(g);
+    g->impl.destroy();
+    delete g;
+    return B200_OK;
+}
+
+int b200_frontend_group_size(b200_frontend_group* g) { GROUP_OR_FAIL(g); return g->impl.n; }
+int b200_frontend_group_uses_nccl(b200_frontend_group* g) { GROUP_OR_FAIL(g); return g->impl.useNccl ? 1 : 0; }
+
+b200_frontend* b200_frontend_group_member(b200_frontend_group* g, int member) {
+    if (!g || member < 0 || member >= g->impl.n) { return nullptr; }
+    return g->impl.fe[member];
+}
+
+int b200_frontend_group_add_vfo(b200_frontend_group* g, double out_samplerate, double bandwidth, double offset) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    const double cost = vfoCost(G.effectiveSr, out_samplerate, bandwidth);
+    int best = 0;
+    for (int m = 1; m < G.n; m++) { if (G.load[m] < G.load[best]) { best = m; } }
+    const int local = b200_vfo_bank_add(b200_frontend_vfo_bank(G.fe[best]), out_samplerate, bandwidth, offset);
+    if (local < 0) { return local; }
+    FrontEndGroup::Loc loc; loc.member = best; loc.local = local; loc.cost = cost;
+    G.load[best] += cost;
+    for (size_t i = 0; i < G.vfos.size(); i++) { if (G.vfos[i].member < 0) { G.vfos[i] = loc; return (int)i; } }
+    G.vfos.push_back(loc);
+    return (int)G.vfos.size() - 1;
+}
+
+int b200_frontend_group_remove_vfo(b200_frontend_group* g, int vfo) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    if (vfo < 0 || vfo >= (int)G.vfos.size() || G.vfos[vfo].member < 0) { setError("no VFO %d in the group", vfo); return B200_EINVAL; }
+    const FrontEndGroup::Loc loc = G.vfos[vfo];
+    B200_TRY(b200_vfo_bank_remove(b200_frontend_vfo_bank(G.fe[loc.member]), loc.local));
+    G.load[loc.member] -= loc.cost;
+    G.vfos[vfo] = FrontEndGroup::Loc();
+    return B200_OK;
+}
+
+int b200_frontend_group_vfo_location(b200_frontend_group* g, int vfo, int* member, int* local_index) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    if (vfo < 0 || vfo >= (int)G.vfos.size() || G.vfos[vfo].member < 0) { setError("no VFO %d in the group", vfo); return B200_EINVAL; }
+    if (member) { *member = G.vfos[vfo].member; }
+    if (local_index) { *local_index = G.vfos[vfo].local; }
+    return B200_OK;
+}
+
+int b200_frontend_group_attach_waterfall(b200_frontend_group* g, b200_waterfall* wf, int data_width, float* d_zoom, uint32_t* d_rgba, int max_rows) {
+    GROUP_OR_FAIL(g);
+    if (wf && (data_width <= 0 || max_rows <= 0 || (!d_zoom && !d_rgba))) { setError("bad arguments to b200_frontend_group_attach_waterfall"); return B200_EINVAL; }
+    FrontEndGroup& G = g->impl;
+    B200_TRY(G.member(0).syncLast());
+    G.wf = wf; G.wfZoom = d_zoom; G.wfRgba = d_rgba; G.wfMaxRows = wf ? max_rows : 0; G.wfWidth = data_width;
+    return B200_OK;
+}
+
+int b200_frontend_group_process(b200_frontend_group* g, const float* d_in, int count, void* stream) {
+    GROUP_OR_FAIL(g);
+    if (!d_in && count > 0) { setError("NULL input"); return B200_EINVAL; }
+    return g->impl.run((const cf32*)d_in, 0, 1.0f, count, (cudaStream_t)stream);
+}
+
+static int groupStage(FrontEndGroup& G, const void* h_in, size_t bytes, cudaStream_t s) {
+    DeviceGuard dg(G.devices[0]);
+    if (bytes > G.stageBytes) {
+        if (G.dStage) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(G.dStage); G.dStage = nullptr; }
+        G.stageBytes = std::max(bytes, (size_t)G.maxBlock * sizeof(cf32));
+        B200_CUDA(cudaMalloc(&G.dStage, G.stageBytes));
+    }
+    // the staging buffer of the previous call may still be read by its broadcast: the broadcast's end is ordered into `s`
+    if (bytes) { B200_CUDA(cudaMemcpyAsync(G.dStage, h_in, bytes, cudaMemcpyHostToDevice, s)); }
+    return B200_OK;
+}
+
+int b200_frontend_group_process_host(b200_frontend_group* g, const float* h_in, int count, void* stream) {
+    GROUP_OR_FAIL(g);
+    if ((!h_in && count > 0) || count < 0 || count > g->impl.maxBlock) { setError("bad block"); return B200_EINVAL; }
+    B200_TRY(groupStage(g->impl, h_in, (size_t)count * sizeof(cf32), (cudaStream_t)stream));
+    return g->impl.run((const cf32*)g->impl.dStage, 0, 1.0f, count, (cudaStream_t)stream);
+}
+
+int b200_frontend_group_process_host_i16(b200_frontend_group* g, const int16_t* h_in, int count, float scalar, void* stream) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    if ((!h_in && count > 0) || count < 0 || count > G.maxBlock || !(scalar != 0.0f)) { setError("bad block"); return B200_EINVAL; }
+    cudaStream_t s = (cudaStream_t)stream;
+    B200_TRY(groupStage(G, h_in, (size_t)count * sizeof(short2), s));
+    FrontEnd& root = G.member(0);
+    if (root.decimRatio == 1 && !root.dcBlocking && !root.invertIQ) { return G.run(nullptr, 2, scalar, count, s); }
+    // a pre-processing chain is configured: it runs on the ingest GPU on the converted block, and its output is broadcast
+    DeviceGuard dg(G.devices[0]);
+    if ((size_t)count > G.convSamples) {
+        if (G.dConv) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(G.dConv); G.dConv = nullptr; }
+        G.convSamples = (size_t)std::max(count, G.maxBlock);
+        B200_CUDA(cudaMalloc((void**)&G.dConv, G.convSamples * sizeof(cf32)));
+    }
+    if (count > 0) {
+        convertI16Kernel<<<std::min(148 * 8, (count + 255) / 256), 256, 0, s>>>((const short2*)G.dStage, (float2*)G.dConv, count, scalar);
+        B200_CHECK_LAUNCH(); countLaunch();
+    }
+    return G.run(G.dConv, 0, 1.0f, count, s);
+}
+
+int b200_frontend_group_frame_count(b200_frontend_group* g) { GROUP_OR_FAIL(g); return (int)g->impl.frameIdx.size(); }
+
+const float* b200_frontend_group_frame_ptr(b200_frontend_group* g, int i) {
+    if (!g || i < 0 || i >= (int)g->impl.frameIdx.size()) { return nullptr; }
+    return g->impl.dRowsAll + (size_t)i * g->impl.fftSize;
+}
+
+int64_t b200_frontend_group_frame_index(b200_frontend_group* g, int i) {
+    if (!g || i < 0 || i >= (int)g->impl.frameIdx.size()) { return -1; }
+    return g->impl.frameIdx[i];
+}
+
+int b200_frontend_group_sync(b200_frontend_group* g) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    for (int m = 0; m < G.n; m++) {
+        DeviceGuard dg(G.devices[m]);
+        B200_CUDA(cudaStreamSynchronize(G.procStream[m]));
+        B200_CUDA(cudaStreamSynchronize(G.commStream[m]));
+        B200_TRY(G.member(m).syncLast());
+    }
+    return B200_OK;
+}
+
+int b200_frontend_group_broadcast_ms(b200_frontend_group* g, double* ms) {
+    GROUP_OR_FAIL(g);
+    FrontEndGroup& G = g->impl;
+    if (!ms) { return B200_EINVAL; }
+    *ms = 0.0;
+    if (!G.bTimed) { return B200_OK; }
+    DeviceGuard dg(G.devices[0]);
+    B200_CUDA(cudaEventSynchronize(G.evB1));
+    float t = 0.f;
+    B200_CUDA(cudaEventElapsedTime(&t, G.evB0, G.evB1));
+    *ms = t;
+    return B200_OK;
+}
+
+} // extern "C"
