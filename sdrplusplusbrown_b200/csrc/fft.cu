@@ -32,26 +32,29 @@ __device__ __forceinline__ float2 mulNegI(float2 a) { return make_float2(a.y, -a
 // stage (and stride-2^k accesses in general) spread over the banks
 __device__ __host__ __forceinline__ int slot(int i) { return i + (i >> 4); }
 
-// exp(-2*pi*i*m/16), m = 0..15
-__device__ __forceinline__ float2 w16(int m) {
-    constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, C2 = 0.70710678118654752f;
-    switch (m & 15) {
-    case 0: return make_float2(1.f, 0.f);
-    case 1: return make_float2(C1, -S1);
-    case 2: return make_float2(C2, -C2);
-    case 3: return make_float2(S1, -C1);
-    case 4: return make_float2(0.f, -1.f);
-    case 5: return make_float2(-S1, -C1);
-    case 6: return make_float2(-C2, -C2);
-    case 7: return make_float2(-C1, -S1);
-    case 8: return make_float2(-1.f, 0.f);
-    case 9: return make_float2(-C1, S1);
-    case 10: return make_float2(-C2, C2);
-    case 11: return make_float2(-S1, C1);
-    case 12: return make_float2(0.f, 1.f);
-    case 13: return make_float2(S1, C1);
-    case 14: return make_float2(C2, C2);
-    default: return make_float2(C1, S1);
+// exp(-2*pi*i*m/32), m = 0..31 (m is a compile-time constant wherever this is called: the switch folds away)
+__device__ __forceinline__ float2 w32(int m) {
+    constexpr float C1 = 0.98078528040323044913f, S1 = 0.19509032201612826785f;   // cos, sin of 1 * pi/16
+    constexpr float C2 = 0.92387953251128675613f, S2 = 0.38268343236508977173f;   // 2 * pi/16
+    constexpr float C3 = 0.83146961230254523708f, S3 = 0.55557023301960222474f;   // 3 * pi/16
+    constexpr float C4 = 0.70710678118654752440f;                                  // 4 * pi/16
+    float c, sn;
+    switch (m & 7) {
+    case 0: c = 1.f; sn = 0.f; break;
+    case 1: c = C1; sn = S1; break;
+    case 2: c = C2; sn = S2; break;
+    case 3: c = C3; sn = S3; break;
+    case 4: c = C4; sn = C4; break;
+    case 5: c = S3; sn = C3; break;
+    case 6: c = S2; sn = C2; break;
+    default: c = S1; sn = C1; break;
+    }
+    // e^{-i a} = (c, -sn) for a in the first quadrant; every further quadrant multiplies by -i
+    switch ((m >> 3) & 3) {
+    case 0: return make_float2(c, -sn);
+    case 1: return make_float2(-sn, -c);
+    case 2: return make_float2(-c, sn);
+    default: return make_float2(sn, c);
     }
 }
 
@@ -82,7 +85,7 @@ __device__ __forceinline__ void dftComposite(float2* v) {
         for (int n1 = 0; n1 < R1; n1++) { x[n1] = v[R2 * n1 + n2]; }
         Dft<R1>::run(x);
 #pragma unroll
-        for (int k1 = 0; k1 < R1; k1++) { t[k1 * R2 + n2] = (n2 * k1 == 0) ? x[k1] : cmul(x[k1], w16(n2 * k1 * (16 / R))); }
+        for (int k1 = 0; k1 < R1; k1++) { t[k1 * R2 + n2] = (n2 * k1 == 0) ? x[k1] : cmul(x[k1], w32(n2 * k1 * (32 / R))); }
     }
 #pragma unroll
     for (int k1 = 0; k1 < R1; k1++) {
@@ -96,6 +99,7 @@ __device__ __forceinline__ void dftComposite(float2* v) {
 }
 template <> struct Dft<8> { static __device__ __forceinline__ void run(float2* v) { dftComposite<4, 2>(v); } };
 template <> struct Dft<16> { static __device__ __forceinline__ void run(float2* v) { dftComposite<4, 4>(v); } };
+template <> struct Dft<32> { static __device__ __forceinline__ void run(float2* v) { dftComposite<8, 4>(v); } };
 
 // One Stockham stage of radix R on nb rows of length L (row pitch LP slots) from src to dst.
 // Ns = product of the radices already applied.  tw[m] = exp(-2*pi*i*m/L), m < L (staged in shared memory).
@@ -310,26 +314,38 @@ __global__ void __launch_bounds__(kThreads, 3) fftPass2Kernel(int logN1, int log
 // (inter-pass twiddle or |X|^2 -> dB applied on the way).  Shared memory is touched twice per point instead of
 // ten times, there is one barrier per CTA, and every global access is a 64-128 byte contiguous run per half-warp.
 template <int RA, int RB> struct TwoStage {
+    static constexpr int L = RA * RB;
     static constexpr int TPC = RA > RB ? RA : RB;     // threads per column (row): stage 1 uses RB of them, stage 2 RA
+    // columns (rows) per tile: 16 where the tile fits twice into shared memory beside a second CTA; 8 for the 512- and
+    // 1024-point transforms (radix-32 butterflies hold 64 registers of data per thread, so a CTA is 256 threads)
+    static constexpr int LOGC = (L > 256) ? 3 : 4;
+    static constexpr int C = 1 << LOGC;
+    static constexpr int NT = C * TPC;
+    static constexpr int MINB = (L > 256) ? 1 : (512 / NT);
 };
 
-// pass 1: a tile = 16 adjacent columns n2 = c0 .. c0+15 of one frame, transforms over n1 (global stride N2).
-// Persistent CTAs: CTA b owns column block b % (N2/16) and walks the frames b / (N2/16), += gridDim.x / (N2/16), so
+// pass 1: a tile = C adjacent columns n2 = c0 .. c0+C-1 of one frame, transforms over n1 (global stride N2).
+// Persistent CTAs: CTA b owns column block b % (N2/C) and walks the frames b / (N2/C), += gridDim.x / (N2/C), so
 // its window samples and inter-pass twiddles are loaded once; the next tile's samples are in flight (cp.async into the
 // other half of a double buffer) while the current tile is transformed.  The exchange between the two stages reuses
-// the tile's own buffer.
+// the tile's own buffer.  Tile layout [point p][column] with one spare row of C elements per RA points, so that the
+// lanes of a warp (C columns x 32/C consecutive j) hit distinct banks in the stage-1 stores (p = j * RA + r) as well
+// as in the contiguous accesses.
 template <int RA, int RB>
-__global__ void __launch_bounds__(16 * TwoStage<RA, RB>::TPC, 512 / (16 * TwoStage<RA, RB>::TPC))
+__global__ void __launch_bounds__(TwoStage<RA, RB>::NT, TwoStage<RA, RB>::MINB)
 fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __restrict__ win, int nz, int logN2,
               const float2* __restrict__ twN1, const float2* __restrict__ twLo, const float2* __restrict__ twHi, int logS,
               cf32* __restrict__ scratch, int scratchFrames) {
-    constexpr int L = RA * RB, C = 16, NT = 16 * TwoStage<RA, RB>::TPC;
-    extern __shared__ __align__(16) float2 sm[];         // raw[2][L * C], [point][column]
-    const int blocksPerFrame = 1 << (logN2 - 4);
+    using TS = TwoStage<RA, RB>;
+    constexpr int L = TS::L, C = TS::C, LOGC = TS::LOGC, NT = TS::NT;
+    constexpr int TILE = (L + RB) * C;                   // padded tile: slot(p) = (p + p / RA) * C
+    extern __shared__ __align__(16) float2 sm[];         // raw[2][TILE]
+    const int blocksPerFrame = 1 << (logN2 - LOGC);
     const int cb = blockIdx.x & (blocksPerFrame - 1);
-    const int fStep = gridDim.x >> (logN2 - 4);
-    const int c = threadIdx.x & (C - 1), j = threadIdx.x >> 4;
-    const int n2 = (cb << 4) + c;
+    const int fStep = gridDim.x >> (logN2 - LOGC);
+    const int c = threadIdx.x & (C - 1), j = threadIdx.x >> LOGC;
+    const int n2 = (cb << LOGC) + c;
+    auto slotOf = [](int pnt) { return (pnt + pnt / RA) * C; };
 
     // this thread's cp.async duties for a tile: elements e = threadIdx.x + u * NT of [n1][c]
     auto issue = [&](int frame, float2* dst) {
@@ -337,15 +353,15 @@ fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __
         // element e = threadIdx.x + u * NT of [n1][c] is frame sample i0 + u * iStep
         const float2* p0 = reinterpret_cast<const float2*>(f.src0);
         const float2* p1 = reinterpret_cast<const float2*>(f.src1) - f.len0;
-        int i = ((threadIdx.x >> 4) << logN2) + (cb << 4) + (threadIdx.x & 15);
-        const int iStep = (NT >> 4) << logN2;
-        float2* d = dst + threadIdx.x;
+        int i = ((threadIdx.x >> LOGC) << logN2) + (cb << LOGC) + (threadIdx.x & (C - 1));
+        const int iStep = (NT >> LOGC) << logN2;
 #pragma unroll 4
         for (int u = 0; u < (L * C) / NT; u++) {
             const bool ok = i < nz;
             const int ii = ok ? i : 0;
-            cpAsync8(d, (ii < f.len0 ? p0 : p1) + ii, ok);
-            i += iStep; d += NT;
+            const int pnt = (threadIdx.x >> LOGC) + u * (NT >> LOGC);
+            cpAsync8(dst + slotOf(pnt) + c, (ii < f.len0 ? p0 : p1) + ii, ok);
+            i += iStep;
         }
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
@@ -368,19 +384,19 @@ fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __
         wb = cmul(__ldg(twLo + (mb & maskS)), __ldg(twHi + (mb >> logS)));
     }
 
-    int frame = blockIdx.x >> (logN2 - 4);
+    int frame = blockIdx.x >> (logN2 - LOGC);
     if (frame >= nFrames) { return; }
     issue(frame, sm);
     for (int it = 0; frame < nFrames; frame += fStep, it++) {
-        float2* raw = sm + (it & 1) * (L * C);
+        float2* raw = sm + (it & 1) * TILE;
         asm volatile("cp.async.wait_group 0;\n" ::: "memory");
         __syncthreads();                                 // tile landed; everyone is done with the previous tile
-        if (frame + fStep < nFrames) { issue(frame + fStep, sm + ((it & 1) ^ 1) * (L * C)); }
+        if (frame + fStep < nFrames) { issue(frame + fStep, sm + ((it & 1) ^ 1) * TILE); }
         float2 v[RA > RB ? RA : RB];
         if (j < RB) {
 #pragma unroll
             for (int r = 0; r < RA; r++) {
-                const float2 x = raw[(j + r * RB) * C + c];
+                const float2 x = raw[slotOf(j + r * RB) + c];
                 v[r] = make_float2(x.x * wv[r], x.y * wv[r]);
             }
             Dft<RA>::run(v);
@@ -388,12 +404,12 @@ fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __
         __syncthreads();                                 // all stage-1 reads done: the buffer becomes the exchange
         if (j < RB) {
 #pragma unroll
-            for (int r = 0; r < RA; r++) { raw[(j * RA + r) * C + c] = v[r]; }
+            for (int r = 0; r < RA; r++) { raw[(j * RA + r + j) * C + c] = v[r]; }     // slotOf(j * RA + r), r < RA
         }
         __syncthreads();
         if (j < RA) {
 #pragma unroll
-            for (int r = 0; r < RB; r++) { v[r] = raw[(j + r * RA) * C + c]; }
+            for (int r = 0; r < RB; r++) { v[r] = raw[(j + r * RA + r) * C + c]; }     // slotOf(j + r * RA), j < RA
 #pragma unroll
             for (int r = 1; r < RB; r++) { v[r] = cmul(v[r], __ldg(twN1 + j * r)); }
             Dft<RB>::run(v);
@@ -413,22 +429,23 @@ fftColsKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __
     }
 }
 
-// pass 2: a tile = 16 adjacent rows k1 = r0 .. r0+15 of one frame's intermediate (32 KB contiguous in the scratch
+// pass 2: a tile = R adjacent rows k1 = r0 .. r0+R-1 of one frame's intermediate (contiguous in the scratch
 // ring), transforms over n2; X[k1 + N1*k2].  Persistent CTAs walk the tiles in order with the next tile's copy
 // (16-byte cp.async) in flight behind the current transform; the stage-2 twiddles stay in registers for the CTA's
 // lifetime.
 template <int RA, int RB>
-__global__ void __launch_bounds__(16 * TwoStage<RA, RB>::TPC, 512 / (16 * TwoStage<RA, RB>::TPC))
+__global__ void __launch_bounds__(TwoStage<RA, RB>::NT, TwoStage<RA, RB>::MINB)
 fftRowsKernel(int logN1, int nTiles, const float2* __restrict__ twN2, const cf32* __restrict__ scratch, int frameBase,
               float* __restrict__ outDb, cf32* __restrict__ outSpec) {
-    constexpr int L = RA * RB, R = 16, NT = 16 * TwoStage<RA, RB>::TPC;
+    using TS = TwoStage<RA, RB>;
+    constexpr int L = TS::L, R = TS::C, LOGR = TS::LOGC, NT = TS::NT;
     // exchange layout [point p][row] with one pad element per RA points: the stage-1 stores (lanes step p by RA) and the
     // stage-2 loads (lanes step the row) are both conflict-free.  Each buffer first receives the raw tile [row][n2].
     constexpr int BUF = (L * R + RB + 2) & ~1;
     extern __shared__ __align__(16) float2 sm[];
     const size_t N = (size_t)L << logN1;
     const float invN = 1.0f / (float)N;
-    const int tilesPerFrame = 1 << (logN1 - 4);
+    const int tilesPerFrame = 1 << (logN1 - LOGR);
 
     auto issue = [&](int tile, float2* dst) {
         const float4* src = reinterpret_cast<const float4*>(scratch) + (size_t)tile * (L * R / 2);
@@ -442,10 +459,14 @@ fftRowsKernel(int logN1, int nTiles, const float2* __restrict__ twN2, const cf32
     };
 
     const int j1 = threadIdx.x % RB, row1 = threadIdx.x / RB;      // stage 1: lanes walk n2
-    const int row2 = threadIdx.x & (R - 1), j2 = threadIdx.x >> 4;  // stage 2: lanes walk the row (contiguous stores)
-    float2 tw[RB];
+    const int row2 = threadIdx.x & (R - 1), j2 = threadIdx.x >> LOGR;  // stage 2: lanes walk the row (contiguous stores)
+    // stage-2 twiddles W_L^(j2 * r): kept in registers where that is cheap, re-read (L1 hits) for the radix-32 forms
+    constexpr bool kTwRegs = (RB <= 16);
+    float2 tw[kTwRegs ? RB : 1];
+    if constexpr (kTwRegs) {
 #pragma unroll
-    for (int r = 1; r < RB; r++) { tw[r] = (j2 < RA) ? __ldg(twN2 + j2 * r) : make_float2(1.f, 0.f); }
+        for (int r = 1; r < RB; r++) { tw[r] = (j2 < RA) ? __ldg(twN2 + j2 * r) : make_float2(1.f, 0.f); }
+    }
 
     int tile = blockIdx.x;
     if (tile >= nTiles) { return; }
@@ -471,10 +492,10 @@ fftRowsKernel(int logN1, int nTiles, const float2* __restrict__ twN2, const cf32
 #pragma unroll
             for (int r = 0; r < RB; r++) { v[r] = buf[(j2 + r * RA) * R + r + row2]; }
 #pragma unroll
-            for (int r = 1; r < RB; r++) { v[r] = cmul(v[r], tw[r]); }
+            for (int r = 1; r < RB; r++) { v[r] = cmul(v[r], kTwRegs ? tw[kTwRegs ? r : 0] : __ldg(twN2 + j2 * r)); }
             Dft<RB>::run(v);
-            const int frame = frameBase + (tile >> (logN1 - 4));
-            const int r0 = (tile & (tilesPerFrame - 1)) << 4;
+            const int frame = frameBase + (tile >> (logN1 - LOGR));
+            const int r0 = (tile & (tilesPerFrame - 1)) << LOGR;
             const size_t k0 = (size_t)frame * N + ((size_t)j2 << logN1) + r0 + row2;
             const size_t kStep = (size_t)RA << logN1;
             if (outDb) {
@@ -494,28 +515,27 @@ fftRowsKernel(int logN1, int nTiles, const float2* __restrict__ twN2, const cf32
 template <int RA, int RB>
 int launchCols(int nf, int N2, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, int logN2, const float2* twN1,
                const float2* twLo, const float2* twHi, int logS, cf32* scratch, int scratchFrames) {
-    constexpr int L = RA * RB;
-    const size_t smem = (size_t)2 * L * 16 * sizeof(float2);
+    using TS = TwoStage<RA, RB>;
+    const size_t smem = (size_t)2 * (TS::L + RB) * TS::C * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fftColsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // persistent grid: a whole number of column-block sets, about three CTAs per SM
-    const int blocksPerFrame = N2 >> 4;
-    const int ctasPerSm = fftCtasPerSm > 0 ? fftCtasPerSm : 512 / (16 * TwoStage<RA, RB>::TPC);
+    // persistent grid: a whole number of column-block sets, as many CTAs per SM as fit
+    const int blocksPerFrame = N2 >> TS::LOGC;
+    const int ctasPerSm = fftCtasPerSm > 0 ? std::min(fftCtasPerSm, TS::MINB) : TS::MINB;
     int sets = std::max(1, (148 * ctasPerSm) / blocksPerFrame);
     sets = std::min(sets, nf);
-    fftColsKernel<RA, RB><<<sets * blocksPerFrame, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(frames, nf, win, nz, logN2, twN1, twLo, twHi, logS,
-                                                                                     scratch, scratchFrames);
+    fftColsKernel<RA, RB><<<sets * blocksPerFrame, TS::NT, smem, s>>>(frames, nf, win, nz, logN2, twN1, twLo, twHi, logS, scratch, scratchFrames);
     return B200_OK;
 }
 template <int RA, int RB>
 int launchRows(int nf, int N1, cudaStream_t s, int logN1, const float2* twN2, const cf32* scratch, int frameBase, float* outDb, cf32* outSpec) {
-    constexpr int L = RA * RB;
-    constexpr int BUF = (L * 16 + RB + 2) & ~1;
+    using TS = TwoStage<RA, RB>;
+    constexpr int BUF = (TS::L * TS::C + RB + 2) & ~1;
     const size_t smem = (size_t)2 * BUF * sizeof(float2);
     B200_CUDA(cudaFuncSetAttribute(fftRowsKernel<RA, RB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int nTiles = nf * (N1 >> 4);
-    const int ctasPerSm = fftCtasPerSm > 0 ? fftCtasPerSm : 512 / (16 * TwoStage<RA, RB>::TPC);
+    const int nTiles = nf * (N1 >> TS::LOGC);
+    const int ctasPerSm = fftCtasPerSm > 0 ? std::min(fftCtasPerSm, TS::MINB) : TS::MINB;
     const int grid = std::min(nTiles, 148 * ctasPerSm);
-    fftRowsKernel<RA, RB><<<grid, 16 * TwoStage<RA, RB>::TPC, smem, s>>>(logN1, nTiles, twN2, scratch, frameBase, outDb, outSpec);
+    fftRowsKernel<RA, RB><<<grid, TS::NT, smem, s>>>(logN1, nTiles, twN2, scratch, frameBase, outDb, outSpec);
     return B200_OK;
 }
 
@@ -625,8 +645,8 @@ int FftPlan::runPasses(const FrameDesc* dFrames, int nFrames, const float* dWind
     }
     B200_TRY(ensureScratch(nFrames));
     const int logN1 = log2i(N1), logN2 = log2i(N2);
-    if (logN1 >= 4 && logN1 <= 8 && logN2 >= 4 && logN2 <= 8) {
-        // register-resident passes (16 = 4x4, 32 = 8x4, 64 = 8x8, 128 = 16x8, 256 = 16x16)
+    if (logN1 >= 4 && logN1 <= 10 && logN2 >= 4 && logN2 <= 10) {
+        // register-resident passes (16 = 4x4, 32 = 8x4, 64 = 8x8, 128 = 16x8, 256 = 16x16, 512 = 32x16, 1024 = 32x32)
         for (int f0 = 0; f0 < nFrames; f0 += scratchFrames) {
             const int nf = std::min(scratchFrames, nFrames - f0);
             switch (logN1) {
@@ -634,7 +654,9 @@ int FftPlan::runPasses(const FrameDesc* dFrames, int nFrames, const float* dWind
             case 5: B200_TRY((launchCols<8, 4>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             case 6: B200_TRY((launchCols<8, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             case 7: B200_TRY((launchCols<16, 8>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
-            default: B200_TRY((launchCols<16, 16>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            case 8: B200_TRY((launchCols<16, 16>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            case 9: B200_TRY((launchCols<32, 16>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
+            default: B200_TRY((launchCols<32, 32>(nf, N2, s, dFrames + f0, dWindow, nz, logN2, dTwN1, dTwLo, dTwHi, logS, dScratch, scratchFrames))); break;
             }
             B200_CHECK_LAUNCH();
             switch (logN2) {
@@ -642,7 +664,9 @@ int FftPlan::runPasses(const FrameDesc* dFrames, int nFrames, const float* dWind
             case 5: B200_TRY((launchRows<8, 4>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             case 6: B200_TRY((launchRows<8, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             case 7: B200_TRY((launchRows<16, 8>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
-            default: B200_TRY((launchRows<16, 16>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            case 8: B200_TRY((launchRows<16, 16>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            case 9: B200_TRY((launchRows<32, 16>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
+            default: B200_TRY((launchRows<32, 32>(nf, N1, s, logN1, dTwN2, dScratch, f0, outDb, outSpec))); break;
             }
             B200_CHECK_LAUNCH();
             countLaunch(2);
