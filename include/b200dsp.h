@@ -146,6 +146,9 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * sweeps them. */
 #define B200_OPT_VFOS_PER_PASS 7
 #define B200_OPT_VFOS_PER_CTA 8
+/* B200_OPT_FFT_DIRECT_MAX_LOG (process-wide, default 13; 9 = off): FFT plans created afterwards use the one-pass kernel (one CTA
+ * per frame) for sizes up to 2^value and the two-pass kernels above.  Results agree to rounding. */
+#define B200_OPT_FFT_DIRECT_MAX_LOG 9
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)

@@ -146,6 +146,11 @@ int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
         fusedVfosPerCta = value;
         return B200_OK;
     }
+    if (option == B200_OPT_FFT_DIRECT_MAX_LOG) {
+        if (value < 9 || value > 14) { setError("one-pass FFT limit must be 9 (off) .. 14"); return B200_EINVAL; }
+        fftDirectMaxLog = value;
+        return B200_OK;
+    }
     if (option == B200_OPT_FFT_CTAS_PER_SM) {
         if (value < 0 || value > 4) { setError("FFT CTAs per SM must be 0 (automatic) .. 4"); return B200_EINVAL; }
         fftCtasPerSm = value;

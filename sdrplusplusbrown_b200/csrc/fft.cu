@@ -17,6 +17,7 @@
 
 namespace b200 {
 
+int fftDirectMaxLog = 13;    // largest log2(N) served by the one-pass kernel (B200_OPT_FFT_DIRECT_MAX_LOG; 9 = never)
 int fftCtasPerSm = 0;       // B200_OPT_FFT_CTAS_PER_SM: persistent CTAs per SM of the two register-resident passes; 0 = as many as fit
 
 namespace {
@@ -539,6 +540,130 @@ int launchRows(int nf, int N1, cudaStream_t s, int logN1, const float2* twN2, co
     return B200_OK;
 }
 
+// ---- N = 2^10 .. 2^14 in one pass: one CTA per frame, three register-resident Stockham stages
+// N = R0 * R1 * R2.  Every thread keeps PT = N / T points in registers: the first stage loads them straight from the frame
+// (window applied on the way; lanes read consecutive samples), stages hand over through one shared-memory buffer
+// (read everything, barrier, write in Stockham order, barrier), and the last stage's results leave from registers as dB
+// values (lanes write consecutive bins).  The samples cross HBM once and the rows once; nothing else does.
+//   stage with radix R after stages of total size Ns: butterfly j < N/R, k = j mod Ns,
+//   in x[j + r N/R] * W_{Ns R}^{k r}, out y[(j - k) R + k + r Ns]
+template <int R0, int R1, int R2> struct DirectCfg {
+    static constexpr int N = R0 * R1 * R2;
+    static constexpr int PT = (R0 == 32 || R1 == 32 || R2 == 32) ? 32 : 16;
+    static constexpr int T = N / PT;
+    // resident CTAs per SM the register allocation is held to (one frame per CTA and no prefetch: the overlap between
+    // a frame's loads and another frame's butterflies comes from the other resident CTAs)
+    static constexpr int F = (T >= 256) ? 1 : 256 / T;      // frames a CTA transforms side by side (threadIdx.y): CTAs of 256 threads
+    static constexpr int MINB = (PT == 32) ? 1 : 2;
+};
+
+template <int R, int PT, int T, int N, int NS, bool FROM_FRAME, bool TO_GLOBAL>
+__device__ __forceinline__ void directStage(float2* __restrict__ buf, const FrameDesc& f, const float* __restrict__ wv, int nz,
+                                            const float2 (*twr)[R], float* __restrict__ outDb, float2* __restrict__ outSpec, float invN) {
+    constexpr int NB = PT / R;               // butterflies per thread
+    constexpr int PER = N / R;               // butterflies per frame = input stride
+    float2 v[NB][R];
+#pragma unroll
+    for (int m = 0; m < NB; m++) {
+        const int j = threadIdx.x + m * T;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            if constexpr (FROM_FRAME) {
+                const int i = j + r * PER;
+                float2 x = make_float2(0.f, 0.f);
+                if (i < nz) { x = __ldg(frameAddr(f, i)); }
+                v[m][r] = make_float2(x.x * wv[m * R + r], x.y * wv[m * R + r]);
+            }
+            else { v[m][r] = buf[slot(j + r * PER)]; }
+        }
+        if constexpr (NS > 1) {
+#pragma unroll
+            for (int r = 1; r < R; r++) { v[m][r] = cmul(v[m][r], twr[m][r]); }
+        }
+        Dft<R>::run(v[m]);
+    }
+    if constexpr (!FROM_FRAME) { __syncthreads(); }       // every thread has read its inputs: the buffer may be overwritten
+#pragma unroll
+    for (int m = 0; m < NB; m++) {
+        const int j = threadIdx.x + m * T;
+        const int k = j & (NS - 1);
+        const int o = ((j - k) * R) + k;
+#pragma unroll
+        for (int r = 0; r < R; r++) {
+            if constexpr (TO_GLOBAL) {
+                if (outDb) { outDb[o + r * NS] = powerDb(v[m][r], invN); }
+                if (outSpec) { outSpec[o + r * NS] = v[m][r]; }
+            }
+            else { buf[slot(o + r * NS)] = v[m][r]; }
+        }
+    }
+    if constexpr (!TO_GLOBAL) { __syncthreads(); }
+}
+
+// Persistent CTAs: a thread's butterflies sit at the same places in every frame, so its window samples and the
+// twiddles of its second- and third-stage butterflies are loaded once and stay in registers for the CTA's lifetime.
+template <int R0, int R1, int R2>
+__global__ void __launch_bounds__(DirectCfg<R0, R1, R2>::T * DirectCfg<R0, R1, R2>::F, DirectCfg<R0, R1, R2>::MINB)
+fftDirectKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __restrict__ win, int nz, const float2* __restrict__ tw,
+                float* __restrict__ outDb, cf32* __restrict__ outSpec) {
+    using DC = DirectCfg<R0, R1, R2>;
+    constexpr int N = DC::N, PT = DC::PT, T = DC::T;
+    extern __shared__ __align__(16) float2 sm[];
+    const float invN = 1.0f / (float)N;
+    float wv[PT];
+    float2 tw1[PT / R1][R1], tw2[PT / R2][R2];
+#pragma unroll
+    for (int m = 0; m < PT / R0; m++) {
+#pragma unroll
+        for (int r = 0; r < R0; r++) {
+            const int i = threadIdx.x + m * T + r * (N / R0);
+            wv[m * R0 + r] = (win && i < nz) ? __ldg(win + i) : 1.0f;
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < PT / R1; m++) {
+        const int k = (threadIdx.x + m * T) & (R0 - 1);
+#pragma unroll
+        for (int r = 0; r < R1; r++) { tw1[m][r] = __ldg(tw + (k * r) * R2); }              // W_{R0 R1}^(k r)
+    }
+#pragma unroll
+    for (int m = 0; m < PT / R2; m++) {
+        const int k = threadIdx.x + m * T;                                                    // < N / R2
+#pragma unroll
+        for (int r = 0; r < R2; r++) { tw2[m][r] = __ldg(tw + k * r); }                     // W_N^(k r)
+    }
+    float2* buf = sm + threadIdx.y * (slot(N) + 1);
+    for (int base = blockIdx.x * DC::F; base < nFrames; base += gridDim.x * DC::F) {
+        const int frame = base + threadIdx.y;
+        const bool live = frame < nFrames;                // a CTA's last group may be short: idle slots still meet the barriers
+        const FrameDesc f = frames[live ? frame : base];
+        float* oDb = (outDb && live) ? outDb + (size_t)frame * N : nullptr;
+        float2* oSp = (outSpec && live) ? reinterpret_cast<float2*>(outSpec) + (size_t)frame * N : nullptr;
+        directStage<R0, PT, T, N, 1, true, false>(buf, f, wv, nz, nullptr, nullptr, nullptr, invN);
+        directStage<R1, PT, T, N, R0, false, false>(buf, f, nullptr, nz, tw1, nullptr, nullptr, invN);
+        directStage<R2, PT, T, N, R0 * R1, false, true>(buf, f, nullptr, nz, tw2, oDb, oSp, invN);
+        __syncthreads();       // the next frame's first stage writes the buffer this frame's last stage has just read
+    }
+}
+
+template <int R0, int R1, int R2>
+int launchDirect(int nFrames, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, const float2* tw, float* outDb, cf32* outSpec) {
+    using DC = DirectCfg<R0, R1, R2>;
+    const size_t smem = (size_t)DC::F * (slot(DC::N) + 1) * sizeof(float2);
+    static int perSm = 0;
+    if (perSm == 0) {
+        B200_CUDA(cudaFuncSetAttribute(fftDirectKernel<R0, R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fftDirectKernel<R0, R1, R2>, DC::T * DC::F, smem));
+        if (perSm < 1) { perSm = 1; }
+    }
+    const int groups = (nFrames + DC::F - 1) / DC::F;
+    const int grid = std::min(groups, 148 * perSm);
+    fftDirectKernel<R0, R1, R2><<<grid, dim3(DC::T, DC::F), smem, s>>>(frames, nFrames, win, nz, tw, outDb, outSpec);
+    B200_CHECK_LAUNCH();
+    countLaunch();
+    return B200_OK;
+}
+
 int uploadTwiddles(float2** d, int count, int N, int stride) {
     std::vector<float2> h((size_t)std::max(count, 1));
     for (int j = 0; j < count; j++) {
@@ -588,7 +713,8 @@ int FftPlan::create(int N_, int device_) {
     N = N_;
     logN = log2i(N);
     if ((1 << logN) != N || logN < 5 || logN > 22) { setError("fft size %d is not a power of two in [32, 4194304]", N); return B200_EINVAL; }
-    if (logN <= 9) {           // up to 512 points: one CTA per frame (measured equal at 512, slower from 1024 up); above: two register-resident passes
+    direct = (logN >= 10 && logN <= fftDirectMaxLog);
+    if (logN <= 9 || direct) {  // up to 512 points: generic one-CTA kernel; 2^10 .. 2^14: one CTA per frame, three register-resident stages
         N1 = 1; N2 = N;
         B200_TRY(uploadTwiddles(&dTwN2, N, N, 1));
     }
@@ -635,6 +761,15 @@ int FftPlan::run(const FrameDesc* dFrames, int nFrames, const float* dWindow, in
 }
 
 int FftPlan::runPasses(const FrameDesc* dFrames, int nFrames, const float* dWindow, int nz, float* outDb, cf32* outSpec, cudaStream_t s) {
+    if (N1 == 1 && direct) {
+        switch (logN) {
+        case 10: return launchDirect<16, 8, 8>(nFrames, s, dFrames, dWindow, nz, dTwN2, outDb, outSpec);
+        case 11: return launchDirect<16, 16, 8>(nFrames, s, dFrames, dWindow, nz, dTwN2, outDb, outSpec);
+        case 12: return launchDirect<16, 16, 16>(nFrames, s, dFrames, dWindow, nz, dTwN2, outDb, outSpec);
+        case 13: return launchDirect<32, 16, 16>(nFrames, s, dFrames, dWindow, nz, dTwN2, outDb, outSpec);
+        default: return launchDirect<32, 32, 16>(nFrames, s, dFrames, dWindow, nz, dTwN2, outDb, outSpec);
+        }
+    }
     if (N1 == 1) {
         const size_t smem = rowsSmem(N, 1, N);
         B200_CUDA(cudaFuncSetAttribute(fftSingleKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

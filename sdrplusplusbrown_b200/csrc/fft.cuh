@@ -7,6 +7,7 @@
 namespace b200 {
 
 extern int fftCtasPerSm;
+extern int fftDirectMaxLog;
 extern int branchOrder;    // frontend.cu
 
 // One frame of the Reshaper (keep nz samples every I): the samples may straddle the carry buffer
@@ -22,6 +23,7 @@ struct FftPlan {
     int device = 0;
     int N = 0, logN = 0;
     int N1 = 1, N2 = 0;          // N = N1 * N2; N1 == 1 -> single pass
+    bool direct = false;         // single pass by fftDirectKernel (three register-resident stages)
     float2* dTwN1 = nullptr;     // W_N1^j, j < N1/2
     float2* dTwN2 = nullptr;     // W_N2^j, j < N2/2
     float2* dTwLo = nullptr;     // W_N^j,      j < S      (inter-pass twiddle, two-level)
