@@ -662,7 +662,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=1 << 24, help="samples per step, device resident (default 16 Mi = 134 MB > L2)")
-    ap.add_argument("--e2e-batch", type=int, default=1 << 23)
+    ap.add_argument("--e2e-batch", type=int, default=1 << 24)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-samples", type=int, default=1000000, help="samples per CPU-arm step (bounded sample of the workload: one reference stream block)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

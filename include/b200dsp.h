@@ -282,7 +282,8 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i);   /* global index o
  * of `h_frames` (frame_count x fft_size floats, may be NULL) and each VFO's output (h_vfo_out[v],
  * may be NULL) / audio (h_audio[v], may be NULL; b200_vfo_audio_count(v) stereo samples, size it with
  * b200_vfo_audio_max_out).  Blocks until done.
- * Blocks of 32 MiB or more (without decimation / DC blocking / IQ inversion) are cut into 16 MiB chunks (2^21 cf32 samples):
+ * Blocks of 32 MiB or more (without decimation / DC blocking / IQ inversion) are cut into 16 MiB chunks (2^21 cf32 samples;
+ * 64 MiB chunks, from 128 MiB on, when the bank holds 64 VFOs or more):
  * the copy of the following chunks runs behind the kernels of the current one and the results travel back over the
  * other PCIe direction meanwhile (give pinned host buffers, b200_host_alloc, for that to overlap).  All dB rows of
  * the block stay resident (frame_count / frame_ptr / frame_index cover the whole block); the per-VFO device

@@ -164,6 +164,155 @@ __global__ void __launch_bounds__(kDcThreads) dcApplyKernel(const cf32* in, cf32
     }
 }
 
+// ---- the same recurrence in ONE pass over the block (16 bytes of HBM traffic per sample instead of 24): chained scan with
+// decoupled look-back.  CTAs take chunk numbers from a counter in issue order, so a chunk only ever waits for chunks
+// that are already running or done.  A chunk (2048 samples) is staged in shared memory with coalesced 16-byte copies,
+// every thread folds its 8 samples (o -> aRun * o + B_t), the CTA scans the thread folds, publishes the chunk's fold
+// (flag 1), looks back over its predecessors -- a warp at a time: 32 chunks per step, each either a bare fold or an
+// inclusive prefix, combined with the powers of aChunk -- until it meets an inclusive prefix, publishes its own
+// inclusive prefix (flag 2), and re-walks its samples from their exact entering offsets.  Same arithmetic per sample
+// as dcReduce/dcScan/dcApply above (those stay in use for b200_dc_block_noalloc).
+struct DcLookback {
+    int counter;             // next chunk to hand out
+    int pad[3];
+    // followed by: int flag[nChunks] (0 nothing, 1 fold, 2 inclusive prefix), double2 fold[nChunks], double2 prefix[nChunks]
+};
+
+__global__ void __launch_bounds__(kDcThreads, 4) dcSinglePassKernel(const cf32* __restrict__ in, cf32* __restrict__ out, int n, int nChunks, DcParams p,
+                                                                 DcLookback* __restrict__ lb, int* __restrict__ flag, double2* __restrict__ foldOf,
+                                                                 double2* __restrict__ prefixOf, double2* __restrict__ state, int conj) {
+    const bool aligned16 = (reinterpret_cast<uintptr_t>(in) & 15) == 0;      // a view that starts on an odd sample takes 8-byte loads
+    constexpr int PITCH = kDcPerThread + 1;                  // 9 float2 per thread: 72-byte stride, conflict-free 64-bit accesses
+    constexpr int NW = kDcThreads / 32;
+    __shared__ __align__(16) float2 tile[kDcThreads * PITCH];
+    __shared__ double2 sWarp[NW];                            // inclusive fold of each warp's 32 runs
+    __shared__ int sChunk;
+    __shared__ double2 sEnter;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const double2 o0 = state[0];                            // offset entering the block (only chunk 0's CTA uses it)
+    // powers of the slopes, once per CTA: aRun^(2^k) for the in-warp scan, aRun^32 per warp, aRun^tid for the re-walk,
+    // aChunk^lane and aChunk^32 for the look-back
+    double aPow[5];
+    aPow[0] = p.aRun;
+#pragma unroll
+    for (int k = 1; k < 5; k++) { aPow[k] = aPow[k - 1] * aPow[k - 1]; }
+    const double aWarp = aPow[4] * aPow[4];                 // aRun^32
+    const double aLane1 = pow(p.aRun, (double)(lane + 1));  // slope of this lane's inclusive in-warp fold
+    const double aTid = pow(p.aRun, (double)tid);
+    const double wLane = pow(p.aChunk, (double)lane);
+    const double w32 = pow(p.aChunk, 32.0);
+    while (true) {
+        __syncthreads();                                     // previous chunk's tile / sWarp / sChunk no longer in use
+        if (tid == 0) { sChunk = atomicAdd(&lb->counter, 1); }
+        __syncthreads();
+        const int c = sChunk;
+        if (c >= nChunks) { break; }
+        const int base = c * kDcChunk;
+        // ---- coalesced load: thread t brings samples 2e, 2e+1 (e = t + u * 256) into the slot of the thread that owns them
+#pragma unroll
+        for (int u = 0; u < kDcChunk / 2 / kDcThreads; u++) {
+            const int e = tid + u * kDcThreads, i = 2 * e;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (aligned16 && base + i + 1 < n) { v = __ldcs(reinterpret_cast<const float4*>(in + base) + e); }
+            else {
+                if (base + i < n) { const float2 a = reinterpret_cast<const float2*>(in)[base + i]; v.x = a.x; v.y = a.y; }
+                if (base + i + 1 < n) { const float2 a = reinterpret_cast<const float2*>(in)[base + i + 1]; v.z = a.x; v.w = a.y; }
+            }
+            float2* d = tile + (i / kDcPerThread) * PITCH + (i % kDcPerThread);
+            d[0] = make_float2(v.x, v.y); d[1] = make_float2(v.z, v.w);
+        }
+        __syncthreads();
+        float2 x[kDcPerThread];
+#pragma unroll
+        for (int i = 0; i < kDcPerThread; i++) { x[i] = tile[tid * PITCH + i]; }
+        // ---- fold of this thread's run (zero padding keeps every slope at aRun, see dcReduceKernel), inclusive scan over the
+        // warp by shuffles: S_t = aRun^d * S_{t-d} + S_t
+        const float2 b = dcRunFold(x, kDcPerThread, p.rate);
+        double sx = (double)b.x, sy = (double)b.y;
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+            const int d = 1 << k;
+            const double ux = __shfl_up_sync(0xffffffffu, sx, d), uy = __shfl_up_sync(0xffffffffu, sy, d);
+            if (lane >= d) { sx += aPow[k] * ux; sy += aPow[k] * uy; }
+        }
+        if (lane == 31) { sWarp[warp] = make_double2(sx, sy); }
+        __syncthreads();
+        // fold of everything in front of this warp inside the chunk (serial over at most 7 warp folds)
+        double px = 0.0, py = 0.0;
+        for (int w = 0; w < warp; w++) { const double2 t = sWarp[w]; px = aWarp * px + t.x; py = aWarp * py + t.y; }
+        // ---- publish the chunk's fold, look back for the offset entering the chunk, publish the inclusive prefix
+        if (warp == NW - 1) {
+            // the last warp holds the whole chunk's fold in its lane 31: B = aWarp * P + S_31
+            const double Bx = __shfl_sync(0xffffffffu, aWarp * px + sx, 31), By = __shfl_sync(0xffffffffu, aWarp * py + sy, 31);
+            double2 enter;
+            if (c == 0) { enter = o0; }
+            else {
+                if (lane == 0) {
+                    foldOf[c] = make_double2(Bx, By);
+                    __threadfence();
+                    atomicExch(&flag[c], 1);
+                }
+                // lane l looks at chunk q = c - 1 - l - 32 * step; weight of its value: aChunk^(l + 32 * step)
+                double w = wLane;
+                double2 acc = make_double2(0.0, 0.0);
+                for (int q0 = c - 1; ; q0 -= 32) {
+                    const int q = q0 - lane;
+                    int fl = 2;                                      // lanes before the block's start read as "prefix 0": stops the walk
+                    if (q >= 0) { do { fl = atomicAdd(&flag[q], 0); } while (fl == 0); }
+                    __threadfence();
+                    const unsigned full = __ballot_sync(0xffffffffu, fl == 2);
+                    const int stop = full ? (__ffs(full) - 1) : 32;    // first lane (nearest chunk) that holds an inclusive prefix
+                    double2 v = make_double2(0.0, 0.0);
+                    if (q >= 0 && lane <= stop) { v = (lane == stop) ? __ldcg(prefixOf + q) : __ldcg(foldOf + q); }
+                    double tx = w * v.x, ty = w * v.y;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) { tx += __shfl_xor_sync(0xffffffffu, tx, o); ty += __shfl_xor_sync(0xffffffffu, ty, o); }
+                    acc.x += tx; acc.y += ty;
+                    if (full) { break; }
+                    w *= w32;
+                }
+                enter = acc;
+            }
+            if (lane == 0) {
+                prefixOf[c] = make_double2(p.aChunk * enter.x + Bx, p.aChunk * enter.y + By);
+                __threadfence();
+                atomicExch(&flag[c], 2);
+                sEnter = enter;
+                if (c == nChunks - 1) {
+                    // the last chunk was zero padded to a full chunk: undo the surplus decay a^(pad)
+                    const int padN = nChunks * kDcChunk - n;
+                    const double undo = pow(p.a, -(double)padN);
+                    state[1] = make_double2((p.aChunk * enter.x + Bx) * undo, (p.aChunk * enter.y + By) * undo);
+                }
+            }
+        }
+        __syncthreads();
+        // ---- offset entering this thread's run: aRun^t * enter + (fold of the runs in front of it); then the reference's own
+        // recurrence per sample.  Fold in front = aRun^lane * (warps in front) + (this warp's lanes in front).
+        const double2 cs = sEnter;
+        double ex = __shfl_up_sync(0xffffffffu, sx, 1), ey = __shfl_up_sync(0xffffffffu, sy, 1);
+        if (lane == 0) { ex = 0.0; ey = 0.0; }
+        const double aLane = (lane == 0) ? 1.0 : aLane1 / p.aRun;      // aRun^lane
+        const double ox0 = aTid * cs.x + aLane * px + ex, oy0 = aTid * cs.y + aLane * py + ey;
+        float ox = (float)ox0, oy = (float)oy0;
+        const float sgn = conj ? -1.0f : 1.0f;
+#pragma unroll
+        for (int i = 0; i < kDcPerThread; i++) {
+            const float yx = x[i].x - ox, yy = x[i].y - oy;
+            ox += yx * p.rate; oy += yy * p.rate;
+            tile[tid * PITCH + i] = make_float2(yx, sgn * yy);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < kDcChunk / 2 / kDcThreads; u++) {
+            const int e = tid + u * kDcThreads, i = 2 * e;
+            const float2* sp = tile + (i / kDcPerThread) * PITCH + (i % kDcPerThread);
+            if (base + i + 1 < n) { __stcs(reinterpret_cast<float4*>(out + base) + e, make_float4(sp[0].x, sp[0].y, sp[1].x, sp[1].y)); }
+            else if (base + i < n) { reinterpret_cast<float2*>(out)[base + i] = sp[0]; }
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) conjKernel(const cf32* __restrict__ in, cf32* __restrict__ out, int n) {
     const int i = blockIdx.x * 256 + threadIdx.x;
     if (i < n) {
@@ -270,7 +419,8 @@ struct FrontEnd {
     // pre-processing
     std::vector<Stage> decimStages;
     cf32* dDcOut = nullptr; size_t dcCap = 0;
-    double2* dChunkB = nullptr; double2* dChunkStart = nullptr; double2* dDcState = nullptr; int dcChunksCap = 0;
+    double2* dDcState = nullptr; int dcChunksCap = 0;
+    void* dDcLookback = nullptr; size_t dcFlagBytes = 0;      // chunk counter, flags, folds and prefixes of the single-pass DC blocker
     void* dJobDesc = nullptr; size_t jobDescBytes = 0;
     PinnedRing ring;
     const cf32* preOut = nullptr; int preCount = 0;
@@ -294,6 +444,8 @@ struct FrontEnd {
     cudaStream_t hostCopyStream = nullptr;      // H2D of the next chunks while the current one is processed
     std::vector<cudaEvent_t> hostCopyDone;
     cudaEvent_t evHostStart = nullptr;
+    void* dCopyJobs = nullptr; size_t copyJobBytes = 0;                  // scatterToHostKernel's job table
+    std::vector<std::pair<const void*, float2*>> hostAlias;               // per VFO: last host output pointer seen and its device alias
 
     int init();
     void destroy();
@@ -380,7 +532,7 @@ void FrontEnd::destroy() {
     decimStages.clear();
     plan.destroy();
     ring.destroy();
-    void* ptrs[] = { dDcOut, dChunkB, dChunkStart, dDcState, dJobDesc, dWindow, dCarry, dRows, dFrameDesc, dStageIn, dStageI16 };
+    void* ptrs[] = { dDcOut, dDcLookback, dDcState, dJobDesc, dWindow, dCarry, dRows, dFrameDesc, dStageIn, dStageI16, dCopyJobs };
     for (void* p : ptrs) { if (p) { cudaFree(p); } }
 }
 
@@ -423,10 +575,11 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
         }
         const int nChunks = (n + kDcChunk - 1) / kDcChunk;
         if (nChunks > dcChunksCap) {
-            if (dChunkB) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dChunkB); cudaFree(dChunkStart); }
+            if (dDcLookback) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(dDcLookback); dDcLookback = nullptr; }
             dcChunksCap = std::max(nChunks, (int)(dcCap / kDcChunk) + 2);
-            B200_CUDA(cudaMalloc((void**)&dChunkB, (size_t)dcChunksCap * sizeof(double2)));
-            B200_CUDA(cudaMalloc((void**)&dChunkStart, (size_t)dcChunksCap * sizeof(double2)));
+            // [DcLookback][flag: int x cap, padded to 16 bytes][fold: double2 x cap][prefix: double2 x cap]
+            dcFlagBytes = ((size_t)dcChunksCap * sizeof(int) + 15) & ~(size_t)15;
+            B200_CUDA(cudaMalloc(&dDcLookback, sizeof(DcLookback) + dcFlagBytes + 2 * (size_t)dcChunksCap * sizeof(double2)));
         }
         DcParams p;
         p.rate = (float)(50.0 / effectiveSr);
@@ -435,16 +588,27 @@ int FrontEnd::preprocess(const cf32* dIn, int count, cudaStream_t s) {
         p.aChunk = pow(p.a, (double)kDcChunk);
         size_t slot = 0;
         B200_TRY(profBegin(PROF_DC, s, 16.0 * n, 6.0 * n, &slot));      // algorithmic: every sample read once, written once
-        dcReduceKernel<<<nChunks, kDcThreads, 0, s>>>(cur, n, p, dChunkB);
-        B200_CHECK_LAUNCH();
-        dcScanKernel<<<1, 1024, 0, s>>>(dChunkB, nChunks, n, p, dChunkStart, dDcState);
-        B200_CHECK_LAUNCH();
-        dcApplyKernel<<<nChunks, kDcThreads, 0, s>>>(cur, dDcOut, n, p, dChunkStart, invertIQ ? 1 : 0);
-        B200_CHECK_LAUNCH();
+        // counter and flags start at zero for every block; folds and prefixes are written before they are read
+        B200_CUDA(cudaMemsetAsync(dDcLookback, 0, sizeof(DcLookback) + dcFlagBytes, s));
+        {
+            DcLookback* lb = (DcLookback*)dDcLookback;
+            int* flag = (int*)((char*)dDcLookback + sizeof(DcLookback));
+            double2* foldOf = (double2*)((char*)flag + dcFlagBytes);
+            double2* prefixOf = foldOf + dcChunksCap;
+            static int perSm = 0;
+            if (perSm == 0) {
+                B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, dcSinglePassKernel, kDcThreads, 0));
+                if (perSm < 1) { perSm = 1; }
+            }
+            // never more CTAs than can be resident at once: a waiting CTA must not keep the chunk it waits for off the GPU
+            const int grid = std::min(nChunks, 148 * perSm);
+            dcSinglePassKernel<<<grid, kDcThreads, 0, s>>>(cur, dDcOut, n, nChunks, p, lb, flag, foldOf, prefixOf, dDcState, invertIQ ? 1 : 0);
+            B200_CHECK_LAUNCH();
+        }
         B200_TRY(profEnd(PROF_DC, slot, s));
         // state[1] -> state[0] for the next block
         B200_CUDA(cudaMemcpyAsync(dDcState, dDcState + 1, sizeof(double2), cudaMemcpyDeviceToDevice, s));
-        countLaunch(3);
+        countLaunch(1);
         cur = dDcOut;
         conjDone = invertIQ;
     }
@@ -708,6 +872,22 @@ int64_t b200_frontend_frame_index(b200_frontend* fe, int i) {
     return fe->impl.frameIdx[i];
 }
 
+// Many small results back to the host in one go: when every destination is page-locked (mapped) host memory, one
+// kernel stores all VFO outputs of a chunk straight into the callers' buffers over PCIe -- a bank of a thousand VFOs
+// would otherwise pay a thousand small cudaMemcpyAsync calls per chunk, each with its own engine latency.
+struct HostCopyJob { const float2* src; float2* dst; int n; int pad; };
+static __global__ void __launch_bounds__(256) scatterToHostKernel(const HostCopyJob* __restrict__ jobs) {
+    const HostCopyJob j = jobs[blockIdx.x];
+    for (int i = threadIdx.x; i < j.n; i += 256) { j.dst[i] = j.src[i]; }
+}
+// device-visible alias of a host pointer, or NULL when the memory is pageable (plain malloc)
+static float2* mappedAlias(const void* h) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, h) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (a.type != cudaMemoryTypeHost || !a.devicePointer) { return nullptr; }
+    return reinterpret_cast<float2*>(a.devicePointer);
+}
+
 // D2H of what the last f.process() call produced; host buffers are filled from `framesDone` / `done[v]` on
 static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& framesDone, float* const* h_vfo_out, float* const* h_audio,
                        std::vector<int>& done, std::vector<int>& audioDone, cudaStream_t s) {
@@ -719,10 +899,43 @@ static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& frames
     framesDone = std::max(framesDone, total);
     VfoBank& b = f.bank->impl;
     B200_TRY(b.joinTail());
+    // a large bank: gather the (device pointer, mapped host pointer, count) triples and let one kernel do the copies
+    bool scattered = false;
+    if (h_vfo_out && b.liveCount() >= 16) {
+        std::vector<HostCopyJob> jobs;
+        jobs.reserve(b.vfos.size());
+        bool allMapped = true;
+        if (f.hostAlias.size() != b.vfos.size()) { f.hostAlias.assign(b.vfos.size(), std::make_pair((const void*)nullptr, (float2*)nullptr)); }
+        for (size_t i = 0; i < b.vfos.size() && allMapped; i++) {
+            const Vfo& v = b.vfos[i];
+            if (!v.live || v.lastOut <= 0 || !h_vfo_out[i]) { continue; }
+            if (f.hostAlias[i].first != (const void*)h_vfo_out[i]) { f.hostAlias[i] = std::make_pair((const void*)h_vfo_out[i], mappedAlias(h_vfo_out[i])); }
+            float2* alias = f.hostAlias[i].second;
+            if (!alias) { allMapped = false; break; }
+            HostCopyJob j; j.src = reinterpret_cast<const float2*>(v.lastOutPtr); j.dst = alias + done[i]; j.n = v.lastOut; j.pad = 0;
+            jobs.push_back(j);
+        }
+        if (allMapped && !jobs.empty()) {
+            const size_t bytes = jobs.size() * sizeof(HostCopyJob);
+            if (bytes > f.copyJobBytes) {
+                if (f.dCopyJobs) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(f.dCopyJobs); f.dCopyJobs = nullptr; }
+                f.copyJobBytes = std::max(bytes * 2, (size_t)64 * 1024);
+                B200_CUDA(cudaMalloc(&f.dCopyJobs, f.copyJobBytes + 16));
+            }
+            void* hp = nullptr; int slot = 0;
+            B200_TRY(f.ring.acquire(bytes, &hp, &slot));
+            memcpy(hp, jobs.data(), bytes);
+            B200_TRY(uploadDesc(f.dCopyJobs, hp, bytes, s, b.descViaParams));
+            B200_TRY(f.ring.release(slot, s));
+            scatterToHostKernel<<<(int)jobs.size(), 256, 0, s>>>((const HostCopyJob*)f.dCopyJobs);
+            B200_CHECK_LAUNCH(); countLaunch();
+            scattered = true;
+        }
+    }
     for (size_t i = 0; i < b.vfos.size(); i++) {
         const Vfo& v = b.vfos[i];
         if (!v.live) { continue; }
-        if (v.lastOut > 0 && h_vfo_out && h_vfo_out[i]) {
+        if (!scattered && v.lastOut > 0 && h_vfo_out && h_vfo_out[i]) {
             B200_CUDA(cudaMemcpyAsync(h_vfo_out[i] + 2 * (size_t)done[i], v.lastOutPtr, (size_t)v.lastOut * sizeof(cf32), cudaMemcpyDeviceToHost, s));
         }
         done[i] += v.lastOut;
@@ -775,7 +988,10 @@ static int processHostImpl(b200_frontend* fe, const void* h_in, int sampleBytes,
     // processed and its results go back over the other PCIe direction.  The stages are streaming (results do not
     // depend on how a block is cut), and the dB rows of all chunks stay in the row buffer.  Only without
     // pre-processing, so that b200_frontend_preproc_out still names the whole block afterwards.
-    const int kChunk = (16 << 20) / sampleBytes;          // 16 MiB of host data per chunk: 2^21 cf32 or 2^22 int16 samples
+    // 16 MiB of host data per chunk (2^21 cf32 or 2^22 int16 samples) when the block's kernels are short beside its copy;
+    // a heavy bank (its kernels take several times the copy) runs 64 MiB chunks, so that the per-call fixed costs of
+    // its later stages are paid four times less often
+    const int kChunk = ((f.bank->impl.liveCount() >= 64 ? 64 : 16) << 20) / sampleBytes;
     const bool plain = f.decimRatio == 1 && !f.dcBlocking && !f.invertIQ;
     if (plain && count >= 2 * kChunk) {
         const int nChunks = (count + kChunk - 1) / kChunk;

@@ -501,3 +501,50 @@ def test_server_sample_packet_matches_the_reference_compressor(pcm):
         res = fe.process_host(payload, vfos=(v,), **kw)
         got = res["vfo"][v] if isinstance(res, dict) and "vfo" in res else res[1][v]
         assert err_db(got, ref) <= -120.0
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_process_host_returns_a_large_bank_in_one_scatter(pinned):
+    """With 16 or more VFOs b200_frontend_process_host stores all IF outputs of a chunk into the callers' buffers with
+    one kernel when those buffers are page-locked; pageable buffers take one copy per VFO.  Either way the bytes equal the
+    device-resident outputs of the same blocks, call after call (the second call continues every buffer's stream)."""
+    import ctypes
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate = 2.4e6, 8192, 20.0
+    nv = 24
+    n = 300000
+    offs = [(-1.0e6 + 80e3 * k + 7.0) for k in range(nv)]
+    x = synth.make_iq(3, 2 * n, sr, sigma=0.05, tones=[(o + 900.0, 0.02) for o in offs])
+    a = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+    b = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+    for fe in (a, b):
+        fe.vfos.set_rotator_mode(binding.ROTATOR_EXACT)
+    va = [a.vfos.add(50e3 if k % 3 else 24e3, 12.5e3 if k % 3 else 2.8e3, o) for k, o in enumerate(offs)]
+    vb = [b.vfos.add(50e3 if k % 3 else 24e3, 12.5e3 if k % 3 else 2.8e3, o) for k, o in enumerate(offs)]
+    sizes = [b.vfos.max_out(v, n) for v in vb]
+    total = sum(sizes)
+    if pinned:
+        store = torch.zeros((total, 2), dtype=torch.float32).pin_memory()
+        base, keep = store.data_ptr(), store
+        view = store.numpy().view(np.complex64).reshape(-1)
+    else:
+        view = np.zeros(total, np.complex64)
+        base, keep = view.ctypes.data, view
+    optr = (ctypes.c_void_p * (max(vb) + 1))()
+    starts, pos = [], 0
+    for v, m in zip(vb, sizes):
+        optr[v] = base + 8 * pos
+        starts.append(pos)
+        pos += m
+    counts = np.zeros(max(vb) + 1, np.int32)
+    for blk in (x[:n], x[n:]):
+        a.process(to_dev(blk))
+        xin = np.ascontiguousarray(blk)
+        rc = binding.lib.b200_frontend_process_host(b.h, xin.ctypes.data, len(xin), None, 0, optr, None, counts.ctypes.data, None)
+        assert rc == 0, binding.lib.b200_last_error()
+        for v_a, v_b, st in zip(va, vb, starts):
+            want = a.vfos.output(v_a)
+            assert counts[v_b] == len(want) > 0
+            assert np.array_equal(view[st:st + len(want)], want)
+    assert keep is not None
