@@ -372,7 +372,7 @@ def run_gpu(args):
     else:
         src = None
         bufs = [torch.empty((B, 2), dtype=torch.float32, device=dev) for _ in range(2)]
-    compute = torch.cuda.Stream(device=dev)
+    compute = torch.cuda.Stream(device=dev, priority=-1)      # above the library's deferred-tail stream (lowest priority)
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     ev_ready = [torch.cuda.Event() for _ in bufs]
     ev_free = [torch.cuda.Event() for _ in bufs]

@@ -149,6 +149,10 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
 /* B200_OPT_FFT_DIRECT_MAX_LOG (process-wide, default 13; 9 = off): FFT plans created afterwards use the one-pass kernel (one CTA
  * per frame) for sizes up to 2^value and the two-pass kernels above.  Results agree to rounding. */
 #define B200_OPT_FFT_DIRECT_MAX_LOG 9
+/* B200_OPT_SPLIT_RUNS (process-wide, default 0; measured slower on B200: 13.8 against 12.2 ms for cfg4's bank): first-stage plans whose unrolled loop body exceeds the 32 KB instruction
+ * cache level (the /8192 plan) run as two launches, each over half of every sub-block's samples, the second adding to
+ * the first's outputs.  Results agree to rounding. */
+#define B200_OPT_SPLIT_RUNS 10
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)

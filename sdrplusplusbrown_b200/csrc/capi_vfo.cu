@@ -141,6 +141,7 @@ int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
         fusedVfosPerPass = value;
         return B200_OK;
     }
+    if (option == B200_OPT_SPLIT_RUNS) { fusedSplitRuns = value != 0; return B200_OK; }
     if (option == B200_OPT_VFOS_PER_CTA) {
         if (value < 2 || value > 4096) { setError("VFOs per CTA must be 2 .. 4096"); return B200_EINVAL; }
         fusedVfosPerCta = value;

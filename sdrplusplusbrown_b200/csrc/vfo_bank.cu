@@ -403,7 +403,12 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s, const std::func
         if (!tailStream) {
             int lo = 0, hi = 0;
             B200_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-            B200_CUDA(cudaStreamCreateWithPriority(&tailStream, cudaStreamNonBlocking, hi));   // measured: the priority makes no difference (221-227 us/step either way)
+            // LOWEST priority: the tail is bandwidth-bound filler for what the next block's full-rate kernel leaves free.  With the
+            // highest priority (round 1) the tail's kernels went in front of the next block's rotator-checkpoint kernel, which then
+            // waited 2.8 ms for an SM (cfg4, 1024 VFOs) and held the whole next block back.  A caller that wants the overlap gives
+            // its own stream a higher priority than the default.
+            (void)hi;
+            B200_CUDA(cudaStreamCreateWithPriority(&tailStream, cudaStreamNonBlocking, lo));
             for (int i = 0; i < 2; i++) { B200_CUDA(cudaEventCreateWithFlags(&evTail[i], cudaEventDisableTiming)); }
         }
         // at most two blocks in flight: this block reuses the first-stage output buffers of block k-2

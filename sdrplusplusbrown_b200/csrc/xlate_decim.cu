@@ -33,6 +33,7 @@ namespace b200 {
 
 int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grouped kernel for a one-VFO launch too; 0 / 2048 = default
 int fusedVfosPerPass = 0;   // B200_OPT_VFOS_PER_PASS: 0 = by code size (launchPlan), else 2 / 4
+bool fusedSplitRuns = false;// plans whose unrolled body exceeds 32 KB run as two launches of half the runs each (B200_OPT_SPLIT_RUNS)
 int fusedVfosPerCta = 32;   // B200_OPT_VFOS_PER_CTA: VFOs a CTA of the grouped kernel serves from one staged tile
 // One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
 // the single-VFO kernel at 0.65 of the copy peak; with 16-byte cp.async.cg and LDS.128 it reaches 0.94.
@@ -223,15 +224,23 @@ __device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xr
 // through a small shared-memory exchange), one barrier, and the outputs leave.  The next pass's rotation table is
 // fetched from global memory at the start of a pass and stored at its end (two table buffers), the start phases of a
 // pass are loaded at its start and used at its end, so no global load is waited for inside the pass loop.
-template <int RATIO, int NP, int TILE, int ODD>
-__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS)
+// HALF: 0 = a CTA covers all RS runs of its sub-blocks.  1 / 2 = it covers only the lower / upper half of the runs (the
+// first / second half of every sub-block's samples) and the launch with HALF = 2 ADDS its sums to the outputs the
+// HALF = 1 launch stored: the unrolled loop body of the /8192 plan (D = 128, T = 726: 34 KB for all four runs) does
+// not fit the 32 KB instruction cache level, its two halves do.
+template <int RATIO, int NP, int TILE, int ODD, int HALF>
+__global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS / (HALF ? 2 : 1))
 fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
     constexpr int Q = (T + D - 1) / D;
     static_assert(Q <= 8, "accumulator array is sized for Q <= 8");
-    constexpr int SB = TC::SB, RS = TC::RS, DS = TC::DS, NT = TC::THREADS;
+    static_assert(HALF == 0 || TC::RS % 2 == 0, "halving needs an even number of runs");
+    constexpr int SB = TC::SB, RSA = TC::RS, DS = TC::DS;
+    constexpr int RS = HALF ? RSA / 2 : RSA;              // runs this CTA covers
+    constexpr int RUN0 = (HALF == 2) ? RSA / 2 : 0;       // ... starting with this one
+    constexpr int NT = SB * RS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
     constexpr int LP = D + 2;               // even sub-block pitch: rows 16-byte aligned, LDS.128 of a quarter-warp covers all banks
     constexpr int VB = 2 * NP;
@@ -251,7 +260,8 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
 
     const int tid = threadIdx.x;
     const int sb = tid % SB;                // sub-block of this thread
-    const int run = tid / SB;               // which DS-sample slice of it (warp-uniform: SB % 32 == 0)
+    const int runLocal = tid / SB;          // which of this CTA's runs (warp-uniform: SB % 32 == 0)
+    const int run = runLocal + RUN0;        // which DS-sample slice of the sub-block
     const int lane = tid & 31;
     const int ws = sb >> 5;
     const int g0 = blockIdx.y * GV;
@@ -263,8 +273,19 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
 
     // ---- stage the input tile once for the whole VFO range (zero outside [0, count));
     // all copies of a thread are in flight at once, no register staging
-    constexpr bool kImmediateStaging = ((2 * NT) % D == 0);   // a thread's copies land one constant smem stride apart
-    if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
+    constexpr bool kImmediateStaging = (HALF == 0) && ((2 * NT) % D == 0);   // a thread's copies land one constant smem stride apart
+    if constexpr (HALF != 0) {
+        // only the half of every row this CTA reads
+        constexpr int DH = D / 2;
+#pragma unroll 8
+        for (int i = tid; i < SB * DH; i += NT) {
+            const int rowI = i / DH, col = (i - rowI * DH) + RUN0 * DS;
+            const int m = mStart + rowI * D + col;
+            const bool ok = (m >= 0 && m < j0.count);
+            cpAsync8(xs + rowI * LP + col, in + (ok ? m : 0), ok);
+        }
+    }
+    else if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
         // interior tile: 16-byte copies (two samples, no L1 allocation), no bounds to check, and copy u of a thread is a
         // compile-time offset from copy 0 on both sides (samples 2e, 2e+1 of pair e = tid + u*NT land in slot
         // 2e + 2*(2e/D)), so the loop is LDGSTS with immediates only
@@ -346,20 +367,20 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
             for (int q = 0; q < Q; q++) { accX[p][q] = make_float2(0.f, 0.f); accY[p][q] = make_float2(0.f, 0.f); }
         }
         switch (run) {
-        case 0: accumulateRunPairs<RATIO, 0, NP, DS, ODD>(xrow, wq, accX, accY); break;
-        case 1: if constexpr (RS > 1) { accumulateRunPairs<RATIO, 1, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 2: if constexpr (RS > 2) { accumulateRunPairs<RATIO, 2, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 3: if constexpr (RS > 3) { accumulateRunPairs<RATIO, 3, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 4: if constexpr (RS > 4) { accumulateRunPairs<RATIO, 4, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 5: if constexpr (RS > 5) { accumulateRunPairs<RATIO, 5, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 6: if constexpr (RS > 6) { accumulateRunPairs<RATIO, 6, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        default: if constexpr (RS > 7) { accumulateRunPairs<RATIO, 7, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 0: if constexpr (RUN0 <= 0 && RUN0 + RS > 0) { accumulateRunPairs<RATIO, 0, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 1: if constexpr (RUN0 <= 1 && RUN0 + RS > 1) { accumulateRunPairs<RATIO, 1, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 2: if constexpr (RUN0 <= 2 && RUN0 + RS > 2) { accumulateRunPairs<RATIO, 2, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 3: if constexpr (RUN0 <= 3 && RUN0 + RS > 3) { accumulateRunPairs<RATIO, 3, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 4: if constexpr (RUN0 <= 4 && RUN0 + RS > 4) { accumulateRunPairs<RATIO, 4, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 5: if constexpr (RUN0 <= 5 && RUN0 + RS > 5) { accumulateRunPairs<RATIO, 5, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        case 6: if constexpr (RUN0 <= 6 && RUN0 + RS > 6) { accumulateRunPairs<RATIO, 6, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        default: if constexpr (RUN0 <= 7 && RUN0 + RS > 7) { accumulateRunPairs<RATIO, 7, NP, DS, ODD>(xrow, wq, accX, accY); } break;
         }
         // ---- c_q = acc_q * P, then the in-warp part of y[k] = sum_q c_q[k + q]
 #pragma unroll
         for (int p = 0; p < NP; p++) {
             float2 fX = make_float2(0.f, 0.f), fY = fX;
-            float2* hl = halo + ((((buf * NP + p) * 2) * RS + run) * WS + ws) * HQ;      // X plane; the Y plane is RS * WS * HQ further
+            float2* hl = halo + ((((buf * NP + p) * 2) * RS + runLocal) * WS + ws) * HQ;      // X plane; the Y plane is RS * WS * HQ further
 #pragma unroll
             for (int q = 0; q < Q; q++) {
                 // (cX, cY) = (accX * PX - accY * PY, accX * PY + accY * PX), lane-wise over the pair
@@ -377,7 +398,7 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
                     }
                 }
             }
-            float2* fb = fbuf + (((buf * NP + p) * 2) * RS + run) * SB + sb;
+            float2* fb = fbuf + (((buf * NP + p) * 2) * RS + runLocal) * SB + sb;
             fb[0] = fX;
             fb[RS * SB] = fY;
         }
@@ -405,8 +426,21 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
                         }
                     }
                 }
-                sOutPtr[a][k0 + k] = make_float2(yX.x, yY.x);
-                if (a + 1 < nG) { sOutPtr[a + 1][k0 + k] = make_float2(yX.y, yY.y); }
+                if constexpr (HALF == 2) {
+                    // the lower-half launch has stored its sums already (stream order): add this half
+                    float2 ya = sOutPtr[a][k0 + k];
+                    ya.x += yX.x; ya.y += yY.x;
+                    sOutPtr[a][k0 + k] = ya;
+                    if (a + 1 < nG) {
+                        float2 yb = sOutPtr[a + 1][k0 + k];
+                        yb.x += yX.y; yb.y += yY.y;
+                        sOutPtr[a + 1][k0 + k] = yb;
+                    }
+                }
+                else {
+                    sOutPtr[a][k0 + k] = make_float2(yX.x, yY.x);
+                    if (a + 1 < nG) { sOutPtr[a + 1][k0 + k] = make_float2(yX.y, yY.y); }
+                }
             }
         }
     }
@@ -588,30 +622,48 @@ __global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restric
     }
 }
 
-template <int RATIO, int NP, int TILE, int ODD>
-int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, cudaStream_t s) {
+template <int RATIO, int NP, int TILE, int ODD, int HALF>
+int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T + ODD;
     constexpr int Q = (T + D - 1) / D;
     using TC = TileCfg<D, TILE>;
-    constexpr int SB = TC::SB, RS = TC::RS;
+    constexpr int SB = TC::SB, RS = HALF ? TC::RS / 2 : TC::RS;
     constexpr int NB = SB - (Q - 1);
     constexpr size_t smem = ((size_t)SB * (D + 2) + (size_t)2 * 2 * NP * D + (size_t)2 * NP * 2 * RS * SB
                              + (size_t)2 * NP * 2 * RS * (SB / 32) * (Q * (Q - 1) / 2)) * sizeof(float2);
     static bool attrSet = false;        // per instantiation
     if (!attrSet) {
-        B200_CUDA(cudaFuncSetAttribute(fusedBankKernel<RATIO, NP, TILE, ODD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA(cudaFuncSetAttribute(fusedBankKernel<RATIO, NP, TILE, ODD, HALF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attrSet = true;
     }
     const int tiles = (nOut + NB - 1) / NB;
     dim3 grid(tiles, (nJobs + GV - 1) / GV);
+    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<grid, SB * RS, smem, s>>>(dJobs, nJobs, GV);
+    B200_CHECK_LAUNCH(); countLaunch();
+    return B200_OK;
+}
+
+template <int RATIO, int NP, int TILE, int ODD>
+int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, cudaStream_t s) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T + ODD;
+    using TC = TileCfg<D, TILE>;
     size_t slot = 0;
     // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples; algorithmic flops
     // (SURVEY 8(d)): 6 for the rotation + 4 per tap and output, i.e. 6 + 4 T/D per input sample and VFO
     B200_TRY(profBegin(PROF_STAGE1, s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs,
                        (6.0 * (double)count + 4.0 * (double)FS::T * (double)nOut) * (double)nJobs, &slot));
-    fusedBankKernel<RATIO, NP, TILE, ODD><<<grid, TC::THREADS, smem, s>>>(dJobs, nJobs, GV);
-    B200_CHECK_LAUNCH(); countLaunch();
+    // a loop body beyond the 32 KB instruction cache level runs as two launches of half the runs each
+    constexpr int kBodyBytes = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0) * NP;
+    if constexpr (kBodyBytes > 32 * 1024 && TC::RS % 2 == 0 && TC::RS >= 2) {
+        if (fusedSplitRuns) {
+            B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 1>(dJobs, nJobs, nOut, GV, s)));
+            B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 2>(dJobs, nJobs, nOut, GV, s)));
+        }
+        else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0>(dJobs, nJobs, nOut, GV, s))); }
+    }
+    else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0>(dJobs, nJobs, nOut, GV, s))); }
     B200_TRY(profEnd(PROF_STAGE1, slot, s));
     return B200_OK;
 }
@@ -685,8 +737,10 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
             // B200_OPT_VFOS_PER_PASS overrides the choice (2 or 4; results do not depend on it).
             constexpr int kBodyPair = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0);
             constexpr bool kTwoPairsFit = (2 * kBodyPair <= 34 * 1024) && (2 * D <= TileCfg<D, kTile>::THREADS);
-            int np = (kTwoPairsFit && nJobs >= 4) ? 2 : 1;
-            if (fusedVfosPerPass == 2) { np = 1; }
+            // measured (cfg3 / cfg4): one pair per pass is faster everywhere -- two pairs need 110-140 registers, and the resident
+            // warps that costs outweigh the halved tile reads (/128 plan: 1 CTA per SM, FMA pipe 38 % busy against 84 % for the
+            // one-pair /4096 plan) -- so two pairs run only when asked for
+            int np = 1;
             if (fusedVfosPerPass == 4 && kTwoPairsFit) { np = 2; }
             // VFOs per CTA: the more, the better the tile load and the CTA prologue are amortised; but keep the SMs full
             int GV = std::min(nJobs, std::min(kMaxVfosPerCta, std::max(2 * np, fusedVfosPerCta)));

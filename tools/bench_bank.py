@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--tile", type=int, default=0, help="fused-kernel tile samples (0 = library default)")
     ap.add_argument("--vb", type=int, default=0, help="VFOs per register pass of the grouped first-stage kernel (0 = library default, 2, 4)")
     ap.add_argument("--gv", type=int, default=32, help="VFOs per CTA of the grouped first-stage kernel")
+    ap.add_argument("--split", type=int, default=0, help="split plans whose loop body exceeds the instruction cache into two launches")
     args = ap.parse_args()
     cfg = configs.CONFIGS[args.cfg]
     sr = cfg["sample_rate"]
@@ -49,6 +50,7 @@ def main():
         bank.set_option(binding.OPT_TILE_SAMPLES, args.tile)
         bank.set_option(binding.OPT_VFOS_PER_PASS, args.vb)
         bank.set_option(binding.OPT_VFOS_PER_CTA, args.gv)
+        bank.set_option(binding.OPT_SPLIT_RUNS, args.split)
         instr = 0.0
         for mode, out_sr, bw, off in vfos:
             v = bank.add(out_sr, bw, off)
@@ -93,7 +95,7 @@ def main():
             "fused_hbm_frac": ((kb / args.steps) / 1e9 / (kms_per * 1e-3)) / hbm if kms_per > 0 else None,
             "fused_fp32_instr_per_s": instr * args.batch / (kms_per * 1e-3) if kms_per > 0 else None,
             "fused_fp32_frac": (instr * args.batch / (kms_per * 1e-3)) / peak_fp32 if kms_per > 0 else None,
-            "demod": args.demod, "vfos_per_pass": args.vb, "vfos_per_cta": args.gv,
+            "demod": args.demod, "vfos_per_pass": args.vb, "vfos_per_cta": args.gv, "split_runs": args.split,
         }
         print(json.dumps(line), flush=True)
         bank.close()

@@ -57,7 +57,7 @@ def main():
     d_zoom = torch.empty((max_frames, width), dtype=torch.float32, device=dev)
     d_rgba = torch.empty((max_frames, width), dtype=torch.int32, device=dev)
     x = synth.make_iq_torch(B, sr, dev, tones=[(3.3e6, 0.2)])
-    s = torch.cuda.Stream(device=dev)
+    s = torch.cuda.Stream(device=dev, priority=-1)
 
     fe.vfos.set_option(binding.OPT_BRANCH_ORDER, args.order)
     fe.vfos.set_option(binding.OPT_FFT_CTAS_PER_SM, args.fft_ctas)
