@@ -124,3 +124,60 @@ def test_iq_frontend_survives_vfo_removal_unbind_and_fft_resize_while_running(tm
     r = subprocess.run([exe, inp, str(n), str(blk)], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "dropin_remove_gpu ok" in r.stdout
+
+
+def _write_wav_int16(path, xi, samplerate):
+    """minimal RIFF/WAVE writer (PCM int16, two channels) -- the layout wav::Reader and the reference's reader expect"""
+    import struct
+    data = np.ascontiguousarray(xi, np.int16).tobytes()
+    hdr = b"RIFF" + struct.pack("<I", 36 + len(data)) + b"WAVE" + b"fmt " + struct.pack("<IHHIIHH", 16, 1, 2, int(samplerate), int(samplerate) * 4, 4, 16) + \
+        b"data" + struct.pack("<I", len(data))
+    with open(path, "wb") as f:
+        f.write(hdr + data)
+
+
+def test_file_source_program_compiles(tmp_path):
+    _compile(os.path.join(ROOT, "tests", "cpp", "file_source_gpu.cpp"), str(tmp_path / "file_source_gpu"))
+
+
+@pytest.mark.gpu
+def test_wav_file_source_through_the_front_end_matches_the_oracle(tmp_path):
+    """The reference's in-app scenario (tests/baseband_file_test.cpp:41-53: File source, a baseband WAV, radio VFO in USB)
+    on a synthetic int16 capture: file -> WavFileSource -> front end -> 24 kS/s USB channel, through the reference's own
+    arrangement (worker thread, dsp::stream, IQFrontEnd) and through the int16 pump; both against the oracle's RxVFO fed
+    with the file source's conversion (x / 32768)."""
+    import oracle_lib as ol
+    from gpu_util import err_db
+    from sdrplusplusbrown_b200 import synth
+    exe = str(tmp_path / "file_source_gpu")
+    _compile(os.path.join(ROOT, "tests", "cpp", "file_source_gpu.cpp"), exe)
+    sr = 2.4e6
+    blk = int(np.float32(sr) / np.float32(200.0))          # the reference's block: sampleRate / 200
+    blocks = 24
+    x = synth.make_iq(0, blk * blocks, sr, sigma=0.02, tones=[(10e3 + 900.0, 0.2), (-300e3, 0.1)])
+    xi = np.round(x.view(np.float32).reshape(-1, 2) * 20000.0).astype(np.int16)
+    wav = str(tmp_path / "baseband_2400000Hz.wav")
+    _write_wav_int16(wav, xi, sr)
+    outp = str(tmp_path / "out.bin")
+    r = subprocess.run([exe, wav, str(blocks), outp], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(outp, "rb").read()
+    na, nb, ra, rb = np.frombuffer(raw[:16], np.int32)
+    pos = 16
+    got_a = np.frombuffer(raw[pos:pos + 8 * na], np.complex64); pos += 8 * na
+    got_b = np.frombuffer(raw[pos:pos + 8 * nb], np.complex64); pos += 8 * nb
+    rows_a = np.frombuffer(raw[pos:pos + 4 * 8192 * ra], np.float32).reshape(ra, 8192); pos += 4 * 8192 * ra
+    rows_b = np.frombuffer(raw[pos:pos + 4 * 8192 * rb], np.float32).reshape(rb, 8192)
+    xf = (xi.astype(np.float32) / np.float32(32768.0)).view(np.complex64).reshape(-1)
+    port = ol.Oracle("port")
+    o = ol.Vfo(port, sr, 24e3, 2.8e3, 10e3)
+    ref = np.concatenate([o.process(xf[i:i + blk]) for i in range(0, len(xf), blk)])
+    assert nb == len(ref) and na >= len(ref) - blk // 100 - 1          # the stream path stops after `blocks` non-empty swaps
+    assert err_db(got_b, ref) <= -80.0
+    assert err_db(got_a[:min(na, len(ref))], ref[:min(na, len(ref))]) <= -80.0
+    w = port.fft_window(2, 8192)
+    want_rows = [port.fft_frame(xf[f * 120000:f * 120000 + 8192], w, 8192) for f in range(rb)]
+    assert rb == 3 and ra >= 2
+    for got, want in list(zip(rows_b, want_rows)) + list(zip(rows_a[:2], want_rows[:2])):
+        strong = want > want.max() - 80.0
+        assert np.max(np.abs(got[strong] - want[strong])) <= 0.01
