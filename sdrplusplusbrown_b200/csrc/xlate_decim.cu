@@ -217,7 +217,7 @@ __device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xr
     }
 }
 
-// grid.x = output tiles, grid.y = ranges of GV VFOs; all jobs of a launch share in/count/offset/nOut.
+// one CTA per (output tile, range of GV VFOs); all jobs of a launch share in/count/offset/nOut.
 // A CTA stages its input tile once and walks its VFO range in passes of VB = 2 * NP VFOs.  Per pass: the threads
 // accumulate (above), multiply by their sub-block's start phase, fold the Q partial sums of neighbouring sub-blocks
 // with warp shuffles (output k = sum_q c_q[k + q]; what crosses a warp boundary or comes from another run goes
@@ -264,9 +264,12 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
     const int run = runLocal + RUN0;        // which DS-sample slice of the sub-block
     const int lane = tid & 31;
     const int ws = sb >> 5;
-    const int g0 = blockIdx.y * GV;
+    // one-dimensional grid, VFO range fastest: the CTAs that share an input tile run at the same time, so only the first of
+    // them brings the tile in from HBM and the others find it in L2
+    const int nRanges = (nJobs + GV - 1) / GV;
+    const int g0 = (int)(blockIdx.x % nRanges) * GV;
     const FusedJob j0 = jobs[g0];
-    const int k0 = blockIdx.x * NB;
+    const int k0 = (int)(blockIdx.x / nRanges) * NB;
     if (k0 >= j0.nOut) { return; }
     const int mStart = j0.offset - H - ODD + k0 * D;     // sample index of this tile's first sub-block (even, 16-byte aligned address)
     const float2* in = reinterpret_cast<const float2*>(j0.in);
@@ -638,8 +641,9 @@ int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStr
         attrSet = true;
     }
     const int tiles = (nOut + NB - 1) / NB;
-    dim3 grid(tiles, (nJobs + GV - 1) / GV);
-    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<grid, SB * RS, smem, s>>>(dJobs, nJobs, GV);
+    const long long ctas = (long long)tiles * ((nJobs + GV - 1) / GV);
+    if (ctas > 0x7fffffffLL) { setError("first-stage launch of %lld CTAs is too large", ctas); return B200_ETOOBIG; }
+    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<(unsigned)ctas, SB * RS, smem, s>>>(dJobs, nJobs, GV);
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }
