@@ -42,6 +42,17 @@ inline void countLaunch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memo
         if (rc__ != B200_OK) { return rc__; }  \
     } while (0)
 
+#ifdef __CUDACC__
+// Blackwell's packed FP32 pair arithmetic (fma.rn.f32x2 -> SASS FFMA2): two IEEE FMAs in one issue slot.  A scalar
+// multiplier is given as the pair (h, h); ptxas folds it into the instruction's broadcast operand form.
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra, rb, rc, rd;
+    ra = *reinterpret_cast<unsigned long long*>(&a); rb = *reinterpret_cast<unsigned long long*>(&b); rc = *reinterpret_cast<unsigned long long*>(&c);
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    return *reinterpret_cast<float2*>(&rd);
+}
+#endif
+
 // RAII device selection
 struct DeviceGuard {
     int prev = -1;

@@ -69,7 +69,8 @@ template <int EF> struct Elem;
 template <> struct Elem<2> {
     using T = float2;
     static __device__ __forceinline__ T zero() { return make_float2(0.f, 0.f); }
-    static __device__ __forceinline__ void fma(T& a, float t, T x) { a.x = fmaf(t, x.x, a.x); a.y = fmaf(t, x.y, a.y); }
+    // complex sample x real tap: one packed FMA (both components round exactly as two scalar fmaf would)
+    static __device__ __forceinline__ void fma(T& a, float t, T x) { a = fma2(make_float2(t, t), x, a); }
     static __device__ __forceinline__ void add(T& a, T b) { a.x += b.x; a.y += b.y; }
     static __device__ __forceinline__ T shflXor(T a, int m) { return make_float2(__shfl_xor_sync(0xffffffffu, a.x, m), __shfl_xor_sync(0xffffffffu, a.y, m)); }
     // shared-memory slot of window position p (simple path): one pad element per 16 keeps lanes that step by 1, 2, 4
@@ -224,8 +225,7 @@ __device__ __forceinline__ void planStage(const FirJob& j, float2* win) {
         for (int r = 0; r < R; r++) {
             if (q - r * D >= 0 && q - r * D < T) {
                 const float h = PlanStage<D, T>::tap(q - r * D);
-                acc[r].x = fmaf(h, x.x, acc[r].x);
-                acc[r].y = fmaf(h, x.y, acc[r].y);
+                acc[r] = fma2(make_float2(h, h), x, acc[r]);
             }
         }
     }
