@@ -154,6 +154,12 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * the first's outputs.  Results agree to rounding. */
 #define B200_OPT_SPLIT_RUNS 10
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
+/* The process-wide switches above without a handle (B200_OPT_FUSED_STAGE1, _TILE_SAMPLES, _FFT_CTAS_PER_SM, _BRANCH_ORDER,
+ * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS).  b200_vfo_bank_set_option forwards these here: naming a
+ * bank does NOT confine them to that bank -- every bank and front end of the process sees the change.  Only
+ * B200_OPT_CALIBRATION_STEPS is per bank; B200_OPT_DEFER_TAIL is process-wide too but is switched through a bank handle,
+ * because that bank's deferred work is drained first.  Calls are serialised by the library. */
+int b200_set_global_option(int option, int value);
 
 /* info[0]=mode (0 BOTH, 1 DECIM_ONLY, 2 RESAMP_ONLY, 3 NONE; rational_resampler.h:120-125)
  * [1]=power-of-two ratio [2]=interp [3]=decim [4]=resampler tap count [5]=taps per phase

@@ -46,6 +46,7 @@ _SIGS = {
     "b200_vfo_describe": (_i, [_vp, _i, _vp]),
     "b200_vfo_bank_set_rotator_mode": (_i, [_vp, _i]),
     "b200_vfo_bank_set_option": (_i, [_vp, _i, _i]),
+    "b200_set_global_option": (_i, [_i, _i]),
     "b200_vfo_get_taps": (_i, [_vp, _i, _i, _vp, _i]),
     "b200_vfo_bank_process": (_i, [_vp, _vp, _i, _vp]),
     "b200_vfo_out_count": (_i, [_vp, _i]),

@@ -2,6 +2,8 @@
 #include <cmath>
 #include <cstring>
 
+#include <mutex>
+
 #include "vfo_bank.cuh"
 #include "fft.cuh"
 #include "xlate_decim.cuh"
@@ -122,53 +124,64 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode) {
     return bank->impl.setRotatorMode(mode);
 }
 
+// Process-wide tuning switches (they select kernels / schedules, never results).  One mutex orders concurrent callers; a
+// switch that changes how the next block is scheduled takes effect at each handle's next process call.
+static std::mutex g_optMtx;
+
+int b200_set_global_option(int option, int value) {
+    std::lock_guard<std::mutex> lk(g_optMtx);
+    switch (option) {
+    case B200_OPT_FUSED_STAGE1: fusedEnabled = value != 0; return B200_OK;
+    case B200_OPT_TILE_SAMPLES:
+        if (value != 0 && value != 2048 && value != 4096) { setError("tile must be 0 (automatic), 2048 or 4096"); return B200_EINVAL; }
+        fusedTileSamples = value;
+        return B200_OK;
+    case B200_OPT_VFOS_PER_PASS:
+        if (value != 0 && value != 2 && value != 4) { setError("VFOs per register pass must be 0 (automatic), 2 or 4"); return B200_EINVAL; }
+        fusedVfosPerPass = value;
+        return B200_OK;
+    case B200_OPT_SPLIT_RUNS: fusedSplitRuns = value != 0; return B200_OK;
+    case B200_OPT_VFOS_PER_CTA:
+        if (value < 2 || value > 4096) { setError("VFOs per CTA must be 2 .. 4096"); return B200_EINVAL; }
+        fusedVfosPerCta = value;
+        return B200_OK;
+    case B200_OPT_FFT_DIRECT_MAX_LOG:
+        if (value < 9 || value > 14) { setError("one-pass FFT limit must be 9 (off) .. 14"); return B200_EINVAL; }
+        fftDirectMaxLog = value;
+        return B200_OK;
+    case B200_OPT_FFT_CTAS_PER_SM:
+        if (value < 0 || value > 4) { setError("FFT CTAs per SM must be 0 (automatic) .. 4"); return B200_EINVAL; }
+        fftCtasPerSm = value;
+        return B200_OK;
+    case B200_OPT_BRANCH_ORDER:
+        if (value != 0 && value != 1) { setError("branch order must be 0 or 1"); return B200_EINVAL; }
+        branchOrder = value;
+        return B200_OK;
+    default:
+        setError("option %d is not process-wide (or unknown)", option);
+        return B200_EINVAL;
+    }
+}
+
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value) {
     BANK_OR_FAIL(bank);
-    if (option == B200_OPT_FUSED_STAGE1) { fusedEnabled = value != 0; return B200_OK; }
+    // per-handle switches
     if (option == B200_OPT_CALIBRATION_STEPS) {
         if (value < 0) { setError("bad calibration length"); return B200_EINVAL; }
         bank->impl.calSteps = value;
         for (auto& v : bank->impl.vfos) { v.calDirty = true; }
         return B200_OK;
     }
-    if (option == B200_OPT_TILE_SAMPLES) {
-        if (value != 0 && value != 2048 && value != 4096) { setError("tile must be 0 (automatic), 2048 or 4096"); return B200_EINVAL; }
-        fusedTileSamples = value;
-        return B200_OK;
-    }
-    if (option == B200_OPT_VFOS_PER_PASS) {
-        if (value != 0 && value != 2 && value != 4) { setError("VFOs per register pass must be 0 (automatic), 2 or 4"); return B200_EINVAL; }
-        fusedVfosPerPass = value;
-        return B200_OK;
-    }
-    if (option == B200_OPT_SPLIT_RUNS) { fusedSplitRuns = value != 0; return B200_OK; }
-    if (option == B200_OPT_VFOS_PER_CTA) {
-        if (value < 2 || value > 4096) { setError("VFOs per CTA must be 2 .. 4096"); return B200_EINVAL; }
-        fusedVfosPerCta = value;
-        return B200_OK;
-    }
-    if (option == B200_OPT_FFT_DIRECT_MAX_LOG) {
-        if (value < 9 || value > 14) { setError("one-pass FFT limit must be 9 (off) .. 14"); return B200_EINVAL; }
-        fftDirectMaxLog = value;
-        return B200_OK;
-    }
-    if (option == B200_OPT_FFT_CTAS_PER_SM) {
-        if (value < 0 || value > 4) { setError("FFT CTAs per SM must be 0 (automatic) .. 4"); return B200_EINVAL; }
-        fftCtasPerSm = value;
-        return B200_OK;
-    }
     if (option == B200_OPT_DEFER_TAIL) {
+        // the mode itself is process-wide, but switching it needs THIS bank's deferred work drained first; other banks
+        // pick the new mode up at their next process call (each drains its own tail when it finds the mode changed)
         B200_TRY(bank->impl.syncLast());
+        std::lock_guard<std::mutex> lk(g_optMtx);
         deferTail = value != 0;
         return B200_OK;
     }
-    if (option == B200_OPT_BRANCH_ORDER) {
-        if (value != 0 && value != 1) { setError("branch order must be 0 or 1"); return B200_EINVAL; }
-        branchOrder = value;
-        return B200_OK;
-    }
-    setError("unknown option %d", option);
-    return B200_EINVAL;
+    // everything else is process-wide: same effect as b200_set_global_option, whichever handle is named
+    return b200_set_global_option(option, value);
 }
 
 int b200_vfo_describe(b200_vfo_bank* bank, int vfo, int* info) {
