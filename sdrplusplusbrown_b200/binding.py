@@ -14,8 +14,22 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200dsp.so")
 
-if not os.path.exists(LIB_PATH) or _build.stale():
-    _build.build()
+def _ensure_built():
+    """Build the library when it is missing or older than its sources -- under a file lock, so that several ranks
+    importing this module at once (torchrun) do not run nvcc into the same output at the same time."""
+    if os.path.exists(LIB_PATH) and not _build.stale():
+        return
+    import fcntl
+    with open(os.path.join(_HERE, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not os.path.exists(LIB_PATH) or _build.stale():      # another rank may have built it while we waited
+                _build.build()
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+_ensure_built()
 lib = C.CDLL(LIB_PATH)
 
 _vp, _i, _d, _f, _pp = C.c_void_p, C.c_int, C.c_double, C.c_float, C.POINTER(C.c_void_p)

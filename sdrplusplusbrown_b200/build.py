@@ -66,7 +66,10 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed; see sdrplusplusbrown_b200/build/nvcc.log")
     if verbose:
         sys.stdout.write("\n".join(log))
-    subprocess.check_call([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", OUT] + objs + ["-lcudart"])
+    # link beside the target and move into place: a process that loads the library meanwhile never sees half a file
+    tmp = OUT + ".tmp.%d" % os.getpid()
+    subprocess.check_call([NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp] + objs + ["-lcudart"])
+    os.replace(tmp, OUT)
     return OUT
 
 

@@ -24,6 +24,7 @@ sys.path.insert(0, ROOT)
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cfg", default="cfg3")
+    ap.add_argument("--vfos", type=int, default=0, help="BASELINE config[4] (cfg5): this many NFM VFOs at cfg3's rate instead of the configuration's own bank (1 ... 4096)")
     ap.add_argument("--batch", type=int, default=1 << 24)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
@@ -54,6 +55,14 @@ def main():
     if world > 1:
         fe.set_frame_shard(rank, world)
     vl = configs.vfo_list(args.cfg)
+    if args.vfos > 0:
+        # cfg5: the NFM bank of cfg3 swept in size; beyond the 256 grid points the offsets are spread over the band
+        import numpy as np
+        if args.vfos <= len(vl):
+            vl = vl[:args.vfos]
+        else:
+            rng = np.random.default_rng(4096)
+            vl = [("NFM48", 48000.0, 12500.0, float(f)) for f in np.sort(rng.uniform(-0.45 * sr, 0.45 * sr, args.vfos))]
     # deal the bank out by cost (WFM > SSB > AM; sharding.shard_vfos, the same function the gloo tests cover).
     # For cfg4 that is 64 AM + 48 SSB + 16 WFM on every one of 8 ranks -- the mix the recorded 46.4 x run had, dealt there
     # mode by mode (the j-th VFO of a mode to rank j % N); plain i % N puts cfg4's 128 WFM channels on one rank.
@@ -79,7 +88,7 @@ def main():
         bufs = [src, src]
     else:
         bufs = [torch.empty((B, 2), dtype=torch.float32, device=dev) for _ in range(2)]
-    compute = torch.cuda.Stream(device=dev)
+    compute = torch.cuda.Stream(device=dev, priority=-1)
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     ev_ready = [torch.cuda.Event() for _ in bufs]
     ev_free = [torch.cuda.Event() for _ in bufs]
@@ -136,7 +145,7 @@ def main():
         n = min(args.steps, 64)
         bc = sum(ev_b0[i].elapsed_time(ev_b1[i]) for i in range(n)) / n
     if rank == 0:
-        line = {"cfg": args.cfg, "n_gpus": world, "vfos_total": len(vl), "vfos_per_gpu": len(mine), "demod": bool(args.demod), "wfm_stereo": bool(args.wfm_stereo) if args.demod else None,
+        line = {"cfg": args.cfg if args.vfos == 0 else "cfg5 (%d NFM VFOs at %s's rate)" % (args.vfos, args.cfg), "n_gpus": world, "vfos_total": len(vl), "vfos_per_gpu": len(mine), "demod": bool(args.demod), "wfm_stereo": bool(args.wfm_stereo) if args.demod else None,
                 "batch": B, "steps": args.steps, "ms_per_block": ms / args.steps,
                 "input_MSps": B * args.steps / (ms * 1e-3) / 1e6, "x_real_time": B * args.steps / (ms * 1e-3) / sr,
                 "broadcast_ms_per_block_rank0": bc, "scaling": "strong", "defer_tail": args.defer_tail,
