@@ -153,9 +153,16 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * cache level (the /8192 plan) run as two launches, each over half of every sub-block's samples, the second adding to
  * the first's outputs.  Results agree to rounding. */
 #define B200_OPT_SPLIT_RUNS 10
+/* B200_OPT_LEAVE_ROOM (process-wide, default 0): 1 = in streaming mode (B200_OPT_DEFER_TAIL) the first-stage bank kernel is
+ * launched as a persistent grid that leaves about 40 KB of shared memory and 17 K registers free on every SM, so that the
+ * previous block's later stages (bandwidth-bound, on their own low-priority stream) run beside it.  Measured on cfg4: the
+ * later stages then do overlap (profiles/r02_timeline_cfg4_room.txt), but the bank kernels lose more (12.2 -> 16.3 ms per
+ * block with one resident CTA fewer per SM and the shared L1 / issue slots) than the 2.7 ms the overlap hides: 16.8 against
+ * 15.2 ms per step.  Off. */
+#define B200_OPT_LEAVE_ROOM 11
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 /* The process-wide switches above without a handle (B200_OPT_FUSED_STAGE1, _TILE_SAMPLES, _FFT_CTAS_PER_SM, _BRANCH_ORDER,
- * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS).  b200_vfo_bank_set_option forwards these here: naming a
+ * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM).  b200_vfo_bank_set_option forwards these here: naming a
  * bank does NOT confine them to that bank -- every bank and front end of the process sees the change.  Only
  * B200_OPT_CALIBRATION_STEPS is per bank; B200_OPT_DEFER_TAIL is process-wide too but is switched through a bank handle,
  * because that bank's deferred work is drained first.  Calls are serialised by the library. */

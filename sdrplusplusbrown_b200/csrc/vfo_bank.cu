@@ -14,7 +14,8 @@
 
 namespace b200 {
 
-bool deferTail = false;     // B200_OPT_DEFER_TAIL
+bool deferTail = false;               // B200_OPT_DEFER_TAIL
+bool fusedLeaveRoomEnabled = false;  // B200_OPT_LEAVE_ROOM (measured slower: see include/b200dsp.h)
 
 // ------------------------------------------------------------------ Stage
 int Stage::create(int kind_, const std::vector<float>& taps, int D_, int L_, int M_, int elemFloats_, int outCap_, bool planTaps_) {
@@ -531,7 +532,10 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s, const std::func
     if (count > 0) {
         B200_TRY(launchCheckpoints((const RotJob*)(d + oR), (int)rj.size(), exact ? (int)rj.size() : 0, count, s));
         B200_TRY(launchXlate((const XlateJob*)(d + oX), (int)xj.size(), count, s));
-        B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
+        fusedLeaveRoom = defer && fusedLeaveRoomEnabled;      // streaming mode: the previous block's tail runs beside this launch
+        const int rcFused = launchFused((const FusedJob*)(d + oF), fj, s);
+        fusedLeaveRoom = false;
+        B200_TRY(rcFused);
         if (afterStage1) { B200_TRY((*afterStage1)()); afterStage1 = nullptr; }
         B200_CUDA(cudaEventRecord(evStage1, s));
         if (defer) {
@@ -544,7 +548,10 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s, const std::func
     }
     else if (!fj.empty()) {
         // an empty block: the fused stages still flip their history ping-pong; copy the history across
-        B200_TRY(launchFused((const FusedJob*)(d + oF), fj, s));
+        fusedLeaveRoom = defer && fusedLeaveRoomEnabled;      // streaming mode: the previous block's tail runs beside this launch
+        const int rcFused = launchFused((const FusedJob*)(d + oF), fj, s);
+        fusedLeaveRoom = false;
+        B200_TRY(rcFused);
     }
     if (afterStage1) { B200_TRY((*afterStage1)()); }
     B200_TRY(launchHistoryUpdate((const FirJob*)(dt + oH - tailOff), (int)histJobs.size(), maxH, ts));

@@ -129,6 +129,7 @@ struct VfoBank {
 };
 
 extern bool deferTail;
+extern bool fusedLeaveRoomEnabled;
 int launchXlate(const XlateJob* dJobs, int nJobs, int maxN, cudaStream_t s);
 
 } // namespace b200

@@ -33,6 +33,7 @@ namespace b200 {
 
 int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grouped kernel for a one-VFO launch too; 0 / 2048 = default
 int fusedVfosPerPass = 0;   // B200_OPT_VFOS_PER_PASS: 0 = by code size (launchPlan), else 2 / 4
+bool fusedLeaveRoom = false; // set by the bank for a launch whose block has a deferred tail beside it (streaming mode)
 bool fusedSplitRuns = false;// plans whose unrolled body exceeds 32 KB run as two launches of half the runs each (B200_OPT_SPLIT_RUNS)
 int fusedVfosPerCta = 32;   // B200_OPT_VFOS_PER_CTA: VFOs a CTA of the grouped kernel serves from one staged tile
 // One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
@@ -230,7 +231,7 @@ __device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xr
 // not fit the 32 KB instruction cache level, its two halves do.
 template <int RATIO, int NP, int TILE, int ODD, int HALF>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS / (HALF ? 2 : 1))
-fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
+fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned nItems) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
@@ -267,10 +268,14 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
     // one-dimensional grid, VFO range fastest: the CTAs that share an input tile run at the same time, so only the first of
     // them brings the tile in from HBM and the others find it in L2
     const int nRanges = (nJobs + GV - 1) / GV;
-    const int g0 = (int)(blockIdx.x % nRanges) * GV;
+    // A launch may hold fewer CTAs than work items (streaming mode: a grid that leaves room on every SM for the previous
+    // block's later stages); each CTA then walks the items blockIdx.x, + gridDim.x, ...
+    for (unsigned item = blockIdx.x; item < nItems; item += gridDim.x) {
+    if (item != blockIdx.x) { __syncthreads(); }          // the previous item's shared-memory state is no longer read
+    const int g0 = (int)(item % nRanges) * GV;
     const FusedJob j0 = jobs[g0];
-    const int k0 = (int)(blockIdx.x / nRanges) * NB;
-    if (k0 >= j0.nOut) { return; }
+    const int k0 = (int)(item / nRanges) * NB;
+    if (k0 >= j0.nOut) { continue; }
     const int mStart = j0.offset - H - ODD + k0 * D;     // sample index of this tile's first sub-block (even, 16-byte aligned address)
     const float2* in = reinterpret_cast<const float2*>(j0.in);
 
@@ -447,6 +452,7 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV) {
             }
         }
     }
+    }   // work items
 }
 
 // ---- single-VFO variant with 16-byte staging --------------------------------------------------------------------
@@ -641,9 +647,27 @@ int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStr
         attrSet = true;
     }
     const int tiles = (nOut + NB - 1) / NB;
-    const long long ctas = (long long)tiles * ((nJobs + GV - 1) / GV);
-    if (ctas > 0x7fffffffLL) { setError("first-stage launch of %lld CTAs is too large", ctas); return B200_ETOOBIG; }
-    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<(unsigned)ctas, SB * RS, smem, s>>>(dJobs, nJobs, GV);
+    const long long items = (long long)tiles * ((nJobs + GV - 1) / GV);
+    if (items > 0x7fffffffLL) { setError("first-stage launch of %lld work items is too large", items); return B200_ETOOBIG; }
+    unsigned grid = (unsigned)items;
+    if (fusedLeaveRoom) {
+        // Streaming mode (B200_OPT_DEFER_TAIL): the previous block's later stages run on their own low-priority stream at
+        // the same time.  They are bandwidth-bound and this kernel is FP32-bound, so they fit beside it -- if this launch
+        // leaves them an SM's worth of room: about 40 KB of shared memory and 17 K registers per SM (one CTA of the FIR job
+        // kernels).  A persistent grid of that many CTAs per SM keeps the room free for the whole launch.
+        static int perSm = 0, regs = 0;         // per instantiation
+        if (perSm == 0) {
+            cudaFuncAttributes fa;
+            B200_CUDA(cudaFuncGetAttributes(&fa, fusedBankKernel<RATIO, NP, TILE, ODD, HALF>));
+            regs = fa.numRegs;
+            B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fusedBankKernel<RATIO, NP, TILE, ODD, HALF>, SB * RS, smem));
+            const int bySmem = (int)((227 * 1024 - 40 * 1024) / (smem + 1024));
+            const int byRegs = (65536 - 17 * 1024) / std::max(1, regs * SB * RS);
+            perSm = std::max(1, std::min(perSm, std::min(bySmem, byRegs)));
+        }
+        grid = (unsigned)std::min<long long>(items, 148LL * perSm);
+    }
+    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<grid, SB * RS, smem, s>>>(dJobs, nJobs, GV, (unsigned)items);
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }

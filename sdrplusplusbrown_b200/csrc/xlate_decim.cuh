@@ -26,6 +26,7 @@ struct FusedJob {
 extern bool fusedEnabled;   // test hook: false forces the unfused xlate -> generic FIR path
 extern int fusedTileSamples; // tuning hook: 0 = by VFO count, else input samples per CTA tile
 extern int fusedVfosPerPass; // tuning hook: 0 = by code size, else VFOs accumulated per register pass of the grouped kernel
+extern bool fusedLeaveRoom;  // the next first-stage launches keep part of every SM free for the deferred tail of the previous block
 extern bool fusedSplitRuns;  // tuning hook: split a plan whose loop body exceeds the instruction cache into two launches
 extern int fusedVfosPerCta;  // tuning hook: VFOs a CTA of the grouped kernel serves from one staged tile
 bool fusedStageSupported(const Vfo& v);

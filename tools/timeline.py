@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--order", type=int, default=0, help="B200_OPT_BRANCH_ORDER")
     ap.add_argument("--fft-ctas", type=int, default=0, help="B200_OPT_FFT_CTAS_PER_SM")
     ap.add_argument("--defer", type=int, default=0, help="B200_OPT_DEFER_TAIL")
+    ap.add_argument("--room", type=int, default=0, help="B200_OPT_LEAVE_ROOM")
     args = ap.parse_args()
     import torch
     from torch.profiler import ProfilerActivity, profile
@@ -62,6 +63,7 @@ def main():
     fe.vfos.set_option(binding.OPT_BRANCH_ORDER, args.order)
     fe.vfos.set_option(binding.OPT_FFT_CTAS_PER_SM, args.fft_ctas)
     fe.vfos.set_option(binding.OPT_DEFER_TAIL, args.defer)
+    fe.vfos.set_option(binding.OPT_LEAVE_ROOM, args.room)
     if args.attach:
         fe.attach_waterfall(wf, d_zoom.data_ptr(), d_rgba.data_ptr(), max_frames)
 
