@@ -548,3 +548,54 @@ def test_process_host_returns_a_large_bank_in_one_scatter(pinned):
             assert counts[v_b] == len(want) > 0
             assert np.array_equal(view[st:st + len(want)], want)
     assert keep is not None
+
+
+@pytest.mark.parametrize("tuned_to_signal", [False, True])
+def test_reference_snr_threshold_scenario_on_a_synthetic_cw_capture(tuned_to_signal):
+    """The reference's only numeric test, re-created (tests/baseband_file_test.cpp:36-88): a baseband capture with CW
+    stations is played through the front end, the radio VFO is USB (2.8 kHz wide, lower edge on the tuned frequency,
+    waterfall.cpp:1595-1598), and the largest selectedVFOSNR seen over the run must stay below 20 dB when tuned to a
+    clear frequency and exceed 20 dB when tuned to a station.  Its WAV fixtures are absent from the mount, so the
+    capture is synthetic: int16 I/Q, noise plus keyed carriers, played through the int16 ingest in the file source's
+    block size; SNR = calculateVFOSignalInfo over every dB row (waterfall.cpp:688-759), on the device and -- to pin the
+    numbers -- from the oracle on the same rows."""
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate = 192000.0, 8192, 20.0
+    blk = int(np.float32(sr) / np.float32(200.0))
+    n = blk * 400                                            # two seconds
+    t = np.arange(n) / sr
+    rng = np.random.default_rng(1397)
+    x = (rng.standard_normal(n) + 1j * rng.standard_normal(n)) * 0.02
+    for f0, amp, wpm in ((14.9e3, 0.25, 0.11), (-31.2e3, 0.1, 0.07)):      # two keyed carriers ("CW contest")
+        keyed = (np.floor(t / wpm) % 3 != 2).astype(np.float64)
+        x += amp * keyed * np.exp(2j * np.pi * f0 * t)
+    xi = np.round(np.stack([x.real, x.imag], 1) * 20000.0).clip(-32768, 32767).astype(np.int16)
+    tuned = 14.0e3 if tuned_to_signal else 60.0e3           # USB: the channel spans [tuned, tuned + 2.8 kHz]
+    bw = 2800.0
+    center = tuned + bw / 2.0
+    fe = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=blk)
+    v = fe.vfos.add(24e3, bw, center)
+    fe.vfos.set_demod(v, binding.DEMOD_USB, 0, 50.0 / 24e3, 5.0 / 24e3, 0)
+    wf = binding.Waterfall(N, 1000)
+    wf.set_view(0, N)
+    d_sig = torch.empty((4, 2), dtype=torch.float32, device="cuda")
+    max_snr, max_ref, rows_seen = 0.0, 0.0, 0
+    for i in range(0, n, blk):
+        res = fe.process_host(xi[i:i + blk], max_frames=4, vfos=[v], audio=[v], i16_scalar=32768.0)
+        k = res["n_frames"]
+        if k:
+            assert wf.vfo_signal(fe.frame_ptr(0), k, sr, center, bw, d_sig.data_ptr())
+            got = d_sig[:k].cpu().numpy()
+            for f in range(k):
+                ref = PORT.vfo_signal_info(res["frames"][f], sr, center, bw)
+                assert ref is not None and abs(got[f, 1] - ref[1]) <= 1e-3
+                max_ref = max(max_ref, ref[1])
+            max_snr = max(max_snr, float(got[:, 1].max()))
+            rows_seen += k
+    assert rows_seen >= 38 and max_snr != 0.0                # "MaxSNR is not captured" in the reference's test
+    assert abs(max_snr - max_ref) <= 1e-3
+    if tuned_to_signal:
+        assert max_snr > 20.0, max_snr
+    else:
+        assert max_snr < 20.0, max_snr
