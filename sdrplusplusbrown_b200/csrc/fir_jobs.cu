@@ -315,6 +315,69 @@ __device__ __forceinline__ void classPoly(const FirJob& j, typename Elem<EF>::T*
     }
 }
 
+// ---- polyphase resampler, samples shared between the outputs of a residue class --------------------------------------
+// Outputs k and k + L use the same bank row and their windows start M samples apart; with more taps per phase than M
+// those windows overlap.  A thread takes R (2 or 3) consecutive members of a class: every sample of their joint window
+// is read from shared memory ONCE and feeds up to R accumulators, each with its own tap of the same row (tap index
+// i - r * M).  A warp works on one class at a time, so the row is read with uniform 16-byte loads (one wavefront), and
+// the lanes' windows, R * M samples apart, are padded to an odd stride.  Against eight lanes per output (lanesPoly) this
+// is one shared-memory read per R MACs instead of one per MAC and no shuffles: the 25/48 resampler of the WFM channels
+// (146 taps per phase) ran with the L1 data pipe 92 % busy there.
+constexpr int kSharePlan = 3;
+__host__ __device__ inline int shareR(int rowStride, int M) { const int r = 1 + (rowStride - 1) / M; return r > 3 ? 3 : r; }
+// pad shift that makes the lane stride step * (1 + 2^-s) odd (step even), none for an odd step
+__host__ __device__ inline int sharePad(int step) {
+    if (step & 1) { return 30; }
+    int sft = 0;
+    while (!((step >> sft) & 1)) { sft++; }
+    return sft;
+}
+template <int EF>
+__device__ __forceinline__ void sharedPoly(const FirJob& j, typename Elem<EF>::T* win) {
+    using E = Elem<EF>;
+    using T = typename E::T;
+    const int R = shareR(j.rowStride, j.M);
+    const int opc = 32 * R * j.L;
+    const int k0 = blockIdx.x * opc;
+    if (k0 >= j.nOut) { return; }
+    const int nk = min(opc, j.nOut - k0);
+    const long long tot0 = (long long)j.phase0 + (long long)k0 * j.M;
+    const int base = j.offset + (int)(tot0 / j.L);
+    const unsigned rem0 = (unsigned)(tot0 % j.L);
+    const int span = (int)(((long long)rem0 + (long long)(nk - 1) * j.M) / j.L) + j.rowStride + 1;
+    const int ps = sharePad(R * j.M);
+    stageWindow<EF>(j, win, base, span, ps);
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int walk = (R - 1) * j.M + j.rowStride;            // joint window of a thread's R members
+    for (int c = warp; c < j.L; c += kThreads / 32) {
+        const int u0 = lane * R;                             // member u of class c is output c + L * u
+        if (c + j.L * u0 >= nk) { continue; }
+        const unsigned total = rem0 + (unsigned)c * (unsigned)j.M;
+        const unsigned adv = total / (unsigned)j.L;
+        const float* row = j.taps + (size_t)(total - adv * (unsigned)j.L) * j.rowStride;
+        const int p0 = (int)adv + u0 * j.M;
+        T acc[3] = { E::zero(), E::zero(), E::zero() };
+        for (int i = 0; i < walk; i += 4) {
+            const int p = p0 + i;
+            const T x0 = win[p + (p >> ps)], x1 = win[p + 1 + ((p + 1) >> ps)], x2 = win[p + 2 + ((p + 2) >> ps)], x3 = win[p + 3 + ((p + 3) >> ps)];
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                const int idx = i - r * j.M;
+                if (r < R && idx >= 0 && idx < j.rowStride) {
+                    const float4 h = __ldg(reinterpret_cast<const float4*>(row + idx));
+                    E::fma(acc[r], h.x, x0); E::fma(acc[r], h.y, x1); E::fma(acc[r], h.z, x2); E::fma(acc[r], h.w, x3);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const int kk = c + j.L * (u0 + r);
+            if (r < R && kk < nk) { reinterpret_cast<T*>(j.out)[k0 + kk] = acc[r]; }
+        }
+    }
+}
+
 // ---- one output per thread ----------------------------------------------------------------------------------------
 template <int EF>
 __device__ __forceinline__ void simpleJob(const FirJob& j, typename Elem<EF>::T* win, int smemElems) {
@@ -381,6 +444,7 @@ __global__ void __launch_bounds__(kThreads) firJobsKernel(const FirJob* __restri
     }
     else if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { blockedFir<EF>(j, win, smemElems); }
     else if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) { classPoly<EF>(j, win); }
+    else if (j.plan == kSharePlan && j.kind == JOB_POLYPHASE) { sharedPoly<EF>(j, win); }
     else if (j.plan > 0) { lanesPoly<EF>(j, win, smemElems); }
     else { simpleJob<EF>(j, win, smemElems); }
 }
@@ -404,6 +468,7 @@ int outPerCta(const FirJob& j) {
     if (j.plan >= kPlanBase) { return kThreads * planOutPerThread(j.D); }
     if (j.plan > 0 && j.kind == JOB_DECIM_FIR) { return (kThreads / j.plan) * kR; }
     if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) { return kThreads * j.L; }
+    if (j.plan == kSharePlan && j.kind == JOB_POLYPHASE) { return 32 * shareR(j.rowStride, j.M) * j.L; }
     if (j.plan > 0) { return kPolyOutPerCta; }
     return kSimpleOutPerCta;
 }
@@ -421,6 +486,11 @@ size_t smemElemsFor(const FirJob& j) {
     if (j.plan == kClassPlan && j.kind == JOB_POLYPHASE) {
         const size_t span = (size_t)kThreads * j.M + j.rowStride + 4;
         return span + (span >> 4) + 2;
+    }
+    if (j.plan == kSharePlan && j.kind == JOB_POLYPHASE) {
+        const int R = shareR(j.rowStride, j.M);
+        const size_t span = (size_t)32 * R * j.M + j.M + j.rowStride + 8;
+        return span + (span >> sharePad(R * j.M)) + 4;
     }
     if (j.plan > 0) {
         const size_t span = (size_t)(((long long)kPolyOutPerCta * j.M) / j.L) + j.rowStride + 2;
@@ -455,6 +525,11 @@ void firJobPlan(FirJob& j) {
     }
     else {
         if (j.rowStride % 4 != 0 || (long long)j.L + (long long)kPolyOutPerCta * j.M >= (1LL << 31)) { return; }
+        const int R = shareR(j.rowStride, j.M);
+        if (R >= 2 && j.M % 4 == 0 && j.L <= 64 && j.nOut >= 2 * 32 * R * j.L) {
+            j.plan = kSharePlan;
+            if (smemElemsFor(j) * elemBytes <= kSmemCap / 2) { return; }
+        }
         if (j.L <= 16 && j.nOut >= 4 * kThreads * j.L) {
             j.plan = kClassPlan;
             if (smemElemsFor(j) * elemBytes <= kSmemCap / 2) { return; }

@@ -29,7 +29,8 @@ struct FirJob {
     int elemFloats;        // 2 = complex samples, 1 = real samples
     int plan;              // how a CTA works on this job (firJobPlan): 0 = one output per thread;
                            // DECIM_FIR > 0: 8 outputs per thread, taps split over `plan` adjacent lanes;
-                           // POLYPHASE > 0: `plan` (= 8) lanes per output
+                           // POLYPHASE: 8 = eight lanes per output, 2 = one output per thread by residue class (short
+                           // banks), 3 = two or three outputs of a class per thread sharing their samples
 };
 
 // chooses FirJob::plan from the job's shape (host side, called by Stage::fillJob)

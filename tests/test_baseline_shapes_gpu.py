@@ -118,3 +118,36 @@ def test_cfg4_bank_with_demodulators_at_bench_block_size():
         got = b.audio(ids[i])
         assert got.shape[0] == ref.shape[0]
         assert err_db(got[:, 0], ref[:, 0]) <= TOL_DB, (i, m)
+
+
+@pytest.mark.parametrize("mode", ["fast", "exact"])
+def test_wfm_channels_on_long_blocks_take_the_shared_sample_resampler(mode):
+    """cfg4's WFM channels (122.88 MS/s -> /128 -> 25/48 polyphase, 146 taps per phase -> 500 kS/s) on blocks long enough
+    (>= 4800 outputs) for the polyphase path in which a thread computes three outputs of a residue class from one walk
+    over their joint window (fir_jobs.cu: sharedPoly) -- the path the 16 Mi-sample bench blocks run.  Two ragged blocks,
+    so the carried resampler phase / offset enter the second one; against the oracle per VFO."""
+    from sdrplusplusbrown_b200 import binding
+    sr = configs.CONFIGS["cfg4"]["sample_rate"]
+    specs = [(500e3, 150e3, -20e6 + 11.0), (500e3, 150e3, 7.3e6), (500e3, 150e3, 41e6 - 5.0), (15e3, 10e3, 1.1e6), (24e3, 2.8e3, -3.3e6)]
+    sizes = [(1 << 21) + 12345, 1500000]
+    exact = mode == "exact"
+    b = binding.VfoBank(sr, max_block=max(sizes))
+    if exact:
+        b.set_rotator_mode(binding.ROTATOR_EXACT)
+    ids = [b.add(*sp) for sp in specs]
+    oracles = [ol.Vfo(PORT, sr, *sp) for sp in specs]
+    d = b.describe(ids[0])
+    assert (d["interp"], d["decim"], d["taps_per_phase"]) == (25, 48, 146)
+    pos = 0
+    for n in sizes:
+        x = synth.make_iq(pos, n, sr, tones=[(sp[2] + 0.1 * sp[1], 0.05) for sp in specs])
+        pos += n
+        if not exact:
+            for i, o in zip(ids, oracles):
+                b.set_phase(i, o.phase())
+        b.process(to_dev(x))
+        for i, o in zip(ids, oracles):
+            ref = o.process(x)
+            assert b.out_count(i) == len(ref)
+            assert err_db(b.output(i), ref) <= TOL_DB
+    assert b.out_count(ids[0]) >= 4800
