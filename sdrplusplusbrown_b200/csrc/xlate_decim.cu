@@ -109,6 +109,9 @@ constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4
 // Input samples per CTA tile: 2048 for the single-VFO kernel (fusedStreamKernel, HBM-bound: more resident CTAs), 4096
 // for the grouped kernel (FP32-bound from a few VFOs on: fewer overlap sub-blocks recomputed per output; measured
 // 0.35 of the FFMA peak against 0.32 with 2048-sample tiles, before pairing and 16-byte staging).
+#ifndef B200_D128_SMALL_TILE
+#define B200_D128_SMALL_TILE 0      // 1 = 4096-sample tiles for the /8192 plan too: measured slower (cfg4 15.3 against 14.6 ms per block)
+#endif
 constexpr int kTileSmall = 2048, kTileLarge = 4096;
 
 template <int D, int TILE> struct TileCfg {
@@ -248,7 +251,7 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
     constexpr int WS = SB / 32;             // warps per run
     constexpr int HQ = Q * (Q - 1) / 2;     // halo entries per warp: (q, lane < q)
     static_assert(SB % 32 == 0, "a warp holds 32 consecutive sub-blocks of one run");
-    static_assert(NP * D <= NT, "one table entry per thread");
+    constexpr int EPT = (NP * D + NT - 1) / NT;     // rotation-table entries a thread fetches per pass
     extern __shared__ __align__(16) float2 sm[];
     float2* xs = sm;                                               // SB * LP
     float4* wqBuf = reinterpret_cast<float4*>(xs + SB * LP);       // 2 * NP * D      : rotation tables of two passes
@@ -320,14 +323,15 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
     }
     __syncthreads();
     // table entry e = r * NP + p of pass `pass`: (wA.re, wB.re, wA.im, wB.im), A = VFO gp + 2p, B = A + 1 (zero beyond the range)
-    const int eR = tid / NP, eP = tid % NP;
-    auto tableEntry = [&](int pass) -> float4 {
+    auto tableEntry = [&](int pass, int e) -> float4 {
+        const int eR = e / NP, eP = e % NP;
         const int a = pass * VB + 2 * eP;
         const float2 wA = (a < nG) ? __ldg(sWtab[a] + eR) : make_float2(0.f, 0.f);
         const float2 wB = (a + 1 < nG) ? __ldg(sWtab[a + 1] + eR) : make_float2(0.f, 0.f);
         return make_float4(wA.x, wB.x, wA.y, wB.y);
     };
-    if (tid < NP * D) { wqBuf[tid] = tableEntry(0); }
+#pragma unroll
+    for (int u = 0; u < EPT; u++) { const int e = tid + u * NT; if (e < NP * D) { wqBuf[e] = tableEntry(0, e); } }
 
     const float2* xrow = xs + sb * LP + run * DS;
     const int ms = mStart + sb * D;                      // first sample of this thread's sub-block
@@ -362,9 +366,14 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
             }
             PX[p] = make_float2(pa.x, pb.x); PY[p] = make_float2(pa.y, pb.y);
         }
-        float4 nextEntry = make_float4(0.f, 0.f, 0.f, 0.f);
-        const bool haveNext = (pass + 1 < nPass) && (tid < NP * D);
-        if (haveNext) { nextEntry = tableEntry(pass + 1); }
+        float4 nextEntry[EPT];
+        const bool haveNext = (pass + 1 < nPass);
+#pragma unroll
+        for (int u = 0; u < EPT; u++) {
+            const int e = tid + u * NT;
+            nextEntry[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (haveNext && e < NP * D) { nextEntry[u] = tableEntry(pass + 1, e); }
+        }
         if (pass + 1 < nPass) { phaseLoads(pass + 1); }
         // ---- accumulate
         const float4* wq = wqBuf + buf * (NP * D) + run * DS * NP;
@@ -410,7 +419,10 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
             fb[0] = fX;
             fb[RS * SB] = fY;
         }
-        if (haveNext) { wqBuf[(buf ^ 1) * (NP * D) + tid] = nextEntry; }
+        if (haveNext) {
+#pragma unroll
+            for (int u = 0; u < EPT; u++) { const int e = tid + u * NT; if (e < NP * D) { wqBuf[(buf ^ 1) * (NP * D) + e] = nextEntry[u]; } }
+        }
         __syncthreads();
         // ---- outputs: sum over the runs, add what came from the next warp, store (coalesced over k per VFO)
         for (int idx = tid; idx < NP * SB; idx += NT) {
@@ -755,7 +767,7 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
         else {
             // D = 128 (ratio 8192): 64 sub-blocks per tile instead of 32, so that the Q - 1 sub-blocks a tile recomputes for
             // its neighbour are 8 % of it instead of 16 %
-            constexpr int kTile = (D >= 128) ? 2 * kTileLarge : kTileLarge;
+            constexpr int kTile = (D >= 128 && !B200_D128_SMALL_TILE) ? 2 * kTileLarge : kTileLarge;
             const int NB = TileCfg<D, kTile>::SB - (Q - 1);
             const int tiles = (nOut + NB - 1) / NB;
             // VFOs per register pass: the loop body is fully unrolled over the D samples of a sub-block (every tap is an
