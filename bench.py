@@ -274,7 +274,7 @@ def cpu_baseline(args):
 class Job:
     """One front end with this rank's share of a configuration's VFO bank and its waterfall reduction attached."""
 
-    def __init__(self, binding, torch, cfg_name, B, local, rank, world, defer_tail=True, vfo_indices=None):
+    def __init__(self, binding, torch, cfg_name, B, local, rank, world, defer_tail=True, vfo_indices=None, demod=None):
         cfg = configs.CONFIGS[cfg_name]
         self.cfg, self.name, self.B = cfg, cfg_name, B
         self.sr = cfg["sample_rate"]
@@ -294,6 +294,17 @@ class Job:
             if d["fused"]:
                 D, T = STAGE1[d["ratio"]]
                 self.lane_ops_per_sample += 4.0 + 2.0 * T / D
+            if demod is not None:
+                # the radio module's demodulator for the VFO's mode, with the module's defaults (demodulators/*.h)
+                mode = vl[i][0]
+                if mode == "AM":
+                    self.fe.vfos.set_demod(v, binding.DEMOD_AM, 1, 50.0 / out_sr, 5.0 / out_sr, 100.0 / out_sr)
+                elif mode in ("USB", "LSB"):
+                    self.fe.vfos.set_demod(v, binding.DEMOD_USB if mode == "USB" else binding.DEMOD_LSB, 0, 50.0 / out_sr, 5.0 / out_sr, 0)
+                elif mode == "WFM":
+                    self.fe.vfos.set_demod(v, binding.DEMOD_WFM, 1 if demod == "stereo" else 0, 1, 0, 0)
+                else:
+                    self.fe.vfos.set_demod(v, binding.DEMOD_NFM, 1, 0, 0, 0)
         self.fe.vfos.set_option(binding.OPT_DEFER_TAIL, 1 if defer_tail else 0)
         self.wf = binding.Waterfall(cfg["fft_size"], DATA_WIDTH, device=local)
         self.wf.set_view(0, cfg["fft_size"])
@@ -481,6 +492,18 @@ def run_gpu(args):
     if world == 1 and args.extras:
         del job
         torch.cuda.empty_cache()
+        # the headline bank with the radio module's demodulators behind every VFO (AM, USB + AGC, WFM mono / stereo): outside
+        # the metric ("through FFT + N-VFO channelizer"), reported beside it -- the AGC and the stereo pilot PLL are
+        # sequential walks per VFO
+        for key, kind in (("cfg4_demod_wfm_mono", "mono"), ("cfg4_demod_wfm_stereo", "stereo")):
+            jd = Job(binding, torch, WORKLOAD, B, local, 0, 1, defer_tail=args.defer_tail, demod=kind)
+            kd = max(3, args.steps // 4)
+            msd, _, ld = timed_run(jd, kd, 2)
+            binding.profile_enable(False)
+            extra[key] = {"workload": workload_text(WORKLOAD) + ", every VFO with its demodulator (WFM %s)" % kind, "value": B * kd / (msd * 1e-3) / 1e6, "unit": UNIT,
+                          "ms_per_step": msd / kd, "steps": kd, "x_real_time": B * kd / (msd * 1e-3) / sr, "gpu_launches": ld}
+            del jd
+            torch.cuda.empty_cache()
         for name, Bx, fused_name, fft_name in (("cfg2", 1 << 26, "fusedStreamKernel<512> (single-VFO variant, 16-byte staging)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)"),
                                                ("cfg3", 1 << 24, "fusedBankKernel<1024> (256 NFM VFOs)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)")):
             cx = configs.CONFIGS[name]
