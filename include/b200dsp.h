@@ -160,9 +160,14 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * block with one resident CTA fewer per SM and the shared L1 / issue slots) than the 2.7 ms the overlap hides: 16.8 against
  * 15.2 ms per step.  Off. */
 #define B200_OPT_LEAVE_ROOM 11
+/* B200_OPT_PARAM_TABLES (process-wide, default 1): the first-stage bank kernel takes its per-VFO rotation tables from the
+ * kernel parameter block (constant bank, uniform loads) instead of gathering them into shared memory pass by pass; a
+ * launch then carries at most 1920 / D VFO pairs and a bank larger than that runs as several launches.  0 = the
+ * shared-memory table path for every launch.  Same table values either way: results are identical. */
+#define B200_OPT_PARAM_TABLES 12
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 /* The process-wide switches above without a handle (B200_OPT_FUSED_STAGE1, _TILE_SAMPLES, _FFT_CTAS_PER_SM, _BRANCH_ORDER,
- * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM).  b200_vfo_bank_set_option forwards these here: naming a
+ * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM, _PARAM_TABLES).  b200_vfo_bank_set_option forwards these here: naming a
  * bank does NOT confine them to that bank -- every bank and front end of the process sees the change.  Only
  * B200_OPT_CALIBRATION_STEPS is per bank; B200_OPT_DEFER_TAIL is process-wide too but is switched through a bank handle,
  * because that bank's deferred work is drained first.  Calls are serialised by the library. */

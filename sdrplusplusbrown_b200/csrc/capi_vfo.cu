@@ -142,6 +142,7 @@ int b200_set_global_option(int option, int value) {
         return B200_OK;
     case B200_OPT_SPLIT_RUNS: fusedSplitRuns = value != 0; return B200_OK;
     case B200_OPT_LEAVE_ROOM: fusedLeaveRoomEnabled = value != 0; return B200_OK;
+    case B200_OPT_PARAM_TABLES: fusedParamTables = value != 0; return B200_OK;
     case B200_OPT_VFOS_PER_CTA:
         if (value < 2 || value > 4096) { setError("VFOs per CTA must be 2 .. 4096"); return B200_EINVAL; }
         fusedVfosPerCta = value;

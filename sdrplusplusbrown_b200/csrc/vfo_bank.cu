@@ -517,6 +517,7 @@ int VfoBank::process(const cf32* dIn, int count, cudaStream_t s, const std::func
     for (Vfo* v : dirtyTables) {
         float2* tab = (float2*)(h + off);
         makeRotatorTable(v->dRe, v->dIm, tab);
+        v->hWtab.assign(tab, tab + kRotChunk);
         off += kRotChunk * sizeof(float2);
         B200_CUDA(cudaMemcpyAsync(v->dWtab, tab, kRotChunk * sizeof(float2), cudaMemcpyHostToDevice, s));
         v->tableDirty = false;

@@ -62,6 +62,7 @@ struct Vfo {
     bool tableDirty = true;          // wtab must be re-uploaded (phaseDelta changed)
     float2* dChk = nullptr; int chkCap = 0;   // per-block phase checkpoints
     float2* dWtab = nullptr;                  // phaseDelta^j, j < 512
+    std::vector<float2> hWtab;                // the same table on the host (the bank kernel takes it in its parameter block)
     float2* dRotState = nullptr;              // EXACT mode: the reference's fp32 phase
     // RationalResampler configuration
     int mode = 3, ratio = 1, interp = 1, decim = 1, resampTapCount = 0;

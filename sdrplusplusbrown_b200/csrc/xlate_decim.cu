@@ -34,6 +34,7 @@ namespace b200 {
 int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grouped kernel for a one-VFO launch too; 0 / 2048 = default
 int fusedVfosPerPass = 0;   // B200_OPT_VFOS_PER_PASS: 0 = by code size (launchPlan), else 2 / 4
 bool fusedLeaveRoom = false; // set by the bank for a launch whose block has a deferred tail beside it (streaming mode)
+bool fusedParamTables = true;
 bool fusedSplitRuns = false;// plans whose unrolled body exceeds 32 KB run as two launches of half the runs each (B200_OPT_SPLIT_RUNS)
 int fusedVfosPerCta = 32;   // B200_OPT_VFOS_PER_CTA: VFOs a CTA of the grouped kernel serves from one staged tile
 // One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
@@ -221,6 +222,48 @@ __device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xr
     }
 }
 
+// The rotation tables of a launch in the kernel's parameter block (constant bank): a warp-uniform operand is what the
+// constant path is for -- `LDCU` loads the entry into uniform registers, which FMUL2 / FFMA2 take directly, and the
+// shared-memory pipe is left to the samples.  (A broadcast LDS.128 costs four wavefronts like any other; with the table
+// in shared memory the inner loop ran at 83 FMA/clk/SM, from the parameter block at 95: tools/microbench/wtab_paths.cu.)
+// 30 KB of the 32 KB parameter limit: D = 64 -> 30 pairs = 60 VFOs per launch, D = 128 -> 30 VFOs, D = 16 -> 240.
+constexpr int kParamEntries = 1920;
+template <bool CT> struct BankTablesT { float4 w[CT ? kParamEntries : 1]; };      // CT = false: the table path in shared memory, nothing to pass
+using BankTables = BankTablesT<true>;
+
+template <int RATIO, int RUN, int NP, int DS, int ODD>
+__device__ __forceinline__ void accumulateRunPairsC(const float2* __restrict__ xrow, const BankTablesT<true>& tp, int tbase, float2 (*accX)[8], float2 (*accY)[8]) {
+    using FS = FirstStage<RATIO>;
+    constexpr int D = FS::D, T = FS::T + ODD;
+    constexpr int Q = (T + D - 1) / D;
+    const float4* x2 = reinterpret_cast<const float4*>(xrow);
+#pragma unroll
+    for (int r2 = 0; r2 < DS / 2; r2++) {
+        const float4 xx = x2[r2];
+#pragma unroll
+        for (int half = 0; half < 2; half++) {
+            const float xr = half ? xx.z : xx.x, xi = half ? xx.w : xx.y;
+            const int r = 2 * r2 + half;
+#pragma unroll
+            for (int p = 0; p < NP; p++) {
+                const float4 w = tp.w[tbase + (RUN * DS + r) * NP + p];      // uniform index: the parameter block is read by LDCU
+                const float2 wX = make_float2(w.x, w.y), wY = make_float2(w.z, w.w);
+                const float2 zX = ffma2(make_float2(-xi, -xi), wY, fmul2(make_float2(xr, xr), wX));
+                const float2 zY = ffma2(make_float2(xi, xi), wX, fmul2(make_float2(xr, xr), wY));
+#pragma unroll
+                for (int q = 0; q < Q; q++) {
+                    const int t = q * D + RUN * DS + r;
+                    if (t < T && t - ODD >= 0) {
+                        const float h = FS::tapImm(t - ODD);
+                        accX[p][q] = ffma2(make_float2(h, h), zX, accX[p][q]);
+                        accY[p][q] = ffma2(make_float2(h, h), zY, accY[p][q]);
+                    }
+                }
+            }
+        }
+    }
+}
+
 // one CTA per (output tile, range of GV VFOs); all jobs of a launch share in/count/offset/nOut.
 // A CTA stages its input tile once and walks its VFO range in passes of VB = 2 * NP VFOs.  Per pass: the threads
 // accumulate (above), multiply by their sub-block's start phase, fold the Q partial sums of neighbouring sub-blocks
@@ -232,9 +275,11 @@ __device__ __forceinline__ void accumulateRunPairs(const float2* __restrict__ xr
 // first / second half of every sub-block's samples) and the launch with HALF = 2 ADDS its sums to the outputs the
 // HALF = 1 launch stored: the unrolled loop body of the /8192 plan (D = 128, T = 726: 34 KB for all four runs) does
 // not fit the 32 KB instruction cache level, its two halves do.
-template <int RATIO, int NP, int TILE, int ODD, int HALF>
+// CT: the rotation tables of the launch's jobs come in the parameter block `tp` (entry (pair * D + r) * 1, one pair per pass)
+// instead of being gathered into shared memory pass by pass.
+template <int RATIO, int NP, int TILE, int ODD, int HALF, bool CT>
 __global__ void __launch_bounds__(TileCfg<FirstStage<RATIO>::D, TILE>::THREADS / (HALF ? 2 : 1))
-fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned nItems) {
+fusedBankKernel(const __grid_constant__ BankTablesT<CT> tp, const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned nItems) {
     using FS = FirstStage<RATIO>;
     using TC = TileCfg<FS::D, TILE>;
     constexpr int D = FS::D, T = FS::T + ODD, H = FS::T - 1;
@@ -330,8 +375,10 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
         const float2 wB = (a + 1 < nG) ? __ldg(sWtab[a + 1] + eR) : make_float2(0.f, 0.f);
         return make_float4(wA.x, wB.x, wA.y, wB.y);
     };
+    if constexpr (!CT) {
 #pragma unroll
-    for (int u = 0; u < EPT; u++) { const int e = tid + u * NT; if (e < NP * D) { wqBuf[e] = tableEntry(0, e); } }
+        for (int u = 0; u < EPT; u++) { const int e = tid + u * NT; if (e < NP * D) { wqBuf[e] = tableEntry(0, e); } }
+    }
 
     const float2* xrow = xs + sb * LP + run * DS;
     const int ms = mStart + sb * D;                      // first sample of this thread's sub-block
@@ -367,7 +414,7 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
             PX[p] = make_float2(pa.x, pb.x); PY[p] = make_float2(pa.y, pb.y);
         }
         float4 nextEntry[EPT];
-        const bool haveNext = (pass + 1 < nPass);
+        const bool haveNext = !CT && (pass + 1 < nPass);
 #pragma unroll
         for (int u = 0; u < EPT; u++) {
             const int e = tid + u * NT;
@@ -383,15 +430,31 @@ fusedBankKernel(const FusedJob* __restrict__ jobs, int nJobs, int GV, unsigned n
 #pragma unroll
             for (int q = 0; q < Q; q++) { accX[p][q] = make_float2(0.f, 0.f); accY[p][q] = make_float2(0.f, 0.f); }
         }
-        switch (run) {
-        case 0: if constexpr (RUN0 <= 0 && RUN0 + RS > 0) { accumulateRunPairs<RATIO, 0, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 1: if constexpr (RUN0 <= 1 && RUN0 + RS > 1) { accumulateRunPairs<RATIO, 1, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 2: if constexpr (RUN0 <= 2 && RUN0 + RS > 2) { accumulateRunPairs<RATIO, 2, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 3: if constexpr (RUN0 <= 3 && RUN0 + RS > 3) { accumulateRunPairs<RATIO, 3, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 4: if constexpr (RUN0 <= 4 && RUN0 + RS > 4) { accumulateRunPairs<RATIO, 4, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 5: if constexpr (RUN0 <= 5 && RUN0 + RS > 5) { accumulateRunPairs<RATIO, 5, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        case 6: if constexpr (RUN0 <= 6 && RUN0 + RS > 6) { accumulateRunPairs<RATIO, 6, NP, DS, ODD>(xrow, wq, accX, accY); } break;
-        default: if constexpr (RUN0 <= 7 && RUN0 + RS > 7) { accumulateRunPairs<RATIO, 7, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+        if constexpr (CT) {
+            // this pass's table block in the parameter block: pairs are numbered through the launch
+            const int tbase = ((g0 / 2) + pass * NP) * D;
+            switch (run) {
+            case 0: if constexpr (RUN0 <= 0 && RUN0 + RS > 0) { accumulateRunPairsC<RATIO, 0, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 1: if constexpr (RUN0 <= 1 && RUN0 + RS > 1) { accumulateRunPairsC<RATIO, 1, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 2: if constexpr (RUN0 <= 2 && RUN0 + RS > 2) { accumulateRunPairsC<RATIO, 2, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 3: if constexpr (RUN0 <= 3 && RUN0 + RS > 3) { accumulateRunPairsC<RATIO, 3, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 4: if constexpr (RUN0 <= 4 && RUN0 + RS > 4) { accumulateRunPairsC<RATIO, 4, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 5: if constexpr (RUN0 <= 5 && RUN0 + RS > 5) { accumulateRunPairsC<RATIO, 5, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            case 6: if constexpr (RUN0 <= 6 && RUN0 + RS > 6) { accumulateRunPairsC<RATIO, 6, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            default: if constexpr (RUN0 <= 7 && RUN0 + RS > 7) { accumulateRunPairsC<RATIO, 7, NP, DS, ODD>(xrow, tp, tbase, accX, accY); } break;
+            }
+        }
+        else {
+            switch (run) {
+            case 0: if constexpr (RUN0 <= 0 && RUN0 + RS > 0) { accumulateRunPairs<RATIO, 0, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 1: if constexpr (RUN0 <= 1 && RUN0 + RS > 1) { accumulateRunPairs<RATIO, 1, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 2: if constexpr (RUN0 <= 2 && RUN0 + RS > 2) { accumulateRunPairs<RATIO, 2, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 3: if constexpr (RUN0 <= 3 && RUN0 + RS > 3) { accumulateRunPairs<RATIO, 3, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 4: if constexpr (RUN0 <= 4 && RUN0 + RS > 4) { accumulateRunPairs<RATIO, 4, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 5: if constexpr (RUN0 <= 5 && RUN0 + RS > 5) { accumulateRunPairs<RATIO, 5, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            case 6: if constexpr (RUN0 <= 6 && RUN0 + RS > 6) { accumulateRunPairs<RATIO, 6, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            default: if constexpr (RUN0 <= 7 && RUN0 + RS > 7) { accumulateRunPairs<RATIO, 7, NP, DS, ODD>(xrow, wq, accX, accY); } break;
+            }
         }
         // ---- c_q = acc_q * P, then the in-warp part of y[k] = sum_q c_q[k + q]
 #pragma unroll
@@ -643,8 +706,8 @@ __global__ void __launch_bounds__(256) fusedEdgeKernel(const FusedJob* __restric
     }
 }
 
-template <int RATIO, int NP, int TILE, int ODD, int HALF>
-int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStream_t s) {
+template <int RATIO, int NP, int TILE, int ODD, int HALF, bool CT>
+int launchBankKernel(const BankTablesT<CT>& tp, const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T + ODD;
     constexpr int Q = (T + D - 1) / D;
@@ -655,7 +718,7 @@ int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStr
                              + (size_t)2 * NP * 2 * RS * (SB / 32) * (Q * (Q - 1) / 2)) * sizeof(float2);
     static bool attrSet = false;        // per instantiation
     if (!attrSet) {
-        B200_CUDA(cudaFuncSetAttribute(fusedBankKernel<RATIO, NP, TILE, ODD, HALF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA(cudaFuncSetAttribute(fusedBankKernel<RATIO, NP, TILE, ODD, HALF, CT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attrSet = true;
     }
     const int tiles = (nOut + NB - 1) / NB;
@@ -663,54 +726,86 @@ int launchBankKernel(const FusedJob* dJobs, int nJobs, int nOut, int GV, cudaStr
     if (items > 0x7fffffffLL) { setError("first-stage launch of %lld work items is too large", items); return B200_ETOOBIG; }
     unsigned grid = (unsigned)items;
     if (fusedLeaveRoom) {
-        // Streaming mode (B200_OPT_DEFER_TAIL): the previous block's later stages run on their own low-priority stream at
-        // the same time.  They are bandwidth-bound and this kernel is FP32-bound, so they fit beside it -- if this launch
-        // leaves them an SM's worth of room: about 40 KB of shared memory and 17 K registers per SM (one CTA of the FIR job
-        // kernels).  A persistent grid of that many CTAs per SM keeps the room free for the whole launch.
+        // Streaming mode (B200_OPT_DEFER_TAIL) with B200_OPT_LEAVE_ROOM: the previous block's later stages run on their own
+        // low-priority stream at the same time; a persistent grid that leaves them about 40 KB of shared memory and 17 K
+        // registers per SM (one CTA of the FIR job kernels) keeps that room free for the whole launch.
         static int perSm = 0, regs = 0;         // per instantiation
         if (perSm == 0) {
             cudaFuncAttributes fa;
-            B200_CUDA(cudaFuncGetAttributes(&fa, fusedBankKernel<RATIO, NP, TILE, ODD, HALF>));
+            B200_CUDA(cudaFuncGetAttributes(&fa, fusedBankKernel<RATIO, NP, TILE, ODD, HALF, CT>));
             regs = fa.numRegs;
-            B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fusedBankKernel<RATIO, NP, TILE, ODD, HALF>, SB * RS, smem));
+            B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fusedBankKernel<RATIO, NP, TILE, ODD, HALF, CT>, SB * RS, smem));
             const int bySmem = (int)((227 * 1024 - 40 * 1024) / (smem + 1024));
             const int byRegs = (65536 - 17 * 1024) / std::max(1, regs * SB * RS);
             perSm = std::max(1, std::min(perSm, std::min(bySmem, byRegs)));
         }
         grid = (unsigned)std::min<long long>(items, 148LL * perSm);
     }
-    fusedBankKernel<RATIO, NP, TILE, ODD, HALF><<<grid, SB * RS, smem, s>>>(dJobs, nJobs, GV, (unsigned)items);
+    fusedBankKernel<RATIO, NP, TILE, ODD, HALF, CT><<<grid, SB * RS, smem, s>>>(tp, dJobs, nJobs, GV, (unsigned)items);
     B200_CHECK_LAUNCH(); countLaunch();
     return B200_OK;
 }
 
+// VFOs per CTA: the more, the better the tile load and the CTA prologue are amortised; but keep the SMs full
+static int pickRange(int nJobs, int tiles, int np) {
+    int GV = std::min(nJobs, std::min(kMaxVfosPerCta, std::max(2 * np, fusedVfosPerCta)));
+    // (ranges start at even VFO indices: the pairs of a launch are numbered through it)
+    while (GV > 2 * np && (long long)tiles * ((nJobs + GV - 1) / GV) < 148 * 8) { GV = std::max(2 * np, ((GV / 2) + 1) & ~1); }
+    return GV;
+}
+
 template <int RATIO, int NP, int TILE, int ODD>
-int launchMainV(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, cudaStream_t s) {
+int launchMainV(const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOut, int count, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T + ODD;
+    constexpr int Q = (T + D - 1) / D;
     using TC = TileCfg<D, TILE>;
+    const int tiles = (nOut + (TC::SB - (Q - 1)) - 1) / (TC::SB - (Q - 1));
     size_t slot = 0;
     // algorithmic bytes: the block is read once for the whole bank, each VFO writes nOut samples; algorithmic flops
     // (SURVEY 8(d)): 6 for the rotation + 4 per tap and output, i.e. 6 + 4 T/D per input sample and VFO
     B200_TRY(profBegin(PROF_STAGE1, s, 8.0 * (double)count + 8.0 * (double)nOut * (double)nJobs,
                        (6.0 * (double)count + 4.0 * (double)FS::T * (double)nOut) * (double)nJobs, &slot));
-    // a loop body beyond the 32 KB instruction cache level runs as two launches of half the runs each
-    constexpr int kBodyBytes = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0) * NP;
-    if constexpr (kBodyBytes > 32 * 1024 && TC::RS % 2 == 0 && TC::RS >= 2) {
-        if (fusedSplitRuns) {
-            B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 1>(dJobs, nJobs, nOut, GV, s)));
-            B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 2>(dJobs, nJobs, nOut, GV, s)));
+    BankTables tp;               // launch arguments are copied at launch time: one host buffer serves every launch of the group
+    BankTablesT<false> none{};
+    // D = 128 would carry only 30 VFOs per launch: measured slower than the shared-memory tables (cfg4: 14.3 against 12.3 ms)
+    bool haveHost = fusedParamTables && NP == 1 && D <= 64;
+    for (int i = 0; i < nJobs && haveHost; i++) { haveHost = hJobs[i].hWtab != nullptr; }
+    if (haveHost) {
+        // the tables ride in the parameter block: as many pairs per launch as fit (the block is re-read per launch, from
+        // L2 / HBM at a small fraction of what this FP32-bound kernel leaves unused)
+        constexpr int kPairs = kParamEntries / D;
+        for (int c0 = 0; c0 < nJobs; c0 += 2 * kPairs) {
+            const int nc = std::min(2 * kPairs, nJobs - c0);
+            for (int q = 0; 2 * q < nc; q++) {
+                const float2* wA = hJobs[c0 + 2 * q].hWtab;
+                const float2* wB = (2 * q + 1 < nc) ? hJobs[c0 + 2 * q + 1].hWtab : nullptr;
+                float4* dst = tp.w + (size_t)q * D;
+                for (int r = 0; r < D; r++) { dst[r] = make_float4(wA[r].x, wB ? wB[r].x : 0.f, wA[r].y, wB ? wB[r].y : 0.f); }
+            }
+            B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0, true>(tp, dJobs + c0, nc, nOut, pickRange(nc, tiles, NP), s)));
         }
-        else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0>(dJobs, nJobs, nOut, GV, s))); }
     }
-    else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0>(dJobs, nJobs, nOut, GV, s))); }
+    else {
+        const int GV = pickRange(nJobs, tiles, NP);
+        // a loop body beyond the 32 KB instruction cache level can run as two launches of half the runs each
+        constexpr int kBodyBytes = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0) * NP;
+        if constexpr (kBodyBytes > 32 * 1024 && TC::RS % 2 == 0 && TC::RS >= 2) {
+            if (fusedSplitRuns) {
+                B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 1, false>(none, dJobs, nJobs, nOut, GV, s)));
+                B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 2, false>(none, dJobs, nJobs, nOut, GV, s)));
+            }
+            else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0, false>(none, dJobs, nJobs, nOut, GV, s))); }
+        }
+        else { B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 0, false>(none, dJobs, nJobs, nOut, GV, s))); }
+    }
     B200_TRY(profEnd(PROF_STAGE1, slot, s));
     return B200_OK;
 }
 
 template <int RATIO, int NP, int TILE>
-int launchMain(const FusedJob* dJobs, int nJobs, int nOut, int count, int GV, bool odd, cudaStream_t s) {
-    return odd ? launchMainV<RATIO, NP, TILE, 1>(dJobs, nJobs, nOut, count, GV, s) : launchMainV<RATIO, NP, TILE, 0>(dJobs, nJobs, nOut, count, GV, s);
+int launchMain(const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOut, int count, bool odd, cudaStream_t s) {
+    return odd ? launchMainV<RATIO, NP, TILE, 1>(dJobs, hJobs, nJobs, nOut, count, s) : launchMainV<RATIO, NP, TILE, 0>(dJobs, hJobs, nJobs, nOut, count, s);
 }
 
 template <int RATIO, int ODD, int PERSIST>
@@ -752,7 +847,7 @@ int launchStream(const FusedJob* dJobs, int nJobs, int nOut, int count, bool odd
 }
 
 template <int RATIO>
-int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
+int launchPlan(const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
     using FS = FirstStage<RATIO>;
     constexpr int D = FS::D, T = FS::T;
     constexpr int Q = (T + D - 1) / D;
@@ -782,14 +877,11 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
             // one-pair /4096 plan) -- so two pairs run only when asked for
             int np = 1;
             if (fusedVfosPerPass == 4 && kTwoPairsFit) { np = 2; }
-            // VFOs per CTA: the more, the better the tile load and the CTA prologue are amortised; but keep the SMs full
-            int GV = std::min(nJobs, std::min(kMaxVfosPerCta, std::max(2 * np, fusedVfosPerCta)));
-            while (GV > 2 * np && (long long)tiles * ((nJobs + GV - 1) / GV) < 148 * 8) { GV = std::max(2 * np, GV / 2); }
             if constexpr (kTwoPairsFit) {
-                if (np == 2) { B200_TRY((launchMain<RATIO, 2, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
-                else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
+                if (np == 2) { B200_TRY((launchMain<RATIO, 2, kTile>(dJobs, hJobs, nJobs, nOut, count, odd, s))); }
+                else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, hJobs, nJobs, nOut, count, odd, s))); }
             }
-            else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, nJobs, nOut, count, GV, odd, s))); }
+            else { B200_TRY((launchMain<RATIO, 1, kTile>(dJobs, hJobs, nJobs, nOut, count, odd, s))); }
         }
     }
     fusedEdgeKernel<RATIO><<<nJobs, 256, 0, s>>>(dJobs);
@@ -797,18 +889,18 @@ int launchPlan(const FusedJob* dJobs, int nJobs, int nOut, int count, const void
     return B200_OK;
 }
 
-int launchPlanDyn(int ratio, const FusedJob* dJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
+int launchPlanDyn(int ratio, const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOut, int count, const void* in, int offset, cudaStream_t s) {
     switch (ratio) {
-    case 16: return launchPlan<16>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 32: return launchPlan<32>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 64: return launchPlan<64>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 128: return launchPlan<128>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 256: return launchPlan<256>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 512: return launchPlan<512>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 1024: return launchPlan<1024>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 2048: return launchPlan<2048>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 4096: return launchPlan<4096>(dJobs, nJobs, nOut, count, in, offset, s);
-    case 8192: return launchPlan<8192>(dJobs, nJobs, nOut, count, in, offset, s);
+    case 16: return launchPlan<16>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 32: return launchPlan<32>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 64: return launchPlan<64>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 128: return launchPlan<128>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 256: return launchPlan<256>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 512: return launchPlan<512>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 1024: return launchPlan<1024>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 2048: return launchPlan<2048>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 4096: return launchPlan<4096>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
+    case 8192: return launchPlan<8192>(dJobs, hJobs, nJobs, nOut, count, in, offset, s);
     default: setError("no fused kernel for ratio %d", ratio); return B200_EINVAL;
     }
 }
@@ -825,6 +917,7 @@ void fillFusedJob(FusedJob& f, const Stage& st, const Vfo& v, const cf32* dIn, i
     f.in = dIn; f.out = (cf32*)st.dOut;
     f.hist = (const cf32*)st.dHist[st.cur]; f.histNext = (cf32*)st.dHist[st.cur ^ 1];
     f.chk = v.dChk; f.wtab = v.dWtab;
+    f.hWtab = (v.hWtab.size() >= (size_t)kRotChunk && !v.tableDirty) ? v.hWtab.data() : nullptr;
     f.thetaEff = atan2((double)v.dIm, (double)v.dRe);
     f.logMag = log(hypot((double)v.dRe, (double)v.dIm));
     f.ratio = v.ratio; f.offset = st.offset; f.count = count; f.nOut = st.outCountFor(count);
@@ -836,7 +929,7 @@ int launchFused(const FusedJob* dJobs, const std::vector<FusedJob>& hostJobs, cu
     while (i < hostJobs.size()) {
         size_t e = i + 1;
         while (e < hostJobs.size() && hostJobs[e].ratio == hostJobs[i].ratio && hostJobs[e].offset == hostJobs[i].offset) { e++; }
-        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, (int)(e - i), hostJobs[i].nOut, hostJobs[i].count, hostJobs[i].in, hostJobs[i].offset, s));
+        B200_TRY(launchPlanDyn(hostJobs[i].ratio, dJobs + i, hostJobs.data() + i, (int)(e - i), hostJobs[i].nOut, hostJobs[i].count, hostJobs[i].in, hostJobs[i].offset, s));
         i = e;
     }
     return B200_OK;

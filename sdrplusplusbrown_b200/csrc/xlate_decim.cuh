@@ -17,6 +17,7 @@ struct FusedJob {
     cf32* histNext;        // T-1 rotated samples to carry
     const float2* chk;     // rotator checkpoints of this block (rotator.cuh)
     const float2* wtab;    // phaseDelta^j, j < 512
+    const float2* hWtab;   // HOST copy of that table (read by the launcher only; may be NULL: tables then come from `wtab`)
     double thetaEff, logMag;   // arg / log|.| of phaseDelta, for the backward extension into the history region
     int ratio;             // pow-2 plan (selects D, T and the taps at compile time)
     int offset;            // DecimatingFIR::offset
@@ -27,6 +28,7 @@ extern bool fusedEnabled;   // test hook: false forces the unfused xlate -> gene
 extern int fusedTileSamples; // tuning hook: 0 = by VFO count, else input samples per CTA tile
 extern int fusedVfosPerPass; // tuning hook: 0 = by code size, else VFOs accumulated per register pass of the grouped kernel
 extern bool fusedLeaveRoom;  // the next first-stage launches keep part of every SM free for the deferred tail of the previous block
+extern bool fusedParamTables; // rotation tables in the kernel parameter block, read through uniform loads (B200_OPT_PARAM_TABLES)
 extern bool fusedSplitRuns;  // tuning hook: split a plan whose loop body exceeds the instruction cache into two launches
 extern int fusedVfosPerCta;  // tuning hook: VFOs a CTA of the grouped kernel serves from one staged tile
 bool fusedStageSupported(const Vfo& v);

@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--tile", type=int, default=0, help="fused-kernel tile samples (0 = library default)")
     ap.add_argument("--vb", type=int, default=0, help="VFOs per register pass of the grouped first-stage kernel (0 = library default, 2, 4)")
     ap.add_argument("--gv", type=int, default=32, help="VFOs per CTA of the grouped first-stage kernel")
+    ap.add_argument("--ptab", type=int, default=1, help="rotation tables in the kernel parameter block (1) or in shared memory (0)")
     ap.add_argument("--split", type=int, default=0, help="split plans whose loop body exceeds the instruction cache into two launches")
     args = ap.parse_args()
     cfg = configs.CONFIGS[args.cfg]
@@ -51,6 +52,7 @@ def main():
         bank.set_option(binding.OPT_VFOS_PER_PASS, args.vb)
         bank.set_option(binding.OPT_VFOS_PER_CTA, args.gv)
         bank.set_option(binding.OPT_SPLIT_RUNS, args.split)
+        bank.set_option(binding.OPT_PARAM_TABLES, args.ptab)
         instr = 0.0
         for mode, out_sr, bw, off in vfos:
             v = bank.add(out_sr, bw, off)
