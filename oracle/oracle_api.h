@@ -129,6 +129,23 @@ void* orc_agc_create(double setPoint, double attack, double decay, double maxGai
 void orc_agc_destroy(void* h);
 int orc_agc_process(void* h, int count, const float* in, float* out);
 
+// ---- dsp::detector::SignalDetector (dsp/detector/signal_detector.cpp; the front end's detectorPreprocessor,
+// signal_path/iq_frontend.cpp:37-44).  FFT size = (int)(sampleRate / 10) -- any length, not a power of two.
+void* orc_sigdet_create(double sampleRate);
+void orc_sigdet_destroy(void* h);
+int orc_sigdet_fft_size(void* h);
+void orc_sigdet_set_center_frequency(void* h, double f);                 // :309-321 (clears the sample buffer, keeps the row history)
+// run() (:359-414) on one block; returns the number of rows completed since creation
+int orc_sigdet_process(void* h, int count, const float* in);
+int orc_sigdet_result(void* h, float* out, int cap);                     // sigs_smoothed (:436-450); returns its length, 0 before the first detection
+int orc_sigdet_history(void* h, int row, float* out, int cap);           // candidate row `row` of the kept history (0 = oldest); returns the number of kept rows
+// one row of run(): Blackman window (no alternation), forward DFT, swapfft, |X|, 20 log10(|X| + 1e-10)  (:373-397)
+void orc_sigdet_row(const float* iq, int N, float* rowDb);
+// getLineCandidates (:151-267) of one dB row: -20 everywhere except the marked line positions
+void orc_sigdet_candidates(const float* rowDb, int N, float* out);
+// addSingleFFTRow (:454-481) with a ready-made dB row (history, detection interval, aggregateAndDetect :416-452)
+void orc_sigdet_add_row(void* h, const float* rowDb, int N);
+
 #ifdef __cplusplus
 }
 #endif

@@ -158,6 +158,30 @@ static inline void volk_32f_x2_subtract_32f(float* out, const float* a, const fl
 static inline void volk_32f_x2_multiply_32f(float* out, const float* a, const float* b, unsigned int n) {
     for (unsigned int i = 0; i < n; i++) { out[i] = a[i] * b[i]; }
 }
+// ---- used by utils/arrays.cpp only (the SignalDetector's and logmmse's array helpers; arrays.cpp:801,837,933,1036)
+static inline void volk_32fc_x2_add_32fc(lv_32fc_t* out, const lv_32fc_t* a, const lv_32fc_t* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = lv_32fc_t(a[i].real() + b[i].real(), a[i].imag() + b[i].imag()); }
+}
+static inline void volk_32f_x2_divide_32f(float* out, const float* a, const float* b, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) { out[i] = a[i] / b[i]; }
+}
+static inline void volk_32fc_s32fc_multiply_32fc(lv_32fc_t* out, const lv_32fc_t* a, const lv_32fc_t s, unsigned int n) {
+    for (unsigned int i = 0; i < n; i++) {
+        const float ar = a[i].real(), ai = a[i].imag(), br = s.real(), bi = s.imag();
+        out[i] = lv_32fc_t(ar * br - ai * bi, ar * bi + ai * br);
+    }
+}
+// VOLK's generic "fast exp" is Schraudolph's construction: the float whose bit pattern is the integer
+// (2^23 / ln 2) * x + (127 * 2^23 - 60801); a few per cent of relative error, monotonic.
+static inline void volk_32f_expfast_32f(float* out, const float* in, unsigned int n) {
+    const float fact = 8388608.0f / 0.6931471805f, bias = 1065353216.0f - 60801.0f;
+    for (unsigned int i = 0; i < n; i++) {
+        const int bits = (int)(fact * in[i] + bias);
+        float f;
+        memcpy(&f, &bits, sizeof(f));
+        out[i] = f;
+    }
+}
 static inline void volk_32f_accumulator_s32f(float* result, const float* in, unsigned int n) {
     float s = 0.0f;
     for (unsigned int i = 0; i < n; i++) { s += in[i]; }

@@ -137,6 +137,38 @@ def _run_taps(orc, name):
     return res
 
 
+def sigdet_input(sr, rows, seed=11):
+    """Noise plus three voice-like groups of spectral lines (harmonics 110 / 170 / 260 Hz apart, i.e. 11 / 17 / 26 of the
+    detector's 10 Hz bins, strongest line last) whose levels wander from row to row, and one plain carrier."""
+    n = int(sr * (1 / 10.0)) * rows
+    rng = np.random.default_rng(seed)
+    t = np.arange(n, dtype=np.float64) / sr
+    x = synth.gaussian_iq(0, n, 0x5D2B200 + seed, 0.05).astype(np.complex128)
+    for (f0, df, k) in ((-0.31 * sr, 110.0, 9), (0.07 * sr, 170.0, 7), (0.33 * sr, 260.0, 6)):
+        for h in range(k):
+            a = 0.004 * (1.0 + h) * (1.0 + 0.5 * np.sin(2 * np.pi * (0.7 + 0.1 * h) * t + rng.uniform(0, 6.28)))
+            x += a * np.exp(2j * np.pi * ((f0 + h * df) * t + rng.uniform(0, 1)))
+    x += 0.05 * np.exp(2j * np.pi * (-0.12 * sr) * t)
+    return x.astype(np.complex64)
+
+
+def _run_sigdet(orc, name):
+    sr, rows = 51200.0, 25
+    x = sigdet_input(sr, rows)
+    d = ol.SigDet(orc, sr)
+    assert d.n == 5120
+    done = 0
+    for b in _blocks(x, 7001):                      # ragged against the 5120-sample rows
+        done = d.process(b)
+    hist = d.history()
+    row0 = ol.sigdet_row(orc, x[:d.n])
+    cand0 = ol.sigdet_candidates(orc, row0)
+    marked = np.flatnonzero(hist != -20.0)
+    return dict(rows=np.array([done, hist.shape[0]], np.int32), row0_sub=row0[::4].copy(), cand0=cand0,
+                smoothed=d.result(), hist_marked=marked.astype(np.int32), hist_values=hist.ravel()[marked].copy(),
+                input_crc=_crc(x))
+
+
 CASES = {}
 for _n in VFO_GOLDEN:
     CASES[_n] = _run_vfo
@@ -146,6 +178,7 @@ for _n in FFT_GOLDEN:
 for _n in ("demod_nfm", "demod_usb", "demod_lsb", "demod_am", "demod_am_carrier"):
     CASES[_n] = _run_demod
 CASES["taps"] = _run_taps
+CASES["sigdet_51200"] = _run_sigdet
 
 
 def run_case(orc, name):

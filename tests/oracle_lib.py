@@ -86,6 +86,16 @@ _SIGS = {
     "orc_agc_create": (_vp, [_d, _d, _d, _d, _d, _d]),
     "orc_agc_destroy": (None, [_vp]),
     "orc_agc_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_sigdet_create": (_vp, [_d]),
+    "orc_sigdet_destroy": (None, [_vp]),
+    "orc_sigdet_fft_size": (_i, [_vp]),
+    "orc_sigdet_set_center_frequency": (None, [_vp, _d]),
+    "orc_sigdet_process": (_i, [_vp, _i, _vp]),
+    "orc_sigdet_result": (_i, [_vp, _vp, _i]),
+    "orc_sigdet_history": (_i, [_vp, _i, _vp, _i]),
+    "orc_sigdet_row": (None, [_vp, _i, _vp]),
+    "orc_sigdet_candidates": (None, [_vp, _i, _vp]),
+    "orc_sigdet_add_row": (None, [_vp, _vp, _i]),
 }
 
 
@@ -406,6 +416,65 @@ class Agc(_Block):
         out = np.zeros(len(x), np.float32)
         self.orc.lib.orc_agc_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
         return out
+
+
+class SigDet:
+    """dsp::detector::SignalDetector (dsp/detector/signal_detector.cpp): feed blocks, read sigs_smoothed."""
+
+    def __init__(self, orc, sample_rate):
+        self.orc = orc
+        self.h = orc.lib.orc_sigdet_create(float(sample_rate))
+        self.n = orc.lib.orc_sigdet_fft_size(self.h)
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        return self.orc.lib.orc_sigdet_process(self.h, len(x), x.ctypes.data)
+
+    def set_center_frequency(self, f):
+        self.orc.lib.orc_sigdet_set_center_frequency(self.h, float(f))
+
+    def add_row(self, row):
+        row = np.ascontiguousarray(row, np.float32)
+        self.orc.lib.orc_sigdet_add_row(self.h, row.ctypes.data, len(row))
+
+    def result(self):
+        n = self.orc.lib.orc_sigdet_result(self.h, None, 0)
+        out = np.zeros(n, np.float32)
+        if n:
+            self.orc.lib.orc_sigdet_result(self.h, out.ctypes.data, n)
+        return out
+
+    def history(self):
+        k = self.orc.lib.orc_sigdet_history(self.h, -1, None, 0)
+        rows = np.zeros((k, self.n), np.float32)
+        for r in range(k):
+            self.orc.lib.orc_sigdet_history(self.h, r, rows[r].ctypes.data, self.n)
+        return rows
+
+    def close(self):
+        if self.h:
+            self.orc.lib.orc_sigdet_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def sigdet_row(orc, x):
+    x = np.ascontiguousarray(x, np.complex64)
+    out = np.zeros(len(x), np.float32)
+    orc.lib.orc_sigdet_row(x.ctypes.data, len(x), out.ctypes.data)
+    return out
+
+
+def sigdet_candidates(orc, row):
+    row = np.ascontiguousarray(row, np.float32)
+    out = np.zeros(len(row), np.float32)
+    orc.lib.orc_sigdet_candidates(row.ctypes.data, len(row), out.ctypes.data)
+    return out
 
 
 def fmif_model(x, bins, hist=None):
