@@ -409,6 +409,42 @@ int b200_frontend_group_sync(b200_frontend_group* g);
 /* duration of the last block's broadcast on the ingest GPU's communication stream (waits for it to finish) */
 int b200_frontend_group_broadcast_ms(b200_frontend_group* g, double* ms);
 
+/* ---- dsp::detector::SignalDetector, the front end's detector pre-processor.
+ * Replaces core/src/dsp/detector/signal_detector.{h,cpp} (class :78-129; run :359-414, getLineCandidates :151-267,
+ * addSingleFFTRow :454-481, aggregateAndDetect :416-452), which IQFrontEnd owns as `detectorPreprocessor`
+ * (signal_path/iq_frontend.h:77, iq_frontend.cpp:37-44,102) and the display menu toggles (gui/menus/display.cpp:144-151).
+ * The detector collects (int)(sample_rate / 10) samples, turns them into a dB row (Blackman window, transform of that --
+ * arbitrary -- length, halves swapped, 20 log10(|X| + 1e-10)), the row into "line candidates", keeps 100 candidate rows and
+ * with every 10th row (once more than 20 are kept) publishes their time average smoothed over three bins: sigs_smoothed.
+ * The samples pass through unchanged, so process() only reads them.  Rows of up to 2^21 points (20.9 MS/s) are served.
+ * For the same dB row the candidates, history and result equal the reference's bit for bit; the dB row agrees to FFT
+ * rounding.  Difference: a sample-rate change that changes the row length restarts the history. */
+typedef struct b200_sigdet b200_sigdet;
+int b200_sigdet_create(b200_sigdet** out, double sample_rate, int device);       /* SignalDetector() + setSampleRate */
+void b200_sigdet_destroy(b200_sigdet* d);                                           /* no-op for a front end's own detector */
+int b200_sigdet_set_sample_rate(b200_sigdet* d, double sample_rate);              /* :297-307 */
+int b200_sigdet_set_center_frequency(b200_sigdet* d, double center_frequency);    /* :309-321: drops the partly collected row */
+int b200_sigdet_set_enabled(b200_sigdet* d, int enabled);                         /* signal_detector.h:96 */
+int b200_sigdet_is_enabled(b200_sigdet* d);
+int b200_sigdet_fft_size(b200_sigdet* d);
+/* one block of DEVICE samples (interleaved cf32), stream-ordered; rows complete as the samples add up */
+int b200_sigdet_process(b200_sigdet* d, const float* d_in, int count, void* stream);
+int b200_sigdet_process_host(b200_sigdet* d, const float* h_in, int count, void* stream);   /* the same for HOST samples */
+/* addSingleFFTRow with a ready-made dB row of fft_size floats on the device (tests; a caller with its own spectrum) */
+int b200_sigdet_add_row(b200_sigdet* d, const float* d_row_db, void* stream);
+int b200_sigdet_sync(b200_sigdet* d);
+int64_t b200_sigdet_rows(b200_sigdet* d);                                          /* rows completed since creation */
+/* sigs_smoothed to the host (waits for the detector's stream): returns its length, 0 before the first detection, < 0 on error */
+int b200_sigdet_result(b200_sigdet* d, float* h_out, int cap);
+const float* b200_sigdet_result_ptr(b200_sigdet* d);                               /* device pointer, NULL before the first detection */
+const float* b200_sigdet_last_row_ptr(b200_sigdet* d);                             /* device pointer: the last dB row */
+/* candidate row `row` of the kept history (0 = oldest) to the host; returns the number of kept rows */
+int b200_sigdet_history(b200_sigdet* d, int row, float* h_out, int cap);
+/* The front end's own detector (IQFrontEnd::detectorPreprocessor): created disabled, follows the effective sample rate,
+ * fed with every pre-processed block while enabled (togglePreprocessor(&detectorPreprocessor, on), iq_frontend.cpp:44). */
+b200_sigdet* b200_frontend_detector(b200_frontend* fe);
+int b200_frontend_set_detector(b200_frontend* fe, int enabled);
+
 /* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
 int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
 

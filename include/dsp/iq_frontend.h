@@ -28,6 +28,7 @@
 #include "buffer/frame_buffer.h"
 #include "chain.h"
 #include "channel/rx_vfo.h"
+#include "detector/signal_detector.h"
 
 class IQFrontEnd {
 public:
@@ -53,6 +54,11 @@ public:
                                  STREAM_BUFFER_SIZE, 0) != B200_OK) { fail("b200_frontend_create"); }
         bank = b200_frontend_vfo_bank(fe);
         b200_vfo_bank_set_rotator_mode(bank, B200_ROTATOR_EXACT);
+        // the detector is the last block of the pre-processing chain, added disabled (iq_frontend.cpp:37-44): it lives on
+        // the device behind the GPU's decimator / DC blocker / conjugate, this object is its host face
+        detectorPreprocessor.init(NULL);
+        if (b200_sigdet* d = b200_frontend_detector(fe)) { detectorPreprocessor.attach(d, &mtx); }
+        else { fail("b200_frontend_detector"); }
         resizeRows();
         _init = true;
     }
@@ -78,6 +84,11 @@ public:
         pauseFor([&] { preproc.removeBlock(processor, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); userBlocks--; });
     }
     void togglePreprocessor(dsp::Processor<dsp::complex_t, dsp::complex_t>* processor, bool enabled) {
+        if (processor == &detectorPreprocessor) {        // display.cpp:144: no host block to re-plumb, the device detector is switched
+            { std::lock_guard<std::mutex> lk(mtx); if (b200_frontend_set_detector(fe, enabled ? 1 : 0) != B200_OK) { fail("togglePreprocessor(detector)"); } }
+            detectorPreprocessor.setEnabled(enabled);
+            return;
+        }
         pauseFor([&] { preproc.setBlockEnabled(processor, enabled, [this](dsp::stream<dsp::complex_t>* o) { workIn = o; }); });
     }
     void setSampleRate(double sampleRate) {
@@ -175,6 +186,7 @@ public:
 
     double getEffectiveSamplerate() { return b200_frontend_effective_samplerate(fe); }
     Event<double> onEffectiveSampleRateChange;     // emitted by setSampleRate / setDecimation (iq_frontend.cpp:99,129)
+    dsp::detector::SignalDetector detectorPreprocessor;   // signal_path/iq_frontend.h:77
     b200_frontend* handle() { return fe; }
 
 protected:
@@ -199,6 +211,7 @@ protected:
             if (b200_frontend_process_host(fe, reinterpret_cast<const float*>(in->readBuf), count, rows.data(), maxRows, outs.data(), nullptr,
                                            counts.data(), nullptr) != B200_OK) { fail("process"); }
             nFrames = std::min(b200_frontend_frame_count(fe), maxRows);
+            detectorPreprocessor.refresh();                // sigs_smoothed, when the block completed detector rows
             rowLen = _fftSize;                             // the geometry these rows were made with (its setters wait on rowMtx)
             for (auto& kv : vfos) { kv.second->pending = counts[kv.second->index()]; live.push_back(kv.second); }
             boundNow = bound;

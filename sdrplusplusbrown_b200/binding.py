@@ -119,6 +119,24 @@ _SIGS = {
     "b200_frontend_group_frame_index": (C.c_int64, [_vp, _i]),
     "b200_frontend_group_sync": (_i, [_vp]),
     "b200_frontend_group_broadcast_ms": (_i, [_vp, C.POINTER(_d)]),
+    "b200_sigdet_create": (_i, [_pp, _d, _i]),
+    "b200_sigdet_destroy": (None, [_vp]),
+    "b200_sigdet_set_sample_rate": (_i, [_vp, _d]),
+    "b200_sigdet_set_center_frequency": (_i, [_vp, _d]),
+    "b200_sigdet_set_enabled": (_i, [_vp, _i]),
+    "b200_sigdet_is_enabled": (_i, [_vp]),
+    "b200_sigdet_fft_size": (_i, [_vp]),
+    "b200_sigdet_process": (_i, [_vp, _vp, _i, _vp]),
+    "b200_sigdet_process_host": (_i, [_vp, _vp, _i, _vp]),
+    "b200_sigdet_add_row": (_i, [_vp, _vp, _vp]),
+    "b200_sigdet_sync": (_i, [_vp]),
+    "b200_sigdet_rows": (C.c_int64, [_vp]),
+    "b200_sigdet_result": (_i, [_vp, _vp, _i]),
+    "b200_sigdet_result_ptr": (_vp, [_vp]),
+    "b200_sigdet_last_row_ptr": (_vp, [_vp]),
+    "b200_sigdet_history": (_i, [_vp, _i, _vp, _i]),
+    "b200_frontend_detector": (_vp, [_vp]),
+    "b200_frontend_set_detector": (_i, [_vp, _i]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
@@ -312,6 +330,70 @@ class VfoBank:
         return {v: bufs[v][:counts[v]].copy() for v in vfos}
 
 
+class SignalDetector:
+    """dsp::detector::SignalDetector (dsp/detector/signal_detector.{h,cpp}) on one GPU."""
+
+    def __init__(self, sample_rate=0.0, device=0, _handle=None):
+        self.device = device
+        self._owned = _handle is None
+        if _handle is None:
+            h = _vp()
+            _chk(lib.b200_sigdet_create(C.byref(h), float(sample_rate), int(device)))
+            _handle = h
+        self.h = _handle
+
+    def close(self):
+        if self.h and self._owned:
+            lib.b200_sigdet_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_sample_rate(self, sr): _chk(lib.b200_sigdet_set_sample_rate(self.h, float(sr)))
+    def set_center_frequency(self, f): _chk(lib.b200_sigdet_set_center_frequency(self.h, float(f)))
+    def set_enabled(self, e): _chk(lib.b200_sigdet_set_enabled(self.h, int(e)))
+    def is_enabled(self): return bool(lib.b200_sigdet_is_enabled(self.h))
+    def fft_size(self): return lib.b200_sigdet_fft_size(self.h)
+    def rows(self): return int(lib.b200_sigdet_rows(self.h))
+
+    def process(self, d_in, count=None, stream=None):
+        if count is None:
+            count = d_in.shape[0]
+        _chk(lib.b200_sigdet_process(self.h, d_in.data_ptr() if count else None, int(count), _stream_ptr(stream)))
+        return self.rows()
+
+    def process_host(self, x, stream=None):
+        x = np.ascontiguousarray(x, np.complex64)
+        _chk(lib.b200_sigdet_process_host(self.h, x.ctypes.data, len(x), _stream_ptr(stream)))
+        return self.rows()
+
+    def add_row(self, d_row, stream=None):
+        _chk(lib.b200_sigdet_add_row(self.h, d_row.data_ptr(), _stream_ptr(stream)))
+
+    def result(self):
+        n = _chk(lib.b200_sigdet_result(self.h, None, 0))
+        out = np.zeros(n, np.float32)
+        if n:
+            _chk(lib.b200_sigdet_result(self.h, out.ctypes.data, n))
+        return out
+
+    def last_row(self):
+        _chk(lib.b200_sigdet_sync(self.h))
+        return _dev_to_numpy(lib.b200_sigdet_last_row_ptr(self.h), self.fft_size(), np.float32, self.device)
+
+    def history(self):
+        n = self.fft_size()
+        k = _chk(lib.b200_sigdet_history(self.h, -1, None, 0))
+        rows = np.zeros((k, n), np.float32)
+        for r in range(k):
+            _chk(lib.b200_sigdet_history(self.h, r, rows[r].ctypes.data, n))
+        return rows
+
+
 class FrontEnd:
     """IQFrontEnd (signal_path/iq_frontend.{h,cpp}) on one GPU."""
 
@@ -336,6 +418,14 @@ class FrontEnd:
         except Exception:
             pass
 
+    def detector(self):
+        """the front end's own detector pre-processor (IQFrontEnd::detectorPreprocessor), disabled until set_detector(True)"""
+        h = lib.b200_frontend_detector(self.h)
+        if not h:
+            raise RuntimeError(lib.b200_last_error().decode())
+        return SignalDetector(device=self.device, _handle=_vp(h))
+
+    def set_detector(self, enabled): _chk(lib.b200_frontend_set_detector(self.h, int(enabled)))
     def set_sample_rate(self, sr): _chk(lib.b200_frontend_set_sample_rate(self.h, float(sr)))
     def set_decimation(self, r): _chk(lib.b200_frontend_set_decimation(self.h, int(r)))
     def set_dc_blocking(self, e): _chk(lib.b200_frontend_set_dc_blocking(self.h, int(e)))

@@ -9,6 +9,7 @@
 #include <mutex>
 
 #include "fft.cuh"
+#include "detector.cuh"
 #include "vfo_bank.cuh"
 
 namespace b200 {
@@ -424,6 +425,9 @@ struct FrontEnd {
     void* dJobDesc = nullptr; size_t jobDescBytes = 0;
     PinnedRing ring;
     const cf32* preOut = nullptr; int preCount = 0;
+    // the last block of the pre-processing chain: the signal detector (iq_frontend.cpp:37-44), created when first asked for
+    b200_sigdet* detector = nullptr;
+    int ensureDetector();
 
     // FFT branch
     FftPlan plan;
@@ -528,6 +532,7 @@ void FrontEnd::destroy() {
     hostCopyDone.clear();
     if (evHostStart) { cudaEventDestroy(evHostStart); evHostStart = nullptr; }
     if (bank) { bank->impl.destroy(); delete bank; bank = nullptr; }
+    if (detector) { detector->impl.destroy(); delete detector; detector = nullptr; }
     for (auto& st : decimStages) { st.destroy(); }
     decimStages.clear();
     plan.destroy();
@@ -694,7 +699,22 @@ int FrontEnd::process(const cf32* dIn, int count, cudaStream_t s, bool append) {
 }
 
 // the two consumers of the pre-processed block (preOut / preCount): FFT branch and VFO bank
+int FrontEnd::ensureDetector() {
+    if (detector) { return B200_OK; }
+    auto* d = new (std::nothrow) b200_sigdet;
+    if (!d) { return B200_ENOMEM; }
+    d->ownedByFrontend = true;
+    d->impl.enabled = false;                    // preproc.addBlock(&detectorPreprocessor, false)
+    int rc = d->impl.init(device);
+    if (rc == B200_OK) { rc = d->impl.setSampleRate(effectiveSr); }
+    if (rc != B200_OK) { d->impl.destroy(); delete d; return rc; }
+    detector = d;
+    return B200_OK;
+}
+
 int FrontEnd::branches(cudaStream_t s, bool append) {
+    // the detector is the chain's last block and passes the samples through: it reads the block the two branches read
+    if (detector && detector->impl.enabled) { B200_TRY(detector->impl.process(preOut, preCount, s)); }
     const bool fork = bank->impl.liveCount() > 0;
     if (fork) {
         B200_CUDA(cudaEventRecord(evFork, s));
@@ -776,7 +796,25 @@ int b200_frontend_set_sample_rate(b200_frontend* fe, double sample_rate) {
     f.sampleRate = sample_rate;
     f.effectiveSr = f.sampleRate / f.decimRatio;
     B200_TRY(b200_vfo_bank_set_in_samplerate(f.bank, f.effectiveSr));
+    if (f.detector) { B200_TRY(f.detector->impl.setSampleRate(f.effectiveSr)); }     // iq_frontend.cpp:102
     return f.updateFftPath();
+}
+
+// IQFrontEnd::detectorPreprocessor (signal_path/iq_frontend.h:77): part of the pre-processing chain, disabled until toggled
+b200_sigdet* b200_frontend_detector(b200_frontend* fe) {
+    if (!fe) { setError("NULL front-end handle"); return nullptr; }
+    DeviceGuard g(fe->impl.device);
+    if (fe->impl.ensureDetector() != B200_OK) { return nullptr; }
+    return fe->impl.detector;
+}
+
+int b200_frontend_set_detector(b200_frontend* fe, int enabled) {
+    FE_OR_FAIL(fe);
+    DeviceGuard g(fe->impl.device);
+    if (!enabled && !fe->impl.detector) { return B200_OK; }
+    B200_TRY(fe->impl.ensureDetector());
+    fe->impl.detector->impl.enabled = enabled != 0;
+    return B200_OK;
 }
 
 // IQFrontEnd::setDecimation (iq_frontend.cpp:124-141)

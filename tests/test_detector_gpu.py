@@ -1,0 +1,173 @@
+"""GPU parity of the signal detector against the oracle, through the C ABI.
+
+Reference: core/src/dsp/detector/signal_detector.cpp (run :359-414, getLineCandidates :151-267, addSingleFFTRow
+:454-481, aggregateAndDetect :416-452), the front end's detectorPreprocessor (signal_path/iq_frontend.cpp:37-44).
+
+  * everything behind the dB row is integer decisions on fp32 sums: fed the SAME dB rows, the device's candidate rows,
+    their 100-row history and sigs_smoothed must equal the oracle's bit for bit;
+  * the dB row itself (Blackman window, transform of sampleRate / 10 points -- not a power of two --, halves swapped,
+    20 log10(|X| + 1e-10)): |delta| <= 0.005 dB on every bin within 60 dB of the row's peak (the reference's FFTW is
+    single precision too; the oracle's DFT is float64);
+  * end to end on ragged blocks the rows differ by that rounding, so a few near-tie decisions flip: the marked line
+    positions must agree on >= 99 % (Jaccard) and sigs_smoothed on >= 99 % of the bins."""
+import numpy as np
+import pytest
+
+import golden_cases
+import oracle_lib as ol
+from gpu_util import to_dev
+
+pytestmark = pytest.mark.gpu
+
+PORT = ol.Oracle("port")
+ROW_TOL_DB = 0.005
+
+
+def _dev_f32(a):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(a, np.float32)).cuda()
+
+
+@pytest.mark.parametrize("sr", [51200.0, 100010.0, 240000.0, 1000.0])
+def test_same_rows_give_the_same_candidates_history_and_result_bit_for_bit(sr):
+    from sdrplusplusbrown_b200 import binding
+    rows = 34 if sr < 200e3 else 23
+    n = int(sr * (1 / 10.0))
+    x = golden_cases.sigdet_input(sr, rows, seed=3)
+    dev = binding.SignalDetector(sr)
+    orc = ol.SigDet(PORT, sr)
+    assert dev.fft_size() == orc.n == n
+    for r in range(rows):
+        row = ol.sigdet_row(PORT, x[r * n:(r + 1) * n])
+        orc.add_row(row)
+        dev.add_row(_dev_f32(row))
+        if r in (20, 21, rows - 1):
+            got, ref = dev.result(), orc.result()
+            assert len(got) == len(ref)
+            assert np.array_equal(got, ref), r
+    h, g = orc.history(), dev.history()
+    assert h.shape == g.shape == (rows, n)
+    assert np.array_equal(h, g)
+    assert dev.rows() == rows
+    if n >= 100:
+        assert np.count_nonzero(h != -20.0) > 0
+
+
+def test_history_keeps_the_last_hundred_rows():
+    from sdrplusplusbrown_b200 import binding
+    sr, n = 10000.0, 1000
+    rng = np.random.default_rng(5)
+    dev, orc = binding.SignalDetector(sr), ol.SigDet(PORT, sr)
+    for r in range(117):
+        row = (-60.0 + 10.0 * rng.standard_normal(n)).astype(np.float32)
+        row[200 + (r % 7)::17] += 25.0
+        orc.add_row(row)
+        dev.add_row(_dev_f32(row))
+    assert np.array_equal(orc.history(), dev.history())
+    assert dev.history().shape == (100, n)
+    assert np.array_equal(orc.result(), dev.result())
+
+
+@pytest.mark.parametrize("n", [5120, 10001, 24000, 240000, 4099, 2000000])
+def test_db_row_of_any_length(n):
+    """the chirp-z transform on the power-of-two passes: 2^10*5, odd, 2^6*3*5^3, cfg1's 240 000, a prime, cfg2's 2 M"""
+    from sdrplusplusbrown_b200 import binding
+    sr = n * 10.0
+    x = golden_cases.sigdet_input(sr, 1, seed=n % 1000)
+    dev = binding.SignalDetector(sr)
+    assert dev.fft_size() == n
+    assert dev.process(to_dev(x)) == 1
+    got = dev.last_row()
+    ref = ol.sigdet_row(PORT, x)
+    strong = ref > ref.max() - 60.0
+    assert np.count_nonzero(strong) > n // 4
+    worst = np.abs(got - ref)[strong].max()
+    print("n = %d: worst dB difference within 60 dB of the peak %.4f" % (n, worst))
+    assert worst <= ROW_TOL_DB
+
+
+@pytest.mark.parametrize("sr", [51200.0, 240000.0])
+def test_stream_on_ragged_blocks_against_the_oracle(sr):
+    from sdrplusplusbrown_b200 import binding
+    rows = 33
+    n = int(sr * (1 / 10.0))
+    x = golden_cases.sigdet_input(sr, rows, seed=9)
+    dev, orc = binding.SignalDetector(sr), ol.SigDet(PORT, sr)
+    pos, k = 0, 0
+    sizes = [n // 3 + 1, 2 * n + 7, 1000, n, 5 * n // 2]
+    while pos < len(x):
+        m = min(sizes[k % len(sizes)], len(x) - pos)
+        rd = dev.process(to_dev(x[pos:pos + m]))
+        ro = orc.process(x[pos:pos + m])
+        assert rd == ro                                   # row counts follow the same integer bookkeeping
+        pos += m
+        k += 1
+        if k == 7:
+            dev.set_center_frequency(14.2e6)              # drops the partly collected row on both sides
+            orc.set_center_frequency(14.2e6)
+    h, g = orc.history(), dev.history()
+    assert h.shape == g.shape
+    a, b = h != -20.0, g != -20.0
+    jac = np.count_nonzero(a & b) / max(1, np.count_nonzero(a | b))
+    ref, got = orc.result(), dev.result()
+    assert len(ref) == len(got) == n
+    same = np.count_nonzero(np.abs(ref - got) <= 1e-3) / n
+    print("sr %g: marked positions agree %.4f (Jaccard), sigs_smoothed within 1e-3 on %.4f of the bins" % (sr, jac, same))
+    assert jac >= 0.99
+    assert same >= 0.99
+
+
+def test_host_blocks_take_the_same_path():
+    from sdrplusplusbrown_b200 import binding
+    sr = 51200.0
+    x = golden_cases.sigdet_input(sr, 24, seed=4)
+    a, b = binding.SignalDetector(sr), binding.SignalDetector(sr)
+    for i in range(0, len(x), 7001):
+        a.process(to_dev(x[i:i + 7001]))
+        b.process_host(x[i:i + 7001])
+    assert a.rows() == b.rows() == 24
+    assert np.array_equal(a.history(), b.history())
+    assert np.array_equal(a.result(), b.result()) and len(a.result()) == 5120
+
+
+def test_disabled_detector_and_sample_rate_change():
+    from sdrplusplusbrown_b200 import binding
+    dev = binding.SignalDetector(51200.0)
+    x = golden_cases.sigdet_input(51200.0, 3)
+    dev.set_enabled(False)
+    assert dev.process(to_dev(x)) == 0                    # pass-through only (:366-371)
+    dev.set_enabled(True)
+    assert dev.process(to_dev(x)) == 3
+    dev.set_sample_rate(100010.0)                         # a new row length: 10001 points, history restarts
+    assert dev.fft_size() == 10001
+    assert dev.history().shape == (0, 10001)
+    assert len(dev.result()) == 0
+    with pytest.raises(binding.B200Error):
+        dev.set_sample_rate(61.44e6)                      # 6 144 000 points: beyond the 2^21 served
+    assert dev.fft_size() == 10001
+
+
+def test_front_end_feeds_its_detector_with_the_preprocessed_block():
+    """IQFrontEnd::detectorPreprocessor sits behind decimator, DC blocker and conjugate (iq_frontend.cpp:40-44) and follows
+    the effective sample rate (:102); off until toggled (display.cpp:144)."""
+    from sdrplusplusbrown_b200 import binding
+    sr = 204800.0
+    fe = binding.FrontEnd(sr, decim_ratio=2, dc_blocking=True, fft_size=4096, fft_rate=20.0, max_block=200000)
+    det = fe.detector()
+    assert not det.is_enabled()
+    assert det.fft_size() == 10240                        # (204800 / 2) / 10
+    x = golden_cases.sigdet_input(sr, 6, seed=21)
+    own = binding.SignalDetector(sr / 2)
+    fe.process(to_dev(x[:150000]))
+    assert det.rows() == 0                                # still disabled
+    fe.set_detector(True)
+    pos = 0
+    for m in (20480, 61440, 41000):
+        fe.process(to_dev(x[pos:pos + m]))
+        own.process(to_dev(fe.preproc_out()))
+        pos += m
+    assert det.rows() == own.rows() == (20480 + 61440 + 41000) // 2 // 10240
+    assert np.array_equal(det.history(), own.history())
+    assert np.array_equal(det.last_row(), own.last_row())
+    fe.set_decimation(4)
+    assert det.fft_size() == 5120

@@ -181,3 +181,39 @@ def test_wav_file_source_through_the_front_end_matches_the_oracle(tmp_path):
     for got, want in list(zip(rows_b, want_rows)) + list(zip(rows_a[:2], want_rows[:2])):
         strong = want > want.max() - 80.0
         assert np.max(np.abs(got[strong] - want[strong])) <= 0.01
+
+
+def test_detector_dropin_compiles(tmp_path):
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_detector_gpu.cpp"), str(tmp_path / "dropin_detector_gpu"))
+
+
+@pytest.mark.gpu
+def test_detector_dropin_against_oracle(tmp_path):
+    """IQFrontEnd::detectorPreprocessor toggled on in a running front end, and the stand-alone SignalDetector block:
+    sigs_smoothed of both against the oracle fed with the same samples (signal_detector.cpp:359-481).  The dB rows
+    differ from the oracle's by FFT rounding, so >= 97 % of the bins must agree to 1e-3."""
+    import golden_cases
+    import oracle_lib as ol
+    exe = str(tmp_path / "dropin_detector_gpu")
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_detector_gpu.cpp"), exe)
+    sr, rows, blk = 51200.0, 34, 4000
+    n = 5120
+    x = golden_cases.sigdet_input(sr, rows, seed=17)
+    inp, outp = str(tmp_path / "in.cf32"), str(tmp_path / "out.bin")
+    x.tofile(inp)
+    r = subprocess.run([exe, inp, str(len(x)), str(blk), str(sr), outp], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(outp, "rb").read()
+    n_fe, n_sa, rows_fe, rows_sa = np.frombuffer(raw[:16], np.int32)
+    via_fe = np.frombuffer(raw[16:16 + 4 * n_fe], np.float32)
+    alone = np.frombuffer(raw[16 + 4 * n_fe:], np.float32)
+    fed = (len(x) // blk) * blk
+    assert n_fe == n_sa == n
+    assert rows_fe == rows_sa == fed // n
+    assert np.array_equal(via_fe, alone)            # same device code on the same samples
+    o = ol.SigDet(ol.Oracle("port"), sr)
+    o.set_center_frequency(7.1e6)
+    o.process(x[:fed])
+    ref = o.result()
+    assert len(ref) == n
+    assert np.count_nonzero(np.abs(ref - via_fe) <= 1e-3) >= 0.97 * n
