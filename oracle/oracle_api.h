@@ -146,6 +146,17 @@ void orc_sigdet_candidates(const float* rowDb, int N, float* out);
 // addSingleFFTRow (:454-481) with a ready-made dB row (history, detection interval, aggregateAndDetect :416-452)
 void orc_sigdet_add_row(void* h, const float* rowDb, int N);
 
+// ---- dsp::IFNRLogMMSE (misc_modules/noise_reduction_logmmse/src/if_nr.h:15-113 over logmmse.h), the pre-processor the
+// logmmse module adds to the front end (main.cpp:165): wide-band log-MMSE spectral noise reduction, 20 ms Hann frames with
+// 50 % overlap, transform length 2 * even(floor(0.02 * sampleRate)).
+void* orc_logmmse_create(int sampleRate);
+void orc_logmmse_destroy(void* h);
+void orc_logmmse_reset(void* h);                                          // if_nr.h:58-61 (the module calls it when the tuning changes)
+void orc_logmmse_set_hold(void* h, int hold);                             // :46-48 (noise profile frozen while transmitting)
+int orc_logmmse_process(void* h, int count, const float* in, float* out); // process() :63-113; returns the output sample count
+float orc_expn(float x);                                                  // dsp::math::expn (utils/arrays.cpp:60-431): E1 from its table
+int orc_logmmse_noise(void* h, float* out, int cap);                      // SavedParamsC::noise_mu2; returns its length (0 before sampling)
+
 #ifdef __cplusplus
 }
 #endif

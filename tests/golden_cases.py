@@ -169,6 +169,26 @@ def _run_sigdet(orc, name):
                 input_crc=_crc(x))
 
 
+def logmmse_input(sr, seconds, seed=1):
+    """white noise with an amplitude-modulated carrier and a weaker keyed one: what the noise reduction is meant to clean up"""
+    n = int(sr * seconds)
+    t = np.arange(n, dtype=np.float64) / sr
+    x = synth.gaussian_iq(0, n, 0x5D2B200 + 77 + seed, 0.05).astype(np.complex128)
+    x += 0.3 * np.exp(2j * np.pi * (0.0625 * sr) * t) * (1 + 0.5 * np.sin(2 * np.pi * 3 * t))
+    x += 0.02 * np.exp(2j * np.pi * (-0.21 * sr) * t) * (np.sin(2 * np.pi * 1.5 * t) > 0)
+    return x.astype(np.complex64)
+
+
+def _run_logmmse(orc, name):
+    sr = 24000
+    x = logmmse_input(sr, 2.5)
+    d = ol.LogMmse(orc, sr)
+    outs = [d.process(b) for b in _blocks(x, 1000)]
+    y = np.concatenate(outs)
+    return dict(counts=np.array([len(o) for o in outs], np.int32), out_sub=y[::16].copy(), out_crc=_crc(y), noise=d.noise()[::2].copy(),
+                input_crc=_crc(x))
+
+
 CASES = {}
 for _n in VFO_GOLDEN:
     CASES[_n] = _run_vfo
@@ -179,6 +199,7 @@ for _n in ("demod_nfm", "demod_usb", "demod_lsb", "demod_am", "demod_am_carrier"
     CASES[_n] = _run_demod
 CASES["taps"] = _run_taps
 CASES["sigdet_51200"] = _run_sigdet
+CASES["logmmse_24000"] = _run_logmmse
 
 
 def run_case(orc, name):

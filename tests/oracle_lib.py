@@ -96,6 +96,13 @@ _SIGS = {
     "orc_sigdet_row": (None, [_vp, _i, _vp]),
     "orc_sigdet_candidates": (None, [_vp, _i, _vp]),
     "orc_sigdet_add_row": (None, [_vp, _vp, _i]),
+    "orc_logmmse_create": (_vp, [_i]),
+    "orc_logmmse_destroy": (None, [_vp]),
+    "orc_logmmse_reset": (None, [_vp]),
+    "orc_logmmse_set_hold": (None, [_vp, _i]),
+    "orc_logmmse_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_logmmse_noise": (_i, [_vp, _vp, _i]),
+    "orc_expn": (_f, [_f]),
 }
 
 
@@ -461,6 +468,33 @@ class SigDet:
             self.close()
         except Exception:
             pass
+
+
+class LogMmse(_Block):
+    """dsp::IFNRLogMMSE (noise_reduction_logmmse/src/if_nr.h): blocks in, de-noised blocks out (fewer or more samples per call)."""
+
+    def __init__(self, orc, sample_rate):
+        super().__init__(orc, orc.lib.orc_logmmse_create(int(sample_rate)), "orc_logmmse")
+        self.rate = int(sample_rate)
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(len(x) + 40 * (self.rate // 100) + 1024, np.complex64)
+        n = self.orc.lib.orc_logmmse_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:n].copy()
+
+    def reset(self):
+        self.orc.lib.orc_logmmse_reset(self.h)
+
+    def set_hold(self, hold):
+        self.orc.lib.orc_logmmse_set_hold(self.h, int(hold))
+
+    def noise(self):
+        n = self.orc.lib.orc_logmmse_noise(self.h, None, 0)
+        out = np.zeros(n, np.float32)
+        if n:
+            self.orc.lib.orc_logmmse_noise(self.h, out.ctypes.data, n)
+        return out
 
 
 def sigdet_row(orc, x):
