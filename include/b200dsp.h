@@ -445,6 +445,29 @@ int b200_sigdet_history(b200_sigdet* d, int row, float* h_out, int cap);
 b200_sigdet* b200_frontend_detector(b200_frontend* fe);
 int b200_frontend_set_detector(b200_frontend* fe, int enabled);
 
+/* ---- dsp::IFNRLogMMSE, the logmmse module's front-end pre-processor: wide-band log-MMSE noise reduction.
+ * Replaces misc_modules/noise_reduction_logmmse/src/if_nr.h:15-113 (process :63-113, reset :58-61, setHold :46-48) over
+ * logmmse.h (logmmse_sample :244-296, logmmse_all :298-405, add_noise_history :117-143, update_noise_mu2 :150-242) and
+ * bgnoise.h:27-59; the module adds it to the front end's chain with addPreprocessor (main.cpp:165).
+ * Samples are collected until 28 hops (of sample_rate / 100) are there; the first 12 frames give the noise estimate; from
+ * then on every call returns all complete 20 ms frames, de-noised and overlap-added (hop = half a frame), times 4.  The
+ * output count of a call is therefore not the input count (0 at first, then a burst, then multiples of the hop).
+ * sample_rate is the integer rate the reference derives its frame length from (if_nr.h:72); up to 52.4 MS/s
+ * (transform length 2 * even(floor(0.02 * sample_rate)) <= 2^21).  max_block bounds `count` of one call. */
+typedef struct b200_logmmse b200_logmmse;
+int b200_logmmse_create(b200_logmmse** out, int sample_rate, int max_block, int device);
+void b200_logmmse_destroy(b200_logmmse* d);
+int b200_logmmse_reset(b200_logmmse* d);                  /* if_nr.h:58-61: forget the noise profile and the buffered samples (at the next call) */
+int b200_logmmse_set_hold(b200_logmmse* d, int hold);     /* if_nr.h:46-48: freeze the noise histories (while transmitting) */
+int b200_logmmse_fft_size(b200_logmmse* d);
+int b200_logmmse_max_out(b200_logmmse* d);                /* the most samples one call can return */
+/* DEVICE samples in; *d_out receives a device pointer to *out_count de-noised samples, valid until the next call (stream-ordered) */
+int b200_logmmse_process(b200_logmmse* d, const float* d_in, int count, const float** d_out, int* out_count, void* stream);
+/* HOST samples in and out (the stand-alone block on dsp::stream buffers); returns when h_out is filled */
+int b200_logmmse_process_host(b200_logmmse* d, const float* h_in, int count, float* h_out, int out_cap, int* out_count, void* stream);
+int b200_logmmse_sync(b200_logmmse* d);
+int b200_logmmse_noise(b200_logmmse* d, float* h_out, int cap);   /* the noise power estimate per bin: returns its length, 0 before sampling */
+
 /* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
 int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
 

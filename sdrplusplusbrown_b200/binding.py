@@ -137,6 +137,16 @@ _SIGS = {
     "b200_sigdet_history": (_i, [_vp, _i, _vp, _i]),
     "b200_frontend_detector": (_vp, [_vp]),
     "b200_frontend_set_detector": (_i, [_vp, _i]),
+    "b200_logmmse_create": (_i, [_pp, _i, _i, _i]),
+    "b200_logmmse_destroy": (None, [_vp]),
+    "b200_logmmse_reset": (_i, [_vp]),
+    "b200_logmmse_set_hold": (_i, [_vp, _i]),
+    "b200_logmmse_fft_size": (_i, [_vp]),
+    "b200_logmmse_max_out": (_i, [_vp]),
+    "b200_logmmse_process": (_i, [_vp, _vp, _i, _pp, C.POINTER(_i), _vp]),
+    "b200_logmmse_process_host": (_i, [_vp, _vp, _i, _vp, _i, C.POINTER(_i), _vp]),
+    "b200_logmmse_sync": (_i, [_vp]),
+    "b200_logmmse_noise": (_i, [_vp, _vp, _i]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
@@ -328,6 +338,55 @@ class VfoBank:
         counts = np.zeros(nslots, np.int32)
         _chk(lib.b200_vfo_bank_process_host(self.h, x.ctypes.data, len(x), ptrs, counts.ctypes.data, _stream_ptr(stream)))
         return {v: bufs[v][:counts[v]].copy() for v in vfos}
+
+
+class LogMmse:
+    """dsp::IFNRLogMMSE (misc_modules/noise_reduction_logmmse/src/if_nr.h) on one GPU."""
+
+    def __init__(self, sample_rate, max_block=1000000, device=0):
+        h = _vp()
+        _chk(lib.b200_logmmse_create(C.byref(h), int(sample_rate), int(max_block), int(device)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if self.h:
+            lib.b200_logmmse_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self): _chk(lib.b200_logmmse_reset(self.h))
+    def set_hold(self, hold): _chk(lib.b200_logmmse_set_hold(self.h, int(hold)))
+    def fft_size(self): return lib.b200_logmmse_fft_size(self.h)
+
+    def process(self, d_in, count=None, stream=None):
+        """device block in; the de-noised samples of this call as a numpy array"""
+        if count is None:
+            count = d_in.shape[0]
+        p, n = _vp(), _i()
+        _chk(lib.b200_logmmse_process(self.h, d_in.data_ptr() if count else None, int(count), C.byref(p), C.byref(n), _stream_ptr(stream)))
+        _chk(lib.b200_logmmse_sync(self.h))
+        return _dev_to_numpy(p.value, n.value, np.complex64, self.device) if n.value else np.zeros(0, np.complex64)
+
+    def process_host(self, x, stream=None):
+        x = np.ascontiguousarray(x, np.complex64)
+        cap = lib.b200_logmmse_max_out(self.h)
+        out = np.zeros(cap, np.complex64)
+        n = _i()
+        _chk(lib.b200_logmmse_process_host(self.h, x.ctypes.data, len(x), out.ctypes.data, cap, C.byref(n), _stream_ptr(stream)))
+        return out[:n.value].copy()
+
+    def noise(self):
+        n = _chk(lib.b200_logmmse_noise(self.h, None, 0))
+        out = np.zeros(n, np.float32)
+        if n:
+            _chk(lib.b200_logmmse_noise(self.h, out.ctypes.data, n))
+        return out
 
 
 class SignalDetector:

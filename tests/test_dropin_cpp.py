@@ -217,3 +217,35 @@ def test_detector_dropin_against_oracle(tmp_path):
     ref = o.result()
     assert len(ref) == n
     assert np.count_nonzero(np.abs(ref - via_fe) <= 1e-3) >= 0.97 * n
+
+
+def test_logmmse_dropin_compiles(tmp_path):
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_logmmse_gpu.cpp"), str(tmp_path / "dropin_logmmse_gpu"))
+
+
+@pytest.mark.gpu
+def test_logmmse_dropin_against_oracle(tmp_path):
+    """dsp::IFNRLogMMSE as a block on dsp::stream buffers: per-call output counts equal the oracle's, samples to -80 dB
+    (if_nr.h:63-113)."""
+    import golden_cases
+    import oracle_lib as ol
+    from gpu_util import err_db
+    exe = str(tmp_path / "dropin_logmmse_gpu")
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_logmmse_gpu.cpp"), exe)
+    sr, blk = 48000, 4000
+    x = golden_cases.logmmse_input(sr, 2.5, seed=8)
+    inp, outp = str(tmp_path / "in.cf32"), str(tmp_path / "out.bin")
+    x.tofile(inp)
+    r = subprocess.run([exe, inp, str(len(x)), str(blk), str(sr), outp], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    raw = open(outp, "rb").read()
+    n_blocks, n_out = np.frombuffer(raw[:8], np.int32)
+    counts = np.frombuffer(raw[8:8 + 4 * n_blocks], np.int32)
+    got = np.frombuffer(raw[8 + 4 * n_blocks:], np.complex64)
+    assert len(got) == n_out
+    o = ol.LogMmse(ol.Oracle("port"), sr)
+    outs = [o.process(x[i:i + blk]) for i in range(0, (len(x) // blk) * blk, blk)]
+    assert [len(v) for v in outs] == list(counts)
+    ref = np.concatenate(outs)
+    assert len(ref) > 0.4 * len(x)
+    assert err_db(got, ref) <= -80.0
