@@ -262,7 +262,7 @@ typedef struct b200_frontend b200_frontend;
 /* IQFrontEnd::init(in, sampleRate, buffering, decimRatio, dcBlocking, fftSize, fftRate, fftWindow, ...)
  * — iq_frontend.cpp:19-83 followed by the updateFFTPath() every setter triggers (:289-325), i.e. the
  * sign-alternating window is in force from the first frame.  fft_size must be a power of two
- * in [32, 4194304]. */
+ * in [32, 33554432]. */
 int b200_frontend_create(b200_frontend** out, double sample_rate, int decim_ratio, int dc_blocking, int invert_iq,
                          int fft_size, double fft_rate, int fft_window, int max_block, int device);
 int b200_frontend_destroy(b200_frontend* fe);
@@ -416,7 +416,7 @@ int b200_frontend_group_broadcast_ms(b200_frontend_group* g, double* ms);
  * The detector collects (int)(sample_rate / 10) samples, turns them into a dB row (Blackman window, transform of that --
  * arbitrary -- length, halves swapped, 20 log10(|X| + 1e-10)), the row into "line candidates", keeps 100 candidate rows and
  * with every 10th row (once more than 20 are kept) publishes their time average smoothed over three bins: sigs_smoothed.
- * The samples pass through unchanged, so process() only reads them.  Rows of up to 2^21 points (20.9 MS/s) are served.
+ * The samples pass through unchanged, so process() only reads them.  Rows of up to 2^24 points (167 MS/s) are served.
  * For the same dB row the candidates, history and result equal the reference's bit for bit; the dB row agrees to FFT
  * rounding.  Difference: a sample-rate change that changes the row length restarts the history. */
 typedef struct b200_sigdet b200_sigdet;
@@ -452,8 +452,8 @@ int b200_frontend_set_detector(b200_frontend* fe, int enabled);
  * Samples are collected until 28 hops (of sample_rate / 100) are there; the first 12 frames give the noise estimate; from
  * then on every call returns all complete 20 ms frames, de-noised and overlap-added (hop = half a frame), times 4.  The
  * output count of a call is therefore not the input count (0 at first, then a burst, then multiples of the hop).
- * sample_rate is the integer rate the reference derives its frame length from (if_nr.h:72); up to 52.4 MS/s
- * (transform length 2 * even(floor(0.02 * sample_rate)) <= 2^21).  max_block bounds `count` of one call. */
+* sample_rate is the integer rate the reference derives its frame length from (if_nr.h:72); up to 419 MS/s
+ * (transform length 2 * even(floor(0.02 * sample_rate)) <= 2^24).  max_block bounds `count` of one call. */
 typedef struct b200_logmmse b200_logmmse;
 int b200_logmmse_create(b200_logmmse** out, int sample_rate, int max_block, int device);
 void b200_logmmse_destroy(b200_logmmse* d);

@@ -49,7 +49,7 @@ int ChirpZ::init(int n, int device_) {
     destroy();
     device = device_;
     if (n <= 0) { setError("transform length %d", n); return B200_EINVAL; }
-    if (n > (1 << 21)) { setError("transform of %d points: at most %d are served", n, 1 << 21); return B200_ETOOBIG; }
+    if (n > (1 << 24)) { setError("transform of %d points: at most %d are served", n, 1 << 24); return B200_ETOOBIG; }
     N = n;
     int m = 32;
     while (m < 2 * N - 1) { m <<= 1; }

@@ -200,7 +200,7 @@ int SignalDetector::setSampleRate(double sr) {
     if (sampleRate == sr) { return B200_OK; }
     if (sr > 0) {
         const double nd = sr * (1 / 10.0);
-        if (nd > (double)(1 << 21)) { setError("signal detector: %g S/s needs a %g-point transform; at most %d points are served", sr, nd, 1 << 21); return B200_ETOOBIG; }
+        if (nd > (double)(1 << 24)) { setError("signal detector: %g S/s needs a %g-point transform; at most %d points are served", sr, nd, 1 << 24); return B200_ETOOBIG; }
     }
     DeviceGuard g(device);
     B200_TRY(syncLast());

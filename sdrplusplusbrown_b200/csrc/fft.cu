@@ -731,7 +731,7 @@ int FftPlan::create(int N_, int device_) {
     device = device_;
     N = N_;
     logN = log2i(N);
-    if ((1 << logN) != N || logN < 5 || logN > 22) { setError("fft size %d is not a power of two in [32, 4194304]", N); return B200_EINVAL; }
+    if ((1 << logN) != N || logN < 5 || logN > 25) { setError("fft size %d is not a power of two in [32, 33554432]", N); return B200_EINVAL; }
     direct = (logN >= 10 && logN <= fftDirectMaxLog);
     if (logN <= 9 || direct) {  // up to 512 points: generic one-CTA kernel; 2^10 .. 2^14: one CTA per frame, three register-resident stages
         N1 = 1; N2 = N;

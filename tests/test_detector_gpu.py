@@ -68,9 +68,10 @@ def test_history_keeps_the_last_hundred_rows():
     assert np.array_equal(orc.result(), dev.result())
 
 
-@pytest.mark.parametrize("n", [5120, 10001, 24000, 240000, 4099, 2000000])
+@pytest.mark.parametrize("n", [5120, 10001, 24000, 240000, 4099, 2000000, 6144000, 12288000])
 def test_db_row_of_any_length(n):
-    """the chirp-z transform on the power-of-two passes: 2^10*5, odd, 2^6*3*5^3, cfg1's 240 000, a prime, cfg2's 2 M"""
+    """the chirp-z transform on the power-of-two passes: 2^10*5, odd, 2^6*3*5^3, cfg1's 240 000, a prime, cfg2's 2 M,
+    cfg3's 6.144 M (convolution length 2^24) and cfg4's 12.288 M (2^25)"""
     from sdrplusplusbrown_b200 import binding
     sr = n * 10.0
     x = golden_cases.sigdet_input(sr, 1, seed=n % 1000)
@@ -80,7 +81,7 @@ def test_db_row_of_any_length(n):
     got = dev.last_row()
     ref = ol.sigdet_row(PORT, x)
     strong = ref > ref.max() - 60.0
-    assert np.count_nonzero(strong) > n // 4
+    assert np.count_nonzero(strong) > min(n // 4, 100000)      # (the longer the row, the higher the carrier stands above the noise bins)
     worst = np.abs(got - ref)[strong].max()
     print("n = %d: worst dB difference within 60 dB of the peak %.4f" % (n, worst))
     assert worst <= ROW_TOL_DB
@@ -143,7 +144,7 @@ def test_disabled_detector_and_sample_rate_change():
     assert dev.history().shape == (0, 10001)
     assert len(dev.result()) == 0
     with pytest.raises(binding.B200Error):
-        dev.set_sample_rate(61.44e6)                      # 6 144 000 points: beyond the 2^21 served
+        dev.set_sample_rate(250e6)                        # 25 000 000 points: beyond the 2^24 served
     assert dev.fft_size() == 10001
 
 

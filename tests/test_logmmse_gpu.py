@@ -69,7 +69,7 @@ def test_reset_hold_and_host_blocks():
     with pytest.raises(binding.B200Error):
         dev.process_host(np.zeros(blk + 1, np.complex64))     # beyond max_block
     with pytest.raises(binding.B200Error):
-        binding.LogMmse(61440000)                             # transform of 2.4 M points: beyond the 2^21 served
+        binding.LogMmse(500000000)                            # transform of 20 M points: beyond the 2^24 served
 
 
 def test_noise_goes_down_and_the_carrier_stays():
