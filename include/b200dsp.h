@@ -149,9 +149,11 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
 /* B200_OPT_FFT_DIRECT_MAX_LOG (process-wide, default 13; 9 = off): FFT plans created afterwards use the one-pass kernel (one CTA
  * per frame) for sizes up to 2^value and the two-pass kernels above.  Results agree to rounding. */
 #define B200_OPT_FFT_DIRECT_MAX_LOG 9
-/* B200_OPT_SPLIT_RUNS (process-wide, default 0; measured slower on B200: 13.8 against 12.2 ms for cfg4's bank): first-stage plans whose unrolled loop body exceeds the 32 KB instruction
- * cache level (the /8192 plan) run as two launches, each over half of every sub-block's samples, the second adding to
- * the first's outputs.  Results agree to rounding. */
+/* B200_OPT_SPLIT_RUNS (process-wide, default 1): first-stage plans whose unrolled loop body exceeds the 32 KB instruction
+ * cache level (the /8192 plan: 34 KB, 28 % of its stall samples were instruction fetches) run as two launches, each over
+ * half of every sub-block's samples -- it stages only that half, so two such CTAs take the shared memory of one -- the second
+ * adding to the first's outputs.  Measured on cfg4's bank: 11.06 against 12.17 ms per 16 Mi-sample block.  (A first form that
+ * staged whole tiles in both launches was slower, 13.8 ms.)  Results agree to rounding. */
 #define B200_OPT_SPLIT_RUNS 10
 /* B200_OPT_LEAVE_ROOM (process-wide, default 0): 1 = in streaming mode (B200_OPT_DEFER_TAIL) the first-stage bank kernel is
  * launched as a persistent grid that leaves about 40 KB of shared memory and 17 K registers free on every SM, so that the

@@ -35,7 +35,7 @@ int fusedTileSamples = 0;   // B200_OPT_TILE_SAMPLES: kTileLarge forces the grou
 int fusedVfosPerPass = 0;   // B200_OPT_VFOS_PER_PASS: 0 = by code size (launchPlan), else 2 / 4
 bool fusedLeaveRoom = false; // set by the bank for a launch whose block has a deferred tail beside it (streaming mode)
 bool fusedParamTables = true;
-bool fusedSplitRuns = false;// plans whose unrolled body exceeds 32 KB run as two launches of half the runs each (B200_OPT_SPLIT_RUNS)
+bool fusedSplitRuns = true;     // B200_OPT_SPLIT_RUNS: the /8192 plan as two launches of half the runs each (13.4 against 14.5 ms per cfg4 block)
 int fusedVfosPerCta = 32;   // B200_OPT_VFOS_PER_CTA: VFOs a CTA of the grouped kernel serves from one staged tile
 // One VFO in the launch: the variant with 16-byte staging (fusedStreamKernel).  8-byte cp.async.ca staging was what held
 // the single-VFO kernel at 0.65 of the copy peak; with 16-byte cp.async.cg and LDS.128 it reaches 0.94.
@@ -291,7 +291,8 @@ fusedBankKernel(const __grid_constant__ BankTablesT<CT> tp, const FusedJob* __re
     constexpr int RUN0 = (HALF == 2) ? RSA / 2 : 0;       // ... starting with this one
     constexpr int NT = SB * RS;
     constexpr int NB = SB - (Q - 1);        // outputs per tile
-    constexpr int LP = D + 2;               // even sub-block pitch: rows 16-byte aligned, LDS.128 of a quarter-warp covers all banks
+    constexpr int DR = HALF ? D / 2 : D;    // samples of a sub-block this CTA reads (a half-launch stages only its half of every row)
+    constexpr int LP = DR + 2;              // even sub-block pitch: rows 16-byte aligned, LDS.128 of a quarter-warp covers all banks
     constexpr int VB = 2 * NP;
     constexpr int WS = SB / 32;             // warps per run
     constexpr int HQ = Q * (Q - 1) / 2;     // halo entries per warp: (q, lane < q)
@@ -331,14 +332,23 @@ fusedBankKernel(const __grid_constant__ BankTablesT<CT> tp, const FusedJob* __re
     // all copies of a thread are in flight at once, no register staging
     constexpr bool kImmediateStaging = (HALF == 0) && ((2 * NT) % D == 0);   // a thread's copies land one constant smem stride apart
     if constexpr (HALF != 0) {
-        // only the half of every row this CTA reads
+        // only the half of every row this CTA reads: 16-byte copies inside the block, guarded 8-byte ones at its ends
         constexpr int DH = D / 2;
+        if (mStart >= 0 && mStart + SB * D <= j0.count) {
 #pragma unroll 8
-        for (int i = tid; i < SB * DH; i += NT) {
-            const int rowI = i / DH, col = (i - rowI * DH) + RUN0 * DS;
-            const int m = mStart + rowI * D + col;
-            const bool ok = (m >= 0 && m < j0.count);
-            cpAsync8(xs + rowI * LP + col, in + (ok ? m : 0), ok);
+            for (int e = tid; e < SB * DH / 2; e += NT) {
+                const int rowI = (2 * e) / DH, col = 2 * e - rowI * DH;
+                cpAsync16(xs + rowI * LP + col, in + mStart + rowI * D + RUN0 * DS + col);
+            }
+        }
+        else {
+#pragma unroll 8
+            for (int i = tid; i < SB * DH; i += NT) {
+                const int rowI = i / DH, col = i - rowI * DH;
+                const int m = mStart + rowI * D + RUN0 * DS + col;
+                const bool ok = (m >= 0 && m < j0.count);
+                cpAsync8(xs + rowI * LP + col, in + (ok ? m : 0), ok);
+            }
         }
     }
     else if (kImmediateStaging && mStart >= 0 && mStart + SB * D <= j0.count) {
@@ -380,7 +390,7 @@ fusedBankKernel(const __grid_constant__ BankTablesT<CT> tp, const FusedJob* __re
         for (int u = 0; u < EPT; u++) { const int e = tid + u * NT; if (e < NP * D) { wqBuf[e] = tableEntry(0, e); } }
     }
 
-    const float2* xrow = xs + sb * LP + run * DS;
+    const float2* xrow = xs + sb * LP + runLocal * DS;    // (runLocal == run unless this is the second half-launch)
     const int ms = mStart + sb * D;                      // first sample of this thread's sub-block
     const bool msLive = ms < j0.count && ms + D > 0;     // the sub-block holds samples of the block
     const bool msFwd = msLive && ms >= 0;                // ... and starts inside it: phase = chk[ms >> 9] * wtab[ms & 511]
@@ -714,7 +724,7 @@ int launchBankKernel(const BankTablesT<CT>& tp, const FusedJob* dJobs, int nJobs
     using TC = TileCfg<D, TILE>;
     constexpr int SB = TC::SB, RS = HALF ? TC::RS / 2 : TC::RS;
     constexpr int NB = SB - (Q - 1);
-    constexpr size_t smem = ((size_t)SB * (D + 2) + (size_t)2 * 2 * NP * D + (size_t)2 * NP * 2 * RS * SB
+    constexpr size_t smem = ((size_t)SB * ((HALF ? D / 2 : D) + 2) + (size_t)2 * 2 * NP * D + (size_t)2 * NP * 2 * RS * SB
                              + (size_t)2 * NP * 2 * RS * (SB / 32) * (Q * (Q - 1) / 2)) * sizeof(float2);
     static bool attrSet = false;        // per instantiation
     if (!attrSet) {
@@ -788,7 +798,9 @@ int launchMainV(const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOu
     }
     else {
         const int GV = pickRange(nJobs, tiles, NP);
-        // a loop body beyond the 32 KB instruction cache level can run as two launches of half the runs each
+        // a loop body beyond the 32 KB instruction cache level runs as two launches of half the runs each: every launch
+        // stages only its half of each sub-block's samples (half the shared memory, twice the CTAs per SM) and its code
+        // (17 KB for the /8192 plan) stays in the instruction cache; the second launch adds to the first one's outputs
         constexpr int kBodyBytes = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0) * NP;
         if constexpr (kBodyBytes > 32 * 1024 && TC::RS % 2 == 0 && TC::RS >= 2) {
             if (fusedSplitRuns) {

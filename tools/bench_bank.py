@@ -37,7 +37,7 @@ def main():
     ap.add_argument("--vb", type=int, default=0, help="VFOs per register pass of the grouped first-stage kernel (0 = library default, 2, 4)")
     ap.add_argument("--gv", type=int, default=32, help="VFOs per CTA of the grouped first-stage kernel")
     ap.add_argument("--ptab", type=int, default=1, help="rotation tables in the kernel parameter block (1) or in shared memory (0)")
-    ap.add_argument("--split", type=int, default=0, help="split plans whose loop body exceeds the instruction cache into two launches")
+    ap.add_argument("--split", type=int, default=1, help="split plans whose loop body exceeds the instruction cache into two launches (library default 1)")
     args = ap.parse_args()
     cfg = configs.CONFIGS[args.cfg]
     sr = cfg["sample_rate"]
