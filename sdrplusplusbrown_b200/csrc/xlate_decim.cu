@@ -111,6 +111,7 @@ constexpr int kMinFusedRatio = 16;     // first-stage decimation >= 8 (plans 2/4
 // for the grouped kernel (FP32-bound from a few VFOs on: fewer overlap sub-blocks recomputed per output; measured
 // 0.35 of the FFMA peak against 0.32 with 2048-sample tiles, before pairing and 16-byte staging).
 #ifndef B200_D128_SMALL_TILE
+#define B200_SPLIT_BODY_BYTES (32 * 1024)   // plans with a larger unrolled body run as two half-launches; 16 KB (the /4096 plan too) measured no faster: 11.30 against 11.23 ms
 #define B200_D128_SMALL_TILE 0      // 1 = 4096-sample tiles for the /8192 plan too: measured slower (cfg4 15.3 against 14.6 ms per block)
 #endif
 constexpr int kTileSmall = 2048, kTileLarge = 4096;
@@ -802,7 +803,7 @@ int launchMainV(const FusedJob* dJobs, const FusedJob* hJobs, int nJobs, int nOu
         // stages only its half of each sub-block's samples (half the shared memory, twice the CTAs per SM) and its code
         // (17 KB for the /8192 plan) stays in the instruction cache; the second launch adds to the first one's outputs
         constexpr int kBodyBytes = (int)(D * (5.5 + 2.0 * (double)T / (double)D) * 16.0) * NP;
-        if constexpr (kBodyBytes > 32 * 1024 && TC::RS % 2 == 0 && TC::RS >= 2) {
+        if constexpr (kBodyBytes > B200_SPLIT_BODY_BYTES && TC::RS % 2 == 0 && TC::RS >= 2) {
             if (fusedSplitRuns) {
                 B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 1, false>(none, dJobs, nJobs, nOut, GV, s)));
                 B200_TRY((launchBankKernel<RATIO, NP, TILE, ODD, 2, false>(none, dJobs, nJobs, nOut, GV, s)));
