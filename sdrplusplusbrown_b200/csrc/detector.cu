@@ -213,6 +213,12 @@ int SignalDetector::setSampleRate(double sr) {
     N = n; M = 0;
     histCount = 0; histHead = 0; haveResult = false;
     if (N <= 0) { return B200_OK; }
+    const int rc = allocate();
+    if (rc != B200_OK) { freeBuffers(); N = 0; M = 0; }      // a detector without buffers passes samples through and makes no rows
+    return rc;
+}
+
+int SignalDetector::allocate() {
     int m = 32;
     while (m < 2 * N - 1) { m <<= 1; }
     M = m;

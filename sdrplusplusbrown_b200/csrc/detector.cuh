@@ -46,6 +46,7 @@ struct SignalDetector {
     void freeBuffers();
     int syncLast() { if (everRan) { B200_CUDA(cudaStreamSynchronize(lastStream)); } return B200_OK; }
     int setSampleRate(double sr);
+    int allocate();              // buffers, window, chirp and chirp-filter spectrum for the current N
     void setCenterFrequency(double f);
     void clear() { pos = 0; sinceDetect = 0; }
     int process(const cf32* dIn, int count, cudaStream_t s);
