@@ -248,6 +248,23 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    # the graph as the reference itself runs it -- a Splitter copying every block to one stream per VFO,
+    # one thread per RxVFO -- for as many VFOs of the workload as the host has cores (reference blocks only; a few seconds)
+    if cpu.kind == "reference":
+        try:
+            vl = configs.vfo_list(WORKLOAD)
+            n_v = min(cpu.threads, len(vl))
+            pick = [vl[(i * len(vl)) // n_v] for i in range(n_v)]
+            blk = x[:min(len(x), 1000000)]
+            secs = cpu.ol.graph_run(cpu.orc, cfg["sample_rate"], [(v[1], v[2], v[3]) for v in pick], blk, 2)
+            if secs > 0:
+                line["cpu_baseline"]["threaded_graph"] = {
+                    "value": 2 * len(blk) / secs / 1e6, "unit": UNIT, "vfos": n_v, "threads": n_v + 1,
+                    "what": "dsp::routing::Splitter + one dsp::channel::RxVFO thread per VFO + Null sinks (iq_frontend.cpp:159-180), %d of the workload's "
+                            "%d VFOs (one per host core), 1 M-sample blocks, no FFT branch; scale by %d / %d for the whole bank on this host"
+                            % (n_v, len(vl), n_v, len(vl))}
+        except Exception as e:       # the measurement is an extra: never fail the arm over it
+            line["cpu_baseline"]["threaded_graph"] = {"unavailable": str(e)}
     print(json.dumps(line))
 
 

@@ -157,6 +157,15 @@ int orc_logmmse_process(void* h, int count, const float* in, float* out); // pro
 float orc_expn(float x);                                                  // dsp::math::expn (utils/arrays.cpp:60-431): E1 from its table
 int orc_logmmse_noise(void* h, float* out, int cap);                      // SavedParamsC::noise_mu2; returns its length (0 before sampling)
 
+// ---- the reference's threaded block graph for the many-VFO case (SURVEY 8(d) CPU baseline mode (ii); timing only):
+// one dsp::routing::Splitter (routing/splitter.h:59-92) fanning the input stream out to nVfos dsp::channel::RxVFO blocks,
+// each on its own thread (dsp/block.h:82-84) behind its own stream, wired as IQFrontEnd::addVFO does
+// (signal_path/iq_frontend.cpp:159-180), every VFO output drained by a dsp::sink::Null.  Feeds `block` (blockLen samples)
+// nBlocks times and returns the seconds until every VFO has processed all of them.  The port has no threads or streams:
+// it returns -1.
+double orc_graph_run(double inSR, int nVfos, const double* outSR, const double* bandwidth, const double* offset,
+                     int blockLen, int nBlocks, const float* block);
+
 #ifdef __cplusplus
 }
 #endif

@@ -743,6 +743,8 @@ struct Preproc {
 extern "C" {
 
 const char* orc_kind(void) { return "port"; }
+// (the threaded graph is measured with the reference's own blocks only)
+double orc_graph_run(double, int, const double*, const double*, const double*, int, int, const float*) { return -1.0; }
 
 void* orc_vfo_create(double inSR, double outSR, double bandwidth, double offset) {
     auto* v = new Vfo; v->init(inSR, outSR, bandwidth, offset); return v;

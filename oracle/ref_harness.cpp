@@ -52,6 +52,10 @@
 #include <utils/wav.h>
 #include <dsp/compression/sample_stream_compressor.h>
 #include <dsp/compression/sample_stream_decompressor.h>
+#include <dsp/routing/splitter.h>
+#include <dsp/sink/null_sink.h>
+#include <chrono>
+#include <memory>
 #undef protected
 #undef private
 
@@ -77,6 +81,45 @@ struct Preproc {
 extern "C" {
 
 const char* orc_kind(void) { return "reference"; }
+
+// The graph the reference runs for a bank of VFOs: Splitter -> per-VFO stream -> RxVFO thread -> consumer
+// (iq_frontend.cpp:159-180; the consumer here is a Null sink).  Timing only.
+double orc_graph_run(double inSR, int nVfos, const double* outSR, const double* bandwidth, const double* offset,
+                     int blockLen, int nBlocks, const float* block) {
+    if (nVfos <= 0 || blockLen <= 0 || blockLen > STREAM_BUFFER_SIZE || nBlocks <= 0) { return -1.0; }
+    dsp::stream<dsp::complex_t> src;
+    dsp::routing::Splitter<dsp::complex_t> split;
+    split.init(&src);
+    std::vector<std::unique_ptr<dsp::stream<dsp::complex_t>>> taps;
+    std::vector<std::unique_ptr<dsp::channel::RxVFO>> vfos;
+    std::vector<std::unique_ptr<dsp::sink::Null<dsp::complex_t>>> sinks;
+    for (int i = 0; i < nVfos; i++) {
+        taps.emplace_back(new dsp::stream<dsp::complex_t>());
+        split.bindStream(taps.back().get());
+        vfos.emplace_back(new dsp::channel::RxVFO(taps.back().get(), inSR, outSR[i], bandwidth[i], offset[i]));
+        sinks.emplace_back(new dsp::sink::Null<dsp::complex_t>());
+        sinks.back()->init(&vfos.back()->out);
+    }
+    for (auto& s : sinks) { s->start(); }
+    for (auto& v : vfos) { v->start(); }
+    split.start();
+    auto feed = [&](int n) {
+        memcpy(src.writeBuf, block, (size_t)n * sizeof(dsp::complex_t));
+        return src.swap(n);
+    };
+    feed(blockLen);                      // one block untimed: threads up, buffers touched
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int b = 0; b < nBlocks; b++) { feed(blockLen); }
+    // a swap returns once the reader has flushed the block before: after two more (small) blocks have gone through the
+    // Splitter, every VFO has flushed -- i.e. processed -- the last timed block
+    feed(16);
+    feed(16);
+    const auto t1 = std::chrono::steady_clock::now();
+    split.stop();
+    for (auto& v : vfos) { v->stop(); }
+    for (auto& s : sinks) { s->stop(); }
+    return std::chrono::duration<double>(t1 - t0).count();
+}
 
 // ---------------------------------------------------------------- RxVFO
 void* orc_vfo_create(double inSR, double outSR, double bandwidth, double offset) {

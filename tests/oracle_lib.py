@@ -103,6 +103,7 @@ _SIGS = {
     "orc_logmmse_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_logmmse_noise": (_i, [_vp, _vp, _i]),
     "orc_expn": (_f, [_f]),
+    "orc_graph_run": (_d, [_d, _i, _vp, _vp, _vp, _i, _i, _vp]),
 }
 
 
@@ -495,6 +496,15 @@ class LogMmse(_Block):
         if n:
             self.orc.lib.orc_logmmse_noise(self.h, out.ctypes.data, n)
         return out
+
+
+def graph_run(orc, in_sr, vfos, block, n_blocks):
+    """the reference's Splitter + one-thread-per-RxVFO graph on `block` fed n_blocks times: seconds, or -1 (port)"""
+    block = np.ascontiguousarray(block, np.complex64)
+    o = np.array([v[0] for v in vfos], np.float64)
+    b = np.array([v[1] for v in vfos], np.float64)
+    f = np.array([v[2] for v in vfos], np.float64)
+    return orc.lib.orc_graph_run(float(in_sr), len(vfos), o.ctypes.data, b.ctypes.data, f.ctypes.data, len(block), int(n_blocks), block.ctypes.data)
 
 
 def sigdet_row(orc, x):
