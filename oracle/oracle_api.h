@@ -166,6 +166,17 @@ int orc_logmmse_noise(void* h, float* out, int cap);                      // Sav
 double orc_graph_run(double inSR, int nVfos, const double* outSR, const double* bandwidth, const double* offset,
                      int blockLen, int nBlocks, const float* block);
 
+// ---- dsp::compression::ExperimentalFFTCompressor (dsp/compression/experimental_fft_compressor.h), the block in front of the
+// server's sample-packet compressor (core/src/server.cpp:101-110): frames of fftSize = 2^floor(log2(sampleRate / 20))
+// samples -> frequency domain, bins under the tracked noise floor zeroed, the rest amplitude-companded; ten frames of delay.
+void* orc_fftcomp_create(int sampleRate, double lossRate);
+void orc_fftcomp_destroy(void* h);
+int orc_fftcomp_fft_size(void* h);
+void orc_fftcomp_set_masked(void* h, const int* fromToHz, int n);            // setMaskedFrequencies :99-103 (pairs from, to)
+// appends the block to the input buffer and runs process() once (:198-427, as run() :431-452 does): returns 0 or fftSize
+int orc_fftcomp_process(void* h, int count, const float* in, float* out);
+int orc_fftcomp_noise_figure(void* h, float* out, int cap);                  // noiseFigure (30 values; server.cpp:470-474 sends it on)
+
 #ifdef __cplusplus
 }
 #endif

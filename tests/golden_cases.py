@@ -189,6 +189,18 @@ def _run_logmmse(orc, name):
                 input_crc=_crc(x))
 
 
+def _run_fftcomp(orc, name):
+    sr = 48000
+    x = logmmse_input(sr, 2.0, seed=6)
+    c = ol.FftCompressor(orc, sr, 10.0)
+    assert c.n == 2048
+    outs = [c.process(b) for b in _blocks(x, c.n)]
+    y = np.concatenate(outs)
+    return dict(counts=np.array([len(o) for o in outs], np.int32), out_first=outs[12].copy(), out_crc=_crc(y),
+                zeroed=np.array([int(np.count_nonzero(o == 0)) for o in outs if len(o)], np.int32), noise_figure=c.noise_figure(),
+                input_crc=_crc(x))
+
+
 CASES = {}
 for _n in VFO_GOLDEN:
     CASES[_n] = _run_vfo
@@ -200,6 +212,7 @@ for _n in ("demod_nfm", "demod_usb", "demod_lsb", "demod_am", "demod_am_carrier"
 CASES["taps"] = _run_taps
 CASES["sigdet_51200"] = _run_sigdet
 CASES["logmmse_24000"] = _run_logmmse
+CASES["fftcomp_48000"] = _run_fftcomp
 
 
 def run_case(orc, name):

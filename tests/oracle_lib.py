@@ -103,6 +103,12 @@ _SIGS = {
     "orc_logmmse_process": (_i, [_vp, _i, _vp, _vp]),
     "orc_logmmse_noise": (_i, [_vp, _vp, _i]),
     "orc_expn": (_f, [_f]),
+    "orc_fftcomp_create": (_vp, [_i, _d]),
+    "orc_fftcomp_destroy": (None, [_vp]),
+    "orc_fftcomp_fft_size": (_i, [_vp]),
+    "orc_fftcomp_set_masked": (None, [_vp, _vp, _i]),
+    "orc_fftcomp_process": (_i, [_vp, _i, _vp, _vp]),
+    "orc_fftcomp_noise_figure": (_i, [_vp, _vp, _i]),
     "orc_graph_run": (_d, [_d, _i, _vp, _vp, _vp, _i, _i, _vp]),
 }
 
@@ -496,6 +502,29 @@ class LogMmse(_Block):
         if n:
             self.orc.lib.orc_logmmse_noise(self.h, out.ctypes.data, n)
         return out
+
+
+class FftCompressor(_Block):
+    """dsp::compression::ExperimentalFFTCompressor: blocks in, one frequency-domain frame (or nothing) out per call"""
+
+    def __init__(self, orc, sample_rate, loss_rate=1.0):
+        super().__init__(orc, orc.lib.orc_fftcomp_create(int(sample_rate), float(loss_rate)), "orc_fftcomp")
+        self.n = orc.lib.orc_fftcomp_fft_size(self.h)
+
+    def process(self, x):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(self.n, np.complex64)
+        k = self.orc.lib.orc_fftcomp_process(self.h, len(x), x.ctypes.data, out.ctypes.data)
+        return out[:k].copy()
+
+    def set_masked(self, from_to_hz):
+        a = np.ascontiguousarray(from_to_hz, np.int32)
+        self.orc.lib.orc_fftcomp_set_masked(self.h, a.ctypes.data, len(a))
+
+    def noise_figure(self):
+        out = np.zeros(64, np.float32)
+        k = self.orc.lib.orc_fftcomp_noise_figure(self.h, out.ctypes.data, 64)
+        return out[:k].copy()
 
 
 def graph_run(orc, in_sr, vfos, block, n_blocks):
