@@ -470,6 +470,28 @@ int b200_logmmse_process_host(b200_logmmse* d, const float* h_in, int count, flo
 int b200_logmmse_sync(b200_logmmse* d);
 int b200_logmmse_noise(b200_logmmse* d, float* h_out, int cap);   /* the noise power estimate per bin: returns its length, 0 before sampling */
 
+/* ---- dsp::compression::ExperimentalFFTCompressor: the spectral compressor of the SDR++ server's sample
+ * stream.  Replaces core/src/dsp/compression/experimental_fft_compressor.h (setSampleRate :66-88, process :198-427,
+ * filterSignal :116-177, estimateNoise :181-189, setMaskedFrequencies :99-103), which core/src/server.cpp:101-110 puts
+ * between its resampler and the PCM sample-packet compressor (here: b200_stream_compress on the frame this returns).
+ * Every 2^floor(log2(sample_rate / 20)) input samples become one frame of as many frequency-domain samples (DC in the
+ * middle), ten frames late: bins that do not rise above the tracked noise floor by the allowance (loss_rate scales it;
+ * 0 = keep every bin) are zeroed, the others carry |X|^(1/4) at X's phase.  As in the reference, a call takes the whole
+ * block into its input buffer but lets at most ONE frame out: feed blocks of at most a frame.  For the same dB rows
+ * every bin is kept or zeroed exactly as by the reference (the noise-floor chain runs in its summation order); the rows
+ * themselves agree to FFT rounding.  Transmit mode (setTxMode) is not served. */
+typedef struct b200_fftcomp b200_fftcomp;
+int b200_fftcomp_create(b200_fftcomp** out, int sample_rate, double loss_rate, int max_block, int device);
+void b200_fftcomp_destroy(b200_fftcomp* c);
+int b200_fftcomp_fft_size(b200_fftcomp* c);
+int b200_fftcomp_set_loss_rate(b200_fftcomp* c, double loss_rate);                       /* the public lossRate member (server.cpp:544) */
+int b200_fftcomp_set_masked(b200_fftcomp* c, const int32_t* from_to_hz, int n);         /* setMaskedFrequencies: n values = n / 2 ranges always kept */
+/* DEVICE samples in; *d_out receives a device pointer to *out_count (0 or fft_size) samples, valid until the next call */
+int b200_fftcomp_process(b200_fftcomp* c, const float* d_in, int count, const float** d_out, int* out_count, void* stream);
+int b200_fftcomp_process_host(b200_fftcomp* c, const float* h_in, int count, float* h_out, int* out_count, void* stream);
+int b200_fftcomp_sync(b200_fftcomp* c);
+int b200_fftcomp_noise_figure(b200_fftcomp* c, float* h_out, int cap);                   /* 30 values (server.cpp:470-474); 0 before the first filtered frame */
+
 /* One complex spectrum for tests: FFT of an already-windowed frame, no log (checks K9 alone). */
 int b200_fft_forward(const float* d_in, int nz, int fft_size, float* d_out, void* stream);
 

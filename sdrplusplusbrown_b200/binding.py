@@ -147,6 +147,15 @@ _SIGS = {
     "b200_logmmse_process_host": (_i, [_vp, _vp, _i, _vp, _i, C.POINTER(_i), _vp]),
     "b200_logmmse_sync": (_i, [_vp]),
     "b200_logmmse_noise": (_i, [_vp, _vp, _i]),
+    "b200_fftcomp_create": (_i, [_pp, _i, _d, _i, _i]),
+    "b200_fftcomp_destroy": (None, [_vp]),
+    "b200_fftcomp_fft_size": (_i, [_vp]),
+    "b200_fftcomp_set_loss_rate": (_i, [_vp, _d]),
+    "b200_fftcomp_set_masked": (_i, [_vp, _vp, _i]),
+    "b200_fftcomp_process": (_i, [_vp, _vp, _i, _pp, C.POINTER(_i), _vp]),
+    "b200_fftcomp_process_host": (_i, [_vp, _vp, _i, _vp, C.POINTER(_i), _vp]),
+    "b200_fftcomp_sync": (_i, [_vp]),
+    "b200_fftcomp_noise_figure": (_i, [_vp, _vp, _i]),
     "b200_fft_forward": (_i, [_vp, _i, _i, _vp, _vp]),
     "b200_dc_block_noalloc": (_i, [_vp, _vp, _i, _d, _vp, _vp]),
     "b200_waterfall_create": (_i, [_pp, _i, _i, _i]),
@@ -338,6 +347,54 @@ class VfoBank:
         counts = np.zeros(nslots, np.int32)
         _chk(lib.b200_vfo_bank_process_host(self.h, x.ctypes.data, len(x), ptrs, counts.ctypes.data, _stream_ptr(stream)))
         return {v: bufs[v][:counts[v]].copy() for v in vfos}
+
+
+class FftCompressor:
+    """dsp::compression::ExperimentalFFTCompressor (dsp/compression/experimental_fft_compressor.h) on one GPU."""
+
+    def __init__(self, sample_rate, loss_rate=1.0, max_block=1000000, device=0):
+        h = _vp()
+        _chk(lib.b200_fftcomp_create(C.byref(h), int(sample_rate), float(loss_rate), int(max_block), int(device)))
+        self.h = h
+        self.device = device
+        self.n = lib.b200_fftcomp_fft_size(h)
+
+    def close(self):
+        if self.h:
+            lib.b200_fftcomp_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_loss_rate(self, r): _chk(lib.b200_fftcomp_set_loss_rate(self.h, float(r)))
+
+    def set_masked(self, from_to_hz):
+        a = np.ascontiguousarray(from_to_hz, np.int32)
+        _chk(lib.b200_fftcomp_set_masked(self.h, a.ctypes.data, len(a)))
+
+    def process(self, d_in, count=None, stream=None):
+        if count is None:
+            count = d_in.shape[0]
+        p, n = _vp(), _i()
+        _chk(lib.b200_fftcomp_process(self.h, d_in.data_ptr() if count else None, int(count), C.byref(p), C.byref(n), _stream_ptr(stream)))
+        _chk(lib.b200_fftcomp_sync(self.h))
+        return _dev_to_numpy(p.value, n.value, np.complex64, self.device) if n.value else np.zeros(0, np.complex64)
+
+    def process_host(self, x, stream=None):
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.zeros(self.n, np.complex64)
+        n = _i()
+        _chk(lib.b200_fftcomp_process_host(self.h, x.ctypes.data, len(x), out.ctypes.data, C.byref(n), _stream_ptr(stream)))
+        return out[:n.value].copy()
+
+    def noise_figure(self):
+        out = np.zeros(30, np.float32)
+        k = _chk(lib.b200_fftcomp_noise_figure(self.h, out.ctypes.data, 30))
+        return out[:k].copy()
 
 
 class LogMmse:

@@ -249,3 +249,11 @@ def test_logmmse_dropin_against_oracle(tmp_path):
     ref = np.concatenate(outs)
     assert len(ref) > 0.4 * len(x)
     assert err_db(got, ref) <= -80.0
+
+
+def test_fft_compressor_dropin_passes_through_while_disabled(tmp_path):
+    exe = str(tmp_path / "dropin_compressor_cpu")
+    _compile(os.path.join(ROOT, "tests", "cpp", "dropin_compressor_cpu.cpp"), exe)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    assert "dropin_compressor_cpu ok" in out.stdout
