@@ -10,9 +10,8 @@
 // The two transforms of a frame are the power-of-two FFT passes of fft.cu.  The noise-floor tracker is a chain of running
 // sums (centeredSma, core/src/utils/arrays.cpp:474-495) and hole interpolations (:433-470) whose fp32 rounding depends on
 // the order of summation, with thresholds taken on the results: it runs in ONE thread block in the reference's order --
-// element-wise steps on all threads, every running sum on one thread (two independent ones on two warps) -- so that for
-// the same dB rows every bin is kept or zeroed exactly as in the reference.  A frame is 50 ms of signal; the chain takes
-// about 3 ms at 65536 bins.  Transmit mode (setTxMode) is not served.
+// element-wise steps on all threads, every running sum on one thread over differences staged in shared memory -- so that
+// for the same dB rows every bin is kept or zeroed exactly as in the reference.  A frame is 27-55 ms of signal.  Transmit mode (setTxMode) is not served.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -62,39 +61,64 @@ __global__ void fcMeanKernel(const float* __restrict__ ring, int head, int count
     out[i] = __fmul_rn(acc, inv);
 }
 
-// centeredSma (utils/arrays.cpp:474-495), one thread
-__device__ void seqCenteredSma(const float* in, float* out, int limit, int winsize) {
-    float total = 0.0f;
-    const int win2 = winsize / 2;
+constexpr int kSmaChunk = 8192;           // running-sum elements staged in shared memory at a time
+
+// centeredSma (utils/arrays.cpp:474-495) by the whole block.  The running total is a sequential fp32 recurrence
+// (total += in[i] - in[i - w], in that order), so ONE thread walks it -- but over shared memory: all threads first form the
+// differences of a chunk (exact, element-wise), thread 0 adds them up leaving the total BEFORE each step in place, all
+// threads divide and store.  in and out must not overlap.
+__device__ void blockCenteredSma(const float* __restrict__ in, float* __restrict__ out, int limit, int winsize, float* sm, float* sTotal) {
+    const int tid = threadIdx.x, win2 = winsize / 2;
     const float fw = (float)winsize;
-    for (int i = 0; i < winsize; i++) { total = __fadd_rn(total, in[i]); }
-    for (int i = winsize; i < limit; i++) {
-        out[i - win2] = __fdiv_rn(total, fw);
-        total = __fadd_rn(total, __fsub_rn(in[i], in[i - winsize]));
+    if (tid == 0) {
+        float total = 0.0f;
+        for (int i = 0; i < winsize; i++) { total = __fadd_rn(total, in[i]); }
+        *sTotal = total;
     }
-    for (int i = 0; i < winsize - win2; i++) { out[i] = out[winsize - win2]; }
-    for (int i = limit - win2; i < limit; i++) { out[i] = out[limit - win2 - 1]; }
+    __syncthreads();
+    for (int c0 = winsize; c0 < limit; c0 += kSmaChunk) {
+        const int m = min(kSmaChunk, limit - c0);
+        for (int k = tid; k < m; k += kTrackThreads) { sm[k] = __fsub_rn(in[c0 + k], in[c0 + k - winsize]); }
+        __syncthreads();
+        if (tid == 0) {
+            float total = *sTotal;
+            for (int k = 0; k < m; k++) { const float before = total; total = __fadd_rn(total, sm[k]); sm[k] = before; }
+            *sTotal = total;
+        }
+        __syncthreads();
+        for (int k = tid; k < m; k += kTrackThreads) { out[c0 + k - win2] = __fdiv_rn(sm[k], fw); }
+        __syncthreads();
+    }
+    const float head = out[winsize - win2], tail = out[limit - win2 - 1];
+    __syncthreads();
+    for (int i = tid; i < winsize - win2; i += kTrackThreads) { out[i] = head; }
+    for (int i = limit - win2 + tid; i < limit; i += kTrackThreads) { out[i] = tail; }
+    __syncthreads();
 }
 
-// linearInterpolateHoles (utils/arrays.cpp:433-470), one thread
-__device__ void seqFillHoles(float* arr, int n) {
-    int first = -1, last = -1;
-    for (int q = 0; q < n; q++) {
-        const float val = arr[q];
-        if (first < 0 && val != 0.0f) { first = q; }
-        if (val != 0.0f) {
-            if (last != -1 && q - last > 1) {
-                const float d = __fdiv_rn(__fsub_rn(val, arr[last]), (float)(q - last));
-                float running = arr[last];
-                for (int w = last + 1; w < q; w++) { running = __fadd_rn(running, d); arr[w] = running; }
-            }
-            last = q;
+// linearInterpolateHoles (utils/arrays.cpp:433-470) by the whole block: src = the array with its zeros, dst receives the
+// filled array.  Every kept element fills the gap to its left neighbour with the reference's running sum (sequential per
+// gap, so one thread per gap); the first / last kept ones also fill the ends.  Nothing kept: dst = src.
+__device__ void blockFillHoles(const float* __restrict__ src, float* __restrict__ dst, int n) {
+    const int tid = threadIdx.x;
+    for (int q = tid; q < n; q += kTrackThreads) { dst[q] = src[q]; }
+    __syncthreads();                                     // (the gap fillers below write other threads' elements)
+    for (int q = tid; q < n; q += kTrackThreads) {
+        const float val = src[q];
+        if (val == 0.0f) { continue; }
+        int last = q - 1;
+        while (last >= 0 && src[last] == 0.0f) { last--; }
+        if (last < 0) { for (int w = q - 1; w >= 0; w--) { dst[w] = val; } }
+        else if (q - last > 1) {
+            const float d = __fdiv_rn(__fsub_rn(val, src[last]), (float)(q - last));
+            float running = src[last];
+            for (int w = last + 1; w < q; w++) { running = __fadd_rn(running, d); dst[w] = running; }
         }
+        int next = q + 1;
+        while (next < n && src[next] == 0.0f) { next++; }
+        if (next >= n) { for (int w = q + 1; w < n; w++) { dst[w] = val; } }
     }
-    if (first < 0 || last < 0) { return; }
-    const float a = arr[first], b = arr[last];
-    for (int q = first - 1; q >= 0; q--) { arr[q] = a; }
-    for (int q = last + 1; q < n; q++) { arr[q] = b; }
+    __syncthreads();
 }
 
 // percentile::percentile_sampling (utils/strings.h:153-175) over kthSmallest / partition (:93-140), whose pivot is held in
@@ -130,7 +154,7 @@ struct TrackArgs {
     const float* win;        // mean windowed dB row
     const float* clr;        // mean plain dB row
     cf32* frame;             // the frame going out (ten frames old), filtered and companded in place
-    float* a; float* b; float* c; float* d;      // scratch, n floats each
+    float* a; float* b; float* c; float* d; float* e;      // scratch, n floats each
     float* prevAllowance;    // carried between frames
     float* noiseFigure;      // 30 values
     const int* masked;       // pairs (from, to) in Hz
@@ -144,17 +168,17 @@ struct TrackArgs {
 // filterSignal :116-177 + estimateNoise :181-189 + the amplitude companding :257-266, one block
 __global__ void __launch_bounds__(kTrackThreads) fcTrackKernel(TrackArgs t) {
     const int tid = threadIdx.x, n = t.n;
+    __shared__ float sm[kSmaChunk];
+    __shared__ float sTotal;
     __shared__ double sAllowance;
     __shared__ float sCmaxAllow;
     if (t.filter) {
-        // mean over 16 bins of the windowed row (-> a), and its long moving average (-> c): independent running sums
-        if (tid == 0) { seqCenteredSma(t.win, t.a, n, kNoisePoints); }
-        if (tid == 32) { seqCenteredSma(t.win, t.c, n, t.largeTick); }
-        __syncthreads();
+        blockCenteredSma(t.win, t.a, n, kNoisePoints, sm, &sTotal);                 // a = mean over 16 bins of the windowed row
         for (int i = tid; i < n; i += kTrackThreads) { const float e = __fsub_rn(t.win[i], t.a[i]); t.b[i] = __fmul_rn(e, e); }
         __syncthreads();
+        blockCenteredSma(t.b, t.a, n, kNoisePoints, sm, &sTotal);                   // a = moving variance
+        blockCenteredSma(t.win, t.c, n, t.largeTick, sm, &sTotal);                  // c = long moving average of the row
         if (tid == 0) {
-            seqCenteredSma(t.b, t.a, n, kNoisePoints);                      // a = moving variance
             const double newAllowance = t.lossRate * (double)seqPercentileSampling(t.a, n, .15);
             const double allowance = __dadd_rn(__dmul_rn(newAllowance, 0.1), __dmul_rn((double)*t.prevAllowance, 0.9));     // (no contraction)
             *t.prevAllowance = (float)allowance;
@@ -164,12 +188,9 @@ __global__ void __launch_bounds__(kTrackThreads) fcTrackKernel(TrackArgs t) {
         const double allowance = sAllowance;
         for (int i = tid; i < n; i += kTrackThreads) { if ((double)t.a[i] > allowance) { t.c[i] = 0.0f; } }
         __syncthreads();
-        if (tid == 0) {
-            seqFillHoles(t.c, n);
-            seqCenteredSma(t.c, t.b, n, t.largeTick);                       // b = cleared noise floor
-            seqCenteredSma(t.b, t.d, n, 5 * t.largeTick);                   // d = its longer average
-        }
-        __syncthreads();
+        blockFillHoles(t.c, t.e, n);
+        blockCenteredSma(t.e, t.b, n, t.largeTick, sm, &sTotal);                    // b = cleared noise floor
+        blockCenteredSma(t.b, t.d, n, 5 * t.largeTick, sm, &sTotal);                // d = its longer average
         for (int i = tid; i < n; i += kTrackThreads) { t.d[i] = fabsf(__fsub_rn(t.b[i], t.d[i])); }
         __syncthreads();
         if (tid == 0) { sCmaxAllow = seqPercentileSampling(t.d, n, .15); }
@@ -177,11 +198,8 @@ __global__ void __launch_bounds__(kTrackThreads) fcTrackKernel(TrackArgs t) {
         const float cmaxAllow = sCmaxAllow;
         for (int i = tid; i < n; i += kTrackThreads) { if (t.d[i] > cmaxAllow) { t.b[i] = 0.0f; } }
         __syncthreads();
-        if (tid == 0) {
-            seqFillHoles(t.b, n);
-            seqCenteredSma(t.b, t.c, n, t.largeTick);                       // c = the noise floor
-        }
-        __syncthreads();
+        blockFillHoles(t.b, t.e, n);
+        blockCenteredSma(t.e, t.c, n, t.largeTick, sm, &sTotal);                    // c = the noise floor
         // bins above the floor by more than the allowance, and the caller's masked ranges, widened by 37 bins
         for (int i = tid; i < n; i += kTrackThreads) { t.a[i] = ((double)t.clr[i] > (double)t.c[i] + allowance) ? 1.0f : 0.0f; }
         __syncthreads();
@@ -191,8 +209,7 @@ __global__ void __launch_bounds__(kTrackThreads) fcTrackKernel(TrackArgs t) {
             for (int j = from + tid; j < to; j += kTrackThreads) { if (j >= 0 && j < n) { t.a[j] = 1.0f; } }
         }
         __syncthreads();
-        if (tid == 0) { seqCenteredSma(t.a, t.b, n, kSignalWidth / 8); }
-        __syncthreads();
+        blockCenteredSma(t.a, t.b, n, kSignalWidth / 8, sm, &sTotal);
         for (int i = tid; i < n; i += kTrackThreads) { if (t.b[i] == 0.0f) { t.frame[i] = cf32{ 0.0f, 0.0f }; } }
         const int slice = n / 30;
         if (tid < 30) { t.noiseFigure[tid] = __fadd_rn(7.0f, t.c[tid * slice + slice / 2]); }
@@ -224,7 +241,7 @@ struct FftCompressor {
     float* dWin = nullptr;
     cf32* dSpec = nullptr; cf32* dFreqRing = nullptr; cf32* dOut = nullptr;
     float* dClrRing = nullptr; float* dWinRing = nullptr; float* dClrAvg = nullptr; float* dWinAvg = nullptr;
-    float* dScratch = nullptr;       // 4 x N
+    float* dScratch = nullptr;       // 5 x N
     float* dState = nullptr;         // [0] prevAllowance, [1..30] noise figure
     int* dMasked = nullptr; int nMasked = 0;
     FrameDesc* dFrames = nullptr;
@@ -260,7 +277,7 @@ int FftCompressor::init(int sampleRate_, double lossRate_, int maxBlock_, int de
     B200_CUDA(cudaMalloc((void**)&dWinRing, (size_t)kMagRows * N * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&dClrAvg, (size_t)N * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&dWinAvg, (size_t)N * sizeof(float)));
-    B200_CUDA(cudaMalloc((void**)&dScratch, (size_t)4 * N * sizeof(float)));
+    B200_CUDA(cudaMalloc((void**)&dScratch, (size_t)5 * N * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&dState, 32 * sizeof(float)));
     B200_CUDA(cudaMemset(dState, 0, 32 * sizeof(float)));
     B200_CUDA(cudaMalloc((void**)&dMasked, 256 * sizeof(int)));
@@ -321,7 +338,7 @@ int FftCompressor::process(const cf32* dIn, int count, int* outCount, cudaStream
     B200_CHECK_LAUNCH(); countLaunch();
     TrackArgs t;
     t.win = dWinAvg; t.clr = dClrAvg; t.frame = dOut;
-    t.a = dScratch; t.b = dScratch + N; t.c = dScratch + 2 * (size_t)N; t.d = dScratch + 3 * (size_t)N;
+    t.a = dScratch; t.b = dScratch + N; t.c = dScratch + 2 * (size_t)N; t.d = dScratch + 3 * (size_t)N; t.e = dScratch + 4 * (size_t)N;
     t.prevAllowance = dState; t.noiseFigure = dState + 1;
     t.masked = dMasked; t.nMasked = nMasked;
     t.n = N; t.largeTick = largeTick; t.hzTick = hzTick; t.lossRate = lossRate; t.filter = lossRate > 0 ? 1 : 0;

@@ -79,6 +79,33 @@ def main():
         print(json.dumps(line), flush=True)
         del d, x
 
+    for sr in (240000, 2400000, 10000000):
+        d = binding.FftCompressor(sr, 10.0, max_block=1 << 20)
+        n = d.n
+        x = synth.make_iq_torch(n * 4, float(sr), dev, tones=[(0.11 * sr, 0.05)])
+        blocks = [x[i * n:(i + 1) * n] for i in range(4)]
+        p, cnt = binding.C.c_void_p(), binding.C.c_int()
+
+        def feed_c():
+            for b in blocks:
+                binding._chk(binding.lib.b200_fftcomp_process(d.h, b.data_ptr(), n, binding.C.byref(p), binding.C.byref(cnt), s.cuda_stream))
+        for _ in range(3):
+            feed_c()                              # past the ten frames of delay
+        ms = timed(feed_c, 3)
+        line = {"plugin": "server spectral compressor", "sample_rate": sr, "fft_size": n, "ms_per_frame": ms / 4, "x_real_time": (4 * n / sr) / (ms * 1e-3)}
+        if sr <= 2400000:
+            xh = x.cpu().numpy().view(np.complex64).reshape(-1)
+            oc = ol.FftCompressor(orc, sr, 10.0)
+            for _ in range(3):
+                for i in range(4):
+                    oc.process(xh[i * n:(i + 1) * n])
+            t0 = time.perf_counter()
+            for i in range(4):
+                oc.process(xh[i * n:(i + 1) * n])
+            line["cpu_oracle"] = {"kind": orc.kind, "cores": 1, "ms_per_frame": (time.perf_counter() - t0) * 1e3 / 4, "sample": "four frames"}
+        print(json.dumps(line), flush=True)
+        del d, x
+
 
 if __name__ == "__main__":
     main()
