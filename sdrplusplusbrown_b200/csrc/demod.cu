@@ -80,7 +80,7 @@ struct DemodState {
 };
 
 // per-call descriptors of the WFM stereo stages
-struct PllJob { const float* pr; const float* pi; float* phaseOut; SeqState* st; float alpha, beta, minFreq, maxFreq; int n, pad; };
+struct PllJob { const float* pr; const float* pi; float* phaseOut; SeqState* st; float alpha, beta, minFreq, maxFreq; int n, pad; };   // pllKernel or pllErrKernel: the bank's rotator mode decides
 struct WfmMixJob { const float* mpx; const float* hist; float* histNext; const float* phase; float* l; float* r; int n, delay; };
 struct LrJob { const float* l; const float* r; float* stereo; int n, pad; };
 
@@ -543,6 +543,194 @@ __global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs)
         __syncwarp();
     }
     if (lane == 0) { j.st->pllPhase = phase; j.st->pllFreq = freq; }
+}
+
+// ---- the pilot PLL of the default (B200_ROTATOR_FAST) banks: the same loop walked in its ERROR form
+// With x[i] the pilot's phase, e[i] = wrap(x[i] - phase[i]) and dx[i] = wrap(x[i+1] - x[i]) (no recurrence: all lanes), the
+// reference's two updates  freq += beta * e;  phase += freq + alpha * e  become
+//     freq[i] = clamp(freq[i-1] + beta * e[i])
+//     e[i+1]  = wrap(dx[i] + (1 - alpha) * e[i] - freq[i])
+// and phase[i] = wrap(x[i] - e[i]) is recovered afterwards, in parallel.  In exact arithmetic that IS the reference's
+// recurrence; in fp32 a step rounds differently by about an ulp of the error, and the loop contracts such differences by
+// (1 - alpha) per sample instead of accumulating them: the VCO phases agree with the reference's to ~1e-6 rad (tests: the
+// decoded channels to -80 dB, the bar of the exact walk).  What it buys is the length of the dependent chain, which is all
+// a sequential walk costs (fourteen dependent instructions per sample in the reference's order, 135 cycles):
+//   * LINEAR walk, for a loop in lock: while no step leaves (-pi, pi] and the frequency keeps clear of its limits, neither
+//     the wrap nor the clamp does anything, and with d[i] = dx[i] - freq[i-1] formed beside the chain (freq runs one step
+//     behind e) the chain is ONE instruction:  e[i+1] = fma(1 - alpha - beta, e[i], d[i]).  The largest step and the range
+//     of the frequency are watched beside the chain and judged after the chunk;
+//   * FULL walk, wrap and clamp in the chain (six dependent instructions), for the chunks the linear walk was not valid
+//     for (they are walked again from the chunk's start) and the chunks after them until one would have been.
+// A chunk that defeats even the full walk (a step beyond 3 pi: not with the loop's gains) is walked in the reference's
+// order.  Every chunk starts from (phase, freq) and ends by advancing them as the reference does, so the carried state
+// means the same in both kernels.  NaN pilot samples: the reference's phase is NaN from the sample after the first one on,
+// for good; so it is here.
+// One CTA per VFO, four warps: warp 0 walks chunk c while warps 1-3 turn chunk c + 1 into phases and increments
+// (atan2f: 18 cycles per sample when the walking warp does it itself) and write chunk c - 1's phases out.
+constexpr int kPeThreads = 128;
+__device__ __forceinline__ float pllWrap(float v) {
+    const float PI = 3.1415926535f;
+    return (v > PI) ? v - 2.0f * PI : ((v <= -PI) ? v + 2.0f * PI : v);
+}
+// the loop's own phase clamp (phase_control_loop.h clampPhase: limits -PI .. PI, both inclusive)
+__device__ __forceinline__ float pllClampPhase(float p) {
+    const float PI = 3.1415926535f;
+    return (p > PI) ? p - 2.0f * PI : ((p < -PI) ? p + 2.0f * PI : p);
+}
+struct PllErrWalk {
+    float c1, k, beta, lo, hi;             // 1 - alpha, 1 - alpha - beta
+    float e, f, eLast, fLo, fHi, rMax;     // e[m], frequency after the chunk, e[m-1]; extremes of the unclamped frequency and of |step|
+    template <bool LINEAR>
+    __device__ __forceinline__ void run(const float* __restrict__ DX, float* __restrict__ E, int m, float e0, float f0) {
+        e = e0; f = f0; eLast = e0; fLo = f0; fHi = f0; rMax = 0.0f;
+        auto step = [&](float dx) {
+            const float cur = e;
+            if (LINEAR) {
+                const float d = dx - f;                 // beside the chain: f is a step behind e
+                f = fmaf(beta, e, f);
+                fLo = fminf(fLo, f); fHi = fmaxf(fHi, f);
+                e = fmaf(k, e, d);
+                rMax = fmaxf(rMax, fabsf(e));
+            }
+            else {
+                const float g = fmaf(c1, e, dx);
+                float fn = fmaf(beta, e, f);
+                fLo = fminf(fLo, fn); fHi = fmaxf(fHi, fn);
+                fn = fminf(fmaxf(fn, lo), hi);
+                f = fn;
+                const float r = g - fn;
+                rMax = fmaxf(rMax, fabsf(r));
+                e = pllWrap(r);
+            }
+            return cur;
+        };
+        int i = 0;
+        // eight samples per trip: increments read ahead of the chain (two 16-byte reads), errors written behind it
+        float4 xa, xb;
+        if (m >= 8) { xa = *reinterpret_cast<const float4*>(&DX[0]); xb = *reinterpret_cast<const float4*>(&DX[4]); }
+#pragma unroll 1
+        for (; i + 8 <= m; i += 8) {
+            const float4 ca = xa, cb = xb;
+            if (i + 16 <= m) { xa = *reinterpret_cast<const float4*>(&DX[i + 8]); xb = *reinterpret_cast<const float4*>(&DX[i + 12]); }
+            float4 oa, ob;
+            oa.x = step(ca.x); oa.y = step(ca.y); oa.z = step(ca.z); oa.w = step(ca.w);
+            ob.x = step(cb.x); ob.y = step(cb.y); ob.z = step(cb.z); ob.w = step(cb.w);
+            eLast = ob.w;
+            *reinterpret_cast<float4*>(&E[i]) = oa;
+            *reinterpret_cast<float4*>(&E[i + 4]) = ob;
+        }
+        for (; i < m; i++) { eLast = step(DX[i]); E[i] = eLast; }
+    }
+};
+
+__global__ void __launch_bounds__(kPeThreads) pllErrKernel(const PllJob* __restrict__ jobs) {
+    const PllJob j = jobs[blockIdx.x];
+    __shared__ __align__(16) float sX[2][kPllChunk], sD[2][kPllChunk + 4], sE[2][kPllChunk];
+    __shared__ int sNanAt[2];        // first NaN pilot sample of the chunk in this buffer (helpers), INT_MAX if none
+    __shared__ int sFrom[2];         // what the helpers write for a walked chunk: phases up to this sample, NaN behind it; -1 all NaN; -2 nothing (already written)
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool walker = tid < 32;
+    const int ht = tid - 32, HT = kPeThreads - 32;
+    const float PI = 3.1415926535f;
+    const int nChunks = (j.n + kPllChunk - 1) / kPllChunk;
+    auto helperBarrier = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(kPeThreads - 32) : "memory"); };
+    // phases and increments of chunk c into buffer c & 1 (helpers)
+    auto prepare = [&](int c) {
+        const int base = c * kPllChunk, m = min(kPllChunk, j.n - base), b = c & 1;
+        for (int i = ht; i < m; i += HT) {
+            float x = atan2f(__ldg(j.pi + base + i), __ldg(j.pr + base + i));
+            if (!(x == x)) { atomicMin(&sNanAt[b], i); x = 0.0f; }
+            sX[b][i] = x;
+        }
+        helperBarrier();
+        for (int i = ht; i < ((m + 3) & ~3); i += HT) { sD[b][i] = (i + 1 < m) ? pllWrap(sX[b][i + 1] - sX[b][i]) : 0.0f; }
+    };
+    if (tid < 2) { sNanAt[tid] = 0x7fffffff; }
+    __syncthreads();
+    if (!walker && nChunks > 0) { prepare(0); }
+    __syncthreads();
+    float phase = 0.f, freq = 0.f;
+    bool dead = false, full = false;
+    PllErrWalk w;
+    if (walker) {
+        phase = j.st->pllPhase; freq = j.st->pllFreq;
+        dead = !(phase == phase && freq == freq);
+        w.c1 = 1.0f - j.alpha; w.k = 1.0f - j.alpha - j.beta; w.beta = j.beta; w.lo = j.minFreq; w.hi = j.maxFreq;
+        full = !(freq > j.minFreq && freq < j.maxFreq);
+    }
+    for (int c = 0; c <= nChunks; c++) {
+        const int b = c & 1;
+        if (walker) {
+            if (c < nChunks) {
+                const int base = c * kPllChunk, m = min(kPllChunk, j.n - base);
+                const int nanAt = sNanAt[b];
+                __syncwarp();
+                if (lane == 0) { sNanAt[b] = 0x7fffffff; }      // for the chunk after next, which the helpers prepare into this buffer
+                int from = dead ? -1 : min(nanAt, m);
+                if (!dead) {
+                    const float* X = sX[b];
+                    const float e0 = pllWrap(X[0] - phase);
+                    bool ok = false;
+                    if (!full) {
+                        w.run<true>(sD[b], sE[b], m, e0, freq);
+                        // no step left (-pi, pi) and the frequency stayed inside its limits: wrap and clamp would have done nothing
+                        ok = w.rMax < PI && fabsf(e0) < PI && w.fLo >= j.minFreq && w.fHi <= j.maxFreq && w.e == w.e && w.f == w.f;
+                    }
+                    if (!ok) {
+                        w.run<false>(sD[b], sE[b], m, e0, freq);
+                        ok = w.rMax < 3.0f * PI && w.e == w.e && w.f == w.f;
+                        // back to the linear walk once a chunk would have been valid for it
+                        full = !(w.rMax < PI && w.fLo > j.minFreq && w.fHi < j.maxFreq);
+                    }
+                    if (ok) {
+                        const float pLast = pllClampPhase(X[m - 1] - w.eLast);
+                        phase = pllClampPhase(pLast + (w.f + j.alpha * w.eLast));
+                        freq = w.f;
+                    }
+                    else {
+                        // the loop as the reference writes it (loop/pll.h:64-70, phase_control_loop.h:58-66), phases straight out
+                        const float TWO_PI = __fsub_rn(PI, -PI);
+                        for (int i = 0; i < m; i++) {
+                            if (lane == 0) { j.phaseOut[base + i] = (i > nanAt) ? __int_as_float(0x7fc00000) : phase; }
+                            float err = __fsub_rn(X[i], phase);
+                            if (err > PI) { err = __fsub_rn(err, 2.0f * PI); }
+                            else if (err <= -PI) { err = __fadd_rn(err, 2.0f * PI); }
+                            freq = __fadd_rn(freq, __fmul_rn(j.beta, err));
+                            freq = fminf(fmaxf(freq, j.minFreq), j.maxFreq);
+                            phase = __fadd_rn(phase, __fadd_rn(freq, __fmul_rn(j.alpha, err)));
+                            while (phase > PI) { phase = __fsub_rn(phase, TWO_PI); }
+                            while (phase < -PI) { phase = __fadd_rn(phase, TWO_PI); }
+                        }
+                        from = -2;
+                        full = true;
+                    }
+                    if (nanAt < m) { dead = true; }
+                }
+                if (lane == 0) { sFrom[b] = from; }
+            }
+        }
+        else {
+            if (c >= 1) {
+                // phases of chunk c - 1: phase[i] = x[i] - e[i], brought into the loop's phase limits
+                const int pb = b ^ 1, base = (c - 1) * kPllChunk, m = min(kPllChunk, j.n - base);
+                const int from = sFrom[pb];
+                if (from != -2) {
+                    for (int i = ht; i < m; i += HT) {
+                        const float p = pllClampPhase(sX[pb][i] - sE[pb][i]);
+                        j.phaseOut[base + i] = (from == -1 || i > from) ? __int_as_float(0x7fc00000) : p;
+                    }
+                }
+            }
+            helperBarrier();
+            if (c + 1 < nChunks) { prepare(c + 1); }
+            else { helperBarrier(); }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        j.st->pllPhase = dead ? __int_as_float(0x7fc00000) : phase;
+        j.st->pllFreq = dead ? __int_as_float(0x7fc00000) : freq;
+    }
 }
 
 // broadcast_fm.h:157-179: the MPX delayed by the pilot filter's group delay is mixed down by the squared conjugate VCO
@@ -1042,6 +1230,7 @@ static size_t soloSmem(size_t nJobs) {
     // (function attributes are per device: set on every use, as the FIR launches do)
     cudaFuncSetAttribute(agcWalkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
     cudaFuncSetAttribute(pllKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
+    cudaFuncSetAttribute(pllErrKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSoloSmemBytes);
     return kSoloSmemBytes;
 }
 
@@ -1276,7 +1465,9 @@ int processDemods(VfoBank& bank, cudaStream_t s) {
         B200_TRY(launchFirJobs((const FirJob*)(dd + oWA), wfmA.data(), (int)wfmA.size(), 1, s));
         B200_TRY(launchHistoryUpdate((const FirJob*)(dd + oWA), (int)wfmA.size(), maxH, s));
         if (!pllJobs.empty()) {
-            pllKernel<<<(unsigned)pllJobs.size(), 32, soloSmem(pllJobs.size()), s>>>((const PllJob*)(dd + oP));
+            // exact banks: the loop in the reference's operation order; default: its error form (see pllErrKernel)
+            if (bank.rotatorMode == B200_ROTATOR_EXACT) { pllKernel<<<(unsigned)pllJobs.size(), 32, soloSmem(pllJobs.size()), s>>>((const PllJob*)(dd + oP)); }
+            else { pllErrKernel<<<(unsigned)pllJobs.size(), kPeThreads, soloSmem(pllJobs.size()), s>>>((const PllJob*)(dd + oP)); }
             B200_CHECK_LAUNCH(); countLaunch();
         }
         wfmMixKernel<<<dim3((maxMix + 255) / 256, (unsigned)mixJobs.size()), 256, 0, s>>>((const WfmMixJob*)(dd + oM));

@@ -13,7 +13,18 @@ b = binding.VfoBank(sr, max_block=B)
 for i in range(V):
     v = b.add(500e3, 150e3, -1.5e6 + 200e3 * i)
     b.set_demod(v, binding.DEMOD_WFM, 1, 1, 0, 0)
-x = synth.make_iq_torch(B, sr, dev, tones=[(1e5, 0.2)])
+if "nopilot" in sys.argv[2:]:
+    x = synth.make_iq_torch(B, sr, dev, tones=[(1e5, 0.2)])          # nothing at 19 kHz: the loop sits at a frequency limit
+else:
+    # a broadcast-FM carrier with a 19 kHz pilot under every VFO: the loop locks
+    t = torch.arange(B, device=dev, dtype=torch.float64) / sr
+    mpx = 0.1 * torch.sin(2 * torch.pi * 19000.0 * t) + 0.4 * torch.sin(2 * torch.pi * 1000.0 * t)
+    ph = 2 * torch.pi * 75e3 * torch.cumsum(mpx, 0) / sr
+    z = torch.zeros(B, dtype=torch.complex128, device=dev)
+    for i in range(V):
+        z += (0.5 / V) * torch.exp(1j * (ph + 2 * torch.pi * (-1.5e6 + 200e3 * i) * t))
+    x = torch.view_as_real(z.to(torch.complex64)).contiguous()
+    del z, t, mpx, ph
 for _ in range(3):
     b.process(x, B)
 torch.cuda.synchronize()
@@ -31,4 +42,5 @@ for e in ev:
 n_out = B * 500e3 / sr
 for k, v in sorted(tot.items(), key=lambda kv: -kv[1])[:8]:
     print("%-42s %9.1f us" % (k, v))
-print("pll walk: %.1f cycles/sample at 1.965 GHz (%d samples per VFO)" % (tot.get("pllKernel", 0) * 1965.0 / n_out, n_out))
+pll = tot.get("pllKernel", 0) + tot.get("pllErrKernel", 0)     # exact banks / default banks
+print("pll walk: %.1f cycles/sample at 1.965 GHz (%d samples per VFO)" % (pll * 1965.0 / n_out, n_out))
