@@ -43,6 +43,7 @@ UNIT = "MS/s"
 WORKLOAD = "cfg4"
 DATA_WIDTH = 1333                    # waterfall pixels per row (a typical dataWidth)
 WF_MIN, WF_MAX = -120.0, -10.0
+E2E_DEFER_TAIL = True                # the host-fed path in streaming mode (B200_OPT_DEFER_TAIL)?  tools/bench_e2e.py measures both
 # first stage of each power-of-two plan: (decimation, taps) -- FMA lane operations per input sample and VFO in the
 # fused kernel = 4 (rotation) + 2 * taps / decimation
 STAGE1 = {16: (8, 54), 32: (8, 44), 64: (8, 36), 128: (16, 72), 256: (32, 143), 512: (32, 129), 1024: (64, 257),
@@ -570,14 +571,15 @@ def job_mine_count(vl, sr, world, rank):
     return sharding.shard_vfos(vl, sr, world)[rank]
 
 
-def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, steps, dist, dev):
+def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, steps, dist, dev, defer_tail=E2E_DEFER_TAIL, chunk_mib=0):
     """b200_frontend_process_host on this rank's shard: pinned host input, H2D, kernels, D2H of the dB rows and of every
     VFO's IF output.  With N ranks every rank feeds its own copy of the block over its own PCIe link (the host-fed path
     has no broadcast; SURVEY 8(e): "replicas per source")."""
     cfg = configs.CONFIGS[name]
     sr = cfg["sample_rate"]
-    j = Job(binding, torch, name, Be, local, rank, world, defer_tail=False)
+    j = Job(binding, torch, name, Be, local, rank, world, defer_tail=defer_tail)
     fe2 = j.fe
+    fe2.vfos.set_option(binding.OPT_HOST_CHUNK_MIB, chunk_mib)
     h_in = torch.empty((Be, 2), dtype=torch.float32).pin_memory()
     h_in.copy_(d_src[:Be].cpu())
     mf = Be // int(round(sr / cfg["fft_rate"])) + 2
@@ -591,9 +593,13 @@ def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, step
         optr[v] = h_iq.data_ptr() + pos * 8
         pos += n
     counts = np.zeros(nslots, np.int32)
+    # the caller's stream at the default priority, i.e. level with the library's stream for the later stages and the copies
+    # back: a chunk's results then cross PCIe beside the next chunk's full-rate kernels.  (On the timed loop's stream, which
+    # sits above it, they waited for the whole call's full-rate kernels: 687 against 963 MS/s.)
+    hs = torch.cuda.Stream(device=dev) if defer_tail else compute
 
     def step():
-        rc = binding.lib.b200_frontend_process_host(fe2.h, h_in.data_ptr(), Be, h_frames.data_ptr(), mf, optr, None, counts.ctypes.data, compute.cuda_stream)
+        rc = binding.lib.b200_frontend_process_host(fe2.h, h_in.data_ptr(), Be, h_frames.data_ptr(), mf, optr, None, counts.ctypes.data, hs.cuda_stream)
         if rc < 0:
             raise RuntimeError(binding.lib.b200_last_error().decode())
 
@@ -612,7 +618,9 @@ def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, step
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     te = float(tt.item())
     d2h = fe2.frame_count() * cfg["fft_size"] * 4 + int(counts.sum()) * 8
-    return {"value": Be * steps / te / 1e6, "unit": UNIT, "h2d_bytes_per_step": Be * 8, "d2h_bytes_per_step": int(d2h), "batch_samples": Be,
+    fe2.vfos.set_option(binding.OPT_HOST_CHUNK_MIB, 0)
+    fe2.vfos.set_option(binding.OPT_DEFER_TAIL, 0)
+    return {"value": Be * steps / te / 1e6, "unit": UNIT, "h2d_bytes_per_step": Be * 8, "d2h_bytes_per_step": int(d2h), "batch_samples": Be, "streaming_mode": bool(defer_tail),
             "path": "b200_frontend_process_host (pinned host buffers; H2D of the block, kernels, D2H of the dB rows and of every VFO's IF output, per call)"}
 
 

@@ -167,9 +167,13 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * launch then carries at most 1920 / D VFO pairs and a bank larger than that runs as several launches.  0 = the
  * shared-memory table path for every launch.  Same table values either way: results are identical. */
 #define B200_OPT_PARAM_TABLES 12
+/* B200_OPT_HOST_CHUNK_MIB (process-wide, default 0 = automatic): the *_process_host entry points cut a long block into chunks
+ * of this many MiB of host data, so that the copy of chunk k+1 runs beside the kernels of chunk k (automatic: 16 MiB, 64 MiB
+ * for a bank of 64 VFOs or more, whose per-chunk fixed costs weigh more).  Results do not depend on it. */
+#define B200_OPT_HOST_CHUNK_MIB 13
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 /* The process-wide switches above without a handle (B200_OPT_FUSED_STAGE1, _TILE_SAMPLES, _FFT_CTAS_PER_SM, _BRANCH_ORDER,
- * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM, _PARAM_TABLES).  b200_vfo_bank_set_option forwards these here: naming a
+ * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM, _PARAM_TABLES, _HOST_CHUNK_MIB).  b200_vfo_bank_set_option forwards these here: naming a
  * bank does NOT confine them to that bank -- every bank and front end of the process sees the change.  Only
  * B200_OPT_CALIBRATION_STEPS is per bank; B200_OPT_DEFER_TAIL is process-wide too but is switched through a bank handle,
  * because that bank's deferred work is drained first.  Calls are serialised by the library. */

@@ -58,10 +58,25 @@ struct DescBlob { uint4 q[248]; };     // 3968 bytes: with the two scalars the l
 __global__ void __launch_bounds__(256) putDescKernel(const __grid_constant__ DescBlob blob, uint4* __restrict__ dst, int n16) {
     if ((int)threadIdx.x < n16) { dst[threadIdx.x] = blob.q[threadIdx.x]; }
 }
+// descriptors too long for a few parameter blocks (a bank of a thousand VFOs): the SMs read the page-locked ring slot over PCIe
+__global__ void __launch_bounds__(256) pullDescKernel(const uint4* __restrict__ hostSrc, uint4* __restrict__ dst, int n16) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n16; i += gridDim.x * 256) { dst[i] = hostSrc[i]; }
+}
 } // namespace
 
 int uploadDesc(void* dDst, const void* hSrc, size_t bytes, cudaStream_t s, bool viaParams) {
     if (bytes == 0) { return B200_OK; }
+    if (viaParams && bytes > 16 * sizeof(DescBlob)) {
+        // not through the copy engine either (the point of viaParams: the upload must not queue behind the block copies)
+        void* alias = nullptr;
+        if (cudaHostGetDevicePointer(&alias, const_cast<void*>(hSrc), 0) == cudaSuccess && alias) {
+            const int n16 = (int)((bytes + 15) / 16);
+            pullDescKernel<<<std::min(64, (n16 + 255) / 256), 256, 0, s>>>((const uint4*)alias, (uint4*)dDst, n16);
+            B200_CHECK_LAUNCH();
+            return B200_OK;
+        }
+        cudaGetLastError();
+    }
     if (!viaParams || bytes > 16 * sizeof(DescBlob)) {
         B200_CUDA(cudaMemcpyAsync(dDst, hSrc, bytes, cudaMemcpyHostToDevice, s));
         return B200_OK;

@@ -9,6 +9,7 @@ namespace b200 {
 extern int fftCtasPerSm;
 extern int fftDirectMaxLog;
 extern int branchOrder;    // frontend.cu
+extern int hostChunkMiB;   // frontend.cu
 
 // One frame of the Reshaper (keep nz samples every I): the samples may straddle the carry buffer
 // and the current block, so a frame is [src0[0..len0) | src1[0..nz-len0)].

@@ -15,6 +15,7 @@
 namespace b200 {
 
 int branchOrder = 0;        // B200_OPT_BRANCH_ORDER
+int hostChunkMiB = 0;       // B200_OPT_HOST_CHUNK_MIB: chunk of the *_process_host entry points in MiB of host data; 0 = 16 (64 for a bank of 64 VFOs or more)
 
 namespace {
 
@@ -446,6 +447,8 @@ struct FrontEnd {
     cf32* dStageIn = nullptr;
     short2* dStageI16 = nullptr;                // int16 I/Q as it arrives from the host (process_host_i16)
     cudaStream_t hostCopyStream = nullptr;      // H2D of the next chunks while the current one is processed
+    cudaEvent_t evRowsReady = nullptr;          // a chunk's dB rows are complete in the caller's stream (host path in streaming mode)
+    bool rowsOnCopyStream = false;              // rows of this call went back on hostCopyStream: the call ends by draining it
     std::vector<cudaEvent_t> hostCopyDone;
     cudaEvent_t evHostStart = nullptr;
     void* dCopyJobs = nullptr; size_t copyJobBytes = 0;                  // scatterToHostKernel's job table
@@ -531,6 +534,7 @@ void FrontEnd::destroy() {
     for (auto e : hostCopyDone) { cudaEventDestroy(e); }
     hostCopyDone.clear();
     if (evHostStart) { cudaEventDestroy(evHostStart); evHostStart = nullptr; }
+    if (evRowsReady) { cudaEventDestroy(evRowsReady); evRowsReady = nullptr; }
     if (bank) { bank->impl.destroy(); delete bank; bank = nullptr; }
     if (detector) { detector->impl.destroy(); delete detector; detector = nullptr; }
     for (auto& st : decimStages) { st.destroy(); }
@@ -930,13 +934,31 @@ static float2* mappedAlias(const void* h) {
 static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& framesDone, float* const* h_vfo_out, float* const* h_audio,
                        std::vector<int>& done, std::vector<int>& audioDone, cudaStream_t s) {
     const int total = std::min((int)f.frameIdx.size(), max_frames);
-    if (h_frames && total > framesDone) {
-        B200_CUDA(cudaMemcpyAsync(h_frames + (size_t)framesDone * f.fftSize, f.dRows + (size_t)framesDone * f.fftSize,
-                                  (size_t)(total - framesDone) * f.fftSize * sizeof(float), cudaMemcpyDeviceToHost, s));
-    }
-    framesDone = std::max(framesDone, total);
     VfoBank& b = f.bank->impl;
-    B200_TRY(b.joinTail());
+    // the chunk's dB rows; `rowsFrom` = the stream they leave on
+    bool rowsPending = h_frames && total > framesDone;
+    auto copyRows = [&](cudaStream_t rowsFrom) -> int {
+        if (!rowsPending) { return B200_OK; }
+        rowsPending = false;
+        if (rowsFrom != s) {
+            // the rows were produced in the caller's stream
+            if (!f.evRowsReady) { B200_CUDA(cudaEventCreateWithFlags(&f.evRowsReady, cudaEventDisableTiming)); }
+            B200_CUDA(cudaEventRecord(f.evRowsReady, s));
+            B200_CUDA(cudaStreamWaitEvent(rowsFrom, f.evRowsReady, 0));
+        }
+        B200_CUDA(cudaMemcpyAsync(h_frames + (size_t)framesDone * f.fftSize, f.dRows + (size_t)framesDone * f.fftSize,
+                                  (size_t)(total - framesDone) * f.fftSize * sizeof(float), cudaMemcpyDeviceToHost, rowsFrom));
+        if (rowsFrom != s && rowsFrom != b.tailStream) { f.rowsOnCopyStream = true; }
+        return B200_OK;
+    };
+    // Streaming mode (B200_OPT_DEFER_TAIL) with the outputs of a large bank going back through the scatter kernel: the
+    // kernel goes on the bank's tail stream, right behind the later stages that produce what it copies and in front of the
+    // next chunk's (which overwrite it), so the caller's stream -- the next chunk's full-rate kernels -- never waits for a
+    // chunk's results to cross PCIe.  The tail event is recorded again behind the kernel: whoever joins the tail joins it.
+    // The rows go the same way, so that the caller's stream holds nothing but the chunks' kernels.
+    const bool onTail = b.tailUnjoined && b.tailStream && h_vfo_out && !h_audio && b.liveCount() >= 16;
+    cudaStream_t cs = onTail ? b.tailStream : s;
+    if (!onTail) { B200_TRY(copyRows(s)); B200_TRY(b.joinTail()); }
     // a large bank: gather the (device pointer, mapped host pointer, count) triples and let one kernel do the copies
     bool scattered = false;
     if (h_vfo_out && b.liveCount() >= 16) {
@@ -956,20 +978,27 @@ static int copyOutputs(FrontEnd& f, float* h_frames, int max_frames, int& frames
         if (allMapped && !jobs.empty()) {
             const size_t bytes = jobs.size() * sizeof(HostCopyJob);
             if (bytes > f.copyJobBytes) {
-                if (f.dCopyJobs) { B200_CUDA(cudaStreamSynchronize(s)); cudaFree(f.dCopyJobs); f.dCopyJobs = nullptr; }
+                if (f.dCopyJobs) { B200_CUDA(cudaStreamSynchronize(s)); B200_TRY(b.syncLast()); cudaFree(f.dCopyJobs); f.dCopyJobs = nullptr; }
                 f.copyJobBytes = std::max(bytes * 2, (size_t)64 * 1024);
                 B200_CUDA(cudaMalloc(&f.dCopyJobs, f.copyJobBytes + 16));
             }
             void* hp = nullptr; int slot = 0;
             B200_TRY(f.ring.acquire(bytes, &hp, &slot));
             memcpy(hp, jobs.data(), bytes);
-            B200_TRY(uploadDesc(f.dCopyJobs, hp, bytes, s, b.descViaParams));
-            B200_TRY(f.ring.release(slot, s));
-            scatterToHostKernel<<<(int)jobs.size(), 256, 0, s>>>((const HostCopyJob*)f.dCopyJobs);
+            // (in streaming mode the rows leave on the stream that brought the block in: its copies are long done, and the
+            // rows then cross beside the scatter kernel's stores instead of in front of them)
+            B200_TRY(copyRows(onTail && f.hostCopyStream ? f.hostCopyStream : cs));
+            B200_TRY(uploadDesc(f.dCopyJobs, hp, bytes, cs, onTail ? true : b.descViaParams));
+            B200_TRY(f.ring.release(slot, cs));
+            scatterToHostKernel<<<(int)jobs.size(), 256, 0, cs>>>((const HostCopyJob*)f.dCopyJobs);
             B200_CHECK_LAUNCH(); countLaunch();
+            if (onTail) { B200_CUDA(cudaEventRecord(b.evTail[b.lastTailPar], cs)); }
             scattered = true;
         }
     }
+    if (onTail && !scattered) { B200_TRY(b.joinTail()); }      // (pageable destinations: plain copies on the caller's stream)
+    B200_TRY(copyRows(s));
+    framesDone = std::max(framesDone, total);
     for (size_t i = 0; i < b.vfos.size(); i++) {
         const Vfo& v = b.vfos[i];
         if (!v.live) { continue; }
@@ -1029,9 +1058,11 @@ static int processHostImpl(b200_frontend* fe, const void* h_in, int sampleBytes,
     // 16 MiB of host data per chunk (2^21 cf32 or 2^22 int16 samples) when the block's kernels are short beside its copy;
     // a heavy bank (its kernels take several times the copy) runs 64 MiB chunks, so that the per-call fixed costs of
     // its later stages are paid four times less often
-    const int kChunk = ((f.bank->impl.liveCount() >= 64 ? 64 : 16) << 20) / sampleBytes;
+    const int kChunk = ((hostChunkMiB > 0 ? hostChunkMiB : (f.bank->impl.liveCount() >= 64 ? 64 : 16)) << 20) / sampleBytes;
     const bool plain = f.decimRatio == 1 && !f.dcBlocking && !f.invertIQ;
     if (plain && count >= 2 * kChunk) {
+        // (chunks are multiples of 512 samples: an exact-mode rotator renormalises every 512 samples of a call, as the reference's
+        // does, so only such cuts leave its phases what one call over the whole block gives)
         const int nChunks = (count + kChunk - 1) / kChunk;
         if (!f.hostCopyStream) {
             B200_CUDA(cudaStreamCreateWithFlags(&f.hostCopyStream, cudaStreamNonBlocking));
@@ -1072,6 +1103,8 @@ static int processHostImpl(b200_frontend* fe, const void* h_in, int sampleBytes,
         B200_TRY(copyOutputs(f, h_frames, max_frames, framesDone, h_vfo_out, h_audio, done, audioDone, s));
     }
     if (vfo_counts) { for (size_t i = 0; i < b.vfos.size(); i++) { if (b.vfos[i].live) { vfo_counts[i] = done[i]; } } }
+    B200_TRY(b.joinTail());        // streaming mode: the last chunk's later stages and its copies back
+    if (f.rowsOnCopyStream) { f.rowsOnCopyStream = false; B200_CUDA(cudaStreamSynchronize(f.hostCopyStream)); }
     B200_CUDA(cudaStreamSynchronize(s));
     return B200_OK;
 }

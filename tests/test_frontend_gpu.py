@@ -550,6 +550,62 @@ def test_process_host_returns_a_large_bank_in_one_scatter(pinned):
     assert keep is not None
 
 
+@pytest.mark.parametrize("streaming", [False, True])
+def test_process_host_chunked_large_bank_inline_and_streaming(streaming):
+    """A long host block through a bank of 24 VFOs, cut into chunks (B200_OPT_HOST_CHUNK_MIB), inline and in streaming mode
+    (B200_OPT_DEFER_TAIL: every chunk's later stages AND its copies back to the callers' page-locked buffers run on the
+    bank's own stream beside the next chunk's full-rate kernels).  Counts, frames and every VFO's output must equal the same
+    blocks processed device-resident in one call each; the second call continues every stream."""
+    import ctypes
+    import torch
+    from sdrplusplusbrown_b200 import binding
+    sr, N, rate = 2.4e6, 8192, 20.0
+    nv, n = 24, 700000                               # 1 MiB chunks = 131072 samples: five chunks and a bit
+    offs = [(-1.0e6 + 80e3 * k + 7.0) for k in range(nv)]
+    x = synth.make_iq(5, 2 * n, sr, sigma=0.05, tones=[(o + 900.0, 0.02) for o in offs])
+    a = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+    b = _fe(sr, fft_size=N, fft_rate=rate, fft_window=2, max_block=n)
+    for fe in (a, b):
+        fe.vfos.set_rotator_mode(binding.ROTATOR_EXACT)
+    va = [a.vfos.add(50e3 if k % 3 else 24e3, 12.5e3 if k % 3 else 2.8e3, o) for k, o in enumerate(offs)]
+    vb = [b.vfos.add(50e3 if k % 3 else 24e3, 12.5e3 if k % 3 else 2.8e3, o) for k, o in enumerate(offs)]
+    sizes = [b.vfos.max_out(v, n) for v in vb]
+    store = torch.zeros((sum(sizes), 2), dtype=torch.float32).pin_memory()
+    view = store.numpy().view(np.complex64).reshape(-1)
+    optr = (ctypes.c_void_p * (max(vb) + 1))()
+    starts, pos = [], 0
+    for v, m in zip(vb, sizes):
+        optr[v] = store.data_ptr() + 8 * pos
+        starts.append(pos)
+        pos += m
+    counts = np.zeros(max(vb) + 1, np.int32)
+    mf = 64
+    h_frames = torch.zeros((mf, N), dtype=torch.float32).pin_memory()
+    try:
+        b.vfos.set_option(binding.OPT_HOST_CHUNK_MIB, 1)
+        b.vfos.set_option(binding.OPT_DEFER_TAIL, int(streaming))
+        for blk in (x[:n], x[n:]):
+            b.vfos.set_option(binding.OPT_DEFER_TAIL, 0)
+            a.process(to_dev(blk))
+            ref_frames = np.stack(a.frames())
+            wants = [a.vfos.output(v) for v in va]
+            b.vfos.set_option(binding.OPT_DEFER_TAIL, int(streaming))
+            xin = torch.from_numpy(np.ascontiguousarray(blk).view(np.float32).reshape(-1, 2)).pin_memory()
+            view[:] = 0
+            rc = binding.lib.b200_frontend_process_host(b.h, xin.data_ptr(), len(blk), h_frames.data_ptr(), mf, optr, None, counts.ctypes.data, None)
+            assert rc == 0, binding.lib.b200_last_error()
+            assert b.frame_count() == len(ref_frames)
+            got_frames = h_frames.numpy()[:len(ref_frames)]
+            m = ref_frames > ref_frames.max(axis=1, keepdims=True) - 80.0
+            assert np.max(np.abs(got_frames[m] - ref_frames[m])) <= 0.01
+            for v_b, st, want in zip(vb, starts, wants):
+                assert counts[v_b] == len(want) > 0
+                assert err_db(view[st:st + len(want)], want) <= -100.0, (v_b, err_db(view[st:st + len(want)], want))
+    finally:
+        b.vfos.set_option(binding.OPT_DEFER_TAIL, 0)
+        b.vfos.set_option(binding.OPT_HOST_CHUNK_MIB, 0)
+
+
 @pytest.mark.parametrize("tuned_to_signal", [False, True])
 def test_reference_snr_threshold_scenario_on_a_synthetic_cw_capture(tuned_to_signal):
     """The reference's only numeric test, re-created (tests/baseband_file_test.cpp:36-88): a baseband capture with CW

@@ -10,6 +10,8 @@ from sdrplusplusbrown_b200 import binding, synth
 sr, B, V = 4e6, 1 << 22, int(sys.argv[1]) if len(sys.argv) > 1 else 16
 dev = torch.device("cuda", 0)
 b = binding.VfoBank(sr, max_block=B)
+if "exact" in sys.argv[2:]:
+    b.set_rotator_mode(binding.ROTATOR_EXACT)       # the loop in the reference's operation order (pllKernel)
 for i in range(V):
     v = b.add(500e3, 150e3, -1.5e6 + 200e3 * i)
     b.set_demod(v, binding.DEMOD_WFM, 1, 1, 0, 0)
