@@ -171,9 +171,14 @@ int b200_vfo_bank_set_rotator_mode(b200_vfo_bank* bank, int mode);
  * of this many MiB of host data, so that the copy of chunk k+1 runs beside the kernels of chunk k (automatic: 16 MiB, 64 MiB
  * for a bank of 64 VFOs or more, whose per-chunk fixed costs weigh more).  Results do not depend on it. */
 #define B200_OPT_HOST_CHUNK_MIB 13
+/* B200_OPT_FFT_DIRECT_PREFETCH (process-wide, default 0): 1 = the one-pass FFT kernel (sizes up to
+ * 2^B200_OPT_FFT_DIRECT_MAX_LOG) stages the samples of its next frame in shared memory with asynchronous copies while it
+ * transforms the current one; 0 = every frame starts by loading its samples from global memory.  Measured 6-13 % slower
+ * at 2048 ... 8192 points (the kernel is short of issue slots, not waiting for loads): off.  Same arithmetic either way. */
+#define B200_OPT_FFT_DIRECT_PREFETCH 14
 int b200_vfo_bank_set_option(b200_vfo_bank* bank, int option, int value);
 /* The process-wide switches above without a handle (B200_OPT_FUSED_STAGE1, _TILE_SAMPLES, _FFT_CTAS_PER_SM, _BRANCH_ORDER,
- * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM, _PARAM_TABLES, _HOST_CHUNK_MIB).  b200_vfo_bank_set_option forwards these here: naming a
+ * _VFOS_PER_PASS, _VFOS_PER_CTA, _FFT_DIRECT_MAX_LOG, _SPLIT_RUNS, _LEAVE_ROOM, _PARAM_TABLES, _HOST_CHUNK_MIB, _FFT_DIRECT_PREFETCH).  b200_vfo_bank_set_option forwards these here: naming a
  * bank does NOT confine them to that bank -- every bank and front end of the process sees the change.  Only
  * B200_OPT_CALIBRATION_STEPS is per bank; B200_OPT_DEFER_TAIL is process-wide too but is switched through a bank handle,
  * because that bank's deferred work is drained first.  Calls are serialised by the library. */

@@ -180,7 +180,7 @@ for _name, (_res, _args) in _SIGS.items():
 
 
 ROTATOR_FAST, ROTATOR_EXACT = 0, 1
-OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS, OPT_TILE_SAMPLES, OPT_FFT_CTAS_PER_SM, OPT_BRANCH_ORDER, OPT_DEFER_TAIL, OPT_VFOS_PER_PASS, OPT_VFOS_PER_CTA, OPT_FFT_DIRECT_MAX_LOG, OPT_SPLIT_RUNS, OPT_LEAVE_ROOM, OPT_PARAM_TABLES, OPT_HOST_CHUNK_MIB = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13
+OPT_FUSED_STAGE1, OPT_CALIBRATION_STEPS, OPT_TILE_SAMPLES, OPT_FFT_CTAS_PER_SM, OPT_BRANCH_ORDER, OPT_DEFER_TAIL, OPT_VFOS_PER_PASS, OPT_VFOS_PER_CTA, OPT_FFT_DIRECT_MAX_LOG, OPT_SPLIT_RUNS, OPT_LEAVE_ROOM, OPT_PARAM_TABLES, OPT_HOST_CHUNK_MIB, OPT_FFT_DIRECT_PREFETCH = 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14
 DEMOD_NONE, DEMOD_NFM, DEMOD_AM, DEMOD_USB, DEMOD_LSB, DEMOD_DSB, DEMOD_WFM = 0, 1, 2, 3, 4, 5, 6
 
 

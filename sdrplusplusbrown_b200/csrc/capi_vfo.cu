@@ -159,6 +159,7 @@ int b200_set_global_option(int option, int value) {
         if (value != 0 && value != 1) { setError("branch order must be 0 or 1"); return B200_EINVAL; }
         branchOrder = value;
         return B200_OK;
+    case B200_OPT_FFT_DIRECT_PREFETCH: fftDirectPrefetch = value != 0; return B200_OK;
     case B200_OPT_HOST_CHUNK_MIB:
         if (value < 0 || value > 1024) { setError("host chunk must be 0 (automatic) .. 1024 MiB"); return B200_EINVAL; }
         hostChunkMiB = value;

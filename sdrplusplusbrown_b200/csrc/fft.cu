@@ -18,6 +18,7 @@
 namespace b200 {
 
 int fftDirectMaxLog = 13;    // largest log2(N) served by the one-pass kernel (B200_OPT_FFT_DIRECT_MAX_LOG; 9 = never)
+int fftDirectPrefetch = 0;   // B200_OPT_FFT_DIRECT_PREFETCH: the one-pass kernel stages its next frame in shared memory while it transforms this one (measured slower: off)
 int fftCtasPerSm = 0;       // B200_OPT_FFT_CTAS_PER_SM: persistent CTAs per SM of the two register-resident passes; 0 = as many as fit
 
 namespace {
@@ -578,7 +579,8 @@ template <int R0, int R1, int R2> struct DirectCfg {
 
 template <int R, int PT, int T, int N, int NS, bool FROM_FRAME, bool TO_GLOBAL>
 __device__ __forceinline__ void directStage(float2* __restrict__ buf, const FrameDesc& f, const float* __restrict__ wv, int nz,
-                                            const float2 (*twr)[R], float* __restrict__ outDb, float2* __restrict__ outSpec, float invN) {
+                                            const float2 (*twr)[R], float* __restrict__ outDb, float2* __restrict__ outSpec, float invN,
+                                            const float2* __restrict__ pre = nullptr) {
     constexpr int NB = PT / R;               // butterflies per thread
     constexpr int PER = N / R;               // butterflies per frame = input stride
     float2 v[NB][R];
@@ -590,7 +592,8 @@ __device__ __forceinline__ void directStage(float2* __restrict__ buf, const Fram
             if constexpr (FROM_FRAME) {
                 const int i = j + r * PER;
                 float2 x = make_float2(0.f, 0.f);
-                if (i < nz) { x = __ldg(frameAddr(f, i)); }
+                if (pre) { x = pre[(m * R + r) * T + threadIdx.x]; }       // staged ahead by this very thread (zero filled past nz)
+                else if (i < nz) { x = __ldg(frameAddr(f, i)); }
                 v[m][r] = make_float2(x.x * wv[m * R + r], x.y * wv[m * R + r]);
             }
             else { v[m][r] = buf[slot(j + r * PER)]; }
@@ -621,7 +624,13 @@ __device__ __forceinline__ void directStage(float2* __restrict__ buf, const Fram
 
 // Persistent CTAs: a thread's butterflies sit at the same places in every frame, so its window samples and the
 // twiddles of its second- and third-stage butterflies are loaded once and stay in registers for the CTA's lifetime.
-template <int R0, int R1, int R2>
+// PRE (B200_OPT_FFT_DIRECT_PREFETCH, off): every thread brings its own PT samples of the CTA's NEXT frame into shared memory
+// with cp.async while the current frame's second and third stage run (only the copying thread reads them back: no barrier,
+// just its own wait_group), so that a frame's transform does not start with a round trip to HBM that only the other
+// resident CTA can hide.  Measured (13 Mi points per batch, us without / with): 2048: 77.8 / 88.4, 4096: 73.0 / 77.4,
+// 8192: 88.8 / 99.7 -- slower at every size: the kernel does not wait for those loads, it is short of issue slots and
+// shared-memory bandwidth, and the staged copy adds to both (profiles/r02_fft_direct_prefetch.txt).
+template <int R0, int R1, int R2, bool PRE>
 __global__ void __launch_bounds__(DirectCfg<R0, R1, R2>::T * DirectCfg<R0, R1, R2>::F, DirectCfg<R0, R1, R2>::MINB)
 fftDirectKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* __restrict__ win, int nz, const float2* __restrict__ tw,
                 float* __restrict__ outDb, cf32* __restrict__ outSpec) {
@@ -652,35 +661,58 @@ fftDirectKernel(const FrameDesc* __restrict__ frames, int nFrames, const float* 
         for (int r = 0; r < R2; r++) { tw2[m][r] = __ldg(tw + k * r); }                     // W_N^(k r)
     }
     float2* buf = sm + threadIdx.y * (slot(N) + 1);
+    float2* pre = PRE ? sm + DC::F * (slot(N) + 1) + threadIdx.y * N : nullptr;     // sample (m, r) of thread t at (m * R0 + r) * T + t
+    auto stageAhead = [&](int frame) {
+        if (frame < nFrames) {
+            const FrameDesc f = frames[frame];
+#pragma unroll
+            for (int k = 0; k < PT; k++) {
+                const int i = threadIdx.x + (k / R0) * T + (k % R0) * (N / R0);
+                const bool ok = i < nz;
+                cpAsync8(pre + k * T + threadIdx.x, frameAddr(f, ok ? i : 0), ok);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    if (PRE) { stageAhead(blockIdx.x * DC::F + threadIdx.y); }
     for (int base = blockIdx.x * DC::F; base < nFrames; base += gridDim.x * DC::F) {
         const int frame = base + threadIdx.y;
         const bool live = frame < nFrames;                // a CTA's last group may be short: idle slots still meet the barriers
         const FrameDesc f = frames[live ? frame : base];
         float* oDb = (outDb && live) ? outDb + (size_t)frame * N : nullptr;
         float2* oSp = (outSpec && live) ? reinterpret_cast<float2*>(outSpec) + (size_t)frame * N : nullptr;
-        directStage<R0, PT, T, N, 1, true, false>(buf, f, wv, nz, nullptr, nullptr, nullptr, invN);
+        if (PRE) { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
+        directStage<R0, PT, T, N, 1, true, false>(buf, f, wv, nz, nullptr, nullptr, nullptr, invN, pre);
+        // (behind the first stage's closing barrier: the values read from `pre` have long been consumed)
+        if (PRE) { stageAhead(frame + gridDim.x * DC::F); }
         directStage<R1, PT, T, N, R0, false, false>(buf, f, nullptr, nz, tw1, nullptr, nullptr, invN);
         directStage<R2, PT, T, N, R0 * R1, false, true>(buf, f, nullptr, nz, tw2, oDb, oSp, invN);
         __syncthreads();       // the next frame's first stage writes the buffer this frame's last stage has just read
     }
 }
 
-template <int R0, int R1, int R2>
-int launchDirect(int nFrames, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, const float2* tw, float* outDb, cf32* outSpec) {
+template <int R0, int R1, int R2, bool PRE>
+int launchDirectAs(int nFrames, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, const float2* tw, float* outDb, cf32* outSpec) {
     using DC = DirectCfg<R0, R1, R2>;
-    const size_t smem = (size_t)DC::F * (slot(DC::N) + 1) * sizeof(float2);
+    const size_t smem = (size_t)DC::F * ((slot(DC::N) + 1) + (PRE ? DC::N : 0)) * sizeof(float2);
     static int perSm = 0;
+    // (function attributes are per device: set on every use)
+    B200_CUDA(cudaFuncSetAttribute(fftDirectKernel<R0, R1, R2, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (perSm == 0) {
-        B200_CUDA(cudaFuncSetAttribute(fftDirectKernel<R0, R1, R2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fftDirectKernel<R0, R1, R2>, DC::T * DC::F, smem));
+        B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, fftDirectKernel<R0, R1, R2, PRE>, DC::T * DC::F, smem));
         if (perSm < 1) { perSm = 1; }
     }
     const int groups = (nFrames + DC::F - 1) / DC::F;
     const int grid = std::min(groups, 148 * perSm);
-    fftDirectKernel<R0, R1, R2><<<grid, dim3(DC::T, DC::F), smem, s>>>(frames, nFrames, win, nz, tw, outDb, outSpec);
+    fftDirectKernel<R0, R1, R2, PRE><<<grid, dim3(DC::T, DC::F), smem, s>>>(frames, nFrames, win, nz, tw, outDb, outSpec);
     B200_CHECK_LAUNCH();
     countLaunch();
     return B200_OK;
+}
+template <int R0, int R1, int R2>
+int launchDirect(int nFrames, cudaStream_t s, const FrameDesc* frames, const float* win, int nz, const float2* tw, float* outDb, cf32* outSpec) {
+    return fftDirectPrefetch ? launchDirectAs<R0, R1, R2, true>(nFrames, s, frames, win, nz, tw, outDb, outSpec)
+                             : launchDirectAs<R0, R1, R2, false>(nFrames, s, frames, win, nz, tw, outDb, outSpec);
 }
 
 int uploadTwiddles(float2** d, int count, int N, int stride) {

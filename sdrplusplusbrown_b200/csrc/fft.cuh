@@ -8,6 +8,7 @@ namespace b200 {
 
 extern int fftCtasPerSm;
 extern int fftDirectMaxLog;
+extern int fftDirectPrefetch;
 extern int branchOrder;    // frontend.cu
 extern int hostChunkMiB;   // frontend.cu
 
