@@ -581,7 +581,10 @@ def host_path(binding, torch, name, Be, local, rank, world, d_src, compute, step
     fe2 = j.fe
     fe2.vfos.set_option(binding.OPT_HOST_CHUNK_MIB, chunk_mib)
     h_in = torch.empty((Be, 2), dtype=torch.float32).pin_memory()
-    h_in.copy_(d_src[:Be].cpu())
+    n_src = int(d_src.shape[0])
+    for pos in range(0, Be, n_src):                      # a host block longer than the resident batch repeats it
+        n = min(n_src, Be - pos)
+        h_in[pos:pos + n].copy_(d_src[:n].cpu())
     mf = Be // int(round(sr / cfg["fft_rate"])) + 2
     h_frames = torch.empty((mf, cfg["fft_size"]), dtype=torch.float32).pin_memory()
     nslots = max(j.ids) + 1 if j.ids else 1
@@ -713,7 +716,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=1 << 24, help="samples per step, device resident (default 16 Mi = 134 MB > L2)")
-    ap.add_argument("--e2e-batch", type=int, default=1 << 24)
+    ap.add_argument("--e2e-batch", type=int, default=1 << 25)
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-samples", type=int, default=1000000, help="samples per CPU-arm step (bounded sample of the workload: one reference stream block)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)

@@ -47,6 +47,40 @@ struct Walk {
     }
 };
 
+// the loop in lock: no step leaves (-pi, pi) and the frequency stays inside its limits, so neither the wrap nor the clamp acts;
+// with d[i] = dx[i] - f[i-1] formed beside the chain (f runs a step behind e) the chain is one FFMA per sample
+struct WalkLinear {
+    float k, beta;
+    float e, f, eLast, fLo, fHi, rMax;
+    __device__ __forceinline__ void run(const float* __restrict__ DX, float* __restrict__ E, int m, float e0, float f0) {
+        e = e0; f = f0; eLast = e0; fLo = f0; fHi = f0; rMax = 0.0f;
+        auto step = [&](float dx) {
+            const float cur = e;
+            const float d = dx - f;
+            f = fmaf(beta, e, f);
+            fLo = fminf(fLo, f); fHi = fmaxf(fHi, f);
+            e = fmaf(k, e, d);
+            rMax = fmaxf(rMax, fabsf(e));
+            return cur;
+        };
+        int i = 0;
+        float4 xa, xb;
+        if (m >= 8) { xa = *reinterpret_cast<const float4*>(&DX[0]); xb = *reinterpret_cast<const float4*>(&DX[4]); }
+#pragma unroll 1
+        for (; i + 8 <= m; i += 8) {
+            const float4 ca = xa, cb = xb;
+            if (i + 16 <= m) { xa = *reinterpret_cast<const float4*>(&DX[i + 8]); xb = *reinterpret_cast<const float4*>(&DX[i + 12]); }
+            float4 oa, ob;
+            oa.x = step(ca.x); oa.y = step(ca.y); oa.z = step(ca.z); oa.w = step(ca.w);
+            ob.x = step(cb.x); ob.y = step(cb.y); ob.z = step(cb.z); ob.w = step(cb.w);
+            eLast = ob.w;
+            *reinterpret_cast<float4*>(&E[i]) = oa;
+            *reinterpret_cast<float4*>(&E[i + 4]) = ob;
+        }
+        for (; i < m; i++) { eLast = step(DX[i]); E[i] = eLast; }
+    }
+};
+
 // the same loop on 32-bit phases (2^32 per turn: wrapping is the integer overflow), gains as 0.32 fixed point
 struct WalkFixed {
     int A, Aa, B, lo, hi;          // (alpha + beta), alpha, beta as fractions of 2^32; frequency limits
@@ -137,16 +171,19 @@ __global__ void __launch_bounds__(32) probe(const float* __restrict__ pr, const 
         for (int i = lane; i < ((m + 3) & ~3); i += 32) { sDx[i] = (i + 1 < m) ? wrapPi(sIn[i + 1] - sIn[i]) : 0.0f; }
         __syncwarp();
         b = clock64(); t[1] += b - a; a = b;
+        WalkLinear wl; wl.k = 1.0f - alpha - beta; wl.beta = beta;
+        wl.run(sDx, sOut, m, wrapPi(sIn[0] - phase), freq);
+        const float keep3 = wl.e + wl.fLo + wl.fHi + wl.rMax;
+        b = clock64(); t[4] += b - a; a = b;
         w.run<false, true>(sDx, sOut, m, wrapPi(sIn[0] - phase), freq);
         const float keep = w.e + w.fLo + w.fHi + w.rMax;
         b = clock64(); t[2] += b - a; a = b;
         w.run<true, true>(sDx, sOut, m, wrapPi(sIn[0] - phase), freq);
         const float keep2 = w.e + w.fLo + w.fHi + w.rMax;
         b = clock64(); t[3] += b - a; a = b;
-        w.run<false, false>(sDx, sOut, m, wrapPi(sIn[0] - phase), freq);
-        b = clock64(); t[4] += b - a; a = b;
+
         __syncwarp();
-        for (int k = lane; k < m; k += 32) { out[base + k] = wrapPi(sIn[k] - sOut[k]) + 1e-30f * (keep + keep2); }
+        for (int k = lane; k < m; k += 32) { out[base + k] = wrapPi(sIn[k] - sOut[k]) + 1e-30f * (keep + keep2 + keep3); }
         const float p0 = wrapPi(sIn[m - 1] - w.eLast) + (w.f + alpha * w.eLast);
         phase = wrapPi(p0); freq = w.f;
         __syncwarp();
@@ -169,15 +206,15 @@ int main() {
     for (int rep = 0; rep < 2; rep++) { probe<<<1, 32>>>(dr, di, dout, n, dc, alpha, beta, lo, hi); cudaDeviceSynchronize(); }
     long long c[6];
     cudaMemcpy(c, dc, 48, cudaMemcpyDeviceToHost);
-    const char* names[] = { "atan2f from global -> smem", "phase increments", "error-form walk, clamp watched", "error-form walk, clamp in chain",
-                            "error-form walk, nothing watched", "phases out + state" };
+    const char* names[] = { "atan2f from global -> smem", "phase increments", "error-form walk, wrap in chain", "error-form walk, wrap + clamp in chain",
+                            "error-form walk in lock (one FFMA)", "phases out + state" };
     for (int k = 0; k < 6; k++) { printf("%-36s %7.2f cycles/sample\n", names[k], (double)c[k] / n); }
     std::vector<float> a(n), bb(n);
     cudaMemcpy(a.data(), dout, n * 4, cudaMemcpyDeviceToHost);
     for (int rep = 0; rep < 2; rep++) { probeFixed<<<1, 32>>>(dr, di, dout, n, dc, alpha, beta, lo, hi); cudaDeviceSynchronize(); }
     cudaMemcpy(c, dc, 32, cudaMemcpyDeviceToHost);
     cudaMemcpy(bb.data(), dout, n * 4, cudaMemcpyDeviceToHost);
-    const char* namesF[] = { "fixed point: phases + increments", "fixed-point walk, clamp in chain", "fixed-point walk, clamp watched", "phases out + state" };
+    const char* namesF[] = { "fixed point: phases + increments", "fixed-point walk, clamp in chain", "fixed-point walk, clamp beside chain", "phases out + state" };
     for (int k = 0; k < 4; k++) { printf("%-36s %7.2f cycles/sample\n", namesF[k], (double)c[k] / n); }
     double worst = 0; int at = -1;
     for (int i = 0; i < n; i++) { double d = fabs((double)a[i] - (double)bb[i]); if (d > 3.0) { d = fabs(d - 2 * M_PI); } if (d > worst) { worst = d; at = i; } }
