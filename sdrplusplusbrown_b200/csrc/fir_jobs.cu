@@ -106,6 +106,20 @@ __device__ __forceinline__ void stageWindow(const FirJob& j, typename Elem<EF>::
     using T = typename Elem<EF>::T;
     if (base >= j.H && base - j.H + span <= j.nIn) {
         const T* src = reinterpret_cast<const T*>(j.data) + (base - j.H);
+        if constexpr (EF == 2) {
+            // complex samples: asynchronous 8-byte copies, the whole window in flight at once.  The CTAs of a large bank's
+            // later stages are many and short (cfg4's first wave: 262144 CTAs of one 34 KB window each); with the window
+            // staged through registers, eight loads per thread at a time, an SM had about 24 KB in flight and the wave read
+            // its 2.4 GB at 3.5 TB/s (ncu: warps 34 % active, issue slots 23 %, FMA pipe 15 % busy).  (16-byte loads
+            // through registers changed nothing: the width of the loads was not the limit.)
+            for (int i = threadIdx.x; i < span; i += kThreads) {
+                const unsigned d = (unsigned)__cvta_generic_to_shared(win + i + (i >> padShift));
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(d), "l"(src + i) : "memory");
+            }
+            asm volatile("cp.async.commit_group;\n" ::: "memory");
+            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+            return;
+        }
         int i = threadIdx.x;
         for (; i + 7 * kThreads < span; i += 8 * kThreads) {
             T v[8];
@@ -572,7 +586,40 @@ void firJobsBalance(FirJob* jobs, int nJobs) {
     // launch and a four-row bank, 297 us against 229 us)
 }
 
+int firJobTiles(const FirJob& j) {
+    if (j.nOut <= 0) { return 0; }
+    const int opc = outPerCta(j);
+    return (j.nOut + opc - 1) / opc;
+}
+
+void firJobsSortByTiles(FirJob* jobs, int nJobs) {
+    std::stable_sort(jobs, jobs + nJobs, [](const FirJob& a, const FirJob& b) { return firJobTiles(a) > firJobTiles(b); });
+}
+
+static int launchFirJobRange(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s);
+
+// grid = (tiles of the longest job, jobs): a CTA whose tile lies beyond its job's end still has to be launched and to fetch
+// its descriptor before it can leave.  In a mixed bank that is most of them -- cfg4's first later-stage wave: 128 WFM jobs of
+// 256 tiles beside 384 jobs of 64 and 512 of 32, 72 % of 262144 CTAs empty -- so a list that comes sorted by tile count
+// (firJobsSortByTiles) is launched run by run, a run ending where the tile count falls below half of its first job's.
 int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s) {
+    if (nJobs <= 0) { return B200_OK; }
+    bool sorted = true;
+    for (int i = 1; i < nJobs && sorted; i++) { sorted = firJobTiles(h_jobs[i]) <= firJobTiles(h_jobs[i - 1]); }
+    if (!sorted) { return launchFirJobRange(d_jobs, h_jobs, nJobs, elemFloats, s); }
+    for (int i = 0; i < nJobs;) {
+        const int t0 = firJobTiles(h_jobs[i]);
+        if (t0 == 0) { break; }                           // only empty jobs are left
+        int e = i + 1;
+        while (e < nJobs && 2 * firJobTiles(h_jobs[e]) > t0) { e++; }
+        if (nJobs - e < 8) { e = nJobs; }                  // not worth a launch of its own
+        B200_TRY(launchFirJobRange(d_jobs + i, h_jobs + i, e - i, elemFloats, s));
+        i = e;
+    }
+    return B200_OK;
+}
+
+static int launchFirJobRange(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s) {
     if (nJobs <= 0) { return B200_OK; }
     int tiles = 0;
     size_t elems = 0;

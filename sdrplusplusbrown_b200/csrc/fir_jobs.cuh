@@ -40,6 +40,10 @@ void firJobPlan(FirJob& j);
 // whole launch would have too few CTAs to fill the GPU (a single VFO: 512 fat CTAs measured slower than 2048 thin ones).
 void firJobsBalance(FirJob* jobs, int nJobs);
 
+// CTAs job j occupies along grid.x; sorting a launch's jobs by it (descending) lets launchFirJobs leave the empty CTAs out
+int firJobTiles(const FirJob& j);
+void firJobsSortByTiles(FirJob* jobs, int nJobs);
+
 // Launchers (all jobs of one "level" in a single launch; grid.y = job index)
 // every job of a launch must have the same elemFloats; h_jobs is the host copy of d_jobs (grid and shared-memory sizing)
 int launchFirJobs(const FirJob* d_jobs, const FirJob* h_jobs, int nJobs, int elemFloats, cudaStream_t s);
