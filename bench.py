@@ -525,6 +525,17 @@ def run_gpu(args):
                           "ms_per_step": msd / kd, "steps": kd, "x_real_time": B * kd / (msd * 1e-3) / sr, "gpu_launches": ld}
             del jd
             torch.cuda.empty_cache()
+        # the headline bank with the rotators in EXACT mode (what the drop-in IQFrontEnd header runs: the reference's fp32 phase
+        # recursion replayed bit for bit, one thread per VFO walking the block) next to the FAST mode the headline is quoted on
+        je = Job(binding, torch, WORKLOAD, B, local, 0, 1, defer_tail=args.defer_tail)
+        je.fe.vfos.set_rotator_mode(binding.ROTATOR_EXACT)
+        ke = 3
+        mse, _, le = timed_run(je, ke, 1)
+        binding.profile_enable(False)
+        extra["cfg4_exact_rotator"] = {"workload": workload_text(WORKLOAD) + ", rotators in B200_ROTATOR_EXACT mode", "value": B * ke / (mse * 1e-3) / 1e6, "unit": UNIT,
+                                       "ms_per_step": mse / ke, "steps": ke, "x_real_time": B * ke / (mse * 1e-3) / sr, "gpu_launches": le}
+        del je
+        torch.cuda.empty_cache()
         for name, Bx, fused_name, fft_name in (("cfg2", 1 << 26, "fusedStreamKernel<512> (single-VFO variant, 16-byte staging)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)"),
                                                ("cfg3", 1 << 24, "fusedBankKernel<1024> (256 NFM VFOs)", "fftColsKernel + fftRowsKernel (65536 = 256 x 256)")):
             cx = configs.CONFIGS[name]

@@ -393,3 +393,30 @@ def test_deferred_tail_gives_identical_results(with_fft):
             assert b.out_count(vb) == len(blk)
     finally:
         b.set_option(binding.OPT_DEFER_TAIL, 0)
+
+
+def test_later_stage_jobs_sorted_by_length_launch_run_by_run_with_identical_results():
+    """launchFirJobs leaves the empty CTAs of a mixed launch out when its job list comes sorted by tile count: the list is
+    launched run by run (a run ends where the tile count falls below half of its first job's).  A bank whose VFOs were added
+    in descending output rate has such lists; the same VFOs added in a mixed order do not.  More launches, the same bits."""
+    from sdrplusplusbrown_b200 import binding
+    sr, n = 2.4e6, 1 << 20
+    groups = [(150e3, 50e3, 10), (24e3, 2.8e3, 10), (6e3, 2.4e3, 10)]
+    specs = [(out_sr, bw, -1.0e6 + 61e3 * (g * 10 + k) + 11.0) for g, (out_sr, bw, cnt) in enumerate(groups) for k in range(cnt)]
+    mixed = [specs[(i % 3) * 10 + i // 3] for i in range(len(specs))]
+    x = synth.make_iq(9, n, sr, sigma=0.05, tones=[(s[2] + 500.0, 0.02) for s in specs[::3]])
+    outs, launches = [], []
+    for order in (specs, mixed):
+        b = binding.VfoBank(sr, max_block=n)
+        b.set_rotator_mode(binding.ROTATOR_EXACT)
+        ids = {s: b.add(*s) for s in order}
+        b.process(to_dev(x[:1000]))                    # (tables, first-call allocations)
+        l0 = binding.lib.b200_launch_count()
+        b.process(to_dev(x))
+        launches.append(binding.lib.b200_launch_count() - l0)
+        outs.append({s: b.output(ids[s]) for s in specs})
+    assert launches[0] > launches[1], launches          # the sorted bank's levels went out in several runs
+    for s in specs:
+        a, c = outs[0][s], outs[1][s]
+        assert len(a) == len(c) > 0
+        assert np.array_equal(a.view(np.uint32), c.view(np.uint32)), s
