@@ -266,6 +266,34 @@ def run_reference(args):
                             % (n_v, len(vl), n_v, len(vl))}
         except Exception as e:       # the measurement is an extra: never fail the arm over it
             line["cpu_baseline"]["threaded_graph"] = {"unavailable": str(e)}
+    # the FFT branch on ONE thread, as the reference runs it (IQFrontEnd::handler on the FFT sink's thread,
+    # signal_path/iq_frontend.cpp:267-287: window, forward FFT, log power; then the waterfall's zoom and palette), with the
+    # oracle's FFT stand-in -- and numpy's pocketfft in float32 on the same windowed frame as a sanity comparison of the
+    # transform alone (FFTW itself is not installable here)
+    try:
+        nz, N, I = cpu.nz, cpu.N, cpu.interval
+        frame = np.resize(x, nz).astype(np.complex64)
+        reps = 2 if N >= (1 << 18) else 8
+        cpu.orc.fft_frame(frame, cpu.window, N)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            db = cpu.orc.fft_frame(frame, cpu.window, N)
+            cpu.orc.palette_indices(cpu.orc.do_zoom(0, N, db, DATA_WIDTH), WF_MIN, WF_MAX)
+        t_frame = (time.perf_counter() - t0) / reps
+        xw = np.zeros(N, np.complex64)
+        xw[:nz] = frame * np.asarray(cpu.window, np.float32)[:nz]
+        np.fft.fft(xw)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            y = np.fft.fft(xw)
+        t_np = (time.perf_counter() - t0) / reps
+        line["cpu_baseline"]["fft_branch"] = {
+            "ms_per_frame": 1e3 * t_frame, "frames_per_s": 1.0 / t_frame, "stream_rate_it_sustains": I / t_frame / 1e6, "unit": UNIT, "threads": 1,
+            "numpy_pocketfft_ms_per_transform": 1e3 * t_np, "numpy_dtype": str(y.dtype),
+            "what": "window + %d-point forward FFT (oracle's float64 stand-in for FFTW) + log power + zoom to %d px + palette on one thread; a frame every "
+                    "%d samples, so the branch alone keeps up with this stream rate; numpy: the bare transform of the same windowed frame" % (N, DATA_WIDTH, I)}
+    except Exception as e:
+        line["cpu_baseline"]["fft_branch"] = {"unavailable": str(e)}
     print(json.dumps(line))
 
 
