@@ -73,16 +73,21 @@ def err_loop(x, alpha, beta, lo, hi, phase, freq, chunk=512):
     return out, phase, freq, nfull
 def pdiff(a,b):
     d=np.abs(a.astype(np.float64)-b.astype(np.float64)); d=np.minimum(d,2*np.pi-d); return d
-sr=250e3
-alpha,beta=crit(25000.0/sr)
-lo=f32(2*np.pi*18750/sr); hi=f32(2*np.pi*19250/sr); f0=f32(2*np.pi*19000/sr)
-rng=np.random.default_rng(1)
-n=60000
-for name,amp,noise,fp in (("clean pilot",0.1,1e-4,19000.0),("noisy pilot",0.1,0.03,19000.0),("very noisy",0.1,0.2,19000.0),("no pilot",0.0,0.1,19000.0),("pilot off limits",0.1,1e-3,19600.0),("edge of limits",0.1,1e-2,19245.0)):
+SCENARIOS=(("clean pilot",0.1,1e-4,19000.0),("noisy pilot",0.1,0.03,19000.0),("very noisy",0.1,0.2,19000.0),("no pilot",0.0,0.1,19000.0),
+           ("pilot off limits",0.1,1e-3,19600.0),("edge of limits",0.1,1e-2,19245.0))
+def scenario(name,amp,noise,fp,n=60000,sr=250e3,seed=1):
+    """both walks over one synthetic pilot; returns (largest phase difference, chunks that needed the full walk, chunks, end-state differences)"""
+    alpha,beta=crit(25000.0/sr)
+    lo=f32(2*np.pi*18750/sr); hi=f32(2*np.pi*19250/sr); f0=f32(2*np.pi*19000/sr)
+    rng=np.random.default_rng(seed)
     t=np.arange(n)/sr
     z=amp*np.exp(1j*(2*np.pi*fp*t+0.7))+noise*(rng.standard_normal(n)+1j*rng.standard_normal(n))
     x=np.arctan2(z.imag.astype(np.float32),z.real.astype(np.float32)).astype(np.float32)
     a,pa,fa=ref_loop(x,alpha,beta,lo,hi,f32(0),f0)
     b,pb,fb,nfull=err_loop(x,alpha,beta,lo,hi,f32(0),f0)
     d=pdiff(a,b)
-    print("%-18s max phase diff %.3g rad (mean %.3g), at %d; full-walk chunks %d of %d; end state diff %.3g / %.3g" % (name,d.max(),d.mean(),int(d.argmax()),nfull,(n+511)//512,abs(float(pa)-float(pb)),abs(float(fa)-float(fb))))
+    return d, nfull, (n+511)//512, abs(float(pa)-float(pb)), abs(float(fa)-float(fb))
+if __name__ == "__main__":
+    for name,amp,noise,fp in SCENARIOS:
+        d,nfull,nch,dp,df=scenario(name,amp,noise,fp)
+        print("%-18s max phase diff %.3g rad (mean %.3g), at %d; full-walk chunks %d of %d; end state diff %.3g / %.3g" % (name,d.max(),d.mean(),int(d.argmax()),nfull,nch,dp,df))
